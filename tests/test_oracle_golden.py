@@ -1,0 +1,69 @@
+"""The oracle (oracle/mcaat_oracle.c) against the pins made from the UNMODIFIED reference:
+raw results of reference CycleFinder at threads=1 (src/cycle_finder.cpp:433-492) and the
+reference SDBG navigation API (libs/megahit/src/sdbg/sdbg.h:328-357)."""
+import numpy as np
+import pytest
+
+import golden_util as G
+import oracle_py as O
+
+_graphs = {}
+
+
+def graph(name):
+    if name not in _graphs:
+        _graphs[name] = G.load_graph_npz(name)
+    r = _graphs[name]
+    return O.OracleGraph.from_arrays(r["w"], r["last"], r["tip"], r["mult"], r["f"], r["k"])
+
+
+@pytest.mark.parametrize("name,thr,mn,mx,dump", G.cases(), ids=lambda v: str(v) if not isinstance(v, str) or "/" not in v else "")
+def test_oracle_matches_reference_dump(name, thr, mn, mx, dump):
+    ref = O.parse_dump(dump)
+    got = graph(name).run(thr, mn, mx)
+    assert O.same_run(ref, got) == []
+
+
+def test_oracle_navigation_matches_reference_api():
+    z = np.load(G.GOLD + "/tiny.nav.npz")
+    g = graph("tiny")
+    od, idg, o, i_ = g.nav_table()
+    assert np.array_equal(od, z["od"]) and np.array_equal(idg, z["id"])
+    assert np.array_equal(o.astype(np.int64), z["o"]) and np.array_equal(i_.astype(np.int64), z["i"])
+    assert np.array_equal(g.raw()["mult"], z["m"])
+
+
+def test_file_loader_matches_raw_arrays(tmp_path):
+    prefix = G.unpack_sdbg_files("tiny", str(tmp_path))
+    a = O.OracleGraph.load(prefix).raw()
+    b = G.load_graph_npz("tiny")
+    for key in ("w", "last", "tip", "mult", "f"):
+        assert np.array_equal(a[key], b[key]), key
+    assert a["k"] == b["k"] == 23
+
+
+def test_cluster_bound_case_is_exercised():
+    """biallelic: the 500-cycle cluster bound (cycle_finder.cpp:162-165) must fire in the pin."""
+    got = graph("biallelic").run(20, 27, 77)
+    assert got.stats["n_bound_hits"] >= 1 and got.stats["n_cap_hits"] >= 1
+
+
+def test_uset_order_model():
+    """libstdc++ unordered_set<uint64_t> iteration order (SURVEY §4.5 probe)."""
+    ids = np.array([1001, 1002, 1014, 27], np.uint64)
+    out = np.zeros(8, np.uint64)
+    n = O.lib().orc_uset_order(ids.ctypes.data, 4, out.ctypes.data)
+    assert list(out[:n]) == [27, 1002, 1014, 1001]
+
+
+def test_rank_select_edge_cases():
+    """kmrns.h:287-292,313-320 edge cases."""
+    g = graph("tiny")
+    L = O.lib()
+    n = g.n
+    assert L.orc_rank_last(g.h, n) == -1
+    assert L.orc_rank_last(g.h, -1) == 0
+    tot = L.orc_rank_last(g.h, n - 1)
+    assert L.orc_select_last(g.h, tot) == n
+    assert L.orc_select_last(g.h, tot + 1) == -1
+    assert L.orc_rank_last(g.h, L.orc_select_last(g.h, 5)) == 6

@@ -1,0 +1,104 @@
+#!/usr/bin/env python3
+"""Regenerates tests/golden/ (TEST INFRASTRUCTURE; needs /root/reference to have been compiled into
+oracle/_ref by `make -C oracle`).
+
+For each named case: seeded synthetic reads (tools/gen_reads.py) -> the reference's own SDBG builder
+(oracle/_ref/build_sdbg = reference src/sdbg_build.cpp + vendored MEGAHIT, unmodified) -> the
+UNMODIFIED reference CycleFinder at threads=1 (oracle/_ref/ref_cyclefinder) for each parameter set.
+Stored per case:
+  <case>.graph.npz      raw SDBG arrays (w nibbles packed 2/byte, last/tip bit-packed, mult u16, f[6], k)
+  <case>.<params>.dump.gz   the reference's dump (layout: oracle/ref_harness/dump_format.h)
+  <case>.nav.npz        (small cases) per-item degrees / neighbour ids through the reference SDBG API
+One case also keeps the on-disk MEGAHIT files (gzip'ed) to pin the file-format reader.
+"""
+import argparse
+import gzip
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import oracle_py as O  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+# name -> (gen_reads args, [(thr, min, max), ...], keep_nav, keep_files)
+CASES = {
+    "tiny": (["--seed", "1", "--genomes", "2", "--genome-len", "30000", "--arrays", "2",
+              "--spacers-min", "8", "--spacers-max", "12", "--pairs", "6000"],
+             [(20, 27, 77), (10, 20, 100)], True, True),
+    "repeatrich": (["--seed", "2", "--genomes", "1", "--genome-len", "60000", "--arrays", "6",
+                    "--spacers-min", "6", "--spacers-max", "14", "--shared-family-arrays", "4",
+                    "--tandem", "12", "--pairs", "9000", "--error-rate", "0.003"],
+                   [(20, 27, 77), (10, 20, 100), (5, 5, 120), (50, 27, 77)], False, False),
+    "biallelic": (["--seed", "3", "--genomes", "1", "--genome-len", "40000", "--arrays", "1",
+                   "--spacers-min", "150", "--spacers-max", "150", "--biallelic-arrays", "1",
+                   "--sites", "2", "--spacer-min-len", "38", "--pairs", "8000"],
+                  [(20, 27, 77)], False, False),
+    "strain": (["--seed", "4", "--genomes", "2", "--genome-len", "40000", "--arrays", "3",
+                "--spacers-min", "8", "--spacers-max", "16", "--strain-pairs", "2",
+                "--pairs", "16000", "--error-rate", "0.005"],
+               [(20, 27, 77), (10, 27, 77)], False, False),
+}
+
+
+def pack_graph(raw, path):
+    w = raw["w"]
+    if w.size % 2:
+        w = np.append(w, np.uint8(0))
+    w4 = (w[0::2] | (w[1::2] << 4)).astype(np.uint8)
+    np.savez_compressed(path, n=np.uint64(raw["w"].size), k=np.uint32(raw["k"]), w4=w4,
+                        last=np.packbits(raw["last"], bitorder="little"),
+                        tip=np.packbits(raw["tip"], bitorder="little"),
+                        mult=raw["mult"], f=raw["f"])
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("cases", nargs="*", default=list(CASES))
+    ap.add_argument("--keep-tmp", default=None)
+    a = ap.parse_args()
+    os.makedirs(GOLD, exist_ok=True)
+    for name in a.cases:
+        gen, params, keep_nav, keep_files = CASES[name]
+        tmp = a.keep_tmp and os.path.join(a.keep_tmp, name) or tempfile.mkdtemp(prefix="golden_")
+        os.makedirs(tmp, exist_ok=True)
+        subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_reads.py"), "--out", tmp] + gen, check=True)
+        gdir = os.path.join(tmp, "gdir")
+        subprocess.run([O.ref_binary("build_sdbg"), f"{tmp}/r1.fq {tmp}/r2.fq", gdir, "4", "4e9"],
+                       check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        prefix = os.path.join(gdir, "graph")
+        g = O.OracleGraph.load(prefix)
+        pack_graph(g.raw(), os.path.join(GOLD, f"{name}.graph.npz"))
+        print(f"{name}: n_items={g.n}")
+        for thr, mn, mx in params:
+            dump = os.path.join(tmp, "out.dump")
+            info, _ = O.run_reference(prefix, dump, 1, thr, mn, mx)
+            with open(dump, "rb") as fi, gzip.GzipFile(os.path.join(GOLD, f"{name}.t{thr}_{mn}_{mx}.dump.gz"), "wb", mtime=0) as fo:
+                shutil.copyfileobj(fi, fo)
+            print("   ", (thr, mn, mx), info)
+        if keep_nav:
+            nav = os.path.join(tmp, "out.nav")
+            subprocess.run([O.ref_binary("ref_cyclefinder"), "--nav", prefix, nav], check=True)
+            rec = np.dtype([("od", "i1"), ("id", "i1"), ("m", "<u2"), ("o", "<u8", 4), ("i", "<u8", 4)])
+            t = np.fromfile(nav, dtype=rec, offset=16)
+            np.savez_compressed(os.path.join(GOLD, f"{name}.nav.npz"), od=t["od"], id=t["id"], m=t["m"],
+                                o=t["o"].astype(np.int64), i=t["i"].astype(np.int64))
+        if keep_files:
+            fd = os.path.join(GOLD, f"{name}.sdbg")
+            os.makedirs(fd, exist_ok=True)
+            for fn in sorted(os.listdir(gdir)):
+                if fn.startswith("graph.sdbg"):
+                    with open(os.path.join(gdir, fn), "rb") as fi, gzip.GzipFile(os.path.join(fd, fn + ".gz"), "wb", mtime=0) as fo:
+                        shutil.copyfileobj(fi, fo)
+        if not a.keep_tmp:
+            shutil.rmtree(tmp)
+
+
+if __name__ == "__main__":
+    main()
