@@ -1,0 +1,168 @@
+/* libmcaat_gpu — C ABI of the B200-native (CUDA sm_100a) implementation of MCAAT's bounded-length
+ * multicycle search.  This is the drop-in boundary: the C++ `CycleFinder` shim
+ * (mcaat_b200/host/cycle_finder_gpu.cpp) and the Python binding (mcaat_b200/gpu.py) call only
+ * these entry points.  Plain pointers and sizes; no exceptions, no STL, no torch types.
+ *
+ * The reference has no FFI of its own: the interface replaced is the C++ class
+ * `CycleFinder` (reference include/cycle_finder.h:25-85) and the MEGAHIT `SDBG` navigation API it
+ * calls (reference libs/megahit/src/sdbg/sdbg.h:63-121,245-370).  Each entry point below cites the
+ * reference code whose behaviour it reproduces bit-exactly.
+ *
+ * Conventions: every function returns 0 on success or a negative MG_E* code (mg_last_error() gives
+ * the text); all calls are blocking; a handle is used from one thread at a time; output arrays
+ * that the library allocates are released with mg_free().  Node ids are uint64_t at the ABI
+ * (as in the reference) and must be < 2^32 - 1 items per graph (the reference itself is only
+ * well defined below 2^31, reference src/cycle_finder.cpp:192-199).
+ * There is NO CPU fallback: without a CUDA device every compute entry fails with MG_ECUDA.
+ */
+#ifndef MCAAT_GPU_H
+#define MCAAT_GPU_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MG_OK 0
+#define MG_EINVAL (-1)   /* bad argument */
+#define MG_ECUDA (-2)    /* CUDA runtime error / no device */
+#define MG_ENOMEM (-3)   /* host or device allocation failed */
+#define MG_ELIMIT (-4)   /* graph or parameter outside the supported range */
+#define MG_EINTERNAL (-5)
+
+#define MG_MEM_HOST 0
+#define MG_MEM_DEVICE 1
+
+typedef struct mg_graph mg_graph;
+
+/* Raw SDBG arrays in MEGAHIT's in-memory packing (reference
+ * libs/megahit/src/sdbg/sdbg_raw_content.h:16-26, kmlib/kmcompactvector.h:53-58):
+ *   w        4-bit edge labels, 16 per uint64 word, item i in bits [4*(i%16), 4*(i%16)+4) of word i/16
+ *   last/tip 1 bit per item, item i = bit i%64 of word i/64
+ *   invalid  optional initial invalid bitmap (same packing); NULL => tip | (w==0)
+ *            (reference sdbg.h:34,56-60)
+ *   mult16   uint16 multiplicity per item, or NULL in which case mult8 (sentinel 255) plus the
+ *            id-sorted (large_ids, large_vals) table is used (reference sdbg.h:96-105)
+ *   f        character-class boundaries f_[0..5] (reference sdbg.h:36-50)
+ * With memory == MG_MEM_DEVICE all array pointers are device pointers on `device` (this is the
+ * path used after an NCCL broadcast of the raw arrays); the library copies what it needs. */
+typedef struct {
+  uint64_t n_items;
+  uint32_t k;
+  int32_t memory;
+  int32_t device;
+  int32_t reserved;
+  const uint64_t *w;
+  const uint64_t *last;
+  const uint64_t *tip;
+  const uint64_t *invalid;
+  const uint16_t *mult16;
+  const uint8_t *mult8;
+  const uint64_t *large_ids;
+  const uint16_t *large_vals;
+  uint64_t n_large;
+  int64_t f[6];
+} mg_graph_desc;
+
+/* Upload + build the device-resident succinct graph (replaces SDBG::LoadFromFile's index
+ * construction, reference sdbg.h:26-61 and kmlib/kmrns.h:122-167). */
+int mg_graph_create(const mg_graph_desc *desc, mg_graph **out);
+void mg_graph_destroy(mg_graph *g);
+/* Restore the invalid bitmap to its state at creation and clear `visited` (lets one resident
+ * graph be searched repeatedly with different parameters). */
+int mg_graph_reset(mg_graph *g);
+uint64_t mg_graph_size(const mg_graph *g);
+/* bytes of device memory held by the resident graph (arrays + rank/select samples) */
+uint64_t mg_graph_device_bytes(const mg_graph *g);
+
+/* SDBG navigation for items [first, first+count): EdgeOutdegree / EdgeIndegree / OutgoingEdges /
+ * IncomingEdges / EdgeMultiplicity of reference sdbg.h:328-357,96-105 evaluated on the CURRENT
+ * invalid bitmap.  Host output arrays; out_ids/in_ids are [count][4], unused slots = UINT64_MAX;
+ * any output pointer may be NULL. */
+int mg_navigate(mg_graph *g, uint64_t first, uint64_t count, int8_t *outdeg, int8_t *indeg,
+                uint64_t *out_ids, uint64_t *in_ids, uint16_t *mult);
+
+/* Graph pruning: CollectTips -> InvalidateMultiplicityOneNodes -> RecursiveReduction per tip ->
+ * valid-edge count -> CollectTips (reference src/cycle_finder.cpp:436-452). */
+typedef struct {
+  uint64_t n_tips_before; /* "gathered tips" (:437) */
+  uint64_t n_mult1;       /* "Pre-filter: invalidated" (:381) */
+  uint64_t n_tips_after;  /* "After pruning, tips" (:452) */
+  uint64_t n_valid;       /* "valid edges" (:452) */
+  uint64_t n_peeled;      /* nodes invalidated by the reduction itself */
+} mg_prune_stats;
+int mg_prune(mg_graph *g, mg_prune_stats *stats);
+
+/* Current invalid bitmap -> host words ((n+63)/64 uint64), for write-back into the host SDBG
+ * (reference SetInvalidEdge, sdbg.h:94). */
+int mg_invalid_readback(mg_graph *g, uint64_t *host_words);
+
+/* Candidate start nodes: valid AND indegree >= 2 AND multiplicity > threshold AND no self-loop
+ * incoming edge (reference src/cycle_finder.cpp:398-408), ascending ids.  *ids is library
+ * allocated (mg_free). */
+int mg_candidates(mg_graph *g, uint64_t threshold_multiplicity, uint64_t **ids, uint64_t *n);
+
+/* DepthLevelSearch(node, node, limit) for each given node (reference src/cycle_finder.cpp:248-343);
+ * pass[i] = 1/0.  expansions (optional) receives the number of expanded nodes. */
+int mg_dls(mg_graph *g, const uint64_t *ids, uint64_t n, int limit, uint8_t *pass, uint64_t *expansions);
+
+/* ChunkStartNodes at threads=1 (reference src/cycle_finder.cpp:387-427): candidates, admission
+ * search, bucketing by ceil(log2(multiplicity)); buckets in descending key order, ascending ids
+ * inside a bucket. */
+typedef struct {
+  uint64_t n_candidates;
+  uint64_t n_starts;
+  uint64_t n_buckets;
+  int64_t *bucket_key;  /* [n_buckets] descending */
+  uint64_t *bucket_off; /* [n_buckets+1] offsets into start_ids */
+  uint64_t *start_ids;  /* [n_starts] */
+  uint64_t dls_expansions;
+} mg_starts;
+int mg_select_starts(mg_graph *g, uint64_t threshold_multiplicity, int max_len, mg_starts *out);
+/* Same bucketing for an externally supplied set of admitted nodes (multi-GPU: every rank ran
+ * mg_dls on its shard of the candidates). */
+int mg_bucket_starts(mg_graph *g, const uint64_t *ids, uint64_t n, mg_starts *out);
+void mg_starts_free(mg_starts *s);
+
+/* Per-start bounded multicycle enumeration with the sequential `visited` coupling of the
+ * reference driver loop (reference src/cycle_finder.cpp:468-487, FindCycleUtil :231-243,
+ * FindCycle :140-225): start nodes are taken in the given order; a start already marked visited
+ * is skipped; results hold the raw per-start cycle sequence (emission order and duplicates). */
+typedef struct {
+  uint64_t n_searched;      /* entries of `results`, in insertion order */
+  uint64_t *searched_start; /* [n_searched] */
+  uint64_t *cyc_off;        /* [n_searched+1] offsets into the cycle list */
+  uint64_t n_cycles;
+  uint64_t *node_off;       /* [n_cycles+1] offsets into nodes */
+  uint64_t *nodes;
+  uint64_t n_skipped;       /* starts skipped because already visited (:476) */
+  uint64_t n_bound_hits;    /* searches cleared by the 500-cycle cluster bound (:162-165) */
+  uint64_t n_cap_hits;      /* searches stopped by the 10 000 000-step cap (:148-151) */
+  uint64_t n_reruns;        /* speculative searches repeated after an ordered-commit conflict */
+  uint64_t n_rounds;        /* speculation windows launched */
+  uint64_t expansions;      /* _GetOutgoings/_GetIncomings evaluations of committed searches */
+} mg_cycles;
+int mg_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len, int max_len, mg_cycles *out);
+void mg_cycles_free(mg_cycles *c);
+
+/* Multi-GPU support: mark nodes visited / read the visited bitmap, so that ranks that ran
+ * disjoint parts of the start list can exchange their commits. */
+int mg_visited_readback(mg_graph *g, uint64_t *host_words);
+
+/* Device timers: CUDA-event time (ms) and launch count accumulated per kernel family since the
+ * last mg_timers_reset().  names[i] are static strings.  Returns the number of entries written
+ * (<= cap). */
+int mg_timers(mg_graph *g, const char **names, double *ms, uint64_t *launches, uint64_t *units, int cap);
+void mg_timers_reset(mg_graph *g);
+/* kernels launched by this library in this process so far */
+uint64_t mg_launch_count(void);
+
+void mg_free(void *p);
+const char *mg_last_error(void);
+const char *mg_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,278 @@
+// C ABI of libmcaat_gpu (include/mcaat_gpu.h).  No CPU fallback: without a CUDA device every
+// compute entry returns MG_ECUDA.
+#include <stdarg.h>
+
+#include "common.cuh"
+#include "search_dev.cuh"
+
+namespace mg {
+
+static thread_local char g_err[512] = "";
+unsigned long long g_launches = 0;
+const char *kTimerNames[T_COUNT] = {"build_index", "collect_tips", "invalidate_mult1", "peel",      "nav_cache",
+                                    "candidates",  "dls",          "enumerate",        "commit",    "navigate"};
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+}
+
+void flush_timers(mg_graph *g) {
+  for (auto &p : g->pending) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) g->t_ms[p.id] += ms;
+    g->event_pool.push_back(p.a);
+    g->event_pool.push_back(p.b);
+  }
+  g->pending.clear();
+}
+
+static int upload_ids(mg_graph *g, const uint64_t *ids, uint64_t n, DevBuf &dev) {
+  std::vector<uint32_t> v(n);
+  for (uint64_t i = 0; i < n; ++i) {
+    if (ids[i] >= g->view.n) {
+      set_error("node id %llu out of range (graph has %llu items)", (unsigned long long)ids[i],
+                (unsigned long long)g->view.n);
+      return MG_EINVAL;
+    }
+    v[i] = (uint32_t)ids[i];
+  }
+  MG_TRY(dev.alloc(n * 4 + 16));
+  if (n) MG_CUDA(cudaMemcpy(dev.p, v.data(), n * 4, cudaMemcpyHostToDevice));
+  return MG_OK;
+}
+
+}  // namespace mg
+
+using namespace mg;
+
+#define MG_CHECK_HANDLE(g)                   \
+  do {                                       \
+    if (!(g)) {                              \
+      set_error("null graph handle");        \
+      return MG_EINVAL;                      \
+    }                                        \
+    cudaError_t e__ = cudaSetDevice((g)->device); \
+    if (e__ != cudaSuccess) {                \
+      set_error("cudaSetDevice(%d) -> %s", (g)->device, cudaGetErrorString(e__)); \
+      return MG_ECUDA;                       \
+    }                                        \
+  } while (0)
+
+extern "C" {
+
+const char *mg_last_error(void) { return g_err; }
+const char *mg_version(void) { return "mcaat_b200 libmcaat_gpu 0.1 (sm_100a)"; }
+uint64_t mg_launch_count(void) { return g_launches; }
+void mg_free(void *p) { free(p); }
+
+int mg_graph_create(const mg_graph_desc *d, mg_graph **out) {
+  if (!d || !out) { set_error("mg_graph_create: null argument"); return MG_EINVAL; }
+  *out = nullptr;
+  if (!d->w || !d->last || !d->tip) { set_error("mg_graph_create: w/last/tip are required"); return MG_EINVAL; }
+  if (d->n_items >= 0xFFFFFFFFull) {
+    set_error("mg_graph_create: %llu items; this build addresses < 2^32-1 items per graph",
+              (unsigned long long)d->n_items);
+    return MG_ELIMIT;
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    set_error("no CUDA device available (%s); libmcaat_gpu has no CPU fallback",
+              e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    return MG_ECUDA;
+  }
+  if (d->device < 0 || d->device >= ndev) { set_error("mg_graph_create: device %d of %d", d->device, ndev); return MG_EINVAL; }
+  MG_CUDA(cudaSetDevice(d->device));
+  mg_graph *g = new (std::nothrow) mg_graph();
+  if (!g) return MG_ENOMEM;
+  g->device = d->device;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, d->device) == cudaSuccess) g->sm_count = prop.multiProcessorCount;
+  if (cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    set_error("cudaStreamCreate failed");
+    delete g;
+    return MG_ECUDA;
+  }
+  int r = build_graph(g, d);
+  if (r != MG_OK) { mg_graph_destroy(g); return r; }
+  flush_timers(g);
+  *out = g;
+  return MG_OK;
+}
+
+void mg_graph_destroy(mg_graph *g) {
+  if (!g) return;
+  cudaSetDevice(g->device);
+  if (g->stream) cudaStreamSynchronize(g->stream);
+  flush_timers(g);
+  for (auto e : g->event_pool) cudaEventDestroy(e);
+  if (g->stream) cudaStreamDestroy(g->stream);
+  delete g;
+}
+
+int mg_graph_reset(mg_graph *g) {
+  MG_CHECK_HANDLE(g);
+  return reset_graph(g);
+}
+uint64_t mg_graph_size(const mg_graph *g) { return g ? g->view.n : 0; }
+uint64_t mg_graph_device_bytes(const mg_graph *g) { return g ? g->device_bytes + g->adj.bytes : 0; }
+
+int mg_navigate(mg_graph *g, uint64_t first, uint64_t count, int8_t *outdeg, int8_t *indeg, uint64_t *out_ids,
+                uint64_t *in_ids, uint16_t *mult) {
+  MG_CHECK_HANDLE(g);
+  if (first + count > g->view.n) { set_error("mg_navigate: range past the end"); return MG_EINVAL; }
+  if (count == 0) return MG_OK;
+  return run_navigate(g, first, count, outdeg, indeg, out_ids, in_ids, mult);
+}
+
+int mg_prune(mg_graph *g, mg_prune_stats *stats) {
+  MG_CHECK_HANDLE(g);
+  mg_prune_stats tmp;
+  return run_prune(g, stats ? stats : &tmp);
+}
+
+__global__ void k_inv_words(uint64_t n_fblocks, const FBlock *fb, uint64_t *out) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_fblocks * 4) out[i] = fb[i >> 2].inv[i & 3];
+}
+
+int mg_invalid_readback(mg_graph *g, uint64_t *host_words) {
+  MG_CHECK_HANDLE(g);
+  if (!host_words) return MG_EINVAL;
+  const uint64_t nb = g->view.n_fblocks;
+  if (!nb) return MG_OK;
+  DevBuf tmp;
+  MG_TRY(tmp.alloc(nb * 32));
+  MG_LAUNCH(k_inv_words, (unsigned)((nb * 4 + 255) / 256), 256, 0, g->stream, nb, g->fb.as<FBlock>(), tmp.as<uint64_t>());
+  MG_CUDA(cudaMemcpyAsync(host_words, tmp.p, (size_t)((g->view.n + 63) / 64) * 8, cudaMemcpyDeviceToHost, g->stream));
+  MG_CUDA(cudaStreamSynchronize(g->stream));
+  return MG_OK;
+}
+
+int mg_visited_readback(mg_graph *g, uint64_t *host_words) {
+  MG_CHECK_HANDLE(g);
+  if (!host_words) return MG_EINVAL;
+  if (!g->view.n) return MG_OK;
+  size_t bytes = (size_t)((g->view.n + 31) / 32) * 4;
+  host_words[(g->view.n + 63) / 64 - 1] = 0;
+  MG_CUDA(cudaMemcpy(host_words, g->visited.p, bytes, cudaMemcpyDeviceToHost));
+  return MG_OK;
+}
+
+int mg_candidates(mg_graph *g, uint64_t thr, uint64_t **ids, uint64_t *n) {
+  MG_CHECK_HANDLE(g);
+  if (!ids || !n) return MG_EINVAL;
+  *ids = nullptr;
+  *n = 0;
+  DevBuf dev;
+  uint64_t cnt = 0;
+  MG_TRY(run_candidates(g, thr, dev, &cnt));
+  std::vector<uint32_t> h(cnt);
+  if (cnt) MG_CUDA(cudaMemcpy(h.data(), dev.p, cnt * 4, cudaMemcpyDeviceToHost));
+  uint64_t *o = (uint64_t *)malloc((cnt + 1) * 8);
+  if (!o) return MG_ENOMEM;
+  for (uint64_t i = 0; i < cnt; ++i) o[i] = h[i];
+  *ids = o;
+  *n = cnt;
+  return MG_OK;
+}
+
+int mg_dls(mg_graph *g, const uint64_t *ids, uint64_t n, int limit, uint8_t *pass, uint64_t *expansions) {
+  MG_CHECK_HANDLE(g);
+  if (n && (!ids || !pass)) return MG_EINVAL;
+  DevBuf dev;
+  MG_TRY(upload_ids(g, ids, n, dev));
+  return run_dls(g, dev.as<uint32_t>(), n, limit, pass, expansions);
+}
+
+int mg_select_starts(mg_graph *g, uint64_t thr, int max_len, mg_starts *out) {
+  MG_CHECK_HANDLE(g);
+  if (!out) return MG_EINVAL;
+  memset(out, 0, sizeof *out);
+  DevBuf cand;
+  uint64_t nc = 0;
+  MG_TRY(run_candidates(g, thr, cand, &nc));
+  std::vector<uint8_t> pass(nc);
+  uint64_t exp = 0;
+  MG_TRY(run_dls(g, cand.as<uint32_t>(), nc, max_len, pass.data(), &exp));
+  std::vector<uint32_t> h(nc);
+  std::vector<uint16_t> hm;
+  if (nc) MG_CUDA(cudaMemcpy(h.data(), cand.p, nc * 4, cudaMemcpyDeviceToHost));
+  MG_TRY(gather_mult(g, cand.as<uint32_t>(), nc, hm));
+  std::vector<uint64_t> ids;
+  std::vector<uint16_t> mult;
+  for (uint64_t i = 0; i < nc; ++i)
+    if (pass[i]) { ids.push_back(h[i]); mult.push_back(hm[i]); }
+  int r = bucket_on_host(ids, mult, out);
+  out->n_candidates = nc;
+  out->dls_expansions = exp;
+  if (r != MG_OK) mg_starts_free(out);
+  return r;
+}
+
+int mg_bucket_starts(mg_graph *g, const uint64_t *ids, uint64_t n, mg_starts *out) {
+  MG_CHECK_HANDLE(g);
+  if (!out || (n && !ids)) return MG_EINVAL;
+  memset(out, 0, sizeof *out);
+  DevBuf dev;
+  MG_TRY(upload_ids(g, ids, n, dev));
+  std::vector<uint16_t> hm;
+  MG_TRY(gather_mult(g, dev.as<uint32_t>(), n, hm));
+  std::vector<uint64_t> v(ids, ids + n);
+  int r = bucket_on_host(v, hm, out);
+  if (r != MG_OK) mg_starts_free(out);
+  return r;
+}
+
+void mg_starts_free(mg_starts *s) {
+  if (!s) return;
+  free(s->bucket_key);
+  free(s->bucket_off);
+  free(s->start_ids);
+  memset(s, 0, sizeof *s);
+}
+
+int mg_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len, int max_len, mg_cycles *out) {
+  MG_CHECK_HANDLE(g);
+  if (!out || (n && !starts)) return MG_EINVAL;
+  memset(out, 0, sizeof *out);
+  int r = run_find_cycles(g, starts, n, min_len, max_len, out);
+  if (r != MG_OK) mg_cycles_free(out);
+  return r;
+}
+
+void mg_cycles_free(mg_cycles *c) {
+  if (!c) return;
+  free(c->searched_start);
+  free(c->cyc_off);
+  free(c->node_off);
+  free(c->nodes);
+  memset(c, 0, sizeof *c);
+}
+
+int mg_timers(mg_graph *g, const char **names, double *ms, uint64_t *launches, uint64_t *units, int cap) {
+  if (!g) return 0;
+  cudaSetDevice(g->device);
+  cudaStreamSynchronize(g->stream);
+  flush_timers(g);
+  int n = cap < (int)T_COUNT ? cap : (int)T_COUNT;
+  for (int i = 0; i < n; ++i) {
+    if (names) names[i] = kTimerNames[i];
+    if (ms) ms[i] = g->t_ms[i];
+    if (launches) launches[i] = g->t_launches[i];
+    if (units) units[i] = g->t_units[i];
+  }
+  return n;
+}
+void mg_timers_reset(mg_graph *g) {
+  if (!g) return;
+  cudaSetDevice(g->device);
+  cudaStreamSynchronize(g->stream);
+  flush_timers(g);
+  for (int i = 0; i < (int)T_COUNT; ++i) { g->t_ms[i] = 0; g->t_launches[i] = 0; g->t_units[i] = 0; }
+}
+
+}  // extern "C"

@@ -1,0 +1,168 @@
+// Host-side plumbing shared by the .cu files of libmcaat_gpu: error handling, device buffers,
+// the graph handle, kernel-family timers and the launch counter.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/mcaat_gpu.h"
+#include "sdbg_dev.cuh"
+
+namespace mg {
+
+void set_error(const char *fmt, ...);
+extern unsigned long long g_launches;
+
+#define MG_CUDA(call)                                                                      \
+  do {                                                                                     \
+    cudaError_t e__ = (call);                                                              \
+    if (e__ != cudaSuccess) {                                                              \
+      mg::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+      return MG_ECUDA;                                                                     \
+    }                                                                                      \
+  } while (0)
+#define MG_TRY(call)          \
+  do {                        \
+    int r__ = (call);         \
+    if (r__ != MG_OK) return r__; \
+  } while (0)
+
+// every kernel launch of the library goes through this macro (launch counter + error check)
+#define MG_LAUNCH(kernel, grid, block, smem, stream, ...)                     \
+  do {                                                                        \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);               \
+    ++mg::g_launches;                                                         \
+    cudaError_t e__ = cudaGetLastError();                                     \
+    if (e__ != cudaSuccess) {                                                 \
+      mg::set_error("%s:%d: launch %s -> %s", __FILE__, __LINE__, #kernel, cudaGetErrorString(e__)); \
+      return MG_ECUDA;                                                        \
+    }                                                                         \
+  } while (0)
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t bytes = 0;
+  DevBuf() = default;
+  DevBuf(const DevBuf &) = delete;
+  DevBuf &operator=(const DevBuf &) = delete;
+  ~DevBuf() { release(); }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+  }
+  int alloc(size_t b) {
+    release();
+    if (b == 0) b = 16;
+    cudaError_t e = cudaMalloc(&p, b);
+    if (e != cudaSuccess) {
+      p = nullptr;
+      set_error("cudaMalloc(%zu) -> %s", b, cudaGetErrorString(e));
+      return MG_ENOMEM;
+    }
+    bytes = b;
+    return MG_OK;
+  }
+  // grow-only
+  int ensure(size_t b) { return b <= bytes ? MG_OK : alloc(b); }
+  template <class T> T *as() const { return (T *)p; }
+};
+
+enum TimerId {
+  T_BUILD = 0,     // index construction
+  T_TIPS,          // CollectTips scans
+  T_MULT1,         // InvalidateMultiplicityOneNodes
+  T_PEEL,          // RecursiveReduction
+  T_ADJ,           // navigation cache + tips-after + valid count
+  T_CAND,          // candidate predicate + compaction
+  T_DLS,           // DepthLevelSearch
+  T_ENUM,          // FindCycle searches
+  T_COMMIT,        // ordered commit + gather
+  T_NAV,           // mg_navigate (diagnostic)
+  T_COUNT
+};
+extern const char *kTimerNames[T_COUNT];
+
+}  // namespace mg
+
+// The opaque handle of the C ABI.
+struct mg_graph {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  mg::GraphView view{};  // pointers below
+  mg::DevBuf wb, fb, mult, hints, inv0;
+  mg::DevBuf adj;        // navigation cache (built by mg_prune)
+  mg::DevBuf visited;    // n bits, uint32 words
+  bool pruned = false;
+  uint64_t device_bytes = 0;
+  int sm_count = 148;
+  // timers
+  double t_ms[mg::T_COUNT] = {0};
+  uint64_t t_launches[mg::T_COUNT] = {0};
+  uint64_t t_units[mg::T_COUNT] = {0};
+  struct Pending { int id; cudaEvent_t a, b; };
+  std::vector<Pending> pending;
+  std::vector<cudaEvent_t> event_pool;
+};
+
+namespace mg {
+
+// Records CUDA events on the graph's stream around a group of launches of one kernel family.
+struct TimedScope {
+  mg_graph *g;
+  int id;
+  cudaEvent_t a = nullptr, b = nullptr;
+  unsigned long long launches0;
+  TimedScope(mg_graph *g_, int id_, uint64_t units = 0) : g(g_), id(id_), launches0(g_launches) {
+    a = get();
+    b = get();
+    if (a) cudaEventRecord(a, g->stream);
+    g->t_units[id] += units;
+  }
+  ~TimedScope() {
+    if (b) cudaEventRecord(b, g->stream);
+    g->t_launches[id] += g_launches - launches0;
+    if (a && b) g->pending.push_back({id, a, b});
+  }
+  cudaEvent_t get() {
+    if (!g->event_pool.empty()) {
+      cudaEvent_t e = g->event_pool.back();
+      g->event_pool.pop_back();
+      return e;
+    }
+    cudaEvent_t e = nullptr;
+    if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+    return e;
+  }
+};
+// call after the stream has been synchronised
+void flush_timers(mg_graph *g);
+
+// in-place exclusive prefix sum over n uint32 values; *total (device pointer, may be null)
+// receives the grand total.  scan.cu
+int exclusive_scan_u32(uint32_t *data, size_t n, uint32_t *total_dev, cudaStream_t stream);
+// ascending list of set bit positions of a bitmap of n bits (uint32 words); allocates *out_ids
+// (device) and writes the count to *count.  scan.cu
+int bitmap_to_ids(const uint32_t *bits, uint64_t n, DevBuf &out_ids, uint64_t *count, cudaStream_t stream);
+
+// graph_build.cu
+int build_graph(mg_graph *g, const mg_graph_desc *d);
+int reset_graph(mg_graph *g);
+// prune.cu
+int run_prune(mg_graph *g, mg_prune_stats *st);
+int run_navigate(mg_graph *g, uint64_t first, uint64_t count, int8_t *outdeg, int8_t *indeg, uint64_t *out_ids,
+                 uint64_t *in_ids, uint16_t *mult);
+// starts.cu
+int run_candidates(mg_graph *g, uint64_t thr, DevBuf &ids, uint64_t *n);
+int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t *pass_host, uint64_t *expansions);
+int bucket_on_host(const std::vector<uint64_t> &ids, const std::vector<uint16_t> &mult, mg_starts *out);
+int gather_mult(mg_graph *g, const uint32_t *ids_dev, uint64_t n, std::vector<uint16_t> &out);
+// enumerate.cu
+int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len, int max_len, mg_cycles *out);
+
+}  // namespace mg

@@ -1,0 +1,197 @@
+// K1-K3 + navigation cache: graph pruning of reference src/cycle_finder.cpp:436-452
+// (CollectTips :346-357, InvalidateMultiplicityOneNodes :372-382, RecursiveReduction :359-371),
+// and the diagnostic navigation table (reference sdbg.h:328-357).
+#include "common.cuh"
+#include "search_dev.cuh"
+
+namespace mg {
+
+static inline unsigned grid_for(uint64_t n, int block) { return (unsigned)((n + block - 1) / block); }
+
+// CollectTips: bit i of `bits` = valid(i) && outdegree(i) == 0.  One thread per item; a warp
+// covers 32 consecutive items = one bitmap word.
+__global__ void k_tips(GraphView g, uint32_t *bits, unsigned long long *count) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool tip = false;
+  if (i < g.n) tip = outgoing(g, (uint32_t)i, nullptr) == 0;
+  unsigned m = __ballot_sync(0xffffffffu, tip);
+  if ((threadIdx.x & 31) == 0 && i < g.n) {
+    bits[i >> 5] = m;
+    if (m) atomicAdd(count, (unsigned long long)__popc(m));
+  }
+}
+// InvalidateMultiplicityOneNodes: every item with multiplicity <= 1 becomes invalid; the count
+// includes items that were invalid already, like the reference's counter.
+__global__ void k_mult1(GraphView g, unsigned long long *count) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool low = i < g.n && g.mult[i] <= 1;
+  unsigned m = __ballot_sync(0xffffffffu, low);
+  if ((threadIdx.x & 31) == 0 && m) {
+    uint32_t *w32 = (uint32_t *)&g.fb[i >> 8].inv[(i >> 6) & 3] + ((i >> 5) & 1);
+    atomicOr(w32, m);
+    atomicAdd(count, (unsigned long long)__popc(m));
+  }
+}
+// RecursiveReduction: one thread per work item follows its chain with a small private stack;
+// parents that do not fit go to the next work list.
+constexpr int kPeelLocal = 24;
+__global__ void k_peel(GraphView g, const uint32_t *work, uint32_t n_work, uint32_t *next, uint32_t *next_count,
+                       uint32_t next_cap, unsigned long long *peeled, int *overflow) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t cnt = 0;
+  if (i < n_work) {
+    uint32_t lst[kPeelLocal];
+    int sp = 0;
+    lst[sp++] = work[i];
+    while (sp) {
+      uint32_t v = lst[--sp];
+      cnt += peel_one(g, v, [&](uint32_t p) {
+        if (sp < kPeelLocal) {
+          lst[sp++] = p;
+        } else {
+          uint32_t idx = atomicAdd(next_count, 1u);
+          if (idx < next_cap) next[idx] = p;
+          else *overflow = 1;
+        }
+      });
+    }
+  }
+  for (int d = 16; d; d >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, d);
+  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(peeled, (unsigned long long)cnt);
+}
+// navigation cache + "After pruning" statistics (:443-452): valid count and tips
+__global__ void k_adj(GraphView g, uint64_t *adj, unsigned long long *n_valid, unsigned long long *n_tips) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool valid = false, tip = false;
+  if (i < g.n) {
+    valid = !get_inv(g, (uint32_t)i);
+    uint64_t a = adj_encode(g, (uint32_t)i);
+    adj[i] = a;
+    tip = valid && (a >> 32) == 0;
+  }
+  unsigned mv = __ballot_sync(0xffffffffu, valid), mt = __ballot_sync(0xffffffffu, tip);
+  if ((threadIdx.x & 31) == 0) {
+    if (mv) atomicAdd(n_valid, (unsigned long long)__popc(mv));
+    if (mt) atomicAdd(n_tips, (unsigned long long)__popc(mt));
+  }
+}
+
+int run_prune(mg_graph *g, mg_prune_stats *st) {
+  GraphView &v = g->view;
+  cudaStream_t s = g->stream;
+  const uint64_t n = v.n;
+  memset(st, 0, sizeof *st);
+  DevBuf counters;  // [0] tips before, [1] mult1, [2] peeled, [3] valid, [4] tips after, [5] next_count(u32), [6] overflow
+  MG_TRY(counters.alloc(8 * 8));
+  MG_CUDA(cudaMemsetAsync(counters.p, 0, 64, s));
+  unsigned long long *c = counters.as<unsigned long long>();
+  const unsigned grid = grid_for(n, 256);
+  // --- CollectTips on the loaded graph (:436)
+  DevBuf tipbits, work, next;
+  uint64_t n_work = 0;
+  MG_TRY(tipbits.alloc((size_t)((n + 31) / 32) * 4 + 16));
+  if (n) {
+    TimedScope ts(g, T_TIPS, n);
+    MG_LAUNCH(k_tips, grid, 256, 0, s, v, tipbits.as<uint32_t>(), c + 0);
+  }
+  MG_TRY(bitmap_to_ids(tipbits.as<uint32_t>(), n, work, &n_work, s));
+  tipbits.release();
+  // --- InvalidateMultiplicityOneNodes (:439)
+  if (n) {
+    TimedScope ts(g, T_MULT1, n);
+    MG_LAUNCH(k_mult1, grid, 256, 0, s, v, c + 1);
+  }
+  // --- RecursiveReduction for every tip (:440-442)
+  {
+    TimedScope ts(g, T_PEEL, n_work);
+    uint32_t next_cap = (uint32_t)(n < (1u << 20) ? (1u << 20) : n);
+    uint32_t *next_count = (uint32_t *)(c + 5);
+    int *overflow = (int *)(c + 6);
+    MG_TRY(next.alloc((size_t)next_cap * 4));
+    while (n_work) {
+      MG_CUDA(cudaMemsetAsync(next_count, 0, 4, s));
+      MG_LAUNCH(k_peel, grid_for(n_work, 128), 128, 0, s, v, work.as<uint32_t>(), (uint32_t)n_work,
+                next.as<uint32_t>(), next_count, next_cap, c + 2, overflow);
+      uint32_t h[4];
+      MG_CUDA(cudaMemcpyAsync(h, c + 5, 16, cudaMemcpyDeviceToHost, s));
+      MG_CUDA(cudaStreamSynchronize(s));
+      if (h[2]) {
+        set_error("peel: work list overflow (%u entries)", next_cap);
+        return MG_EINTERNAL;
+      }
+      n_work = h[0];
+      if (n_work) {
+        MG_TRY(work.ensure((size_t)n_work * 4));
+        MG_CUDA(cudaMemcpyAsync(work.p, next.p, (size_t)n_work * 4, cudaMemcpyDeviceToDevice, s));
+      }
+    }
+  }
+  next.release();
+  work.release();
+  // --- navigation cache, valid-edge count (:443-449) and CollectTips after pruning (:451)
+  MG_TRY(g->adj.ensure((size_t)n * 8 + 16));
+  if (n) {
+    TimedScope ts(g, T_ADJ, n);
+    MG_LAUNCH(k_adj, grid, 256, 0, s, v, g->adj.as<uint64_t>(), c + 3, c + 4);
+  }
+  unsigned long long h[5];
+  MG_CUDA(cudaMemcpyAsync(h, c, sizeof h, cudaMemcpyDeviceToHost, s));
+  MG_CUDA(cudaStreamSynchronize(s));
+  flush_timers(g);
+  st->n_tips_before = h[0];
+  st->n_mult1 = h[1];
+  st->n_peeled = h[2];
+  st->n_valid = h[3];
+  st->n_tips_after = h[4];
+  g->pruned = true;
+  return MG_OK;
+}
+
+// ------------------------------------------------------------------ mg_navigate
+__global__ void k_navigate(GraphView g, uint64_t first, uint64_t count, int8_t *outdeg, int8_t *indeg,
+                           uint64_t *out_ids, uint64_t *in_ids, uint16_t *mult) {
+  uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= count) return;
+  uint32_t e = (uint32_t)(first + t);
+  uint32_t o[4] = {kNull, kNull, kNull, kNull}, in[4] = {kNull, kNull, kNull, kNull};
+  int od = outgoing(g, e, o);
+  int id = incoming(g, e, in);
+  if (outdeg) outdeg[t] = (int8_t)od;
+  if (indeg) indeg[t] = (int8_t)id;
+  for (int j = 0; j < 4; ++j) {
+    if (out_ids) out_ids[t * 4 + j] = (j < od) ? (uint64_t)o[j] : ~0ull;
+    if (in_ids) in_ids[t * 4 + j] = (j < id) ? (uint64_t)in[j] : ~0ull;
+  }
+  if (mult) mult[t] = g.mult[e];
+}
+
+int run_navigate(mg_graph *g, uint64_t first, uint64_t count, int8_t *outdeg, int8_t *indeg, uint64_t *out_ids,
+                 uint64_t *in_ids, uint16_t *mult) {
+  cudaStream_t s = g->stream;
+  const uint64_t chunk = 1u << 22;
+  DevBuf d_od, d_id, d_o, d_i, d_m;
+  uint64_t cap = count < chunk ? count : chunk;
+  MG_TRY(d_od.alloc(cap));
+  MG_TRY(d_id.alloc(cap));
+  MG_TRY(d_o.alloc(cap * 32));
+  MG_TRY(d_i.alloc(cap * 32));
+  MG_TRY(d_m.alloc(cap * 2));
+  for (uint64_t off = 0; off < count; off += chunk) {
+    uint64_t c = count - off < chunk ? count - off : chunk;
+    {
+      TimedScope ts(g, T_NAV, c);
+      MG_LAUNCH(k_navigate, grid_for(c, 128), 128, 0, s, g->view, first + off, c, d_od.as<int8_t>(), d_id.as<int8_t>(),
+                d_o.as<uint64_t>(), d_i.as<uint64_t>(), d_m.as<uint16_t>());
+    }
+    if (outdeg) MG_CUDA(cudaMemcpyAsync(outdeg + off, d_od.p, c, cudaMemcpyDeviceToHost, s));
+    if (indeg) MG_CUDA(cudaMemcpyAsync(indeg + off, d_id.p, c, cudaMemcpyDeviceToHost, s));
+    if (out_ids) MG_CUDA(cudaMemcpyAsync(out_ids + off * 4, d_o.p, c * 32, cudaMemcpyDeviceToHost, s));
+    if (in_ids) MG_CUDA(cudaMemcpyAsync(in_ids + off * 4, d_i.p, c * 32, cudaMemcpyDeviceToHost, s));
+    if (mult) MG_CUDA(cudaMemcpyAsync(mult + off, d_m.p, c * 2, cudaMemcpyDeviceToHost, s));
+    MG_CUDA(cudaStreamSynchronize(s));
+  }
+  flush_timers(g);
+  return MG_OK;
+}
+
+}  // namespace mg

@@ -1,0 +1,401 @@
+// Search logic of the hot path as host+device inline functions: tip peeling, the start-node
+// predicate, the depth-limited admission search and the bounded multicycle enumeration.
+// Each function cites the reference lines (relative to /root/reference) whose results it
+// reproduces bit-exactly.  Kernels in prune.cu / starts.cu / enumerate.cu drive these per
+// thread / per warp; tests/emu drives the same code on the host against the oracle.
+#pragma once
+#include "sdbg_dev.cuh"
+
+namespace mg {
+
+// ------------------------------------------------------------------ navigation cache
+// After pruning the graph is static (nothing on the path invalidates edges any more,
+// src/cycle_finder.cpp:458-487), so Forward(e) and the validity of the target group are
+// materialised once per valid item: low 32 bits = Forward(e), bits 32..39 = validity mask of
+// items Forward(e)-i.  One 8-byte load then replaces rank + select + group scan.
+MG_HD uint64_t adj_encode(const GraphView &g, uint32_t e) {
+  if (get_inv(g, e)) return 0;
+  uint32_t next = forward(g, e);
+  if (next >= g.n) return 0;
+  uint64_t mask = 0;
+  uint32_t x = next;
+  int i = 0;
+  do {
+    if (!get_inv(g, x) && i < 8) mask |= 1ull << i;
+    --x;
+    ++i;
+  } while (x != kNull && !get_lt(g, x));
+  return (uint64_t)next | (mask << 32);
+}
+// OutgoingEdges (sdbg.h:354) from the cache: valid out-neighbours, descending id
+MG_HD int adj_outgoing(uint64_t a, uint32_t *out) {
+  uint32_t next = (uint32_t)a;
+  unsigned mask = (unsigned)(a >> 32) & 0xFFu;
+  int deg = 0;
+  for (int i = 0; mask; ++i, mask >>= 1)
+    if (mask & 1) {
+      if (deg < 4) out[deg] = next - i;
+      ++deg;
+    }
+  return deg;
+}
+
+// ------------------------------------------------------------------ atomics / fences
+MG_HD bool set_inv_atomic(const GraphView &g, uint32_t i) {
+  uint64_t *p = &g.fb[i >> 8].inv[(i >> 6) & 3];
+  uint64_t bit = 1ull << (i & 63);
+#if defined(__CUDA_ARCH__)
+  unsigned long long old = atomicOr((unsigned long long *)p, (unsigned long long)bit);
+  return !(old & bit);
+#else
+  uint64_t old = *p;
+  *p = old | bit;
+  return !(old & bit);
+#endif
+}
+MG_HD void fence_sc() {
+#if defined(__CUDA_ARCH__)
+  asm volatile("fence.sc.gpu;" ::: "memory");
+#endif
+}
+
+// ------------------------------------------------------------------ peel (RecursiveReduction)
+// src/cycle_finder.cpp:359-371 driven as at :440-442.  Work items are nodes KNOWN to have valid
+// out-degree 0 (tips collected before the multiplicity filter, then parents that lost their last
+// child).  A worker invalidates its node, then re-tests every valid parent; the fence between the
+// invalidation and the re-test guarantees that when two children of a parent are peeled
+// concurrently at least one worker sees out-degree 0.  Duplicates are arbitrated by the atomic
+// bit set.  `emit(p)` receives parents that became peelable.
+template <class Emit>
+MG_HD uint32_t peel_one(const GraphView &g, uint32_t v, Emit emit) {
+  if (get_inv<true>(g, v)) return 0;
+  uint32_t in[4];
+  int deg = incoming<true, false>(g, v, in);  // _GetIncomings(node,set), :111-123
+  if (!set_inv_atomic(g, v)) return 0;        // SetInvalidEdge, :364
+  fence_sc();
+  if (deg > 4) deg = 4;
+  for (int i = 0; i < deg; ++i) {
+    uint32_t p = in[i];
+    if (get_inv<true>(g, p)) continue;                 // :366
+    if (outgoing<true>(g, p, nullptr) > 0) continue;   // :360
+    emit(p);
+  }
+  return 1;
+}
+
+// ------------------------------------------------------------------ start-node predicate
+// src/cycle_finder.cpp:398-408: valid, indegree >= 2, multiplicity > threshold, no incoming edge
+// equal to the node itself (_IncomingNotEqualToCurrentNode, :29-36).
+MG_HD bool is_candidate(const GraphView &g, uint32_t v, uint64_t thr) {
+  if (get_inv(g, v)) return false;
+  if ((uint64_t)get_mult(g, v) <= thr) return false;
+  uint32_t in[4];
+  int deg = incoming(g, v, in);
+  if (deg < 2) return false;
+  if (deg > 4) deg = 4;
+  for (int i = 0; i < deg; ++i)
+    if (in[i] == v) return false;
+  return true;
+}
+// bucket key (int)ceil(log2((double)mult)), src/cycle_finder.cpp:414, exact for mult >= 1
+MG_HD int log2_bucket(uint32_t m) {
+  if (m <= 1) return 0;
+  uint32_t x = m - 1;
+  int b = 0;
+  while (x) { ++b; x >>= 1; }
+  return b;
+}
+
+// ------------------------------------------------------------------ DepthLevelSearch
+struct U32HashSet {  // open addressing, linear probing, empty = kNull
+  uint32_t *tab;
+  uint32_t log2cap;
+  uint32_t count;
+  uint32_t max_count;
+};
+MG_HD uint32_t hash_u32(uint32_t k, uint32_t log2cap) { return (k * 2654435761u) >> (32 - log2cap); }
+// 1 = inserted, 0 = already present, -1 = full
+MG_HD int set_insert(U32HashSet &s, uint32_t key) {
+  uint32_t mask = (1u << s.log2cap) - 1;
+  uint32_t h = hash_u32(key, s.log2cap);
+  for (;;) {
+    uint32_t cur = s.tab[h];
+    if (cur == key) return 0;
+    if (cur == kNull) {
+      if (s.count >= s.max_count) return -1;
+      s.tab[h] = key;
+      ++s.count;
+      return 1;
+    }
+    h = (h + 1) & mask;
+  }
+}
+struct BitSet {  // one bit per graph item; exact fallback for very large searches
+  uint32_t *bits;
+};
+MG_HD int set_insert(BitSet &s, uint32_t key) {
+  uint32_t w = s.bits[key >> 5], b = 1u << (key & 31);
+  if (w & b) return 0;
+  s.bits[key >> 5] = w | b;
+  return 1;
+}
+
+constexpr int kDlsFound = 1, kDlsNotFound = 0, kDlsSetFull = -1, kDlsStackFull = -2;
+
+// src/cycle_finder.cpp:248-343 with target == start (the only call site, :411).  `adj` is the
+// navigation cache.  The explicit stack holds at most 3*limit+5 entries.
+template <class Set>
+MG_HD int dls_run(const uint64_t *adj, uint32_t start, int limit, Set &seen, uint32_t *stk_node,
+                  uint16_t *stk_depth, uint32_t stk_cap, uint32_t &expansions) {
+  uint32_t sp = 0;
+  stk_node[0] = start;
+  stk_depth[0] = 0;
+  sp = 1;
+  while (sp) {
+    --sp;
+    uint32_t v = stk_node[sp];
+    int depth = stk_depth[sp];
+    uint32_t nb[4];
+    int outdeg = adj_outgoing(ld_ro(&adj[v]), nb);  // :285-302 (adj == 0 for an invalid v)
+    if (outdeg == 0) continue;                      // :294
+    ++expansions;
+    if (depth >= limit) continue;                   // :312
+    if (outdeg > 4) outdeg = 4;
+    for (int i = 0; i < outdeg; ++i) {              // :320-334, descending ids
+      uint32_t x = nb[i];
+      int r = set_insert(seen, x);
+      if (r < 0) return kDlsSetFull;
+      if (r == 1 || (x == start && depth > 0)) {
+        if (sp >= stk_cap) return kDlsStackFull;
+        stk_node[sp] = x;
+        stk_depth[sp] = (uint16_t)(depth + 1);
+        ++sp;
+      }
+    }
+    if (v == start && depth > 1) return kDlsFound;  // :337-339
+  }
+  return kDlsNotFound;
+}
+
+// ------------------------------------------------------------------ FindCycle
+// libstdc++ std::unordered_set<uint64_t> iteration order for the <= 4-element neighbour sets of
+// FindCycle: 13 buckets, identity hash; a new element goes to the list head when its bucket is
+// empty, else to the front of its bucket's run; erase keeps the relative order.
+struct USet {
+  uint32_t e[7];
+  uint32_t n;
+};
+MG_HD void uset_insert(USet &s, uint32_t x) {
+  int first_same = -1;
+  for (uint32_t i = 0; i < s.n; ++i) {
+    if (s.e[i] == x) return;
+    if (first_same < 0 && s.e[i] % 13 == x % 13) first_same = (int)i;
+  }
+  if (s.n >= 7) return;
+  int at = first_same < 0 ? 0 : first_same;
+  for (int i = (int)s.n; i > at; --i) s.e[i] = s.e[i - 1];
+  s.e[at] = x;
+  s.n++;
+}
+MG_HD void uset_erase(USet &s, uint32_t x) {
+  for (uint32_t i = 0; i < s.n; ++i)
+    if (s.e[i] == x) {
+      for (uint32_t j = i; j + 1 < s.n; ++j) s.e[j] = s.e[j + 1];
+      s.n--;
+      return;
+    }
+}
+
+constexpr int kMaxSteps = 10000000;  // src/cycle_finder.cpp:149
+constexpr int kClusterBound = 500;   // src/cycle_finder.cpp:132
+enum EnumStatus : int32_t {
+  kEnumDone = 0,
+  kEnumBound = 1,      // cluster bound reached: result is empty (:162-165), search stopped early
+  kEnumCap = 2,        // step cap reached (:148-151): cycles found so far are kept
+  kEnumOverflow = 3,   // arena too small: must be re-run with a larger arena
+  kEnumPreSkipped = 4  // start already visited in the snapshot (:476)
+};
+
+struct EnumArena {
+  uint32_t *path;       // [M+2]
+  int32_t *bl;          // [M+2]
+  USet *stk;            // [M+2]
+  uint64_t *lock;       // [1 << lock_log]  low 32 = key, high 32 = value; empty = ~0
+  uint32_t lock_log;
+  uint32_t *keylog;     // every key ever inserted into `lock` (+ leftovers on early stop)
+  uint32_t keylog_cap;
+  uint64_t *relax;      // relax_stack entries (bl << 32 | node), :192-193
+  uint32_t relax_cap;
+  uint32_t *cyc_nodes;  // staged raw cycles
+  uint32_t cyc_nodes_cap;
+  uint32_t *cyc_off;    // [kClusterBound + 1]
+};
+struct EnumResult {
+  int32_t status;
+  uint32_t n_cycles;
+  uint32_t n_nodes;
+  uint32_t n_keys;
+  uint32_t steps;
+  uint32_t expansions;
+};
+
+MG_HD bool visited_bit(const uint32_t *visited, uint32_t i) { return (visited[i >> 5] >> (i & 31)) & 1; }
+
+// value slot of `key` in the lock map, inserting `defval` when absent (std::map::try_emplace /
+// operator[] as used at :168,:200); nullptr when the arena is full.
+MG_HD uint32_t *lock_get(EnumArena &A, uint32_t &n_keys, uint32_t key, uint32_t defval) {
+  uint32_t mask = (1u << A.lock_log) - 1;
+  uint32_t h = hash_u32(key, A.lock_log);
+  for (;;) {
+    uint64_t cur = A.lock[h];
+    if ((uint32_t)cur == key && cur != ~0ull) return ((uint32_t *)&A.lock[h]) + 1;
+    if (cur == ~0ull) {
+      if (n_keys >= A.keylog_cap) return nullptr;
+      A.lock[h] = (uint64_t)key | ((uint64_t)defval << 32);
+      A.keylog[n_keys++] = key;
+      return ((uint32_t *)&A.lock[h]) + 1;
+    }
+    h = (h + 1) & mask;
+  }
+}
+
+// _BackgroundCheck, src/cycle_finder.cpp:40-52
+MG_HD bool background_ok(const GraphView &g, const uint32_t *visited, uint32_t from, uint32_t mu, uint32_t nb) {
+  if (visited_bit(visited, nb)) return false;
+  uint32_t m = get_mult(g, nb);
+  if (m == 0) return false;  // the reference would divide by zero; mult <= 1 items are invalid
+  if (mu / m > 500) return false;
+  if (from == nb) return false;
+  return true;
+}
+// _GetOutgoings(node,set,mult), src/cycle_finder.cpp:58-72
+MG_HD void enum_outgoings(const GraphView &g, const uint64_t *adj, const uint32_t *visited, uint32_t node,
+                          uint32_t mu, USet &s, uint32_t &expansions) {
+  s.n = 0;
+  ++expansions;
+  uint32_t nb[4];
+  int deg = adj_outgoing(ld_ro(&adj[node]), nb);
+  if (deg > 4) deg = 4;
+  for (int i = 0; i < deg; ++i)
+    if (background_ok(g, visited, node, mu, nb[i])) uset_insert(s, nb[i]);
+}
+// _GetIncomings(node,set,mult), src/cycle_finder.cpp:76-88
+MG_HD void enum_incomings(const GraphView &g, const uint32_t *visited, uint32_t node, uint32_t mu, USet &s,
+                          uint32_t &expansions) {
+  s.n = 0;
+  ++expansions;
+  uint32_t nb[4];
+  int deg = incoming(g, node, nb);
+  if (deg > 4) deg = 4;
+  for (int i = 0; i < deg; ++i)
+    if (background_ok(g, visited, node, mu, nb[i])) uset_insert(s, nb[i]);
+}
+
+// FindCycleUtil + FindCycle, src/cycle_finder.cpp:231-243,140-225, against the `visited` snapshot.
+// Does NOT mark visited (the ordered commit does, :217-222).  Exact shortcut: once the cluster
+// bound fires every later hit clears the list again, so the result is empty whatever follows;
+// the search stops there instead of spinning to the step cap.
+MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint32_t *visited, uint32_t start,
+                             int min_len, int max_len, EnumArena &A, EnumResult &R) {
+  const int M = max_len;
+  const uint32_t mu = get_mult(g, start);
+  uint32_t n_keys = 0, expansions = 0, n_cycles = 0, n_nodes = 0;
+  int plen = 0, slen = 0, blen = 0;
+  int counter = 0, steps = 0;
+  int32_t status = kEnumDone;
+  A.cyc_off[0] = 0;
+
+  A.path[plen++] = start;
+  uint32_t *lk0 = lock_get(A, n_keys, start, 0);  // lock[start] = 0, :237
+  if (!lk0) { status = kEnumOverflow; goto done; }
+  enum_outgoings(g, adj, visited, start, mu, A.stk[slen++], expansions);
+  A.bl[blen++] = M;
+
+  while (slen > 0) {
+    if (++steps > kMaxSteps) { status = kEnumCap; break; }  // :148-151
+    USet nbs = A.stk[slen - 1];                             // :153 (copy)
+    bool flag = true;
+    for (uint32_t i = 0; i < nbs.n; ++i) {
+      uint32_t nb = nbs.e[i];
+      if (nb == start) {                                    // :157-166
+        A.bl[blen - 1] = 1;
+        if (plen > min_len) {
+          if (++counter >= kClusterBound) {                 // cluster bound: final answer is empty
+            status = kEnumBound;
+            n_cycles = 0;
+            n_nodes = 0;
+            goto leftovers;
+          }
+          if (n_nodes + (uint32_t)plen > A.cyc_nodes_cap) { status = kEnumOverflow; goto done; }
+          for (int j = 0; j < plen; ++j) A.cyc_nodes[n_nodes + j] = A.path[j];
+          n_nodes += (uint32_t)plen;
+          A.cyc_off[++n_cycles] = n_nodes;
+        }
+      } else {
+        uint32_t *lk = lock_get(A, n_keys, nb, (uint32_t)M);  // try_emplace(nb, M), :168
+        if (!lk) { status = kEnumOverflow; goto done; }
+        if ((uint32_t)plen < *lk) {
+          A.path[plen++] = nb;                              // :170
+          A.bl[blen++] = M;                                 // :171
+          *lk = (uint32_t)plen;                             // :172
+          uset_erase(A.stk[slen - 1], nb);                  // :173
+          enum_outgoings(g, adj, visited, nb, mu, A.stk[slen], expansions);  // :174-176
+          ++slen;
+          flag = false;
+          break;
+        }
+      }
+    }
+    if (flag) {                                             // :181-211
+      --slen;
+      uint32_t v = A.path[--plen];
+      int b = A.bl[--blen];
+      if (blen > 0 && b < A.bl[blen - 1]) A.bl[blen - 1] = b;
+      if (b < M) {
+        uint32_t rn = 0;
+        A.relax[rn++] = ((uint64_t)(uint32_t)b << 32) | v;  // :192-193
+        while (rn) {
+          uint64_t r = A.relax[--rn];
+          int rb = (int)(r >> 32);
+          uint32_t u = (uint32_t)r;
+          uint32_t *lk = lock_get(A, n_keys, u, (uint32_t)M);
+          if (!lk) { status = kEnumOverflow; goto done; }
+          if ((int)*lk < M - rb + 1) {
+            *lk = (uint32_t)(M - rb + 1);
+            USet inc;
+            enum_incomings(g, visited, u, mu, inc, expansions);
+            for (uint32_t i = 0; i < inc.n; ++i) {
+              bool on_path = false;
+              for (int j = 0; j < plen; ++j)
+                if (A.path[j] == inc.e[i]) { on_path = true; break; }
+              if (!on_path) {
+                if (rn >= A.relax_cap) { status = kEnumOverflow; goto done; }
+                A.relax[rn++] = ((uint64_t)(uint32_t)(rb + 1) << 32) | inc.e[i];
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+leftovers:
+  // On an early stop the neighbour sets still on the stack hold accepted nodes that never got a
+  // lock entry; the ordered commit must see them as examined.
+  if (status == kEnumBound || status == kEnumCap) {
+    for (int l = 0; l < slen; ++l)
+      for (uint32_t i = 0; i < A.stk[l].n; ++i) {
+        uint32_t x = A.stk[l].e[i];
+        if (x == start) continue;
+        if (!lock_get(A, n_keys, x, (uint32_t)M)) { status = kEnumOverflow; goto done; }
+      }
+  }
+done:
+  R.status = status;
+  R.n_cycles = n_cycles;
+  R.n_nodes = n_nodes;
+  R.n_keys = n_keys;
+  R.steps = (uint32_t)steps;
+  R.expansions = expansions;
+}
+
+}  // namespace mg

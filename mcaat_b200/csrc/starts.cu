@@ -1,0 +1,263 @@
+// K4-K6: start-node selection of reference src/cycle_finder.cpp:387-427 (ChunkStartNodes):
+// candidate predicate + ordered compaction, DepthLevelSearch admission (:248-343), bucketing.
+#include <algorithm>
+
+#include "common.cuh"
+#include "search_dev.cuh"
+
+namespace mg {
+
+static inline unsigned grid_for(uint64_t n, int block) { return (unsigned)((n + block - 1) / block); }
+
+// ------------------------------------------------------------------ candidates
+__global__ void k_candidates(GraphView g, uint64_t thr, uint32_t *bits) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool c = i < g.n && is_candidate(g, (uint32_t)i, thr);
+  unsigned m = __ballot_sync(0xffffffffu, c);
+  if ((threadIdx.x & 31) == 0 && i < g.n) bits[i >> 5] = m;
+}
+
+int run_candidates(mg_graph *g, uint64_t thr, DevBuf &ids, uint64_t *n_out) {
+  GraphView &v = g->view;
+  cudaStream_t s = g->stream;
+  DevBuf bits;
+  MG_TRY(bits.alloc((size_t)((v.n + 31) / 32) * 4 + 16));
+  *n_out = 0;
+  if (v.n) {
+    TimedScope ts(g, T_CAND, v.n);
+    MG_LAUNCH(k_candidates, grid_for(v.n, 256), 256, 0, s, v, thr, bits.as<uint32_t>());
+  }
+  MG_TRY(bitmap_to_ids(bits.as<uint32_t>(), v.n, ids, n_out, s));
+  flush_timers(g);
+  return MG_OK;
+}
+
+// ------------------------------------------------------------------ DepthLevelSearch
+// Tier 1: persistent threads, one candidate per thread at a time, pulled from an atomic work
+// queue.  Each thread owns a small open-addressing `seen` set and a DFS stack in global memory
+// (hot parts stay in L1/L2); the set is cleared by undoing the logged slots.
+struct DlsArena {
+  uint32_t *tabs;      // [threads][1 << log2cap]
+  uint16_t *slotlog;   // [threads][max_count]
+  uint32_t *stk_node;  // [threads][stk_cap]
+  uint16_t *stk_depth; // [threads][stk_cap]
+  uint32_t log2cap, max_count, stk_cap;
+};
+
+struct LoggedSet {
+  uint32_t *tab;
+  uint16_t *log;
+  uint32_t log2cap, count, max_count;
+};
+MG_HD int set_insert(LoggedSet &s, uint32_t key) {
+  uint32_t mask = (1u << s.log2cap) - 1;
+  uint32_t h = hash_u32(key, s.log2cap);
+  for (;;) {
+    uint32_t cur = s.tab[h];
+    if (cur == key) return 0;
+    if (cur == kNull) {
+      if (s.count >= s.max_count) return -1;
+      s.tab[h] = key;
+      s.log[s.count++] = (uint16_t)h;
+      return 1;
+    }
+    h = (h + 1) & mask;
+  }
+}
+
+__global__ void __launch_bounds__(128) k_dls(const uint64_t *__restrict__ adj, const uint32_t *__restrict__ cand,
+                                            uint32_t n_cand, int limit, DlsArena A, int8_t *result,
+                                            uint32_t *queue, unsigned long long *expansions) {
+  const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+  LoggedSet seen;
+  seen.tab = A.tabs + ((size_t)tid << A.log2cap);
+  seen.log = A.slotlog + (size_t)tid * A.max_count;
+  seen.log2cap = A.log2cap;
+  seen.max_count = A.max_count;
+  uint32_t *stk_node = A.stk_node + (size_t)tid * A.stk_cap;
+  uint16_t *stk_depth = A.stk_depth + (size_t)tid * A.stk_cap;
+  uint32_t exp = 0;
+  unsigned long long exp_total = 0;
+  for (;;) {
+    uint32_t idx = atomicAdd(queue, 1u);
+    if (idx >= n_cand) break;
+    seen.count = 0;
+    exp = 0;
+    int r = dls_run(adj, cand[idx], limit, seen, stk_node, stk_depth, A.stk_cap, exp);
+    result[idx] = (int8_t)r;
+    exp_total += exp;
+    for (uint32_t j = 0; j < seen.count; ++j) seen.tab[seen.log[j]] = kNull;  // undo
+  }
+  for (int d = 16; d; d >>= 1) exp_total += __shfl_down_sync(0xffffffffu, exp_total, d);
+  if ((threadIdx.x & 31) == 0 && exp_total) atomicAdd(expansions, exp_total);
+}
+
+// Tier 2 (exact fallback when a tier-1 set fills up): one block per candidate, `seen` is a full
+// bitmap over the graph's items; thread 0 searches, the block clears the bitmap afterwards.
+__global__ void __launch_bounds__(256) k_dls_big(const uint64_t *__restrict__ adj, const uint32_t *__restrict__ cand,
+                                                const uint32_t *__restrict__ todo, uint32_t n_todo, int limit,
+                                                uint32_t *bitmaps, size_t words_per_map, uint32_t *stk_node,
+                                                uint16_t *stk_depth, uint32_t stk_cap, int8_t *result,
+                                                unsigned long long *expansions) {
+  uint32_t *bits = bitmaps + (size_t)blockIdx.x * words_per_map;
+  __shared__ int r_sh;
+  for (uint32_t t = blockIdx.x; t < n_todo; t += gridDim.x) {
+    for (size_t w = threadIdx.x; w < words_per_map; w += blockDim.x) bits[w] = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      BitSet seen{bits};
+      uint32_t exp = 0;
+      uint32_t idx = todo[t];
+      r_sh = dls_run(adj, cand[idx], limit, seen, stk_node + (size_t)blockIdx.x * stk_cap,
+                     stk_depth + (size_t)blockIdx.x * stk_cap, stk_cap, exp);
+      result[idx] = (int8_t)r_sh;
+      atomicAdd(expansions, (unsigned long long)exp);
+    }
+    __syncthreads();
+  }
+}
+
+static uint32_t env_u32(const char *name, uint32_t def, uint32_t lo, uint32_t hi) {
+  const char *e = getenv(name);
+  if (!e || !*e) return def;
+  long v = strtol(e, nullptr, 10);
+  if (v < (long)lo) v = lo;
+  if (v > (long)hi) v = hi;
+  return (uint32_t)v;
+}
+
+int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t *pass_host, uint64_t *expansions) {
+  cudaStream_t s = g->stream;
+  if (expansions) *expansions = 0;
+  if (n == 0) return MG_OK;
+  if (!g->pruned || !g->adj.p) {
+    set_error("mg_dls: call mg_prune first (it builds the navigation cache)");
+    return MG_EINVAL;
+  }
+  if (limit < 1 || limit > 4000) {
+    set_error("mg_dls: limit %d outside [1, 4000]", limit);
+    return MG_ELIMIT;
+  }
+  if (n > 0xFFFFFFF0ull) return MG_ELIMIT;
+  const uint32_t log2cap = env_u32("MCAAT_DLS_LOG2CAP", 11, 6, 16);
+  const int block = 128;
+  uint32_t blocks = (uint32_t)g->sm_count * env_u32("MCAAT_DLS_BLOCKS_PER_SM", 8, 1, 16);
+  if ((uint64_t)blocks * block > n) blocks = (uint32_t)((n + block - 1) / block);
+  const size_t threads = (size_t)blocks * block;
+  DlsArena A;
+  A.log2cap = log2cap;
+  A.max_count = (1u << log2cap) / 2;
+  A.stk_cap = (uint32_t)(4 * limit + 8);
+  DevBuf tabs, slotlog, sn, sd, result, ctr;
+  MG_TRY(tabs.alloc((threads << log2cap) * 4));
+  MG_TRY(slotlog.alloc(threads * A.max_count * 2));
+  MG_TRY(sn.alloc(threads * A.stk_cap * 4));
+  MG_TRY(sd.alloc(threads * A.stk_cap * 2));
+  MG_TRY(result.alloc(n));
+  MG_TRY(ctr.alloc(16));
+  MG_CUDA(cudaMemsetAsync(tabs.p, 0xFF, tabs.bytes, s));
+  MG_CUDA(cudaMemsetAsync(ctr.p, 0, 16, s));
+  A.tabs = tabs.as<uint32_t>();
+  A.slotlog = slotlog.as<uint16_t>();
+  A.stk_node = sn.as<uint32_t>();
+  A.stk_depth = sd.as<uint16_t>();
+  {
+    TimedScope ts(g, T_DLS, n);
+    MG_LAUNCH(k_dls, blocks, block, 0, s, g->adj.as<uint64_t>(), ids_dev, (uint32_t)n, limit, A, result.as<int8_t>(),
+              ctr.as<uint32_t>(), (unsigned long long *)(ctr.as<uint64_t>() + 1));
+  }
+  std::vector<int8_t> res(n);
+  MG_CUDA(cudaMemcpyAsync(res.data(), result.p, n, cudaMemcpyDeviceToHost, s));
+  MG_CUDA(cudaStreamSynchronize(s));
+  tabs.release();
+  slotlog.release();
+  // --- tier 2 for searches whose set filled up
+  std::vector<uint32_t> todo;
+  for (uint64_t i = 0; i < n; ++i) {
+    if (res[i] == kDlsSetFull) todo.push_back((uint32_t)i);
+    else if (res[i] == kDlsStackFull) {
+      set_error("mg_dls: DFS stack bound violated (internal)");
+      return MG_EINTERNAL;
+    }
+  }
+  if (!todo.empty()) {
+    const size_t words = (size_t)((g->view.n + 31) / 32);
+    size_t free_b = 0, total_b = 0;
+    MG_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    size_t maps = std::min<size_t>(todo.size(), std::min<size_t>((size_t)g->sm_count * 2, (free_b / 2) / (words * 4 + 1)));
+    if (maps == 0) {
+      set_error("mg_dls: not enough device memory for the exact bitmap tier");
+      return MG_ENOMEM;
+    }
+    DevBuf maps_b, todo_b, sn2, sd2;
+    MG_TRY(maps_b.alloc(maps * words * 4));
+    MG_TRY(todo_b.alloc(todo.size() * 4));
+    MG_TRY(sn2.alloc(maps * A.stk_cap * 4));
+    MG_TRY(sd2.alloc(maps * A.stk_cap * 2));
+    MG_CUDA(cudaMemcpyAsync(todo_b.p, todo.data(), todo.size() * 4, cudaMemcpyHostToDevice, s));
+    {
+      TimedScope ts(g, T_DLS, 0);
+      MG_LAUNCH(k_dls_big, (unsigned)maps, 256, 0, s, g->adj.as<uint64_t>(), ids_dev, todo_b.as<uint32_t>(),
+                (uint32_t)todo.size(), limit, maps_b.as<uint32_t>(), words, sn2.as<uint32_t>(), sd2.as<uint16_t>(),
+                A.stk_cap, result.as<int8_t>(), (unsigned long long *)(ctr.as<uint64_t>() + 1));
+    }
+    MG_CUDA(cudaMemcpyAsync(res.data(), result.p, n, cudaMemcpyDeviceToHost, s));
+    MG_CUDA(cudaStreamSynchronize(s));
+  }
+  uint64_t exp = 0;
+  MG_CUDA(cudaMemcpy(&exp, ctr.as<uint64_t>() + 1, 8, cudaMemcpyDeviceToHost));
+  if (expansions) *expansions = exp;
+  for (uint64_t i = 0; i < n; ++i) {
+    if (res[i] < 0) {
+      set_error("mg_dls: search %llu did not complete (code %d)", (unsigned long long)i, (int)res[i]);
+      return MG_EINTERNAL;
+    }
+    pass_host[i] = (uint8_t)res[i];
+  }
+  flush_timers(g);
+  return MG_OK;
+}
+
+// ------------------------------------------------------------------ bucketing
+__global__ void k_gather_mult(GraphView g, const uint32_t *ids, uint64_t n, uint16_t *out) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = ids[i] < g.n ? g.mult[ids[i]] : 0;
+}
+
+// ids (ascending) + their multiplicities -> map<int, vector, greater<int>> of :414-416 flattened
+int bucket_on_host(const std::vector<uint64_t> &ids, const std::vector<uint16_t> &mult, mg_starts *out) {
+  std::vector<std::vector<uint64_t>> buckets(33);
+  for (size_t i = 0; i < ids.size(); ++i) buckets[log2_bucket(mult[i])].push_back(ids[i]);
+  uint64_t nb = 0;
+  for (auto &b : buckets) nb += !b.empty();
+  out->n_buckets = nb;
+  out->n_starts = ids.size();
+  out->bucket_key = (int64_t *)malloc((nb + 1) * 8);
+  out->bucket_off = (uint64_t *)malloc((nb + 1) * 8);
+  out->start_ids = (uint64_t *)malloc((ids.size() + 1) * 8);
+  if (!out->bucket_key || !out->bucket_off || !out->start_ids) return MG_ENOMEM;
+  uint64_t bi = 0, off = 0;
+  for (int k = 32; k >= 0; --k) {
+    if (buckets[k].empty()) continue;
+    out->bucket_key[bi] = k;
+    out->bucket_off[bi] = off;
+    memcpy(out->start_ids + off, buckets[k].data(), buckets[k].size() * 8);
+    off += buckets[k].size();
+    ++bi;
+  }
+  out->bucket_off[bi] = off;
+  return MG_OK;
+}
+
+int gather_mult(mg_graph *g, const uint32_t *ids_dev, uint64_t n, std::vector<uint16_t> &out) {
+  out.resize(n);
+  if (!n) return MG_OK;
+  DevBuf m;
+  MG_TRY(m.alloc(n * 2));
+  MG_LAUNCH(k_gather_mult, grid_for(n, 256), 256, 0, g->stream, g->view, ids_dev, n, m.as<uint16_t>());
+  MG_CUDA(cudaMemcpyAsync(out.data(), m.p, n * 2, cudaMemcpyDeviceToHost, g->stream));
+  MG_CUDA(cudaStreamSynchronize(g->stream));
+  return MG_OK;
+}
+
+}  // namespace mg

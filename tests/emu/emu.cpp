@@ -1,0 +1,278 @@
+// TEST INFRASTRUCTURE — NOT PRODUCT CODE, never loaded by mcaat_b200/.
+//
+// Host-side driver for the device functions of mcaat_b200/csrc/{sdbg_dev,search_dev}.cuh (they are
+// written `__host__ __device__`): builds the same block layout in host memory with the same
+// per-block routines and runs the same navigation / peel / admission-search / enumeration code one
+// "thread" at a time, so that the exact logic the CUDA kernels execute can be checked against the
+// oracle on a machine without a GPU.  The speculative window + ordered commit of enumerate.cu is
+// mirrored here (emu_find_cycles) to check that it reproduces the sequential loop for any window.
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "../../mcaat_b200/csrc/search_dev.cuh"
+
+using namespace mg;
+
+struct Emu {
+  GraphView v;
+  std::vector<WBlock> wb;
+  std::vector<FBlock> fb;
+  std::vector<uint16_t> mult;
+  std::vector<uint32_t> hints;
+  std::vector<uint64_t> adj;
+  std::vector<uint32_t> visited;
+};
+
+extern "C" {
+
+Emu *emu_create(uint64_t n, const uint64_t *w, const uint64_t *last, const uint64_t *tip, const uint16_t *mult16,
+                const int64_t *f) {
+  Emu *e = new Emu();
+  GraphView &v = e->v;
+  memset(&v, 0, sizeof v);
+  v.n = n;
+  v.n_wblocks = (n + kWNib - 1) / kWNib;
+  v.n_fblocks = (n + kFItems - 1) / kFItems;
+  for (int i = 0; i < 6; ++i) v.f[i] = f[i];
+  e->wb.resize(v.n_wblocks + 1);
+  e->fb.resize(v.n_fblocks + 1);
+  memset(e->wb.data(), 0, e->wb.size() * sizeof(WBlock));
+  memset(e->fb.data(), 0, e->fb.size() * sizeof(FBlock));
+  uint32_t run[4] = {0, 0, 0, 0};
+  for (uint64_t b = 0; b < v.n_wblocks; ++b) {
+    uint32_t c[4];
+    uint64_t words[kWWords];
+    wblock_counts(w, n, b, c, words);
+    for (int j = 0; j < kWWords; ++j) e->wb[b].w[j] = words[j];
+    for (int a = 0; a < 4; ++a) {
+      e->wb[b].cnt[a] = run[a];
+      run[a] += c[a];
+    }
+  }
+  for (int a = 0; a < 4; ++a) v.total_w[a] = run[a];
+  uint32_t lr = 0;
+  for (uint64_t b = 0; b < v.n_fblocks; ++b) {
+    e->fb[b].rank_before = lr;
+    for (int j = 0; j < 4; ++j) {
+      uint64_t wi = b * 4 + j;
+      uint64_t l = tail_mask_word(last, n, wi), t = tail_mask_word(tip, n, wi);
+      e->fb[b].last[j] = l;
+      e->fb[b].lt[j] = l | t;
+      e->fb[b].inv[j] = t | w_zero_mask(w, n, wi);
+      lr += popc64(l);
+    }
+  }
+  v.total_last = lr;
+  size_t hl = (size_t)lr / kSelH + 2, off[5];
+  off[0] = hl;
+  for (int a = 0; a < 4; ++a) off[a + 1] = off[a] + (size_t)v.total_w[a] / kSelH + 2;
+  e->hints.assign(off[4], 0);
+  for (uint64_t b = 0; b < v.n_wblocks; ++b)
+    for (int a = 0; a < 4; ++a) {
+      uint32_t before = e->wb[b].cnt[a];
+      uint32_t after = b + 1 < v.n_wblocks ? e->wb[b + 1].cnt[a] : v.total_w[a];
+      for (uint32_t j = (before + kSelH - 1) / kSelH; (uint64_t)j * kSelH < after; ++j) e->hints[off[a] + j] = (uint32_t)b;
+    }
+  for (uint64_t b = 0; b < v.n_fblocks; ++b) {
+    uint32_t before = e->fb[b].rank_before;
+    uint32_t after = b + 1 < v.n_fblocks ? e->fb[b + 1].rank_before : lr;
+    for (uint32_t j = (before + kSelH - 1) / kSelH; (uint64_t)j * kSelH < after; ++j) e->hints[j] = (uint32_t)b;
+  }
+  e->mult.assign(mult16, mult16 + n);
+  v.wb = e->wb.data();
+  v.fb = e->fb.data();
+  v.mult = e->mult.data();
+  v.hint_last = e->hints.data();
+  for (int a = 0; a < 4; ++a) v.hint_w[a] = e->hints.data() + off[a];
+  v.rank_f[0] = 0;
+  for (int i = 1; i < 6; ++i) {
+    int64_t pos = v.f[i] - 1;
+    v.rank_f[i] = pos >= (int64_t)n ? -1 : pos == (int64_t)n - 1 ? (int64_t)lr : (int64_t)rank_last(v, pos);
+  }
+  e->visited.assign((n + 31) / 32 + 1, 0);
+  return e;
+}
+void emu_free(Emu *e) { delete e; }
+
+void emu_navigate(Emu *e, int8_t *outdeg, int8_t *indeg, uint64_t *out_ids, uint64_t *in_ids) {
+  for (uint64_t i = 0; i < e->v.n; ++i) {
+    uint32_t o[4] = {kNull, kNull, kNull, kNull}, in[4] = {kNull, kNull, kNull, kNull};
+    int od = outgoing(e->v, (uint32_t)i, o), id = incoming(e->v, (uint32_t)i, in);
+    outdeg[i] = (int8_t)od;
+    indeg[i] = (int8_t)id;
+    for (int j = 0; j < 4; ++j) {
+      out_ids[i * 4 + j] = j < od ? o[j] : ~0ull;
+      in_ids[i * 4 + j] = j < id ? in[j] : ~0ull;
+    }
+  }
+}
+
+void emu_rank_select_check(Emu *e, int64_t *bad) {  // rank/select round trips over every occurrence
+  GraphView &v = e->v;
+  *bad = 0;
+  for (unsigned a = 1; a <= 4; ++a)
+    for (uint32_t k = 0; k < v.total_w[a - 1]; ++k) {
+      uint32_t p = select_w(v, a, k);
+      if (p >= v.n || get_w(v, p) != a || rank_w(v, a, p) != k + 1) ++*bad;
+    }
+  for (uint32_t k = 0; k < v.total_last; ++k) {
+    uint32_t p = select_last(v, k);
+    if (p >= v.n || rank_last(v, p) != k + 1) ++*bad;
+  }
+}
+
+// stats: tips_before, mult1, peeled, valid, tips_after
+void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
+  GraphView &v = e->v;
+  std::vector<uint32_t> work, next;
+  for (uint64_t i = 0; i < v.n; ++i)
+    if (outgoing(v, (uint32_t)i, nullptr) == 0) work.push_back((uint32_t)i);
+  stats[0] = work.size();
+  uint64_t m1 = 0;
+  for (uint64_t i = 0; i < v.n; ++i)
+    if (v.mult[i] <= 1) { set_inv_atomic(v, (uint32_t)i); ++m1; }
+  stats[1] = m1;
+  uint64_t peeled = 0;
+  if (reverse_order) std::reverse(work.begin(), work.end());
+  while (!work.empty()) {  // level-synchronous like the kernel loop; order inside a level is free
+    next.clear();
+    for (uint32_t x : work) peeled += peel_one(v, x, [&](uint32_t p) { next.push_back(p); });
+    if (reverse_order) std::reverse(next.begin(), next.end());
+    work.swap(next);
+  }
+  stats[2] = peeled;
+  e->adj.resize(v.n + 1);
+  uint64_t valid = 0, tips = 0;
+  for (uint64_t i = 0; i < v.n; ++i) {
+    uint64_t a = adj_encode(v, (uint32_t)i);
+    e->adj[i] = a;
+    bool ok = !get_inv(v, (uint32_t)i);
+    valid += ok;
+    tips += ok && (a >> 32) == 0;
+  }
+  stats[3] = valid;
+  stats[4] = tips;
+}
+void emu_invalid(Emu *e, uint8_t *out) {
+  for (uint64_t i = 0; i < e->v.n; ++i) out[i] = get_inv(e->v, (uint32_t)i);
+}
+
+uint64_t emu_candidates(Emu *e, uint64_t thr, uint64_t *ids) {
+  uint64_t c = 0;
+  for (uint64_t i = 0; i < e->v.n; ++i)
+    if (is_candidate(e->v, (uint32_t)i, thr)) ids[c++] = i;
+  return c;
+}
+int emu_bucket(Emu *e, uint64_t id) { return log2_bucket(e->v.mult[id]); }
+
+// tier 1 hash set with the given log2 capacity; returns the dls_run code
+int emu_dls(Emu *e, uint64_t start, int limit, int log2cap, uint64_t *expansions) {
+  std::vector<uint32_t> tab((size_t)1 << log2cap, kNull), sn(4 * limit + 8);
+  std::vector<uint16_t> sd(4 * limit + 8);
+  U32HashSet s{tab.data(), (uint32_t)log2cap, 0, (1u << log2cap) / 2};
+  uint32_t exp = 0;
+  int r = dls_run(e->adj.data(), (uint32_t)start, limit, s, sn.data(), sd.data(), (uint32_t)sn.size(), exp);
+  if (expansions) *expansions += exp;
+  return r;
+}
+int emu_dls_bitmap(Emu *e, uint64_t start, int limit) {
+  std::vector<uint32_t> bits((e->v.n + 31) / 32 + 1, 0), sn(4 * limit + 8);
+  std::vector<uint16_t> sd(4 * limit + 8);
+  BitSet s{bits.data()};
+  uint32_t exp = 0;
+  return dls_run(e->adj.data(), (uint32_t)start, limit, s, sn.data(), sd.data(), (uint32_t)sn.size(), exp);
+}
+
+struct EmuSlot {
+  std::vector<uint32_t> path, keylog, cyc_nodes, cyc_off;
+  std::vector<int32_t> bl;
+  std::vector<USet> stk;
+  std::vector<uint64_t> lock, relax;
+  EnumArena A;
+  EnumResult R;
+  void init(int M, uint32_t lock_log, uint32_t relax_cap, uint32_t cyc_cycles) {
+    path.resize(M + 4); bl.resize(M + 4); stk.resize(M + 4);
+    lock.assign((size_t)1 << lock_log, ~0ull);
+    keylog.resize(((size_t)1 << lock_log) / 2);
+    relax.resize(relax_cap);
+    cyc_nodes.resize((size_t)cyc_cycles * (M + 1));
+    cyc_off.resize(kClusterBound + 1);
+    A.path = path.data(); A.bl = bl.data(); A.stk = stk.data(); A.lock = lock.data(); A.lock_log = lock_log;
+    A.keylog = keylog.data(); A.keylog_cap = (uint32_t)keylog.size(); A.relax = relax.data(); A.relax_cap = relax_cap;
+    A.cyc_nodes = cyc_nodes.data(); A.cyc_nodes_cap = (uint32_t)cyc_nodes.size(); A.cyc_off = cyc_off.data();
+  }
+};
+
+// Mirrors run_find_cycles (enumerate.cu) with `window` speculative searches per round.
+// Outputs: searched starts, per-search cycle counts, flat cycle lengths and nodes (caller-sized
+// generously), stats = {skipped, bound, cap, reruns, rounds, overflow_reruns}.
+int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int max_len, uint32_t window,
+                    uint32_t lock_log, uint64_t *searched, uint64_t *n_searched, uint64_t *cyc_count,
+                    uint64_t *cyc_len, uint64_t *n_cycles, uint64_t *nodes, uint64_t *n_nodes, uint64_t *stats) {
+  GraphView &v = e->v;
+  std::fill(e->visited.begin(), e->visited.end(), 0u);
+  uint32_t *vis = e->visited.data();
+  *n_searched = *n_cycles = *n_nodes = 0;
+  for (int i = 0; i < 6; ++i) stats[i] = 0;
+  std::vector<EmuSlot> slots(window);
+  for (auto &s : slots) s.init(max_len, lock_log, 4096, 128);
+  uint64_t pos = 0;
+  auto accept = [&](uint32_t s, EmuSlot &sl) {
+    for (uint32_t j = 0; j < sl.R.n_nodes; ++j) vis[sl.cyc_nodes[j] >> 5] |= 1u << (sl.cyc_nodes[j] & 31);
+    searched[*n_searched] = s;
+    cyc_count[*n_searched] = sl.R.n_cycles;
+    ++*n_searched;
+    for (uint32_t c = 0; c < sl.R.n_cycles; ++c) cyc_len[(*n_cycles)++] = sl.cyc_off[c + 1] - sl.cyc_off[c];
+    for (uint32_t j = 0; j < sl.R.n_nodes; ++j) nodes[(*n_nodes)++] = sl.cyc_nodes[j];
+    stats[1] += sl.R.status == kEnumBound;
+    stats[2] += sl.R.status == kEnumCap;
+  };
+  while (pos < n) {
+    uint32_t cnt = (uint32_t)std::min<uint64_t>(window, n - pos);
+    std::vector<uint32_t> snapshot(e->visited);
+    for (uint32_t i = 0; i < cnt; ++i) {  // "search kernel": all against the snapshot
+      EmuSlot &sl = slots[i];
+      uint32_t s = (uint32_t)starts[pos + i];
+      if (visited_bit(snapshot.data(), s)) { sl.R.status = kEnumPreSkipped; sl.R.n_keys = sl.R.n_nodes = sl.R.n_cycles = 0; continue; }
+      std::fill(sl.lock.begin(), sl.lock.end(), ~0ull);
+      enum_run(v, e->adj.data(), snapshot.data(), s, min_len, max_len, sl.A, sl.R);
+    }
+    ++stats[4];
+    uint32_t i = 0;
+    int reason = 0;
+    for (; i < cnt; ++i) {  // "commit kernel"
+      EmuSlot &sl = slots[i];
+      uint32_t s = (uint32_t)starts[pos + i];
+      if (visited_bit(vis, s)) { ++stats[0]; continue; }
+      if (sl.R.status == kEnumOverflow) { reason = 2; break; }
+      bool conflict = false;
+      for (uint32_t j = 0; j < sl.R.n_keys; ++j)
+        if (sl.keylog[j] != s && visited_bit(vis, sl.keylog[j])) { conflict = true; break; }
+      if (conflict) { reason = 1; break; }
+      accept(s, sl);
+    }
+    pos += i;
+    if (reason == 1) ++stats[3];
+    if (reason == 2) {
+      uint32_t ll = lock_log + 4, rc = 1u << 16;
+      for (;;) {
+        EmuSlot big;
+        big.init(max_len, ll, rc, kClusterBound);
+        uint32_t s = (uint32_t)starts[pos];
+        enum_run(v, e->adj.data(), vis, s, min_len, max_len, big.A, big.R);
+        ++stats[5];
+        if (big.R.status != kEnumOverflow) { accept(s, big); break; }
+        if (ll >= 26) return -1;
+        ll += 2; rc *= 4;
+      }
+      pos += 1;
+    }
+  }
+  return 0;
+}
+
+}  // extern "C"

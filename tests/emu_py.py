@@ -1,0 +1,124 @@
+"""TEST INFRASTRUCTURE: ctypes view of tests/emu/libemu.so — the product's `__host__ __device__`
+search logic (mcaat_b200/csrc/*.cuh) compiled for the host, so it can be checked against the
+oracle without a GPU.  Never imported by the product."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "emu", "emu.cpp")
+LIB = os.path.join(HERE, "emu", "libemu.so")
+HDRS = [os.path.join(HERE, "..", "mcaat_b200", "csrc", h) for h in ("sdbg_dev.cuh", "search_dev.cuh")]
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        newest = max(os.path.getmtime(p) for p in [SRC] + HDRS)
+        if not os.path.exists(LIB) or os.path.getmtime(LIB) < newest:
+            gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+            subprocess.run([gxx, "-std=c++17", "-O2", "-fPIC", "-shared", "-x", "c++", SRC, "-o", LIB], check=True)
+        L = C.CDLL(LIB)
+        L.emu_create.restype = C.c_void_p
+        L.emu_create.argtypes = [C.c_uint64] + [C.c_void_p] * 5
+        L.emu_free.argtypes = [C.c_void_p]
+        L.emu_navigate.argtypes = [C.c_void_p] * 5
+        L.emu_rank_select_check.argtypes = [C.c_void_p, C.c_void_p]
+        L.emu_prune.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        L.emu_invalid.argtypes = [C.c_void_p, C.c_void_p]
+        L.emu_candidates.restype = C.c_uint64
+        L.emu_candidates.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
+        L.emu_bucket.restype = C.c_int
+        L.emu_bucket.argtypes = [C.c_void_p, C.c_uint64]
+        L.emu_dls.restype = C.c_int
+        L.emu_dls.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p]
+        L.emu_dls_bitmap.restype = C.c_int
+        L.emu_dls_bitmap.argtypes = [C.c_void_p, C.c_uint64, C.c_int]
+        L.emu_find_cycles.restype = C.c_int
+        L.emu_find_cycles.argtypes = ([C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.c_uint32]
+                                      + [C.c_void_p] * 8)
+        _lib = L
+    return _lib
+
+
+class EmuGraph:
+    def __init__(self, packed):
+        self.p = packed
+        self.n = packed["n"]
+        self.h = C.c_void_p(lib().emu_create(self.n, packed["w"].ctypes.data, packed["last"].ctypes.data,
+                                             packed["tip"].ctypes.data, packed["mult"].ctypes.data,
+                                             packed["f"].ctypes.data))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().emu_free(self.h)
+            self.h = None
+
+    def navigate(self):
+        n = self.n
+        od = np.empty(n, np.int8)
+        idg = np.empty(n, np.int8)
+        o = np.empty((n, 4), np.uint64)
+        i_ = np.empty((n, 4), np.uint64)
+        lib().emu_navigate(self.h, od.ctypes.data, idg.ctypes.data, o.ctypes.data, i_.ctypes.data)
+        return od, idg, o, i_
+
+    def rank_select_bad(self):
+        bad = C.c_int64(0)
+        lib().emu_rank_select_check(self.h, C.byref(bad))
+        return bad.value
+
+    def prune(self, reverse_order=False):
+        st = np.zeros(5, np.uint64)
+        lib().emu_prune(self.h, st.ctypes.data, int(reverse_order))
+        return dict(zip(("n_tips_before", "n_mult1", "n_peeled", "n_valid", "n_tips_after"), map(int, st)))
+
+    def invalid(self):
+        out = np.empty(self.n, np.uint8)
+        lib().emu_invalid(self.h, out.ctypes.data)
+        return out.astype(bool)
+
+    def candidates(self, thr):
+        ids = np.empty(self.n, np.uint64)
+        c = lib().emu_candidates(self.h, thr, ids.ctypes.data)
+        return ids[:c].copy()
+
+    def bucket(self, node):
+        return lib().emu_bucket(self.h, int(node))
+
+    def dls(self, start, limit, log2cap=11):
+        exp = C.c_uint64(0)
+        return lib().emu_dls(self.h, int(start), limit, log2cap, C.byref(exp)), exp.value
+
+    def dls_bitmap(self, start, limit):
+        return lib().emu_dls_bitmap(self.h, int(start), limit)
+
+    def find_cycles(self, starts, min_len, max_len, window=64, lock_log=13):
+        starts = np.ascontiguousarray(starts, np.uint64)
+        n = starts.size
+        searched = np.empty(n + 1, np.uint64)
+        cyc_count = np.empty(n + 1, np.uint64)
+        cap_c = 500 * (n + 1)
+        cyc_len = np.empty(cap_c, np.uint64)
+        nodes = np.empty(cap_c * (max_len + 1), np.uint64)
+        ns, nc, nn = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+        stats = np.zeros(6, np.uint64)
+        r = lib().emu_find_cycles(self.h, starts.ctypes.data, n, min_len, max_len, window, lock_log,
+                                  searched.ctypes.data, C.byref(ns), cyc_count.ctypes.data, cyc_len.ctypes.data,
+                                  C.byref(nc), nodes.ctypes.data, C.byref(nn), stats.ctypes.data)
+        assert r == 0
+        out = []
+        ci = ni = 0
+        for i in range(ns.value):
+            paths = []
+            for _ in range(int(cyc_count[i])):
+                ln = int(cyc_len[ci])
+                ci += 1
+                paths.append(nodes[ni:ni + ln].copy())
+                ni += ln
+            out.append((int(searched[i]), paths))
+        return out, dict(zip(("skipped", "bound", "cap", "reruns", "rounds", "overflow_reruns"), map(int, stats)))

@@ -40,3 +40,22 @@ def unpack_sdbg_files(name, dst):
         with gzip.open(os.path.join(src, fn), "rb") as fi, open(os.path.join(dst, fn[:-3]), "wb") as fo:
             shutil.copyfileobj(fi, fo)
     return os.path.join(dst, "graph")
+
+
+def pack_raw(raw):
+    """Unpacked golden arrays -> MEGAHIT's in-memory packing (include/mcaat_gpu.h mg_graph_desc):
+    w 16 nibbles per uint64 (little-endian nibble order), last/tip 64 bits per uint64."""
+    n = raw["w"].size
+    w = np.zeros((n + 15) // 16 * 16, np.uint8)
+    w[:n] = raw["w"]
+    w8 = (w[0::2] | (w[1::2] << 4)).astype(np.uint8)
+    pad = (-w8.size) % 8
+    w64 = np.concatenate([w8, np.zeros(pad, np.uint8)]).view("<u8").copy()
+
+    def bits(a):
+        b = np.packbits(a.astype(np.uint8), bitorder="little")
+        pad = (-b.size) % 8
+        return np.concatenate([b, np.zeros(pad, np.uint8)]).view("<u8").copy()
+
+    return dict(n=n, k=raw["k"], w=w64, last=bits(raw["last"]), tip=bits(raw["tip"]),
+                mult=np.ascontiguousarray(raw["mult"], np.uint16), f=np.ascontiguousarray(raw["f"], np.int64))
