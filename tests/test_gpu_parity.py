@@ -1,0 +1,120 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (libmcaat_gpu.so), against the
+golden dumps of the UNMODIFIED reference CycleFinder at threads=1 and against the oracle.
+Bit-exact: invalid bitmap, ordered start lists per bucket, raw per-start cycle sequences."""
+import numpy as np
+import pytest
+
+import golden_util as G
+import oracle_py as O
+from mcaat_b200 import CycleFinder, DeviceGraph, Settings, gpu
+
+pytestmark = pytest.mark.gpu
+
+_packed = {}
+
+
+def packed(name):
+    if name not in _packed:
+        _packed[name] = G.pack_raw(G.load_graph_npz(name))
+    return _packed[name]
+
+
+def run_gpu(g, thr, mn, mx):
+    s = Settings(quiet=True)
+    s.sdbg = g
+    s.cycle_finder_settings.threshold_multiplicity = thr
+    s.cycle_finder_settings.cycle_min_length = mn
+    s.cycle_finder_settings.cycle_max_length = mx
+    cf = CycleFinder(s)
+    r = O.Run()
+    r.n_items = g.n
+    r.invalid = g.invalid()
+    r.buckets = cf.start_nodes_chunked
+    r.searched = list(cf.results.items())
+    r.stats = cf.stats
+    return r
+
+
+def test_navigation_matches_reference_api():
+    z = np.load(G.GOLD + "/tiny.nav.npz")
+    g = DeviceGraph(packed("tiny"))
+    od, idg, o, i_, m = g.navigate()
+    assert np.array_equal(od, z["od"]) and np.array_equal(idg, z["id"])
+    assert np.array_equal(o.astype(np.int64), z["o"]) and np.array_equal(i_.astype(np.int64), z["i"])
+    assert np.array_equal(m, z["m"])
+    before = gpu.launch_count()
+    g.navigate(0, 100)
+    assert gpu.launch_count() > before
+
+
+@pytest.mark.parametrize("name,thr,mn,mx,dump", G.cases(),
+                         ids=lambda v: str(v) if not isinstance(v, str) or "/" not in v else "")
+def test_cuda_matches_reference_dump(name, thr, mn, mx, dump):
+    ref = O.parse_dump(dump)
+    got = run_gpu(DeviceGraph(packed(name)), thr, mn, mx)
+    assert O.same_run(ref, got) == []
+
+
+def test_prune_stats_match_oracle():
+    raw = G.load_graph_npz("strain")
+    og = O.OracleGraph.from_arrays(raw["w"], raw["last"], raw["tip"], raw["mult"], raw["f"], raw["k"])
+    want = og.run(20, 27, 77).stats
+    g = DeviceGraph(packed("strain"))
+    st = g.prune()
+    for k in ("n_tips_before", "n_mult1", "n_tips_after", "n_valid"):
+        assert st[k] == want[k], k
+    cand = g.candidates(20)
+    assert cand.size == want["n_candidates"]
+    ok, exp = g.dls(cand, 77)
+    assert exp == want["dls_expansions"]
+
+
+def test_reset_gives_identical_second_run():
+    g = DeviceGraph(packed("repeatrich"))
+    a = run_gpu(g, 20, 27, 77)
+    g.reset()
+    b = run_gpu(g, 20, 27, 77)
+    assert O.same_run(a, b) == []
+
+
+def test_small_arenas_take_the_exact_fallback_tiers(monkeypatch):
+    """tier-1 set overflow -> bitmap tier; slot overflow -> large arena; tiny windows -> many rounds"""
+    monkeypatch.setenv("MCAAT_DLS_LOG2CAP", "6")
+    monkeypatch.setenv("MCAAT_ENUM_LOCK_LOG", "8")
+    monkeypatch.setenv("MCAAT_ENUM_SLOTS_PER_SM", "1")
+    name, thr, mn, mx, dump = [c for c in G.cases() if c[0] == "repeatrich" and c[1] == 5][0]
+    ref = O.parse_dump(dump)
+    got = run_gpu(DeviceGraph(packed(name)), thr, mn, mx)
+    assert O.same_run(ref, got) == []
+
+
+def test_cluster_bound_case():
+    name, thr, mn, mx, dump = [c for c in G.cases() if c[0] == "biallelic"][0]
+    got = run_gpu(DeviceGraph(packed(name)), thr, mn, mx)
+    assert got.stats["n_bound_hits"] >= 1
+
+
+def test_visited_equals_union_of_cycle_nodes():
+    g = DeviceGraph(packed("repeatrich"))
+    r = run_gpu(g, 20, 27, 77)
+    want = np.zeros(g.n, bool)
+    for _, paths in r.searched:
+        for p in paths:
+            want[p.astype(np.int64)] = True
+    assert np.array_equal(g.visited(), want)
+
+
+def test_empty_and_degenerate_inputs():
+    g = DeviceGraph(packed("tiny"))
+    g.prune()
+    searched, st = g.find_cycles([], 27, 77)
+    assert searched == [] and st["n_cycles"] == 0
+    ok, _ = g.dls([], 77)
+    assert ok.size == 0
+    with pytest.raises(gpu.MgError):
+        g.find_cycles([g.n + 5], 27, 77)
+    # a start that is not on any cycle yields an empty entry, like results[start] = {} in the reference
+    inv = g.invalid()
+    v = int(np.nonzero(~inv)[0][0])
+    searched, _ = g.find_cycles([v], 27, 77)
+    assert len(searched) == 1 and searched[0][0] == v
