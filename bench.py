@@ -1,0 +1,391 @@
+#!/usr/bin/env python3
+"""bench.py — MCAAT cycle-search hot path on B200 (BASELINE.json metric: cycle-search start nodes/s
+and cycle-find wall time).
+
+A "step" is one full pass of the hot path over the resident graph: reset -> prune (tips,
+multiplicity filter, peel) -> start-node selection (candidate scan + admission search) -> ordered
+cycle enumeration, results back on the host (reference src/cycle_finder.cpp:433-492).
+Workload: BASELINE.json configs[1] — synthetic 50-genome community (+5 strain copies), ~200M-item
+SDBG built on the GPU by tools/synth_sdbg.py (pinned against the reference's own graph producer),
+default cycle bounds 27-77, multiplicity threshold 20.
+
+  python bench.py --gpus 1 --steps K --warmup W            our arm (CUDA, libmcaat_gpu.so)
+  python bench.py --impl reference ...                     the reference's CPU CycleFinder (oracle/_ref)
+  torchrun ... bench.py --gpus N ...                       N ranks: NCCL broadcast of the raw graph,
+                                                           admission searches sharded over ranks
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tools")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "cycle_search_start_nodes_per_sec"
+UNIT = "start_nodes/s"
+THR, MIN_LEN, MAX_LEN = 20, 27, 77
+# algorithmic bytes per unit of work
+BYTES_STREAM_NODE = 2.875   # W 4 bit + last/tip/invalid 3 bit + uint16 multiplicity, per node per pass
+BYTES_EXPANSION = 256.0     # 8 sectors per node expansion (layout-independent nominal)
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.proc = None
+        self.idx = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) > 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) > 8 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) > 8:
+                for nm, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+def unpack_for_oracle(g):
+    n = g["n"]
+    w8 = g["w"].view(np.uint8)
+    w = np.empty(w8.size * 2, np.uint8)
+    w[0::2] = w8 & 15
+    w[1::2] = w8 >> 4
+    last = np.unpackbits(g["last"].view(np.uint8), bitorder="little")[:n]
+    tip = np.unpackbits(g["tip"].view(np.uint8), bitorder="little")[:n]
+    return w[:n], last, tip
+
+
+def hot_path_step(g, rank=0, world=1, dist=None, torch=None):
+    """One pass of the hot path through the C ABI.  With world > 1 the admission searches
+    (DepthLevelSearch, the dominant phase) are sharded block-cyclically over the ranks and their
+    pass flags all-gathered; prune / candidate scan / ordered enumeration run replicated (no
+    collective inside a search)."""
+    g.reset()
+    st = g.prune()
+    cand = g.candidates(THR)
+    if world == 1:
+        ok, exp = g.dls(cand, MAX_LEN)
+    else:
+        mine = cand[rank::world]
+        ok_m, exp = g.dls(mine, MAX_LEN)
+        per = (cand.size + world - 1) // world
+        buf = torch.zeros(per, dtype=torch.uint8, device="cuda")
+        buf[:ok_m.size] = torch.from_numpy(ok_m.astype(np.uint8)).cuda()
+        out = [torch.empty_like(buf) for _ in range(world)]
+        dist.all_gather(out, buf)
+        ok = np.zeros(cand.size, bool)
+        for r in range(world):
+            part = out[r].cpu().numpy().astype(bool)
+            cnt = cand[r::world].size
+            ok[r::world] = part[:cnt]
+        e = torch.tensor([exp], dtype=torch.int64, device="cuda")
+        dist.all_reduce(e)
+        exp = int(e.item())
+    buckets, _ = g.bucket_starts(cand[ok])
+    starts = np.concatenate([ids for _, ids in buckets]) if buckets else np.zeros(0, np.uint64)
+    searched, cs = g.find_cycles(starts, MIN_LEN, MAX_LEN)
+    res_bytes = 8 * (sum(sum(p.size for p in paths) for _, paths in searched) + len(searched))
+    stats = dict(st, n_candidates=int(cand.size), n_starts=int(starts.size), dls_expansions=int(exp), **cs)
+    return stats, res_bytes
+
+
+def cpu_baseline_port(sample_name, device):
+    """Oracle port (oracle/mcaat_oracle.c, 1 thread) on the bounded sample workload."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as O
+    import synth_sdbg as S
+    g, info = S.make_workload(sample_name, device=device)
+    w, last, tip = unpack_for_oracle(g)
+    og = O.OracleGraph.from_arrays(w, last, tip, g["mult"], g["f"], g["k"])
+    t0 = time.perf_counter()
+    r = og.run(THR, MIN_LEN, MAX_LEN)
+    dt = time.perf_counter() - t0
+    n_starts = int(r.start_list().size)
+    return dict(value=n_starts / dt, unit=UNIT, cores=1, kind="port",
+                sample=f"workload '{sample_name}' (same recipe at 1/20 scale): {g['n']} items, {n_starts} start nodes, "
+                       f"{dt:.2f} s for the whole search with oracle/mcaat_oracle.c on 1 thread",
+                seconds=dt, n_items=int(g["n"]), n_starts=n_starts)
+
+
+def reference_arm(args):
+    """--impl reference: the reference's own CPU CycleFinder (oracle/_ref/ref_cyclefinder, compiled from the
+    unmodified sources) with all host threads, on the bounded sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as O
+    import synth_sdbg as S
+    try:
+        import torch
+        device = "cuda" if torch.cuda.is_available() else "cpu"
+    except Exception:
+        device = "cpu"
+    cores = os.cpu_count() or 1
+    g, info = S.make_workload(args.sample, device=device, want_labels=True)
+    exe = O.ref_binary("ref_cyclefinder")
+    times, n_starts, kind = [], 0, "reference"
+    if exe:
+        tmp = tempfile.mkdtemp(prefix="mcaat_ref_")
+        prefix = os.path.join(tmp, "graph")
+        S.write_megahit_files(g, prefix)
+        env = dict(os.environ, MCAAT_REF_COUNT_STARTS="1")
+        for i in range(args.warmup + args.steps):
+            out = subprocess.run([exe, prefix, "-", str(cores), str(THR), str(MIN_LEN), str(MAX_LEN)], check=True,
+                                 capture_output=True, text=True, env=env).stdout
+            js = json.loads([ln for ln in out.splitlines() if ln.startswith("REF_JSON ")][0][9:])
+            n_starts = js["start_nodes"]
+            if i >= args.warmup:
+                times.append(js["ctor_s"])
+    else:  # reference binary absent: the oracle port is the CPU implementation
+        kind, cores = "port", 1
+        w, last, tip = unpack_for_oracle(g)
+        for i in range(args.warmup + args.steps):
+            og = O.OracleGraph.from_arrays(w, last, tip, g["mult"], g["f"], g["k"])
+            t0 = time.perf_counter()
+            r = og.run(THR, MIN_LEN, MAX_LEN)
+            if i >= args.warmup:
+                times.append(time.perf_counter() - t0)
+            n_starts = int(r.start_list().size)
+    dt = float(np.mean(times))
+    val = n_starts / dt
+    sample = (f"workload '{args.sample}' (same recipe at 1/20 scale): {g['n']} items, {n_starts} start nodes; "
+              f"CycleFinder constructor {dt:.2f} s with {cores} threads")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: BASELINE.json configs[1]; timed on the bounded sample '{args.sample}'",
+                   "sample_n_items": int(g["n"]), "threshold_multiplicity": THR,
+                   "cycle_min_length": MIN_LEN, "cycle_max_length": MAX_LEN},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def pinned(a, torch):
+    """numpy array -> numpy view of a pinned (page-locked) copy"""
+    t = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).copy()).pin_memory()
+    return t, t.numpy().view(a.dtype)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--sample", default="c2_sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import synth_sdbg as S
+    from mcaat_b200 import DeviceGraph, gpu
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback (use --impl reference for the CPU arm)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    # ---- workload: built on the GPU by rank 0; raw arrays broadcast over NCCL (NVLink) to the other ranks
+    t_gen = time.perf_counter()
+    if rank == 0:
+        graph, info = S.make_workload(args.workload, device="cuda")
+        torch.cuda.empty_cache()
+    if world > 1:
+        meta = [dict(n=graph["n"], k=graph["k"], f=[int(x) for x in graph["f"]], info=info,
+                     sizes=[graph[k].size for k in ("w", "last", "tip", "mult")])] if rank == 0 else [None]
+        dist.broadcast_object_list(meta, src=0)
+        m = meta[0]
+        dev = {}
+        tb = time.perf_counter()
+        for key, size, dt in zip(("w", "last", "tip", "mult"), m["sizes"], (torch.int64, torch.int64, torch.int64, torch.int16)):
+            if rank == 0:
+                t = torch.from_numpy(graph[key].view(np.int64 if dt == torch.int64 else np.int16)).cuda()
+            else:
+                t = torch.empty(size, dtype=dt, device="cuda")
+            dist.broadcast(t, src=0)
+            dev[key] = t
+        torch.cuda.synchronize()
+        bcast_s = time.perf_counter() - tb
+        packed_dev = dict(n=m["n"], k=m["k"], f=np.array(m["f"], np.int64), **dev)
+        info = m["info"]
+        g = DeviceGraph(packed_dev, device=local, memory=gpu.MG_MEM_DEVICE)
+        n_items = m["n"]
+    else:
+        bcast_s = 0.0
+        g = DeviceGraph(graph, device=local)
+        n_items = graph["n"]
+    gen_s = time.perf_counter() - t_gen
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up, then EXACTLY --steps timed steps
+    for _ in range(args.warmup):
+        stats, res_bytes = hot_path_step(g, rank, world, dist, torch)
+    g.timers_reset()
+    launches0 = gpu.launch_count()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    barrier()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    for _ in range(args.steps):
+        g.step_begin()
+        stats, res_bytes = hot_path_step(g, rank, world, dist, torch)
+        dev_ms += g.step_end()
+    barrier()
+    wall = time.perf_counter() - t0
+    launches = gpu.launch_count() - launches0
+    timers = g.timers()
+    clk = clocks.stop() if rank == 0 else None
+    # max over ranks of the CUDA-event time of the K steps
+    if world > 1:
+        t = torch.tensor([dev_ms, wall * 1e3], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, wall_ms = float(t[0]), float(t[1])
+        lt = torch.tensor([launches], dtype=torch.int64, device="cuda")
+        dist.all_reduce(lt)
+        launches = int(lt.item())
+    else:
+        wall_ms = wall * 1e3
+    ms_per_step = dev_ms / args.steps
+    value = stats["n_starts"] / (ms_per_step / 1e3)
+
+    # ---- end to end through the C ABI with HOST buffers (N = 1): upload + index build + search + read-back
+    e2e = None
+    if world == 1 and not args.no_e2e:
+        keep, host = [], dict(n=graph["n"], k=graph["k"], f=graph["f"])
+        for key in ("w", "last", "tip", "mult"):
+            t, v = pinned(graph[key], torch)
+            keep.append(t)
+            host[key] = v
+        h2d = sum(host[k].nbytes for k in ("w", "last", "tip", "mult"))
+        g.close()
+        e2e_t = []
+        for i in range(1 + max(1, min(args.steps, 2))):
+            torch.cuda.synchronize()
+            ta = time.perf_counter()
+            g2 = DeviceGraph(host, device=local)
+            st2, rb = hot_path_step(g2)
+            inv = g2.invalid_words()
+            torch.cuda.synchronize()
+            tb_ = time.perf_counter()
+            g2.close()
+            if i > 0:
+                e2e_t.append(tb_ - ta)
+        dt = float(np.mean(e2e_t))
+        e2e = dict(value=st2["n_starts"] / dt, unit=UNIT, h2d_bytes_per_step=int(h2d),
+                   d2h_bytes_per_step=int(inv.nbytes + rb), ms_per_step=dt * 1e3)
+
+    if rank != 0:
+        return
+    # ---- roofline of the dominant kernel family (CUDA-event time accumulated inside the library)
+    peak, peak_kind = peaks()
+    alg = {  # algorithmic bytes per step and family
+        "collect_tips": n_items * BYTES_STREAM_NODE, "invalidate_mult1": n_items * BYTES_STREAM_NODE,
+        "nav_cache": n_items * BYTES_STREAM_NODE, "candidates": n_items * BYTES_STREAM_NODE,
+        "peel": stats["n_peeled"] * BYTES_EXPANSION, "dls": stats["dls_expansions"] / world * BYTES_EXPANSION,
+        "enumerate": stats["expansions"] * BYTES_EXPANSION,
+    }
+    fam = {k: v for k, v in timers.items() if k in alg and v["launches"]}
+    top = max(fam, key=lambda k: fam[k]["ms"])
+    per_launch_ms = fam[top]["ms"] / fam[top]["launches"]
+    launches_per_step = fam[top]["launches"] / args.steps
+    achieved = alg[top] / launches_per_step / (per_launch_ms * 1e-3) / 1e9
+    roofline = dict(bound="hbm", kernel=top, achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
+                    traffic=None, peak_source=peak_kind, ms_per_launch=per_launch_ms,
+                    algorithmic_bytes_per_launch=alg[top] / launches_per_step)
+    phases = {k: round(v["ms"] / args.steps, 3) for k, v in timers.items() if v["launches"]}
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_port(args.sample, "cuda")
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: BASELINE.json configs[1], synthetic 50-genome community + 5 strain copies, "
+                               f"{n_items} SDBG items (k=23), built by tools/synth_sdbg.py",
+                   "n_items": int(n_items), "threshold_multiplicity": THR, "cycle_min_length": MIN_LEN,
+                   "cycle_max_length": MAX_LEN, "l2": "graph arrays + navigation cache (>2 GB) exceed the 126 MB L2; "
+                                                       "no explicit flush", "parallelism": f"dls-shard x{world}",
+                   "timing": "CUDA events on the library stream around each step (mg_step_begin/end), max over ranks"},
+        "cycle_find_wall_ms": wall_ms / args.steps, "gpu_launches": int(launches), "clocks": clk,
+        "counts": {k: stats[k] for k in ("n_tips_before", "n_mult1", "n_peeled", "n_valid", "n_tips_after", "n_candidates",
+                                          "n_starts", "n_searched", "n_cycles", "n_skipped", "n_bound_hits", "n_cap_hits",
+                                          "n_reruns", "n_rounds", "dls_expansions", "expansions")},
+        "phase_ms_per_step": phases,
+        "rates": {"nodes_scanned_per_s": n_items / (ms_per_step / 1e3),
+                  "candidates_per_s": stats["n_candidates"] / max(phases.get("dls", 0) / 1e3, 1e-9),
+                  "edges_traversed_per_s": (stats["dls_expansions"] + stats["expansions"] + stats["n_peeled"]) / (ms_per_step / 1e3)},
+        "roofline": roofline, "setup": {"generate_s": round(gen_s, 2), "nccl_broadcast_s": round(bcast_s, 4),
+                                        "graph_device_bytes": g.device_bytes() if g.h else None},
+    }
+    if e2e:
+        line["e2e"] = e2e
+    if cpu:
+        line["cpu_baseline"] = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -155,6 +155,11 @@ int mg_visited_readback(mg_graph *g, uint64_t *host_words);
  * (<= cap). */
 int mg_timers(mg_graph *g, const char **names, double *ms, uint64_t *launches, uint64_t *units, int cap);
 void mg_timers_reset(mg_graph *g);
+/* Whole-step device timing: mg_step_begin records a CUDA event on the graph's stream, mg_step_end
+ * records a second one, waits for it and returns the elapsed milliseconds between the two (kernel
+ * time plus the gaps in which the stream waited for the host). */
+int mg_step_begin(mg_graph *g);
+int mg_step_end(mg_graph *g, double *elapsed_ms);
 /* kernels launched by this library in this process so far */
 uint64_t mg_launch_count(void);
 

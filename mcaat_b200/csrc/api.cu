@@ -109,6 +109,8 @@ void mg_graph_destroy(mg_graph *g) {
   if (g->stream) cudaStreamSynchronize(g->stream);
   flush_timers(g);
   for (auto e : g->event_pool) cudaEventDestroy(e);
+  if (g->step_a) cudaEventDestroy(g->step_a);
+  if (g->step_b) cudaEventDestroy(g->step_b);
   if (g->stream) cudaStreamDestroy(g->stream);
   delete g;
 }
@@ -266,6 +268,23 @@ int mg_timers(mg_graph *g, const char **names, double *ms, uint64_t *launches, u
     if (units) units[i] = g->t_units[i];
   }
   return n;
+}
+int mg_step_begin(mg_graph *g) {
+  MG_CHECK_HANDLE(g);
+  if (!g->step_a) MG_CUDA(cudaEventCreate(&g->step_a));
+  if (!g->step_b) MG_CUDA(cudaEventCreate(&g->step_b));
+  MG_CUDA(cudaEventRecord(g->step_a, g->stream));
+  return MG_OK;
+}
+int mg_step_end(mg_graph *g, double *elapsed_ms) {
+  MG_CHECK_HANDLE(g);
+  if (!g->step_a || !g->step_b || !elapsed_ms) { set_error("mg_step_end without mg_step_begin"); return MG_EINVAL; }
+  MG_CUDA(cudaEventRecord(g->step_b, g->stream));
+  MG_CUDA(cudaEventSynchronize(g->step_b));
+  float ms = 0.f;
+  MG_CUDA(cudaEventElapsedTime(&ms, g->step_a, g->step_b));
+  *elapsed_ms = ms;
+  return MG_OK;
 }
 void mg_timers_reset(mg_graph *g) {
   if (!g) return;

@@ -108,6 +108,7 @@ struct mg_graph {
   struct Pending { int id; cudaEvent_t a, b; };
   std::vector<Pending> pending;
   std::vector<cudaEvent_t> event_pool;
+  cudaEvent_t step_a = nullptr, step_b = nullptr;
 };
 
 namespace mg {

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(128) k_dls(const uint64_t *__restrict__ adj, c
     exp = 0;
     int r = dls_run(adj, cand[idx], limit, seen, stk_node, stk_depth, A.stk_cap, exp);
     result[idx] = (int8_t)r;
-    exp_total += exp;
+    if (r >= 0) exp_total += exp;  // a search that filled its set is repeated (and counted) by tier 2
     for (uint32_t j = 0; j < seen.count; ++j) seen.tab[seen.log[j]] = kNull;  // undo
   }
   for (int d = 16; d; d >>= 1) exp_total += __shfl_down_sync(0xffffffffu, exp_total, d);

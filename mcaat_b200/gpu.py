@@ -22,7 +22,7 @@ SYMBOLS = [
     "mg_graph_create", "mg_graph_destroy", "mg_graph_reset", "mg_graph_size", "mg_graph_device_bytes",
     "mg_navigate", "mg_prune", "mg_invalid_readback", "mg_candidates", "mg_dls", "mg_select_starts",
     "mg_bucket_starts", "mg_starts_free", "mg_find_cycles", "mg_cycles_free", "mg_visited_readback",
-    "mg_timers", "mg_timers_reset", "mg_launch_count", "mg_free", "mg_last_error", "mg_version",
+    "mg_timers", "mg_timers_reset", "mg_step_begin", "mg_step_end", "mg_launch_count", "mg_free", "mg_last_error", "mg_version",
 ]
 
 
@@ -91,6 +91,8 @@ def lib():
         L.mg_timers.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.mg_timers_reset.argtypes = [C.c_void_p]
         L.mg_timers_reset.restype = None
+        L.mg_step_begin.argtypes = [C.c_void_p]
+        L.mg_step_end.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.mg_launch_count.restype = C.c_uint64
         L.mg_free.argtypes = [C.c_void_p]
         L.mg_free.restype = None
@@ -271,3 +273,11 @@ class DeviceGraph:
 
     def timers_reset(self):
         lib().mg_timers_reset(self.h)
+
+    def step_begin(self):
+        _check(lib().mg_step_begin(self.h))
+
+    def step_end(self):
+        ms = C.c_double(0)
+        _check(lib().mg_step_end(self.h, C.byref(ms)))
+        return ms.value

@@ -96,6 +96,21 @@ def build_community(args, rng):
             hap = genomes[g][lo:hi].copy()
             hap[pos - lo:pos - lo + alt.size] = alt
             alt_haplotypes.append(hap)
+    for a in range(getattr(args, "bound_arrays", 0)):
+        # large arrays whose spacers carry 2 alleles at 2 independent sites: >= 500 cycles through the
+        # repeat, the reference's cluster-bound case (src/cycle_finder.cpp:162-165)
+        g = (args.arrays + a) % len(genomes)
+        repeat = rand_seq(rng, args.repeat_len)
+        seq, alts = make_array(rng, repeat, 150, 38, 38, 2, 2)
+        pos = 1000 + int(rng.integers(0, max(1, genomes[g].size - seq.size - 2000)))
+        genomes[g][pos:pos + seq.size] = seq
+        truth.append({"genome": g, "pos": pos, "repeat": bytes(repeat).decode(), "spacers": 150, "biallelic": True})
+        for alt in alts:
+            lo = max(0, pos - args.frag_max)
+            hi = min(genomes[g].size, pos + seq.size + args.frag_max)
+            hap = genomes[g][lo:hi].copy()
+            hap[pos - lo:pos - lo + alt.size] = alt
+            alt_haplotypes.append(hap)
     abund = np.ones(len(genomes))
     if args.abundance_sigma > 0:
         abund = rng.lognormal(0.0, args.abundance_sigma, size=len(genomes))
@@ -165,32 +180,39 @@ def write_fastq(path, reads, tag):
             rec[i:i + step].tofile(f)
 
 
+ARGSPEC = [
+    ("--out", dict(required=True)),
+    ("--seed", dict(type=int, default=11)),
+    ("--genomes", dict(type=int, default=5)),
+    ("--genome-len", dict(type=int, default=2_000_000)),
+    ("--arrays", dict(type=int, default=10)),
+    ("--repeat-len", dict(type=int, default=30)),
+    ("--spacer-min-len", dict(type=int, default=32)),
+    ("--spacer-max-len", dict(type=int, default=38)),
+    ("--spacers-min", dict(type=int, default=15)),
+    ("--spacers-max", dict(type=int, default=40)),
+    ("--shared-family-arrays", dict(type=int, default=0)),
+    ("--biallelic-arrays", dict(type=int, default=0)),
+    ("--alleles", dict(type=int, default=2, help="alleles per spacer in the multi-allelic arrays (<= 4)")),
+    ("--sites", dict(type=int, default=1, help="variant sites per spacer in those arrays (1 or 2)")),
+    ("--bound-arrays", dict(type=int, default=0, help="extra 150-spacer arrays with 2 alleles at 2 sites")),
+    ("--strain-pairs", dict(type=int, default=0)),
+    ("--strain-snp", dict(type=float, default=0.01)),
+    ("--tandem", dict(type=int, default=0)),
+    ("--tandem-div", dict(type=float, default=0.03)),
+    ("--abundance-sigma", dict(type=float, default=0.0)),
+    ("--pairs", dict(type=int, default=1_000_000)),
+    ("--read-len", dict(type=int, default=150)),
+    ("--frag-min", dict(type=int, default=300)),
+    ("--frag-max", dict(type=int, default=400)),
+    ("--error-rate", dict(type=float, default=0.0)),
+]
+
+
 def main(argv=None):
     p = argparse.ArgumentParser()
-    p.add_argument("--out", required=True)
-    p.add_argument("--seed", type=int, default=11)
-    p.add_argument("--genomes", type=int, default=5)
-    p.add_argument("--genome-len", type=int, default=2_000_000)
-    p.add_argument("--arrays", type=int, default=10)
-    p.add_argument("--repeat-len", type=int, default=30)
-    p.add_argument("--spacer-min-len", type=int, default=32)
-    p.add_argument("--spacer-max-len", type=int, default=38)
-    p.add_argument("--spacers-min", type=int, default=15)
-    p.add_argument("--spacers-max", type=int, default=40)
-    p.add_argument("--shared-family-arrays", type=int, default=0)
-    p.add_argument("--biallelic-arrays", type=int, default=0)
-    p.add_argument("--alleles", type=int, default=2, help="alleles per spacer in the multi-allelic arrays (<= 4)")
-    p.add_argument("--sites", type=int, default=1, help="variant sites per spacer in those arrays (1 or 2)")
-    p.add_argument("--strain-pairs", type=int, default=0)
-    p.add_argument("--strain-snp", type=float, default=0.01)
-    p.add_argument("--tandem", type=int, default=0)
-    p.add_argument("--tandem-div", type=float, default=0.03)
-    p.add_argument("--abundance-sigma", type=float, default=0.0)
-    p.add_argument("--pairs", type=int, default=1_000_000)
-    p.add_argument("--read-len", type=int, default=150)
-    p.add_argument("--frag-min", type=int, default=300)
-    p.add_argument("--frag-max", type=int, default=400)
-    p.add_argument("--error-rate", type=float, default=0.0)
+    for name, kw in ARGSPEC:
+        p.add_argument(name, **kw)
     args = p.parse_args(argv)
     rng = np.random.Generator(np.random.PCG64(args.seed))
     os.makedirs(args.out, exist_ok=True)
