@@ -32,45 +32,79 @@ __global__ void k_mult1(GraphView g, unsigned long long *count) {
     atomicAdd(count, (unsigned long long)__popc(m));
   }
 }
-// RecursiveReduction: one thread per work item follows its chain with a small private stack;
-// parents that do not fit go to the next work list.
-constexpr int kPeelLocal = 24;
-__global__ void k_peel(GraphView g, const uint32_t *work, uint32_t n_work, uint32_t *next, uint32_t *next_count,
-                       uint32_t next_cap, unsigned long long *peeled, int *overflow) {
+// ---- RecursiveReduction by chain contraction (search_dev.cuh, "peel") -------------------------
+// step 1: navigation cache on the post-filter graph, chain / seed bitmaps, chain pointers
+__global__ void k_chain_init(GraphView g, PeelView P, unsigned long long *n_pairs) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t cnt = 0;
-  if (i < n_work) {
-    uint32_t lst[kPeelLocal];
-    int sp = 0;
-    lst[sp++] = work[i];
-    while (sp) {
-      uint32_t v = lst[--sp];
-      cnt += peel_one(g, v, [&](uint32_t p) {
-        if (sp < kPeelLocal) {
-          lst[sp++] = p;
-        } else {
-          uint32_t idx = atomicAdd(next_count, 1u);
-          if (idx < next_cap) next[idx] = p;
-          else *overflow = 1;
-        }
-      });
-    }
+  bool is_chain = false, is_seed = false;
+  int deg = -1;
+  if (i < g.n) deg = chain_init_item(g, P, (uint32_t)i, is_chain, is_seed);
+  unsigned mc = __ballot_sync(0xffffffffu, is_chain), ms = __ballot_sync(0xffffffffu, is_seed);
+  unsigned pairs = deg >= 2 ? (unsigned)deg : 0u;
+  for (int d = 16; d; d >>= 1) pairs += __shfl_down_sync(0xffffffffu, pairs, d);
+  if ((threadIdx.x & 31) == 0 && i < g.n) {
+    P.chain[i >> 5] = mc;
+    P.tpeeled[i >> 5] = ms;
+    if (pairs) atomicAdd(n_pairs, (unsigned long long)pairs);
   }
-  for (int d = 16; d; d >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, d);
-  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(peeled, (unsigned long long)cnt);
 }
-// navigation cache + "After pruning" statistics (:443-452): valid count and tips
-__global__ void k_adj(GraphView g, uint64_t *adj, unsigned long long *n_valid, unsigned long long *n_tips) {
+// step 2: one pointer-jumping round
+__global__ void k_chain_jump(uint64_t n, PeelView P, int *unresolved) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool valid = false, tip = false;
+  bool u = i < n && chain_jump_item(P, (uint32_t)i);
+  if (__any_sync(0xffffffffu, u) && (threadIdx.x & 31) == 0) *unresolved = 1;
+}
+// step 3a: (terminal -> dependent branch node) multimap
+__global__ void k_dep_register(GraphView g, PeelView P) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < g.n) dep_register_item(g, P, (uint32_t)i);
+}
+// step 3b: asynchronous work list over peeled terminals; each thread follows its cascade with a
+// small private stack, the rest goes to the next work list
+constexpr int kPeelLocal = 24;
+__global__ void k_cpeel(PeelView P, const uint32_t *work, uint32_t n_work, uint32_t *next, uint32_t *next_count,
+                        uint32_t next_cap, int *overflow) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_work) return;
+  uint32_t lst[kPeelLocal];
+  int sp = 0;
+  lst[sp++] = work[i];
+  while (sp) {
+    uint32_t t = lst[--sp];
+    cpeel_one(P, t, [&](uint32_t b) {
+      if (sp < kPeelLocal) {
+        lst[sp++] = b;
+      } else {
+        uint32_t idx = atomicAdd(next_count, 1u);
+        if (idx < next_cap) next[idx] = b;
+        else *overflow = 1;
+      }
+    });
+  }
+}
+// step 4: invalid bits of the removed items, final navigation cache, "After pruning" statistics
+// (:443-452): valid count and tips
+__global__ void k_peel_final(GraphView g, PeelView P, unsigned long long *n_peeled, unsigned long long *n_valid,
+                             unsigned long long *n_tips) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool peeled = false, valid = false, tip = false;
+  uint64_t a = 0;
   if (i < g.n) {
-    valid = !get_inv(g, (uint32_t)i);
-    uint64_t a = adj_encode(g, (uint32_t)i);
-    adj[i] = a;
+    a = peel_final_item(g, P, (uint32_t)i, peeled);
+    valid = !peeled && !get_inv(g, (uint32_t)i);
     tip = valid && (a >> 32) == 0;
   }
-  unsigned mv = __ballot_sync(0xffffffffu, valid), mt = __ballot_sync(0xffffffffu, tip);
-  if ((threadIdx.x & 31) == 0) {
+  unsigned mp = __ballot_sync(0xffffffffu, peeled), mv = __ballot_sync(0xffffffffu, valid),
+           mt = __ballot_sync(0xffffffffu, tip);
+  __syncwarp();
+  if (i < g.n) P.adj[i] = a;  // every lane has finished reading adj[] of its own item; children's entries
+                              // are only read through chain/ptr/tpeeled, never through adj[]
+  if ((threadIdx.x & 31) == 0 && i < g.n) {
+    if (mp) {
+      uint32_t *w32 = (uint32_t *)&g.fb[i >> 8].inv[(i >> 6) & 3] + ((i >> 5) & 1);
+      *w32 |= mp;  // this warp owns the word
+      atomicAdd(n_peeled, (unsigned long long)__popc(mp));
+    }
     if (mv) atomicAdd(n_valid, (unsigned long long)__popc(mv));
     if (mt) atomicAdd(n_tips, (unsigned long long)__popc(mt));
   }
@@ -81,58 +115,92 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
   cudaStream_t s = g->stream;
   const uint64_t n = v.n;
   memset(st, 0, sizeof *st);
-  DevBuf counters;  // [0] tips before, [1] mult1, [2] peeled, [3] valid, [4] tips after, [5] next_count(u32), [6] overflow
+  // [0] tips before, [1] mult1, [2] peeled, [3] valid, [4] tips after, [5] pairs, [6] next_count(u32) | overflow, [7] unresolved
+  DevBuf counters;
   MG_TRY(counters.alloc(8 * 8));
   MG_CUDA(cudaMemsetAsync(counters.p, 0, 64, s));
   unsigned long long *c = counters.as<unsigned long long>();
   const unsigned grid = grid_for(n, 256);
+  const size_t bm_bytes = (size_t)((n + 31) / 32) * 4 + 16;
   // --- CollectTips on the loaded graph (:436)
-  DevBuf tipbits, work, next;
-  uint64_t n_work = 0;
-  MG_TRY(tipbits.alloc((size_t)((n + 31) / 32) * 4 + 16));
+  DevBuf tipbits;
+  MG_TRY(tipbits.alloc(bm_bytes));
   if (n) {
     TimedScope ts(g, T_TIPS, n);
     MG_LAUNCH(k_tips, grid, 256, 0, s, v, tipbits.as<uint32_t>(), c + 0);
   }
-  MG_TRY(bitmap_to_ids(tipbits.as<uint32_t>(), n, work, &n_work, s));
-  tipbits.release();
   // --- InvalidateMultiplicityOneNodes (:439)
   if (n) {
     TimedScope ts(g, T_MULT1, n);
     MG_LAUNCH(k_mult1, grid, 256, 0, s, v, c + 1);
   }
-  // --- RecursiveReduction for every tip (:440-442)
-  {
-    TimedScope ts(g, T_PEEL, n_work);
-    uint32_t next_cap = (uint32_t)(n < (1u << 20) ? (1u << 20) : n);
-    uint32_t *next_count = (uint32_t *)(c + 5);
-    int *overflow = (int *)(c + 6);
-    MG_TRY(next.alloc((size_t)next_cap * 4));
-    while (n_work) {
-      MG_CUDA(cudaMemsetAsync(next_count, 0, 4, s));
-      MG_LAUNCH(k_peel, grid_for(n_work, 128), 128, 0, s, v, work.as<uint32_t>(), (uint32_t)n_work,
-                next.as<uint32_t>(), next_count, next_cap, c + 2, overflow);
-      uint32_t h[4];
-      MG_CUDA(cudaMemcpyAsync(h, c + 5, 16, cudaMemcpyDeviceToHost, s));
-      MG_CUDA(cudaStreamSynchronize(s));
-      if (h[2]) {
-        set_error("peel: work list overflow (%u entries)", next_cap);
-        return MG_EINTERNAL;
-      }
-      n_work = h[0];
-      if (n_work) {
-        MG_TRY(work.ensure((size_t)n_work * 4));
-        MG_CUDA(cudaMemcpyAsync(work.p, next.p, (size_t)n_work * 4, cudaMemcpyDeviceToDevice, s));
-      }
-    }
-  }
-  next.release();
-  work.release();
-  // --- navigation cache, valid-edge count (:443-449) and CollectTips after pruning (:451)
+  // --- RecursiveReduction for every tip (:440-442), valid-edge count (:443-449), CollectTips (:451)
   MG_TRY(g->adj.ensure((size_t)n * 8 + 16));
   if (n) {
-    TimedScope ts(g, T_ADJ, n);
-    MG_LAUNCH(k_adj, grid, 256, 0, s, v, g->adj.as<uint64_t>(), c + 3, c + 4);
+    DevBuf ptr, chain, tpeeled, dep, work, next;
+    MG_TRY(ptr.alloc((size_t)n * 4 + 16));
+    MG_TRY(chain.alloc(bm_bytes));
+    MG_TRY(tpeeled.alloc(bm_bytes));
+    PeelView P;
+    P.adj = g->adj.as<uint64_t>();
+    P.ptr = ptr.as<uint32_t>();
+    P.chain = chain.as<uint32_t>();
+    P.tpeeled = tpeeled.as<uint32_t>();
+    P.tipbits = tipbits.as<uint32_t>();
+    P.dep = nullptr;
+    P.dep_log = 0;
+    {
+      TimedScope ts(g, T_ADJ, n);
+      MG_LAUNCH(k_chain_init, grid, 256, 0, s, v, P, c + 5);
+    }
+    uint64_t n_work = 0;
+    MG_TRY(bitmap_to_ids(tpeeled.as<uint32_t>(), n, work, &n_work, s));  // seeds
+    TimedScope ts(g, T_PEEL, n);
+    if (n_work) {
+      int *unresolved = (int *)(c + 7);
+      for (int round = 0; round < 34; round += 2) {
+        MG_CUDA(cudaMemsetAsync(unresolved, 0, 4, s));
+        MG_LAUNCH(k_chain_jump, grid, 256, 0, s, n, P, unresolved);
+        MG_LAUNCH(k_chain_jump, grid, 256, 0, s, n, P, unresolved);
+        int h = 0;
+        MG_CUDA(cudaMemcpyAsync(&h, unresolved, 4, cudaMemcpyDeviceToHost, s));
+        MG_CUDA(cudaStreamSynchronize(s));
+        if (!h) break;
+      }
+      unsigned long long pairs = 0;
+      MG_CUDA(cudaMemcpyAsync(&pairs, c + 5, 8, cudaMemcpyDeviceToHost, s));
+      MG_CUDA(cudaStreamSynchronize(s));
+      uint32_t dep_log = 10;
+      while (((uint64_t)1 << dep_log) < 2 * pairs + 16) ++dep_log;
+      MG_TRY(dep.alloc((size_t)8 << dep_log));
+      MG_CUDA(cudaMemsetAsync(dep.p, 0xFF, dep.bytes, s));
+      P.dep = dep.as<uint64_t>();
+      P.dep_log = dep_log;
+      MG_LAUNCH(k_dep_register, grid, 256, 0, s, v, P);
+      uint32_t next_cap = (uint32_t)(pairs + 1024 < 0xFFFFFFF0ull ? pairs + 1024 : 0xFFFFFFF0ull);
+      uint32_t *next_count = (uint32_t *)(c + 6);
+      int *overflow = (int *)(c + 6) + 1;
+      MG_TRY(next.alloc((size_t)next_cap * 4));
+      while (n_work) {
+        MG_CUDA(cudaMemsetAsync(c + 6, 0, 8, s));
+        MG_LAUNCH(k_cpeel, grid_for(n_work, 128), 128, 0, s, P, work.as<uint32_t>(), (uint32_t)n_work,
+                  next.as<uint32_t>(), next_count, next_cap, overflow);
+        uint32_t h[2];
+        MG_CUDA(cudaMemcpyAsync(h, c + 6, 8, cudaMemcpyDeviceToHost, s));
+        MG_CUDA(cudaStreamSynchronize(s));
+        if (h[1]) {
+          set_error("peel: work list overflow (%u entries)", next_cap);
+          return MG_EINTERNAL;
+        }
+        n_work = h[0];
+        if (n_work) {
+          MG_TRY(work.ensure((size_t)n_work * 4));
+          MG_CUDA(cudaMemcpyAsync(work.p, next.p, (size_t)n_work * 4, cudaMemcpyDeviceToDevice, s));
+        }
+      }
+    }
+    MG_LAUNCH(k_peel_final, grid, 256, 0, s, v, P, c + 2, c + 3, c + 4);
+    MG_CUDA(cudaStreamSynchronize(s));
   }
   unsigned long long h[5];
   MG_CUDA(cudaMemcpyAsync(h, c, sizeof h, cudaMemcpyDeviceToHost, s));

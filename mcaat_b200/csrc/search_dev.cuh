@@ -40,6 +40,8 @@ MG_HD int adj_outgoing(uint64_t a, uint32_t *out) {
   return deg;
 }
 
+MG_HD uint32_t hash_u32_fwd(uint32_t k, uint32_t log2cap) { return (k * 2654435761u) >> (32 - log2cap); }
+
 // ------------------------------------------------------------------ atomics / fences
 MG_HD bool set_inv_atomic(const GraphView &g, uint32_t i) {
   uint64_t *p = &g.fb[i >> 8].inv[(i >> 6) & 3];
@@ -60,27 +62,153 @@ MG_HD void fence_sc() {
 }
 
 // ------------------------------------------------------------------ peel (RecursiveReduction)
-// src/cycle_finder.cpp:359-371 driven as at :440-442.  Work items are nodes KNOWN to have valid
-// out-degree 0 (tips collected before the multiplicity filter, then parents that lost their last
-// child).  A worker invalidates its node, then re-tests every valid parent; the fence between the
-// invalidation and the re-test guarantees that when two children of a parent are peeled
-// concurrently at least one worker sees out-degree 0.  Duplicates are arbitrated by the atomic
-// bit set.  `emit(p)` receives parents that became peelable.
-template <class Emit>
-MG_HD uint32_t peel_one(const GraphView &g, uint32_t v, Emit emit) {
-  if (get_inv<true>(g, v)) return 0;
-  uint32_t in[4];
-  int deg = incoming<true, false>(g, v, in);  // _GetIncomings(node,set), :111-123
-  if (!set_inv_atomic(g, v)) return 0;        // SetInvalidEdge, :364
-  fence_sc();
-  if (deg > 4) deg = 4;
-  for (int i = 0; i < deg; ++i) {
-    uint32_t p = in[i];
-    if (get_inv<true>(g, p)) continue;                 // :366
-    if (outgoing<true>(g, p, nullptr) > 0) continue;   // :360
-    emit(p);
+// src/cycle_finder.cpp:359-371 driven as at :440-442 computes a closure: starting from the tips
+// collected BEFORE the multiplicity filter, a valid node is removed when all its valid
+// out-neighbours have been removed (the set does not depend on the visiting order).  The reference
+// walks it one node per recursion level; chains of 10^5..10^6 nodes make that a serial pointer
+// chase.  Here the closure is computed by chain contraction on the post-filter graph:
+//   1. every valid node with exactly one valid out-neighbour is a CHAIN node pointing at it; every
+//      other valid node is a terminal (sink: out-degree 0, branch: >= 2) pointing at itself;
+//   2. pointer jumping (ptr[v] = ptr[ptr[v]]) resolves each chain node to its terminal in
+//      O(log chain length) data-parallel rounds (unresolvable = a cycle of chain nodes, never peeled);
+//   3. a chain node is peeled iff its terminal is; a sink is peeled iff it is one of the collected
+//      tips; a branch node is peeled iff the terminals of all its valid out-neighbours are —
+//      evaluated by an asynchronous work list over a (terminal -> dependent branch nodes) multimap.
+struct PeelView {
+  uint64_t *adj;            // per item: Forward | validity mask << 32 on the post-filter graph
+  uint32_t *ptr;            // chain pointer
+  uint32_t *chain;          // bitmap: chain nodes
+  uint32_t *tpeeled;        // bitmap: peeled terminals
+  const uint32_t *tipbits;  // bitmap: CollectTips on the loaded graph (:436)
+  uint64_t *dep;            // multimap entries (terminal << 32 | branch node), empty = ~0
+  uint32_t dep_log;
+};
+MG_HD bool bm_get(const uint32_t *bm, uint32_t i) { return (bm[i >> 5] >> (i & 31)) & 1; }
+MG_HD bool bm_get_coherent(const uint32_t *bm, uint32_t i) { return (ld_cg32(&bm[i >> 5]) >> (i & 31)) & 1; }
+// returns true when this call set the bit
+MG_HD bool bm_set_atomic(uint32_t *bm, uint32_t i) {
+  uint32_t bit = 1u << (i & 31);
+#if defined(__CUDA_ARCH__)
+  return !(atomicOr(&bm[i >> 5], bit) & bit);
+#else
+  uint32_t old = bm[i >> 5];
+  bm[i >> 5] = old | bit;
+  return !(old & bit);
+#endif
+}
+MG_HD int ctz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __ffs((int)x) - 1;
+#else
+  return __builtin_ctz(x);
+#endif
+}
+// Step 1 for one item.  Outputs the per-item flags (the caller packs them into bitmap words) and
+// returns the out-degree on the post-filter graph (-1 for an invalid item).
+MG_HD int chain_init_item(const GraphView &g, const PeelView &P, uint32_t v, bool &is_chain, bool &is_seed) {
+  uint64_t a = adj_encode(g, v);
+  P.adj[v] = a;
+  is_chain = is_seed = false;
+  P.ptr[v] = v;
+  if (get_inv(g, v)) return -1;
+  uint32_t mask = (uint32_t)(a >> 32) & 0xFFu;
+  int deg = popc32(mask);
+  if (deg == 1) {
+    is_chain = true;
+    P.ptr[v] = (uint32_t)a - (uint32_t)ctz32(mask);
+  } else if (deg == 0) {
+    is_seed = bm_get(P.tipbits, v);  // a collected tip that survived the multiplicity filter
   }
-  return 1;
+  return deg;
+}
+// Step 2, one round for one item; returns true while the item is still unresolved.
+MG_HD bool chain_jump_item(const PeelView &P, uint32_t v) {
+  if (!bm_get(P.chain, v)) return false;
+  uint32_t p = P.ptr[v];
+  if (!bm_get(P.chain, p)) return false;
+  P.ptr[v] = P.ptr[p];
+  return true;
+}
+// terminal of an out-neighbour (kNull when it sits on an unresolvable chain cycle)
+MG_HD uint32_t terminal_of(const PeelView &P, uint32_t c) {
+  if (!bm_get(P.chain, c)) return c;
+  uint32_t t = ld_ro(&P.ptr[c]);
+  return bm_get(P.chain, t) ? kNull : t;
+}
+MG_HD void dep_insert(const PeelView &P, uint32_t term, uint32_t b) {
+  uint32_t mask = (1u << P.dep_log) - 1, h = hash_u32_fwd(term, P.dep_log);
+  uint64_t val = ((uint64_t)term << 32) | b;
+  for (;;) {
+#if defined(__CUDA_ARCH__)
+    unsigned long long old = atomicCAS((unsigned long long *)&P.dep[h], ~0ull, (unsigned long long)val);
+    if (old == ~0ull) return;
+#else
+    if (P.dep[h] == ~0ull) { P.dep[h] = val; return; }
+#endif
+    h = (h + 1) & mask;
+  }
+}
+// Step 3a for one branch node: register it with the terminals of its out-neighbours, unless one of
+// them can never be peeled (chain cycle, or a sink that is not a collected tip).
+MG_HD void dep_register_item(const GraphView &g, const PeelView &P, uint32_t b) {
+  uint64_t a = P.adj[b];
+  uint32_t mask = (uint32_t)(a >> 32) & 0xFFu, next = (uint32_t)a;
+  if (get_inv(g, b) || popc32(mask) < 2) return;
+  uint32_t t[8];
+  int n = 0;
+  for (int i = 0; mask; ++i, mask >>= 1) {
+    if (!(mask & 1)) continue;
+    uint32_t tc = terminal_of(P, next - i);
+    if (tc == kNull) return;
+    uint32_t ma = (uint32_t)(P.adj[tc] >> 32) & 0xFFu;
+    if (ma == 0 && !bm_get(P.tpeeled, tc)) return;  // sink that is not a seed
+    t[n++] = tc;
+  }
+  for (int i = 0; i < n; ++i) dep_insert(P, t[i], b);
+}
+// Step 3b: terminal t has just been peeled; emit every dependent branch node that is now peeled.
+// The sequentially consistent fence between setting a terminal's bit and testing its siblings
+// guarantees that when the last two out-neighbours of a branch node are peeled concurrently at
+// least one worker sees both bits; duplicates are arbitrated by the atomic bit set.
+template <class Emit>
+MG_HD void cpeel_one(const PeelView &P, uint32_t t, Emit emit) {
+  uint32_t mask = (1u << P.dep_log) - 1, h = hash_u32_fwd(t, P.dep_log);
+  for (;; h = (h + 1) & mask) {
+    uint64_t e = ld_ro(&P.dep[h]);
+    if (e == ~0ull) return;
+    if ((uint32_t)(e >> 32) != t) continue;
+    uint32_t b = (uint32_t)e;
+    if (bm_get_coherent(P.tpeeled, b)) continue;
+    uint64_t a = ld_ro(&P.adj[b]);
+    uint32_t m = (uint32_t)(a >> 32) & 0xFFu, next = (uint32_t)a;
+    bool all = true;
+    for (int i = 0; m; ++i, m >>= 1)
+      if (m & 1) {
+        uint32_t tc = terminal_of(P, next - i);
+        if (tc == kNull || !bm_get_coherent(P.tpeeled, tc)) { all = false; break; }
+      }
+    if (!all) continue;
+    if (!bm_set_atomic(P.tpeeled, b)) continue;
+    fence_sc();
+    emit(b);
+  }
+}
+// Step 4: is item v removed by the reduction?  (valid items only)
+MG_HD bool is_peeled(const PeelView &P, uint32_t v) {
+  uint32_t t = terminal_of(P, v);
+  return t != kNull && bm_get(P.tpeeled, t);
+}
+// Step 4 for one item: final navigation-cache entry (children removed by the reduction drop out of
+// the validity mask); `peeled` tells the caller to set the item's invalid bit.
+MG_HD uint64_t peel_final_item(const GraphView &g, const PeelView &P, uint32_t v, bool &peeled) {
+  peeled = false;
+  if (get_inv(g, v)) return 0;
+  if (is_peeled(P, v)) { peeled = true; return 0; }
+  uint64_t a = P.adj[v];
+  uint32_t mask = (uint32_t)(a >> 32) & 0xFFu, next = (uint32_t)a, keep = 0;
+  for (int i = 0; i < 8; ++i)
+    if (((mask >> i) & 1) && !is_peeled(P, next - i)) keep |= 1u << i;
+  return (uint64_t)next | ((uint64_t)keep << 32);
 }
 
 // ------------------------------------------------------------------ start-node predicate

@@ -125,37 +125,69 @@ void emu_rank_select_check(Emu *e, int64_t *bad) {  // rank/select round trips o
   }
 }
 
-// stats: tips_before, mult1, peeled, valid, tips_after
+// stats: tips_before, mult1, peeled, valid, tips_after.  Mirrors run_prune (prune.cu): the same
+// per-item device functions in the same phase order; `reverse_order` permutes the work lists to
+// show that the result does not depend on scheduling.
 void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   GraphView &v = e->v;
-  std::vector<uint32_t> work, next;
-  for (uint64_t i = 0; i < v.n; ++i)
-    if (outgoing(v, (uint32_t)i, nullptr) == 0) work.push_back((uint32_t)i);
-  stats[0] = work.size();
+  const uint64_t n = v.n;
+  const size_t words = (n + 31) / 32 + 1;
+  std::vector<uint32_t> tipbits(words, 0), chain(words, 0), tpeeled(words, 0), ptr(n + 1);
+  uint64_t tips0 = 0;
+  for (uint64_t i = 0; i < n; ++i)
+    if (outgoing(v, (uint32_t)i, nullptr) == 0) { tipbits[i >> 5] |= 1u << (i & 31); ++tips0; }
+  stats[0] = tips0;
   uint64_t m1 = 0;
-  for (uint64_t i = 0; i < v.n; ++i)
+  for (uint64_t i = 0; i < n; ++i)
     if (v.mult[i] <= 1) { set_inv_atomic(v, (uint32_t)i); ++m1; }
   stats[1] = m1;
-  uint64_t peeled = 0;
+  e->adj.assign(n + 1, 0);
+  PeelView P;
+  P.adj = e->adj.data(); P.ptr = ptr.data(); P.chain = chain.data(); P.tpeeled = tpeeled.data();
+  P.tipbits = tipbits.data(); P.dep = nullptr; P.dep_log = 0;
+  uint64_t pairs = 0;
+  std::vector<uint32_t> work, next;
+  for (uint64_t i = 0; i < n; ++i) {
+    bool c, sd;
+    int deg = chain_init_item(v, P, (uint32_t)i, c, sd);
+    if (c) chain[i >> 5] |= 1u << (i & 31);
+    if (sd) { tpeeled[i >> 5] |= 1u << (i & 31); work.push_back((uint32_t)i); }
+    if (deg >= 2) pairs += deg;
+  }
+  for (int round = 0; round < 34; ++round) {
+    bool any = false;
+    if (reverse_order) { for (uint64_t i = n; i-- > 0;) any |= chain_jump_item(P, (uint32_t)i); }
+    else for (uint64_t i = 0; i < n; ++i) any |= chain_jump_item(P, (uint32_t)i);
+    if (!any) break;
+  }
+  uint32_t dep_log = 4;
+  while (((uint64_t)1 << dep_log) < 2 * pairs + 16) ++dep_log;
+  std::vector<uint64_t> dep((size_t)1 << dep_log, ~0ull);
+  P.dep = dep.data(); P.dep_log = dep_log;
+  for (uint64_t i = 0; i < n; ++i) dep_register_item(v, P, (uint32_t)i);
   if (reverse_order) std::reverse(work.begin(), work.end());
-  while (!work.empty()) {  // level-synchronous like the kernel loop; order inside a level is free
+  while (!work.empty()) {
     next.clear();
-    for (uint32_t x : work) peeled += peel_one(v, x, [&](uint32_t p) { next.push_back(p); });
+    for (uint32_t t : work) cpeel_one(P, t, [&](uint32_t b) { next.push_back(b); });
     if (reverse_order) std::reverse(next.begin(), next.end());
     work.swap(next);
   }
-  stats[2] = peeled;
-  e->adj.resize(v.n + 1);
-  uint64_t valid = 0, tips = 0;
-  for (uint64_t i = 0; i < v.n; ++i) {
-    uint64_t a = adj_encode(v, (uint32_t)i);
-    e->adj[i] = a;
-    bool ok = !get_inv(v, (uint32_t)i);
-    valid += ok;
-    tips += ok && (a >> 32) == 0;
+  uint64_t peeled = 0, valid = 0, tips = 0;
+  std::vector<uint8_t> pl(n + 1, 0);
+  std::vector<uint64_t> fin(n + 1, 0);
+  for (uint64_t i = 0; i < n; ++i) {
+    bool p;
+    fin[i] = peel_final_item(v, P, (uint32_t)i, p);
+    pl[i] = p;
   }
-  stats[3] = valid;
-  stats[4] = tips;
+  for (uint64_t i = 0; i < n; ++i) {
+    bool ok = !pl[i] && !get_inv(v, (uint32_t)i);
+    if (pl[i]) { set_inv_atomic(v, (uint32_t)i); ++peeled; }
+    e->adj[i] = fin[i];
+    valid += ok;
+    tips += ok && (fin[i] >> 32) == 0;
+  }
+  stats[2] = peeled; stats[3] = valid; stats[4] = tips;
 }
 void emu_invalid(Emu *e, uint8_t *out) {
   for (uint64_t i = 0; i < e->v.n; ++i) out[i] = get_inv(e->v, (uint32_t)i);

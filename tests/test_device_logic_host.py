@@ -93,3 +93,20 @@ def test_dls_tiers_agree():
         else:
             assert small == exact
     assert full > 0  # the tier-1 overflow path is exercised
+
+
+def test_synthetic_community_matches_oracle():
+    """bench-style input (tools/synth_sdbg.py 'mini'): nested bubbles, tandem repeats, error tips"""
+    import synth_sdbg as S
+    g, _ = S.make_workload("mini")
+    n = g["n"]
+    w8 = g["w"].view(np.uint8)
+    w = np.empty(w8.size * 2, np.uint8)
+    w[0::2] = w8 & 15
+    w[1::2] = w8 >> 4
+    last = np.unpackbits(g["last"].view(np.uint8), bitorder="little")[:n]
+    tip = np.unpackbits(g["tip"].view(np.uint8), bitorder="little")[:n]
+    want = O.OracleGraph.from_arrays(w[:n], last, tip, g["mult"], g["f"], g["k"]).run(20, 27, 77)
+    got = run_emu(E.EmuGraph(g), 20, 27, 77, window=256, reverse_peel=True)
+    assert O.same_run(want, got) == []
+    assert got.stats["n_peeled"] > 1000
