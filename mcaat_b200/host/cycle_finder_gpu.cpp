@@ -1,0 +1,291 @@
+// Drop-in replacement for the reference's src/cycle_finder.cpp: same class, same header
+// (reference include/cycle_finder.h:25-85, compiled UNCHANGED from where it lies), same observable
+// behaviour — `CycleFinder cf(settings);` runs the whole search (reference
+// src/cycle_finder.cpp:131-138), `cf.results` holds one entry per searched start node inserted in
+// the reference's threads=1 order with the raw per-start cycle sequence, the host SDBG's invalid
+// bits are updated (SetInvalidEdge) and the same progress lines go to std::cout.
+// Everything between is libmcaat_gpu.so (include/mcaat_gpu.h): the graph is extracted once through
+// the public SDBG getters, uploaded, and searched on the GPU.  No CPU fallback: a C-ABI error
+// becomes std::runtime_error.
+//
+// Build: see mcaat_b200/host/Makefile (needs the reference's headers on the include path; nothing
+// of the reference is copied).  Device: env MCAAT_GPU_DEVICE (default 0).
+#include <cmath>
+#include <cstdlib>
+#include <iostream>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "cycle_finder.h"  // the reference's header
+#include "mcaat_gpu.h"
+
+namespace {
+
+struct GpuState {
+  mg_graph *g = nullptr;
+  bool pruned = false;
+  mg_prune_stats stats{};
+};
+std::mutex g_mu;
+std::unordered_map<const CycleFinder *, GpuState> g_state;  // the header has no room for a handle
+
+[[noreturn]] void fail(const char *what, int rc) {
+  throw std::runtime_error(std::string("libmcaat_gpu: ") + what + " failed (" + std::to_string(rc) +
+                           "): " + mg_last_error());
+}
+
+// f_[0..5] (reference sdbg.h:36-50) is private; LastCharOf (sdbg.h:79-86, public) is monotone in
+// its argument, so f_[i] = the smallest x with LastCharOf(x) >= i.
+void recover_f(const SDBG &sdbg, int64_t f[6]) {
+  const uint64_t n = sdbg.size();
+  f[0] = -1;
+  for (int i = 1; i <= 5; ++i) {
+    uint64_t lo = 0, hi = n;
+    while (lo < hi) {
+      uint64_t mid = lo + (hi - lo) / 2;
+      if (sdbg.LastCharOf(mid) >= i) hi = mid;
+      else lo = mid + 1;
+    }
+    f[i] = (int64_t)lo;
+  }
+}
+
+// Extract MEGAHIT's arrays through the public getters (reference sdbg.h:63-105) and upload them.
+mg_graph *upload(SDBG &sdbg) {
+  const uint64_t n = sdbg.size();
+  std::vector<uint64_t> w((n + 15) / 16 + 1, 0), last((n + 63) / 64 + 1, 0), tip((n + 63) / 64 + 1, 0),
+      inv((n + 63) / 64 + 1, 0);
+  std::vector<uint16_t> mult(n + 1, 0);
+  const int64_t n_words = (int64_t)((n + 63) / 64);
+#pragma omp parallel for schedule(static)
+  for (int64_t wi = 0; wi < n_words; ++wi) {  // one thread owns whole 64-item words: no write sharing
+    uint64_t lo = (uint64_t)wi * 64, hi = std::min<uint64_t>(lo + 64, n);
+    uint64_t lw = 0, tw = 0, iw = 0;
+    for (uint64_t i = lo; i < hi; ++i) {
+      w[i >> 4] |= (uint64_t)(sdbg.GetW(i) & 15) << ((i & 15) * 4);
+      lw |= (uint64_t)sdbg.IsLast(i) << (i & 63);
+      tw |= (uint64_t)sdbg.IsTip(i) << (i & 63);
+      iw |= (uint64_t)(!sdbg.IsValidEdge(i)) << (i & 63);
+      mult[i] = (uint16_t)sdbg.EdgeMultiplicity(i);
+    }
+    last[wi] = lw;
+    tip[wi] = tw;
+    inv[wi] = iw;
+  }
+  mg_graph_desc d{};
+  d.n_items = n;
+  d.k = sdbg.k();
+  d.memory = MG_MEM_HOST;
+  const char *dev = std::getenv("MCAAT_GPU_DEVICE");
+  d.device = dev ? std::atoi(dev) : 0;
+  d.w = w.data();
+  d.last = last.data();
+  d.tip = tip.data();
+  d.invalid = inv.data();
+  d.mult16 = mult.data();
+  recover_f(sdbg, d.f);
+  mg_graph *g = nullptr;
+  int rc = mg_graph_create(&d, &g);
+  if (rc != MG_OK) fail("mg_graph_create", rc);
+  return g;
+}
+
+GpuState &state_of(const CycleFinder *cf, SDBG &sdbg) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  GpuState &s = g_state[cf];
+  if (!s.g) s.g = upload(sdbg);
+  return s;
+}
+
+// invalid bits the GPU set -> host SDBG (reference SetInvalidEdge, sdbg.h:94)
+void write_back_invalid(mg_graph *g, SDBG &sdbg) {
+  const uint64_t n = sdbg.size();
+  std::vector<uint64_t> inv((n + 63) / 64 + 1, 0);
+  int rc = mg_invalid_readback(g, inv.data());
+  if (rc != MG_OK) fail("mg_invalid_readback", rc);
+  const int64_t n_words = (int64_t)((n + 63) / 64);
+#pragma omp parallel for schedule(static)
+  for (int64_t wi = 0; wi < n_words; ++wi) {
+    uint64_t word = inv[wi];
+    while (word) {
+      uint64_t i = (uint64_t)wi * 64 + __builtin_ctzll(word);
+      word &= word - 1;
+      if (i < n && sdbg.IsValidEdge(i)) sdbg.SetInvalidEdge(i);
+    }
+  }
+}
+
+void ensure_pruned(GpuState &s, SDBG &sdbg, mg_prune_stats *out) {
+  if (!s.pruned) {
+    int rc = mg_prune(s.g, &s.stats);
+    if (rc != MG_OK) fail("mg_prune", rc);
+    s.pruned = true;
+    write_back_invalid(s.g, sdbg);
+  }
+  if (out) *out = s.stats;
+}
+
+}  // namespace
+
+// ---- reference src/cycle_finder.cpp:131-138
+CycleFinder::CycleFinder(Settings &settings) : settings(settings), cluster_bounds(500) {
+  if (this->settings.sdbg == nullptr) {
+    throw std::runtime_error("CycleFinder requires settings.sdbg to be set to a valid SDBG instance");
+  }
+  this->FindApproximateCRISPRArrays();
+}
+
+CycleFinder::~CycleFinder() {
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto it = g_state.find(this);
+  if (it != g_state.end()) {
+    mg_graph_destroy(it->second.g);
+    g_state.erase(it);
+  }
+}
+
+// ---- reference :346-357.  Evaluated on the CURRENT graph state, like the reference.
+vector<uint64_t> CycleFinder::CollectTips() {
+  SDBG &sdbg = *this->settings.sdbg;
+  GpuState &s = state_of(this, sdbg);
+  const uint64_t n = sdbg.size();
+  std::vector<int8_t> od(n);
+  int rc = mg_navigate(s.g, 0, n, od.data(), nullptr, nullptr, nullptr, nullptr);
+  if (rc != MG_OK) fail("mg_navigate", rc);
+  vector<uint64_t> tips;
+  for (uint64_t i = 0; i < n; ++i)
+    if (od[i] == 0) tips.push_back(i);
+  return tips;
+}
+
+// ---- reference :359-371 / :372-382.  The reduction is a whole-graph closure on the device
+// (mg_prune = CollectTips -> InvalidateMultiplicityOneNodes -> RecursiveReduction of every tip);
+// the per-tip and per-phase entry points run that pipeline once and are idempotent afterwards.
+void CycleFinder::RecursiveReduction(uint64_t) {
+  SDBG &sdbg = *this->settings.sdbg;
+  ensure_pruned(state_of(this, sdbg), sdbg, nullptr);
+}
+void CycleFinder::InvalidateMultiplicityOneNodes() {
+  SDBG &sdbg = *this->settings.sdbg;
+  GpuState &s = state_of(this, sdbg);
+  bool first = !s.pruned;
+  mg_prune_stats st{};
+  ensure_pruned(s, sdbg, &st);
+  if (first)
+    std::cout << "Pre-filter: invalidated " << st.n_mult1 << " node(s) with multiplicity <= 1." << std::endl;
+}
+
+// ---- reference :387-427
+size_t CycleFinder::ChunkStartNodes(map<int, vector<uint64_t>, greater<int>> &start_nodes_chunked) {
+  SDBG &sdbg = *this->settings.sdbg;
+  GpuState &s = state_of(this, sdbg);
+  ensure_pruned(s, sdbg, nullptr);
+  mg_starts st{};
+  int rc = mg_select_starts(s.g, this->settings.cycle_finder_settings.threshold_multiplicity,
+                            this->settings.cycle_finder_settings.cycle_max_length, &st);
+  if (rc != MG_OK) fail("mg_select_starts", rc);
+  for (uint64_t b = 0; b < st.n_buckets; ++b) {
+    auto &v = start_nodes_chunked[(int)st.bucket_key[b]];
+    v.insert(v.end(), st.start_ids + st.bucket_off[b], st.start_ids + st.bucket_off[b + 1]);
+  }
+  mg_starts_free(&st);
+  size_t total = 0;
+  for (const auto &[key, value] : start_nodes_chunked) {
+    std::cout << "Chunked start nodes: multiplicity bucket (log2)=" << key << ", nodes=" << value.size() << std::endl;
+    total += value.size();
+  }
+  return total;
+}
+
+// ---- reference :248-343 (only target == start is used, :411)
+bool CycleFinder::DepthLevelSearch(uint64_t start, uint64_t target, int limit, int &reached_depth) {
+  if (start != target) throw std::runtime_error("DepthLevelSearch: only target == start is supported on the GPU path");
+  SDBG &sdbg = *this->settings.sdbg;
+  GpuState &s = state_of(this, sdbg);
+  ensure_pruned(s, sdbg, nullptr);
+  uint8_t pass = 0;
+  int rc = mg_dls(s.g, &start, 1, limit, &pass, nullptr);
+  if (rc != MG_OK) fail("mg_dls", rc);
+  reached_depth = 0;
+  return pass != 0;
+}
+
+static vector<vector<uint64_t>> cycles_of(const mg_cycles &c, uint64_t idx) {
+  vector<vector<uint64_t>> out;
+  for (uint64_t j = c.cyc_off[idx]; j < c.cyc_off[idx + 1]; ++j)
+    out.emplace_back(c.nodes + c.node_off[j], c.nodes + c.node_off[j + 1]);
+  return out;
+}
+
+// ---- reference :231-243 (+ :140-225): one start node against the current `visited` state
+vector<vector<uint64_t>> CycleFinder::FindCycleUtil(uint64_t start_node) {
+  SDBG &sdbg = *this->settings.sdbg;
+  GpuState &s = state_of(this, sdbg);
+  ensure_pruned(s, sdbg, nullptr);
+  mg_cycles c{};
+  int rc = mg_find_cycles(s.g, &start_node, 1, this->settings.cycle_finder_settings.cycle_min_length,
+                          this->settings.cycle_finder_settings.cycle_max_length, &c);
+  if (rc != MG_OK) fail("mg_find_cycles", rc);
+  vector<vector<uint64_t>> out;
+  if (c.n_searched) out = cycles_of(c, 0);
+  mg_cycles_free(&c);
+  return out;
+}
+// The reference's FindCycle takes the search state by value; only the FindCycleUtil entry state is
+// ever passed (:242), which is what the device search starts from.
+vector<vector<uint64_t>> CycleFinder::FindCycle(uint64_t start_node, vector<uint64_t>, map<uint64_t, int>,
+                                                vector<unordered_set<uint64_t>>, vector<int>) {
+  return this->FindCycleUtil(start_node);
+}
+
+// ---- reference :433-492
+int CycleFinder::FindApproximateCRISPRArrays() {
+  SDBG &sdbg = *this->settings.sdbg;
+  GpuState &s = state_of(this, sdbg);
+  const auto &cfs = this->settings.cycle_finder_settings;
+  mg_prune_stats ps{};
+  ensure_pruned(s, sdbg, &ps);
+  std::cout << "Graph size: " << sdbg.size() << " nodes; gathered tips: " << ps.n_tips_before << std::endl;
+  std::cout << "Pre-filter: invalidated " << ps.n_mult1 << " node(s) with multiplicity <= 1." << std::endl;
+  std::cout << "After pruning, tips: " << ps.n_tips_after << ", valid edges: " << (int)ps.n_valid << std::endl;
+  std::cout << "Total nodes in graph: " << sdbg.size() << std::endl;
+  this->visited.resize(sdbg.size(), false);
+  std::cout << "Starting cycle enumeration: max_len=" << cfs.cycle_max_length << " min_len=" << cfs.cycle_min_length
+            << " threads=" << this->settings.threads << std::endl;
+  map<int, vector<uint64_t>, greater<int>> start_nodes_chunked;
+  size_t start_nodes_amount = this->ChunkStartNodes(start_nodes_chunked);
+  std::cout << "Start nodes found in chunks: " << start_nodes_amount << std::endl;
+
+  vector<uint64_t> order;
+  order.reserve(start_nodes_amount);
+  for (auto &kv : start_nodes_chunked) order.insert(order.end(), kv.second.begin(), kv.second.end());
+  mg_cycles c{};
+  int rc = mg_find_cycles(s.g, order.data(), order.size(), cfs.cycle_min_length, cfs.cycle_max_length, &c);
+  if (rc != MG_OK) fail("mg_find_cycles", rc);
+  // results[start] = cycles in the reference's insertion sequence (:479; F14: downstream iterates
+  // the unordered_map, whose order depends on it)
+  std::unordered_map<uint64_t, uint64_t> n_cycles_of;
+  for (uint64_t i = 0; i < c.n_searched; ++i) {
+    this->results[c.searched_start[i]] = cycles_of(c, i);
+    n_cycles_of[c.searched_start[i]] = c.cyc_off[i + 1] - c.cyc_off[i];
+    for (uint64_t j = c.node_off[c.cyc_off[i]]; j < c.node_off[c.cyc_off[i + 1]]; ++j) this->visited[c.nodes[j]] = true;
+  }
+  mg_cycles_free(&c);
+  int cumulative = 0;
+  for (auto &kv : start_nodes_chunked) {
+    size_t in_bucket = 0;
+    for (uint64_t v : kv.second) {
+      auto it = n_cycles_of.find(v);
+      if (it != n_cycles_of.end()) in_bucket += it->second;
+    }
+    cumulative += (int)in_bucket;
+    std::cout << "Bucket log2_mult=" << kv.first << ": processed " << kv.second.size() << " nodes, found " << in_bucket
+              << " cycles (cumulative " << cumulative << ")" << std::endl;
+  }
+  std::cout << "Cycle enumeration completed: total cycles=" << cumulative << ", result nodes=" << this->results.size()
+            << std::endl;
+  return cumulative;
+}

@@ -118,3 +118,22 @@ def test_empty_and_degenerate_inputs():
     v = int(np.nonzero(~inv)[0][0])
     searched, _ = g.find_cycles([v], 27, 77)
     assert len(searched) == 1 and searched[0][0] == v
+
+
+def test_cpp_drop_in_cyclefinder_matches_reference_dump(tmp_path):
+    """The C++ `CycleFinder` shim (mcaat_b200/host/cycle_finder_gpu.cpp, compiled against the reference's
+    unchanged header) driven by the oracle harness main: its dump — invalid bitmap of the HOST SDBG after
+    write-back, ordered start lists, raw results, unordered_map iteration order — must equal the dump of
+    the unmodified reference byte for byte."""
+    import gzip
+    import os
+    import subprocess
+    exe = os.path.join(gpu.ROOT, "mcaat_b200", "host", "_build", "shim_cyclefinder")
+    if not os.path.exists(exe):
+        pytest.skip("shim_cyclefinder not built (needs the reference headers at build time)")
+    prefix = G.unpack_sdbg_files("tiny", str(tmp_path))
+    for thr, mn, mx in ((20, 27, 77), (10, 20, 100)):
+        out = str(tmp_path / f"shim_{thr}.dump")
+        subprocess.run([exe, prefix, out, "1", str(thr), str(mn), str(mx)], check=True, capture_output=True)
+        want = gzip.open(os.path.join(G.GOLD, f"tiny.t{thr}_{mn}_{mx}.dump.gz"), "rb").read()
+        assert open(out, "rb").read() == want
