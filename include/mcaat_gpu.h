@@ -139,8 +139,10 @@ typedef struct {
   uint64_t n_skipped;       /* starts skipped because already visited (:476) */
   uint64_t n_bound_hits;    /* searches cleared by the 500-cycle cluster bound (:162-165) */
   uint64_t n_cap_hits;      /* searches stopped by the 10 000 000-step cap (:148-151) */
-  uint64_t n_reruns;        /* speculative searches repeated after an ordered-commit conflict */
-  uint64_t n_rounds;        /* speculation windows launched */
+  uint64_t n_reruns;        /* speculative searches repeated at commit time (saw a stale bitmap) */
+  uint64_t n_rounds;        /* pipeline launches (1 unless an arena or the result pool had to grow) */
+  uint64_t n_searches_run;  /* searches started, speculative ones included */
+  uint64_t n_abandoned;     /* running searches given up because an earlier commit marked their start */
   uint64_t expansions;      /* _GetOutgoings/_GetIncomings evaluations of committed searches */
 } mg_cycles;
 int mg_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len, int max_len, mg_cycles *out);

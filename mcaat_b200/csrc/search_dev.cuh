@@ -336,21 +336,45 @@ MG_HD void uset_erase(USet &s, uint32_t x) {
 
 constexpr int kMaxSteps = 10000000;  // src/cycle_finder.cpp:149
 constexpr int kClusterBound = 500;   // src/cycle_finder.cpp:132
+constexpr int kPollSteps = 256;      // how often a running search polls for its own start being marked
 enum EnumStatus : int32_t {
   kEnumDone = 0,
-  kEnumBound = 1,      // cluster bound reached: result is empty (:162-165), search stopped early
-  kEnumCap = 2,        // step cap reached (:148-151): cycles found so far are kept
-  kEnumOverflow = 3,   // arena too small: must be re-run with a larger arena
-  kEnumPreSkipped = 4  // start already visited in the snapshot (:476)
+  kEnumBound = 1,     // cluster bound reached: result is empty (:162-165), search stopped early
+  kEnumCap = 2,       // step cap reached (:148-151): cycles found so far are kept
+  kEnumOverflow = 3,  // arena too small: must be re-run with a larger arena
+  kEnumSkipped = 4,   // start already visited (:476) — seen before or while searching
 };
+
+// One entry of the per-search lock map (std::map<uint64_t,int> lock of :140) — 64 bytes = two
+// sectors, first sector = everything the inner loop needs.  Besides the lock value it memoises what
+// the search derives again and again for the same node: the filtered out-neighbour set
+// (_GetOutgoings(node,set,mult), :58-72, in std::unordered_set iteration order), the filtered
+// in-neighbour set (_GetIncomings, :76-88) and whether the node is on the current path (the
+// reference rebuilds a set from `path` for every relaxation, :196).  Entries are valid when
+// their epoch equals the search's epoch, so the table never needs clearing between searches.
+struct LockEnt {
+  uint32_t key;
+  uint32_t epoch;
+  int32_t val;       // lock value
+  uint32_t nout;     // kMemoNone = not computed yet
+  uint32_t out[4];
+  uint32_t nin;      // kMemoNone = not computed yet
+  uint32_t in[4];
+  uint32_t on_path;
+  uint32_t pad[2];
+};
+static_assert(sizeof(LockEnt) == 64, "lock entry layout");
+constexpr uint32_t kMemoNone = 0xFFFFFFFFu;
 
 struct EnumArena {
   uint32_t *path;       // [M+2]
+  uint32_t *pent;       // [M+2] lock-table slot of path[i]
   int32_t *bl;          // [M+2]
   USet *stk;            // [M+2]
-  uint64_t *lock;       // [1 << lock_log]  low 32 = key, high 32 = value; empty = ~0
+  LockEnt *lock;        // [1 << lock_log]
   uint32_t lock_log;
-  uint32_t *keylog;     // every key ever inserted into `lock` (+ leftovers on early stop)
+  uint32_t epoch;       // current search
+  uint32_t *keylog;     // every key inserted into `lock` during this search = the examined set
   uint32_t keylog_cap;
   uint64_t *relax;      // relax_stack entries (bl << 32 | node), :192-193
   uint32_t relax_cap;
@@ -368,63 +392,94 @@ struct EnumResult {
 };
 
 MG_HD bool visited_bit(const uint32_t *visited, uint32_t i) { return (visited[i >> 5] >> (i & 31)) & 1; }
+// `visited` is marked by other SMs while searches run (ordered commit): read it through L2
+MG_HD bool visited_live(const uint32_t *visited, uint32_t i) { return (ld_cg32(&visited[i >> 5]) >> (i & 31)) & 1; }
 
-// value slot of `key` in the lock map, inserting `defval` when absent (std::map::try_emplace /
+// entry of `key` in the lock map, inserting (val = defval) when absent (std::map::try_emplace /
 // operator[] as used at :168,:200); nullptr when the arena is full.
-MG_HD uint32_t *lock_get(EnumArena &A, uint32_t &n_keys, uint32_t key, uint32_t defval) {
+MG_HD LockEnt *lock_get(EnumArena &A, uint32_t &n_keys, uint32_t key, int32_t defval, uint32_t *slot_out = nullptr) {
   uint32_t mask = (1u << A.lock_log) - 1;
   uint32_t h = hash_u32(key, A.lock_log);
   for (;;) {
-    uint64_t cur = A.lock[h];
-    if ((uint32_t)cur == key && cur != ~0ull) return ((uint32_t *)&A.lock[h]) + 1;
-    if (cur == ~0ull) {
+    LockEnt *e = &A.lock[h];
+    if (e->epoch != A.epoch) {
       if (n_keys >= A.keylog_cap) return nullptr;
-      A.lock[h] = (uint64_t)key | ((uint64_t)defval << 32);
+      e->key = key;
+      e->epoch = A.epoch;
+      e->val = defval;
+      e->nout = kMemoNone;
+      e->nin = kMemoNone;
+      e->on_path = 0;
       A.keylog[n_keys++] = key;
-      return ((uint32_t *)&A.lock[h]) + 1;
+      if (slot_out) *slot_out = h;
+      return e;
+    }
+    if (e->key == key) {
+      if (slot_out) *slot_out = h;
+      return e;
     }
     h = (h + 1) & mask;
   }
 }
 
-// _BackgroundCheck, src/cycle_finder.cpp:40-52
-MG_HD bool background_ok(const GraphView &g, const uint32_t *visited, uint32_t from, uint32_t mu, uint32_t nb) {
-  if (visited_bit(visited, nb)) return false;
-  uint32_t m = get_mult(g, nb);
-  if (m == 0) return false;  // the reference would divide by zero; mult <= 1 items are invalid
-  if (mu / m > 500) return false;
-  if (from == nb) return false;
-  return true;
-}
-// _GetOutgoings(node,set,mult), src/cycle_finder.cpp:58-72
-MG_HD void enum_outgoings(const GraphView &g, const uint64_t *adj, const uint32_t *visited, uint32_t node,
-                          uint32_t mu, USet &s, uint32_t &expansions) {
+// _BackgroundCheck (src/cycle_finder.cpp:40-52) for up to 4 neighbours at once: all multiplicity and
+// visited words are loaded before any is tested, so the loads overlap instead of forming a chain.
+MG_HD void filtered_set(const GraphView &g, const uint32_t *visited, uint32_t node, uint32_t mu, const uint32_t *nb,
+                        int deg, uint32_t &n_out, uint32_t *out) {
+  uint32_t m[4] = {0, 0, 0, 0}, vw[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (i < deg) {
+      m[i] = ld_ro(&g.mult[nb[i]]);
+      vw[i] = ld_cg32(&visited[nb[i] >> 5]);
+    }
+  USet s;
   s.n = 0;
-  ++expansions;
-  uint32_t nb[4];
-  int deg = adj_outgoing(ld_ro(&adj[node]), nb);
-  if (deg > 4) deg = 4;
-  for (int i = 0; i < deg; ++i)
-    if (background_ok(g, visited, node, mu, nb[i])) uset_insert(s, nb[i]);
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (i < deg) {
+      bool ok = !((vw[i] >> (nb[i] & 31)) & 1) && m[i] != 0 && mu / m[i] <= 500 && nb[i] != node;
+      if (ok) uset_insert(s, nb[i]);
+    }
+  n_out = s.n;
+  for (uint32_t i = 0; i < s.n && i < 4; ++i) out[i] = s.e[i];
 }
-// _GetIncomings(node,set,mult), src/cycle_finder.cpp:76-88
-MG_HD void enum_incomings(const GraphView &g, const uint32_t *visited, uint32_t node, uint32_t mu, USet &s,
-                          uint32_t &expansions) {
-  s.n = 0;
+// _GetOutgoings(node,set,mult), src/cycle_finder.cpp:58-72, memoised in the node's lock entry
+MG_HD void enum_outgoings(const GraphView &g, const uint64_t *adj, const uint32_t *visited, LockEnt *e, uint32_t mu,
+                          USet &s, uint32_t &expansions) {
   ++expansions;
-  uint32_t nb[4];
-  int deg = incoming(g, node, nb);
-  if (deg > 4) deg = 4;
-  for (int i = 0; i < deg; ++i)
-    if (background_ok(g, visited, node, mu, nb[i])) uset_insert(s, nb[i]);
+  if (e->nout == kMemoNone) {
+    uint32_t nb[4];
+    int deg = adj_outgoing(ld_ro(&adj[e->key]), nb);
+    if (deg > 4) deg = 4;
+    filtered_set(g, visited, e->key, mu, nb, deg, e->nout, e->out);
+  }
+  s.n = e->nout;
+  for (uint32_t i = 0; i < 4; ++i) s.e[i] = e->out[i];
+}
+// _GetIncomings(node,set,mult), src/cycle_finder.cpp:76-88, memoised likewise
+MG_HD void enum_incomings(const GraphView &g, const uint32_t *visited, LockEnt *e, uint32_t mu, uint32_t &expansions) {
+  ++expansions;
+  if (e->nin == kMemoNone) {
+    uint32_t nb[4];
+    int deg = incoming(g, e->key, nb);
+    if (deg > 4) deg = 4;
+    if (deg < 0) deg = 0;
+    filtered_set(g, visited, e->key, mu, nb, deg, e->nin, e->in);
+  }
 }
 
-// FindCycleUtil + FindCycle, src/cycle_finder.cpp:231-243,140-225, against the `visited` snapshot.
-// Does NOT mark visited (the ordered commit does, :217-222).  Exact shortcut: once the cluster
-// bound fires every later hit clears the list again, so the result is empty whatever follows;
-// the search stops there instead of spinning to the step cap.
+// FindCycleUtil + FindCycle, src/cycle_finder.cpp:231-243,140-225.  Does NOT mark visited (the
+// ordered commit does, :217-222).  `visited` may gain marks while the search runs; every node the
+// search ACCEPTED is in the key log, and the commit re-checks those, so a search is only kept when
+// it is identical to one run against the bitmap of its position in the sequential order.
+// `poll()` is called every kPollSteps steps; returning true abandons the search (its start has been
+// marked by an earlier start's commit: the reference would skip it, :476).
+// Exact shortcut: once the cluster bound fires every later hit clears the list again, so the result
+// is empty whatever follows; the search stops there instead of spinning to the step cap.
+template <class Poll>
 MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint32_t *visited, uint32_t start,
-                             int min_len, int max_len, EnumArena &A, EnumResult &R) {
+                             int min_len, int max_len, EnumArena &A, EnumResult &R, Poll poll) {
   const int M = max_len;
   const uint32_t mu = get_mult(g, start);
   uint32_t n_keys = 0, expansions = 0, n_cycles = 0, n_nodes = 0;
@@ -432,15 +487,21 @@ MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint
   int counter = 0, steps = 0;
   int32_t status = kEnumDone;
   A.cyc_off[0] = 0;
-
-  A.path[plen++] = start;
-  uint32_t *lk0 = lock_get(A, n_keys, start, 0);  // lock[start] = 0, :237
-  if (!lk0) { status = kEnumOverflow; goto done; }
-  enum_outgoings(g, adj, visited, start, mu, A.stk[slen++], expansions);
-  A.bl[blen++] = M;
-
+  {
+    uint32_t slot = 0;
+    LockEnt *e0 = lock_get(A, n_keys, start, 0, &slot);  // lock[start] = 0, :237
+    if (!e0) { status = kEnumOverflow; goto done; }
+    e0->val = 0;
+    e0->on_path = 1;
+    A.path[0] = start;
+    A.pent[0] = slot;
+    plen = 1;
+    enum_outgoings(g, adj, visited, e0, mu, A.stk[slen++], expansions);
+    A.bl[blen++] = M;
+  }
   while (slen > 0) {
     if (++steps > kMaxSteps) { status = kEnumCap; break; }  // :148-151
+    if ((steps & (kPollSteps - 1)) == 0 && poll()) { status = kEnumSkipped; n_cycles = n_nodes = 0; goto done; }
     USet nbs = A.stk[slen - 1];                             // :153 (copy)
     bool flag = true;
     for (uint32_t i = 0; i < nbs.n; ++i) {
@@ -460,14 +521,18 @@ MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint
           A.cyc_off[++n_cycles] = n_nodes;
         }
       } else {
-        uint32_t *lk = lock_get(A, n_keys, nb, (uint32_t)M);  // try_emplace(nb, M), :168
-        if (!lk) { status = kEnumOverflow; goto done; }
-        if ((uint32_t)plen < *lk) {
-          A.path[plen++] = nb;                              // :170
+        uint32_t slot = 0;
+        LockEnt *e = lock_get(A, n_keys, nb, M, &slot);     // try_emplace(nb, M), :168
+        if (!e) { status = kEnumOverflow; goto done; }
+        if (plen < e->val) {
+          A.path[plen] = nb;                                // :170
+          A.pent[plen] = slot;
+          ++plen;
           A.bl[blen++] = M;                                 // :171
-          *lk = (uint32_t)plen;                             // :172
+          e->val = plen;                                    // :172
+          e->on_path = 1;
           uset_erase(A.stk[slen - 1], nb);                  // :173
-          enum_outgoings(g, adj, visited, nb, mu, A.stk[slen], expansions);  // :174-176
+          enum_outgoings(g, adj, visited, e, mu, A.stk[slen], expansions);  // :174-176
           ++slen;
           flag = false;
           break;
@@ -476,7 +541,9 @@ MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint
     }
     if (flag) {                                             // :181-211
       --slen;
-      uint32_t v = A.path[--plen];
+      --plen;
+      uint32_t v = A.path[plen];
+      A.lock[A.pent[plen]].on_path = 0;
       int b = A.bl[--blen];
       if (blen > 0 && b < A.bl[blen - 1]) A.bl[blen - 1] = b;
       if (b < M) {
@@ -486,19 +553,18 @@ MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint
           uint64_t r = A.relax[--rn];
           int rb = (int)(r >> 32);
           uint32_t u = (uint32_t)r;
-          uint32_t *lk = lock_get(A, n_keys, u, (uint32_t)M);
-          if (!lk) { status = kEnumOverflow; goto done; }
-          if ((int)*lk < M - rb + 1) {
-            *lk = (uint32_t)(M - rb + 1);
-            USet inc;
-            enum_incomings(g, visited, u, mu, inc, expansions);
-            for (uint32_t i = 0; i < inc.n; ++i) {
-              bool on_path = false;
-              for (int j = 0; j < plen; ++j)
-                if (A.path[j] == inc.e[i]) { on_path = true; break; }
-              if (!on_path) {
+          LockEnt *e = lock_get(A, n_keys, u, M);
+          if (!e) { status = kEnumOverflow; goto done; }
+          if (e->val < M - rb + 1) {
+            e->val = M - rb + 1;
+            enum_incomings(g, visited, e, mu, expansions);
+            uint32_t nin = e->nin, in[4] = {e->in[0], e->in[1], e->in[2], e->in[3]};
+            for (uint32_t i = 0; i < nin; ++i) {
+              LockEnt *ew = lock_get(A, n_keys, in[i], M);  // every accepted neighbour gets an entry
+              if (!ew) { status = kEnumOverflow; goto done; }
+              if (!ew->on_path) {                           // :197-199
                 if (rn >= A.relax_cap) { status = kEnumOverflow; goto done; }
-                A.relax[rn++] = ((uint64_t)(uint32_t)(rb + 1) << 32) | inc.e[i];
+                A.relax[rn++] = ((uint64_t)(uint32_t)(rb + 1) << 32) | in[i];
               }
             }
           }
@@ -514,7 +580,7 @@ leftovers:
       for (uint32_t i = 0; i < A.stk[l].n; ++i) {
         uint32_t x = A.stk[l].e[i];
         if (x == start) continue;
-        if (!lock_get(A, n_keys, x, (uint32_t)M)) { status = kEnumOverflow; goto done; }
+        if (!lock_get(A, n_keys, x, M)) { status = kEnumOverflow; goto done; }
       }
   }
 done:

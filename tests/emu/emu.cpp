@@ -220,89 +220,103 @@ int emu_dls_bitmap(Emu *e, uint64_t start, int limit) {
 }
 
 struct EmuSlot {
-  std::vector<uint32_t> path, keylog, cyc_nodes, cyc_off;
+  std::vector<uint32_t> path, pent, keylog, cyc_nodes, cyc_off;
   std::vector<int32_t> bl;
   std::vector<USet> stk;
-  std::vector<uint64_t> lock, relax;
+  std::vector<LockEnt> lock;
+  std::vector<uint64_t> relax;
   EnumArena A;
   EnumResult R;
   void init(int M, uint32_t lock_log, uint32_t relax_cap, uint32_t cyc_cycles) {
-    path.resize(M + 4); bl.resize(M + 4); stk.resize(M + 4);
-    lock.assign((size_t)1 << lock_log, ~0ull);
+    path.resize(M + 4); pent.resize(M + 4); bl.resize(M + 4); stk.resize(M + 4);
+    lock.resize((size_t)1 << lock_log);
+    memset(lock.data(), 0, lock.size() * sizeof(LockEnt));
     keylog.resize(((size_t)1 << lock_log) / 2);
     relax.resize(relax_cap);
     cyc_nodes.resize((size_t)cyc_cycles * (M + 1));
     cyc_off.resize(kClusterBound + 1);
-    A.path = path.data(); A.bl = bl.data(); A.stk = stk.data(); A.lock = lock.data(); A.lock_log = lock_log;
+    A.path = path.data(); A.pent = pent.data(); A.bl = bl.data(); A.stk = stk.data(); A.lock = lock.data();
+    A.lock_log = lock_log; A.epoch = 0;
     A.keylog = keylog.data(); A.keylog_cap = (uint32_t)keylog.size(); A.relax = relax.data(); A.relax_cap = relax_cap;
     A.cyc_nodes = cyc_nodes.data(); A.cyc_nodes_cap = (uint32_t)cyc_nodes.size(); A.cyc_off = cyc_off.data();
   }
 };
 
-// Mirrors run_find_cycles (enumerate.cu) with `window` speculative searches per round.
+// Mirrors the ordered-commit pipeline of enumerate.cu with `window` workers: ticket t is searched
+// against a LAGGING view of `visited` (the state `window` commits ago) that catches up one commit at
+// every poll — i.e. the bitmap changes under the running search, as it does on the device — and is
+// then committed in order against the exact bitmap (skip / conflict -> re-run / accept).
 // Outputs: searched starts, per-search cycle counts, flat cycle lengths and nodes (caller-sized
-// generously), stats = {skipped, bound, cap, reruns, rounds, overflow_reruns}.
+// generously), stats = {skipped, bound, cap, reruns, abandoned, overflow_reruns}.
 int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int max_len, uint32_t window,
                     uint32_t lock_log, uint64_t *searched, uint64_t *n_searched, uint64_t *cyc_count,
                     uint64_t *cyc_len, uint64_t *n_cycles, uint64_t *nodes, uint64_t *n_nodes, uint64_t *stats) {
   GraphView &v = e->v;
   std::fill(e->visited.begin(), e->visited.end(), 0u);
   uint32_t *vis = e->visited.data();
+  std::vector<uint32_t> view(e->visited.size(), 0u);
+  std::vector<std::vector<uint32_t>> marks(n + 1);  // nodes marked by the commit of ticket i
+  uint64_t view_idx = 0;                            // commits [0, view_idx) are applied to `view`
   *n_searched = *n_cycles = *n_nodes = 0;
   for (int i = 0; i < 6; ++i) stats[i] = 0;
-  std::vector<EmuSlot> slots(window);
-  for (auto &s : slots) s.init(max_len, lock_log, 4096, 128);
-  uint64_t pos = 0;
-  auto accept = [&](uint32_t s, EmuSlot &sl) {
-    for (uint32_t j = 0; j < sl.R.n_nodes; ++j) vis[sl.cyc_nodes[j] >> 5] |= 1u << (sl.cyc_nodes[j] & 31);
-    searched[*n_searched] = s;
-    cyc_count[*n_searched] = sl.R.n_cycles;
-    ++*n_searched;
-    for (uint32_t c = 0; c < sl.R.n_cycles; ++c) cyc_len[(*n_cycles)++] = sl.cyc_off[c + 1] - sl.cyc_off[c];
-    for (uint32_t j = 0; j < sl.R.n_nodes; ++j) nodes[(*n_nodes)++] = sl.cyc_nodes[j];
-    stats[1] += sl.R.status == kEnumBound;
-    stats[2] += sl.R.status == kEnumCap;
+  EmuSlot sl;
+  sl.init(max_len, lock_log, 8192, 128);
+  auto advance_view = [&](uint64_t upto) {
+    while (view_idx < upto) {
+      for (uint32_t x : marks[view_idx]) view[x >> 5] |= 1u << (x & 31);
+      ++view_idx;
+    }
   };
-  while (pos < n) {
-    uint32_t cnt = (uint32_t)std::min<uint64_t>(window, n - pos);
-    std::vector<uint32_t> snapshot(e->visited);
-    for (uint32_t i = 0; i < cnt; ++i) {  // "search kernel": all against the snapshot
-      EmuSlot &sl = slots[i];
-      uint32_t s = (uint32_t)starts[pos + i];
-      if (visited_bit(snapshot.data(), s)) { sl.R.status = kEnumPreSkipped; sl.R.n_keys = sl.R.n_nodes = sl.R.n_cycles = 0; continue; }
-      std::fill(sl.lock.begin(), sl.lock.end(), ~0ull);
-      enum_run(v, e->adj.data(), snapshot.data(), s, min_len, max_len, sl.A, sl.R);
+  for (uint64_t t = 0; t < n; ++t) {
+    uint32_t s = (uint32_t)starts[t];
+    advance_view(t > window ? t - window : 0);
+    EmuSlot *cur = &sl;
+    EmuSlot big;
+    cur->R.status = kEnumSkipped;
+    cur->R.n_keys = cur->R.n_nodes = cur->R.n_cycles = 0;
+    if (!visited_bit(view.data(), s)) {
+      ++cur->A.epoch;
+      enum_run(v, e->adj.data(), view.data(), s, min_len, max_len, cur->A, cur->R, [&]() {
+        advance_view(std::min<uint64_t>(view_idx + 1, t));
+        return visited_bit(view.data(), s);
+      });
+      if (cur->R.status == kEnumSkipped) ++stats[4];
     }
-    ++stats[4];
-    uint32_t i = 0;
-    int reason = 0;
-    for (; i < cnt; ++i) {  // "commit kernel"
-      EmuSlot &sl = slots[i];
-      uint32_t s = (uint32_t)starts[pos + i];
-      if (visited_bit(vis, s)) { ++stats[0]; continue; }
-      if (sl.R.status == kEnumOverflow) { reason = 2; break; }
-      bool conflict = false;
-      for (uint32_t j = 0; j < sl.R.n_keys; ++j)
-        if (sl.keylog[j] != s && visited_bit(vis, sl.keylog[j])) { conflict = true; break; }
-      if (conflict) { reason = 1; break; }
-      accept(s, sl);
-    }
-    pos += i;
-    if (reason == 1) ++stats[3];
-    if (reason == 2) {
-      uint32_t ll = lock_log + 4, rc = 1u << 16;
-      for (;;) {
-        EmuSlot big;
-        big.init(max_len, ll, rc, kClusterBound);
-        uint32_t s = (uint32_t)starts[pos];
-        enum_run(v, e->adj.data(), vis, s, min_len, max_len, big.A, big.R);
-        ++stats[5];
-        if (big.R.status != kEnumOverflow) { accept(s, big); break; }
+    // ---- commit at position t: `vis` is the exact bitmap
+    if (cur->R.status == kEnumSkipped || visited_bit(vis, s)) { ++stats[0]; continue; }
+    uint32_t ll = lock_log + 4, rc = 1u << 16;
+    for (;;) {
+      if (cur->R.status == kEnumOverflow) {
         if (ll >= 26) return -1;
+        big = EmuSlot();
+        big.init(max_len, ll, rc, kClusterBound);
+        cur = &big;
+        ++cur->A.epoch;
+        enum_run(v, e->adj.data(), vis, s, min_len, max_len, cur->A, cur->R, []() { return false; });
+        ++stats[5];
         ll += 2; rc *= 4;
+        continue;
       }
-      pos += 1;
+      bool conflict = false;
+      for (uint32_t j = 0; j < cur->R.n_keys; ++j)
+        if (cur->keylog[j] != s && visited_bit(vis, cur->keylog[j])) { conflict = true; break; }
+      if (!conflict) break;
+      ++stats[3];
+      ++cur->A.epoch;
+      enum_run(v, e->adj.data(), vis, s, min_len, max_len, cur->A, cur->R, []() { return false; });
     }
+    for (uint32_t j = 0; j < cur->R.n_nodes; ++j) {
+      uint32_t x = cur->cyc_nodes[j];
+      vis[x >> 5] |= 1u << (x & 31);
+      marks[t].push_back(x);
+    }
+    searched[*n_searched] = s;
+    cyc_count[*n_searched] = cur->R.n_cycles;
+    ++*n_searched;
+    for (uint32_t c = 0; c < cur->R.n_cycles; ++c) cyc_len[(*n_cycles)++] = cur->cyc_off[c + 1] - cur->cyc_off[c];
+    for (uint32_t j = 0; j < cur->R.n_nodes; ++j) nodes[(*n_nodes)++] = cur->cyc_nodes[j];
+    stats[1] += cur->R.status == kEnumBound;
+    stats[2] += cur->R.status == kEnumCap;
   }
   return 0;
 }

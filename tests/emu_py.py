@@ -121,4 +121,4 @@ class EmuGraph:
                 paths.append(nodes[ni:ni + ln].copy())
                 ni += ln
             out.append((int(searched[i]), paths))
-        return out, dict(zip(("skipped", "bound", "cap", "reruns", "rounds", "overflow_reruns"), map(int, stats)))
+        return out, dict(zip(("skipped", "bound", "cap", "reruns", "abandoned", "overflow_reruns"), map(int, stats)))

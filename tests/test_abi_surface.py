@@ -31,7 +31,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(gpu.GraphDesc) == 8 + 4 * 4 + 8 * 8 + 8 + 48
     assert C.sizeof(gpu.PruneStats) == 40
     assert C.sizeof(gpu.Starts) == 56
-    assert C.sizeof(gpu.Cycles) == 96
+    assert C.sizeof(gpu.Cycles) == 112
 
 
 def _has_cuda():
