@@ -27,44 +27,43 @@
 
 namespace mg {
 
-struct SlotLayout {  // per-worker arena (byte offsets inside one slot)
-  uint32_t lock_log, keylog_cap, relax_cap, cyc_nodes_cap, depth_cap;
-  size_t off_hdr, off_path, off_pent, off_bl, off_stk, off_lock, off_keylog, off_relax, off_cyc_nodes, off_cyc_off,
-      bytes;
+struct SlotLayout {  // per-worker arena in global memory (byte offsets inside one slot)
+  uint32_t index_log, ent_cap, relax_cap, cyc_nodes_cap, depth_cap;
+  size_t off_index, off_hot, off_cold, off_relax, off_cyc_nodes, off_cyc_off, bytes;
+  uint32_t smem_bytes;  // per worker: path, pent, bl, stk live in shared memory
 };
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
-static SlotLayout make_layout(int max_len, uint32_t lock_log, uint32_t relax_cap, uint32_t cyc_cap_cycles) {
+static SlotLayout make_layout(int max_len, uint32_t index_log, uint32_t relax_cap, uint32_t cyc_cap_cycles) {
   SlotLayout L;
-  L.lock_log = lock_log;
-  L.keylog_cap = (1u << lock_log) / 2;
+  L.index_log = index_log;
+  L.ent_cap = (1u << index_log) / 2;
   L.relax_cap = relax_cap;
   L.depth_cap = (uint32_t)max_len + 4;
   L.cyc_nodes_cap = cyc_cap_cycles * (uint32_t)(max_len + 1);
   size_t o = 0;
-  L.off_hdr = o; o = align_up(o + 64, 64);
-  L.off_lock = o; o = align_up(o + ((size_t)sizeof(LockEnt) << lock_log), 64);
-  L.off_path = o; o = align_up(o + (size_t)L.depth_cap * 4, 16);
-  L.off_pent = o; o = align_up(o + (size_t)L.depth_cap * 4, 16);
-  L.off_bl = o; o = align_up(o + (size_t)L.depth_cap * 4, 16);
-  L.off_stk = o; o = align_up(o + (size_t)L.depth_cap * sizeof(USet), 16);
-  L.off_keylog = o; o = align_up(o + (size_t)L.keylog_cap * 4, 16);
-  L.off_relax = o; o = align_up(o + (size_t)L.relax_cap * 8, 16);
-  L.off_cyc_nodes = o; o = align_up(o + (size_t)L.cyc_nodes_cap * 4, 16);
-  L.off_cyc_off = o; o = align_up(o + (size_t)(kClusterBound + 1) * 4, 16);
+  L.off_hot = o; o = align_up(o + (size_t)L.ent_cap * sizeof(HotEnt), 128);
+  L.off_cold = o; o = align_up(o + (size_t)L.ent_cap * sizeof(ColdEnt), 128);
+  L.off_index = o; o = align_up(o + ((size_t)4 << index_log), 128);
+  L.off_relax = o; o = align_up(o + (size_t)L.relax_cap * 8, 128);
+  L.off_cyc_nodes = o; o = align_up(o + (size_t)L.cyc_nodes_cap * 4, 128);
+  L.off_cyc_off = o; o = align_up(o + (size_t)(kClusterBound + 1) * 4, 128);
   L.bytes = align_up(o, 128);
+  L.smem_bytes = (uint32_t)align_up((size_t)L.depth_cap * (4 + 4 + 4 + sizeof(USet)), 16);
   return L;
 }
-__device__ __forceinline__ EnumArena arena_of(uint8_t *base, const SlotLayout &L) {
+// hot per-level state (path, entry numbers, backtrack lengths, neighbour sets) in shared memory;
+// the lock map, relax stack and staged cycles in the worker's global arena
+__device__ __forceinline__ EnumArena arena_of(uint8_t *base, uint8_t *smem, const SlotLayout &L) {
   EnumArena A;
-  A.path = (uint32_t *)(base + L.off_path);
-  A.pent = (uint32_t *)(base + L.off_pent);
-  A.bl = (int32_t *)(base + L.off_bl);
-  A.stk = (USet *)(base + L.off_stk);
-  A.lock = (LockEnt *)(base + L.off_lock);
-  A.lock_log = L.lock_log;
-  A.epoch = *(uint32_t *)(base + L.off_hdr);
-  A.keylog = (uint32_t *)(base + L.off_keylog);
-  A.keylog_cap = L.keylog_cap;
+  A.stk = (USet *)smem;
+  A.path = (uint32_t *)(smem + (size_t)L.depth_cap * sizeof(USet));
+  A.pent = A.path + L.depth_cap;
+  A.bl = (int32_t *)(A.pent + L.depth_cap);
+  A.index = (uint32_t *)(base + L.off_index);
+  A.index_log = L.index_log;
+  A.hot = (HotEnt *)(base + L.off_hot);
+  A.cold = (ColdEnt *)(base + L.off_cold);
+  A.ent_cap = L.ent_cap;
   A.relax = (uint64_t *)(base + L.off_relax);
   A.relax_cap = L.relax_cap;
   A.cyc_nodes = (uint32_t *)(base + L.off_cyc_nodes);
@@ -80,6 +79,7 @@ struct TicketRec {
   uint32_t n_cycles, n_nodes;
   uint32_t cyc_base, node_base;  // offsets into the output pools
   uint32_t expansions, steps;
+  uint32_t us_searched, us_committed;  // microseconds since the worker entered the kernel
 };
 struct PipeCtl {
   uint32_t ticket;       // next ticket to hand out
@@ -95,17 +95,27 @@ struct PipeCtl {
 
 __device__ __forceinline__ uint32_t ld_vol(const uint32_t *p) { return *(const volatile uint32_t *)p; }
 
-// One warp per block = one worker.  See the header comment for the protocol.
-__global__ void __launch_bounds__(32) k_enum_pipeline(GraphView g, const uint64_t *__restrict__ adj, uint32_t *visited,
+__device__ __forceinline__ unsigned long long gtime_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// One warp = one worker (kWarpsPerBlock workers per block).  See the header comment for the protocol.
+constexpr int kWarpsPerBlock = 4;
+__global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView g, const uint64_t *__restrict__ adj, uint32_t *visited,
                                                      const uint32_t *__restrict__ starts, uint32_t n_end, int min_len,
                                                      int max_len, uint8_t *arena, SlotLayout L, PipeCtl *ctl,
                                                      TicketRec *recs, uint32_t *pool_nodes, uint32_t pool_nodes_cap,
                                                      uint32_t *pool_len, uint32_t pool_len_cap) {
-  const int lane = threadIdx.x;
-  uint8_t *base = arena + (size_t)blockIdx.x * L.bytes;
-  EnumArena A = arena_of(base, L);
+  extern __shared__ __align__(16) uint8_t smem_all[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t worker = blockIdx.x * kWarpsPerBlock + warp;
+  uint8_t *base = arena + (size_t)worker * L.bytes;
+  EnumArena A = arena_of(base, smem_all + (size_t)warp * L.smem_bytes, L);
   unsigned long long searches = 0;
-  uint32_t abandoned = 0;
+  uint32_t abandoned = 0, reruns = 0;
+  const unsigned long long t_kernel = gtime_ns();
   for (;;) {
     uint32_t t = 0;
     if (lane == 0) t = atomicAdd(&ctl->ticket, 1u);
@@ -116,52 +126,78 @@ __global__ void __launch_bounds__(32) k_enum_pipeline(GraphView g, const uint64_
     R.status = kEnumSkipped;
     R.n_cycles = R.n_nodes = R.n_keys = R.steps = R.expansions = 0;
     int stopped = 0;
-    // ---- speculative search against the live bitmap
-    if (lane == 0 && !visited_live(visited, s)) {
-      ++A.epoch;
+    // speculative search against the live bitmap (lane 0); gives up when the start gets marked
+    auto speculate = [&]() {
       ++searches;
       enum_run(g, adj, visited, s, min_len, max_len, A, R, [&]() {
         if (ld_vol(&ctl->stop)) { stopped = 1; return true; }
         return visited_live(visited, s);
       });
       if (R.status == kEnumSkipped && !stopped) ++abandoned;
-    }
-    __syncwarp();  // lane 0's arena writes (key log, staged cycles) are visible to the warp
-    // ---- wait for this ticket's turn
-    if (lane == 0 && !stopped) {
-      while (ld_vol(&ctl->commit_idx) != t) {
-        if (ld_vol(&ctl->stop)) { stopped = 1; break; }
-        __nanosleep(200);
+    };
+    // does the finished search rest on a node that has been marked since? (warp-cooperative)
+    auto stale = [&](uint32_t n_keys) {
+      int conflict = 0;
+      for (uint32_t j = lane; j < n_keys; j += 32) {
+        uint32_t k = A.hot[j].key;
+        if (k != s && visited_live(visited, k)) conflict = 1;
       }
+      return __any_sync(0xffffffffu, conflict) != 0;
+    };
+    if (lane == 0 && !visited_live(visited, s)) speculate();
+    __syncwarp();  // lane 0's arena writes (key log, staged cycles) are visible to the warp
+    const uint32_t us_searched = (uint32_t)((gtime_ns() - t_kernel) / 1000);
+    // ---- wait for this ticket's turn; meanwhile keep the speculative result fresh, so that the
+    //      repeat of a stale search happens here, in parallel, and not inside the ordered commit
+    for (uint32_t spins = 1;; ++spins) {
+      uint32_t ci = 0;
+      int st = stopped;
+      if (lane == 0) {
+        ci = ld_vol(&ctl->commit_idx);
+        st |= (int)ld_vol(&ctl->stop);
+      }
+      ci = __shfl_sync(0xffffffffu, ci, 0);
+      st = __shfl_sync(0xffffffffu, st, 0);
+      if (st) { stopped = 1; break; }
+      if (ci == t) break;
+      int status = __shfl_sync(0xffffffffu, R.status, 0);
+      if ((spins & 7) == 0 && status != kEnumSkipped && status != kEnumOverflow) {
+        if (__shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0)) {
+          R.status = kEnumSkipped;  // an earlier start's cycles cover this one: it will be skipped
+        } else if (stale(__shfl_sync(0xffffffffu, R.n_keys, 0))) {
+          if (lane == 0) speculate();
+          ++reruns;
+          __syncwarp();
+        }
+      }
+      __nanosleep(400);
     }
     stopped = __shfl_sync(0xffffffffu, stopped, 0);
     if (stopped) break;
     __threadfence();  // everything committed before this turn is visible from here on
+    // ---- ordered commit: the bitmap is now exactly the one of position t in the sequential loop
     int status = __shfl_sync(0xffffffffu, R.status, 0);
-    uint32_t n_keys = __shfl_sync(0xffffffffu, R.n_keys, 0);
-    bool skip = status == kEnumSkipped || visited_live(visited, s);  // :476
-    uint32_t reruns = 0;
+    bool skip = __shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0) != 0;  // :476
+    if (!skip && status == kEnumSkipped) {
+      // cannot happen: a search is only abandoned after its start was marked; kept as a safe path
+      if (lane == 0) speculate();
+      __syncwarp();
+      status = __shfl_sync(0xffffffffu, R.status, 0);
+    }
     if (!skip) {
       for (;;) {
         if (status == kEnumOverflow) { stopped = 1; break; }
-        int conflict = 0;
-        for (uint32_t j = lane; j < n_keys; j += 32) {
-          uint32_t k = A.keylog[j];
-          if (k != s && visited_live(visited, k)) conflict = 1;
-        }
-        if (!__any_sync(0xffffffffu, conflict)) break;
-        if (lane == 0) {  // the search saw a stale bitmap: repeat it against the final one
-          ++A.epoch;
+        if (!stale(__shfl_sync(0xffffffffu, R.n_keys, 0))) break;
+        if (lane == 0) {  // exclusive repeat against the final bitmap
           ++searches;
           enum_run(g, adj, visited, s, min_len, max_len, A, R, []() { return false; });
         }
-        __syncwarp();
         ++reruns;
+        __syncwarp();
         status = __shfl_sync(0xffffffffu, R.status, 0);
-        n_keys = __shfl_sync(0xffffffffu, R.n_keys, 0);
       }
     }
-    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0};
+    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0};
     if (!skip && !stopped) {
       const uint32_t n_nodes = __shfl_sync(0xffffffffu, R.n_nodes, 0);
       const uint32_t n_cycles = __shfl_sync(0xffffffffu, R.n_cycles, 0);
@@ -189,24 +225,21 @@ __global__ void __launch_bounds__(32) k_enum_pipeline(GraphView g, const uint64_
       }
     }
     if (stopped) {  // this ticket needs the host (larger arena / larger pool): drain the pipeline
-      if (lane == 0) {
-        if (reruns) atomicAdd(&ctl->n_reruns, reruns);
-        atomicExch(&ctl->stop, (uint32_t)stopped);
-      }
+      if (lane == 0) atomicExch(&ctl->stop, (uint32_t)stopped);
       break;
     }
     if (lane == 0) {
+      rec.us_committed = (uint32_t)((gtime_ns() - t_kernel) / 1000);
       recs[t] = rec;
-      if (reruns) atomicAdd(&ctl->n_reruns, reruns);
     }
     __threadfence();
     __syncwarp();
     if (lane == 0) atomicExch(&ctl->commit_idx, t + 1);  // hand over to the next ticket
   }
   if (lane == 0) {
-    *(uint32_t *)(base + L.off_hdr) = A.epoch;
     if (searches) atomicAdd(&ctl->searches_run, searches);
     if (abandoned) atomicAdd(&ctl->n_abandoned, abandoned);
+    if (reruns) atomicAdd(&ctl->n_reruns, reruns);
   }
 }
 
@@ -262,17 +295,16 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     uint32_t nodes_cap = 1u << 22, len_cap = 1u << 18;
     MG_TRY(pool_nodes.alloc((size_t)nodes_cap * 4));
     MG_TRY(pool_len.alloc((size_t)len_cap * 4));
-    // worker arenas live in the graph handle (epoch-stamped lock tables are reused across calls)
-    const uint32_t workers =
-        (uint32_t)std::min<uint64_t>(n, (uint64_t)g->sm_count * env_u32("MCAAT_ENUM_WORKERS_PER_SM", 16, 1, 32));
-    const SlotLayout L = make_layout(max_len, env_u32("MCAAT_ENUM_LOCK_LOG", 13, 6, 20), 8192, 128);
-    const uint64_t sig = ((uint64_t)L.bytes << 20) ^ (uint64_t)max_len;
-    if (g->enum_arena.bytes < (size_t)workers * L.bytes || g->enum_arena_sig != sig) {
+    // worker arenas live in the graph handle (they need no clearing between searches or calls)
+    const uint32_t want =
+        (uint32_t)std::min<uint64_t>(n, (uint64_t)g->sm_count * env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32));
+    const uint32_t blocks = (want + kWarpsPerBlock - 1) / kWarpsPerBlock, workers = blocks * kWarpsPerBlock;
+    const SlotLayout L = make_layout(max_len, env_u32("MCAAT_ENUM_LOCK_LOG", 16, 6, 22), 32768, kClusterBound);
+    if (g->enum_arena.bytes < (size_t)workers * L.bytes) {
       MG_TRY(g->enum_arena.alloc((size_t)workers * L.bytes));
       MG_CUDA(cudaMemsetAsync(g->enum_arena.p, 0, g->enum_arena.bytes, s));
-      g->enum_arena_sig = sig;
     }
-    uint32_t big_lock_log = std::max<uint32_t>(L.lock_log + 4, 17), big_relax = 1u << 18;
+    uint32_t big_lock_log = std::max<uint32_t>(L.index_log + 3, 19), big_relax = 1u << 20;
     uint32_t pos = 0;
     bool solo = false;  // the ticket at `pos` overflowed a worker arena: run it alone in the big arena
     while (pos < n) {
@@ -283,7 +315,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
       {
         TimedScope ts(g, T_ENUM, solo ? 1 : n - pos);
         if (!solo) {
-          MG_LAUNCH(k_enum_pipeline, workers, 32, 0, s, g->view, g->adj.as<uint64_t>(), g->visited.as<uint32_t>(),
+          MG_LAUNCH(k_enum_pipeline, blocks, 32 * kWarpsPerBlock, L.smem_bytes * kWarpsPerBlock, s, g->view, g->adj.as<uint64_t>(), g->visited.as<uint32_t>(),
                     starts_dev.as<uint32_t>(), (uint32_t)n, min_len, max_len, g->enum_arena.as<uint8_t>(), L,
                     ctl_dev.as<PipeCtl>(), recs_dev.as<TicketRec>(), pool_nodes.as<uint32_t>(), nodes_cap,
                     pool_len.as<uint32_t>(), len_cap);
@@ -293,7 +325,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
             MG_TRY(big_arena.alloc(LB.bytes));
           }
           MG_CUDA(cudaMemsetAsync(big_arena.p, 0, LB.bytes, s));
-          MG_LAUNCH(k_enum_pipeline, 1, 32, 0, s, g->view, g->adj.as<uint64_t>(), g->visited.as<uint32_t>(),
+          MG_LAUNCH(k_enum_pipeline, 1, 32, LB.smem_bytes, s, g->view, g->adj.as<uint64_t>(), g->visited.as<uint32_t>(),
                     starts_dev.as<uint32_t>(), pos + 1, min_len, max_len, big_arena.as<uint8_t>(), LB,
                     ctl_dev.as<PipeCtl>(), recs_dev.as<TicketRec>(), pool_nodes.as<uint32_t>(), nodes_cap,
                     pool_len.as<uint32_t>(), len_cap);
@@ -334,6 +366,15 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     MG_CUDA(cudaStreamSynchronize(s));
   }
   flush_timers(g);
+  if (const char *trace = getenv("MCAAT_ENUM_TRACE")) {  // per-ticket timeline for profiling
+    if (FILE *f = fopen(trace, "w")) {
+      fprintf(f, "ticket,fate,status,steps,n_cycles,us_searched,us_committed\n");
+      for (uint64_t i = 0; i < n; ++i)
+        fprintf(f, "%llu,%d,%d,%u,%u,%u,%u\n", (unsigned long long)i, recs[i].fate, recs[i].status, recs[i].steps,
+                recs[i].n_cycles, recs[i].us_searched, recs[i].us_committed);
+      fclose(f);
+    }
+  }
   // ---- assemble `results` in insertion order (:479; empty results are stored)
   uint64_t n_searched = 0;
   for (uint64_t i = 0; i < n; ++i) n_searched += recs[i].fate == kFateAccepted;

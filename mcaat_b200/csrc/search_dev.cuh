@@ -345,37 +345,42 @@ enum EnumStatus : int32_t {
   kEnumSkipped = 4,   // start already visited (:476) — seen before or while searching
 };
 
-// One entry of the per-search lock map (std::map<uint64_t,int> lock of :140) — 64 bytes = two
-// sectors, first sector = everything the inner loop needs.  Besides the lock value it memoises what
-// the search derives again and again for the same node: the filtered out-neighbour set
-// (_GetOutgoings(node,set,mult), :58-72, in std::unordered_set iteration order), the filtered
-// in-neighbour set (_GetIncomings, :76-88) and whether the node is on the current path (the
-// reference rebuilds a set from `path` for every relaxation, :196).  Entries are valid when
-// their epoch equals the search's epoch, so the table never needs clearing between searches.
-struct LockEnt {
+// The per-search lock map (std::map<uint64_t,int> lock of :140) plus what the search derives again
+// and again for the same node.  Entries are allocated DENSELY in first-touch order, so the working
+// set of a search is contiguous (cache resident) whatever the capacity; a hash index of entry
+// numbers finds them.  An index slot h is live iff index[h] < n_keys and hot[index[h]].home == h,
+// so neither the index nor the entries are ever cleared between searches, and the entry array
+// doubles as the key log (the "examined" set the ordered commit re-checks).
+//   HotEnt  (32 B, one sector): key, lock value, on-path flag, memoised filtered out-neighbour set
+//           (_GetOutgoings(node,set,mult), :58-72, in std::unordered_set iteration order)
+//   ColdEnt (32 B): memoised filtered in-neighbour set (_GetIncomings, :76-88), used by relaxations
+struct HotEnt {
   uint32_t key;
-  uint32_t epoch;
+  uint32_t home;     // index slot that points here
   int32_t val;       // lock value
-  uint32_t nout;     // kMemoNone = not computed yet
+  uint32_t nout;     // low 8 bits: size of out[] or kMemoNone8; bit 8: node is on the current path
   uint32_t out[4];
+};
+struct ColdEnt {
   uint32_t nin;      // kMemoNone = not computed yet
   uint32_t in[4];
-  uint32_t on_path;
-  uint32_t pad[2];
+  uint32_t pad[3];
 };
-static_assert(sizeof(LockEnt) == 64, "lock entry layout");
+static_assert(sizeof(HotEnt) == 32 && sizeof(ColdEnt) == 32, "lock entry layout");
 constexpr uint32_t kMemoNone = 0xFFFFFFFFu;
+constexpr uint32_t kMemoNone8 = 0xFFu;
+constexpr uint32_t kOnPath = 0x100u;
 
 struct EnumArena {
   uint32_t *path;       // [M+2]
-  uint32_t *pent;       // [M+2] lock-table slot of path[i]
+  uint32_t *pent;       // [M+2] entry number of path[i]
   int32_t *bl;          // [M+2]
   USet *stk;            // [M+2]
-  LockEnt *lock;        // [1 << lock_log]
-  uint32_t lock_log;
-  uint32_t epoch;       // current search
-  uint32_t *keylog;     // every key inserted into `lock` during this search = the examined set
-  uint32_t keylog_cap;
+  uint32_t *index;      // [1 << index_log] entry numbers
+  uint32_t index_log;
+  HotEnt *hot;          // [ent_cap]
+  ColdEnt *cold;        // [ent_cap]
+  uint32_t ent_cap;
   uint64_t *relax;      // relax_stack entries (bl << 32 | node), :192-193
   uint32_t relax_cap;
   uint32_t *cyc_nodes;  // staged raw cycles
@@ -386,7 +391,7 @@ struct EnumResult {
   int32_t status;
   uint32_t n_cycles;
   uint32_t n_nodes;
-  uint32_t n_keys;
+  uint32_t n_keys;      // entries in A.hot[] = nodes the search accepted (+ its start)
   uint32_t steps;
   uint32_t expansions;
 };
@@ -395,30 +400,28 @@ MG_HD bool visited_bit(const uint32_t *visited, uint32_t i) { return (visited[i 
 // `visited` is marked by other SMs while searches run (ordered commit): read it through L2
 MG_HD bool visited_live(const uint32_t *visited, uint32_t i) { return (ld_cg32(&visited[i >> 5]) >> (i & 31)) & 1; }
 
-// entry of `key` in the lock map, inserting (val = defval) when absent (std::map::try_emplace /
-// operator[] as used at :168,:200); nullptr when the arena is full.
-MG_HD LockEnt *lock_get(EnumArena &A, uint32_t &n_keys, uint32_t key, int32_t defval, uint32_t *slot_out = nullptr) {
-  uint32_t mask = (1u << A.lock_log) - 1;
-  uint32_t h = hash_u32(key, A.lock_log);
+// entry number of `key` in the lock map, inserting (val = defval) when absent (std::map::try_emplace
+// / operator[] as used at :168,:200); kNull when the arena is full.
+MG_HD uint32_t lock_get(EnumArena &A, uint32_t &n_keys, uint32_t key, int32_t defval) {
+  uint32_t mask = (1u << A.index_log) - 1;
+  uint32_t h = hash_u32(key, A.index_log);
   for (;;) {
-    LockEnt *e = &A.lock[h];
-    if (e->epoch != A.epoch) {
-      if (n_keys >= A.keylog_cap) return nullptr;
-      e->key = key;
-      e->epoch = A.epoch;
-      e->val = defval;
-      e->nout = kMemoNone;
-      e->nin = kMemoNone;
-      e->on_path = 0;
-      A.keylog[n_keys++] = key;
-      if (slot_out) *slot_out = h;
-      return e;
+    uint32_t v = A.index[h];
+    if (v < n_keys && A.hot[v].home == h) {
+      if (A.hot[v].key == key) return v;
+      h = (h + 1) & mask;
+      continue;
     }
-    if (e->key == key) {
-      if (slot_out) *slot_out = h;
-      return e;
-    }
-    h = (h + 1) & mask;
+    if (n_keys >= A.ent_cap) return kNull;
+    v = n_keys++;
+    A.index[h] = v;
+    HotEnt &e = A.hot[v];
+    e.key = key;
+    e.home = h;
+    e.val = defval;
+    e.nout = kMemoNone8;
+    A.cold[v].nin = kMemoNone;
+    return v;
   }
 }
 
@@ -444,35 +447,37 @@ MG_HD void filtered_set(const GraphView &g, const uint32_t *visited, uint32_t no
   n_out = s.n;
   for (uint32_t i = 0; i < s.n && i < 4; ++i) out[i] = s.e[i];
 }
-// _GetOutgoings(node,set,mult), src/cycle_finder.cpp:58-72, memoised in the node's lock entry
-MG_HD void enum_outgoings(const GraphView &g, const uint64_t *adj, const uint32_t *visited, LockEnt *e, uint32_t mu,
+// _GetOutgoings(node,set,mult), src/cycle_finder.cpp:58-72, memoised in the node's entry
+MG_HD void enum_outgoings(const GraphView &g, const uint64_t *adj, const uint32_t *visited, HotEnt &e, uint32_t mu,
                           USet &s, uint32_t &expansions) {
   ++expansions;
-  if (e->nout == kMemoNone) {
-    uint32_t nb[4];
-    int deg = adj_outgoing(ld_ro(&adj[e->key]), nb);
+  if ((e.nout & 0xFFu) == kMemoNone8) {
+    uint32_t nb[4], n = 0;
+    int deg = adj_outgoing(ld_ro(&adj[e.key]), nb);
     if (deg > 4) deg = 4;
-    filtered_set(g, visited, e->key, mu, nb, deg, e->nout, e->out);
+    filtered_set(g, visited, e.key, mu, nb, deg, n, e.out);
+    e.nout = (e.nout & ~0xFFu) | n;
   }
-  s.n = e->nout;
-  for (uint32_t i = 0; i < 4; ++i) s.e[i] = e->out[i];
+  s.n = e.nout & 0xFFu;
+  for (uint32_t i = 0; i < 4; ++i) s.e[i] = e.out[i];
 }
 // _GetIncomings(node,set,mult), src/cycle_finder.cpp:76-88, memoised likewise
-MG_HD void enum_incomings(const GraphView &g, const uint32_t *visited, LockEnt *e, uint32_t mu, uint32_t &expansions) {
+MG_HD void enum_incomings(const GraphView &g, const uint32_t *visited, uint32_t key, ColdEnt &c, uint32_t mu,
+                          uint32_t &expansions) {
   ++expansions;
-  if (e->nin == kMemoNone) {
+  if (c.nin == kMemoNone) {
     uint32_t nb[4];
-    int deg = incoming(g, e->key, nb);
+    int deg = incoming(g, key, nb);
     if (deg > 4) deg = 4;
     if (deg < 0) deg = 0;
-    filtered_set(g, visited, e->key, mu, nb, deg, e->nin, e->in);
+    filtered_set(g, visited, key, mu, nb, deg, c.nin, c.in);
   }
 }
 
 // FindCycleUtil + FindCycle, src/cycle_finder.cpp:231-243,140-225.  Does NOT mark visited (the
 // ordered commit does, :217-222).  `visited` may gain marks while the search runs; every node the
-// search ACCEPTED is in the key log, and the commit re-checks those, so a search is only kept when
-// it is identical to one run against the bitmap of its position in the sequential order.
+// search ACCEPTED has an entry in A.hot[], and the commit re-checks those, so a search is only kept
+// when it is identical to one run against the bitmap of its position in the sequential order.
 // `poll()` is called every kPollSteps steps; returning true abandons the search (its start has been
 // marked by an earlier start's commit: the reference would skip it, :476).
 // Exact shortcut: once the cluster bound fires every later hit clears the list again, so the result
@@ -488,15 +493,14 @@ MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint
   int32_t status = kEnumDone;
   A.cyc_off[0] = 0;
   {
-    uint32_t slot = 0;
-    LockEnt *e0 = lock_get(A, n_keys, start, 0, &slot);  // lock[start] = 0, :237
-    if (!e0) { status = kEnumOverflow; goto done; }
-    e0->val = 0;
-    e0->on_path = 1;
+    uint32_t v0 = lock_get(A, n_keys, start, 0);  // lock[start] = 0, :237
+    if (v0 == kNull) { status = kEnumOverflow; goto done; }
+    A.hot[v0].val = 0;
+    A.hot[v0].nout |= kOnPath;
     A.path[0] = start;
-    A.pent[0] = slot;
+    A.pent[0] = v0;
     plen = 1;
-    enum_outgoings(g, adj, visited, e0, mu, A.stk[slen++], expansions);
+    enum_outgoings(g, adj, visited, A.hot[v0], mu, A.stk[slen++], expansions);
     A.bl[blen++] = M;
   }
   while (slen > 0) {
@@ -521,16 +525,16 @@ MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint
           A.cyc_off[++n_cycles] = n_nodes;
         }
       } else {
-        uint32_t slot = 0;
-        LockEnt *e = lock_get(A, n_keys, nb, M, &slot);     // try_emplace(nb, M), :168
-        if (!e) { status = kEnumOverflow; goto done; }
-        if (plen < e->val) {
+        uint32_t v = lock_get(A, n_keys, nb, M);            // try_emplace(nb, M), :168
+        if (v == kNull) { status = kEnumOverflow; goto done; }
+        HotEnt &e = A.hot[v];
+        if (plen < e.val) {
           A.path[plen] = nb;                                // :170
-          A.pent[plen] = slot;
+          A.pent[plen] = v;
           ++plen;
           A.bl[blen++] = M;                                 // :171
-          e->val = plen;                                    // :172
-          e->on_path = 1;
+          e.val = plen;                                     // :172
+          e.nout |= kOnPath;
           uset_erase(A.stk[slen - 1], nb);                  // :173
           enum_outgoings(g, adj, visited, e, mu, A.stk[slen], expansions);  // :174-176
           ++slen;
@@ -543,7 +547,7 @@ MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint
       --slen;
       --plen;
       uint32_t v = A.path[plen];
-      A.lock[A.pent[plen]].on_path = 0;
+      A.hot[A.pent[plen]].nout &= ~kOnPath;
       int b = A.bl[--blen];
       if (blen > 0 && b < A.bl[blen - 1]) A.bl[blen - 1] = b;
       if (b < M) {
@@ -553,16 +557,17 @@ MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint
           uint64_t r = A.relax[--rn];
           int rb = (int)(r >> 32);
           uint32_t u = (uint32_t)r;
-          LockEnt *e = lock_get(A, n_keys, u, M);
-          if (!e) { status = kEnumOverflow; goto done; }
-          if (e->val < M - rb + 1) {
-            e->val = M - rb + 1;
-            enum_incomings(g, visited, e, mu, expansions);
-            uint32_t nin = e->nin, in[4] = {e->in[0], e->in[1], e->in[2], e->in[3]};
+          uint32_t vu = lock_get(A, n_keys, u, M);
+          if (vu == kNull) { status = kEnumOverflow; goto done; }
+          if (A.hot[vu].val < M - rb + 1) {
+            A.hot[vu].val = M - rb + 1;
+            enum_incomings(g, visited, u, A.cold[vu], mu, expansions);
+            uint32_t nin = A.cold[vu].nin;
+            uint32_t in[4] = {A.cold[vu].in[0], A.cold[vu].in[1], A.cold[vu].in[2], A.cold[vu].in[3]};
             for (uint32_t i = 0; i < nin; ++i) {
-              LockEnt *ew = lock_get(A, n_keys, in[i], M);  // every accepted neighbour gets an entry
-              if (!ew) { status = kEnumOverflow; goto done; }
-              if (!ew->on_path) {                           // :197-199
+              uint32_t vw = lock_get(A, n_keys, in[i], M);  // every accepted neighbour gets an entry
+              if (vw == kNull) { status = kEnumOverflow; goto done; }
+              if (!(A.hot[vw].nout & kOnPath)) {            // :197-199
                 if (rn >= A.relax_cap) { status = kEnumOverflow; goto done; }
                 A.relax[rn++] = ((uint64_t)(uint32_t)(rb + 1) << 32) | in[i];
               }
@@ -573,14 +578,14 @@ MG_HD_NOINLINE void enum_run(const GraphView &g, const uint64_t *adj, const uint
     }
   }
 leftovers:
-  // On an early stop the neighbour sets still on the stack hold accepted nodes that never got a
-  // lock entry; the ordered commit must see them as examined.
+  // On an early stop the neighbour sets still on the stack hold accepted nodes that never got an
+  // entry; the ordered commit must see them as examined.
   if (status == kEnumBound || status == kEnumCap) {
     for (int l = 0; l < slen; ++l)
       for (uint32_t i = 0; i < A.stk[l].n; ++i) {
         uint32_t x = A.stk[l].e[i];
         if (x == start) continue;
-        if (!lock_get(A, n_keys, x, M)) { status = kEnumOverflow; goto done; }
+        if (lock_get(A, n_keys, x, M) == kNull) { status = kEnumOverflow; goto done; }
       }
   }
 done:

@@ -220,24 +220,26 @@ int emu_dls_bitmap(Emu *e, uint64_t start, int limit) {
 }
 
 struct EmuSlot {
-  std::vector<uint32_t> path, pent, keylog, cyc_nodes, cyc_off;
+  std::vector<uint32_t> path, pent, index, cyc_nodes, cyc_off;
   std::vector<int32_t> bl;
   std::vector<USet> stk;
-  std::vector<LockEnt> lock;
+  std::vector<HotEnt> hot;
+  std::vector<ColdEnt> cold;
   std::vector<uint64_t> relax;
   EnumArena A;
   EnumResult R;
-  void init(int M, uint32_t lock_log, uint32_t relax_cap, uint32_t cyc_cycles) {
+  void init(int M, uint32_t index_log, uint32_t relax_cap, uint32_t cyc_cycles) {
     path.resize(M + 4); pent.resize(M + 4); bl.resize(M + 4); stk.resize(M + 4);
-    lock.resize((size_t)1 << lock_log);
-    memset(lock.data(), 0, lock.size() * sizeof(LockEnt));
-    keylog.resize(((size_t)1 << lock_log) / 2);
+    index.assign((size_t)1 << index_log, 0x5A5A5A5Au);  // deliberately not cleared between searches
+    hot.resize(((size_t)1 << index_log) / 2);
+    cold.resize(hot.size());
+    memset(hot.data(), 0x33, hot.size() * sizeof(HotEnt));
     relax.resize(relax_cap);
     cyc_nodes.resize((size_t)cyc_cycles * (M + 1));
     cyc_off.resize(kClusterBound + 1);
-    A.path = path.data(); A.pent = pent.data(); A.bl = bl.data(); A.stk = stk.data(); A.lock = lock.data();
-    A.lock_log = lock_log; A.epoch = 0;
-    A.keylog = keylog.data(); A.keylog_cap = (uint32_t)keylog.size(); A.relax = relax.data(); A.relax_cap = relax_cap;
+    A.path = path.data(); A.pent = pent.data(); A.bl = bl.data(); A.stk = stk.data();
+    A.index = index.data(); A.index_log = index_log; A.hot = hot.data(); A.cold = cold.data();
+    A.ent_cap = (uint32_t)hot.size(); A.relax = relax.data(); A.relax_cap = relax_cap;
     A.cyc_nodes = cyc_nodes.data(); A.cyc_nodes_cap = (uint32_t)cyc_nodes.size(); A.cyc_off = cyc_off.data();
   }
 };
@@ -260,7 +262,7 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
   *n_searched = *n_cycles = *n_nodes = 0;
   for (int i = 0; i < 6; ++i) stats[i] = 0;
   EmuSlot sl;
-  sl.init(max_len, lock_log, 8192, 128);
+  sl.init(max_len, lock_log, 32768, kClusterBound);
   auto advance_view = [&](uint64_t upto) {
     while (view_idx < upto) {
       for (uint32_t x : marks[view_idx]) view[x >> 5] |= 1u << (x & 31);
@@ -275,7 +277,6 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
     cur->R.status = kEnumSkipped;
     cur->R.n_keys = cur->R.n_nodes = cur->R.n_cycles = 0;
     if (!visited_bit(view.data(), s)) {
-      ++cur->A.epoch;
       enum_run(v, e->adj.data(), view.data(), s, min_len, max_len, cur->A, cur->R, [&]() {
         advance_view(std::min<uint64_t>(view_idx + 1, t));
         return visited_bit(view.data(), s);
@@ -291,18 +292,16 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
         big = EmuSlot();
         big.init(max_len, ll, rc, kClusterBound);
         cur = &big;
-        ++cur->A.epoch;
-        enum_run(v, e->adj.data(), vis, s, min_len, max_len, cur->A, cur->R, []() { return false; });
+          enum_run(v, e->adj.data(), vis, s, min_len, max_len, cur->A, cur->R, []() { return false; });
         ++stats[5];
         ll += 2; rc *= 4;
         continue;
       }
       bool conflict = false;
       for (uint32_t j = 0; j < cur->R.n_keys; ++j)
-        if (cur->keylog[j] != s && visited_bit(vis, cur->keylog[j])) { conflict = true; break; }
+        if (cur->hot[j].key != s && visited_bit(vis, cur->hot[j].key)) { conflict = true; break; }
       if (!conflict) break;
       ++stats[3];
-      ++cur->A.epoch;
       enum_run(v, e->adj.data(), vis, s, min_len, max_len, cur->A, cur->R, []() { return false; });
     }
     for (uint32_t j = 0; j < cur->R.n_nodes; ++j) {

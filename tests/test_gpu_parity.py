@@ -81,7 +81,7 @@ def test_small_arenas_take_the_exact_fallback_tiers(monkeypatch):
     """tier-1 set overflow -> bitmap tier; slot overflow -> large arena; tiny windows -> many rounds"""
     monkeypatch.setenv("MCAAT_DLS_LOG2CAP", "6")
     monkeypatch.setenv("MCAAT_ENUM_LOCK_LOG", "8")
-    monkeypatch.setenv("MCAAT_ENUM_SLOTS_PER_SM", "1")
+    monkeypatch.setenv("MCAAT_ENUM_WORKERS_PER_SM", "1")
     name, thr, mn, mx, dump = [c for c in G.cases() if c[0] == "repeatrich" and c[1] == 5][0]
     ref = O.parse_dump(dump)
     got = run_gpu(DeviceGraph(packed(name)), thr, mn, mx)
