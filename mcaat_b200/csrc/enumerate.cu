@@ -89,7 +89,7 @@ struct PipeCtl {
   uint32_t pool_cycles;
   uint32_t n_reruns;
   uint32_t n_abandoned;  // searches given up because their start got marked
-  uint32_t pad;
+  uint32_t mark_epoch;   // number of commits that marked nodes so far (waiting workers re-check on change)
   unsigned long long searches_run;
 };
 
@@ -148,29 +148,39 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView
     __syncwarp();  // lane 0's arena writes (key log, staged cycles) are visible to the warp
     const uint32_t us_searched = (uint32_t)((gtime_ns() - t_kernel) / 1000);
     // ---- wait for this ticket's turn; meanwhile keep the speculative result fresh, so that the
-    //      repeat of a stale search happens here, in parallel, and not inside the ordered commit
-    for (uint32_t spins = 1;; ++spins) {
-      uint32_t ci = 0;
+    //      repeat of a stale search happens here, in parallel, and not inside the ordered commit.
+    //      `visited` only changes inside commits that mark nodes (mark_epoch), so the result is
+    //      re-examined only when the epoch has moved; the poll itself is one 32-byte sector and backs
+    //      off with the distance to the commit front, so waiting workers leave the L2 to the searches.
+    uint32_t epoch_checked = 0xFFFFFFFFu;
+    for (;;) {
+      uint32_t ci = 0, ep = 0;
       int st = stopped;
       if (lane == 0) {
         ci = ld_vol(&ctl->commit_idx);
+        ep = ld_vol(&ctl->mark_epoch);
         st |= (int)ld_vol(&ctl->stop);
       }
       ci = __shfl_sync(0xffffffffu, ci, 0);
+      ep = __shfl_sync(0xffffffffu, ep, 0);
       st = __shfl_sync(0xffffffffu, st, 0);
       if (st) { stopped = 1; break; }
       if (ci == t) break;
       int status = __shfl_sync(0xffffffffu, R.status, 0);
-      if ((spins & 7) == 0 && status != kEnumSkipped && status != kEnumOverflow) {
+      if (ep != epoch_checked && status != kEnumSkipped && status != kEnumOverflow) {
+        epoch_checked = ep;  // marks made after this read are caught by the next epoch change
+        __threadfence();
         if (__shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0)) {
           R.status = kEnumSkipped;  // an earlier start's cycles cover this one: it will be skipped
         } else if (stale(__shfl_sync(0xffffffffu, R.n_keys, 0))) {
           if (lane == 0) speculate();
           ++reruns;
           __syncwarp();
+          continue;
         }
       }
-      __nanosleep(400);
+      const uint32_t dist = t - ci;
+      __nanosleep(dist <= 2 ? 100u : (dist < 100 ? dist * 200u : 20000u));
     }
     stopped = __shfl_sync(0xffffffffu, stopped, 0);
     if (stopped) break;
@@ -234,7 +244,10 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView
     }
     __threadfence();
     __syncwarp();
-    if (lane == 0) atomicExch(&ctl->commit_idx, t + 1);  // hand over to the next ticket
+    if (lane == 0) {
+      if (rec.n_nodes) atomicAdd(&ctl->mark_epoch, 1u);  // after the fence: the marks are visible first
+      atomicExch(&ctl->commit_idx, t + 1);               // hand over to the next ticket
+    }
   }
   if (lane == 0) {
     if (searches) atomicAdd(&ctl->searches_run, searches);

@@ -33,8 +33,8 @@ int run_candidates(mg_graph *g, uint64_t thr, DevBuf &ids, uint64_t *n_out) {
 }
 
 // ------------------------------------------------------------------ DepthLevelSearch
-// Tier 1: persistent threads, one candidate per thread at a time, pulled from an atomic work
-// queue.  Each thread owns a small open-addressing `seen` set and a DFS stack in global memory
+// Hash tiers: persistent threads, one candidate per thread at a time, pulled from an atomic work
+// queue (tier 1: 2^11-slot sets, every candidate; tier 2: 2^16-slot sets, the overflows of tier 1).  Each thread owns a small open-addressing `seen` set and a DFS stack in global memory
 // (hot parts stay in L1/L2); the set is cleared by undoing the logged slots.
 struct DlsArena {
   uint32_t *tabs;      // [threads][1 << log2cap]
@@ -66,8 +66,8 @@ MG_HD int set_insert(LoggedSet &s, uint32_t key) {
 }
 
 __global__ void __launch_bounds__(128) k_dls(const uint64_t *__restrict__ adj, const uint32_t *__restrict__ cand,
-                                            uint32_t n_cand, int limit, DlsArena A, int8_t *result,
-                                            uint32_t *queue, unsigned long long *expansions) {
+                                            const uint32_t *__restrict__ todo, uint32_t n_cand, int limit, DlsArena A,
+                                            int8_t *result, uint32_t *queue, unsigned long long *expansions) {
   const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
   LoggedSet seen;
   seen.tab = A.tabs + ((size_t)tid << A.log2cap);
@@ -81,18 +81,19 @@ __global__ void __launch_bounds__(128) k_dls(const uint64_t *__restrict__ adj, c
   for (;;) {
     uint32_t idx = atomicAdd(queue, 1u);
     if (idx >= n_cand) break;
+    if (todo) idx = todo[idx];  // later tiers: positions of the searches a smaller set could not hold
     seen.count = 0;
     exp = 0;
     int r = dls_run(adj, cand[idx], limit, seen, stk_node, stk_depth, A.stk_cap, exp);
     result[idx] = (int8_t)r;
-    if (r >= 0) exp_total += exp;  // a search that filled its set is repeated (and counted) by tier 2
+    if (r >= 0) exp_total += exp;  // a search that filled its set is repeated (and counted) by the next tier
     for (uint32_t j = 0; j < seen.count; ++j) seen.tab[seen.log[j]] = kNull;  // undo
   }
   for (int d = 16; d; d >>= 1) exp_total += __shfl_down_sync(0xffffffffu, exp_total, d);
   if ((threadIdx.x & 31) == 0 && exp_total) atomicAdd(expansions, exp_total);
 }
 
-// Tier 2 (exact fallback when a tier-1 set fills up): one block per candidate, `seen` is a full
+// Last tier (exact fallback when the largest hash set fills up): one block per candidate, `seen` is a full
 // bitmap over the graph's items; thread 0 searches, the block clears the bitmap afterwards.
 __global__ void __launch_bounds__(256) k_dls_big(const uint64_t *__restrict__ adj, const uint32_t *__restrict__ cand,
                                                 const uint32_t *__restrict__ todo, uint32_t n_todo, int limit,
@@ -139,47 +140,62 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
     return MG_ELIMIT;
   }
   if (n > 0xFFFFFFF0ull) return MG_ELIMIT;
-  const uint32_t log2cap = env_u32("MCAAT_DLS_LOG2CAP", 11, 6, 16);
   const int block = 128;
-  uint32_t blocks = (uint32_t)g->sm_count * env_u32("MCAAT_DLS_BLOCKS_PER_SM", 8, 1, 16);
-  if ((uint64_t)blocks * block > n) blocks = (uint32_t)((n + block - 1) / block);
-  const size_t threads = (size_t)blocks * block;
-  DlsArena A;
-  A.log2cap = log2cap;
-  A.max_count = (1u << log2cap) / 2;
-  A.stk_cap = (uint32_t)(4 * limit + 8);
-  DevBuf tabs, slotlog, sn, sd, result, ctr;
-  MG_TRY(tabs.alloc((threads << log2cap) * 4));
-  MG_TRY(slotlog.alloc(threads * A.max_count * 2));
-  MG_TRY(sn.alloc(threads * A.stk_cap * 4));
-  MG_TRY(sd.alloc(threads * A.stk_cap * 2));
+  DevBuf sn, sd, result, ctr, todo_b;
   MG_TRY(result.alloc(n));
-  MG_TRY(ctr.alloc(16));
-  MG_CUDA(cudaMemsetAsync(tabs.p, 0xFF, tabs.bytes, s));
-  MG_CUDA(cudaMemsetAsync(ctr.p, 0, 16, s));
-  A.tabs = tabs.as<uint32_t>();
-  A.slotlog = slotlog.as<uint16_t>();
-  A.stk_node = sn.as<uint32_t>();
-  A.stk_depth = sd.as<uint16_t>();
-  {
-    TimedScope ts(g, T_DLS, n);
-    MG_LAUNCH(k_dls, blocks, block, 0, s, g->adj.as<uint64_t>(), ids_dev, (uint32_t)n, limit, A, result.as<int8_t>(),
-              ctr.as<uint32_t>(), (unsigned long long *)(ctr.as<uint64_t>() + 1));
-  }
+  MG_TRY(ctr.alloc(64));
+  MG_CUDA(cudaMemsetAsync(ctr.p, 0, 64, s));
+  unsigned long long *exp_dev = (unsigned long long *)(ctr.as<uint64_t>() + 1);
   std::vector<int8_t> res(n);
-  MG_CUDA(cudaMemcpyAsync(res.data(), result.p, n, cudaMemcpyDeviceToHost, s));
-  MG_CUDA(cudaStreamSynchronize(s));
-  tabs.release();
-  slotlog.release();
-  // --- tier 2 for searches whose set filled up
   std::vector<uint32_t> todo;
-  for (uint64_t i = 0; i < n; ++i) {
-    if (res[i] == kDlsSetFull) todo.push_back((uint32_t)i);
-    else if (res[i] == kDlsStackFull) {
-      set_error("mg_dls: DFS stack bound violated (internal)");
-      return MG_EINTERNAL;
+  // hash tiers: (slots per search, searches in flight).  A search whose set fills up is repeated
+  // from scratch by the next tier; nothing of a failed attempt is kept.
+  const uint32_t tier_log[2] = {env_u32("MCAAT_DLS_LOG2CAP", 11, 6, 16), env_u32("MCAAT_DLS_LOG2CAP2", 16, 6, 16)};
+  const uint32_t tier_threads[2] = {(uint32_t)g->sm_count * env_u32("MCAAT_DLS_BLOCKS_PER_SM", 8, 1, 16) * block,
+                                    (uint32_t)g->sm_count * env_u32("MCAAT_DLS_THREADS2_PER_SM", 64, 1, 256)};
+  DlsArena A;
+  A.stk_cap = (uint32_t)(4 * limit + 8);
+  for (int tier = 0; tier < 2; ++tier) {
+    const uint64_t n_work = tier == 0 ? n : todo.size();
+    if (n_work == 0 || (tier == 1 && tier_log[1] <= tier_log[0])) continue;
+    uint32_t blocks = (uint32_t)std::min<uint64_t>((tier_threads[tier] + block - 1) / block, (n_work + block - 1) / block);
+    const size_t threads = (size_t)blocks * block;
+    A.log2cap = tier_log[tier];
+    A.max_count = (1u << A.log2cap) / 2;
+    DevBuf tabs, slotlog;
+    MG_TRY(tabs.alloc((threads << A.log2cap) * 4));
+    MG_TRY(slotlog.alloc(threads * A.max_count * 2));
+    MG_TRY(sn.ensure(threads * A.stk_cap * 4));
+    MG_TRY(sd.ensure(threads * A.stk_cap * 2));
+    MG_CUDA(cudaMemsetAsync(tabs.p, 0xFF, tabs.bytes, s));
+    MG_CUDA(cudaMemsetAsync(ctr.p, 0, 4, s));
+    if (tier == 1) {
+      MG_TRY(todo_b.alloc(todo.size() * 4));
+      MG_CUDA(cudaMemcpyAsync(todo_b.p, todo.data(), todo.size() * 4, cudaMemcpyHostToDevice, s));
     }
+    A.tabs = tabs.as<uint32_t>();
+    A.slotlog = slotlog.as<uint16_t>();
+    A.stk_node = sn.as<uint32_t>();
+    A.stk_depth = sd.as<uint16_t>();
+    {
+      TimedScope ts(g, T_DLS, tier == 0 ? n : 0);
+      MG_LAUNCH(k_dls, blocks, block, 0, s, g->adj.as<uint64_t>(), ids_dev, tier == 0 ? nullptr : todo_b.as<uint32_t>(),
+                (uint32_t)n_work, limit, A, result.as<int8_t>(), ctr.as<uint32_t>(), exp_dev);
+    }
+    MG_CUDA(cudaMemcpyAsync(res.data(), result.p, n, cudaMemcpyDeviceToHost, s));
+    MG_CUDA(cudaStreamSynchronize(s));
+    todo.clear();
+    for (uint64_t i = 0; i < n; ++i) {
+      if (res[i] == kDlsSetFull) todo.push_back((uint32_t)i);
+      else if (res[i] == kDlsStackFull) {
+        set_error("mg_dls: DFS stack bound violated (internal)");
+        return MG_EINTERNAL;
+      }
+    }
+    if (getenv("MCAAT_DLS_VERBOSE")) fprintf(stderr, "[mg_dls] tier %d (2^%u slots): %llu searches, %zu overflowed\n", tier,
+                                             A.log2cap, (unsigned long long)n_work, todo.size());
   }
+  // --- exact bitmap tier for searches that overflowed the largest hash set
   if (!todo.empty()) {
     const size_t words = (size_t)((g->view.n + 31) / 32);
     size_t free_b = 0, total_b = 0;
@@ -189,7 +205,7 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
       set_error("mg_dls: not enough device memory for the exact bitmap tier");
       return MG_ENOMEM;
     }
-    DevBuf maps_b, todo_b, sn2, sd2;
+    DevBuf maps_b, sn2, sd2;
     MG_TRY(maps_b.alloc(maps * words * 4));
     MG_TRY(todo_b.alloc(todo.size() * 4));
     MG_TRY(sn2.alloc(maps * A.stk_cap * 4));
@@ -199,7 +215,7 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
       TimedScope ts(g, T_DLS, 0);
       MG_LAUNCH(k_dls_big, (unsigned)maps, 256, 0, s, g->adj.as<uint64_t>(), ids_dev, todo_b.as<uint32_t>(),
                 (uint32_t)todo.size(), limit, maps_b.as<uint32_t>(), words, sn2.as<uint32_t>(), sd2.as<uint16_t>(),
-                A.stk_cap, result.as<int8_t>(), (unsigned long long *)(ctr.as<uint64_t>() + 1));
+                A.stk_cap, result.as<int8_t>(), exp_dev);
     }
     MG_CUDA(cudaMemcpyAsync(res.data(), result.p, n, cudaMemcpyDeviceToHost, s));
     MG_CUDA(cudaStreamSynchronize(s));
