@@ -26,8 +26,8 @@ namespace mg {
 struct alignas(32) LNode {
   uint32_t meta;     // bits 0-15 lock value | 16-18 |out| | 20-22 |in| | 24 node is on the current path
   uint32_t key;      // graph item id
-  uint16_t out[4];   // local ids, iteration order of the std::unordered_set built at :58-72
-  uint16_t in[4];    // local ids, iteration order of the set built at :76-88
+  union { uint16_t out[4]; uint64_t out4; };  // local ids, iteration order of the std::unordered_set built at :58-72
+  union { uint16_t in[4]; uint64_t in4; };    // local ids, iteration order of the set built at :76-88
   uint32_t slot;     // index slot of `key` (for clearing)
   uint32_t pad;
 };
@@ -248,7 +248,7 @@ MG_HD_NOINLINE void ball_dfs(int min_len, int max_len, const BallArena &A, EnumR
     N[0].meta = (m0 & ~kMetaLock) | kMetaOnPath;  // lock[start] = 0, :237
     A.path[0] = 0;
     plen = 1;
-    A.stk[0] = *(const uint64_t *)N[0].out;        // _GetOutgoings(start), :238-240
+    A.stk[0] = N[0].out4;        // _GetOutgoings(start), :238-240
     A.stk_n[0] = (uint8_t)((m0 >> kMetaOutShift) & 7u);
     slen = 1;
     ++expansions;
@@ -292,7 +292,7 @@ MG_HD_NOINLINE void ball_dfs(int min_len, int max_len, const BallArena &A, EnumR
           A.stk[slen - 1] = low | high;
           A.stk_n[slen - 1] = (uint8_t)(n - 1);
         }
-        A.stk[slen] = *(const uint64_t *)N[nb].out;         // :174-176
+        A.stk[slen] = N[nb].out4;         // :174-176
         A.stk_n[slen] = (uint8_t)((meta[i] >> kMetaOutShift) & 7u);
         ++slen;
         ++expansions;
@@ -319,7 +319,7 @@ MG_HD_NOINLINE void ball_dfs(int min_len, int max_len, const BallArena &A, EnumR
             N[u].meta = (mu_ & ~kMetaLock) | (uint32_t)(M - rb + 1);
             ++expansions;                                   // _GetIncomings(u), :197
             const uint32_t nin = (mu_ >> kMetaInShift) & 7u;
-            const uint64_t ins = *(const uint64_t *)N[u].in;
+            const uint64_t ins = N[u].in4;
             if (rn + nin > A.relax_cap) { status = kEnumOverflow; goto done; }
             for (uint32_t i = 0; i < nin; ++i) {
               const uint32_t w = (uint32_t)(ins >> (16 * i)) & 0xFFFFu;

@@ -99,6 +99,7 @@ struct mg_graph {
   mg::DevBuf adj;        // navigation cache (built by mg_prune)
   mg::DevBuf visited;    // n bits, uint32 words
   mg::DevBuf enum_arena; // per-worker search arenas of the enumeration pipeline (grow-only)
+  uint64_t enum_arena_sig = 0;  // layout the arenas were initialised for
   bool pruned = false;
   uint64_t device_bytes = 0;
   int sm_count = 148;

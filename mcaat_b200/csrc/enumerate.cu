@@ -6,8 +6,9 @@
 // loop is a persistent-kernel pipeline with an ORDERED COMMIT:
 //   * worker warps pull tickets (= positions in the start list) from an atomic counter, so the
 //     start nodes in flight are always a contiguous window of the sequential order;
-//   * a worker searches its start immediately (lane 0 drives the sequential search; the warp
-//     shares the bulk work), reading the live `visited` bitmap;
+//   * a worker searches its start immediately, reading the live `visited` bitmap: the warp extracts
+//     the ball the search can touch (parallel BFS, ball_dev.cuh), lane 0 runs the sequential search
+//     on the dense ball records;
 //   * workers commit strictly in ticket order (commit_idx hand-over).  `visited` is only ever
 //     marked inside a commit, so every mark a search sees belongs to a start that precedes it in the
 //     sequential order.  At its turn the worker knows the exact bitmap of its position:
@@ -16,13 +17,14 @@
 //                                                   on the spot (exclusive, hence exact)
 //       otherwise                               -> identical to the sequential search: its cycles'
 //                                                   nodes are marked (:217-222), results appended
-//     ("accepted" = the key log of the lock map, search_dev.cuh; nodes rejected for being visited
-//     stay rejected under a superset, the other tests of _BackgroundCheck ignore `visited`);
+//     ("accepted" = the nodes of the extracted ball; nodes rejected for being visited stay rejected
+//     under a superset, the other tests of _BackgroundCheck ignore `visited`);
 //   * a running search polls visited[start] and gives up as soon as an earlier commit marks it.
 // The committed sequence is identical to the reference's threads=1 loop for any number of workers.
 #include <algorithm>
 
 #include "common.cuh"
+#include "ball_dev.cuh"
 #include "search_dev.cuh"
 
 namespace mg {
@@ -102,8 +104,10 @@ __device__ __forceinline__ unsigned long long gtime_ns() {
 }
 
 // One warp = one worker (kWarpsPerBlock workers per block).  See the header comment for the protocol.
+// k_enum_solo searches with the hash-map search enum_run (search_dev.cuh): the host launches it with
+// ONE worker and a large arena for a ticket whose ball overflowed the arenas of k_enum_pipeline below.
 constexpr int kWarpsPerBlock = 4;
-__global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView g, const uint64_t *__restrict__ adj, uint32_t *visited,
+__global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_solo(GraphView g, const uint64_t *__restrict__ adj, uint32_t *visited,
                                                      const uint32_t *__restrict__ starts, uint32_t n_end, int min_len,
                                                      int max_len, uint8_t *arena, SlotLayout L, PipeCtl *ctl,
                                                      TicketRec *recs, uint32_t *pool_nodes, uint32_t pool_nodes_cap,
@@ -256,6 +260,209 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView
   }
 }
 
+// ---- the pipeline proper: extracted-ball searches (ball_dev.cuh)
+struct BallLayout {  // per-worker arena in global memory (byte offsets inside one slot)
+  uint32_t index_log, node_cap, relax_cap, cyc_cap, depth_cap;
+  size_t off_nodes, off_index, off_relax, off_cyc, off_cyc_off, bytes;
+  uint32_t smem_bytes;  // per worker: path, bl, stk, stk_n live in shared memory
+};
+static BallLayout make_ball_layout(int max_len, uint32_t index_log) {
+  BallLayout L;
+  L.index_log = index_log;
+  L.node_cap = std::min<uint32_t>((1u << index_log) / 2, 65535u);
+  L.relax_cap = std::max<uint32_t>(L.node_cap, 32768u);  // also holds the in-degree counters of the build
+  L.depth_cap = (uint32_t)max_len + 4;
+  L.cyc_cap = (uint32_t)kClusterBound * (uint32_t)(max_len + 1);
+  size_t o = 0;
+  L.off_nodes = o; o = align_up(o + (size_t)L.node_cap * sizeof(LNode), 128);
+  L.off_index = o; o = align_up(o + ((size_t)8 << index_log), 128);
+  L.off_relax = o; o = align_up(o + (size_t)L.relax_cap * 4, 128);
+  L.off_cyc = o; o = align_up(o + (size_t)L.cyc_cap * 2, 128);
+  L.off_cyc_off = o; o = align_up(o + (size_t)(kClusterBound + 1) * 4, 128);
+  L.bytes = align_up(o, 128);
+  L.smem_bytes = (uint32_t)align_up((size_t)L.depth_cap * (8 + 2 + 2 + 1), 16);
+  return L;
+}
+__device__ __forceinline__ BallArena ball_arena_of(uint8_t *base, uint8_t *smem, const BallLayout &L) {
+  BallArena A;
+  A.nodes = (LNode *)(base + L.off_nodes);
+  A.node_cap = L.node_cap;
+  A.index = (uint64_t *)(base + L.off_index);
+  A.index_log = L.index_log;
+  A.relax = (uint32_t *)(base + L.off_relax);
+  A.relax_cap = L.relax_cap;
+  A.cyc = (uint16_t *)(base + L.off_cyc);
+  A.cyc_cap = L.cyc_cap;
+  A.cyc_off = (uint32_t *)(base + L.off_cyc_off);
+  A.stk = (uint64_t *)smem;
+  A.path = (uint16_t *)(smem + (size_t)L.depth_cap * 8);
+  A.bl = (int16_t *)(A.path + L.depth_cap);
+  A.stk_n = (uint8_t *)(A.bl + L.depth_cap);
+  return A;
+}
+
+__global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView g, const uint64_t *__restrict__ adj, uint32_t *visited,
+                                                     const uint32_t *__restrict__ starts, uint32_t n_end, int min_len,
+                                                     int max_len, uint8_t *arena, BallLayout L, PipeCtl *ctl,
+                                                     TicketRec *recs, uint32_t *pool_nodes, uint32_t pool_nodes_cap,
+                                                     uint32_t *pool_len, uint32_t pool_len_cap) {
+  extern __shared__ __align__(16) uint8_t smem_all[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t worker = blockIdx.x * kWarpsPerBlock + warp;
+  const BallArena A = ball_arena_of(arena + (size_t)worker * L.bytes, smem_all + (size_t)warp * L.smem_bytes, L);
+  Coop co;
+  co.lane = lane;
+  unsigned long long searches = 0;
+  uint32_t abandoned = 0, reruns = 0;
+  uint32_t live = 0;  // ball nodes whose index slots are still occupied
+  const unsigned long long t_kernel = gtime_ns();
+  for (;;) {
+    uint32_t t = 0;
+    if (lane == 0) t = atomicAdd(&ctl->ticket, 1u);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    if (t >= n_end || __shfl_sync(0xffffffffu, ld_vol(&ctl->stop), 0)) break;
+    const uint32_t s = starts[t];
+    EnumResult R;
+    R.status = kEnumSkipped;
+    R.n_cycles = R.n_nodes = R.n_keys = R.steps = R.expansions = 0;
+    int stopped = 0;
+    // speculative search against the live bitmap: the warp extracts the ball, lane 0 searches it and
+    // gives up when the start gets marked.  Called by all lanes.
+    auto speculate = [&](bool exclusive) {
+      ++searches;
+      ball_clear(A, live, co);
+      const int st = ball_build(g, adj, visited, s, max_len, A, live, co);
+      if (lane == 0) {
+        R.status = st;
+        R.n_cycles = R.n_nodes = R.steps = R.expansions = 0;
+        R.n_keys = live;
+        if (st == kEnumDone) {
+          if (exclusive) {
+            ball_dfs(min_len, max_len, A, R, []() { return false; });
+          } else {
+            ball_dfs(min_len, max_len, A, R, [&]() {
+              if (ld_vol(&ctl->stop)) { stopped = 1; return true; }
+              return visited_live(visited, s);
+            });
+            if (R.status == kEnumSkipped && !stopped) ++abandoned;
+          }
+        }
+      }
+      __syncwarp();  // lane 0's arena writes (staged cycles) are visible to the warp
+    };
+    // does the finished search rest on a node that has been marked since? (warp-cooperative)
+    auto stale = [&](uint32_t n_keys) {
+      int conflict = 0;
+      for (uint32_t j = 1 + lane; j < n_keys; j += 32) {
+        uint32_t k = A.nodes[j].key;
+        if (k != s && visited_live(visited, k)) conflict = 1;
+      }
+      return __any_sync(0xffffffffu, conflict) != 0;
+    };
+    if (!__shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0)) speculate(false);
+    const uint32_t us_searched = (uint32_t)((gtime_ns() - t_kernel) / 1000);
+    // ---- wait for this ticket's turn; meanwhile keep the speculative result fresh, so that the
+    //      repeat of a stale search happens here, in parallel, and not inside the ordered commit.
+    //      `visited` only changes inside commits that mark nodes (mark_epoch), so the result is
+    //      re-examined only when the epoch has moved; the poll itself is one 32-byte sector and backs
+    //      off with the distance to the commit front, so waiting workers leave the L2 to the searches.
+    uint32_t epoch_checked = 0xFFFFFFFFu;
+    for (;;) {
+      uint32_t ci = 0, ep = 0;
+      int st = stopped;
+      if (lane == 0) {
+        ci = ld_vol(&ctl->commit_idx);
+        ep = ld_vol(&ctl->mark_epoch);
+        st |= (int)ld_vol(&ctl->stop);
+      }
+      ci = __shfl_sync(0xffffffffu, ci, 0);
+      ep = __shfl_sync(0xffffffffu, ep, 0);
+      st = __shfl_sync(0xffffffffu, st, 0);
+      if (st) { stopped = 1; break; }
+      if (ci == t) break;
+      const int status = __shfl_sync(0xffffffffu, R.status, 0);
+      if (ep != epoch_checked && status != kEnumSkipped && status != kEnumOverflow) {
+        epoch_checked = ep;  // marks made after this read are caught by the next epoch change
+        __threadfence();
+        if (__shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0)) {
+          R.status = kEnumSkipped;  // an earlier start's cycles cover this one: it will be skipped
+        } else if (stale(__shfl_sync(0xffffffffu, R.n_keys, 0))) {
+          speculate(false);
+          ++reruns;
+          continue;
+        }
+      }
+      const uint32_t dist = t - ci;
+      __nanosleep(dist <= 2 ? 100u : (dist < 100 ? dist * 200u : 20000u));
+    }
+    stopped = __shfl_sync(0xffffffffu, stopped, 0);
+    if (stopped) break;
+    __threadfence();  // everything committed before this turn is visible from here on
+    // ---- ordered commit: the bitmap is now exactly the one of position t in the sequential loop
+    int status = __shfl_sync(0xffffffffu, R.status, 0);
+    const bool skip = __shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0) != 0;  // :476
+    if (!skip) {
+      // kEnumSkipped here cannot happen (a search is only abandoned after its start was marked); it
+      // takes the same exclusive repeat as a stale result
+      while (status != kEnumOverflow &&
+             (status == kEnumSkipped || stale(__shfl_sync(0xffffffffu, R.n_keys, 0)))) {
+        speculate(true);  // exclusive repeat against the final bitmap
+        ++reruns;
+        status = __shfl_sync(0xffffffffu, R.status, 0);
+      }
+      if (status == kEnumOverflow) stopped = 1;
+    }
+    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0};
+    if (!skip && !stopped) {
+      const uint32_t n_nodes = __shfl_sync(0xffffffffu, R.n_nodes, 0);
+      const uint32_t n_cycles = __shfl_sync(0xffffffffu, R.n_cycles, 0);
+      const uint32_t node_base = ld_vol(&ctl->pool_nodes), cyc_base = ld_vol(&ctl->pool_cycles);
+      if ((uint64_t)node_base + n_nodes > pool_nodes_cap || (uint64_t)cyc_base + n_cycles > pool_len_cap) {
+        stopped = 2;
+      } else {
+        for (uint32_t j = lane; j < n_nodes; j += 32) {  // :217-222 + results[start] = cycles (:479)
+          const uint32_t x = A.nodes[A.cyc[j]].key;
+          pool_nodes[node_base + j] = x;
+          atomicOr(&visited[x >> 5], 1u << (x & 31));
+        }
+        for (uint32_t j = lane; j < n_cycles; j += 32) pool_len[cyc_base + j] = A.cyc_off[j + 1] - A.cyc_off[j];
+        rec.fate = kFateAccepted;
+        rec.n_cycles = n_cycles;
+        rec.n_nodes = n_nodes;
+        rec.cyc_base = cyc_base;
+        rec.node_base = node_base;
+        rec.expansions = __shfl_sync(0xffffffffu, R.expansions, 0);
+        rec.steps = __shfl_sync(0xffffffffu, R.steps, 0);
+        if (lane == 0) {
+          ctl->pool_nodes = node_base + n_nodes;
+          ctl->pool_cycles = cyc_base + n_cycles;
+        }
+      }
+    }
+    if (stopped) {  // this ticket needs the host (hash-map search in a large arena / larger pool): drain
+      if (lane == 0) atomicExch(&ctl->stop, (uint32_t)stopped);
+      break;
+    }
+    if (lane == 0) {
+      rec.us_committed = (uint32_t)((gtime_ns() - t_kernel) / 1000);
+      recs[t] = rec;
+    }
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) {
+      if (rec.n_nodes) atomicAdd(&ctl->mark_epoch, 1u);  // after the fence: the marks are visible first
+      atomicExch(&ctl->commit_idx, t + 1);               // hand over to the next ticket
+    }
+  }
+  __syncwarp();
+  ball_clear(A, live, co);  // the index is left empty for the next launch
+  if (lane == 0) {
+    if (searches) atomicAdd(&ctl->searches_run, searches);
+    if (abandoned) atomicAdd(&ctl->n_abandoned, abandoned);
+    if (reruns) atomicAdd(&ctl->n_reruns, reruns);
+  }
+}
+
 static uint32_t env_u32(const char *name, uint32_t def, uint32_t lo, uint32_t hi) {
   const char *e = getenv(name);
   if (!e || !*e) return def;
@@ -312,12 +519,15 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     const uint32_t want =
         (uint32_t)std::min<uint64_t>(n, (uint64_t)g->sm_count * env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32));
     const uint32_t blocks = (want + kWarpsPerBlock - 1) / kWarpsPerBlock, workers = blocks * kWarpsPerBlock;
-    const SlotLayout L = make_layout(max_len, env_u32("MCAAT_ENUM_LOCK_LOG", 16, 6, 22), 32768, kClusterBound);
-    if (g->enum_arena.bytes < (size_t)workers * L.bytes) {
-      MG_TRY(g->enum_arena.alloc((size_t)workers * L.bytes));
-      MG_CUDA(cudaMemsetAsync(g->enum_arena.p, 0, g->enum_arena.bytes, s));
+    const BallLayout L = make_ball_layout(max_len, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 17));
+    const uint64_t sig = ((uint64_t)L.bytes << 20) ^ ((uint64_t)L.index_log << 8) ^ (uint64_t)workers;
+    if (g->enum_arena.bytes < (size_t)workers * L.bytes || g->enum_arena_sig != sig) {
+      // the hash indices must start out empty (all ones); every launch leaves them empty again
+      MG_TRY(g->enum_arena.ensure((size_t)workers * L.bytes));
+      MG_CUDA(cudaMemsetAsync(g->enum_arena.p, 0xFF, g->enum_arena.bytes, s));
+      g->enum_arena_sig = sig;
     }
-    uint32_t big_lock_log = std::max<uint32_t>(L.index_log + 3, 19), big_relax = 1u << 20;
+    uint32_t big_lock_log = env_u32("MCAAT_ENUM_LOCK_LOG", 19, 6, 26), big_relax = 1u << 20;
     uint32_t pos = 0;
     bool solo = false;  // the ticket at `pos` overflowed a worker arena: run it alone in the big arena
     while (pos < n) {
@@ -338,7 +548,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
             MG_TRY(big_arena.alloc(LB.bytes));
           }
           MG_CUDA(cudaMemsetAsync(big_arena.p, 0, LB.bytes, s));
-          MG_LAUNCH(k_enum_pipeline, 1, 32, LB.smem_bytes, s, g->view, g->adj.as<uint64_t>(), g->visited.as<uint32_t>(),
+          MG_LAUNCH(k_enum_solo, 1, 32, LB.smem_bytes, s, g->view, g->adj.as<uint64_t>(), g->visited.as<uint32_t>(),
                     starts_dev.as<uint32_t>(), pos + 1, min_len, max_len, big_arena.as<uint8_t>(), LB,
                     ctl_dev.as<PipeCtl>(), recs_dev.as<TicketRec>(), pool_nodes.as<uint32_t>(), nodes_cap,
                     pool_len.as<uint32_t>(), len_cap);
@@ -357,7 +567,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
         MG_TRY(grow_copy(pool_len, (size_t)len_cap * 8, (size_t)ctl.pool_cycles * 4, s));
         nodes_cap *= 2;
         len_cap *= 2;
-      } else if (ctl.stop == 1) {  // arena overflow at ticket `pos`
+      } else if (ctl.stop == 1) {  // ticket `pos`: ball overflow -> hash-map search alone in a large arena
         if (solo) {
           if (big_lock_log >= 26) {
             set_error("mg_find_cycles: start %llu does not fit the largest search arena", (unsigned long long)starts[pos]);

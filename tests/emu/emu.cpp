@@ -13,7 +13,7 @@
 #include <algorithm>
 #include <vector>
 
-#include "../../mcaat_b200/csrc/search_dev.cuh"
+#include "../../mcaat_b200/csrc/ball_dev.cuh"
 
 using namespace mg;
 
@@ -219,6 +219,34 @@ int emu_dls_bitmap(Emu *e, uint64_t start, int limit) {
   return dls_run(e->adj.data(), (uint32_t)start, limit, s, sn.data(), sd.data(), (uint32_t)sn.size(), exp);
 }
 
+// 0 = hash-map search (enum_run) only, 1 = extracted-ball search with enum_run as overflow fallback
+static int g_algo = 1;
+static uint32_t g_ball_log = 16;  // ball index slots (node capacity = half)
+
+struct BallSlot {
+  std::vector<LNode> nodes;
+  std::vector<uint64_t> index, stk;
+  std::vector<uint32_t> relax, cyc_off;
+  std::vector<uint16_t> cyc, path;
+  std::vector<int16_t> bl;
+  std::vector<uint8_t> stk_n;
+  BallArena A;
+  uint32_t live = 0;  // nodes of the last build (their index slots are still occupied)
+  void init(int M, uint32_t index_log) {
+    uint32_t cap = std::min<uint32_t>((1u << index_log) / 2, 65535u);
+    nodes.resize(cap);
+    memset((void *)nodes.data(), 0x77, nodes.size() * sizeof(LNode));
+    index.assign((size_t)1 << index_log, kIndexEmpty);
+    relax.resize(std::max<uint32_t>(cap, 32768));
+    cyc.resize((size_t)kClusterBound * (M + 1));
+    cyc_off.resize(kClusterBound + 1);
+    path.resize(M + 4); bl.resize(M + 4); stk.resize(M + 4); stk_n.resize(M + 4);
+    A.nodes = nodes.data(); A.node_cap = cap; A.index = index.data(); A.index_log = index_log;
+    A.relax = relax.data(); A.relax_cap = (uint32_t)relax.size(); A.cyc = cyc.data(); A.cyc_cap = (uint32_t)cyc.size();
+    A.cyc_off = cyc_off.data(); A.path = path.data(); A.bl = bl.data(); A.stk = stk.data(); A.stk_n = stk_n.data();
+  }
+};
+
 struct EmuSlot {
   std::vector<uint32_t> path, pent, index, cyc_nodes, cyc_off;
   std::vector<int32_t> bl;
@@ -263,6 +291,43 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
   for (int i = 0; i < 6; ++i) stats[i] = 0;
   EmuSlot sl;
   sl.init(max_len, lock_log, 32768, kClusterBound);
+  BallSlot bs;
+  if (g_algo == 1) bs.init(max_len, g_ball_log);
+  std::vector<uint32_t> keys, cyc_nodes_flat, cyc_lens;  // result of the last search, whatever ran it
+  EnumResult RR;
+  // one search against bitmap `bm`: fills RR, keys (examined nodes), cyc_lens / cyc_nodes_flat
+  auto collect_legacy = [&](EmuSlot *c) {
+    RR = c->R;
+    keys.clear();
+    for (uint32_t j = 0; j < c->R.n_keys; ++j) keys.push_back(c->hot[j].key);
+    cyc_lens.clear();
+    for (uint32_t j = 0; j < c->R.n_cycles; ++j) cyc_lens.push_back(c->cyc_off[j + 1] - c->cyc_off[j]);
+    cyc_nodes_flat.assign(c->cyc_nodes.begin(), c->cyc_nodes.begin() + c->R.n_nodes);
+  };
+  auto search = [&](const uint32_t *bm, uint32_t s, auto poll) {
+    if (g_algo == 1) {
+      Coop co;
+      ball_clear(bs.A, bs.live, co);
+      uint32_t nn = 0;
+      int st = ball_build(v, e->adj.data(), bm, s, max_len, bs.A, nn, co);
+      bs.live = nn;
+      RR.status = st;
+      RR.n_cycles = RR.n_nodes = RR.n_keys = RR.steps = RR.expansions = 0;
+      if (st == kEnumDone) ball_dfs(min_len, max_len, bs.A, RR, poll);
+      keys.clear();
+      cyc_lens.clear();
+      cyc_nodes_flat.clear();
+      if (RR.status != kEnumOverflow) {
+        for (uint32_t j = 0; j < nn; ++j) keys.push_back(bs.nodes[j].key);
+        RR.n_keys = nn;
+        for (uint32_t j = 0; j < RR.n_cycles; ++j) cyc_lens.push_back(bs.cyc_off[j + 1] - bs.cyc_off[j]);
+        for (uint32_t j = 0; j < RR.n_nodes; ++j) cyc_nodes_flat.push_back(bs.nodes[bs.cyc[j]].key);
+      }
+      return;
+    }
+    enum_run(v, e->adj.data(), bm, s, min_len, max_len, sl.A, sl.R, poll);
+    collect_legacy(&sl);
+  };
   auto advance_view = [&](uint64_t upto) {
     while (view_idx < upto) {
       for (uint32_t x : marks[view_idx]) view[x >> 5] |= 1u << (x & 31);
@@ -272,52 +337,62 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
   for (uint64_t t = 0; t < n; ++t) {
     uint32_t s = (uint32_t)starts[t];
     advance_view(t > window ? t - window : 0);
-    EmuSlot *cur = &sl;
     EmuSlot big;
-    cur->R.status = kEnumSkipped;
-    cur->R.n_keys = cur->R.n_nodes = cur->R.n_cycles = 0;
+    RR.status = kEnumSkipped;
+    RR.n_keys = RR.n_nodes = RR.n_cycles = 0;
     if (!visited_bit(view.data(), s)) {
-      enum_run(v, e->adj.data(), view.data(), s, min_len, max_len, cur->A, cur->R, [&]() {
+      search(view.data(), s, [&]() {
         advance_view(std::min<uint64_t>(view_idx + 1, t));
         return visited_bit(view.data(), s);
       });
-      if (cur->R.status == kEnumSkipped) ++stats[4];
+      if (RR.status == kEnumSkipped) ++stats[4];
     }
     // ---- commit at position t: `vis` is the exact bitmap
-    if (cur->R.status == kEnumSkipped || visited_bit(vis, s)) { ++stats[0]; continue; }
+    if (RR.status == kEnumSkipped || visited_bit(vis, s)) { ++stats[0]; continue; }
     uint32_t ll = lock_log + 4, rc = 1u << 16;
+    bool solo = false;  // after an overflow the ticket is repeated with the hash-map search in a large arena
     for (;;) {
-      if (cur->R.status == kEnumOverflow) {
+      if (RR.status == kEnumOverflow) {
         if (ll >= 26) return -1;
         big = EmuSlot();
         big.init(max_len, ll, rc, kClusterBound);
-        cur = &big;
-          enum_run(v, e->adj.data(), vis, s, min_len, max_len, cur->A, cur->R, []() { return false; });
+        solo = true;
+        enum_run(v, e->adj.data(), vis, s, min_len, max_len, big.A, big.R, []() { return false; });
+        collect_legacy(&big);
         ++stats[5];
         ll += 2; rc *= 4;
         continue;
       }
       bool conflict = false;
-      for (uint32_t j = 0; j < cur->R.n_keys; ++j)
-        if (cur->hot[j].key != s && visited_bit(vis, cur->hot[j].key)) { conflict = true; break; }
+      for (uint32_t k : keys)
+        if (k != s && visited_bit(vis, k)) { conflict = true; break; }
       if (!conflict) break;
       ++stats[3];
-      enum_run(v, e->adj.data(), vis, s, min_len, max_len, cur->A, cur->R, []() { return false; });
+      if (solo) {
+        enum_run(v, e->adj.data(), vis, s, min_len, max_len, big.A, big.R, []() { return false; });
+        collect_legacy(&big);
+      } else {
+        search(vis, s, []() { return false; });
+      }
     }
-    for (uint32_t j = 0; j < cur->R.n_nodes; ++j) {
-      uint32_t x = cur->cyc_nodes[j];
+    for (uint32_t x : cyc_nodes_flat) {
       vis[x >> 5] |= 1u << (x & 31);
       marks[t].push_back(x);
     }
     searched[*n_searched] = s;
-    cyc_count[*n_searched] = cur->R.n_cycles;
+    cyc_count[*n_searched] = RR.n_cycles;
     ++*n_searched;
-    for (uint32_t c = 0; c < cur->R.n_cycles; ++c) cyc_len[(*n_cycles)++] = cur->cyc_off[c + 1] - cur->cyc_off[c];
-    for (uint32_t j = 0; j < cur->R.n_nodes; ++j) nodes[(*n_nodes)++] = cur->cyc_nodes[j];
-    stats[1] += cur->R.status == kEnumBound;
-    stats[2] += cur->R.status == kEnumCap;
+    for (uint32_t l : cyc_lens) cyc_len[(*n_cycles)++] = l;
+    for (uint32_t x : cyc_nodes_flat) nodes[(*n_nodes)++] = x;
+    stats[1] += RR.status == kEnumBound;
+    stats[2] += RR.status == kEnumCap;
   }
   return 0;
+}
+
+void emu_set_algo(int algo, uint32_t ball_log) {
+  g_algo = algo;
+  g_ball_log = ball_log;
 }
 
 }  // extern "C"

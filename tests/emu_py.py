@@ -10,7 +10,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "emu", "emu.cpp")
 LIB = os.path.join(HERE, "emu", "libemu.so")
-HDRS = [os.path.join(HERE, "..", "mcaat_b200", "csrc", h) for h in ("sdbg_dev.cuh", "search_dev.cuh")]
+HDRS = [os.path.join(HERE, "..", "mcaat_b200", "csrc", h) for h in ("sdbg_dev.cuh", "search_dev.cuh", "ball_dev.cuh")]
 
 _lib = None
 
@@ -41,8 +41,14 @@ def lib():
         L.emu_find_cycles.restype = C.c_int
         L.emu_find_cycles.argtypes = ([C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.c_uint32]
                                       + [C.c_void_p] * 8)
+        L.emu_set_algo.argtypes = [C.c_int, C.c_uint32]
         _lib = L
     return _lib
+
+
+def set_algo(algo=1, ball_log=16):
+    """0 = hash-map search (enum_run) only; 1 = extracted-ball search (ball_dev.cuh), enum_run on overflow"""
+    lib().emu_set_algo(algo, ball_log)
 
 
 class EmuGraph:

@@ -61,6 +61,18 @@ def test_device_logic_matches_reference_dump(name, thr, mn, mx, dump):
     assert O.same_run(ref, got) == []
 
 
+@pytest.mark.parametrize("name,thr,mn,mx,dump", G.cases(),
+                         ids=lambda v: str(v) if not isinstance(v, str) or "/" not in v else "")
+def test_hash_map_search_matches_reference_dump(name, thr, mn, mx, dump):
+    """enum_run (the overflow fallback of the extracted-ball search) on its own"""
+    E.set_algo(0)
+    try:
+        got = run_emu(emu(name), thr, mn, mx)
+    finally:
+        E.set_algo(1)
+    assert O.same_run(O.parse_dump(dump), got) == []
+
+
 @pytest.mark.parametrize("window", [1, 3, 1000])
 def test_speculative_window_is_order_exact(window):
     name, thr, mn, mx, dump = [c for c in G.cases() if c[0] == "repeatrich" and c[1] == 20][0]
@@ -72,7 +84,11 @@ def test_speculative_window_is_order_exact(window):
 def test_small_arena_overflow_is_rerun_exactly():
     name, thr, mn, mx, dump = [c for c in G.cases() if c[0] == "repeatrich" and c[1] == 5][0]
     ref = O.parse_dump(dump)
-    got = run_emu(emu(name), thr, mn, mx, window=32, lock_log=6)
+    E.set_algo(1, ball_log=7)  # 64-node balls: most searches overflow into the hash-map search ...
+    try:
+        got = run_emu(emu(name), thr, mn, mx, window=32, lock_log=6)  # ... whose first arena overflows too
+    finally:
+        E.set_algo(1)
     assert O.same_run(ref, got) == []
     assert got.stats["overflow_reruns"] > 0
 

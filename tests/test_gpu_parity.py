@@ -78,9 +78,11 @@ def test_reset_gives_identical_second_run():
 
 
 def test_small_arenas_take_the_exact_fallback_tiers(monkeypatch):
-    """tier-1 set overflow -> tier-2 hash set -> bitmap tier; slot overflow -> large arena; few workers"""
+    """tier-1 set overflow -> tier-2 hash set -> bitmap tier; ball overflow -> hash-map search alone, whose
+    first arena overflows as well; few workers"""
     monkeypatch.setenv("MCAAT_DLS_LOG2CAP", "6")
     monkeypatch.setenv("MCAAT_DLS_LOG2CAP2", "8")
+    monkeypatch.setenv("MCAAT_ENUM_BALL_LOG", "7")
     monkeypatch.setenv("MCAAT_ENUM_LOCK_LOG", "8")
     monkeypatch.setenv("MCAAT_ENUM_WORKERS_PER_SM", "1")
     name, thr, mn, mx, dump = [c for c in G.cases() if c[0] == "repeatrich" and c[1] == 5][0]
