@@ -55,6 +55,7 @@ class ClockSampler:
 
     def __init__(self, gpu_index):
         self.rows = []
+        self.rows_before = 0
         self.proc = None
         self.idx = gpu_index
 
@@ -73,6 +74,8 @@ class ClockSampler:
     def stop(self):
         if self.proc:
             self.proc.terminate()
+        if len(self.rows) > self.rows_before:
+            self.rows = self.rows[self.rows_before:]
         sm = [float(r[1]) for r in self.rows if len(r) > 8 and r[1].replace(".", "").isdigit()]
         mx = [float(r[2]) for r in self.rows if len(r) > 8 and r[2].replace(".", "").isdigit()]
         reasons = set()
@@ -276,21 +279,25 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- warm-up, then EXACTLY --steps timed steps
+    # ---- warm-up, then EXACTLY --steps timed steps.  nvidia-smi starts before the warm-up (its start-up
+    #      takes driver locks for about a second and would stall a timed step); only the samples taken
+    #      during the timed region are used.
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
     for _ in range(args.warmup):
         stats, res_bytes = hot_path_step(g, rank, world, dist, torch)
     g.timers_reset()
     launches0 = gpu.launch_count()
-    clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()
     barrier()
+    clocks.rows_before = len(clocks.rows)
     t0 = time.perf_counter()
-    dev_ms = 0.0
+    dev_ms, step_ms = 0.0, []
     for _ in range(args.steps):
         g.step_begin()
         stats, res_bytes = hot_path_step(g, rank, world, dist, torch)
-        dev_ms += g.step_end()
+        step_ms.append(g.step_end())
+        dev_ms += step_ms[-1]
     barrier()
     wall = time.perf_counter() - t0
     launches = gpu.launch_count() - launches0
@@ -367,7 +374,7 @@ def main():
                    "cycle_max_length": MAX_LEN, "l2": "graph arrays + navigation cache (>2 GB) exceed the 126 MB L2; "
                                                        "no explicit flush", "parallelism": f"dls-shard x{world}",
                    "timing": "CUDA events on the library stream around each step (mg_step_begin/end), max over ranks"},
-        "cycle_find_wall_ms": wall_ms / args.steps, "gpu_launches": int(launches), "clocks": clk,
+        "cycle_find_wall_ms": wall_ms / args.steps, "step_ms": [round(x, 2) for x in step_ms], "gpu_launches": int(launches), "clocks": clk,
         "counts": {k: stats[k] for k in ("n_tips_before", "n_mult1", "n_peeled", "n_valid", "n_tips_after", "n_candidates",
                                           "n_starts", "n_searched", "n_cycles", "n_skipped", "n_bound_hits", "n_cap_hits",
                                           "n_reruns", "n_rounds", "n_searches_run", "n_abandoned", "dls_expansions", "expansions")},

@@ -9,6 +9,7 @@ namespace mg {
 
 static thread_local char g_err[512] = "";
 unsigned long long g_launches = 0;
+thread_local cudaStream_t g_alloc_stream = nullptr;
 const char *kTimerNames[T_COUNT] = {"build_index", "collect_tips", "invalidate_mult1", "peel",      "nav_cache",
                                     "candidates",  "dls",          "enumerate",        "commit",    "navigate"};
 
@@ -40,7 +41,8 @@ static int upload_ids(mg_graph *g, const uint64_t *ids, uint64_t n, DevBuf &dev)
     v[i] = (uint32_t)ids[i];
   }
   MG_TRY(dev.alloc(n * 4 + 16));
-  if (n) MG_CUDA(cudaMemcpy(dev.p, v.data(), n * 4, cudaMemcpyHostToDevice));
+  if (n) MG_CUDA(cudaMemcpyAsync(dev.p, v.data(), n * 4, cudaMemcpyHostToDevice, g->stream));
+  MG_CUDA(cudaStreamSynchronize(g->stream));
   return MG_OK;
 }
 
@@ -59,6 +61,7 @@ using namespace mg;
       set_error("cudaSetDevice(%d) -> %s", (g)->device, cudaGetErrorString(e__)); \
       return MG_ECUDA;                       \
     }                                        \
+    mg::g_alloc_stream = (g)->stream;        \
   } while (0)
 
 extern "C" {
@@ -96,6 +99,14 @@ int mg_graph_create(const mg_graph_desc *d, mg_graph **out) {
     delete g;
     return MG_ECUDA;
   }
+  g_alloc_stream = g->stream;
+  {  // keep freed scratch memory in the pool instead of returning it to the driver
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, d->device) == cudaSuccess) {
+      uint64_t keep = UINT64_MAX;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+  }
   int r = build_graph(g, d);
   if (r != MG_OK) { mg_graph_destroy(g); return r; }
   flush_timers(g);
@@ -106,8 +117,12 @@ int mg_graph_create(const mg_graph_desc *d, mg_graph **out) {
 void mg_graph_destroy(mg_graph *g) {
   if (!g) return;
   cudaSetDevice(g->device);
+  g_alloc_stream = g->stream;
   if (g->stream) cudaStreamSynchronize(g->stream);
   flush_timers(g);
+  // buffers go back to the pool on the handle's stream, which must still exist
+  for (mg::DevBuf *b : {&g->wb, &g->fb, &g->mult, &g->hints, &g->inv0, &g->adj, &g->visited, &g->enum_arena}) b->release();
+  if (g->stream) cudaStreamSynchronize(g->stream);
   for (auto e : g->event_pool) cudaEventDestroy(e);
   if (g->step_a) cudaEventDestroy(g->step_a);
   if (g->step_b) cudaEventDestroy(g->step_b);
@@ -160,7 +175,8 @@ int mg_visited_readback(mg_graph *g, uint64_t *host_words) {
   if (!g->view.n) return MG_OK;
   size_t bytes = (size_t)((g->view.n + 31) / 32) * 4;
   host_words[(g->view.n + 63) / 64 - 1] = 0;
-  MG_CUDA(cudaMemcpy(host_words, g->visited.p, bytes, cudaMemcpyDeviceToHost));
+  MG_CUDA(cudaMemcpyAsync(host_words, g->visited.p, bytes, cudaMemcpyDeviceToHost, g->stream));
+  MG_CUDA(cudaStreamSynchronize(g->stream));
   return MG_OK;
 }
 
@@ -173,7 +189,8 @@ int mg_candidates(mg_graph *g, uint64_t thr, uint64_t **ids, uint64_t *n) {
   uint64_t cnt = 0;
   MG_TRY(run_candidates(g, thr, dev, &cnt));
   std::vector<uint32_t> h(cnt);
-  if (cnt) MG_CUDA(cudaMemcpy(h.data(), dev.p, cnt * 4, cudaMemcpyDeviceToHost));
+  if (cnt) MG_CUDA(cudaMemcpyAsync(h.data(), dev.p, cnt * 4, cudaMemcpyDeviceToHost, g->stream));
+  MG_CUDA(cudaStreamSynchronize(g->stream));
   uint64_t *o = (uint64_t *)malloc((cnt + 1) * 8);
   if (!o) return MG_ENOMEM;
   for (uint64_t i = 0; i < cnt; ++i) o[i] = h[i];
@@ -202,7 +219,8 @@ int mg_select_starts(mg_graph *g, uint64_t thr, int max_len, mg_starts *out) {
   MG_TRY(run_dls(g, cand.as<uint32_t>(), nc, max_len, pass.data(), &exp));
   std::vector<uint32_t> h(nc);
   std::vector<uint16_t> hm;
-  if (nc) MG_CUDA(cudaMemcpy(h.data(), cand.p, nc * 4, cudaMemcpyDeviceToHost));
+  if (nc) MG_CUDA(cudaMemcpyAsync(h.data(), cand.p, nc * 4, cudaMemcpyDeviceToHost, g->stream));
+  MG_CUDA(cudaStreamSynchronize(g->stream));
   MG_TRY(gather_mult(g, cand.as<uint32_t>(), nc, hm));
   std::vector<uint64_t> ids;
   std::vector<uint16_t> mult;

@@ -13,8 +13,8 @@
 //      std::unordered_set iteration order; the filtered in-neighbour sets (_GetIncomings, :76-88) are the
 //      transpose (in-neighbours outside the expanded ball can never carry a lowered lock, so they
 //      never influence a result).
-//   2. ball_dfs — the literal sequential search of :140-225 by one lane over the dense 32-byte
-//      node records: no hashing, no rank/select, one record load per examined neighbour.
+//   2. ball_dfs — the literal sequential search of :140-225 by one lane over the dense node
+//      records: no hashing, no rank/select, one record load per examined neighbour.
 // The ball is the examined-node set of the ordered commit (enumerate.cu).  Capacity overflow
 // (more than 65535 ball nodes, > 4 in-neighbours, relax stack) is reported as kEnumOverflow and the
 // caller repeats the search with enum_run (search_dev.cuh), which has no such limits.
@@ -23,15 +23,20 @@
 
 namespace mg {
 
-struct alignas(32) LNode {
+// A ball node is split into the half every search step reads (16 bytes: two nodes per sector, so the
+// working set of the search stays small enough for the L1) and the half only relaxations and the
+// build need.
+struct alignas(16) LNode {
   uint32_t meta;     // bits 0-15 lock value | 16-18 |out| | 20-22 |in| | 24 node is on the current path
   uint32_t key;      // graph item id
   union { uint16_t out[4]; uint64_t out4; };  // local ids, iteration order of the std::unordered_set built at :58-72
+};
+struct alignas(16) LTail {
   union { uint16_t in[4]; uint64_t in4; };    // local ids, iteration order of the set built at :76-88
   uint32_t slot;     // index slot of `key` (for clearing)
   uint32_t pad;
 };
-static_assert(sizeof(LNode) == 32, "one sector per node");
+static_assert(sizeof(LNode) == 16 && sizeof(LTail) == 16, "two nodes per sector");
 constexpr uint32_t kMetaLock = 0xFFFFu, kMetaOnPath = 1u << 24;
 constexpr int kMetaOutShift = 16, kMetaInShift = 20;
 constexpr uint64_t kIndexEmpty = ~0ull;
@@ -39,6 +44,7 @@ constexpr uint32_t kLidPending = 0xFFFFFFFFu;
 
 struct BallArena {
   LNode *nodes;
+  LTail *tails;
   uint32_t node_cap;    // <= 65535
   uint64_t *index;      // [1 << index_log]: key << 32 | local id; kIndexEmpty when free.  Always left empty.
   uint32_t index_log;
@@ -52,6 +58,7 @@ struct BallArena {
   int16_t *bl;          // [M + 2] backtrack lengths
   uint64_t *stk;        // [M + 2] the level's remaining neighbour set: 4 x uint16, iteration order
   uint8_t *stk_n;       // [M + 2] its size
+  uint32_t *pmeta;      // [M + 2] meta word of the path's nodes (nobody else changes an on-path node's meta)
 };
 
 // cooperative execution policy: the device runs ball_build with the 32 lanes of a warp, the host
@@ -104,7 +111,7 @@ MG_HD void st_cg64(uint64_t *p, uint64_t v) { *p = v; }
 
 // Leaves the hash index empty again (all lanes).  `n_nodes` = nodes of the previous build.
 MG_HD void ball_clear(const BallArena &A, uint32_t n_nodes, const Coop &co) {
-  for (uint32_t i = (uint32_t)co.lane; i < n_nodes; i += Coop::kLanes) st_cg64(&A.index[A.nodes[i].slot], kIndexEmpty);
+  for (uint32_t i = (uint32_t)co.lane; i < n_nodes; i += Coop::kLanes) st_cg64(&A.index[A.tails[i].slot], kIndexEmpty);
   co.sync();
 }
 
@@ -115,12 +122,13 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
   const uint32_t mu = get_mult(g, start);
   const uint32_t imask = (1u << A.index_log) - 1;
   LNode *N = A.nodes;
+  LTail *T = A.tails;
   if (co.lane == 0) {
     uint32_t h = hash_u32(start, A.index_log);
     st_cg64(&A.index[h], ((uint64_t)start << 32) | 0u);
     N[0].meta = (uint32_t)M;
     N[0].key = start;
-    N[0].slot = h;
+    T[0].slot = h;
     A.relax[0] = 0;
   }
   co.sync();
@@ -169,7 +177,7 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
         if ((mine >> j) & 1) {
           N[lid].meta = (uint32_t)M;  // lock default (try_emplace(n, cycle_max_length), :168), no edges yet
           N[lid].key = okn[j];
-          N[lid].slot = slot[j];
+          T[lid].slot = slot[j];
           A.relax[lid] = 0;  // in-degree counter of the transpose below (the relax stack is idle during the build)
           st_cg64(&A.index[slot[j]], ((uint64_t)okn[j] << 32) | lid);
           ++lid;
@@ -197,7 +205,7 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
     for (uint32_t j = 0; j < nout; ++j) {
       const uint32_t x = N[u].out[j];
       const uint32_t pos = meta_add(&A.relax[x], 1u);
-      if (pos < 4) N[x].in[pos] = (uint16_t)u;
+      if (pos < 4) T[x].in[pos] = (uint16_t)u;
       else too_many = true;
     }
   }
@@ -212,7 +220,7 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
     if (nin < 2) continue;
     uint32_t lid[4], key[4];
     for (uint32_t j = 0; j < nin; ++j) {
-      lid[j] = N[x].in[j];
+      lid[j] = T[x].in[j];
       key[j] = N[lid[j]].key;
     }
     for (uint32_t a = 1; a < nin; ++a)  // insertion sort by key
@@ -225,10 +233,28 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
     for (uint32_t j = 0; j < nin; ++j) uset_insert(s, key[j]);
     for (uint32_t j = 0; j < nin; ++j)
       for (uint32_t q = 0; q < nin; ++q)
-        if (key[q] == s.e[j]) N[x].in[j] = (uint16_t)lid[q];
+        if (key[q] == s.e[j]) T[x].in[j] = (uint16_t)lid[q];
   }
   co.sync();
   return kEnumDone;
+}
+
+// first 16 bytes of a node record (meta, key, out-neighbour set) in one load
+struct NodeHead {
+  uint32_t meta;
+  uint64_t out4;
+};
+MG_HD NodeHead ld_head(const LNode *n) {
+  NodeHead h;
+#if defined(__CUDA_ARCH__)
+  const uint4 v = *reinterpret_cast<const uint4 *>(n);
+  h.meta = v.x;
+  h.out4 = (uint64_t)v.z | ((uint64_t)v.w << 32);
+#else
+  h.meta = n->meta;
+  h.out4 = n->out4;
+#endif
+  return h;
 }
 
 // Stage 2 (one lane).  Literal FindCycleUtil + FindCycle, src/cycle_finder.cpp:231-243,140-225, on the
@@ -239,17 +265,20 @@ template <class Poll>
 MG_HD_NOINLINE void ball_dfs(int min_len, int max_len, const BallArena &A, EnumResult &R, Poll poll) {
   const int M = max_len;
   LNode *N = A.nodes;
+  LTail *T = A.tails;
   uint32_t expansions = 0, n_cycles = 0, n_cyc = 0;
   int plen = 0, slen = 0, blen = 0, counter = 0, steps = 0;
   int32_t status = kEnumDone;
   A.cyc_off[0] = 0;
   {
-    const uint32_t m0 = N[0].meta;
-    N[0].meta = (m0 & ~kMetaLock) | kMetaOnPath;  // lock[start] = 0, :237
+    const NodeHead h0 = ld_head(&N[0]);
+    const uint32_t m0 = (h0.meta & ~kMetaLock) | kMetaOnPath;  // lock[start] = 0, :237
+    N[0].meta = m0;
+    A.pmeta[0] = m0;
     A.path[0] = 0;
     plen = 1;
-    A.stk[0] = N[0].out4;        // _GetOutgoings(start), :238-240
-    A.stk_n[0] = (uint8_t)((m0 >> kMetaOutShift) & 7u);
+    A.stk[0] = h0.out4;                                         // _GetOutgoings(start), :238-240
+    A.stk_n[0] = (uint8_t)((h0.meta >> kMetaOutShift) & 7u);
     slen = 1;
     ++expansions;
     A.bl[blen++] = (int16_t)M;
@@ -259,72 +288,86 @@ MG_HD_NOINLINE void ball_dfs(int min_len, int max_len, const BallArena &A, EnumR
     if ((steps & (kPollSteps - 1)) == 0 && poll()) { status = kEnumSkipped; n_cycles = n_cyc = 0; break; }
     const uint64_t set = A.stk[slen - 1];                   // :153 (copy)
     const int n = A.stk_n[slen - 1];
-    // lock values of all members first: the loads overlap, and no lock changes before the scan ends
-    uint32_t meta[4];
+    // records of all members first: the loads overlap, and no lock changes before the scan ends
+    NodeHead hd[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
-      if (i < n) meta[i] = N[(uint32_t)(set >> (16 * i)) & 0xFFFFu].meta;
+      if (i < n) hd[i] = ld_head(&N[(uint32_t)(set >> (16 * i)) & 0xFFFFu]);
     bool flag = true;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      if (i >= n) break;
-      const uint32_t nb = (uint32_t)(set >> (16 * i)) & 0xFFFFu;
-      if (nb == 0) {                                        // n == start_node, :157-166
-        A.bl[blen - 1] = 1;
-        if (plen > min_len) {
-          if (++counter >= kClusterBound) {                 // cluster bound: final answer is empty
-            status = kEnumBound;
-            n_cycles = n_cyc = 0;
-            goto done;
+    for (int i = 0; i < 4; ++i) {                           // static indices: hd[] stays in registers
+      if (i < n && flag) {
+        const uint32_t nb = (uint32_t)(set >> (16 * i)) & 0xFFFFu;
+        if (nb == 0) {                                      // n == start_node, :157-166
+          A.bl[blen - 1] = 1;
+          if (plen > min_len) {
+            if (++counter >= kClusterBound) {               // cluster bound: final answer is empty
+              status = kEnumBound;
+              n_cycles = n_cyc = 0;
+              goto done;
+            }
+            if (n_cyc + (uint32_t)plen > A.cyc_cap) { status = kEnumOverflow; goto done; }
+            for (int j = 0; j < plen; ++j) A.cyc[n_cyc + j] = A.path[j];
+            n_cyc += (uint32_t)plen;
+            A.cyc_off[++n_cycles] = n_cyc;
           }
-          if (n_cyc + (uint32_t)plen > A.cyc_cap) { status = kEnumOverflow; goto done; }
-          for (int j = 0; j < plen; ++j) A.cyc[n_cyc + j] = A.path[j];
-          n_cyc += (uint32_t)plen;
-          A.cyc_off[++n_cycles] = n_cyc;
+        } else if (plen < (int)(hd[i].meta & kMetaLock)) {  // :168
+          A.path[plen] = (uint16_t)nb;                      // :170
+          ++plen;
+          A.bl[blen++] = (int16_t)M;                        // :171
+          const uint32_t m = (hd[i].meta & ~kMetaLock) | (uint32_t)plen | kMetaOnPath;  // :172
+          N[nb].meta = m;
+          A.pmeta[plen - 1] = m;
+          {                                                 // stack.back().erase(n), :173
+            const uint64_t low = i ? set & ((1ull << (16 * i)) - 1) : 0ull;
+            const uint64_t high = i < 3 ? (set >> (16 * (i + 1))) << (16 * i) : 0ull;
+            A.stk[slen - 1] = low | high;
+            A.stk_n[slen - 1] = (uint8_t)(n - 1);
+          }
+          A.stk[slen] = hd[i].out4;                         // :174-176
+          A.stk_n[slen] = (uint8_t)((hd[i].meta >> kMetaOutShift) & 7u);
+          ++slen;
+          ++expansions;
+          flag = false;                                     // break
         }
-      } else if (plen < (int)(meta[i] & kMetaLock)) {       // :168
-        A.path[plen++] = (uint16_t)nb;                      // :170
-        A.bl[blen++] = (int16_t)M;                          // :171
-        N[nb].meta = (meta[i] & ~kMetaLock) | (uint32_t)plen | kMetaOnPath;  // :172
-        {                                                   // stack.back().erase(n), :173
-          const uint64_t low = i ? set & ((1ull << (16 * i)) - 1) : 0ull;
-          const uint64_t high = i < 3 ? (set >> (16 * (i + 1))) << (16 * i) : 0ull;
-          A.stk[slen - 1] = low | high;
-          A.stk_n[slen - 1] = (uint8_t)(n - 1);
-        }
-        A.stk[slen] = N[nb].out4;         // :174-176
-        A.stk_n[slen] = (uint8_t)((meta[i] >> kMetaOutShift) & 7u);
-        ++slen;
-        ++expansions;
-        flag = false;
-        break;
       }
     }
     if (flag) {                                             // :181-211
       --slen;
       --plen;
       const uint32_t v = A.path[plen];
-      N[v].meta &= ~kMetaOnPath;
+      const uint32_t mv = A.pmeta[plen] & ~kMetaOnPath;
+      N[v].meta = mv;
       const int b = A.bl[--blen];
       if (blen > 0 && b < A.bl[blen - 1]) A.bl[blen - 1] = (int16_t)b;
-      if (b < M) {
+      if (b < M && (int)(mv & kMetaLock) < M - b + 1) {     // the first relax entry is (b, v), :192-196
+        // A relax entry (x, u) only acts when lock[u] < M - x + 1, and locks never decrease during
+        // a relaxation, so entries that fail the test when they would be pushed are dropped at once
+        // (:198-199 push them, :195 discards them when popped); the test is repeated at the pop.
         uint32_t rn = 0;
-        A.relax[rn++] = ((uint32_t)b << 16) | v;            // :192-193
+        A.relax[rn++] = ((uint32_t)b << 16) | v;
         while (rn) {
           const uint32_t r = A.relax[--rn];
           const int rb = (int)(r >> 16);
           const uint32_t u = r & 0xFFFFu;
           const uint32_t mu_ = N[u].meta;
+          const uint64_t ins = T[u].in4;
           if ((int)(mu_ & kMetaLock) < M - rb + 1) {        // :195-196
             N[u].meta = (mu_ & ~kMetaLock) | (uint32_t)(M - rb + 1);
             ++expansions;                                   // _GetIncomings(u), :197
             const uint32_t nin = (mu_ >> kMetaInShift) & 7u;
-            const uint64_t ins = N[u].in4;
             if (rn + nin > A.relax_cap) { status = kEnumOverflow; goto done; }
-            for (uint32_t i = 0; i < nin; ++i) {
-              const uint32_t w = (uint32_t)(ins >> (16 * i)) & 0xFFFFu;
-              if (!(N[w].meta & kMetaOnPath)) A.relax[rn++] = ((uint32_t)(rb + 1) << 16) | w;  // :198-199
-            }
+            uint32_t mw[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if ((uint32_t)i < nin) mw[i] = N[(uint32_t)(ins >> (16 * i)) & 0xFFFFu].meta;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if ((uint32_t)i < nin) {
+                const uint32_t w = (uint32_t)(ins >> (16 * i)) & 0xFFFFu;
+                if (!(mw[i] & kMetaOnPath) && (int)(mw[i] & kMetaLock) < M - rb)  // :198-199 + early :195
+                  A.relax[rn++] = ((uint32_t)(rb + 1) << 16) | w;
+              }
           }
         }
       }

@@ -44,25 +44,31 @@ extern unsigned long long g_launches;
     }                                                                         \
   } while (0)
 
+// Device buffers come from the device's stream-ordered memory pool (cudaMallocAsync) on the stream of
+// the graph handle the running API call belongs to: after the first pass of the hot path the scratch
+// buffers of every phase are served from the pool without touching the driver.
+extern thread_local cudaStream_t g_alloc_stream;
 struct DevBuf {
   void *p = nullptr;
   size_t bytes = 0;
+  cudaStream_t st = nullptr;  // stream the buffer was allocated on (and is freed on)
   DevBuf() = default;
   DevBuf(const DevBuf &) = delete;
   DevBuf &operator=(const DevBuf &) = delete;
   ~DevBuf() { release(); }
   void release() {
-    if (p) cudaFree(p);
+    if (p) cudaFreeAsync(p, st);
     p = nullptr;
     bytes = 0;
   }
   int alloc(size_t b) {
     release();
     if (b == 0) b = 16;
-    cudaError_t e = cudaMalloc(&p, b);
+    st = g_alloc_stream;
+    cudaError_t e = cudaMallocAsync(&p, b, st);
     if (e != cudaSuccess) {
       p = nullptr;
-      set_error("cudaMalloc(%zu) -> %s", b, cudaGetErrorString(e));
+      set_error("cudaMallocAsync(%zu) -> %s", b, cudaGetErrorString(e));
       return MG_ENOMEM;
     }
     bytes = b;

@@ -82,6 +82,7 @@ struct TicketRec {
   uint32_t cyc_base, node_base;  // offsets into the output pools
   uint32_t expansions, steps;
   uint32_t us_searched, us_committed;  // microseconds since the worker entered the kernel
+  uint32_t n_ball, us_build;           // size of the last extracted ball and the time its extraction took
 };
 struct PipeCtl {
   uint32_t ticket;       // next ticket to hand out
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_solo(GraphView g, 
         status = __shfl_sync(0xffffffffu, R.status, 0);
       }
     }
-    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0};
+    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0, 0, 0};
     if (!skip && !stopped) {
       const uint32_t n_nodes = __shfl_sync(0xffffffffu, R.n_nodes, 0);
       const uint32_t n_cycles = __shfl_sync(0xffffffffu, R.n_cycles, 0);
@@ -263,7 +264,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_solo(GraphView g, 
 // ---- the pipeline proper: extracted-ball searches (ball_dev.cuh)
 struct BallLayout {  // per-worker arena in global memory (byte offsets inside one slot)
   uint32_t index_log, node_cap, relax_cap, cyc_cap, depth_cap;
-  size_t off_nodes, off_index, off_relax, off_cyc, off_cyc_off, bytes;
+  size_t off_nodes, off_tails, off_index, off_relax, off_cyc, off_cyc_off, bytes;
   uint32_t smem_bytes;  // per worker: path, bl, stk, stk_n live in shared memory
 };
 static BallLayout make_ball_layout(int max_len, uint32_t index_log) {
@@ -275,17 +276,19 @@ static BallLayout make_ball_layout(int max_len, uint32_t index_log) {
   L.cyc_cap = (uint32_t)kClusterBound * (uint32_t)(max_len + 1);
   size_t o = 0;
   L.off_nodes = o; o = align_up(o + (size_t)L.node_cap * sizeof(LNode), 128);
+  L.off_tails = o; o = align_up(o + (size_t)L.node_cap * sizeof(LTail), 128);
   L.off_index = o; o = align_up(o + ((size_t)8 << index_log), 128);
   L.off_relax = o; o = align_up(o + (size_t)L.relax_cap * 4, 128);
   L.off_cyc = o; o = align_up(o + (size_t)L.cyc_cap * 2, 128);
   L.off_cyc_off = o; o = align_up(o + (size_t)(kClusterBound + 1) * 4, 128);
   L.bytes = align_up(o, 128);
-  L.smem_bytes = (uint32_t)align_up((size_t)L.depth_cap * (8 + 2 + 2 + 1), 16);
+  L.smem_bytes = (uint32_t)align_up((size_t)L.depth_cap * (8 + 4 + 2 + 2 + 1), 16);
   return L;
 }
 __device__ __forceinline__ BallArena ball_arena_of(uint8_t *base, uint8_t *smem, const BallLayout &L) {
   BallArena A;
   A.nodes = (LNode *)(base + L.off_nodes);
+  A.tails = (LTail *)(base + L.off_tails);
   A.node_cap = L.node_cap;
   A.index = (uint64_t *)(base + L.off_index);
   A.index_log = L.index_log;
@@ -295,13 +298,14 @@ __device__ __forceinline__ BallArena ball_arena_of(uint8_t *base, uint8_t *smem,
   A.cyc_cap = L.cyc_cap;
   A.cyc_off = (uint32_t *)(base + L.off_cyc_off);
   A.stk = (uint64_t *)smem;
-  A.path = (uint16_t *)(smem + (size_t)L.depth_cap * 8);
+  A.pmeta = (uint32_t *)(smem + (size_t)L.depth_cap * 8);
+  A.path = (uint16_t *)(A.pmeta + L.depth_cap);
   A.bl = (int16_t *)(A.path + L.depth_cap);
   A.stk_n = (uint8_t *)(A.bl + L.depth_cap);
   return A;
 }
 
-__global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView g, const uint64_t *__restrict__ adj, uint32_t *visited,
+__global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphView g, const uint64_t *__restrict__ adj, uint32_t *visited,
                                                      const uint32_t *__restrict__ starts, uint32_t n_end, int min_len,
                                                      int max_len, uint8_t *arena, BallLayout L, PipeCtl *ctl,
                                                      TicketRec *recs, uint32_t *pool_nodes, uint32_t pool_nodes_cap,
@@ -326,12 +330,15 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView
     R.status = kEnumSkipped;
     R.n_cycles = R.n_nodes = R.n_keys = R.steps = R.expansions = 0;
     int stopped = 0;
+    uint32_t us_build = 0;
     // speculative search against the live bitmap: the warp extracts the ball, lane 0 searches it and
     // gives up when the start gets marked.  Called by all lanes.
     auto speculate = [&](bool exclusive) {
       ++searches;
+      const unsigned long long t_build = gtime_ns();
       ball_clear(A, live, co);
       const int st = ball_build(g, adj, visited, s, max_len, A, live, co);
+      us_build = (uint32_t)((gtime_ns() - t_build) / 1000);
       if (lane == 0) {
         R.status = st;
         R.n_cycles = R.n_nodes = R.steps = R.expansions = 0;
@@ -359,7 +366,9 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView
       }
       return __any_sync(0xffffffffu, conflict) != 0;
     };
-    if (!__shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0)) speculate(false);
+    // a ticket whose start is already marked is skipped for good (:476); the committing worker ahead
+    // consumes such tickets itself (below), so this worker just moves on
+    if (__shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0) == 0) speculate(false);
     const uint32_t us_searched = (uint32_t)((gtime_ns() - t_kernel) / 1000);
     // ---- wait for this ticket's turn; meanwhile keep the speculative result fresh, so that the
     //      repeat of a stale search happens here, in parallel, and not inside the ordered commit.
@@ -367,6 +376,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView
     //      re-examined only when the epoch has moved; the poll itself is one 32-byte sector and backs
     //      off with the distance to the commit front, so waiting workers leave the L2 to the searches.
     uint32_t epoch_checked = 0xFFFFFFFFu;
+    bool consumed = false;
     for (;;) {
       uint32_t ci = 0, ep = 0;
       int st = stopped;
@@ -380,6 +390,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView
       st = __shfl_sync(0xffffffffu, st, 0);
       if (st) { stopped = 1; break; }
       if (ci == t) break;
+      if ((int32_t)(ci - t) > 0) { consumed = true; break; }  // skipped on our behalf by an earlier commit
       const int status = __shfl_sync(0xffffffffu, R.status, 0);
       if (ep != epoch_checked && status != kEnumSkipped && status != kEnumOverflow) {
         epoch_checked = ep;  // marks made after this read are caught by the next epoch change
@@ -397,6 +408,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView
     }
     stopped = __shfl_sync(0xffffffffu, stopped, 0);
     if (stopped) break;
+    if (consumed) continue;
     __threadfence();  // everything committed before this turn is visible from here on
     // ---- ordered commit: the bitmap is now exactly the one of position t in the sequential loop
     int status = __shfl_sync(0xffffffffu, R.status, 0);
@@ -412,7 +424,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView
       }
       if (status == kEnumOverflow) stopped = 1;
     }
-    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0};
+    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0, live, us_build};
     if (!skip && !stopped) {
       const uint32_t n_nodes = __shfl_sync(0xffffffffu, R.n_nodes, 0);
       const uint32_t n_cycles = __shfl_sync(0xffffffffu, R.n_cycles, 0);
@@ -449,9 +461,27 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_pipeline(GraphView
     }
     __threadfence();
     __syncwarp();
+    // The bitmap is now the exact one for ticket t + 1, t + 2, ... as long as those are skipped:
+    // consume every directly following ticket whose start is marked (:476), 32 at a time, so that
+    // runs of covered start nodes cost one hand-over instead of one each.
+    uint32_t next = t + 1;
+    for (;;) {
+      const uint32_t c = next + (uint32_t)lane;
+      const bool sk = c < n_end && visited_live(visited, starts[c]);
+      const unsigned m = __ballot_sync(0xffffffffu, sk);
+      const int run = m == 0xffffffffu ? 32 : __ffs((int)~m) - 1;
+      if (lane < run) {
+        const TicketRec skipped = {kFateSkipped, kEnumSkipped, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+        recs[c] = skipped;
+      }
+      next += (uint32_t)run;
+      if (run < 32) break;
+    }
+    __threadfence();
+    __syncwarp();
     if (lane == 0) {
       if (rec.n_nodes) atomicAdd(&ctl->mark_epoch, 1u);  // after the fence: the marks are visible first
-      atomicExch(&ctl->commit_idx, t + 1);               // hand over to the next ticket
+      atomicExch(&ctl->commit_idx, next);                // hand over
     }
   }
   __syncwarp();
@@ -591,10 +621,10 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
   flush_timers(g);
   if (const char *trace = getenv("MCAAT_ENUM_TRACE")) {  // per-ticket timeline for profiling
     if (FILE *f = fopen(trace, "w")) {
-      fprintf(f, "ticket,fate,status,steps,n_cycles,us_searched,us_committed\n");
+      fprintf(f, "ticket,fate,status,steps,n_cycles,us_searched,us_committed,n_ball,us_build\n");
       for (uint64_t i = 0; i < n; ++i)
-        fprintf(f, "%llu,%d,%d,%u,%u,%u,%u\n", (unsigned long long)i, recs[i].fate, recs[i].status, recs[i].steps,
-                recs[i].n_cycles, recs[i].us_searched, recs[i].us_committed);
+        fprintf(f, "%llu,%d,%d,%u,%u,%u,%u,%u,%u\n", (unsigned long long)i, recs[i].fate, recs[i].status, recs[i].steps,
+                recs[i].n_cycles, recs[i].us_searched, recs[i].us_committed, recs[i].n_ball, recs[i].us_build);
       fclose(f);
     }
   }

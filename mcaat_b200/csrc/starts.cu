@@ -221,7 +221,8 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
     MG_CUDA(cudaStreamSynchronize(s));
   }
   uint64_t exp = 0;
-  MG_CUDA(cudaMemcpy(&exp, ctr.as<uint64_t>() + 1, 8, cudaMemcpyDeviceToHost));
+  MG_CUDA(cudaMemcpyAsync(&exp, ctr.as<uint64_t>() + 1, 8, cudaMemcpyDeviceToHost, s));
+  MG_CUDA(cudaStreamSynchronize(s));
   if (expansions) *expansions = exp;
   for (uint64_t i = 0; i < n; ++i) {
     if (res[i] < 0) {

@@ -225,8 +225,9 @@ static uint32_t g_ball_log = 16;  // ball index slots (node capacity = half)
 
 struct BallSlot {
   std::vector<LNode> nodes;
+  std::vector<LTail> tails;
   std::vector<uint64_t> index, stk;
-  std::vector<uint32_t> relax, cyc_off;
+  std::vector<uint32_t> relax, cyc_off, pmeta;
   std::vector<uint16_t> cyc, path;
   std::vector<int16_t> bl;
   std::vector<uint8_t> stk_n;
@@ -235,13 +236,15 @@ struct BallSlot {
   void init(int M, uint32_t index_log) {
     uint32_t cap = std::min<uint32_t>((1u << index_log) / 2, 65535u);
     nodes.resize(cap);
+    tails.resize(cap);
     memset((void *)nodes.data(), 0x77, nodes.size() * sizeof(LNode));
     index.assign((size_t)1 << index_log, kIndexEmpty);
     relax.resize(std::max<uint32_t>(cap, 32768));
     cyc.resize((size_t)kClusterBound * (M + 1));
     cyc_off.resize(kClusterBound + 1);
-    path.resize(M + 4); bl.resize(M + 4); stk.resize(M + 4); stk_n.resize(M + 4);
-    A.nodes = nodes.data(); A.node_cap = cap; A.index = index.data(); A.index_log = index_log;
+    path.resize(M + 4); bl.resize(M + 4); stk.resize(M + 4); stk_n.resize(M + 4); pmeta.resize(M + 4);
+    A.pmeta = pmeta.data();
+    A.nodes = nodes.data(); A.tails = tails.data(); A.node_cap = cap; A.index = index.data(); A.index_log = index_log;
     A.relax = relax.data(); A.relax_cap = (uint32_t)relax.size(); A.cyc = cyc.data(); A.cyc_cap = (uint32_t)cyc.size();
     A.cyc_off = cyc_off.data(); A.path = path.data(); A.bl = bl.data(); A.stk = stk.data(); A.stk_n = stk_n.data();
   }
