@@ -105,9 +105,14 @@ def hot_path_step(g, rank=0, world=1, dist=None, torch=None):
     (DepthLevelSearch, the dominant phase) are sharded block-cyclically over the ranks and their
     pass flags all-gathered; prune / candidate scan / ordered enumeration run replicated (no
     collective inside a search)."""
+    dbg = os.environ.get("BENCH_DEBUG")
+    tt = [time.perf_counter()]
     g.reset()
+    tt.append(time.perf_counter())
     st = g.prune()
+    tt.append(time.perf_counter())
     cand = g.candidates(THR)
+    tt.append(time.perf_counter())
     if world == 1:
         ok, exp = g.dls(cand, MAX_LEN)
     else:
@@ -126,9 +131,15 @@ def hot_path_step(g, rank=0, world=1, dist=None, torch=None):
         e = torch.tensor([exp], dtype=torch.int64, device="cuda")
         dist.all_reduce(e)
         exp = int(e.item())
+    tt.append(time.perf_counter())
     buckets, _ = g.bucket_starts(cand[ok])
     starts = np.concatenate([ids for _, ids in buckets]) if buckets else np.zeros(0, np.uint64)
+    tt.append(time.perf_counter())
     searched, cs = g.find_cycles(starts, MIN_LEN, MAX_LEN)
+    tt.append(time.perf_counter())
+    if dbg:
+        print("[step wall ms] reset %.1f prune %.1f candidates %.1f dls %.1f bucket %.1f find_cycles %.1f" %
+              tuple((b - a) * 1e3 for a, b in zip(tt, tt[1:])), file=sys.stderr)
     res_bytes = 8 * (sum(sum(p.size for p in paths) for _, paths in searched) + len(searched))
     stats = dict(st, n_candidates=int(cand.size), n_starts=int(starts.size), dls_expansions=int(exp), **cs)
     return stats, res_bytes
@@ -283,7 +294,7 @@ def main():
     #      takes driver locks for about a second and would stall a timed step); only the samples taken
     #      during the timed region are used.
     clocks = ClockSampler(local)
-    if rank == 0:
+    if rank == 0 and not os.environ.get("BENCH_NO_CLOCKS"):
         clocks.start()
     for _ in range(args.warmup):
         stats, res_bytes = hot_path_step(g, rank, world, dist, torch)

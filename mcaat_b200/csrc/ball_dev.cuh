@@ -258,36 +258,48 @@ MG_HD NodeHead ld_head(const LNode *n) {
 }
 
 // Stage 2 (one lane).  Literal FindCycleUtil + FindCycle, src/cycle_finder.cpp:231-243,140-225, on the
-// ball; same contract as enum_run (search_dev.cuh): does not mark visited, `poll()` every kPollSteps
-// steps may abandon the search, the cluster bound stops it at once (the answer is empty whatever
-// follows).  Cycles are staged as local ids in A.cyc.
-template <class Poll>
-MG_HD_NOINLINE void ball_dfs(int min_len, int max_len, const BallArena &A, EnumResult &R, Poll poll) {
+// ball; like enum_run (search_dev.cuh) it does not mark visited, and the cluster bound stops it at
+// once (the answer is empty whatever follows).  Cycles are staged as local ids in A.cyc.
+struct DfsState {  // the scalars of a paused search (everything else lives in the arena)
+  int depth = 0;     // path.size() == stack.size() == backtrack_lengths.size()
+  int counter = 0, steps = 0;
+  uint32_t expansions = 0, n_cycles = 0, n_cyc = 0;
+  bool started = false;
+};
+// Runs at most `budget` further steps.  Returns true when the search has ended (R is filled in) and
+// false when it is merely paused: the caller polls (start marked? examined nodes marked? — see
+// enumerate.cu) and calls again with the same state.
+MG_HD_NOINLINE bool ball_dfs(int min_len, int max_len, const BallArena &A, DfsState &S, int budget, EnumResult &R) {
   const int M = max_len;
   LNode *N = A.nodes;
   LTail *T = A.tails;
-  uint32_t expansions = 0, n_cycles = 0, n_cyc = 0;
-  int plen = 0, slen = 0, blen = 0, counter = 0, steps = 0;
+  uint32_t expansions = S.expansions, n_cycles = S.n_cycles, n_cyc = S.n_cyc;
+  int plen = S.depth, counter = S.counter, steps = S.steps;
   int32_t status = kEnumDone;
-  A.cyc_off[0] = 0;
-  {
+  if (!S.started) {
+    S.started = true;
+    A.cyc_off[0] = 0;
     const NodeHead h0 = ld_head(&N[0]);
     const uint32_t m0 = (h0.meta & ~kMetaLock) | kMetaOnPath;  // lock[start] = 0, :237
     N[0].meta = m0;
     A.pmeta[0] = m0;
     A.path[0] = 0;
-    plen = 1;
     A.stk[0] = h0.out4;                                         // _GetOutgoings(start), :238-240
     A.stk_n[0] = (uint8_t)((h0.meta >> kMetaOutShift) & 7u);
-    slen = 1;
+    A.bl[0] = (int16_t)M;
+    plen = 1;
     ++expansions;
-    A.bl[blen++] = (int16_t)M;
   }
-  while (slen > 0) {
+  const int pause_at = steps + budget;
+  while (plen > 0) {
+    if (steps == pause_at) {
+      S.depth = plen; S.counter = counter; S.steps = steps;
+      S.expansions = expansions; S.n_cycles = n_cycles; S.n_cyc = n_cyc;
+      return false;
+    }
     if (++steps > kMaxSteps) { status = kEnumCap; break; }  // :148-151
-    if ((steps & (kPollSteps - 1)) == 0 && poll()) { status = kEnumSkipped; n_cycles = n_cyc = 0; break; }
-    const uint64_t set = A.stk[slen - 1];                   // :153 (copy)
-    const int n = A.stk_n[slen - 1];
+    const uint64_t set = A.stk[plen - 1];                   // :153 (copy)
+    const int n = A.stk_n[plen - 1];
     // records of all members first: the loads overlap, and no lock changes before the scan ends
     NodeHead hd[4];
 #pragma unroll
@@ -299,7 +311,7 @@ MG_HD_NOINLINE void ball_dfs(int min_len, int max_len, const BallArena &A, EnumR
       if (i < n && flag) {
         const uint32_t nb = (uint32_t)(set >> (16 * i)) & 0xFFFFu;
         if (nb == 0) {                                      // n == start_node, :157-166
-          A.bl[blen - 1] = 1;
+          A.bl[plen - 1] = 1;
           if (plen > min_len) {
             if (++counter >= kClusterBound) {               // cluster bound: final answer is empty
               status = kEnumBound;
@@ -312,34 +324,32 @@ MG_HD_NOINLINE void ball_dfs(int min_len, int max_len, const BallArena &A, EnumR
             A.cyc_off[++n_cycles] = n_cyc;
           }
         } else if (plen < (int)(hd[i].meta & kMetaLock)) {  // :168
-          A.path[plen] = (uint16_t)nb;                      // :170
-          ++plen;
-          A.bl[blen++] = (int16_t)M;                        // :171
-          const uint32_t m = (hd[i].meta & ~kMetaLock) | (uint32_t)plen | kMetaOnPath;  // :172
-          N[nb].meta = m;
-          A.pmeta[plen - 1] = m;
           {                                                 // stack.back().erase(n), :173
             const uint64_t low = i ? set & ((1ull << (16 * i)) - 1) : 0ull;
             const uint64_t high = i < 3 ? (set >> (16 * (i + 1))) << (16 * i) : 0ull;
-            A.stk[slen - 1] = low | high;
-            A.stk_n[slen - 1] = (uint8_t)(n - 1);
+            A.stk[plen - 1] = low | high;
+            A.stk_n[plen - 1] = (uint8_t)(n - 1);
           }
-          A.stk[slen] = hd[i].out4;                         // :174-176
-          A.stk_n[slen] = (uint8_t)((hd[i].meta >> kMetaOutShift) & 7u);
-          ++slen;
+          A.path[plen] = (uint16_t)nb;                      // :170
+          A.bl[plen] = (int16_t)M;                          // :171
+          A.stk[plen] = hd[i].out4;                         // :174-176
+          A.stk_n[plen] = (uint8_t)((hd[i].meta >> kMetaOutShift) & 7u);
+          ++plen;
+          const uint32_t m = (hd[i].meta & ~kMetaLock) | (uint32_t)plen | kMetaOnPath;  // :172
+          N[nb].meta = m;
+          A.pmeta[plen - 1] = m;
           ++expansions;
           flag = false;                                     // break
         }
       }
     }
     if (flag) {                                             // :181-211
-      --slen;
       --plen;
       const uint32_t v = A.path[plen];
       const uint32_t mv = A.pmeta[plen] & ~kMetaOnPath;
       N[v].meta = mv;
-      const int b = A.bl[--blen];
-      if (blen > 0 && b < A.bl[blen - 1]) A.bl[blen - 1] = (int16_t)b;
+      const int b = A.bl[plen];
+      if (plen > 0 && b < A.bl[plen - 1]) A.bl[plen - 1] = (int16_t)b;
       if (b < M && (int)(mv & kMetaLock) < M - b + 1) {     // the first relax entry is (b, v), :192-196
         // A relax entry (x, u) only acts when lock[u] < M - x + 1, and locks never decrease during
         // a relaxation, so entries that fail the test when they would be pushed are dropped at once
@@ -379,6 +389,7 @@ done:
   R.n_nodes = n_cyc;
   R.steps = (uint32_t)steps;
   R.expansions = expansions;
+  return true;
 }
 
 }  // namespace mg

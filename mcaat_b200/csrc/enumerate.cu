@@ -331,33 +331,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     R.n_cycles = R.n_nodes = R.n_keys = R.steps = R.expansions = 0;
     int stopped = 0;
     uint32_t us_build = 0;
-    // speculative search against the live bitmap: the warp extracts the ball, lane 0 searches it and
-    // gives up when the start gets marked.  Called by all lanes.
-    auto speculate = [&](bool exclusive) {
-      ++searches;
-      const unsigned long long t_build = gtime_ns();
-      ball_clear(A, live, co);
-      const int st = ball_build(g, adj, visited, s, max_len, A, live, co);
-      us_build = (uint32_t)((gtime_ns() - t_build) / 1000);
-      if (lane == 0) {
-        R.status = st;
-        R.n_cycles = R.n_nodes = R.steps = R.expansions = 0;
-        R.n_keys = live;
-        if (st == kEnumDone) {
-          if (exclusive) {
-            ball_dfs(min_len, max_len, A, R, []() { return false; });
-          } else {
-            ball_dfs(min_len, max_len, A, R, [&]() {
-              if (ld_vol(&ctl->stop)) { stopped = 1; return true; }
-              return visited_live(visited, s);
-            });
-            if (R.status == kEnumSkipped && !stopped) ++abandoned;
-          }
-        }
-      }
-      __syncwarp();  // lane 0's arena writes (staged cycles) are visible to the warp
-    };
-    // does the finished search rest on a node that has been marked since? (warp-cooperative)
+    // does the search rest on a node that has been marked since its ball was built? (warp-cooperative)
     auto stale = [&](uint32_t n_keys) {
       int conflict = 0;
       for (uint32_t j = 1 + lane; j < n_keys; j += 32) {
@@ -365,6 +339,58 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
         if (k != s && visited_live(visited, k)) conflict = 1;
       }
       return __any_sync(0xffffffffu, conflict) != 0;
+    };
+    // Speculative search against the live bitmap (all lanes call it): the warp extracts the ball, lane 0
+    // searches it in slices of kSliceSteps steps.  Between slices the warp polls: pipeline draining ->
+    // stop; start marked by an earlier commit -> the ticket will be skipped (:476), give up; the mark
+    // epoch moved and a ball node is marked now -> the search is stale, start over at once instead
+    // of finishing a search whose result would be thrown away.  `exclusive` (at the ticket's turn:
+    // the bitmap is final) runs to the end without polling.
+    uint32_t epoch_checked = 0xFFFFFFFFu;  // `visited` as of this epoch is accounted for in R
+    auto speculate = [&](bool exclusive) {
+      for (;;) {
+        ++searches;
+        epoch_checked = __shfl_sync(0xffffffffu, ld_vol(&ctl->mark_epoch), 0);
+        const unsigned long long t_build = gtime_ns();
+        ball_clear(A, live, co);
+        const int st = ball_build(g, adj, visited, s, max_len, A, live, co);
+        us_build = (uint32_t)((gtime_ns() - t_build) / 1000);
+        R.status = st;
+        R.n_cycles = R.n_nodes = R.steps = R.expansions = 0;
+        R.n_keys = live;
+        if (st != kEnumDone) break;
+        DfsState ds;
+        bool restart = false;
+        for (;;) {
+          int fin = 0;
+          if (lane == 0) fin = ball_dfs(min_len, max_len, A, ds, exclusive ? kMaxSteps + 1 : kSliceSteps, R) ? 1 : 0;
+          if (__shfl_sync(0xffffffffu, fin, 0)) break;
+          uint32_t c_stop = 0, c_vis = 0, c_ep = 0;
+          if (lane == 0) {
+            c_stop = ld_vol(&ctl->stop);
+            c_vis = visited_live(visited, s);
+            c_ep = ld_vol(&ctl->mark_epoch);
+          }
+          c_stop = __shfl_sync(0xffffffffu, c_stop, 0);
+          c_vis = __shfl_sync(0xffffffffu, c_vis, 0);
+          c_ep = __shfl_sync(0xffffffffu, c_ep, 0);
+          if (c_stop | c_vis) {
+            if (c_stop) stopped = 1;
+            else ++abandoned;
+            R.status = kEnumSkipped;
+            R.n_cycles = R.n_nodes = 0;
+            break;
+          }
+          if (c_ep != epoch_checked) {
+            epoch_checked = c_ep;
+            __threadfence();
+            if (stale(live)) { restart = true; break; }
+          }
+        }
+        if (!restart) break;
+        ++reruns;
+      }
+      __syncwarp();  // lane 0's arena writes (staged cycles) are visible to the warp
     };
     // a ticket whose start is already marked is skipped for good (:476); the committing worker ahead
     // consumes such tickets itself (below), so this worker just moves on
@@ -375,7 +401,6 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     //      `visited` only changes inside commits that mark nodes (mark_epoch), so the result is
     //      re-examined only when the epoch has moved; the poll itself is one 32-byte sector and backs
     //      off with the distance to the commit front, so waiting workers leave the L2 to the searches.
-    uint32_t epoch_checked = 0xFFFFFFFFu;
     bool consumed = false;
     for (;;) {
       uint32_t ci = 0, ep = 0;

@@ -337,6 +337,7 @@ MG_HD void uset_erase(USet &s, uint32_t x) {
 constexpr int kMaxSteps = 10000000;  // src/cycle_finder.cpp:149
 constexpr int kClusterBound = 500;   // src/cycle_finder.cpp:132
 constexpr int kPollSteps = 256;      // how often a running search polls for its own start being marked
+constexpr int kSliceSteps = 1024;    // extracted-ball search: steps between two polls of the warp
 enum EnumStatus : int32_t {
   kEnumDone = 0,
   kEnumBound = 1,     // cluster bound reached: result is empty (:162-165), search stopped early

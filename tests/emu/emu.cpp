@@ -316,7 +316,15 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
       bs.live = nn;
       RR.status = st;
       RR.n_cycles = RR.n_nodes = RR.n_keys = RR.steps = RR.expansions = 0;
-      if (st == kEnumDone) ball_dfs(min_len, max_len, bs.A, RR, poll);
+      if (st == kEnumDone) {
+        DfsState ds;
+        while (!ball_dfs(min_len, max_len, bs.A, ds, 256, RR))
+          if (poll()) {  // the device polls between slices: start marked -> the search is abandoned
+            RR.status = kEnumSkipped;
+            RR.n_cycles = RR.n_nodes = 0;
+            break;
+          }
+      }
       keys.clear();
       cyc_lens.clear();
       cyc_nodes_flat.clear();
