@@ -48,7 +48,27 @@ __global__ void k_chain_init(GraphView g, PeelView P, unsigned long long *n_pair
     if (pairs) atomicAdd(n_pairs, (unsigned long long)pairs);
   }
 }
-// step 2: one pointer-jumping round
+// step 2 (search_dev.cuh): splitter walks, pointer jumping over the splitters, resolution of the rest
+__global__ void k_split_mark(uint64_t n, PeelView P, uint32_t *split) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool sp = i < n && bm_get(P.chain, (uint32_t)i) && is_splitter_id((uint32_t)i);
+  unsigned m = __ballot_sync(0xffffffffu, sp);
+  if ((threadIdx.x & 31) == 0 && i < n) split[i >> 5] = m;
+}
+__global__ void k_split_walk(PeelView P, const uint32_t *ids, uint32_t n_ids, int *capped) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_ids && !split_walk_item(P, ids[i])) *capped = 1;
+}
+__global__ void k_split_jump(PeelView P, const uint32_t *ids, uint32_t n_ids, int *unresolved) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  bool u = i < n_ids && split_jump_item(P, ids[i]);
+  if (__any_sync(0xffffffffu, u) && (threadIdx.x & 31) == 0) *unresolved = 1;
+}
+__global__ void k_chain_resolve(uint64_t n, PeelView P, int *capped) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && !chain_resolve_item(P, (uint32_t)i)) *capped = 1;
+}
+// exhaustive fallback: one pointer-jumping round over every item
 __global__ void k_chain_jump(uint64_t n, PeelView P, int *unresolved) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   bool u = i < n && chain_jump_item(P, (uint32_t)i);
@@ -149,6 +169,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     P.tipbits = tipbits.as<uint32_t>();
     P.dep = nullptr;
     P.dep_log = 0;
+    P.owner = nullptr;
     {
       TimedScope ts(g, T_ADJ, n);
       MG_LAUNCH(k_chain_init, grid, 256, 0, s, v, P, c + 5);
@@ -157,15 +178,45 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     MG_TRY(bitmap_to_ids(tpeeled.as<uint32_t>(), n, work, &n_work, s));  // seeds
     TimedScope ts(g, T_PEEL, n);
     if (n_work) {
-      int *unresolved = (int *)(c + 7);
-      for (int round = 0; round < 34; round += 2) {
-        MG_CUDA(cudaMemsetAsync(unresolved, 0, 4, s));
-        MG_LAUNCH(k_chain_jump, grid, 256, 0, s, n, P, unresolved);
-        MG_LAUNCH(k_chain_jump, grid, 256, 0, s, n, P, unresolved);
-        int h = 0;
-        MG_CUDA(cudaMemcpyAsync(&h, unresolved, 4, cudaMemcpyDeviceToHost, s));
+      int *unresolved = (int *)(c + 7), *capped = (int *)(c + 7) + 1;
+      {  // chain nodes -> terminals through 1-in-64 splitters
+        DevBuf owner, split, split_ids;
+        MG_TRY(owner.alloc((size_t)n * 4 + 16));
+        MG_TRY(split.alloc(bm_bytes));
+        MG_CUDA(cudaMemsetAsync(owner.p, 0xFF, owner.bytes, s));
+        MG_CUDA(cudaMemsetAsync(c + 7, 0, 8, s));
+        P.owner = owner.as<uint32_t>();
+        MG_LAUNCH(k_split_mark, grid, 256, 0, s, n, P, split.as<uint32_t>());
+        uint64_t n_split = 0;
+        MG_TRY(bitmap_to_ids(split.as<uint32_t>(), n, split_ids, &n_split, s));
+        if (n_split) {
+          MG_LAUNCH(k_split_walk, grid_for(n_split, 128), 128, 0, s, P, split_ids.as<uint32_t>(), (uint32_t)n_split, capped);
+          for (int round = 0; round < 36; round += 4) {
+            MG_CUDA(cudaMemsetAsync(unresolved, 0, 4, s));
+            for (int k = 0; k < 4; ++k)
+              MG_LAUNCH(k_split_jump, grid_for(n_split, 256), 256, 0, s, P, split_ids.as<uint32_t>(), (uint32_t)n_split, unresolved);
+            int h = 0;
+            MG_CUDA(cudaMemcpyAsync(&h, unresolved, 4, cudaMemcpyDeviceToHost, s));
+            MG_CUDA(cudaStreamSynchronize(s));
+            if (!h) break;
+          }
+        }
+        MG_LAUNCH(k_chain_resolve, grid, 256, 0, s, n, P, capped);
+        int hc = 0;
+        MG_CUDA(cudaMemcpyAsync(&hc, capped, 4, cudaMemcpyDeviceToHost, s));
         MG_CUDA(cudaStreamSynchronize(s));
-        if (!h) break;
+        P.owner = nullptr;
+        if (hc || getenv("MCAAT_PEEL_EXHAUSTIVE")) {  // a walk hit its hop cap: exhaustive pointer jumping
+          for (int round = 0; round < 34; round += 2) {
+            MG_CUDA(cudaMemsetAsync(unresolved, 0, 4, s));
+            MG_LAUNCH(k_chain_jump, grid, 256, 0, s, n, P, unresolved);
+            MG_LAUNCH(k_chain_jump, grid, 256, 0, s, n, P, unresolved);
+            int h = 0;
+            MG_CUDA(cudaMemcpyAsync(&h, unresolved, 4, cudaMemcpyDeviceToHost, s));
+            MG_CUDA(cudaStreamSynchronize(s));
+            if (!h) break;
+          }
+        }
       }
       unsigned long long pairs = 0;
       MG_CUDA(cudaMemcpyAsync(&pairs, c + 5, 8, cudaMemcpyDeviceToHost, s));

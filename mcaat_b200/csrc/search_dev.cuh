@@ -82,6 +82,7 @@ struct PeelView {
   const uint32_t *tipbits;  // bitmap: CollectTips on the loaded graph (:436)
   uint64_t *dep;            // multimap entries (terminal << 32 | branch node), empty = ~0
   uint32_t dep_log;
+  uint32_t *owner;          // splitter whose walk passed the item (kNull = none), step 2
 };
 MG_HD bool bm_get(const uint32_t *bm, uint32_t i) { return (bm[i >> 5] >> (i & 31)) & 1; }
 MG_HD bool bm_get_coherent(const uint32_t *bm, uint32_t i) { return (ld_cg32(&bm[i >> 5]) >> (i & 31)) & 1; }
@@ -128,6 +129,68 @@ MG_HD bool chain_jump_item(const PeelView &P, uint32_t v) {
   if (!bm_get(P.chain, p)) return false;
   P.ptr[v] = P.ptr[p];
   return true;
+}
+// Step 2, work-efficient form.  Pointer jumping over ALL chain nodes costs one pass over the graph
+// per doubling (18 passes for the 10^5-node chains of sequencing-error tips).  Instead one chain
+// node in 64 (by hash) is a SPLITTER:
+//   a. every splitter walks forward until it meets a terminal, another splitter or an item another
+//      walk has claimed, claiming the items it passes (owner[]) — every chain node is claimed at most
+//      once, so this is O(n) in total, in walks of ~64 hops;
+//   b. pointer jumping runs over the splitters only (1/64 of the nodes);
+//   c. every other chain node takes the terminal of its owner, or — near the head of a chain, where no
+//      walk passed — walks to the first item that knows it.
+// An item that leads into a cycle of chain nodes ends with a chain node as its pointer, which
+// terminal_of() reports as unresolvable, exactly like the exhaustive pointer jumping.  Walks are
+// capped; hitting the cap (astronomically unlikely away from splitter-free cycles) makes the host
+// fall back to exhaustive pointer jumping — every pointer stays a valid forward pointer throughout.
+constexpr uint32_t kWalkCapSplitter = 1u << 16, kWalkCapHead = 1u << 12;
+MG_HD bool is_splitter_id(uint32_t v) { return ((v * 0x9E3779B1u) >> 26) == 0; }
+MG_HD uint32_t ld_cg_u32(const uint32_t *p) { return ld_cg32(p); }
+MG_HD uint32_t owner_claim(uint32_t *p, uint32_t s) {
+#if defined(__CUDA_ARCH__)
+  return atomicCAS(p, kNull, s);
+#else
+  uint32_t old = *p;
+  if (old == kNull) *p = s;
+  return old;
+#endif
+}
+// a. walk of splitter s; returns false when the hop cap was hit (ptr[s] is then left untouched)
+MG_HD bool split_walk_item(const PeelView &P, uint32_t s) {
+  uint32_t p = P.ptr[s], next = kNull;
+  for (uint32_t hops = 0; hops < kWalkCapSplitter; ++hops) {
+    if (!bm_get(P.chain, p) || is_splitter_id(p)) { next = p; break; }
+    uint32_t old = owner_claim(&P.owner[p], s);
+    if (old != kNull) { next = old; break; }  // old == s: the walk has run into a splitter-free cycle
+    p = ld_cg_u32(&P.ptr[p]);
+  }
+  if (next == kNull) return false;
+  P.ptr[s] = next;
+  return true;
+}
+// b. one pointer-jumping round for splitter s; returns true while it is still unresolved
+MG_HD bool split_jump_item(const PeelView &P, uint32_t s) {
+  uint32_t p = ld_cg_u32(&P.ptr[s]);
+  if (!bm_get(P.chain, p) || p == s) return false;  // terminal reached / known to be unresolvable
+  uint32_t q = ld_cg_u32(&P.ptr[p]);
+  if (q == p) q = s;  // the splitter ahead is unresolvable, so is this one
+  P.ptr[s] = q;
+  return true;
+}
+// c. every chain node that is not a splitter; returns false when the hop cap was hit
+MG_HD bool chain_resolve_item(const PeelView &P, uint32_t v) {
+  if (!bm_get(P.chain, v) || is_splitter_id(v)) return true;
+  uint32_t o = P.owner[v];
+  if (o != kNull) { P.ptr[v] = ld_cg_u32(&P.ptr[o]); return true; }
+  uint32_t p = ld_cg_u32(&P.ptr[v]);
+  for (uint32_t hops = 0; hops < kWalkCapHead; ++hops) {
+    if (!bm_get(P.chain, p)) { P.ptr[v] = p; return true; }
+    if (is_splitter_id(p)) { P.ptr[v] = ld_cg_u32(&P.ptr[p]); return true; }
+    o = ld_cg_u32(&P.owner[p]);
+    if (o != kNull) { P.ptr[v] = ld_cg_u32(&P.ptr[o]); return true; }
+    p = ld_cg_u32(&P.ptr[p]);  // the successor, or already p's terminal: both lie ahead on the same chain
+  }
+  return false;
 }
 // terminal of an out-neighbour (kNull when it sits on an unresolvable chain cycle)
 MG_HD uint32_t terminal_of(const PeelView &P, uint32_t c) {

@@ -144,7 +144,7 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   e->adj.assign(n + 1, 0);
   PeelView P;
   P.adj = e->adj.data(); P.ptr = ptr.data(); P.chain = chain.data(); P.tpeeled = tpeeled.data();
-  P.tipbits = tipbits.data(); P.dep = nullptr; P.dep_log = 0;
+  P.tipbits = tipbits.data(); P.dep = nullptr; P.dep_log = 0; P.owner = nullptr;
   uint64_t pairs = 0;
   std::vector<uint32_t> work, next;
   for (uint64_t i = 0; i < n; ++i) {
@@ -154,22 +154,42 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
     if (sd) { tpeeled[i >> 5] |= 1u << (i & 31); work.push_back((uint32_t)i); }
     if (deg >= 2) pairs += deg;
   }
-  for (int round = 0; round < 34; ++round) {
-    bool any = false;
-    if (reverse_order) { for (uint64_t i = n; i-- > 0;) any |= chain_jump_item(P, (uint32_t)i); }
-    else for (uint64_t i = 0; i < n; ++i) any |= chain_jump_item(P, (uint32_t)i);
-    if (!any) break;
+  // chain nodes -> terminals: splitter walks + jumping over splitters + resolution (as prune.cu), in
+  // forward or reverse item order; reverse_order & 2 forces the exhaustive pointer jumping instead
+  bool capped = false;
+  if (!(reverse_order & 2)) {
+    std::vector<uint32_t> owner(n + 1, kNull), split_ids;
+    P.owner = owner.data();
+    for (uint64_t i = 0; i < n; ++i)
+      if (bm_get(P.chain, (uint32_t)i) && is_splitter_id((uint32_t)i)) split_ids.push_back((uint32_t)i);
+    if (reverse_order & 1) std::reverse(split_ids.begin(), split_ids.end());
+    for (uint32_t sid : split_ids) capped |= !split_walk_item(P, sid);
+    for (int round = 0; round < 36; ++round) {
+      bool any = false;
+      for (uint32_t sid : split_ids) any |= split_jump_item(P, sid);
+      if (!any) break;
+    }
+    if (reverse_order & 1) { for (uint64_t i = n; i-- > 0;) capped |= !chain_resolve_item(P, (uint32_t)i); }
+    else for (uint64_t i = 0; i < n; ++i) capped |= !chain_resolve_item(P, (uint32_t)i);
+    P.owner = nullptr;
   }
+  if (capped || (reverse_order & 2))
+    for (int round = 0; round < 34; ++round) {
+      bool any = false;
+      if (reverse_order & 1) { for (uint64_t i = n; i-- > 0;) any |= chain_jump_item(P, (uint32_t)i); }
+      else for (uint64_t i = 0; i < n; ++i) any |= chain_jump_item(P, (uint32_t)i);
+      if (!any) break;
+    }
   uint32_t dep_log = 4;
   while (((uint64_t)1 << dep_log) < 2 * pairs + 16) ++dep_log;
   std::vector<uint64_t> dep((size_t)1 << dep_log, ~0ull);
   P.dep = dep.data(); P.dep_log = dep_log;
   for (uint64_t i = 0; i < n; ++i) dep_register_item(v, P, (uint32_t)i);
-  if (reverse_order) std::reverse(work.begin(), work.end());
+  if (reverse_order & 1) std::reverse(work.begin(), work.end());
   while (!work.empty()) {
     next.clear();
     for (uint32_t t : work) cpeel_one(P, t, [&](uint32_t b) { next.push_back(b); });
-    if (reverse_order) std::reverse(next.begin(), next.end());
+    if (reverse_order & 1) std::reverse(next.begin(), next.end());
     work.swap(next);
   }
   uint64_t peeled = 0, valid = 0, tips = 0;

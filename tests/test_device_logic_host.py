@@ -93,6 +93,18 @@ def test_small_arena_overflow_is_rerun_exactly():
     assert got.stats["overflow_reruns"] > 0
 
 
+@pytest.mark.parametrize("name", ["tiny", "strain", "repeatrich"])
+def test_peel_variants_agree(name):
+    """splitter-based chain resolution (forward / reverse item order) == exhaustive pointer jumping"""
+    inv = []
+    for mode in (0, 1, 2, 3):
+        g = emu(name)
+        g.prune(reverse_order=mode)
+        inv.append(g.invalid())
+    for other in inv[1:]:
+        assert np.array_equal(inv[0], other)
+
+
 def test_dls_tiers_agree():
     g = emu("strain")
     g.prune()
