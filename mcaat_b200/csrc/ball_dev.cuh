@@ -29,7 +29,7 @@ namespace mg {
 struct alignas(16) LNode {
   uint32_t meta;     // bits 0-15 lock value | 16-18 |out| | 20-22 |in| | 24 node is on the current path
   uint32_t key;      // graph item id
-  union { uint16_t out[4]; uint64_t out4; };  // local ids, iteration order of the std::unordered_set built at :58-72
+  union { uint16_t out[4]; uint64_t out4; };  // local ids (kNoLid = unused), iteration order of the std::unordered_set built at :58-72
 };
 struct alignas(16) LTail {
   union { uint16_t in[4]; uint64_t in4; };    // local ids, iteration order of the set built at :76-88
@@ -42,6 +42,17 @@ constexpr int kMetaOutShift = 16, kMetaInShift = 20;
 constexpr uint64_t kIndexEmpty = ~0ull;
 constexpr uint32_t kLidPending = 0xFFFFFFFFu;
 
+// One path level = path[i], backtrack_lengths[i], the remaining neighbour set stack[i] and the node's
+// meta word (nobody else changes the meta of a node while it is on the path): 16 bytes, one shared-
+// memory access per push or pop.
+struct alignas(16) Lvl {
+  uint64_t set;      // 4 x uint16 local ids in iteration order, unused slots = kNoLid
+  uint32_t pmeta;
+  uint16_t node;
+  int16_t bl;
+};
+constexpr uint32_t kNoLid = 0xFFFFu;
+
 struct BallArena {
   LNode *nodes;
   LTail *tails;
@@ -53,12 +64,7 @@ struct BallArena {
   uint16_t *cyc;        // staged raw cycles as local ids
   uint32_t cyc_cap;
   uint32_t *cyc_off;    // [kClusterBound + 1]
-  // per path level (shared memory on the device)
-  uint16_t *path;       // [M + 2] local ids
-  int16_t *bl;          // [M + 2] backtrack lengths
-  uint64_t *stk;        // [M + 2] the level's remaining neighbour set: 4 x uint16, iteration order
-  uint8_t *stk_n;       // [M + 2] its size
-  uint32_t *pmeta;      // [M + 2] meta word of the path's nodes (nobody else changes an on-path node's meta)
+  Lvl *lvl;             // [M + 2] per path level (shared memory on the device)
 };
 
 // cooperative execution policy: the device runs ball_build with the 32 lanes of a warp, the host
@@ -128,6 +134,7 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
     st_cg64(&A.index[h], ((uint64_t)start << 32) | 0u);
     N[0].meta = (uint32_t)M;
     N[0].key = start;
+    N[0].out4 = ~0ull;
     T[0].slot = h;
     A.relax[0] = 0;
   }
@@ -177,6 +184,7 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
         if ((mine >> j) & 1) {
           N[lid].meta = (uint32_t)M;  // lock default (try_emplace(n, cycle_max_length), :168), no edges yet
           N[lid].key = okn[j];
+          N[lid].out4 = ~0ull;
           T[lid].slot = slot[j];
           A.relax[lid] = 0;  // in-degree counter of the transpose below (the relax stack is idle during the build)
           st_cg64(&A.index[slot[j]], ((uint64_t)okn[j] << 32) | lid);
@@ -273,45 +281,49 @@ MG_HD_NOINLINE bool ball_dfs(int min_len, int max_len, const BallArena &A, DfsSt
   const int M = max_len;
   LNode *N = A.nodes;
   LTail *T = A.tails;
+  Lvl *L = A.lvl;
   uint32_t expansions = S.expansions, n_cycles = S.n_cycles, n_cyc = S.n_cyc;
   int plen = S.depth, counter = S.counter, steps = S.steps;
   int32_t status = kEnumDone;
+  Lvl cur;  // the top level lives in registers; L[plen - 1] is written when it stops being the top
   if (!S.started) {
     S.started = true;
     A.cyc_off[0] = 0;
     const NodeHead h0 = ld_head(&N[0]);
-    const uint32_t m0 = (h0.meta & ~kMetaLock) | kMetaOnPath;  // lock[start] = 0, :237
-    N[0].meta = m0;
-    A.pmeta[0] = m0;
-    A.path[0] = 0;
-    A.stk[0] = h0.out4;                                         // _GetOutgoings(start), :238-240
-    A.stk_n[0] = (uint8_t)((h0.meta >> kMetaOutShift) & 7u);
-    A.bl[0] = (int16_t)M;
+    cur.pmeta = (h0.meta & ~kMetaLock) | kMetaOnPath;  // lock[start] = 0, :237
+    N[0].meta = cur.pmeta;
+    cur.node = 0;
+    cur.set = h0.out4;                                 // _GetOutgoings(start), :238-240
+    cur.bl = (int16_t)M;
     plen = 1;
     ++expansions;
+  } else {
+    cur = L[plen - 1];
   }
   const int pause_at = steps + budget;
   while (plen > 0) {
     if (steps == pause_at) {
+      L[plen - 1] = cur;
       S.depth = plen; S.counter = counter; S.steps = steps;
       S.expansions = expansions; S.n_cycles = n_cycles; S.n_cyc = n_cyc;
       return false;
     }
     if (++steps > kMaxSteps) { status = kEnumCap; break; }  // :148-151
-    const uint64_t set = A.stk[plen - 1];                   // :153 (copy)
-    const int n = A.stk_n[plen - 1];
+    const uint64_t set = cur.set;                           // :153 (copy)
     // records of all members first: the loads overlap, and no lock changes before the scan ends
     NodeHead hd[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-      if (i < n) hd[i] = ld_head(&N[(uint32_t)(set >> (16 * i)) & 0xFFFFu]);
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t nb = (uint32_t)(set >> (16 * i)) & 0xFFFFu;
+      if (nb != kNoLid) hd[i] = ld_head(&N[nb]);
+    }
     bool flag = true;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {                           // static indices: hd[] stays in registers
-      if (i < n && flag) {
-        const uint32_t nb = (uint32_t)(set >> (16 * i)) & 0xFFFFu;
+      const uint32_t nb = (uint32_t)(set >> (16 * i)) & 0xFFFFu;
+      if (nb != kNoLid && flag) {
         if (nb == 0) {                                      // n == start_node, :157-166
-          A.bl[plen - 1] = 1;
+          cur.bl = 1;
           if (plen > min_len) {
             if (++counter >= kClusterBound) {               // cluster bound: final answer is empty
               status = kEnumBound;
@@ -319,7 +331,8 @@ MG_HD_NOINLINE bool ball_dfs(int min_len, int max_len, const BallArena &A, DfsSt
               goto done;
             }
             if (n_cyc + (uint32_t)plen > A.cyc_cap) { status = kEnumOverflow; goto done; }
-            for (int j = 0; j < plen; ++j) A.cyc[n_cyc + j] = A.path[j];
+            for (int j = 0; j + 1 < plen; ++j) A.cyc[n_cyc + j] = L[j].node;
+            A.cyc[n_cyc + plen - 1] = cur.node;
             n_cyc += (uint32_t)plen;
             A.cyc_off[++n_cycles] = n_cyc;
           }
@@ -327,17 +340,15 @@ MG_HD_NOINLINE bool ball_dfs(int min_len, int max_len, const BallArena &A, DfsSt
           {                                                 // stack.back().erase(n), :173
             const uint64_t low = i ? set & ((1ull << (16 * i)) - 1) : 0ull;
             const uint64_t high = i < 3 ? (set >> (16 * (i + 1))) << (16 * i) : 0ull;
-            A.stk[plen - 1] = low | high;
-            A.stk_n[plen - 1] = (uint8_t)(n - 1);
+            cur.set = low | high | (0xFFFFull << 48);
           }
-          A.path[plen] = (uint16_t)nb;                      // :170
-          A.bl[plen] = (int16_t)M;                          // :171
-          A.stk[plen] = hd[i].out4;                         // :174-176
-          A.stk_n[plen] = (uint8_t)((hd[i].meta >> kMetaOutShift) & 7u);
+          L[plen - 1] = cur;
           ++plen;
-          const uint32_t m = (hd[i].meta & ~kMetaLock) | (uint32_t)plen | kMetaOnPath;  // :172
-          N[nb].meta = m;
-          A.pmeta[plen - 1] = m;
+          cur.set = hd[i].out4;                             // :174-176
+          cur.pmeta = (hd[i].meta & ~kMetaLock) | (uint32_t)plen | kMetaOnPath;  // :172
+          cur.node = (uint16_t)nb;                          // :170
+          cur.bl = (int16_t)M;                              // :171
+          N[nb].meta = cur.pmeta;
           ++expansions;
           flag = false;                                     // break
         }
@@ -345,11 +356,14 @@ MG_HD_NOINLINE bool ball_dfs(int min_len, int max_len, const BallArena &A, DfsSt
     }
     if (flag) {                                             // :181-211
       --plen;
-      const uint32_t v = A.path[plen];
-      const uint32_t mv = A.pmeta[plen] & ~kMetaOnPath;
+      const uint32_t v = cur.node;
+      const uint32_t mv = cur.pmeta & ~kMetaOnPath;
       N[v].meta = mv;
-      const int b = A.bl[plen];
-      if (plen > 0 && b < A.bl[plen - 1]) A.bl[plen - 1] = (int16_t)b;
+      const int b = cur.bl;
+      if (plen > 0) {
+        cur = L[plen - 1];
+        if (b < cur.bl) cur.bl = (int16_t)b;
+      }
       if (b < M && (int)(mv & kMetaLock) < M - b + 1) {     // the first relax entry is (b, v), :192-196
         // A relax entry (x, u) only acts when lock[u] < M - x + 1, and locks never decrease during
         // a relaxation, so entries that fail the test when they would be pushed are dropped at once

@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_solo(GraphView g, 
 struct BallLayout {  // per-worker arena in global memory (byte offsets inside one slot)
   uint32_t index_log, node_cap, relax_cap, cyc_cap, depth_cap;
   size_t off_nodes, off_tails, off_index, off_relax, off_cyc, off_cyc_off, bytes;
-  uint32_t smem_bytes;  // per worker: path, bl, stk, stk_n live in shared memory
+  uint32_t smem_bytes;  // per worker: the path levels (Lvl) live in shared memory
 };
 static BallLayout make_ball_layout(int max_len, uint32_t index_log) {
   BallLayout L;
@@ -282,7 +282,7 @@ static BallLayout make_ball_layout(int max_len, uint32_t index_log) {
   L.off_cyc = o; o = align_up(o + (size_t)L.cyc_cap * 2, 128);
   L.off_cyc_off = o; o = align_up(o + (size_t)(kClusterBound + 1) * 4, 128);
   L.bytes = align_up(o, 128);
-  L.smem_bytes = (uint32_t)align_up((size_t)L.depth_cap * (8 + 4 + 2 + 2 + 1), 16);
+  L.smem_bytes = (uint32_t)align_up((size_t)L.depth_cap * sizeof(Lvl), 16);
   return L;
 }
 __device__ __forceinline__ BallArena ball_arena_of(uint8_t *base, uint8_t *smem, const BallLayout &L) {
@@ -297,11 +297,7 @@ __device__ __forceinline__ BallArena ball_arena_of(uint8_t *base, uint8_t *smem,
   A.cyc = (uint16_t *)(base + L.off_cyc);
   A.cyc_cap = L.cyc_cap;
   A.cyc_off = (uint32_t *)(base + L.off_cyc_off);
-  A.stk = (uint64_t *)smem;
-  A.pmeta = (uint32_t *)(smem + (size_t)L.depth_cap * 8);
-  A.path = (uint16_t *)(A.pmeta + L.depth_cap);
-  A.bl = (int16_t *)(A.path + L.depth_cap);
-  A.stk_n = (uint8_t *)(A.bl + L.depth_cap);
+  A.lvl = (Lvl *)smem;
   return A;
 }
 

@@ -7,46 +7,84 @@
 namespace mg {
 
 static inline unsigned grid_for(uint64_t n, int block) { return (unsigned)((n + block - 1) / block); }
+// The streaming kernels below count what they do.  One global atomic per warp on the same address
+// serialises in the L2 (7 M warps at c2 = milliseconds); they run grid-stride over a fixed grid
+// instead, keep per-warp counts in shared memory and issue one global atomic per block and counter.
+static inline unsigned stream_grid(const mg_graph *g, uint64_t n, int block) {
+  uint64_t want = (n + block - 1) / block, cap = (uint64_t)g->sm_count * 16;
+  return (unsigned)(want < cap ? (want ? want : 1) : cap);
+}
+template <int K>
+struct BlockCounters {
+  unsigned *sh;
+  __device__ BlockCounters(unsigned *shared) : sh(shared) {
+    if (threadIdx.x < K) sh[threadIdx.x] = 0;
+    __syncthreads();
+  }
+  __device__ void add(int k, unsigned v) { if (v) atomicAdd(&sh[k], v); }
+  __device__ void flush(unsigned long long *const *dst) {
+    __syncthreads();
+    if (threadIdx.x < K && sh[threadIdx.x]) atomicAdd(dst[threadIdx.x], (unsigned long long)sh[threadIdx.x]);
+  }
+};
 
 // CollectTips: bit i of `bits` = valid(i) && outdegree(i) == 0.  One thread per item; a warp
 // covers 32 consecutive items = one bitmap word.
 __global__ void k_tips(GraphView g, uint32_t *bits, unsigned long long *count) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool tip = false;
-  if (i < g.n) tip = outgoing(g, (uint32_t)i, nullptr) == 0;
-  unsigned m = __ballot_sync(0xffffffffu, tip);
-  if ((threadIdx.x & 31) == 0 && i < g.n) {
-    bits[i >> 5] = m;
-    if (m) atomicAdd(count, (unsigned long long)__popc(m));
+  __shared__ unsigned sh[1];
+  BlockCounters<1> bc(sh);
+  const uint64_t n32 = (g.n + 31) & ~31ull;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
+    bool tip = false;
+    if (i < g.n) tip = outgoing(g, (uint32_t)i, nullptr) == 0;
+    unsigned m = __ballot_sync(0xffffffffu, tip);
+    if ((threadIdx.x & 31) == 0) {
+      bits[i >> 5] = m;
+      bc.add(0, (unsigned)__popc(m));
+    }
   }
+  unsigned long long *dst[1] = {count};
+  bc.flush(dst);
 }
 // InvalidateMultiplicityOneNodes: every item with multiplicity <= 1 becomes invalid; the count
 // includes items that were invalid already, like the reference's counter.
 __global__ void k_mult1(GraphView g, unsigned long long *count) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool low = i < g.n && g.mult[i] <= 1;
-  unsigned m = __ballot_sync(0xffffffffu, low);
-  if ((threadIdx.x & 31) == 0 && m) {
-    uint32_t *w32 = (uint32_t *)&g.fb[i >> 8].inv[(i >> 6) & 3] + ((i >> 5) & 1);
-    atomicOr(w32, m);
-    atomicAdd(count, (unsigned long long)__popc(m));
+  __shared__ unsigned sh[1];
+  BlockCounters<1> bc(sh);
+  const uint64_t n32 = (g.n + 31) & ~31ull;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
+    bool low = i < g.n && g.mult[i] <= 1;
+    unsigned m = __ballot_sync(0xffffffffu, low);
+    if ((threadIdx.x & 31) == 0 && m) {
+      uint32_t *w32 = (uint32_t *)&g.fb[i >> 8].inv[(i >> 6) & 3] + ((i >> 5) & 1);
+      *w32 |= m;  // this warp owns the 32-bit word and nobody else writes invalid bits in this phase
+      bc.add(0, (unsigned)__popc(m));
+    }
   }
+  unsigned long long *dst[1] = {count};
+  bc.flush(dst);
 }
 // ---- RecursiveReduction by chain contraction (search_dev.cuh, "peel") -------------------------
 // step 1: navigation cache on the post-filter graph, chain / seed bitmaps, chain pointers
 __global__ void k_chain_init(GraphView g, PeelView P, unsigned long long *n_pairs) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool is_chain = false, is_seed = false;
-  int deg = -1;
-  if (i < g.n) deg = chain_init_item(g, P, (uint32_t)i, is_chain, is_seed);
-  unsigned mc = __ballot_sync(0xffffffffu, is_chain), ms = __ballot_sync(0xffffffffu, is_seed);
-  unsigned pairs = deg >= 2 ? (unsigned)deg : 0u;
-  for (int d = 16; d; d >>= 1) pairs += __shfl_down_sync(0xffffffffu, pairs, d);
-  if ((threadIdx.x & 31) == 0 && i < g.n) {
-    P.chain[i >> 5] = mc;
-    P.tpeeled[i >> 5] = ms;
-    if (pairs) atomicAdd(n_pairs, (unsigned long long)pairs);
+  __shared__ unsigned sh[1];
+  BlockCounters<1> bc(sh);
+  const uint64_t n32 = (g.n + 31) & ~31ull;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
+    bool is_chain = false, is_seed = false;
+    int deg = -1;
+    if (i < g.n) deg = chain_init_item(g, P, (uint32_t)i, is_chain, is_seed);
+    unsigned mc = __ballot_sync(0xffffffffu, is_chain), ms = __ballot_sync(0xffffffffu, is_seed);
+    unsigned pairs = deg >= 2 ? (unsigned)deg : 0u;
+    for (int d = 16; d; d >>= 1) pairs += __shfl_down_sync(0xffffffffu, pairs, d);
+    if ((threadIdx.x & 31) == 0) {
+      P.chain[i >> 5] = mc;
+      P.tpeeled[i >> 5] = ms;
+      bc.add(0, pairs);
+    }
   }
+  unsigned long long *dst[1] = {n_pairs};
+  bc.flush(dst);
 }
 // step 2 (search_dev.cuh): splitter walks, pointer jumping over the splitters, resolution of the rest
 __global__ void k_split_mark(uint64_t n, PeelView P, uint32_t *split) {
@@ -106,28 +144,34 @@ __global__ void k_cpeel(PeelView P, const uint32_t *work, uint32_t n_work, uint3
 // (:443-452): valid count and tips
 __global__ void k_peel_final(GraphView g, PeelView P, unsigned long long *n_peeled, unsigned long long *n_valid,
                              unsigned long long *n_tips) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool peeled = false, valid = false, tip = false;
-  uint64_t a = 0;
-  if (i < g.n) {
-    a = peel_final_item(g, P, (uint32_t)i, peeled);
-    valid = !peeled && !get_inv(g, (uint32_t)i);
-    tip = valid && (a >> 32) == 0;
-  }
-  unsigned mp = __ballot_sync(0xffffffffu, peeled), mv = __ballot_sync(0xffffffffu, valid),
-           mt = __ballot_sync(0xffffffffu, tip);
-  __syncwarp();
-  if (i < g.n) P.adj[i] = a;  // every lane has finished reading adj[] of its own item; children's entries
-                              // are only read through chain/ptr/tpeeled, never through adj[]
-  if ((threadIdx.x & 31) == 0 && i < g.n) {
-    if (mp) {
-      uint32_t *w32 = (uint32_t *)&g.fb[i >> 8].inv[(i >> 6) & 3] + ((i >> 5) & 1);
-      *w32 |= mp;  // this warp owns the word
-      atomicAdd(n_peeled, (unsigned long long)__popc(mp));
+  __shared__ unsigned sh[3];
+  BlockCounters<3> bc(sh);
+  const uint64_t n32 = (g.n + 31) & ~31ull;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
+    bool peeled = false, valid = false, tip = false;
+    uint64_t a = 0;
+    if (i < g.n) {
+      a = peel_final_item(g, P, (uint32_t)i, peeled);
+      valid = !peeled && !get_inv(g, (uint32_t)i);
+      tip = valid && (a >> 32) == 0;
     }
-    if (mv) atomicAdd(n_valid, (unsigned long long)__popc(mv));
-    if (mt) atomicAdd(n_tips, (unsigned long long)__popc(mt));
+    unsigned mp = __ballot_sync(0xffffffffu, peeled), mv = __ballot_sync(0xffffffffu, valid),
+             mt = __ballot_sync(0xffffffffu, tip);
+    __syncwarp();
+    if (i < g.n) P.adj[i] = a;  // every lane has finished reading adj[] of its own item; children's entries
+                                // are only read through chain/ptr/tpeeled, never through adj[]
+    if ((threadIdx.x & 31) == 0) {
+      if (mp) {
+        uint32_t *w32 = (uint32_t *)&g.fb[i >> 8].inv[(i >> 6) & 3] + ((i >> 5) & 1);
+        *w32 |= mp;  // this warp owns the word
+      }
+      bc.add(0, (unsigned)__popc(mp));
+      bc.add(1, (unsigned)__popc(mv));
+      bc.add(2, (unsigned)__popc(mt));
+    }
   }
+  unsigned long long *dst[3] = {n_peeled, n_valid, n_tips};
+  bc.flush(dst);
 }
 
 int run_prune(mg_graph *g, mg_prune_stats *st) {
@@ -147,12 +191,12 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
   MG_TRY(tipbits.alloc(bm_bytes));
   if (n) {
     TimedScope ts(g, T_TIPS, n);
-    MG_LAUNCH(k_tips, grid, 256, 0, s, v, tipbits.as<uint32_t>(), c + 0);
+    MG_LAUNCH(k_tips, stream_grid(g, n, 256), 256, 0, s, v, tipbits.as<uint32_t>(), c + 0);
   }
   // --- InvalidateMultiplicityOneNodes (:439)
   if (n) {
     TimedScope ts(g, T_MULT1, n);
-    MG_LAUNCH(k_mult1, grid, 256, 0, s, v, c + 1);
+    MG_LAUNCH(k_mult1, stream_grid(g, n, 256), 256, 0, s, v, c + 1);
   }
   // --- RecursiveReduction for every tip (:440-442), valid-edge count (:443-449), CollectTips (:451)
   MG_TRY(g->adj.ensure((size_t)n * 8 + 16));
@@ -172,7 +216,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     P.owner = nullptr;
     {
       TimedScope ts(g, T_ADJ, n);
-      MG_LAUNCH(k_chain_init, grid, 256, 0, s, v, P, c + 5);
+      MG_LAUNCH(k_chain_init, stream_grid(g, n, 256), 256, 0, s, v, P, c + 5);
     }
     uint64_t n_work = 0;
     MG_TRY(bitmap_to_ids(tpeeled.as<uint32_t>(), n, work, &n_work, s));  // seeds
@@ -250,7 +294,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
         }
       }
     }
-    MG_LAUNCH(k_peel_final, grid, 256, 0, s, v, P, c + 2, c + 3, c + 4);
+    MG_LAUNCH(k_peel_final, stream_grid(g, n, 256), 256, 0, s, v, P, c + 2, c + 3, c + 4);
     MG_CUDA(cudaStreamSynchronize(s));
   }
   unsigned long long h[5];

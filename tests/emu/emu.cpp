@@ -246,11 +246,10 @@ static uint32_t g_ball_log = 16;  // ball index slots (node capacity = half)
 struct BallSlot {
   std::vector<LNode> nodes;
   std::vector<LTail> tails;
-  std::vector<uint64_t> index, stk;
-  std::vector<uint32_t> relax, cyc_off, pmeta;
-  std::vector<uint16_t> cyc, path;
-  std::vector<int16_t> bl;
-  std::vector<uint8_t> stk_n;
+  std::vector<uint64_t> index;
+  std::vector<Lvl> lvl;
+  std::vector<uint32_t> relax, cyc_off;
+  std::vector<uint16_t> cyc;
   BallArena A;
   uint32_t live = 0;  // nodes of the last build (their index slots are still occupied)
   void init(int M, uint32_t index_log) {
@@ -262,11 +261,11 @@ struct BallSlot {
     relax.resize(std::max<uint32_t>(cap, 32768));
     cyc.resize((size_t)kClusterBound * (M + 1));
     cyc_off.resize(kClusterBound + 1);
-    path.resize(M + 4); bl.resize(M + 4); stk.resize(M + 4); stk_n.resize(M + 4); pmeta.resize(M + 4);
-    A.pmeta = pmeta.data();
+    lvl.resize(M + 4);
+    A.lvl = lvl.data();
     A.nodes = nodes.data(); A.tails = tails.data(); A.node_cap = cap; A.index = index.data(); A.index_log = index_log;
     A.relax = relax.data(); A.relax_cap = (uint32_t)relax.size(); A.cyc = cyc.data(); A.cyc_cap = (uint32_t)cyc.size();
-    A.cyc_off = cyc_off.data(); A.path = path.data(); A.bl = bl.data(); A.stk = stk.data(); A.stk_n = stk_n.data();
+    A.cyc_off = cyc_off.data();
   }
 };
 
