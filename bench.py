@@ -177,7 +177,11 @@ def reference_arm(args):
         device = "cuda" if torch.cuda.is_available() else "cpu"
     except Exception:
         device = "cpu"
-    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))  # what `nproc` reports; os.cpu_count() ignores the container's CPU set
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    note = ""
     g, info = S.make_workload(args.sample, device=device, want_labels=True)
     exe = O.ref_binary("ref_cyclefinder")
     times, n_starts, kind = [], 0, "reference"
@@ -186,14 +190,26 @@ def reference_arm(args):
         prefix = os.path.join(tmp, "graph")
         S.write_megahit_files(g, prefix)
         env = dict(os.environ, MCAAT_REF_COUNT_STARTS="1")
-        for i in range(args.warmup + args.steps):
-            out = subprocess.run([exe, prefix, "-", str(cores), str(THR), str(MIN_LEN), str(MAX_LEN)], check=True,
-                                 capture_output=True, text=True, env=env).stdout
-            js = json.loads([ln for ln in out.splitlines() if ln.startswith("REF_JSON ")][0][9:])
-            n_starts = js["start_nodes"]
-            if i >= args.warmup:
-                times.append(js["ctor_s"])
-    else:  # reference binary absent: the oracle port is the CPU implementation
+        # BASELINE.json quotes the reference at --threads 16.  With more than one thread the reference
+        # races on its result map and can corrupt it and spin forever, so every run is
+        # bounded and the arm falls back to fewer threads instead of hanging.
+        for cores in [c for c in (min(cores, 16), min(cores, 4), 1) if c >= 1]:
+            times = []
+            try:
+                for i in range(args.warmup + args.steps):
+                    out = subprocess.run([exe, prefix, "-", str(cores), str(THR), str(MIN_LEN), str(MAX_LEN)], check=True,
+                                         capture_output=True, text=True, env=env, timeout=120).stdout
+                    js = json.loads([ln for ln in out.splitlines() if ln.startswith("REF_JSON ")][0][9:])
+                    n_starts = js["start_nodes"]
+                    if i >= args.warmup:
+                        times.append(js["ctor_s"])
+                break
+            except (subprocess.TimeoutExpired, subprocess.CalledProcessError, IndexError) as e:
+                note += f" [{cores} threads: {type(e).__name__}]"
+                times = []
+        if not times:
+            exe = None
+    if not exe:  # reference binary absent (or it failed at every thread count): the oracle port is the CPU implementation
         kind, cores = "port", 1
         w, last, tip = unpack_for_oracle(g)
         for i in range(args.warmup + args.steps):
@@ -206,7 +222,7 @@ def reference_arm(args):
     dt = float(np.mean(times))
     val = n_starts / dt
     sample = (f"workload '{args.sample}' (same recipe at 1/20 scale): {g['n']} items, {n_starts} start nodes; "
-              f"CycleFinder constructor {dt:.2f} s with {cores} threads")
+              f"CycleFinder constructor {dt:.2f} s with {cores} threads" + note)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
@@ -271,7 +287,7 @@ def main():
                 t = torch.from_numpy(graph[key].view(np.int64 if dt == torch.int64 else np.int16)).cuda()
             else:
                 t = torch.empty(size, dtype=dt, device="cuda")
-            dist.broadcast(t, src=0)
+            dist.broadcast(t.view(torch.uint8), src=0)  # NCCL has no 16-bit integer type: broadcast raw bytes
             dev[key] = t
         torch.cuda.synchronize()
         bcast_s = time.perf_counter() - tb
