@@ -106,6 +106,38 @@ __global__ void k_chain_resolve(uint64_t n, PeelView P, int *capped) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n && !chain_resolve_item(P, (uint32_t)i)) *capped = 1;
 }
+// step 2b (search_dev.cuh): unary branch nodes become chain nodes
+__global__ void k_reclass(GraphView g, PeelView P, uint32_t *fresh, uint32_t *newseed, unsigned long long *n_fresh,
+                          unsigned long long *n_seed) {
+  __shared__ unsigned sh[2];
+  BlockCounters<2> bc(sh);
+  const uint64_t n32 = (g.n + 31) & ~31ull;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
+    int r = i < g.n ? reclass_item(g, P, (uint32_t)i) : 0;
+    unsigned mf = __ballot_sync(0xffffffffu, r == 1), ms = __ballot_sync(0xffffffffu, r == 2);
+    if ((threadIdx.x & 31) == 0) {
+      fresh[i >> 5] = mf;
+      newseed[i >> 5] = ms;
+      bc.add(0, (unsigned)__popc(mf));
+      bc.add(1, (unsigned)__popc(ms));
+    }
+  }
+  unsigned long long *dst[2] = {n_fresh, n_seed};
+  bc.flush(dst);
+}
+__global__ void k_reclass_jump(PeelView P, const uint32_t *fresh, const uint32_t *ids, uint32_t n_ids, int *unresolved) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  bool u = i < n_ids && reclass_jump_item(P, fresh, ids[i]);
+  if (__any_sync(0xffffffffu, u) && (threadIdx.x & 31) == 0) *unresolved = 1;
+}
+__global__ void k_or_words(uint32_t *dst, const uint32_t *src, size_t n_words) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_words) dst[i] |= src[i];
+}
+__global__ void k_relink(uint64_t n, PeelView P, const uint32_t *fresh) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) relink_item(P, fresh, (uint32_t)i);
+}
 // exhaustive fallback: one pointer-jumping round over every item
 __global__ void k_chain_jump(uint64_t n, PeelView P, int *unresolved) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -261,6 +293,44 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
             if (!h) break;
           }
         }
+      }
+      if (!getenv("MCAAT_PEEL_NO_RECLASS")) {  // unary branch nodes -> chain nodes, a few rounds
+        DevBuf fresh, newseed, fresh_ids;
+        MG_TRY(fresh.alloc(bm_bytes));
+        MG_TRY(newseed.alloc(bm_bytes));
+        const size_t n_words = (size_t)((n + 31) / 32);
+        DevBuf rc;
+        MG_TRY(rc.alloc(16));
+        for (int round = 0; round < 4; ++round) {
+          MG_CUDA(cudaMemsetAsync(rc.p, 0, 16, s));
+          MG_LAUNCH(k_reclass, stream_grid(g, n, 256), 256, 0, s, v, P, fresh.as<uint32_t>(), newseed.as<uint32_t>(),
+                    rc.as<unsigned long long>(), rc.as<unsigned long long>() + 1);
+          unsigned long long hc[2];
+          MG_CUDA(cudaMemcpyAsync(hc, rc.p, 16, cudaMemcpyDeviceToHost, s));
+          MG_CUDA(cudaStreamSynchronize(s));
+          if (hc[0]) {
+            uint64_t n_fresh = 0;
+            MG_TRY(bitmap_to_ids(fresh.as<uint32_t>(), n, fresh_ids, &n_fresh, s));
+            for (int r2 = 0; r2 < 36; r2 += 4) {
+              MG_CUDA(cudaMemsetAsync(unresolved, 0, 4, s));
+              for (int k = 0; k < 4; ++k)
+                MG_LAUNCH(k_reclass_jump, grid_for(n_fresh, 256), 256, 0, s, P, fresh.as<uint32_t>(),
+                          fresh_ids.as<uint32_t>(), (uint32_t)n_fresh, unresolved);
+              int h = 0;
+              MG_CUDA(cudaMemcpyAsync(&h, unresolved, 4, cudaMemcpyDeviceToHost, s));
+              MG_CUDA(cudaStreamSynchronize(s));
+              if (!h) break;
+            }
+            MG_LAUNCH(k_or_words, grid_for(n_words, 256), 256, 0, s, chain.as<uint32_t>(), fresh.as<uint32_t>(), n_words);
+            MG_LAUNCH(k_relink, grid, 256, 0, s, n, P, fresh.as<uint32_t>());
+          }
+          if (hc[1])
+            MG_LAUNCH(k_or_words, grid_for(n_words, 256), 256, 0, s, tpeeled.as<uint32_t>(), newseed.as<uint32_t>(), n_words);
+          if (getenv("MCAAT_PEEL_VERBOSE"))
+            fprintf(stderr, "[peel] reclass round %d: %llu unary branch nodes, %llu new seeds\n", round, hc[0], hc[1]);
+          if (hc[0] + hc[1] < 64) break;
+        }
+        MG_TRY(bitmap_to_ids(tpeeled.as<uint32_t>(), n, work, &n_work, s));  // collected tips + new seeds
       }
       unsigned long long pairs = 0;
       MG_CUDA(cudaMemcpyAsync(&pairs, c + 5, 8, cudaMemcpyDeviceToHost, s));

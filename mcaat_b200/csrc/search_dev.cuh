@@ -40,6 +40,13 @@ MG_HD int adj_outgoing(uint64_t a, uint32_t *out) {
   return deg;
 }
 
+MG_HD void prefetch_l2(const void *p) {
+#if defined(__CUDA_ARCH__)
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
+  (void)p;
+#endif
+}
 MG_HD uint32_t hash_u32_fwd(uint32_t k, uint32_t log2cap) { return (k * 2654435761u) >> (32 - log2cap); }
 
 // ------------------------------------------------------------------ atomics / fences
@@ -198,6 +205,48 @@ MG_HD uint32_t terminal_of(const PeelView &P, uint32_t c) {
   uint32_t t = ld_ro(&P.ptr[c]);
   return bm_get(P.chain, t) ? kNull : t;
 }
+// Step 2b: UNARY branch nodes.  A branch node whose out-neighbours all resolve to terminals that are
+// already peeled (collected tips) — except for ONE distinct terminal T — is peeled iff T is: for the
+// closure it behaves like a chain node pointing at T.  Typical: a SNP bubble between two strains (both
+// arms end in the same node), or a path node with a sequencing-error tip hanging off it.  Re-classifying
+// them as chain nodes (and resolving the new chains, which only involves the re-classified nodes)
+// removes the long serial cascades the work list of step 3 would otherwise walk one branch node
+// at a time.  Returns 0 = still a terminal, 1 = now a chain node (ptr[b] set), 2 = all out-neighbours
+// are peeled already: b becomes a seed.
+MG_HD int reclass_item(const GraphView &g, const PeelView &P, uint32_t b) {
+  if (get_inv(g, b) || bm_get(P.chain, b) || bm_get(P.tpeeled, b)) return 0;
+  uint64_t a = P.adj[b];
+  uint32_t mask = (uint32_t)(a >> 32) & 0xFFu, next = (uint32_t)a;
+  if (popc32(mask) < 2) return 0;
+  uint32_t uniq = kNull;
+  for (int i = 0; mask; ++i, mask >>= 1) {
+    if (!(mask & 1)) continue;
+    uint32_t tc = terminal_of(P, next - i);
+    if (tc == kNull || tc == b) return 0;          // chain cycle / depends on itself: never peeled
+    if (bm_get(P.tpeeled, tc)) continue;           // peeled already
+    if (((uint32_t)(P.adj[tc] >> 32) & 0xFFu) == 0) return 0;  // a sink that is not a collected tip: never peeled
+    if (uniq == kNull) uniq = tc;
+    else if (uniq != tc) return 0;                 // two distinct open dependencies: a true AND node
+  }
+  if (uniq == kNull) return 2;
+  P.ptr[b] = uniq;
+  return 1;
+}
+// resolution among the re-classified nodes of one round (`fresh` = their bitmap); true while unresolved
+MG_HD bool reclass_jump_item(const PeelView &P, const uint32_t *fresh, uint32_t b) {
+  uint32_t p = ld_cg_u32(&P.ptr[b]);
+  if (!bm_get(fresh, p) || p == b) return false;
+  uint32_t q = ld_cg_u32(&P.ptr[p]);
+  if (q == p) q = b;  // the node ahead is known to be cyclic, so is this one
+  P.ptr[b] = q;
+  return true;
+}
+// chain nodes whose terminal has just been re-classified move on to that node's terminal
+MG_HD void relink_item(const PeelView &P, const uint32_t *fresh, uint32_t v) {
+  if (!bm_get(P.chain, v)) return;
+  uint32_t t = ld_cg_u32(&P.ptr[v]);
+  if (bm_get(fresh, t) && t != v) P.ptr[v] = ld_cg_u32(&P.ptr[t]);
+}
 MG_HD void dep_insert(const PeelView &P, uint32_t term, uint32_t b) {
   uint32_t mask = (1u << P.dep_log) - 1, h = hash_u32_fwd(term, P.dep_log);
   uint64_t val = ((uint64_t)term << 32) | b;
@@ -216,7 +265,7 @@ MG_HD void dep_insert(const PeelView &P, uint32_t term, uint32_t b) {
 MG_HD void dep_register_item(const GraphView &g, const PeelView &P, uint32_t b) {
   uint64_t a = P.adj[b];
   uint32_t mask = (uint32_t)(a >> 32) & 0xFFu, next = (uint32_t)a;
-  if (get_inv(g, b) || popc32(mask) < 2) return;
+  if (get_inv(g, b) || popc32(mask) < 2 || bm_get(P.chain, b) || bm_get(P.tpeeled, b)) return;
   uint32_t t[8];
   int n = 0;
   for (int i = 0; mask; ++i, mask >>= 1) {
@@ -361,6 +410,7 @@ MG_HD int dls_run(const uint64_t *adj, uint32_t start, int limit, Set &seen, uin
         stk_node[sp] = x;
         stk_depth[sp] = (uint16_t)(depth + 1);
         ++sp;
+        prefetch_l2(&adj[x]);  // x is expanded when it is popped; its navigation entry is usually a DRAM miss
       }
     }
     if (v == start && depth > 1) return kDlsFound;  // :337-339

@@ -180,6 +180,29 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
       else for (uint64_t i = 0; i < n; ++i) any |= chain_jump_item(P, (uint32_t)i);
       if (!any) break;
     }
+  if (!(reverse_order & 4)) {  // unary branch nodes -> chain nodes (as prune.cu); reverse_order & 4 skips it
+    for (int round = 0; round < 4; ++round) {
+      std::vector<uint32_t> fresh(words, 0), newseed(words, 0), ids;
+      uint64_t nf = 0, ns = 0;
+      for (uint64_t i = 0; i < n; ++i) {
+        int r = reclass_item(v, P, (uint32_t)i);
+        if (r == 1) { fresh[i >> 5] |= 1u << (i & 31); ids.push_back((uint32_t)i); ++nf; }
+        if (r == 2) { newseed[i >> 5] |= 1u << (i & 31); ++ns; }
+      }
+      if (reverse_order & 1) std::reverse(ids.begin(), ids.end());
+      for (int r2 = 0; r2 < 36; ++r2) {
+        bool any = false;
+        for (uint32_t b : ids) any |= reclass_jump_item(P, fresh.data(), b);
+        if (!any) break;
+      }
+      for (size_t w = 0; w < words; ++w) { chain[w] |= fresh[w]; tpeeled[w] |= newseed[w]; }
+      if (nf) for (uint64_t i = 0; i < n; ++i) relink_item(P, fresh.data(), (uint32_t)i);
+      if (nf + ns < 64) break;
+    }
+    work.clear();
+    for (uint64_t i = 0; i < n; ++i)
+      if (bm_get(P.tpeeled, (uint32_t)i)) work.push_back((uint32_t)i);
+  }
   uint32_t dep_log = 4;
   while (((uint64_t)1 << dep_log) < 2 * pairs + 16) ++dep_log;
   std::vector<uint64_t> dep((size_t)1 << dep_log, ~0ull);

@@ -95,9 +95,10 @@ def test_small_arena_overflow_is_rerun_exactly():
 
 @pytest.mark.parametrize("name", ["tiny", "strain", "repeatrich"])
 def test_peel_variants_agree(name):
-    """splitter-based chain resolution (forward / reverse item order) == exhaustive pointer jumping"""
+    """splitter-based chain resolution (forward / reverse item order) == exhaustive pointer jumping (2, 3);
+    with and without (4..7) the re-classification of unary branch nodes"""
     inv = []
-    for mode in (0, 1, 2, 3):
+    for mode in range(8):
         g = emu(name)
         g.prune(reverse_order=mode)
         inv.append(g.invalid())
