@@ -116,18 +116,9 @@ def hot_path_step(g, rank=0, world=1, dist=None, torch=None):
     if world == 1:
         ok, exp = g.dls(cand, MAX_LEN)
     else:
-        mine = cand[rank::world]
-        ok_m, exp = g.dls(mine, MAX_LEN)
-        per = (cand.size + world - 1) // world
-        buf = torch.zeros(per, dtype=torch.uint8, device="cuda")
-        buf[:ok_m.size] = torch.from_numpy(ok_m.astype(np.uint8)).cuda()
-        out = [torch.empty_like(buf) for _ in range(world)]
-        dist.all_gather(out, buf)
-        ok = np.zeros(cand.size, bool)
-        for r in range(world):
-            part = out[r].cpu().numpy().astype(bool)
-            cnt = cand[r::world].size
-            ok[r::world] = part[:cnt]
+        from mcaat_b200 import shard
+        ok_m, exp = g.dls(shard.my_share(cand, rank, world), MAX_LEN)
+        ok = shard.gather_verdicts(ok_m, cand.size, rank, world, dist, torch, "cuda")
         e = torch.tensor([exp], dtype=torch.int64, device="cuda")
         dist.all_reduce(e)
         exp = int(e.item())
