@@ -349,10 +349,15 @@ def main():
             torch.cuda.synchronize()
             ta = time.perf_counter()
             g2 = DeviceGraph(host, device=local)
+            t_up = time.perf_counter()
             st2, rb = hot_path_step(g2)
+            t_hp = time.perf_counter()
             inv = g2.invalid_words()
             torch.cuda.synchronize()
             tb_ = time.perf_counter()
+            if os.environ.get("BENCH_DEBUG"):
+                print("[e2e wall ms] upload+index %.1f hot path %.1f invalid read-back %.1f" %
+                      ((t_up - ta) * 1e3, (t_hp - t_up) * 1e3, (tb_ - t_hp) * 1e3), file=sys.stderr)
             g2.close()
             if i > 0:
                 e2e_t.append(tb_ - ta)
@@ -375,8 +380,15 @@ def main():
     per_launch_ms = fam[top]["ms"] / fam[top]["launches"]
     launches_per_step = fam[top]["launches"] / args.steps
     achieved = alg[top] / launches_per_step / (per_launch_ms * 1e-3) / 1e9
+    traffic = None  # DRAM bytes per launch of that kernel from the committed ncu --set full capture (same workload)
+    if args.workload == "c2":
+        try:
+            with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+                traffic = json.load(f).get(top, {}).get("bytes_per_launch")
+        except Exception:
+            traffic = None
     roofline = dict(bound="hbm", kernel=top, achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
-                    traffic=None, peak_source=peak_kind, ms_per_launch=per_launch_ms,
+                    traffic=traffic, peak_source=peak_kind, ms_per_launch=per_launch_ms,
                     algorithmic_bytes_per_launch=alg[top] / launches_per_step)
     phases = {k: round(v["ms"] / args.steps, 3) for k, v in timers.items() if v["launches"]}
     cpu = None

@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_solo(GraphView g, 
 // ---- the pipeline proper: extracted-ball searches (ball_dev.cuh)
 struct BallLayout {  // per-worker arena in global memory (byte offsets inside one slot)
   uint32_t index_log, node_cap, relax_cap, cyc_cap, depth_cap;
-  size_t off_nodes, off_tails, off_index, off_relax, off_cyc, off_cyc_off, bytes;
+  size_t off_nodes, off_tails, off_index, off_relax, off_cyc, off_cyc_keys, off_cyc_off, bytes;
   uint32_t smem_bytes;  // per worker: the path levels (Lvl) live in shared memory
 };
 static BallLayout make_ball_layout(int max_len, uint32_t index_log) {
@@ -280,6 +280,7 @@ static BallLayout make_ball_layout(int max_len, uint32_t index_log) {
   L.off_index = o; o = align_up(o + ((size_t)8 << index_log), 128);
   L.off_relax = o; o = align_up(o + (size_t)L.relax_cap * 4, 128);
   L.off_cyc = o; o = align_up(o + (size_t)L.cyc_cap * 2, 128);
+  L.off_cyc_keys = o; o = align_up(o + (size_t)L.cyc_cap * 4, 128);
   L.off_cyc_off = o; o = align_up(o + (size_t)(kClusterBound + 1) * 4, 128);
   L.bytes = align_up(o, 128);
   L.smem_bytes = (uint32_t)align_up((size_t)L.depth_cap * sizeof(Lvl), 16);
@@ -310,6 +311,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t worker = blockIdx.x * kWarpsPerBlock + warp;
   const BallArena A = ball_arena_of(arena + (size_t)worker * L.bytes, smem_all + (size_t)warp * L.smem_bytes, L);
+  uint32_t *cyc_keys = (uint32_t *)(arena + (size_t)worker * L.bytes + L.off_cyc_keys);  // staged cycles as item ids
   Coop co;
   co.lane = lane;
   unsigned long long searches = 0;
@@ -387,6 +389,10 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
         ++reruns;
       }
       __syncwarp();  // lane 0's arena writes (staged cycles) are visible to the warp
+      // item ids of the staged cycles, so that the commit only has to stream them
+      const uint32_t n_staged = __shfl_sync(0xffffffffu, R.n_nodes, 0);
+      for (uint32_t j = lane; j < n_staged; j += 32) cyc_keys[j] = A.nodes[A.cyc[j]].key;
+      __syncwarp();
     };
     // a ticket whose start is already marked is skipped for good (:476); the committing worker ahead
     // consumes such tickets itself (below), so this worker just moves on
@@ -435,30 +441,33 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     int status = __shfl_sync(0xffffffffu, R.status, 0);
     const bool skip = __shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0) != 0;  // :476
     if (!skip) {
-      // kEnumSkipped here cannot happen (a search is only abandoned after its start was marked); it
-      // takes the same exclusive repeat as a stale result
+      // Nothing has been marked since the result was last examined (same epoch) -> it is exact.  Else
+      // re-examine it; a stale (or, impossible, abandoned) result is repeated exclusively.
+      const uint32_t ep_now = __shfl_sync(0xffffffffu, ld_vol(&ctl->mark_epoch), 0);
       while (status != kEnumOverflow &&
-             (status == kEnumSkipped || stale(__shfl_sync(0xffffffffu, R.n_keys, 0)))) {
-        speculate(true);  // exclusive repeat against the final bitmap
+             (status == kEnumSkipped || (ep_now != epoch_checked && stale(__shfl_sync(0xffffffffu, R.n_keys, 0))))) {
+        speculate(true);  // exclusive repeat against the final bitmap (sets epoch_checked = ep_now)
         ++reruns;
         status = __shfl_sync(0xffffffffu, R.status, 0);
       }
       if (status == kEnumOverflow) stopped = 1;
     }
     TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0, live, us_build};
+    uint32_t n_nodes = 0, n_cycles = 0, node_base = 0, cyc_base = 0;
     if (!skip && !stopped) {
-      const uint32_t n_nodes = __shfl_sync(0xffffffffu, R.n_nodes, 0);
-      const uint32_t n_cycles = __shfl_sync(0xffffffffu, R.n_cycles, 0);
-      const uint32_t node_base = ld_vol(&ctl->pool_nodes), cyc_base = ld_vol(&ctl->pool_cycles);
+      n_nodes = __shfl_sync(0xffffffffu, R.n_nodes, 0);
+      n_cycles = __shfl_sync(0xffffffffu, R.n_cycles, 0);
+      node_base = ld_vol(&ctl->pool_nodes);
+      cyc_base = ld_vol(&ctl->pool_cycles);
       if ((uint64_t)node_base + n_nodes > pool_nodes_cap || (uint64_t)cyc_base + n_cycles > pool_len_cap) {
         stopped = 2;
       } else {
-        for (uint32_t j = lane; j < n_nodes; j += 32) {  // :217-222 + results[start] = cycles (:479)
-          const uint32_t x = A.nodes[A.cyc[j]].key;
-          pool_nodes[node_base + j] = x;
+        // :217-222 — only the marks and the reservation of the output range are on the hand-over path;
+        // the cycles themselves are copied out after the next ticket has been given its turn
+        for (uint32_t j = lane; j < n_nodes; j += 32) {
+          const uint32_t x = cyc_keys[j];
           atomicOr(&visited[x >> 5], 1u << (x & 31));
         }
-        for (uint32_t j = lane; j < n_cycles; j += 32) pool_len[cyc_base + j] = A.cyc_off[j + 1] - A.cyc_off[j];
         rec.fate = kFateAccepted;
         rec.n_cycles = n_cycles;
         rec.n_nodes = n_nodes;
@@ -475,10 +484,6 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     if (stopped) {  // this ticket needs the host (hash-map search in a large arena / larger pool): drain
       if (lane == 0) atomicExch(&ctl->stop, (uint32_t)stopped);
       break;
-    }
-    if (lane == 0) {
-      rec.us_committed = (uint32_t)((gtime_ns() - t_kernel) / 1000);
-      recs[t] = rec;
     }
     __threadfence();
     __syncwarp();
@@ -503,6 +508,15 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     if (lane == 0) {
       if (rec.n_nodes) atomicAdd(&ctl->mark_epoch, 1u);  // after the fence: the marks are visible first
       atomicExch(&ctl->commit_idx, next);                // hand over
+    }
+    // ---- off the hand-over path: results[start] = cycles (:479)
+    if (rec.fate == kFateAccepted) {
+      for (uint32_t j = lane; j < n_nodes; j += 32) pool_nodes[node_base + j] = cyc_keys[j];
+      for (uint32_t j = lane; j < n_cycles; j += 32) pool_len[cyc_base + j] = A.cyc_off[j + 1] - A.cyc_off[j];
+    }
+    if (lane == 0) {
+      rec.us_committed = (uint32_t)((gtime_ns() - t_kernel) / 1000);
+      recs[t] = rec;
     }
   }
   __syncwarp();
