@@ -40,9 +40,9 @@ MG_HD int adj_outgoing(uint64_t a, uint32_t *out) {
   return deg;
 }
 
-MG_HD void prefetch_l2(const void *p) {
+MG_HD void prefetch_l2(const void *p) {  // into L1 (and with it L2)
 #if defined(__CUDA_ARCH__)
-  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
 #else
   (void)p;
 #endif
@@ -370,6 +370,28 @@ MG_HD int set_insert(U32HashSet &s, uint32_t key) {
     h = (h + 1) & mask;
   }
 }
+// Two-phase insert: set_peek() loads the first probe slot of a key, set_insert(s, key, peeked) finishes.
+// A node's <= 4 neighbours are peeked together, so their probe loads overlap instead of forming a chain;
+// a slot that was free when peeked is read again before it is taken (a neighbour peeked in the same
+// batch may have taken it), occupied slots never change during a search.
+MG_HD uint32_t set_peek(const U32HashSet &s, uint32_t key) { return s.tab[hash_u32(key, s.log2cap)]; }
+MG_HD int set_insert(U32HashSet &s, uint32_t key, uint32_t peeked) {
+  if (peeked == key) return 0;
+  uint32_t mask = (1u << s.log2cap) - 1;
+  uint32_t h = hash_u32(key, s.log2cap);
+  if (peeked != kNull) h = (h + 1) & mask;
+  for (;;) {
+    uint32_t cur = s.tab[h];
+    if (cur == key) return 0;
+    if (cur == kNull) {
+      if (s.count >= s.max_count) return -1;
+      s.tab[h] = key;
+      ++s.count;
+      return 1;
+    }
+    h = (h + 1) & mask;
+  }
+}
 struct BitSet {  // one bit per graph item; exact fallback for very large searches
   uint32_t *bits;
 };
@@ -380,37 +402,58 @@ MG_HD int set_insert(BitSet &s, uint32_t key) {
   return 1;
 }
 
+MG_HD uint32_t set_peek(const BitSet &s, uint32_t key) { return s.bits[key >> 5]; }
+MG_HD int set_insert(BitSet &s, uint32_t key, uint32_t peeked) {
+  if ((peeked >> (key & 31)) & 1) return 0;
+  return set_insert(s, key);
+}
+
 constexpr int kDlsFound = 1, kDlsNotFound = 0, kDlsSetFull = -1, kDlsStackFull = -2;
 
 // src/cycle_finder.cpp:248-343 with target == start (the only call site, :411).  `adj` is the
 // navigation cache.  The explicit stack holds at most 3*limit+5 entries.
+// A stack entry carries the node's navigation entry: it is loaded together with the probes of the
+// parent's expansion (all <= 4 neighbours at once), so an expansion waits for ONE round of memory
+// latency instead of two dependent ones (pop -> navigation entry -> probes).
 template <class Set>
 MG_HD int dls_run(const uint64_t *adj, uint32_t start, int limit, Set &seen, uint32_t *stk_node,
-                  uint16_t *stk_depth, uint32_t stk_cap, uint32_t &expansions) {
+                  uint16_t *stk_depth, uint64_t *stk_adj, uint32_t stk_cap, uint32_t &expansions) {
   uint32_t sp = 0;
   stk_node[0] = start;
   stk_depth[0] = 0;
+  stk_adj[0] = ld_ro(&adj[start]);
   sp = 1;
   while (sp) {
     --sp;
     uint32_t v = stk_node[sp];
     int depth = stk_depth[sp];
     uint32_t nb[4];
-    int outdeg = adj_outgoing(ld_ro(&adj[v]), nb);  // :285-302 (adj == 0 for an invalid v)
+    int outdeg = adj_outgoing(stk_adj[sp], nb);     // :285-302 (adj == 0 for an invalid v)
     if (outdeg == 0) continue;                      // :294
     ++expansions;
     if (depth >= limit) continue;                   // :312
     if (outdeg > 4) outdeg = 4;
-    for (int i = 0; i < outdeg; ++i) {              // :320-334, descending ids
-      uint32_t x = nb[i];
-      int r = set_insert(seen, x);
-      if (r < 0) return kDlsSetFull;
-      if (r == 1 || (x == start && depth > 0)) {
-        if (sp >= stk_cap) return kDlsStackFull;
-        stk_node[sp] = x;
-        stk_depth[sp] = (uint16_t)(depth + 1);
-        ++sp;
-        prefetch_l2(&adj[x]);  // x is expanded when it is popped; its navigation entry is usually a DRAM miss
+    uint32_t peeked[4] = {0, 0, 0, 0};
+    uint64_t nadj[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (i < outdeg) {
+        peeked[i] = set_peek(seen, nb[i]);
+        nadj[i] = ld_ro(&adj[nb[i]]);
+      }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {                   // :320-334, descending ids
+      if (i < outdeg) {
+        uint32_t x = nb[i];
+        int r = set_insert(seen, x, peeked[i]);
+        if (r < 0) return kDlsSetFull;
+        if (r == 1 || (x == start && depth > 0)) {
+          if (sp >= stk_cap) return kDlsStackFull;
+          stk_node[sp] = x;
+          stk_depth[sp] = (uint16_t)(depth + 1);
+          stk_adj[sp] = nadj[i];
+          ++sp;
+        }
       }
     }
     if (v == start && depth > 1) return kDlsFound;  // :337-339

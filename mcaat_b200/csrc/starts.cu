@@ -41,6 +41,7 @@ struct DlsArena {
   uint16_t *slotlog;   // [threads][max_count]
   uint32_t *stk_node;  // [threads][stk_cap]
   uint16_t *stk_depth; // [threads][stk_cap]
+  uint64_t *stk_adj;   // [threads][stk_cap] navigation entries of the stacked nodes
   uint32_t log2cap, max_count, stk_cap;
 };
 
@@ -65,17 +66,48 @@ MG_HD int set_insert(LoggedSet &s, uint32_t key) {
   }
 }
 
+MG_HD uint32_t set_peek(const LoggedSet &s, uint32_t key) { return s.tab[hash_u32(key, s.log2cap)]; }
+MG_HD int set_insert(LoggedSet &s, uint32_t key, uint32_t peeked) {
+  if (peeked == key) return 0;
+  uint32_t mask = (1u << s.log2cap) - 1;
+  uint32_t h = hash_u32(key, s.log2cap);
+  if (peeked != kNull) h = (h + 1) & mask;
+  for (;;) {
+    uint32_t cur = s.tab[h];
+    if (cur == key) return 0;
+    if (cur == kNull) {
+      if (s.count >= s.max_count) return -1;
+      s.tab[h] = key;
+      s.log[s.count++] = (uint16_t)h;
+      return 1;
+    }
+    h = (h + 1) & mask;
+  }
+}
+
 __global__ void __launch_bounds__(128) k_dls(const uint64_t *__restrict__ adj, const uint32_t *__restrict__ cand,
                                             const uint32_t *__restrict__ todo, uint32_t n_cand, int limit, DlsArena A,
-                                            int8_t *result, uint32_t *queue, unsigned long long *expansions) {
+                                            int8_t *result, uint32_t *queue, unsigned long long *expansions,
+                                            uint32_t *per_search /* nullable: expansions of every search */,
+                                            int smem_stack) {
+  extern __shared__ __align__(16) uint8_t dls_smem[];
   const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
   LoggedSet seen;
   seen.tab = A.tabs + ((size_t)tid << A.log2cap);
   seen.log = A.slotlog + (size_t)tid * A.max_count;
   seen.log2cap = A.log2cap;
   seen.max_count = A.max_count;
+  // DFS stack: global memory, or (later tiers: few, long searches) shared memory — the pop that opens
+  // every expansion then costs a shared-memory access instead of an L2 round trip
   uint32_t *stk_node = A.stk_node + (size_t)tid * A.stk_cap;
   uint16_t *stk_depth = A.stk_depth + (size_t)tid * A.stk_cap;
+  uint64_t *stk_adj = A.stk_adj + (size_t)tid * A.stk_cap;
+  if (smem_stack) {
+    stk_adj = (uint64_t *)dls_smem + (size_t)threadIdx.x * A.stk_cap;
+    uint32_t *nodes = (uint32_t *)((uint64_t *)dls_smem + (size_t)blockDim.x * A.stk_cap);
+    stk_node = nodes + (size_t)threadIdx.x * A.stk_cap;
+    stk_depth = (uint16_t *)(nodes + (size_t)blockDim.x * A.stk_cap) + (size_t)threadIdx.x * A.stk_cap;
+  }
   uint32_t exp = 0;
   unsigned long long exp_total = 0;
   for (;;) {
@@ -84,8 +116,9 @@ __global__ void __launch_bounds__(128) k_dls(const uint64_t *__restrict__ adj, c
     if (todo) idx = todo[idx];  // later tiers: positions of the searches a smaller set could not hold
     seen.count = 0;
     exp = 0;
-    int r = dls_run(adj, cand[idx], limit, seen, stk_node, stk_depth, A.stk_cap, exp);
+    int r = dls_run(adj, cand[idx], limit, seen, stk_node, stk_depth, stk_adj, A.stk_cap, exp);
     result[idx] = (int8_t)r;
+    if (per_search) per_search[idx] = exp;
     if (r >= 0) exp_total += exp;  // a search that filled its set is repeated (and counted) by the next tier
     for (uint32_t j = 0; j < seen.count; ++j) seen.tab[seen.log[j]] = kNull;  // undo
   }
@@ -98,7 +131,7 @@ __global__ void __launch_bounds__(128) k_dls(const uint64_t *__restrict__ adj, c
 __global__ void __launch_bounds__(256) k_dls_big(const uint64_t *__restrict__ adj, const uint32_t *__restrict__ cand,
                                                 const uint32_t *__restrict__ todo, uint32_t n_todo, int limit,
                                                 uint32_t *bitmaps, size_t words_per_map, uint32_t *stk_node,
-                                                uint16_t *stk_depth, uint32_t stk_cap, int8_t *result,
+                                                uint16_t *stk_depth, uint64_t *stk_adj, uint32_t stk_cap, int8_t *result,
                                                 unsigned long long *expansions) {
   uint32_t *bits = bitmaps + (size_t)blockIdx.x * words_per_map;
   __shared__ int r_sh;
@@ -110,7 +143,7 @@ __global__ void __launch_bounds__(256) k_dls_big(const uint64_t *__restrict__ ad
       uint32_t exp = 0;
       uint32_t idx = todo[t];
       r_sh = dls_run(adj, cand[idx], limit, seen, stk_node + (size_t)blockIdx.x * stk_cap,
-                     stk_depth + (size_t)blockIdx.x * stk_cap, stk_cap, exp);
+                     stk_depth + (size_t)blockIdx.x * stk_cap, stk_adj + (size_t)blockIdx.x * stk_cap, stk_cap, exp);
       result[idx] = (int8_t)r_sh;
       atomicAdd(expansions, (unsigned long long)exp);
     }
@@ -141,7 +174,7 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
   }
   if (n > 0xFFFFFFF0ull) return MG_ELIMIT;
   const int block = 128;
-  DevBuf sn, sd, result, ctr, todo_b;
+  DevBuf sn, sd, sa, result, ctr, todo_b;
   MG_TRY(result.alloc(n));
   MG_TRY(ctr.alloc(64));
   MG_CUDA(cudaMemsetAsync(ctr.p, 0, 64, s));
@@ -154,12 +187,19 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
   const uint32_t tier_threads[2] = {(uint32_t)g->sm_count * env_u32("MCAAT_DLS_BLOCKS_PER_SM", 8, 1, 16) * block,
                                     (uint32_t)g->sm_count * env_u32("MCAAT_DLS_THREADS2_PER_SM", 64, 1, 256)};
   DlsArena A;
-  A.stk_cap = (uint32_t)(4 * limit + 8);
+  A.stk_cap = (uint32_t)(4 * limit + 8) | 1u;  // odd: per-thread stacks in shared memory spread over the banks
+  const bool verbose = getenv("MCAAT_DLS_VERBOSE") != nullptr;
+  DevBuf per_search;
+  if (verbose) MG_TRY(per_search.alloc(n * 4));
   for (int tier = 0; tier < 2; ++tier) {
     const uint64_t n_work = tier == 0 ? n : todo.size();
     if (n_work == 0 || (tier == 1 && tier_log[1] <= tier_log[0])) continue;
-    uint32_t blocks = (uint32_t)std::min<uint64_t>((tier_threads[tier] + block - 1) / block, (n_work + block - 1) / block);
-    const size_t threads = (size_t)blocks * block;
+    // tier 1: 128-thread blocks, stacks in global memory; tier 2: 32-thread blocks, stacks in shared memory
+    const int tblock = tier == 0 ? block : 32;
+    uint32_t blocks = (uint32_t)std::min<uint64_t>((tier_threads[tier] + tblock - 1) / tblock, (n_work + tblock - 1) / tblock);
+    const size_t threads = (size_t)blocks * tblock;
+    const size_t smem = tier == 0 ? 0 : (size_t)tblock * A.stk_cap * 14;
+    if (smem) MG_CUDA(cudaFuncSetAttribute(k_dls, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     A.log2cap = tier_log[tier];
     A.max_count = (1u << A.log2cap) / 2;
     DevBuf tabs, slotlog;
@@ -167,6 +207,7 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
     MG_TRY(slotlog.alloc(threads * A.max_count * 2));
     MG_TRY(sn.ensure(threads * A.stk_cap * 4));
     MG_TRY(sd.ensure(threads * A.stk_cap * 2));
+    if (tier == 0) MG_TRY(sa.ensure(threads * A.stk_cap * 8));
     MG_CUDA(cudaMemsetAsync(tabs.p, 0xFF, tabs.bytes, s));
     MG_CUDA(cudaMemsetAsync(ctr.p, 0, 4, s));
     if (tier == 1) {
@@ -177,10 +218,24 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
     A.slotlog = slotlog.as<uint16_t>();
     A.stk_node = sn.as<uint32_t>();
     A.stk_depth = sd.as<uint16_t>();
+    A.stk_adj = sa.as<uint64_t>();
     {
       TimedScope ts(g, T_DLS, tier == 0 ? n : 0);
-      MG_LAUNCH(k_dls, blocks, block, 0, s, g->adj.as<uint64_t>(), ids_dev, tier == 0 ? nullptr : todo_b.as<uint32_t>(),
-                (uint32_t)n_work, limit, A, result.as<int8_t>(), ctr.as<uint32_t>(), exp_dev);
+      MG_LAUNCH(k_dls, blocks, tblock, smem, s, g->adj.as<uint64_t>(), ids_dev, tier == 0 ? nullptr : todo_b.as<uint32_t>(),
+                (uint32_t)n_work, limit, A, result.as<int8_t>(), ctr.as<uint32_t>(), exp_dev,
+                verbose ? per_search.as<uint32_t>() : nullptr, tier == 0 ? 0 : 1);
+    }
+    if (verbose) {
+      std::vector<uint32_t> ps(n);
+      MG_CUDA(cudaMemcpyAsync(ps.data(), per_search.p, n * 4, cudaMemcpyDeviceToHost, s));
+      MG_CUDA(cudaStreamSynchronize(s));
+      uint64_t sum = 0, mx = 0, cnt = 0;
+      for (uint64_t i = 0; i < n_work; ++i) {
+        uint32_t e = ps[tier == 0 ? i : todo[i]];
+        sum += e; mx = std::max<uint64_t>(mx, e); ++cnt;
+      }
+      fprintf(stderr, "[mg_dls] tier %d: expansions per search mean %.0f max %llu\n", tier, cnt ? (double)sum / cnt : 0.0,
+              (unsigned long long)mx);
     }
     MG_CUDA(cudaMemcpyAsync(res.data(), result.p, n, cudaMemcpyDeviceToHost, s));
     MG_CUDA(cudaStreamSynchronize(s));
@@ -192,7 +247,7 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
         return MG_EINTERNAL;
       }
     }
-    if (getenv("MCAAT_DLS_VERBOSE")) fprintf(stderr, "[mg_dls] tier %d (2^%u slots): %llu searches, %zu overflowed\n", tier,
+    if (verbose) fprintf(stderr, "[mg_dls] tier %d (2^%u slots): %llu searches, %zu overflowed\n", tier,
                                              A.log2cap, (unsigned long long)n_work, todo.size());
   }
   // --- exact bitmap tier for searches that overflowed the largest hash set
@@ -205,16 +260,17 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
       set_error("mg_dls: not enough device memory for the exact bitmap tier");
       return MG_ENOMEM;
     }
-    DevBuf maps_b, sn2, sd2;
+    DevBuf maps_b, sn2, sd2, sa2;
     MG_TRY(maps_b.alloc(maps * words * 4));
     MG_TRY(todo_b.alloc(todo.size() * 4));
     MG_TRY(sn2.alloc(maps * A.stk_cap * 4));
     MG_TRY(sd2.alloc(maps * A.stk_cap * 2));
+    MG_TRY(sa2.alloc(maps * A.stk_cap * 8));
     MG_CUDA(cudaMemcpyAsync(todo_b.p, todo.data(), todo.size() * 4, cudaMemcpyHostToDevice, s));
     {
       TimedScope ts(g, T_DLS, 0);
       MG_LAUNCH(k_dls_big, (unsigned)maps, 256, 0, s, g->adj.as<uint64_t>(), ids_dev, todo_b.as<uint32_t>(),
-                (uint32_t)todo.size(), limit, maps_b.as<uint32_t>(), words, sn2.as<uint32_t>(), sd2.as<uint16_t>(),
+                (uint32_t)todo.size(), limit, maps_b.as<uint32_t>(), words, sn2.as<uint32_t>(), sd2.as<uint16_t>(), sa2.as<uint64_t>(),
                 A.stk_cap, result.as<int8_t>(), exp_dev);
     }
     MG_CUDA(cudaMemcpyAsync(res.data(), result.p, n, cudaMemcpyDeviceToHost, s));

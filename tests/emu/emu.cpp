@@ -250,7 +250,8 @@ int emu_dls(Emu *e, uint64_t start, int limit, int log2cap, uint64_t *expansions
   std::vector<uint16_t> sd(4 * limit + 8);
   U32HashSet s{tab.data(), (uint32_t)log2cap, 0, (1u << log2cap) / 2};
   uint32_t exp = 0;
-  int r = dls_run(e->adj.data(), (uint32_t)start, limit, s, sn.data(), sd.data(), (uint32_t)sn.size(), exp);
+  std::vector<uint64_t> sa(sn.size());
+  int r = dls_run(e->adj.data(), (uint32_t)start, limit, s, sn.data(), sd.data(), sa.data(), (uint32_t)sn.size(), exp);
   if (expansions) *expansions += exp;
   return r;
 }
@@ -259,7 +260,8 @@ int emu_dls_bitmap(Emu *e, uint64_t start, int limit) {
   std::vector<uint16_t> sd(4 * limit + 8);
   BitSet s{bits.data()};
   uint32_t exp = 0;
-  return dls_run(e->adj.data(), (uint32_t)start, limit, s, sn.data(), sd.data(), (uint32_t)sn.size(), exp);
+  std::vector<uint64_t> sa(sn.size());
+  return dls_run(e->adj.data(), (uint32_t)start, limit, s, sn.data(), sd.data(), sa.data(), (uint32_t)sn.size(), exp);
 }
 
 // 0 = hash-map search (enum_run) only, 1 = extracted-ball search with enum_run as overflow fallback
