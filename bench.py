@@ -242,6 +242,8 @@ def main():
     ap.add_argument("--sample", default="c2_sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--ingest-check", action="store_true",
+                    help="also time mg_graph_create_from_files on the sample workload written in MEGAHIT's on-disk format")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -365,6 +367,23 @@ def main():
         e2e = dict(value=st2["n_starts"] / dt, unit=UNIT, h2d_bytes_per_step=int(h2d),
                    d2h_bytes_per_step=int(inv.nbytes + rb), ms_per_step=dt * 1e3)
 
+    ingest = None
+    if rank == 0 and args.ingest_check:  # on-disk SDBG decoded on the device
+        gs, _ = S.make_workload(args.sample, device="cuda", want_labels=True)
+        tmp = tempfile.mkdtemp(prefix="mcaat_ingest_")
+        prefix = os.path.join(tmp, "graph")
+        S.write_megahit_files(gs, prefix)
+        nbytes = sum(os.path.getsize(os.path.join(tmp, f)) for f in os.listdir(tmp))
+        ts_ = []
+        for _ in range(3):
+            torch.cuda.synchronize()
+            ta = time.perf_counter()
+            gi = DeviceGraph.from_files(prefix, device=local)
+            ts_.append(time.perf_counter() - ta)
+            n_i = gi.n
+            gi.close()
+        ingest = dict(workload=args.sample, n_items=int(n_i), file_bytes=int(nbytes), seconds=min(ts_),
+                      items_per_s=n_i / min(ts_), note="files in page cache; read + H2D + device decode + index build")
     if rank != 0:
         return
     # ---- roofline of the dominant kernel family (CUDA-event time accumulated inside the library)
@@ -415,6 +434,8 @@ def main():
         "roofline": roofline, "setup": {"generate_s": round(gen_s, 2), "nccl_broadcast_s": round(bcast_s, 4),
                                         "graph_device_bytes": g.device_bytes() if g.h else None},
     }
+    if ingest:
+        line["ingest"] = ingest
     if e2e:
         line["e2e"] = e2e
     if cpu:

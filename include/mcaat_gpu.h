@@ -68,6 +68,11 @@ typedef struct {
 /* Upload + build the device-resident succinct graph (replaces SDBG::LoadFromFile's index
  * construction, reference sdbg.h:26-61 and kmlib/kmrns.h:122-167). */
 int mg_graph_create(const mg_graph_desc *desc, mg_graph **out);
+/* Same graph straight from MEGAHIT's on-disk SDBG (<prefix>.sdbg_info + <prefix>.sdbg.<i>): the files are
+ * read into pinned memory and decoded ON THE DEVICE, bucket-parallel, into the resident layout — replaces
+ * SDBG::LoadFromFile / LoadSdbgRawContent (reference sdbg.h:26-61, sdbg_raw_content.cpp:18-96,
+ * sdbg_meta.cpp:50-75; record layout sdbg_item.h:14-24, sdbg_writer.cpp:25-58).  SURVEY 8(f) N2. */
+int mg_graph_create_from_files(const char *prefix, int device, mg_graph **out);
 void mg_graph_destroy(mg_graph *g);
 /* Restore the invalid bitmap to its state at creation and clear `visited` (lets one resident
  * graph be searched repeatedly with different parameters). */

@@ -19,7 +19,7 @@ MG_MEM_HOST, MG_MEM_DEVICE = 0, 1
 
 # every symbol include/mcaat_gpu.h declares (tests check that the library exports all of them)
 SYMBOLS = [
-    "mg_graph_create", "mg_graph_destroy", "mg_graph_reset", "mg_graph_size", "mg_graph_device_bytes",
+    "mg_graph_create", "mg_graph_create_from_files", "mg_graph_destroy", "mg_graph_reset", "mg_graph_size", "mg_graph_device_bytes",
     "mg_navigate", "mg_prune", "mg_invalid_readback", "mg_candidates", "mg_dls", "mg_select_starts",
     "mg_bucket_starts", "mg_starts_free", "mg_find_cycles", "mg_cycles_free", "mg_visited_readback",
     "mg_timers", "mg_timers_reset", "mg_step_begin", "mg_step_end", "mg_launch_count", "mg_free", "mg_last_error", "mg_version",
@@ -68,6 +68,7 @@ def lib():
                           "(python -c 'import __graft_entry__ as g; g.build()'); there is no CPU fallback")
         L = C.CDLL(LIB_PATH)
         L.mg_graph_create.argtypes = [C.POINTER(GraphDesc), C.POINTER(C.c_void_p)]
+        L.mg_graph_create_from_files.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]
         L.mg_graph_destroy.argtypes = [C.c_void_p]
         L.mg_graph_destroy.restype = None
         L.mg_graph_reset.argtypes = [C.c_void_p]
@@ -155,6 +156,17 @@ class DeviceGraph:
         self.n = d.n_items
         self.h = C.c_void_p()
         _check(lib().mg_graph_create(C.byref(d), C.byref(self.h)))
+
+    @classmethod
+    def from_files(cls, prefix, device=0):
+        """MEGAHIT's on-disk SDBG (<prefix>.sdbg_info, <prefix>.sdbg.<i>) decoded on the device
+        (mg_graph_create_from_files; replaces SDBG::LoadFromFile, reference sdbg.h:26-61)."""
+        self = cls.__new__(cls)
+        self._keep = None
+        self.h = C.c_void_p()
+        _check(lib().mg_graph_create_from_files(str(prefix).encode(), int(device), C.byref(self.h)))
+        self.n = int(lib().mg_graph_size(self.h))
+        return self
 
     def close(self):
         if getattr(self, "h", None):

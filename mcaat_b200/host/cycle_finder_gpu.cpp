@@ -93,10 +93,30 @@ mg_graph *upload(SDBG &sdbg) {
   return g;
 }
 
-GpuState &state_of(const CycleFinder *cf, SDBG &sdbg) {
+// Opt-in fast path (env MCAAT_GPU_INGEST_FILES=1): the graph files the host loaded the SDBG from are
+// decoded on the device (mg_graph_create_from_files) instead of extracting every item through the
+// getters.  `prefix` = settings.graph_folder, which the reference's main has turned into the file
+// prefix before constructing CycleFinder (reference src/main.cpp:522-530).  Only valid while the host
+// has not invalidated anything since SDBG::LoadFromFile — true for the reference's pipeline.
+mg_graph *ingest(const std::string &prefix, SDBG &sdbg) {
+  const char *dev = std::getenv("MCAAT_GPU_DEVICE");
+  mg_graph *g = nullptr;
+  int rc = mg_graph_create_from_files(prefix.c_str(), dev ? std::atoi(dev) : 0, &g);
+  if (rc != MG_OK) fail("mg_graph_create_from_files", rc);
+  if (mg_graph_size(g) != (uint64_t)sdbg.size()) {
+    mg_graph_destroy(g);
+    throw std::runtime_error("libmcaat_gpu: graph files at '" + prefix + "' do not match the loaded SDBG");
+  }
+  return g;
+}
+
+GpuState &state_of(const CycleFinder *cf, SDBG &sdbg, const std::string &prefix = std::string()) {
   std::lock_guard<std::mutex> lk(g_mu);
   GpuState &s = g_state[cf];
-  if (!s.g) s.g = upload(sdbg);
+  if (!s.g) {
+    const char *fast = std::getenv("MCAAT_GPU_INGEST_FILES");
+    s.g = (fast && *fast == '1' && !prefix.empty()) ? ingest(prefix, sdbg) : upload(sdbg);
+  }
   return s;
 }
 
@@ -150,7 +170,7 @@ CycleFinder::~CycleFinder() {
 // ---- reference :346-357.  Evaluated on the CURRENT graph state, like the reference.
 vector<uint64_t> CycleFinder::CollectTips() {
   SDBG &sdbg = *this->settings.sdbg;
-  GpuState &s = state_of(this, sdbg);
+  GpuState &s = state_of(this, sdbg, this->settings.graph_folder);
   const uint64_t n = sdbg.size();
   std::vector<int8_t> od(n);
   int rc = mg_navigate(s.g, 0, n, od.data(), nullptr, nullptr, nullptr, nullptr);
@@ -166,11 +186,11 @@ vector<uint64_t> CycleFinder::CollectTips() {
 // the per-tip and per-phase entry points run that pipeline once and are idempotent afterwards.
 void CycleFinder::RecursiveReduction(uint64_t) {
   SDBG &sdbg = *this->settings.sdbg;
-  ensure_pruned(state_of(this, sdbg), sdbg, nullptr);
+  ensure_pruned(state_of(this, sdbg, this->settings.graph_folder), sdbg, nullptr);
 }
 void CycleFinder::InvalidateMultiplicityOneNodes() {
   SDBG &sdbg = *this->settings.sdbg;
-  GpuState &s = state_of(this, sdbg);
+  GpuState &s = state_of(this, sdbg, this->settings.graph_folder);
   bool first = !s.pruned;
   mg_prune_stats st{};
   ensure_pruned(s, sdbg, &st);
@@ -181,7 +201,7 @@ void CycleFinder::InvalidateMultiplicityOneNodes() {
 // ---- reference :387-427
 size_t CycleFinder::ChunkStartNodes(map<int, vector<uint64_t>, greater<int>> &start_nodes_chunked) {
   SDBG &sdbg = *this->settings.sdbg;
-  GpuState &s = state_of(this, sdbg);
+  GpuState &s = state_of(this, sdbg, this->settings.graph_folder);
   ensure_pruned(s, sdbg, nullptr);
   mg_starts st{};
   int rc = mg_select_starts(s.g, this->settings.cycle_finder_settings.threshold_multiplicity,
@@ -204,7 +224,7 @@ size_t CycleFinder::ChunkStartNodes(map<int, vector<uint64_t>, greater<int>> &st
 bool CycleFinder::DepthLevelSearch(uint64_t start, uint64_t target, int limit, int &reached_depth) {
   if (start != target) throw std::runtime_error("DepthLevelSearch: only target == start is supported on the GPU path");
   SDBG &sdbg = *this->settings.sdbg;
-  GpuState &s = state_of(this, sdbg);
+  GpuState &s = state_of(this, sdbg, this->settings.graph_folder);
   ensure_pruned(s, sdbg, nullptr);
   uint8_t pass = 0;
   int rc = mg_dls(s.g, &start, 1, limit, &pass, nullptr);
@@ -223,7 +243,7 @@ static vector<vector<uint64_t>> cycles_of(const mg_cycles &c, uint64_t idx) {
 // ---- reference :231-243 (+ :140-225): one start node against the current `visited` state
 vector<vector<uint64_t>> CycleFinder::FindCycleUtil(uint64_t start_node) {
   SDBG &sdbg = *this->settings.sdbg;
-  GpuState &s = state_of(this, sdbg);
+  GpuState &s = state_of(this, sdbg, this->settings.graph_folder);
   ensure_pruned(s, sdbg, nullptr);
   mg_cycles c{};
   int rc = mg_find_cycles(s.g, &start_node, 1, this->settings.cycle_finder_settings.cycle_min_length,
@@ -244,7 +264,7 @@ vector<vector<uint64_t>> CycleFinder::FindCycle(uint64_t start_node, vector<uint
 // ---- reference :433-492
 int CycleFinder::FindApproximateCRISPRArrays() {
   SDBG &sdbg = *this->settings.sdbg;
-  GpuState &s = state_of(this, sdbg);
+  GpuState &s = state_of(this, sdbg, this->settings.graph_folder);
   const auto &cfs = this->settings.cycle_finder_settings;
   mg_prune_stats ps{};
   ensure_pruned(s, sdbg, &ps);

@@ -75,6 +75,7 @@ int main(int argc, char **argv) {
   SDBG g;
   g.LoadFromFile(argv[1]);
   s.sdbg = &g;
+  s.graph_folder = argv[1];  // the file prefix, as reference src/main.cpp:522-530 leaves it
   auto t1 = std::chrono::steady_clock::now();
   CycleFinder cf(s);
   auto t2 = std::chrono::steady_clock::now();

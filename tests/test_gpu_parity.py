@@ -135,8 +135,33 @@ def test_cpp_drop_in_cyclefinder_matches_reference_dump(tmp_path):
     if not os.path.exists(exe):
         pytest.skip("shim_cyclefinder not built (needs the reference headers at build time)")
     prefix = G.unpack_sdbg_files("tiny", str(tmp_path))
-    for thr, mn, mx in ((20, 27, 77), (10, 20, 100)):
-        out = str(tmp_path / f"shim_{thr}.dump")
-        subprocess.run([exe, prefix, out, "1", str(thr), str(mn), str(mx)], check=True, capture_output=True)
-        want = gzip.open(os.path.join(G.GOLD, f"tiny.t{thr}_{mn}_{mx}.dump.gz"), "rb").read()
-        assert open(out, "rb").read() == want
+    for ingest in ("0", "1"):  # graph through the SDBG getters / decoded on the device from the graph files
+        env = dict(os.environ, MCAAT_GPU_INGEST_FILES=ingest)
+        for thr, mn, mx in ((20, 27, 77), (10, 20, 100)):
+            out = str(tmp_path / f"shim_{thr}_{ingest}.dump")
+            subprocess.run([exe, prefix, out, "1", str(thr), str(mn), str(mx)], check=True, capture_output=True, env=env)
+            want = gzip.open(os.path.join(G.GOLD, f"tiny.t{thr}_{mn}_{mx}.dump.gz"), "rb").read()
+            assert open(out, "rb").read() == want
+
+
+def test_device_ingest_of_on_disk_sdbg(tmp_path):
+    """the reference's own graph files (built by its SDBGBuild, 4 part files) decoded on
+    the device give the same navigation tables and the same search result as the reference."""
+    prefix = G.unpack_sdbg_files("tiny", str(tmp_path))
+    g = DeviceGraph.from_files(prefix)
+    raw = G.load_graph_npz("tiny")
+    assert g.n == raw["w"].size
+    z = np.load(G.GOLD + "/tiny.nav.npz")
+    od, idg, o, i_, m = g.navigate()
+    assert np.array_equal(od, z["od"]) and np.array_equal(idg, z["id"])
+    assert np.array_equal(o.astype(np.int64), z["o"]) and np.array_equal(i_.astype(np.int64), z["i"])
+    assert np.array_equal(m, z["m"])
+    name, thr, mn, mx, dump = [c for c in G.cases() if c[0] == "tiny" and c[1] == 20][0]
+    assert O.same_run(O.parse_dump(dump), run_gpu(g, thr, mn, mx)) == []
+    with pytest.raises(gpu.MgError):
+        DeviceGraph.from_files(prefix + "_missing")
+    # truncated part file: the decoder must notice, not read past the end
+    with open(prefix + ".sdbg.3", "r+b") as f:
+        f.truncate(100)
+    with pytest.raises(gpu.MgError):
+        DeviceGraph.from_files(prefix)
