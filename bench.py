@@ -132,6 +132,7 @@ def hot_path_step(g, rank=0, world=1, dist=None, torch=None):
         print("[step wall ms] reset %.1f prune %.1f candidates %.1f dls %.1f bucket %.1f find_cycles %.1f" %
               tuple((b - a) * 1e3 for a, b in zip(tt, tt[1:])), file=sys.stderr)
     res_bytes = 8 * (sum(sum(p.size for p in paths) for _, paths in searched) + len(searched))
+    hot_path_step.last_cycles = searched
     stats = dict(st, n_candidates=int(cand.size), n_starts=int(starts.size), dls_expansions=int(exp), **cs)
     return stats, res_bytes
 
@@ -244,6 +245,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--ingest-check", action="store_true",
                     help="also time mg_graph_create_from_files on the sample workload written in MEGAHIT's on-disk format")
+    ap.add_argument("--regions-check", action="store_true",
+                    help="also time mg_keep_regions (SURVEY 8(f) N4, k = 128) on the cycles of the bench workload")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -384,6 +387,29 @@ def main():
             gi.close()
         ingest = dict(workload=args.sample, n_items=int(n_i), file_bytes=int(nbytes), seconds=min(ts_),
                       items_per_s=n_i / min(ts_), note="files in page cache; read + H2D + device decode + index build")
+    regions = None
+    if rank == 0 and args.regions_check:  # k-hop region extraction around the cycles, device resident
+        gr = DeviceGraph(graph, device=local)
+        hot_path_step(gr)
+        seeds = [p for _, ps in hot_path_step.last_cycles for p in ps]
+        seeds = np.concatenate(seeds).astype(np.uint64) if seeds else np.zeros(0, np.uint64)
+        inv_before = gr.invalid_words().copy()
+        ts_, st_r = [], None
+        for _ in range(3):
+            gr.timers_reset()
+            torch.cuda.synchronize()
+            ta = time.perf_counter()
+            st_r = gr.keep_regions(seeds, 128)
+            ts_.append((time.perf_counter() - ta, gr.timers().get("keep_regions", {}).get("ms")))
+            gr.reset()  # back to the loaded graph, then to the pruned state the stage starts from
+            gr.prune()
+        assert np.array_equal(gr.invalid_words(), inv_before)
+        gr.close()
+        best = min(ts_)
+        regions = dict(workload=args.workload, k=128, seed_ids=int(seeds.size), n_kept=st_r["n_kept"],
+                       n_invalidated=st_r["n_invalidated"], levels=st_r["levels"], wall_ms=best[0] * 1e3,
+                       device_ms=best[1], items_per_s=n_items / best[0],
+                       note="graph resident; wall includes the id upload and the counter read-backs")
     if rank != 0:
         return
     # ---- roofline of the dominant kernel family (CUDA-event time accumulated inside the library)
@@ -436,6 +462,8 @@ def main():
     }
     if ingest:
         line["ingest"] = ingest
+    if regions:
+        line["regions"] = regions
     if e2e:
         line["e2e"] = e2e
     if cpu:

@@ -102,6 +102,11 @@ int mg_prune(mg_graph *g, mg_prune_stats *stats);
 /* Current invalid bitmap -> host words ((n+63)/64 uint64), for write-back into the host SDBG
  * (reference SetInvalidEdge, sdbg.h:94). */
 int mg_invalid_readback(mg_graph *g, uint64_t *host_words);
+/* The other direction: ORs the host SDBG's invalid bits (!IsValidEdge, sdbg.h:88-92; (n+63)/64 uint64 words)
+ * into the device bitmap, so that a device graph kept resident across stages follows SetInvalidEdge calls the
+ * host made in between.  *n_new (may be NULL) = bits that were not set on the device.  When anything changed,
+ * mg_prune has to run again before mg_dls / mg_find_cycles. */
+int mg_invalid_merge(mg_graph *g, const uint64_t *host_words, uint64_t *n_new);
 
 /* Candidate start nodes: valid AND indegree >= 2 AND multiplicity > threshold AND no self-loop
  * incoming edge (reference src/cycle_finder.cpp:398-408), ascending ids.  *ids is library
@@ -156,6 +161,25 @@ void mg_cycles_free(mg_cycles *c);
 /* Multi-GPU support: mark nodes visited / read the visited bitmap, so that ranks that ran
  * disjoint parts of the start list can exchange their commits. */
 int mg_visited_readback(mg_graph *g, uint64_t *host_words);
+
+/* ---- region extraction around the cycles ------------------------------------
+ * Replaces keep_crispr_regions_extended_by_k(sdbg, k, cycles), reference src/spacer_ordering.cpp:78-139
+ * (declared include/spacer_ordering.h:127-131; called through get_crispr_regions_extended_by_k,
+ * src/spacer_ordering.cpp:177-184, with k = read length in nodes, src/main_run_and_debug.cpp:40-41).
+ * `ids` = the node ids of all cycles, flattened (duplicates and already-invalid ids allowed, as in the
+ * reference's set); the set grows for k rounds by the valid in-/out-neighbours of its valid members, then every
+ * valid item outside it is invalidated on the device graph (read the bitmap back with mg_invalid_readback).
+ * MG_EINVAL when an id is >= mg_graph_size (the reference would read out of bounds).  After a call that
+ * invalidated something, mg_prune has to run again before mg_dls / mg_find_cycles (their navigation cache
+ * describes the graph before the call). */
+typedef struct {
+  uint64_t n_seed_ids;    /* ids passed in */
+  uint64_t n_added;       /* members found by the expansion (not counting the seeds) */
+  uint64_t levels;        /* rounds executed (<= k; stops once a batch of rounds adds nothing) */
+  uint64_t n_invalidated; /* valid items outside the set, now invalid */
+  uint64_t n_kept;        /* valid items afterwards */
+} mg_region_stats;
+int mg_keep_regions(mg_graph *g, const uint64_t *ids, uint64_t n_ids, uint64_t k, mg_region_stats *stats);
 
 /* Device timers: CUDA-event time (ms) and launch count accumulated per kernel family since the
  * last mg_timers_reset().  names[i] are static strings.  Returns the number of entries written

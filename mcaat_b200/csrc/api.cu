@@ -11,7 +11,8 @@ static thread_local char g_err[512] = "";
 unsigned long long g_launches = 0;
 thread_local cudaStream_t g_alloc_stream = nullptr;
 const char *kTimerNames[T_COUNT] = {"build_index", "collect_tips", "invalidate_mult1", "peel",      "nav_cache",
-                                    "candidates",  "dls",          "enumerate",        "commit",    "navigate"};
+                                    "candidates",  "dls",          "enumerate",        "commit",    "navigate",
+                                    "keep_regions"};
 
 void set_error(const char *fmt, ...) {
   va_list ap;
@@ -167,6 +168,44 @@ int mg_invalid_readback(mg_graph *g, uint64_t *host_words) {
   MG_CUDA(cudaMemcpyAsync(host_words, tmp.p, (size_t)((g->view.n + 63) / 64) * 8, cudaMemcpyDeviceToHost, g->stream));
   MG_CUDA(cudaStreamSynchronize(g->stream));
   return MG_OK;
+}
+
+__global__ void k_inv_merge(uint64_t n, uint64_t n_words, const uint64_t *in, FBlock *fb, unsigned long long *changed) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_words) return;
+  uint64_t first = i * 64, mask = first + 64 <= n ? ~0ull : (~0ull >> (64 - (n - first)));
+  uint64_t *p = &fb[i >> 2].inv[i & 3], old = *p, add = in[i] & mask & ~old;
+  if (add) {
+    *p = old | add;
+    atomicAdd(changed, (unsigned long long)__popcll(add));
+  }
+}
+
+int mg_invalid_merge(mg_graph *g, const uint64_t *host_words, uint64_t *n_new) {
+  MG_CHECK_HANDLE(g);
+  if (!host_words) return MG_EINVAL;
+  if (n_new) *n_new = 0;
+  const uint64_t n = g->view.n, nw = (n + 63) / 64;
+  if (!nw) return MG_OK;
+  DevBuf tmp;
+  MG_TRY(tmp.alloc(nw * 8 + 8));
+  MG_CUDA(cudaMemcpyAsync(tmp.p, host_words, nw * 8, cudaMemcpyHostToDevice, g->stream));
+  unsigned long long *cnt = tmp.as<unsigned long long>() + nw, h = 0;
+  MG_CUDA(cudaMemsetAsync(cnt, 0, 8, g->stream));
+  MG_LAUNCH(k_inv_merge, (unsigned)((nw + 255) / 256), 256, 0, g->stream, n, nw, tmp.as<uint64_t>(), g->fb.as<FBlock>(), cnt);
+  MG_CUDA(cudaMemcpyAsync(&h, cnt, 8, cudaMemcpyDeviceToHost, g->stream));
+  MG_CUDA(cudaStreamSynchronize(g->stream));
+  if (h) g->pruned = false;  // the navigation cache describes the graph before the merge
+  if (n_new) *n_new = h;
+  return MG_OK;
+}
+
+int mg_keep_regions(mg_graph *g, const uint64_t *ids, uint64_t n_ids, uint64_t k, mg_region_stats *stats) {
+  MG_CHECK_HANDLE(g);
+  if (n_ids && !ids) return MG_EINVAL;
+  DevBuf dev;
+  MG_TRY(upload_ids(g, ids, n_ids, dev));
+  return run_keep_regions(g, dev.as<uint32_t>(), n_ids, k, stats);
 }
 
 int mg_visited_readback(mg_graph *g, uint64_t *host_words) {

@@ -90,6 +90,7 @@ enum TimerId {
   T_ENUM,          // FindCycle searches
   T_COMMIT,        // ordered commit + gather
   T_NAV,           // mg_navigate (diagnostic)
+  T_REGION,        // mg_keep_regions
   T_COUNT
 };
 extern const char *kTimerNames[T_COUNT];
@@ -171,6 +172,8 @@ int run_candidates(mg_graph *g, uint64_t thr, DevBuf &ids, uint64_t *n);
 int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t *pass_host, uint64_t *expansions);
 int bucket_on_host(const std::vector<uint64_t> &ids, const std::vector<uint16_t> &mult, mg_starts *out);
 int gather_mult(mg_graph *g, const uint32_t *ids_dev, uint64_t n, std::vector<uint16_t> &out);
+// regions.cu
+int run_keep_regions(mg_graph *g, const uint32_t *ids_dev, uint64_t n_ids, uint64_t k, mg_region_stats *st);
 // enumerate.cu
 int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len, int max_len, mg_cycles *out);
 

@@ -754,4 +754,52 @@ done:
   R.expansions = expansions;
 }
 
+// ------------------------------------------------------------------ region extraction
+// keep_crispr_regions_extended_by_k, src/spacer_ordering.cpp:78-139: the set of cycle node ids grows for k
+// rounds by the in- and out-neighbours (IncomingEdges/OutgoingEdges, i.e. valid items) of its VALID members;
+// every valid item outside the final set is invalidated.  Members found in round r contribute neighbours from
+// round r+1 on and re-scanning older members adds nothing, so round r only has to expand the members that
+// were new in round r-1: a level-synchronous breadth-first search over bitmaps.
+//   member: the set;  cur: members new in the previous round (word `wi` is expanded here);  next: members new
+//   in this round.  Returns the number of members added.
+MG_HD unsigned region_expand_word(const GraphView &g, uint32_t *member, const uint32_t *cur, uint32_t *next,
+                                  uint32_t wi) {
+  uint32_t word = cur[wi];
+  unsigned added = 0;
+  while (word) {
+#if defined(__CUDA_ARCH__)
+    int b = __ffs(word) - 1;
+#else
+    int b = __builtin_ctz(word);
+#endif
+    word &= word - 1;
+    uint32_t v = wi * 32u + (uint32_t)b, nb[4];
+    if (get_inv(g, v)) continue;  // :94-96 (only a seed id can be invalid)
+    int d = incoming(g, v, nb);   // :98-109
+    for (int i = 0; i < d && i < 4; ++i)
+      if (bm_set_atomic(member, nb[i])) { bm_set_atomic(next, nb[i]); ++added; }
+    d = outgoing(g, v, nb);       // :111-122
+    for (int i = 0; i < d && i < 4; ++i)
+      if (bm_set_atomic(member, nb[i])) { bm_set_atomic(next, nb[i]); ++added; }
+  }
+  return added;
+}
+// :131-138 for the 64 items of invalid-bitmap word `wi` (word j of FBlock b holds items 256 b + 64 j ...).
+// Returns the number of items invalidated; *kept += items still valid.
+MG_HD unsigned region_keep_word(const GraphView &g, const uint32_t *member, uint64_t wi, unsigned *kept) {
+  uint64_t *p = &g.fb[wi >> 2].inv[wi & 3];
+  uint64_t inv = *p;
+  uint64_t first = wi * 64, in_range = ~0ull;
+  if (first + 64 > g.n) in_range = g.n > first ? (~0ull >> (64 - (g.n - first))) : 0;
+  uint64_t mem = 0;
+  if (first < g.n) {
+    mem = member[wi * 2];
+    if (first + 32 < g.n) mem |= (uint64_t)member[wi * 2 + 1] << 32;
+  }
+  uint64_t drop = ~inv & ~mem & in_range;
+  if (drop) *p = inv | drop;
+  *kept += (unsigned)popc64(~inv & mem & in_range);
+  return (unsigned)popc64(drop);
+}
+
 }  // namespace mg

@@ -22,8 +22,13 @@ SYMBOLS = [
     "mg_graph_create", "mg_graph_create_from_files", "mg_graph_destroy", "mg_graph_reset", "mg_graph_size", "mg_graph_device_bytes",
     "mg_navigate", "mg_prune", "mg_invalid_readback", "mg_candidates", "mg_dls", "mg_select_starts",
     "mg_bucket_starts", "mg_starts_free", "mg_find_cycles", "mg_cycles_free", "mg_visited_readback",
+    "mg_keep_regions", "mg_invalid_merge",
     "mg_timers", "mg_timers_reset", "mg_step_begin", "mg_step_end", "mg_launch_count", "mg_free", "mg_last_error", "mg_version",
 ]
+
+
+class RegionStats(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("n_seed_ids", "n_added", "levels", "n_invalidated", "n_kept")]
 
 
 class MgError(RuntimeError):
@@ -89,6 +94,8 @@ def lib():
         L.mg_find_cycles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.POINTER(Cycles)]
         L.mg_cycles_free.argtypes = [C.POINTER(Cycles)]
         L.mg_cycles_free.restype = None
+        L.mg_invalid_merge.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
+        L.mg_keep_regions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(RegionStats)]
         L.mg_timers.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.mg_timers_reset.argtypes = [C.c_void_p]
         L.mg_timers_reset.restype = None
@@ -196,6 +203,15 @@ class DeviceGraph:
         _check(lib().mg_invalid_readback(self.h, words.ctypes.data))
         return words
 
+    def merge_invalid(self, invalid):
+        """OR a host invalid array (bool per item) into the device bitmap; returns the number of new bits."""
+        bits = np.packbits(np.asarray(invalid, bool).astype(np.uint8), bitorder="little")
+        words = np.zeros((self.n + 63) // 64 * 8, np.uint8)
+        words[:bits.size] = bits
+        new = C.c_uint64(0)
+        _check(lib().mg_invalid_merge(self.h, words.ctypes.data, C.byref(new)))
+        return int(new.value)
+
     def visited(self):
         words = np.zeros((self.n + 63) // 64, np.uint64)
         _check(lib().mg_visited_readback(self.h, words.ctypes.data))
@@ -226,6 +242,14 @@ class DeviceGraph:
         out = _np(ids, n.value)
         lib().mg_free(ids)
         return out
+
+    def keep_regions(self, ids, k):
+        """keep_crispr_regions_extended_by_k (reference src/spacer_ordering.cpp:78-139) on the device graph:
+        ids = flattened cycle node ids, k = rounds of neighbourhood growth; returns the stats dict."""
+        ids = np.ascontiguousarray(ids, np.uint64)
+        st = RegionStats()
+        _check(lib().mg_keep_regions(self.h, ids.ctypes.data, ids.size, int(k), C.byref(st)))
+        return {k_: int(getattr(st, k_)) for k_, _ in RegionStats._fields_}
 
     def dls(self, ids, limit):
         ids = np.ascontiguousarray(ids, np.uint64)

@@ -21,6 +21,7 @@
 
 #include "cycle_finder.h"  // the reference's header
 #include "mcaat_gpu.h"
+#include "gpu_bridge.h"
 
 namespace {
 
@@ -28,14 +29,31 @@ struct GpuState {
   mg_graph *g = nullptr;
   bool pruned = false;
   mg_prune_stats stats{};
+  const SDBG *sdbg = nullptr;
 };
 std::mutex g_mu;
 std::unordered_map<const CycleFinder *, GpuState> g_state;  // the header has no room for a handle
+
+}  // namespace
+
+namespace mcaat_gpu_bridge {
 
 [[noreturn]] void fail(const char *what, int rc) {
   throw std::runtime_error(std::string("libmcaat_gpu: ") + what + " failed (" + std::to_string(rc) +
                            "): " + mg_last_error());
 }
+
+mg_graph *resident_graph(const SDBG *sdbg) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (auto &kv : g_state)
+    if (kv.second.sdbg == sdbg && kv.second.g) return kv.second.g;
+  return nullptr;
+}
+
+}  // namespace mcaat_gpu_bridge
+
+namespace {
+using mcaat_gpu_bridge::fail;
 
 // f_[0..5] (reference sdbg.h:36-50) is private; LastCharOf (sdbg.h:79-86, public) is monotone in
 // its argument, so f_[i] = the smallest x with LastCharOf(x) >= i.
@@ -53,6 +71,9 @@ void recover_f(const SDBG &sdbg, int64_t f[6]) {
   }
 }
 
+}  // namespace
+
+namespace mcaat_gpu_bridge {
 // Extract MEGAHIT's arrays through the public getters (reference sdbg.h:63-105) and upload them.
 mg_graph *upload(SDBG &sdbg) {
   const uint64_t n = sdbg.size();
@@ -92,6 +113,10 @@ mg_graph *upload(SDBG &sdbg) {
   if (rc != MG_OK) fail("mg_graph_create", rc);
   return g;
 }
+}  // namespace mcaat_gpu_bridge
+
+namespace {
+using mcaat_gpu_bridge::upload;
 
 // Opt-in fast path (env MCAAT_GPU_INGEST_FILES=1): the graph files the host loaded the SDBG from are
 // decoded on the device (mg_graph_create_from_files) instead of extracting every item through the
@@ -116,10 +141,14 @@ GpuState &state_of(const CycleFinder *cf, SDBG &sdbg, const std::string &prefix 
   if (!s.g) {
     const char *fast = std::getenv("MCAAT_GPU_INGEST_FILES");
     s.g = (fast && *fast == '1' && !prefix.empty()) ? ingest(prefix, sdbg) : upload(sdbg);
+    s.sdbg = &sdbg;
   }
   return s;
 }
 
+}  // namespace
+
+namespace mcaat_gpu_bridge {
 // invalid bits the GPU set -> host SDBG (reference SetInvalidEdge, sdbg.h:94)
 void write_back_invalid(mg_graph *g, SDBG &sdbg) {
   const uint64_t n = sdbg.size();
@@ -137,6 +166,10 @@ void write_back_invalid(mg_graph *g, SDBG &sdbg) {
     }
   }
 }
+}  // namespace mcaat_gpu_bridge
+
+namespace {
+using mcaat_gpu_bridge::write_back_invalid;
 
 void ensure_pruned(GpuState &s, SDBG &sdbg, mg_prune_stats *out) {
   if (!s.pruned) {

@@ -340,6 +340,45 @@ void orc_peel(orc_graph *g, const uint64_t *tips, uint64_t n_tips) {
   free(st.a);
 }
 
+/* ---------------------------------------------------------------- region extraction (N4) */
+/* spacer_ordering.cpp:78-139.  `in_set` is the unordered_set cycle_edges as a byte per item; `members` lists
+ * it.  Every round the reference scans ALL members (:93-125), collects neighbours into new_edges and
+ * inserts them afterwards (:127-129) — restated literally, members found in a round are scanned from the
+ * next round on.  Neighbours come from IncomingEdges/OutgoingEdges (:100-122), i.e. valid items only. */
+uint64_t orc_keep_regions(orc_graph *g, const uint64_t *ids, uint64_t n_ids, uint64_t k, uint64_t *n_kept) {
+  for (uint64_t i = 0; i < n_ids; ++i)
+    if (ids[i] >= g->n) return ~0ull;
+  uint8_t *in_set = calloc(g->n ? g->n : 1, 1);
+  vec64 members = {0, 0, 0};
+  for (uint64_t i = 0; i < n_ids; ++i)
+    if (!in_set[ids[i]]) { in_set[ids[i]] = 1; v_push(&members, ids[i]); }
+  for (uint64_t round = 0; round < k; ++round) {
+    vec64 fresh = {0, 0, 0};
+    for (uint64_t j = 0; j < members.n; ++j) {
+      uint64_t e = members.a[j], nb[4];
+      if (g->invalid[e]) continue;                                  /* :94-96 */
+      int d = orc_incoming(g, e, nb);                                /* :98-109 */
+      for (int i = 0; i < d && i < 4; ++i) v_push(&fresh, nb[i]);
+      d = orc_outgoing(g, e, nb);                                    /* :111-122 */
+      for (int i = 0; i < d && i < 4; ++i) v_push(&fresh, nb[i]);
+    }
+    uint64_t added = 0;
+    for (uint64_t j = 0; j < fresh.n; ++j)                           /* :127-129 */
+      if (!in_set[fresh.a[j]]) { in_set[fresh.a[j]] = 1; v_push(&members, fresh.a[j]); ++added; }
+    free(fresh.a);
+    if (!added) break; /* a round that adds nothing makes every later round a no-op */
+  }
+  uint64_t gone = 0, kept = 0;
+  for (uint64_t e = 0; e < g->n; ++e) {                              /* :131-138 */
+    if (g->invalid[e]) continue;
+    if (!in_set[e]) { g->invalid[e] = 1; ++gone; } else ++kept;
+  }
+  if (n_kept) *n_kept = kept;
+  free(in_set);
+  free(members.a);
+  return gone;
+}
+
 /* ---------------------------------------------------------------- DepthLevelSearch */
 /* cycle_finder.cpp:248-343 with target == start (the only call site, :411). */
 int orc_dls(const orc_graph *g, uint64_t start, int limit, uint64_t *expansions) {

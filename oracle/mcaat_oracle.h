@@ -101,6 +101,13 @@ void orc_cycles_free(orc_cycles *c);
 int orc_run(orc_graph *g, uint64_t threshold_multiplicity, int min_len, int max_len, orc_result *res);
 void orc_result_free(orc_result *res);
 
+/* SURVEY 8(f) N4 — keep_crispr_regions_extended_by_k (reference src/spacer_ordering.cpp:78-139): grow the set of
+ * cycle node ids by k rounds of "add every in- and out-neighbour of each VALID member", then invalidate every
+ * valid item outside the set.  Returns the number of items invalidated, or UINT64_MAX when an id is >= size
+ * (the reference would read out of bounds).  *n_kept (may be NULL) = valid items afterwards.
+ * Pinned against the compiled reference function: oracle/_ref/ref_regions, tests/golden/<case>.regions.npz. */
+uint64_t orc_keep_regions(orc_graph *g, const uint64_t *ids, uint64_t n_ids, uint64_t k, uint64_t *n_kept);
+
 /* libstdc++ std::unordered_set<uint64_t> iteration-order model used by FindCycle:
  * inserts ids[0..n) (n <= 8) into an empty set and writes the iteration order; returns the size. */
 int orc_uset_order(const uint64_t *ids, int n, uint64_t *order);

@@ -93,6 +93,8 @@ def lib():
         L.orc_run.restype = C.c_int
         L.orc_run.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p]
         L.orc_result_free.argtypes = [C.c_void_p]
+        L.orc_keep_regions.restype = C.c_uint64
+        L.orc_keep_regions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
         L.orc_uset_order.restype = C.c_int
         L.orc_uset_order.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         _lib = L
@@ -214,6 +216,15 @@ class OracleGraph:
         lib().orc_cycles_free(C.byref(c))
         return paths, info
 
+    def keep_regions(self, ids, k):
+        """reference keep_crispr_regions_extended_by_k (src/spacer_ordering.cpp:78-139); (invalidated, kept)"""
+        ids = np.ascontiguousarray(ids, dtype=np.uint64)
+        kept = C.c_uint64(0)
+        gone = lib().orc_keep_regions(self.h, ids.ctypes.data, ids.size, k, C.byref(kept))
+        if gone == 2**64 - 1:
+            raise ValueError("node id out of range")
+        return int(gone), int(kept.value)
+
     def run(self, thr=20, min_len=27, max_len=77):
         r = OrcResult()
         lib().orc_run(self.h, thr, min_len, max_len, C.byref(r))
@@ -306,6 +317,22 @@ def same_run(a, b):
 def ref_binary(name):
     p = os.path.join(REF_DIR, name)
     return p if os.path.exists(p) else None
+
+
+def run_reference_regions(prefix, out_path, k, *, cycles=None, nodes_file=None):
+    """Run the compiled UNMODIFIED keep_crispr_regions_extended_by_k (oracle/_ref/ref_regions); returns the
+    invalid bitmap (bool per item) after the call.  cycles=(thr,min,max): seeds = all cycles the reference
+    CycleFinder finds; nodes_file: seeds = the u64 ids in that file, graph as loaded."""
+    exe = ref_binary("ref_regions")
+    if exe is None:
+        raise FileNotFoundError("oracle/_ref/ref_regions not built")
+    tail = ["cycles"] + [str(x) for x in cycles] if cycles is not None else ["nodes", nodes_file]
+    subprocess.run([exe, prefix, out_path, str(k)] + tail, check=True, capture_output=True)
+    raw = open(out_path, "rb").read()
+    assert raw[:8] == b"MCAATREG"
+    n, kk, n_seed, n_words = np.frombuffer(raw, "<u8", 4, 8)
+    words = np.frombuffer(raw, "<u8", int(n_words), 40)
+    return np.unpackbits(words.view(np.uint8), bitorder="little")[:int(n)].astype(bool)
 
 
 def run_reference(prefix, dump_path, threads=1, thr=20, min_len=27, max_len=77):

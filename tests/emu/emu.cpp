@@ -236,6 +236,35 @@ void emu_invalid(Emu *e, uint8_t *out) {
   for (uint64_t i = 0; i < e->v.n; ++i) out[i] = get_inv(e->v, (uint32_t)i);
 }
 
+// regions.cu's host loop with the same per-word device functions; `reverse` visits the words of each level
+// from the top, a different scheduling that must give the same set.  st = {added, levels, invalidated, kept}
+void emu_keep_regions(Emu *e, const uint64_t *ids, uint64_t n_ids, uint64_t k, int reverse, uint64_t *st) {
+  const uint64_t n = e->v.n, n_words64 = (n + 63) / 64, n_words = n_words64 * 2;
+  std::vector<uint32_t> member(n_words + 4, 0), cur(n_words + 4, 0), next(n_words + 4, 0);
+  for (uint64_t i = 0; i < n_ids; ++i)
+    if (bm_set_atomic(member.data(), (uint32_t)ids[i])) bm_set_atomic(cur.data(), (uint32_t)ids[i]);
+  uint64_t added = 0, level = 0;
+  for (; level < k; ++level) {
+    std::fill(next.begin(), next.end(), 0u);
+    uint64_t a = 0;
+    for (uint64_t j = 0; j < n_words; ++j) {
+      uint64_t w = reverse ? n_words - 1 - j : j;
+      if (cur[w]) a += region_expand_word(e->v, member.data(), cur.data(), next.data(), (uint32_t)w);
+    }
+    cur.swap(next);
+    added += a;
+    if (!a) { ++level; break; }
+  }
+  unsigned kept = 0;
+  uint64_t gone = 0, kept_total = 0;
+  for (uint64_t w = 0; w < n_words64; ++w) {
+    kept = 0;
+    gone += region_keep_word(e->v, member.data(), w, &kept);
+    kept_total += kept;
+  }
+  st[0] = added; st[1] = level; st[2] = gone; st[3] = kept_total;
+}
+
 uint64_t emu_candidates(Emu *e, uint64_t thr, uint64_t *ids) {
   uint64_t c = 0;
   for (uint64_t i = 0; i < e->v.n; ++i)

@@ -31,6 +31,7 @@ def lib():
         L.emu_prune.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         L.emu_invalid.argtypes = [C.c_void_p, C.c_void_p]
         L.emu_candidates.restype = C.c_uint64
+        L.emu_keep_regions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]
         L.emu_candidates.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
         L.emu_bucket.restype = C.c_int
         L.emu_bucket.argtypes = [C.c_void_p, C.c_uint64]
@@ -87,6 +88,12 @@ class EmuGraph:
         out = np.empty(self.n, np.uint8)
         lib().emu_invalid(self.h, out.ctypes.data)
         return out.astype(bool)
+
+    def keep_regions(self, ids, k, reverse=False):
+        ids = np.ascontiguousarray(ids, np.uint64)
+        st = np.zeros(4, np.uint64)
+        lib().emu_keep_regions(self.h, ids.ctypes.data, ids.size, int(k), int(reverse), st.ctypes.data)
+        return dict(zip(("n_added", "levels", "n_invalidated", "n_kept"), map(int, st)))
 
     def candidates(self, thr):
         ids = np.empty(self.n, np.uint64)

@@ -32,6 +32,41 @@ def cases():
     return out
 
 
+def region_cases():
+    """[(name, key, params or None, k)] for every bitmap in tests/golden/<name>.regions.npz (made by
+    tools/make_golden.py from the UNMODIFIED reference keep_crispr_regions_extended_by_k):
+    params=(thr,min,max): graph state and seed ids = that reference run's pruned graph and all its cycles;
+    params=None: graph as loaded, seed ids = the file's `seeds` array."""
+    out = []
+    for p in sorted(glob.glob(os.path.join(GOLD, "*.regions.npz"))):
+        name = os.path.basename(p)[:-len(".regions.npz")]
+        for key in np.load(p).files:
+            m = re.match(r"cyc_t(\d+)_(\d+)_(\d+)_k(\d+)$", key)
+            if m:
+                out.append((name, key, tuple(int(m.group(i)) for i in (1, 2, 3)), int(m.group(4))))
+            m = re.match(r"nodes_k(\d+)$", key)
+            if m:
+                out.append((name, key, None, int(m.group(1))))
+    return out
+
+
+def region_expected(name, key, n):
+    z = np.load(os.path.join(GOLD, f"{name}.regions.npz"))
+    return np.unpackbits(z[key], bitorder="little")[:n].astype(bool)
+
+
+def region_seeds(name, params):
+    """seed ids of a region case: all cycle nodes of the reference dump, flattened in `results` iteration order
+    like cycles_map_to_cycles (reference src/tmp_utils.cpp:26-38) — or the stored random ids."""
+    if params is None:
+        return np.load(os.path.join(GOLD, f"{name}.regions.npz"))["seeds"].astype(np.uint64)
+    import oracle_py as O
+    thr, mn, mx = params
+    ref = O.parse_dump(os.path.join(GOLD, f"{name}.t{thr}_{mn}_{mx}.dump.gz"))
+    paths = [p for _, ps in ref.searched for p in ps]
+    return np.concatenate(paths).astype(np.uint64) if paths else np.zeros(0, np.uint64)
+
+
 def unpack_sdbg_files(name, dst):
     """gunzip tests/golden/<name>.sdbg/* into dst; returns the MEGAHIT file prefix."""
     src = os.path.join(GOLD, f"{name}.sdbg")

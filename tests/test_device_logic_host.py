@@ -139,3 +139,22 @@ def test_synthetic_community_matches_oracle():
     got = run_emu(E.EmuGraph(g), 20, 27, 77, window=256, reverse_peel=True)
     assert O.same_run(want, got) == []
     assert got.stats["n_peeled"] > 1000
+
+
+@pytest.mark.parametrize("name,key,params,k", [c for c in G.region_cases() if c[0] in ("tiny", "biallelic")],
+                         ids=lambda v: str(v) if isinstance(v, (str, int)) else "")
+def test_region_extraction_matches_reference(name, key, params, k):
+    """region_expand_word / region_keep_word (the code k_region_level / k_region_keep run)
+    against the UNMODIFIED reference keep_crispr_regions_extended_by_k; both scan directions."""
+    seeds = G.region_seeds(name, params)
+    want = None
+    for reverse in (False, True):
+        g = emu(name)
+        if params is not None:
+            g.prune()
+        before = g.invalid()
+        st = g.keep_regions(seeds, k, reverse=reverse)
+        want = G.region_expected(name, key, g.n)
+        assert np.array_equal(g.invalid(), want)
+        assert st["n_invalidated"] == int((want & ~before).sum()) and st["n_kept"] == int((~want).sum())
+        assert st["levels"] <= max(k, 0)

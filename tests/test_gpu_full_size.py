@@ -70,6 +70,22 @@ def test_sample_workload_matches_oracle(thr, mn, mx):
     assert len(got.searched) > 50
 
 
+def test_sample_workload_regions_match_oracle():
+    """SURVEY 8(f) N4 at 11.3 M items: cycles of the run -> mg_keep_regions (k = 128, a 150-bp read at k = 23) against
+    the oracle's restatement of keep_crispr_regions_extended_by_k on the same pruned graph."""
+    g = workload("c2_sample")
+    w, last, tip = unpack(g)
+    og = O.OracleGraph.from_arrays(w, last, tip, g["mult"], g["f"], g["k"])
+    want = og.run(20, 27, 77)
+    seeds = np.concatenate([p for _, ps in want.searched for p in ps]).astype(np.uint64)
+    gone, kept = og.keep_regions(seeds, 128)
+    dg = DeviceGraph(g)
+    run(dg, 20, 27, 77)
+    st = dg.keep_regions(seeds, 128)
+    assert (st["n_invalidated"], st["n_kept"]) == (gone, kept) and kept > seeds.size // 4
+    assert np.array_equal(dg.invalid(), og.invalid())
+
+
 def test_full_size_properties():
     g = workload("c2")
     dg = DeviceGraph(g)
@@ -117,6 +133,16 @@ def test_full_size_properties():
     for u, v in edges[:400]:
         od, _, out, _, _ = dg.navigate(u, 1)
         assert v in [int(x) for x in out[0][:max(int(od[0]), 0)]]
+    # N4 at full size: region extraction keeps every valid cycle node, only valid items, is idempotent, and a
+    # second call with a larger k on the already reduced graph cannot resurrect anything
+    seeds = np.concatenate([p for _, ps in a.searched for p in ps]).astype(np.uint64)
+    st = dg.keep_regions(seeds, 128)
+    inv2 = dg.invalid()
+    assert not inv2[seeds.astype(np.int64)].any() and not (~inv2 & inv).any()
+    assert st["n_kept"] == int((~inv2).sum()) and st["n_invalidated"] == int((inv2 & ~inv).sum())
+    assert st["n_kept"] >= np.unique(seeds).size and st["levels"] <= 128
+    again = dg.keep_regions(seeds, 128)
+    assert again["n_invalidated"] == 0 and again["n_kept"] == st["n_kept"]
     # idempotence: reset + second run gives the identical result
     dg.reset()
     b = run(dg, thr, mn, mx)

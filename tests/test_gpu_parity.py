@@ -165,3 +165,101 @@ def test_device_ingest_of_on_disk_sdbg(tmp_path):
         f.truncate(100)
     with pytest.raises(gpu.MgError):
         DeviceGraph.from_files(prefix)
+
+
+# ------------------------------------------------------------------ region extraction
+@pytest.mark.parametrize("name,key,params,k", G.region_cases(), ids=lambda v: str(v) if isinstance(v, (str, int)) else "")
+def test_region_extraction_matches_reference(name, key, params, k):
+    """mg_keep_regions against the invalid bitmap the UNMODIFIED keep_crispr_regions_extended_by_k leaves
+    (reference src/spacer_ordering.cpp:78-139; tests/golden/<name>.regions.npz)."""
+    g = DeviceGraph(packed(name))
+    if params is not None:
+        g.prune()
+    before = g.invalid()
+    launches = gpu.launch_count()
+    st = g.keep_regions(G.region_seeds(name, params), k)
+    assert gpu.launch_count() > launches
+    want = G.region_expected(name, key, g.n)
+    assert np.array_equal(g.invalid(), want)
+    assert st["n_invalidated"] == int((want & ~before).sum()) and st["n_kept"] == int((~want).sum())
+    assert st["levels"] <= k
+
+
+def test_region_extraction_edge_cases():
+    g = DeviceGraph(packed("tiny"))
+    g.prune()
+    with pytest.raises(gpu.MgError):
+        g.keep_regions([g.n], 3)
+    valid = np.nonzero(~g.invalid())[0]
+    # k = 0: only the seeds themselves survive; duplicates and an invalid seed are harmless
+    bad = int(np.nonzero(g.invalid())[0][0])
+    seeds = np.array([valid[5], valid[5], valid[9], bad], np.uint64)
+    st = g.keep_regions(seeds, 0)
+    assert st["n_kept"] == 2 and st["levels"] == 0
+    assert set(np.nonzero(~g.invalid())[0]) == {int(valid[5]), int(valid[9])}
+    # the navigation cache is stale now: the search entries refuse until mg_prune has run again
+    with pytest.raises(gpu.MgError):
+        g.find_cycles([int(valid[5])], 27, 77)
+    # idempotent; no seeds at all -> nothing stays valid (the reference's loop invalidates every item)
+    assert g.keep_regions(seeds, 0)["n_invalidated"] == 0
+    st = g.keep_regions([], 5)
+    assert st["n_kept"] == 0 and g.invalid().all()
+
+
+def test_region_growth_is_monotone_and_saturates():
+    """size-independent properties: kept(k) grows with k, a huge k stops at the component closure, and the
+    closure is closed under valid in-/out-neighbours"""
+    raw = packed("repeatrich")
+    seeds = G.region_seeds("repeatrich", (20, 27, 77))
+    kept = []
+    for k in (0, 3, 20, 10**9):
+        g = DeviceGraph(raw)
+        g.prune()
+        st = g.keep_regions(seeds, k)
+        kept.append(st["n_kept"])
+        if k == 10**9:
+            assert st["levels"] < 100000
+            od, idg, o, i_, _ = g.navigate()
+            inv = g.invalid()
+            for v in np.nonzero(~inv)[0][::50]:
+                for x in list(o[v][:max(int(od[v]), 0)]) + list(i_[v][:max(int(idg[v]), 0)]):
+                    assert not inv[int(x)]
+    assert kept == sorted(kept) and kept[0] < kept[-1]
+
+
+def test_host_invalid_bits_merge_into_the_device_graph():
+    g = DeviceGraph(packed("tiny"))
+    inv = g.invalid()
+    extra = np.zeros(g.n, bool)
+    picks = np.nonzero(~inv)[0][[3, 77, 500, -1]]
+    extra[picks] = True
+    extra[np.nonzero(inv)[0][:10]] = True  # already invalid on the device: not counted
+    assert g.merge_invalid(extra) == picks.size
+    assert np.array_equal(g.invalid(), inv | extra)
+    assert g.merge_invalid(extra) == 0
+
+
+def test_cpp_drop_in_regions_match_reference(tmp_path):
+    """mcaat_b200/host/regions_gpu.cpp (the reference's signature) under the region harness main: the HOST
+    SDBG's invalid bitmap after the call equals what the unmodified reference function leaves — on the
+    device graph kept resident by the CycleFinder drop-in (`cycles`) and on a fresh upload (`nodes`)."""
+    import os
+    import subprocess
+    exe = os.path.join(gpu.ROOT, "mcaat_b200", "host", "_build", "shim_regions")
+    if not os.path.exists(exe):
+        pytest.skip("shim_regions not built (needs the reference headers at build time)")
+    prefix = G.unpack_sdbg_files("tiny", str(tmp_path))
+    n = G.load_graph_npz("tiny")["w"].size
+    seeds_file = str(tmp_path / "seeds.u64")
+    G.region_seeds("tiny", None).astype("<u8").tofile(seeds_file)
+    runs = [("cyc_t20_27_77_k7", ["7", "cycles", "20", "27", "77"]),
+            ("cyc_t20_27_77_k150", ["150", "cycles", "20", "27", "77"]),
+            ("nodes_k30", ["30", "nodes", seeds_file])]
+    for key, tail in runs:
+        out = str(tmp_path / (key + ".reg"))
+        subprocess.run([exe, prefix, out] + tail, check=True, capture_output=True)
+        raw = open(out, "rb").read()
+        assert raw[:8] == b"MCAATREG"
+        words = np.frombuffer(raw, "<u8", (n + 63) // 64, 40)
+        got = np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool)
+        assert np.array_equal(got, G.region_expected("tiny", key, n)), key

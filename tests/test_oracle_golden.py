@@ -33,6 +33,27 @@ def test_oracle_navigation_matches_reference_api():
     assert np.array_equal(g.raw()["mult"], z["m"])
 
 
+@pytest.mark.parametrize("name,key,params,k", G.region_cases(), ids=lambda v: str(v) if isinstance(v, (str, int)) else "")
+def test_oracle_keep_regions_matches_reference(name, key, params, k):
+    """orc_keep_regions against the UNMODIFIED keep_crispr_regions_extended_by_k
+    (reference src/spacer_ordering.cpp:78-139, oracle/_ref/ref_regions)."""
+    g = graph(name)
+    if params is not None:
+        g.run(*params)
+    before = g.invalid()
+    gone, kept = g.keep_regions(G.region_seeds(name, params), k)
+    want = G.region_expected(name, key, g.n)
+    got = g.invalid()
+    assert np.array_equal(got, want)
+    assert gone == int((want & ~before).sum()) and kept == int((~want).sum())
+
+
+def test_oracle_keep_regions_rejects_bad_ids():
+    g = graph("tiny")
+    with pytest.raises(ValueError):
+        g.keep_regions([g.n], 3)
+
+
 def test_file_loader_matches_raw_arrays(tmp_path):
     prefix = G.unpack_sdbg_files("tiny", str(tmp_path))
     a = O.OracleGraph.load(prefix).raw()

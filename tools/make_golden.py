@@ -9,6 +9,9 @@ Stored per case:
   <case>.graph.npz      raw SDBG arrays (w nibbles packed 2/byte, last/tip bit-packed, mult u16, f[6], k)
   <case>.<params>.dump.gz   the reference's dump (layout: oracle/ref_harness/dump_format.h)
   <case>.nav.npz        (small cases) per-item degrees / neighbour ids through the reference SDBG API
+  <case>.regions.npz    invalid bitmaps after the UNMODIFIED reference keep_crispr_regions_extended_by_k
+                        (oracle/_ref/ref_regions): keys cyc_t<thr>_<min>_<max>_k<k> (seeds = all
+                        cycles of that run) and seeds / nodes_k<k> (seeds = random ids, graph as loaded)
 One case also keeps the on-disk MEGAHIT files (gzip'ed) to pin the file-format reader.
 """
 import argparse
@@ -58,9 +61,33 @@ def pack_graph(raw, path):
                         mult=raw["mult"], f=raw["f"])
 
 
+REGION_KS = (0, 1, 7, 40, 150)  # 150 = the reference's default extension, src/main.cpp
+
+
+def regions(name, prefix, tmp, params, n_items):
+    out = {}
+    reg = os.path.join(tmp, "out.reg")
+    thr, mn, mx = params[0]
+    for k in REGION_KS:
+        out[f"cyc_t{thr}_{mn}_{mx}_k{k}"] = np.packbits(
+            O.run_reference_regions(prefix, reg, k, cycles=(thr, mn, mx)), bitorder="little")
+    rng = np.random.default_rng(sum(map(ord, name)))
+    seeds = rng.integers(0, n_items, 40).astype("<u8")
+    seeds = np.concatenate([seeds, seeds[:5]])  # duplicates, like a node shared by several cycles
+    sf = os.path.join(tmp, "seeds.u64")
+    seeds.tofile(sf)
+    out["seeds"] = seeds
+    for k in (3, 30):
+        out[f"nodes_k{k}"] = np.packbits(O.run_reference_regions(prefix, reg, k, nodes_file=sf), bitorder="little")
+    np.savez_compressed(os.path.join(GOLD, f"{name}.regions.npz"), **out)
+    print("    regions:", {k: int(np.unpackbits(v, bitorder="little")[:n_items].size - np.unpackbits(v, bitorder="little")[:n_items].sum())
+                           for k, v in out.items() if k != "seeds"})
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("cases", nargs="*", default=list(CASES))
+    ap.add_argument("--regions-only", action="store_true", help="rebuild the graphs but write only <case>.regions.npz")
     ap.add_argument("--keep-tmp", default=None)
     a = ap.parse_args()
     os.makedirs(GOLD, exist_ok=True)
@@ -74,8 +101,13 @@ def main():
                        check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
         prefix = os.path.join(gdir, "graph")
         g = O.OracleGraph.load(prefix)
-        pack_graph(g.raw(), os.path.join(GOLD, f"{name}.graph.npz"))
         print(f"{name}: n_items={g.n}")
+        regions(name, prefix, tmp, params, g.n)
+        if a.regions_only:
+            if not a.keep_tmp:
+                shutil.rmtree(tmp)
+            continue
+        pack_graph(g.raw(), os.path.join(GOLD, f"{name}.graph.npz"))
         for thr, mn, mx in params:
             dump = os.path.join(tmp, "out.dump")
             info, _ = O.run_reference(prefix, dump, 1, thr, mn, mx)
