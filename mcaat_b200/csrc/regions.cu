@@ -2,27 +2,92 @@
 // src/spacer_ordering.cpp:78-139 (called from get_crispr_regions_extended_by_k :177-184 with k = read length in
 // nodes, src/main_run_and_debug.cpp:40-41).  The reference grows an unordered_set by re-scanning ALL members
 // each of the k rounds (O(k * |set|) hash operations and rank/select navigations on one core) and then walks
-// every item of the graph.  Here: a level-synchronous multi-source breadth-first search over three n-bit
-// bitmaps in HBM (member / current level / next level) on the resident device graph, followed by one streaming
-// pass that ORs ~member into the invalid bitmap.  The result is a set, so it is bit-exact by construction
-// whatever the scheduling.
+// every item of the graph.  Here: a level-synchronous multi-source breadth-first search on the resident device
+// graph — only the members new in the previous round are expanded — followed by one streaming pass that ORs
+// ~member into the invalid bitmap.  The result is a set, so it is bit-exact whatever the scheduling.
+//
+//   k_region_bfs   all k levels in ONE cooperative launch: the frontier is a queue of node ids in HBM, the
+//                  grid walks it, appends the members it adds to the next queue and meets at a grid barrier.
+//                  A level costs one barrier plus the dependent loads of one expansion (rank/select
+//                  navigation), not a launch and a pass over n bits.
+//   k_region_level the same level over bitmaps (cur -> next), taken from the level at which a queue would
+//                  overflow (nodes that do not fit are recorded in a spill bitmap, so nothing is lost).
+//   k_region_keep  invalid |= ~member, HBM-streaming: 3 x n/8 bytes.
+#include <cooperative_groups.h>
+
 #include <vector>
 
 #include "common.cuh"
 #include "search_dev.cuh"
 
+namespace cg = cooperative_groups;
+
 namespace mg {
 
-// seed ids -> member bitmap; ids new to the set also enter level 0
-__global__ void k_region_seed(const uint32_t *ids, uint64_t n_ids, uint32_t *member, uint32_t *cur) {
-  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_ids; i += (uint64_t)gridDim.x * blockDim.x) {
-    uint32_t v = ids[i];
-    if (bm_set_atomic(member, v)) bm_set_atomic(cur, v);
+struct RegionQueues {
+  uint32_t *q[2];      // frontier queues (node ids), used alternately
+  uint32_t cap;        // entries per queue
+  unsigned *cnt;       // cnt[3]: entries appended to the queue of level l are counted in cnt[l % 3]
+  uint32_t *spill;     // n-bit bitmap: members that did not fit into a queue (then cnt[slot] > cap)
+  unsigned *levels;    // out: levels completed by k_region_bfs
+  unsigned long long *added;  // out: members added
+};
+
+__device__ __forceinline__ void region_push(const RegionQueues &Q, int which, unsigned level_slot, uint32_t v) {
+  unsigned pos = atomicAdd(&Q.cnt[level_slot], 1u);
+  if (pos < Q.cap) {
+    __stcg(&Q.q[which][pos], v);
+  } else {
+    bm_set_atomic(Q.spill, v);
   }
 }
 
-// one level: every 32-item word of the current level's bitmap is scanned by one thread (grid-stride, coalesced
-// 4-byte loads; almost all words are zero), set bits are expanded through the succinct navigation.
+// seed ids -> member bitmap; ids new to the set form level 0
+__global__ void k_region_seed(const uint32_t *ids, uint64_t n_ids, uint32_t *member, RegionQueues Q) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_ids; i += (uint64_t)gridDim.x * blockDim.x) {
+    uint32_t v = ids[i];
+    if (bm_set_atomic(member, v)) region_push(Q, 0, 0, v);
+  }
+}
+
+// queue entries -> bitmap (hand-over to the bitmap levels)
+__global__ void k_region_queue_to_bits(const uint32_t *q, unsigned n_q, uint32_t *bits) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_q; i += gridDim.x * blockDim.x) bm_set_atomic(bits, q[i]);
+}
+
+__global__ void __launch_bounds__(256) k_region_bfs(GraphView g, uint32_t *member, RegionQueues Q, uint64_t k) {
+  cg::grid_group grid = cg::this_grid();
+  const unsigned gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
+  unsigned level = 0;
+  unsigned mine = 0;
+  while (level < k) {
+    const unsigned slot = level % 3, next_slot = (level + 1) % 3;
+    // complete and the same for every thread: all appends to this level's queue happened before the last
+    // barrier.  A count above the capacity means part of the level is in the spill bitmap: hand over.
+    const unsigned n_cur = ld_cg32(&Q.cnt[slot]);
+    if (n_cur == 0 || n_cur > Q.cap) break;
+    if (gtid == 0) Q.cnt[(level + 2) % 3] = 0;     // the slot of level+2: nobody reads or appends to it now
+    const uint32_t *cur = Q.q[level & 1];
+    for (unsigned i = gtid; i < n_cur; i += gsize) {
+      uint32_t fresh[8];
+      int c = region_expand_node(g, member, __ldcg(&cur[i]), fresh);
+      for (int j = 0; j < c; ++j) region_push(Q, (level + 1) & 1, next_slot, fresh[j]);
+      mine += (unsigned)c;
+    }
+    ++level;
+    grid.sync();
+  }
+  __shared__ unsigned sh;
+  if (threadIdx.x == 0) sh = 0;
+  __syncthreads();
+  if (mine) atomicAdd(&sh, mine);
+  __syncthreads();
+  if (threadIdx.x == 0 && sh) atomicAdd(Q.added, (unsigned long long)sh);
+  if (gtid == 0) *Q.levels = level;
+}
+
+// one level over bitmaps: every 32-item word of the current level's bitmap is looked at by one thread
+// (grid-stride, coalesced 4-byte loads), set bits are expanded.
 __global__ void k_region_level(GraphView g, uint32_t *member, const uint32_t *cur, uint32_t *next, uint64_t n_words,
                                unsigned long long *added) {
   __shared__ unsigned sh;
@@ -65,44 +130,89 @@ int run_keep_regions(mg_graph *g, const uint32_t *ids_dev, uint64_t n_ids, uint6
     TimedScope ts(g, T_REGION, n);
     const uint64_t n_words64 = (n + 63) / 64, n_words = n_words64 * 2;
     const size_t bm_bytes = (size_t)n_words * 4 + 16;
-    DevBuf member, lvl_a, lvl_b, counters;
+    // queue capacity: 2^22 ids (16 MB) unless the graph is smaller; MCAAT_REGION_QUEUE_LOG shrinks it (tests)
+    const char *ql = getenv("MCAAT_REGION_QUEUE_LOG");
+    int q_log = ql ? atoi(ql) : 22;
+    if (q_log < 2) q_log = 2;
+    if (q_log > 28) q_log = 28;
+    uint64_t cap = 1ull << q_log;
+    if (cap > n) cap = n;
+    DevBuf member, spill, other, queues, ctl;
     MG_TRY(member.alloc(bm_bytes));
-    MG_TRY(lvl_a.alloc(bm_bytes));
-    MG_TRY(lvl_b.alloc(bm_bytes));
-    MG_TRY(counters.alloc(4 * 8));
+    MG_TRY(spill.alloc(bm_bytes));
+    MG_TRY(queues.alloc(2 * cap * 4 + 16));
+    MG_TRY(ctl.alloc(64));
     MG_CUDA(cudaMemsetAsync(member.p, 0, bm_bytes, s));
-    MG_CUDA(cudaMemsetAsync(lvl_a.p, 0, bm_bytes, s));
-    MG_CUDA(cudaMemsetAsync(counters.p, 0, 4 * 8, s));
-    unsigned long long *c = counters.as<unsigned long long>();
-    if (n_ids) MG_LAUNCH(k_region_seed, grid_for(g, n_ids, 256), 256, 0, s, ids_dev, n_ids, member.as<uint32_t>(), lvl_a.as<uint32_t>());
-    uint32_t *cur = lvl_a.as<uint32_t>(), *next = lvl_b.as<uint32_t>();
-    // The host looks at the running total every kCheck levels only (one 8-byte read-back), so that a level costs
-    // a memset and a launch, not a round trip; levels after the search has died out are no-ops on empty bitmaps.
-    const uint64_t kCheck = 16;
-    unsigned long long total = 0, prev_total = 0;
+    MG_CUDA(cudaMemsetAsync(spill.p, 0, bm_bytes, s));
+    MG_CUDA(cudaMemsetAsync(ctl.p, 0, 64, s));
+    // ctl: [0,1] u64 keep counters | [2] u64 added | u32 at byte 24: cnt[3], levels
+    unsigned long long *c = ctl.as<unsigned long long>();
+    unsigned *cu = (unsigned *)(c + 3);
+    RegionQueues Q;
+    Q.q[0] = queues.as<uint32_t>();
+    Q.q[1] = Q.q[0] + cap;
+    Q.cap = (uint32_t)cap;
+    Q.cnt = cu;
+    Q.levels = cu + 3;
+    Q.spill = spill.as<uint32_t>();
+    Q.added = c + 2;
     uint64_t level = 0;
-    while (level < k && n_ids) {
-      uint64_t stop = level + kCheck < k ? level + kCheck : k;
-      for (; level < stop; ++level) {
-        MG_CUDA(cudaMemsetAsync(next, 0, bm_bytes, s));
-        MG_LAUNCH(k_region_level, grid_for(g, n_words, 256), 256, 0, s, g->view, member.as<uint32_t>(), cur, next, n_words, c + 2);
-        uint32_t *t = cur;
-        cur = next;
-        next = t;
+    unsigned long long total = 0;
+    if (n_ids && k) {
+      MG_LAUNCH(k_region_seed, grid_for(g, n_ids, 256), 256, 0, s, ids_dev, n_ids, member.as<uint32_t>(), Q);
+      int per_sm = 0;
+      MG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_region_bfs, 256, 0));
+      if (per_sm < 1) {
+        set_error("k_region_bfs does not fit on an SM");
+        return MG_ECUDA;
       }
+      if (per_sm > 4) per_sm = 4;
+      GraphView view = g->view;
+      uint32_t *member_p = member.as<uint32_t>();
+      uint64_t k_arg = k > 0xFFFFFFF0ull ? 0xFFFFFFF0ull : k;  // the level counter is 32 bits; see the loop below
+      void *args[] = {&view, &member_p, &Q, &k_arg};
+      MG_CUDA(cudaLaunchCooperativeKernel((void *)k_region_bfs, dim3((unsigned)(g->sm_count * per_sm)), dim3(256), args, 0, s));
+      ++g_launches;
+      unsigned h[4] = {0, 0, 0, 0};
+      MG_CUDA(cudaMemcpyAsync(h, cu, sizeof h, cudaMemcpyDeviceToHost, s));
       MG_CUDA(cudaMemcpyAsync(&total, c + 2, 8, cudaMemcpyDeviceToHost, s));
       MG_CUDA(cudaStreamSynchronize(s));
-      if (total == prev_total) break;  // nothing new in the last kCheck levels: every later level is empty too
-      prev_total = total;
+      level = h[3];
+      const unsigned n_q = h[level % 3] < cap ? h[level % 3] : (unsigned)cap;  // entries of the pending level's queue
+      if (level < k && n_q) {
+        // a queue overflowed (or k exceeds the 32-bit level counter): the pending level = queue entries + spill
+        // bitmap; continue over bitmaps.  The host reads the running total every kCheck levels only.
+        MG_TRY(other.alloc(bm_bytes));
+        uint32_t *cur = spill.as<uint32_t>(), *next = other.as<uint32_t>();
+        if (n_q) MG_LAUNCH(k_region_queue_to_bits, grid_for(g, n_q, 256), 256, 0, s, Q.q[level & 1], n_q, cur);
+        const uint64_t kCheck = 16;
+        unsigned long long prev_total = total;
+        while (level < k) {
+          uint64_t stop = level + kCheck < k ? level + kCheck : k;
+          for (; level < stop; ++level) {
+            MG_CUDA(cudaMemsetAsync(next, 0, bm_bytes, s));
+            MG_LAUNCH(k_region_level, grid_for(g, n_words, 256), 256, 0, s, g->view, member.as<uint32_t>(), cur, next, n_words, c + 2);
+            uint32_t *t = cur;
+            cur = next;
+            next = t;
+          }
+          MG_CUDA(cudaMemcpyAsync(&total, c + 2, 8, cudaMemcpyDeviceToHost, s));
+          MG_CUDA(cudaStreamSynchronize(s));
+          if (total == prev_total) break;  // nothing new in the last kCheck levels: every later level is empty too
+          prev_total = total;
+        }
+      }
+    } else if (n_ids) {
+      MG_LAUNCH(k_region_seed, grid_for(g, n_ids, 256), 256, 0, s, ids_dev, n_ids, member.as<uint32_t>(), Q);
     }
     out.levels = level;
     out.n_added = total;
     MG_LAUNCH(k_region_keep, grid_for(g, n_words64, 256), 256, 0, s, g->view, member.as<uint32_t>(), n_words64, c);
-    unsigned long long h[2] = {0, 0};
-    MG_CUDA(cudaMemcpyAsync(h, c, 16, cudaMemcpyDeviceToHost, s));
+    unsigned long long hk[2] = {0, 0};
+    MG_CUDA(cudaMemcpyAsync(hk, c, 16, cudaMemcpyDeviceToHost, s));
     MG_CUDA(cudaStreamSynchronize(s));
-    out.n_invalidated = h[0];
-    out.n_kept = h[1];
+    out.n_invalidated = hk[0];
+    out.n_kept = hk[1];
     // the navigation cache and the chain tables of mg_prune describe the graph before this call
     if (out.n_invalidated) g->pruned = false;
   }

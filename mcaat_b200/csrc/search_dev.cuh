@@ -760,8 +760,23 @@ done:
 // every valid item outside the final set is invalidated.  Members found in round r contribute neighbours from
 // round r+1 on and re-scanning older members adds nothing, so round r only has to expand the members that
 // were new in round r-1: a level-synchronous breadth-first search over bitmaps.
-//   member: the set;  cur: members new in the previous round (word `wi` is expanded here);  next: members new
-//   in this round.  Returns the number of members added.
+// Two forms of a level: a queue of the new members (regions.cu k_region_bfs, work proportional to the
+// frontier) and, when a queue overflows, bitmaps (region_expand_word: member = the set; cur = members new in
+// the previous round, word `wi` is expanded; next = members new in this round; returns the number added).
+// Expands one member: its valid in-/out-neighbours that were not in the set yet are added to `member` and
+// returned in fresh[0..count) (count <= 8).
+MG_HD int region_expand_node(const GraphView &g, uint32_t *member, uint32_t v, uint32_t fresh[8]) {
+  if (get_inv(g, v)) return 0;  // :94-96 (only a seed id can be invalid)
+  uint32_t nb[4];
+  int c = 0;
+  int d = incoming(g, v, nb);   // :98-109
+  for (int i = 0; i < d && i < 4; ++i)
+    if (bm_set_atomic(member, nb[i])) fresh[c++] = nb[i];
+  d = outgoing(g, v, nb);       // :111-122
+  for (int i = 0; i < d && i < 4; ++i)
+    if (bm_set_atomic(member, nb[i])) fresh[c++] = nb[i];
+  return c;
+}
 MG_HD unsigned region_expand_word(const GraphView &g, uint32_t *member, const uint32_t *cur, uint32_t *next,
                                   uint32_t wi) {
   uint32_t word = cur[wi];
@@ -773,14 +788,10 @@ MG_HD unsigned region_expand_word(const GraphView &g, uint32_t *member, const ui
     int b = __builtin_ctz(word);
 #endif
     word &= word - 1;
-    uint32_t v = wi * 32u + (uint32_t)b, nb[4];
-    if (get_inv(g, v)) continue;  // :94-96 (only a seed id can be invalid)
-    int d = incoming(g, v, nb);   // :98-109
-    for (int i = 0; i < d && i < 4; ++i)
-      if (bm_set_atomic(member, nb[i])) { bm_set_atomic(next, nb[i]); ++added; }
-    d = outgoing(g, v, nb);       // :111-122
-    for (int i = 0; i < d && i < 4; ++i)
-      if (bm_set_atomic(member, nb[i])) { bm_set_atomic(next, nb[i]); ++added; }
+    uint32_t fresh[8];
+    int c = region_expand_node(g, member, wi * 32u + (uint32_t)b, fresh);
+    for (int i = 0; i < c; ++i) bm_set_atomic(next, fresh[i]);
+    added += (unsigned)c;
   }
   return added;
 }

@@ -185,6 +185,20 @@ def test_region_extraction_matches_reference(name, key, params, k):
     assert st["levels"] <= k
 
 
+@pytest.mark.parametrize("qlog", [2, 6, 9])
+def test_region_extraction_with_overflowing_queues(monkeypatch, qlog):
+    """frontier queues of 4 / 64 / 512 ids: levels that do not fit spill into the bitmap form and the remaining
+    levels run as bitmap passes — same set"""
+    monkeypatch.setenv("MCAAT_REGION_QUEUE_LOG", str(qlog))
+    for name, key, params, k in [c for c in G.region_cases() if c[0] == "biallelic" and c[3] in (7, 40, 30)]:
+        g = DeviceGraph(packed(name))
+        if params is not None:
+            g.prune()
+        st = g.keep_regions(G.region_seeds(name, params), k)
+        assert np.array_equal(g.invalid(), G.region_expected(name, key, g.n)), (name, key)
+        assert st["levels"] <= k
+
+
 def test_region_extraction_edge_cases():
     g = DeviceGraph(packed("tiny"))
     g.prune()
