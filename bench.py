@@ -149,6 +149,13 @@ def cpu_baseline_port(sample_name, device):
     r = og.run(THR, MIN_LEN, MAX_LEN)
     dt = time.perf_counter() - t0
     n_starts = int(r.start_list().size)
+    if getattr(cpu_baseline_port, "with_regions", False):  # N4 on the same sample: literal restatement, 1 thread
+        seeds = [p for _, ps in r.searched for p in ps]
+        seeds = np.concatenate(seeds).astype(np.uint64) if seeds else np.zeros(0, np.uint64)
+        t1 = time.perf_counter()
+        gone, kept = og.keep_regions(seeds, 128)
+        cpu_baseline_port.regions = dict(workload=sample_name, n_items=int(g["n"]), k=128, seed_ids=int(seeds.size),
+                                         n_kept=kept, seconds=time.perf_counter() - t1, cores=1, kind="port")
     return dict(value=n_starts / dt, unit=UNIT, cores=1, kind="port",
                 sample=f"workload '{sample_name}' (same recipe at 1/20 scale): {g['n']} items, {n_starts} start nodes, "
                        f"{dt:.2f} s for the whole search with oracle/mcaat_oracle.c on 1 thread",
@@ -438,7 +445,10 @@ def main():
     phases = {k: round(v["ms"] / args.steps, 3) for k, v in timers.items() if v["launches"]}
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
+        cpu_baseline_port.with_regions = bool(regions)
         cpu = cpu_baseline_port(args.sample, "cuda")
+        if regions:
+            regions["cpu_baseline"] = getattr(cpu_baseline_port, "regions", None)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,

@@ -181,6 +181,22 @@ typedef struct {
 } mg_region_stats;
 int mg_keep_regions(mg_graph *g, const uint64_t *ids, uint64_t n_ids, uint64_t k, mg_region_stats *stats);
 
+/* The valid part of the graph in compact form — the input of the reference's SCC split
+ * (find_strongly_connected_components src/spacer_ordering.cpp:44-76 walks `for node < size: IsValidEdge` and
+ * calls OutgoingEdges per node; divide_graph_into_subgraphs :141-175 does so again per component).
+ * ids[0..n_nodes): valid item ids, ascending.  Row i = nbr[off[i]..off[i+1]): positions in `ids` of the valid
+ * out-neighbours of ids[i], in OutgoingEdges order (descending id, sdbg.h:296-320).  Arrays are library
+ * allocated; release with mg_subgraph_free.  Meant for the graph after mg_keep_regions (host arrays hold
+ * 8 + 8 + 4*degree bytes per valid node). */
+typedef struct {
+  uint64_t n_nodes, n_edges;
+  uint64_t *ids;
+  uint64_t *off; /* n_nodes + 1 */
+  uint32_t *nbr; /* n_edges */
+} mg_subgraph;
+int mg_valid_subgraph(mg_graph *g, mg_subgraph *out);
+void mg_subgraph_free(mg_subgraph *sg);
+
 /* Device timers: CUDA-event time (ms) and launch count accumulated per kernel family since the
  * last mg_timers_reset().  names[i] are static strings.  Returns the number of entries written
  * (<= cap). */

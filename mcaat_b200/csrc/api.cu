@@ -208,6 +208,20 @@ int mg_keep_regions(mg_graph *g, const uint64_t *ids, uint64_t n_ids, uint64_t k
   return run_keep_regions(g, dev.as<uint32_t>(), n_ids, k, stats);
 }
 
+int mg_valid_subgraph(mg_graph *g, mg_subgraph *out) {
+  MG_CHECK_HANDLE(g);
+  if (!out) return MG_EINVAL;
+  return run_valid_subgraph(g, out);
+}
+
+void mg_subgraph_free(mg_subgraph *sg) {
+  if (!sg) return;
+  free(sg->ids);
+  free(sg->off);
+  free(sg->nbr);
+  memset(sg, 0, sizeof *sg);
+}
+
 int mg_visited_readback(mg_graph *g, uint64_t *host_words) {
   MG_CHECK_HANDLE(g);
   if (!host_words) return MG_EINVAL;

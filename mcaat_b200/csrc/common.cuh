@@ -174,6 +174,7 @@ int bucket_on_host(const std::vector<uint64_t> &ids, const std::vector<uint16_t>
 int gather_mult(mg_graph *g, const uint32_t *ids_dev, uint64_t n, std::vector<uint16_t> &out);
 // regions.cu
 int run_keep_regions(mg_graph *g, const uint32_t *ids_dev, uint64_t n_ids, uint64_t k, mg_region_stats *st);
+int run_valid_subgraph(mg_graph *g, mg_subgraph *out);
 // enumerate.cu
 int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len, int max_len, mg_cycles *out);
 

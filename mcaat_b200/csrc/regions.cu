@@ -222,4 +222,108 @@ int run_keep_regions(mg_graph *g, const uint32_t *ids_dev, uint64_t n_ids, uint6
   return MG_OK;
 }
 
+// ------------------------------------------------------------------ valid subgraph (input of the SCC split)
+// divide_graph_into_subgraphs / find_strongly_connected_components (reference src/spacer_ordering.cpp:44-76,
+// 141-175) walk every item of the graph with IsValidEdge and call OutgoingEdges per valid node through hash
+// maps.  After region extraction only a sliver of the graph is valid, so the device compacts it: ascending
+// valid ids and, per valid node, the positions (in that list) of its valid out-neighbours in OutgoingEdges
+// order.  Tarjan's visiting order, which fixes the reference's output order, is sequential and runs on the
+// host over this compact form (mcaat_b200/host/regions_gpu.cpp).
+
+// valid bits as 32-bit words + per-word popcounts
+__global__ void k_valid_words(GraphView g, uint64_t n_words, uint32_t *bits, uint32_t *counts) {
+  for (uint64_t w = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; w < n_words; w += (uint64_t)gridDim.x * blockDim.x) {
+    uint64_t first = w * 32;
+    uint32_t v = 0;
+    if (first < g.n) {
+      uint64_t inv = g.fb[first >> 8].inv[(first >> 6) & 3];
+      v = ~(uint32_t)(inv >> (first & 32));
+      if (first + 32 > g.n) v &= 0xFFFFFFFFu >> (32 - (g.n - first));
+    }
+    bits[w] = v;
+    counts[w] = __popc(v);
+  }
+}
+
+// rows of the compact graph: one thread per bitmap word walks its valid items
+__global__ void k_subgraph_rows(GraphView g, uint64_t n_words, const uint32_t *bits, const uint32_t *prefix, uint32_t *ids,
+                                uint32_t *nbr4) {
+  for (uint64_t w = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; w < n_words; w += (uint64_t)gridDim.x * blockDim.x) {
+    uint32_t word = bits[w];
+    uint32_t row = prefix[w];
+    while (word) {
+      int b = __ffs(word) - 1;
+      word &= word - 1;
+      uint32_t v = (uint32_t)(w * 32 + b), out[4];
+      int d = outgoing(g, v, out);
+      ids[row] = v;
+      for (int j = 0; j < 4; ++j) {
+        uint32_t r = kNull;
+        if (j < d) {
+          uint32_t x = out[j];
+          r = prefix[x >> 5] + __popc(bits[x >> 5] & ((1u << (x & 31)) - 1u));
+        }
+        nbr4[(uint64_t)row * 4 + j] = r;
+      }
+      ++row;
+    }
+  }
+}
+
+int run_valid_subgraph(mg_graph *g, mg_subgraph *out) {
+  const uint64_t n = g->view.n;
+  cudaStream_t s = g->stream;
+  memset(out, 0, sizeof *out);
+  std::vector<uint32_t> h_ids, h_nbr;
+  uint32_t tot = 0;
+  if (n) {
+    TimedScope ts(g, T_REGION, n);
+    const uint64_t n_words = (n + 31) / 32;
+    DevBuf bits, prefix, total, ids, nbr4;
+    MG_TRY(bits.alloc(n_words * 4 + 16));
+    MG_TRY(prefix.alloc(n_words * 4 + 16));
+    MG_TRY(total.alloc(4));
+    MG_LAUNCH(k_valid_words, grid_for(g, n_words, 256), 256, 0, s, g->view, n_words, bits.as<uint32_t>(), prefix.as<uint32_t>());
+    MG_TRY(exclusive_scan_u32(prefix.as<uint32_t>(), n_words, total.as<uint32_t>(), s));
+    MG_CUDA(cudaMemcpyAsync(&tot, total.p, 4, cudaMemcpyDeviceToHost, s));
+    MG_CUDA(cudaStreamSynchronize(s));
+    if (tot) {
+      MG_TRY(ids.alloc((size_t)tot * 4));
+      MG_TRY(nbr4.alloc((size_t)tot * 16));
+      MG_LAUNCH(k_subgraph_rows, grid_for(g, n_words, 256), 256, 0, s, g->view, n_words, bits.as<uint32_t>(), prefix.as<uint32_t>(),
+                ids.as<uint32_t>(), nbr4.as<uint32_t>());
+      h_ids.resize(tot);
+      h_nbr.resize((size_t)tot * 4);
+      MG_CUDA(cudaMemcpyAsync(h_ids.data(), ids.p, (size_t)tot * 4, cudaMemcpyDeviceToHost, s));
+      MG_CUDA(cudaMemcpyAsync(h_nbr.data(), nbr4.p, (size_t)tot * 16, cudaMemcpyDeviceToHost, s));
+    }
+    MG_CUDA(cudaStreamSynchronize(s));
+  }
+  flush_timers(g);
+  out->ids = (uint64_t *)malloc(((size_t)tot + 1) * 8);
+  out->off = (uint64_t *)malloc(((size_t)tot + 1) * 8);
+  size_t n_edges = 0;
+  for (size_t i = 0; i < h_nbr.size(); ++i) n_edges += h_nbr[i] != kNull;
+  out->nbr = (uint32_t *)malloc((n_edges + 1) * 4);
+  if (!out->ids || !out->off || !out->nbr) {
+    free(out->ids);
+    free(out->off);
+    free(out->nbr);
+    memset(out, 0, sizeof *out);
+    set_error("out of host memory for a subgraph of %u nodes", tot);
+    return MG_ENOMEM;
+  }
+  size_t e = 0;
+  for (uint32_t i = 0; i < tot; ++i) {
+    out->ids[i] = h_ids[i];
+    out->off[i] = e;
+    for (int j = 0; j < 4; ++j)
+      if (h_nbr[(size_t)i * 4 + j] != kNull) out->nbr[e++] = h_nbr[(size_t)i * 4 + j];
+  }
+  out->off[tot] = e;
+  out->n_nodes = tot;
+  out->n_edges = e;
+  return MG_OK;
+}
+
 }  // namespace mg

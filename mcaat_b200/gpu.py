@@ -22,13 +22,18 @@ SYMBOLS = [
     "mg_graph_create", "mg_graph_create_from_files", "mg_graph_destroy", "mg_graph_reset", "mg_graph_size", "mg_graph_device_bytes",
     "mg_navigate", "mg_prune", "mg_invalid_readback", "mg_candidates", "mg_dls", "mg_select_starts",
     "mg_bucket_starts", "mg_starts_free", "mg_find_cycles", "mg_cycles_free", "mg_visited_readback",
-    "mg_keep_regions", "mg_invalid_merge",
+    "mg_keep_regions", "mg_invalid_merge", "mg_valid_subgraph", "mg_subgraph_free",
     "mg_timers", "mg_timers_reset", "mg_step_begin", "mg_step_end", "mg_launch_count", "mg_free", "mg_last_error", "mg_version",
 ]
 
 
 class RegionStats(C.Structure):
     _fields_ = [(k, C.c_uint64) for k in ("n_seed_ids", "n_added", "levels", "n_invalidated", "n_kept")]
+
+
+class Subgraph(C.Structure):
+    _fields_ = [("n_nodes", C.c_uint64), ("n_edges", C.c_uint64), ("ids", u64p), ("off", u64p),
+                ("nbr", C.POINTER(C.c_uint32))]
 
 
 class MgError(RuntimeError):
@@ -94,6 +99,9 @@ def lib():
         L.mg_find_cycles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.POINTER(Cycles)]
         L.mg_cycles_free.argtypes = [C.POINTER(Cycles)]
         L.mg_cycles_free.restype = None
+        L.mg_valid_subgraph.argtypes = [C.c_void_p, C.POINTER(Subgraph)]
+        L.mg_subgraph_free.argtypes = [C.POINTER(Subgraph)]
+        L.mg_subgraph_free.restype = None
         L.mg_invalid_merge.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
         L.mg_keep_regions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(RegionStats)]
         L.mg_timers.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
@@ -250,6 +258,17 @@ class DeviceGraph:
         st = RegionStats()
         _check(lib().mg_keep_regions(self.h, ids.ctypes.data, ids.size, int(k), C.byref(st)))
         return {k_: int(getattr(st, k_)) for k_, _ in RegionStats._fields_}
+
+    def valid_subgraph(self):
+        """(ids ascending, off, nbr): the valid items and, per item, the positions of its valid out-neighbours
+        in OutgoingEdges order — what the reference's SCC split walks (src/spacer_ordering.cpp:44-76,141-175)."""
+        sg = Subgraph()
+        _check(lib().mg_valid_subgraph(self.h, C.byref(sg)))
+        ids = _np(sg.ids, sg.n_nodes)
+        off = _np(sg.off, sg.n_nodes + 1)
+        nbr = _np(sg.nbr, sg.n_edges, np.uint32)
+        lib().mg_subgraph_free(C.byref(sg))
+        return ids, off, nbr
 
     def dls(self, ids, limit):
         ids = np.ascontiguousarray(ids, np.uint64)

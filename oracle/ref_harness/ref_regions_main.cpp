@@ -9,10 +9,16 @@
 //   ref_regions <sdbg_prefix> <out.reg> <k> nodes <file of little-endian u64 ids>
 //       one "cycle" holding the listed ids, on the graph as loaded (nothing pruned)
 // Output: magic "MCAATREG", n_items, k, n_seed_ids, n_words, invalid bitmap words after the call.
+// With `cycles+scc` / `nodes+scc` the reference's divide_graph_into_subgraphs (src/spacer_ordering.cpp:141-175,
+// Tarjan :3-76) runs next, as in get_crispr_regions_extended_by_k (:177-184), and the output continues with
+// magic "MCAATSCC", n_subgraphs, then per subgraph in the returned order: n_nodes, `nodes` in its
+// unordered_set iteration order, n_adj, and per `adjacency_list` entry in its unordered_map iteration order:
+// from, n_to, to[].
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <string>
 #include <vector>
 
 #include "cycle_finder.h"
@@ -20,18 +26,38 @@
 #include "spacer_ordering.h"
 #include "dump_format.h"
 
+#include <sys/resource.h>
+#include <unistd.h>
+
 void keep_crispr_regions_extended_by_k(SDBG &sdbg, const size_t &k, const vector<vector<uint64_t>> &cycles);
+vector<Graph> divide_graph_into_subgraphs(const SDBG &sdbg);
+
+static void raise_stack_limit(char **argv) {  // the reference's Tarjan and RecursiveReduction recurse per node
+  struct rlimit rl;
+  getrlimit(RLIMIT_STACK, &rl);
+  if (rl.rlim_cur != RLIM_INFINITY && !getenv("MCAAT_REF_REEXEC")) {
+    rl.rlim_cur = rl.rlim_max;
+    if (setrlimit(RLIMIT_STACK, &rl) == 0) {
+      setenv("MCAAT_REF_REEXEC", "1", 1);
+      execv("/proc/self/exe", argv);
+    }
+  }
+}
 
 int main(int argc, char **argv) {
+  raise_stack_limit(argv);
   if (argc < 5) {
-    fprintf(stderr, "usage: %s <sdbg_prefix> <out.reg> <k> cycles [thr min max] | nodes <ids.u64>\n", argv[0]);
+    fprintf(stderr, "usage: %s <sdbg_prefix> <out.reg> <k> cycles[+scc] [thr min max] | nodes[+scc] <ids.u64>\n", argv[0]);
     return 1;
   }
   size_t k = strtoull(argv[3], 0, 10);
   SDBG g;
   g.LoadFromFile(argv[1]);
   std::vector<std::vector<uint64_t>> cycles;
-  if (!strcmp(argv[4], "cycles")) {
+  std::string mode = argv[4];
+  const bool scc = mode.size() > 4 && mode.compare(mode.size() - 4, 4, "+scc") == 0;
+  if (scc) mode.resize(mode.size() - 4);
+  if (mode == "cycles") {
     Settings s;
     s.threads = 1;
     s.cycle_finder_settings.threshold_multiplicity = argc > 5 ? strtoull(argv[5], 0, 10) : 20;
@@ -46,7 +72,7 @@ int main(int argc, char **argv) {
     std::cout.clear();
     for (auto &kv : cf.results)
       for (auto &c : kv.second) cycles.push_back(c);
-  } else if (!strcmp(argv[4], "nodes") && argc > 5) {
+  } else if (mode == "nodes" && argc > 5) {
     FILE *f = fopen(argv[5], "rb");
     if (!f) return 2;
     std::vector<uint64_t> ids;
@@ -75,8 +101,25 @@ int main(int argc, char **argv) {
     else ++kept;
   }
   dump_vec(f, inv);
+  uint64_t n_sub = 0;
+  if (scc) {
+    std::cout.setstate(std::ios_base::failbit);
+    std::vector<Graph> subs = divide_graph_into_subgraphs(g);
+    std::cout.clear();
+    n_sub = subs.size();
+    fwrite("MCAATSCC", 8, 1, f);
+    dump_u64(f, subs.size());
+    for (auto &sg : subs) {
+      dump_vec(f, std::vector<uint64_t>(sg.nodes.begin(), sg.nodes.end()));
+      dump_u64(f, sg.adjacency_list.size());
+      for (auto &kv : sg.adjacency_list) {
+        dump_u64(f, kv.first);
+        dump_vec(f, kv.second);
+      }
+    }
+  }
   fclose(f);
-  printf("REF_JSON {\"n_items\": %llu, \"k\": %zu, \"seed_ids\": %llu, \"kept\": %llu}\n", (unsigned long long)n, k,
-         (unsigned long long)n_seed, (unsigned long long)kept);
+  printf("REF_JSON {\"n_items\": %llu, \"k\": %zu, \"seed_ids\": %llu, \"kept\": %llu, \"subgraphs\": %llu}\n",
+         (unsigned long long)n, k, (unsigned long long)n_seed, (unsigned long long)kept, (unsigned long long)n_sub);
   return 0;
 }

@@ -277,3 +277,60 @@ def test_cpp_drop_in_regions_match_reference(tmp_path):
         words = np.frombuffer(raw, "<u8", (n + 63) // 64, 40)
         got = np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool)
         assert np.array_equal(got, G.region_expected("tiny", key, n)), key
+
+
+def test_valid_subgraph_matches_navigation():
+    """mg_valid_subgraph (input of the reference's SCC split) against the per-item navigation tables: ascending
+    valid ids; rows = valid out-neighbours in OutgoingEdges order, as positions in the id list"""
+    g = DeviceGraph(packed("repeatrich"))
+    g.prune()
+    g.keep_regions(G.region_seeds("repeatrich", (20, 27, 77)), 40)
+    ids, off, nbr = g.valid_subgraph()
+    inv = g.invalid()
+    assert np.array_equal(ids, np.nonzero(~inv)[0].astype(np.uint64))
+    od, _, o, _, _ = g.navigate()
+    deg = np.maximum(od[ids.astype(np.int64)], 0).astype(np.int64)
+    assert np.array_equal(np.diff(off.astype(np.int64)), deg) and off[-1] == nbr.size
+    want = np.concatenate([o[int(v)][:d] for v, d in zip(ids, deg)]) if nbr.size else np.zeros(0, np.uint64)
+    assert np.array_equal(ids[nbr.astype(np.int64)], want)
+    # everything invalid -> empty graph
+    g.keep_regions([], 1)
+    ids, off, nbr = g.valid_subgraph()
+    assert ids.size == 0 and off.tolist() == [0] and nbr.size == 0
+
+
+@pytest.mark.parametrize("name", ["tiny", "biallelic"])
+def test_cpp_drop_in_scc_split_matches_reference(tmp_path, name):
+    """get_crispr_regions_extended_by_k = keep + divide_graph_into_subgraphs (reference
+    src/spacer_ordering.cpp:177-184) through the drop-ins: the harness output — invalid bitmap, components in
+    Tarjan completion order, node order, iteration order of each Graph's unordered containers — equals the
+    unmodified reference's byte for byte."""
+    import glob
+    import gzip
+    import os
+    import subprocess
+    exe = os.path.join(gpu.ROOT, "mcaat_b200", "host", "_build", "shim_regions")
+    if not os.path.exists(exe):
+        pytest.skip("shim_regions not built (needs the reference headers at build time)")
+    prefix = G.unpack_sdbg_files(name, str(tmp_path))
+    seeds_file = str(tmp_path / "seeds.u64")
+    G.region_seeds(name, None).astype("<u8").tofile(seeds_file)
+    golds = sorted(glob.glob(os.path.join(G.GOLD, f"{name}.scc_*.reg.gz")))
+    assert len(golds) == 3
+    n_sub = []
+    for gold in golds:
+        key = os.path.basename(gold)[len(name) + 5:-len(".reg.gz")]
+        if key.startswith("nodes_k"):
+            tail = [key[7:], "nodes+scc", seeds_file]
+        else:
+            _, t, mn, mxk = key.split("_", 3)
+            mx, k = mxk.split("_k")
+            tail = [k, "cycles+scc", t[1:], mn, mx]
+        out = str(tmp_path / (key + ".reg"))
+        subprocess.run([exe, prefix, out] + tail, check=True, capture_output=True)
+        want = gzip.open(gold, "rb").read()
+        got = open(out, "rb").read()
+        assert got == want, key
+        at = want.index(b"MCAATSCC")
+        n_sub.append(int(np.frombuffer(want, "<u8", 1, at + 8)[0]))
+    assert max(n_sub) >= 2

@@ -12,6 +12,7 @@ Stored per case:
   <case>.regions.npz    invalid bitmaps after the UNMODIFIED reference keep_crispr_regions_extended_by_k
                         (oracle/_ref/ref_regions): keys cyc_t<thr>_<min>_<max>_k<k> (seeds = all
                         cycles of that run) and seeds / nodes_k<k> (seeds = random ids, graph as loaded)
+  <case>.scc_<key>.reg.gz   (cases with on-disk files) ref_regions output incl. the reference's SCC split
 One case also keeps the on-disk MEGAHIT files (gzip'ed) to pin the file-format reader.
 """
 import argparse
@@ -42,7 +43,7 @@ CASES = {
     "biallelic": (["--seed", "3", "--genomes", "1", "--genome-len", "40000", "--arrays", "1",
                    "--spacers-min", "150", "--spacers-max", "150", "--biallelic-arrays", "1",
                    "--sites", "2", "--spacer-min-len", "38", "--pairs", "8000"],
-                  [(20, 27, 77)], False, False),
+                  [(20, 27, 77)], False, True),
     "strain": (["--seed", "4", "--genomes", "2", "--genome-len", "40000", "--arrays", "3",
                 "--spacers-min", "8", "--spacers-max", "16", "--strain-pairs", "2",
                 "--pairs", "16000", "--error-rate", "0.005"],
@@ -80,6 +81,15 @@ def regions(name, prefix, tmp, params, n_items):
     for k in (3, 30):
         out[f"nodes_k{k}"] = np.packbits(O.run_reference_regions(prefix, reg, k, nodes_file=sf), bitorder="little")
     np.savez_compressed(os.path.join(GOLD, f"{name}.regions.npz"), **out)
+    if os.path.isdir(os.path.join(GOLD, f"{name}.sdbg")) or CASES[name][3]:
+        # + the reference's SCC split (divide_graph_into_subgraphs, src/spacer_ordering.cpp:141-175): whole
+        # harness output, compared byte for byte with the drop-in's (needs the on-disk graph files)
+        runs = [(f"cyc_t{thr}_{mn}_{mx}_k{k}", [str(k), "cycles+scc", str(thr), str(mn), str(mx)]) for k in (7, 150)]
+        runs.append(("nodes_k30", ["30", "nodes+scc", sf]))
+        for key, tail in runs:
+            subprocess.run([O.ref_binary("ref_regions"), prefix, reg] + tail, check=True, capture_output=True)
+            with open(reg, "rb") as fi, gzip.GzipFile(os.path.join(GOLD, f"{name}.scc_{key}.reg.gz"), "wb", mtime=0) as fo:
+                shutil.copyfileobj(fi, fo)
     print("    regions:", {k: int(np.unpackbits(v, bitorder="little")[:n_items].size - np.unpackbits(v, bitorder="little")[:n_items].sum())
                            for k, v in out.items() if k != "seeds"})
 
