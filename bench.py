@@ -271,6 +271,7 @@ def main():
     dist = None
     if world > 1:
         import torch.distributed as dist
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep NCCL's version banner off stdout (one JSON line)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     # ---- workload: built on the GPU by rank 0; raw arrays broadcast over NCCL (NVLink) to the other ranks
