@@ -24,6 +24,12 @@ struct orc_graph {
   uint64_t cnt_w[5];
   uint64_t *occ_last;
   uint64_t cnt_last;
+  /* k-mer lookup (sdbg.h:141-207), only when loaded from files */
+  uint32_t wptl;          /* words per tip label */
+  uint32_t *tip_labels;   /* file words, wptl per tip, in item order */
+  uint64_t *tip_index;    /* per item: number of tips before it (rs_is_tip_.rank(x) - 1 for a tip x) */
+  uint64_t n_buckets;
+  int64_t *pl_first, *pl_second; /* prefix_look_up_ (sdbg.h:36,44-46); absent buckets stay (0,0) */
 };
 
 /* ---------------------------------------------------------------- small containers */
@@ -119,7 +125,7 @@ orc_graph *orc_from_arrays(uint64_t n, uint32_t k, const uint8_t *w, const uint8
   return g;
 }
 
-typedef struct { uint64_t bucket_id, file_id, off, num_items, num_tips, num_large, acc_items; } bucket_rec;
+typedef struct { uint64_t bucket_id, file_id, off, num_items, num_tips, num_large, acc_items, acc_tips; } bucket_rec;
 static int cmp_bucket_id(const void *a, const void *b) {
   const bucket_rec *x = (const bucket_rec *)a, *y = (const bucket_rec *)b;
   return x->bucket_id < y->bucket_id ? -1 : x->bucket_id > y->bucket_id;
@@ -154,23 +160,33 @@ orc_graph *orc_load(const char *prefix) {
   fclose(fi);
   /* accumulate in bucket_id order, skipping records whose ids are the null id (SIZE_MAX) */
   qsort(rec, nb, sizeof(bucket_rec), cmp_bucket_id);
-  uint64_t n = 0;
+  uint64_t n = 0, n_tips_total = 0;
   for (uint64_t i = 0; i < nb; ++i) {
     if (rec[i].file_id == ~0ull || rec[i].bucket_id == ~0ull) continue;
     rec[i].acc_items = n;
+    rec[i].acc_tips = n_tips_total;
     n += rec[i].num_items;
+    n_tips_total += rec[i].num_tips;
   }
   qsort(rec, nb, sizeof(bucket_rec), cmp_file_off);
   orc_graph *g = alloc_graph(n);
   g->k = (uint32_t)k;
   memset(g->f, 0, sizeof g->f);
   g->f[0] = -1;
+  g->wptl = (uint32_t)wptl;
+  g->n_buckets = nb;
+  g->pl_first = (int64_t *)calloc(nb ? nb : 1, 8);
+  g->pl_second = (int64_t *)calloc(nb ? nb : 1, 8);
+  g->tip_index = (uint64_t *)calloc(n ? n : 1, 8);
+  g->tip_labels = (uint32_t *)calloc(n_tips_total * wptl + 1, 4);
   FILE *fd = NULL;
   uint64_t cur_file = ~0ull;
   int ok = 1;
   for (uint64_t i = 0; i < nb && ok; ++i) {
     if (rec[i].bucket_id == ~0ull) break; /* sdbg.h:40, sdbg_raw_content.cpp:42-44 */
     g->f[rec[i].bucket_id / (nb / 4) + 2] += (int64_t)rec[i].num_items;
+    g->pl_first[rec[i].bucket_id] = (int64_t)rec[i].acc_items;                                  /* sdbg.h:44 */
+    g->pl_second[rec[i].bucket_id] = (int64_t)rec[i].acc_items + (int64_t)rec[i].num_items - 1; /* :45-46 */
     if (rec[i].file_id != cur_file) {
       if (fd) fclose(fd);
       snprintf(path, sizeof path, "%s.sdbg.%llu", prefix, (unsigned long long)rec[i].file_id);
@@ -178,6 +194,7 @@ orc_graph *orc_load(const char *prefix) {
       if (!fd) { ok = 0; break; }
       cur_file = rec[i].file_id;
     }
+    uint64_t lab_n = rec[i].acc_tips * wptl; /* sdbg_raw_content.cpp:58-60 */
     for (uint64_t j = 0; j < rec[i].num_items; ++j) {
       uint64_t idx = rec[i].acc_items + j;
       uint8_t it[2];
@@ -188,7 +205,11 @@ orc_graph *orc_load(const char *prefix) {
       uint16_t mul = it[1];
       if (mul == 255) { if (fread(&mul, 2, 1, fd) != 1) { ok = 0; break; } }
       g->mult[idx] = mul;
-      if (g->tip[idx] && wptl) fseek(fd, (long)(4 * wptl), SEEK_CUR); /* tip label: unused on this path */
+      if (g->tip[idx] && wptl) { /* sdbg_raw_content.cpp:82-88; kept as stored (see tip_char) */
+        if (lab_n + wptl > n_tips_total * wptl) { ok = 0; break; }
+        if (fread(g->tip_labels + lab_n, 4, wptl, fd) != wptl) { ok = 0; break; }
+        lab_n += wptl;
+      }
     }
   }
   if (fd) fclose(fd);
@@ -196,6 +217,11 @@ orc_graph *orc_load(const char *prefix) {
   if (!ok) { orc_free(g); return NULL; }
   for (int i = 2; i < 6; ++i) g->f[i] += g->f[i - 1];
   build_index(g);
+  /* labels sit at accumulate_tip_count + position inside the bucket = number of tips before the item */
+  {
+    uint64_t n_tips = 0;
+    for (uint64_t i = 0; i < n; ++i) { g->tip_index[i] = n_tips; n_tips += g->tip[i]; }
+  }
   return g;
 }
 
@@ -204,6 +230,7 @@ void orc_free(orc_graph *g) {
   free(g->w); free(g->last); free(g->tip); free(g->lt); free(g->invalid); free(g->mult);
   for (int c = 1; c < 5; ++c) free(g->occ_w[c]);
   free(g->occ_last);
+  free(g->tip_labels); free(g->tip_index); free(g->pl_first); free(g->pl_second);
   free(g);
 }
 
@@ -338,6 +365,85 @@ void orc_peel(orc_graph *g, const uint64_t *tips, uint64_t n_tips) {
     }
   }
   free(st.a);
+}
+
+/* ---------------------------------------------------------------- read -> node ids (N3) */
+/* CharAtTipLabel (sdbg.h:128-133) on the words as stored in the file: the loader reverses the 2-bit groups of
+ * each word (sdbg_raw_content.cpp:84-87) and CompactVector<2, uint32_t> is little-endian (kmcompactvector.h:14-15,
+ * 52-60), so char `off` is bits 30-2*(off%16) of file word off/16; values are 1-based. */
+static int tip_char(const orc_graph *g, uint64_t tip_item, unsigned off) {
+  const uint32_t *lab = g->tip_labels + g->tip_index[tip_item] * g->wptl; /* sdbg.h:124-127 */
+  return (int)((lab[off / 16] >> (30 - 2 * (off % 16))) & 3u) + 1;
+}
+/* sdbg.h:77 GetLastIndex = rs_last_.succ(x): first item >= x with the last flag */
+static uint64_t last_index(const orc_graph *g, uint64_t x) {
+  while (x < g->n && !g->last[x]) ++x;
+  return x < g->n ? x : ~0ull;
+}
+/* sdbg.h:141-207, restated line by line — including that W is compared RAW (:187-195: labels 5..8 are not
+ * folded to 1..4 here, unlike GetLabel :225-228), which decides where the binary search goes. */
+uint64_t orc_index_binary_search(const orc_graph *g, const uint8_t *seq) {
+  if (!g->pl_first) return ~0ull;
+  const int k = (int)g->k;
+  uint64_t prefix = 0;
+  for (uint64_t i = 0; (1u << (i * 2)) < g->n_buckets; ++i) prefix = prefix * 4 + seq[k - 1 - i] - 1; /* :142-146 */
+  int64_t l = g->pl_first[prefix], r = g->pl_second[prefix];
+  while (l <= r) {
+    int cmp = 0;
+    uint64_t mid = (uint64_t)((l + r) / 2), y = mid;
+    for (int i = k - 1; i >= 0; --i) {
+      if (g->tip[y]) { /* :156-184 */
+        for (int j = 0; j < i; ++j) {
+          int c = tip_char(g, y, (unsigned)j);
+          if (c < seq[i - j]) { cmp = -1; break; }
+          else if (c > seq[i - j]) { cmp = 1; break; }
+        }
+        if (cmp == 0) {
+          if (g->tip[mid]) cmp = -1;
+          else {
+            int c = tip_char(g, y, (unsigned)i);
+            if (c < seq[0]) cmp = -1;
+            else if (c > seq[0]) cmp = 1;
+          }
+        }
+        break;
+      }
+      y = orc_backward(g, y); /* :186 */
+      int c = g->w[y];        /* :187 raw W */
+      if (c < seq[i]) { cmp = -1; break; }
+      else if (c > seq[i]) { cmp = 1; break; }
+    }
+    if (cmp == 0) return last_index(g, mid); /* :198-199 */
+    else if (cmp > 0) r = (int64_t)mid - 1;
+    else l = (int64_t)mid + 1;
+  }
+  return ~0ull; /* kNullID */
+}
+/* reads.cpp:33-54 k_mer_to_node_id: A,C,G -> 1,2,3, anything else -> 4 */
+static uint64_t kmer_node(const orc_graph *g, const char *kmer) {
+  uint8_t seq[256];
+  for (uint32_t i = 0; i < g->k; ++i) seq[i] = kmer[i] == 'A' ? 1 : kmer[i] == 'C' ? 2 : kmer[i] == 'G' ? 3 : 4;
+  return orc_index_binary_search(g, seq);
+}
+/* reads.cpp:20-31 reverse_pair_ends_sequence, in place */
+void orc_reverse_complement(char *s, uint64_t len) {
+  for (uint64_t i = 0; i < len / 2; ++i) { char t = s[i]; s[i] = s[len - 1 - i]; s[len - 1 - i] = t; }
+  for (uint64_t i = 0; i < len; ++i)
+    s[i] = s[i] == 'A' ? 'T' : s[i] == 'T' ? 'A' : s[i] == 'C' ? 'G' : s[i] == 'G' ? 'C' : s[i];
+}
+/* reads.cpp:56-93 get_read_from_sequence; member = nodes_of_cycles as a byte per item.  Returns the number of
+ * ids written to out (capacity >= len), 0 = the read is dropped. */
+uint64_t orc_get_read(const orc_graph *g, const uint8_t *member, const char *seq, uint64_t len, uint64_t *out) {
+  const uint64_t K = g->k;
+  if (len <= 2 * K) return 0;                                   /* :62-64 */
+  uint64_t a = kmer_node(g, seq), b = kmer_node(g, seq + len - K); /* :66-70 */
+  int in_a = a < g->n && member[a], in_b = b < g->n && member[b];
+  if (!in_a && !in_b) return 0;                                 /* :72-75 */
+  uint64_t c = 0;
+  out[c++] = a;
+  for (uint64_t i = 1; i < len - K; ++i) out[c++] = kmer_node(g, seq + i); /* :78-83 */
+  out[c++] = b;
+  return c;
 }
 
 /* ---------------------------------------------------------------- region extraction (N4) */

@@ -101,6 +101,15 @@ void orc_cycles_free(orc_cycles *c);
 int orc_run(orc_graph *g, uint64_t threshold_multiplicity, int min_len, int max_len, orc_result *res);
 void orc_result_free(orc_result *res);
 
+/* SURVEY 8(f) N3 — read -> node-id mapping.  Needs a graph made by orc_load (tip labels and the bucket table
+ * are not part of orc_from_arrays).  Pinned against the compiled reference functions: oracle/_ref/ref_reads,
+ * tests/golden/<case>.reads.npz.
+ * orc_index_binary_search: SDBG::IndexBinarySearch (sdbg.h:141-207), seq[0..k) in 1..4; ~0 = kNullID.
+ * orc_get_read: get_read_from_sequence (src/reads.cpp:56-93); orc_reverse_complement: :20-31. */
+uint64_t orc_index_binary_search(const orc_graph *g, const uint8_t *seq);
+uint64_t orc_get_read(const orc_graph *g, const uint8_t *member, const char *seq, uint64_t len, uint64_t *out);
+void orc_reverse_complement(char *s, uint64_t len);
+
 /* SURVEY 8(f) N4 — keep_crispr_regions_extended_by_k (reference src/spacer_ordering.cpp:78-139): grow the set of
  * cycle node ids by k rounds of "add every in- and out-neighbour of each VALID member", then invalidate every
  * valid item outside the set.  Returns the number of items invalidated, or UINT64_MAX when an id is >= size

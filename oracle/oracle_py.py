@@ -93,6 +93,11 @@ def lib():
         L.orc_run.restype = C.c_int
         L.orc_run.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p]
         L.orc_result_free.argtypes = [C.c_void_p]
+        L.orc_index_binary_search.restype = C.c_uint64
+        L.orc_index_binary_search.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_get_read.restype = C.c_uint64
+        L.orc_get_read.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, C.c_uint64, C.c_void_p]
+        L.orc_reverse_complement.argtypes = [C.c_char_p, C.c_uint64]
         L.orc_keep_regions.restype = C.c_uint64
         L.orc_keep_regions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
         L.orc_uset_order.restype = C.c_int
@@ -215,6 +220,22 @@ class OracleGraph:
         info = dict(bound_hit=c.bound_hit, cap_hit=c.cap_hit, expansions=c.expansions, steps=c.steps)
         lib().orc_cycles_free(C.byref(c))
         return paths, info
+
+    def map_reads(self, seqs, cycle_nodes, reverse=False):
+        """get_read_from_sequence (reference src/reads.cpp:56-93) per sequence (bytes/str); reverse=True applies
+        reverse_pair_ends_sequence first (:20-31, :119-123).  Returns a list of uint64 arrays (empty = dropped)."""
+        member = np.zeros(self.n, np.uint8)
+        member[np.asarray(cycle_nodes, np.int64)] = 1
+        out = []
+        for s in seqs:
+            b = s.encode() if isinstance(s, str) else bytes(s)
+            buf = C.create_string_buffer(b, len(b) + 1)
+            if reverse:
+                lib().orc_reverse_complement(buf, len(b))
+            ids = np.zeros(max(len(b), 1), np.uint64)
+            c = lib().orc_get_read(self.h, member.ctypes.data, buf, len(b), ids.ctypes.data)
+            out.append(ids[:c].copy())
+        return out
 
     def keep_regions(self, ids, k):
         """reference keep_crispr_regions_extended_by_k (src/spacer_ordering.cpp:78-139); (invalidated, kept)"""

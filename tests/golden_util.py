@@ -67,6 +67,20 @@ def region_seeds(name, params):
     return np.concatenate(paths).astype(np.uint64) if paths else np.zeros(0, np.uint64)
 
 
+def reads_case(name):
+    """tests/golden/<name>.reads.npz (tools/make_golden.py, UNMODIFIED reference get_read_from_sequence):
+    (sequences as bytes, {variant: (cycle node ids, reverse flag, offsets, flat ids)})"""
+    z = np.load(os.path.join(GOLD, f"{name}.reads.npz"))
+    seqs = bytes(z["seqs"]).split(b"\n")
+    n = load_graph_npz(name)["w"].size
+    set_a = region_seeds(name, tuple(int(x) for x in z["set_a_params"]))
+    set_b = np.nonzero(np.unpackbits(z["set_b"], bitorder="little")[:n])[0].astype(np.uint64)
+    variants = {}
+    for key, ids, rev in (("a_fwd", set_a, False), ("a_rev", set_a, True), ("b_fwd", set_b, False), ("b_rev", set_b, True)):
+        variants[key] = (ids, rev, z[key + "_off"].astype(np.int64), z[key + "_ids"].astype(np.uint64))
+    return seqs, variants
+
+
 def unpack_sdbg_files(name, dst):
     """gunzip tests/golden/<name>.sdbg/* into dst; returns the MEGAHIT file prefix."""
     src = os.path.join(GOLD, f"{name}.sdbg")

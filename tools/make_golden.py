@@ -94,6 +94,67 @@ def regions(name, prefix, tmp, params, n_items):
                            for k, v in out.items() if k != "seeds"})
 
 
+def parse_reads_dump(path):
+    raw = open(path, "rb").read()
+    assert raw[:8] == b"MCAATRDS"
+    a = np.frombuffer(raw, "<u8", offset=8)
+    n, pos, off, ids = int(a[0]), 1, [0], []
+    for _ in range(n):
+        c = int(a[pos])
+        ids.append(a[pos + 1:pos + 1 + c])
+        pos += 1 + c
+        off.append(off[-1] + c)
+    return np.array(off, np.uint64), (np.concatenate(ids) if ids else np.zeros(0, np.uint64)).astype(np.uint64)
+
+
+def reads(name, prefix, tmp, params, n_items, k):
+    """SURVEY 8(f) N3 pins: the UNMODIFIED get_read_from_sequence / reverse_pair_ends_sequence (oracle/_ref/ref_reads)
+    on real reads of the case, mutated copies (substitutions, N), random and too-short sequences, against the
+    cycle nodes of the reference run (set A) and a random half of all ids (set B, so that most reads are kept and
+    every k-mer of them is looked up)."""
+    def fastq_seqs(fq, n):
+        out = []
+        with open(fq) as f:
+            for i, line in enumerate(f):
+                if i % 4 == 1:
+                    out.append(line.strip())
+                if len(out) >= n:
+                    break
+        return out
+    rng = np.random.default_rng(1000 + sum(map(ord, name)))
+    real = fastq_seqs(os.path.join(tmp, "r1.fq"), 120) + fastq_seqs(os.path.join(tmp, "r2.fq"), 120)
+    seqs = list(real)
+    for s_ in real[:70]:
+        b = list(s_)
+        for _ in range(int(rng.integers(1, 4))):
+            b[int(rng.integers(len(b)))] = "ACGTN"[int(rng.integers(5))]
+        seqs.append("".join(b))
+    seqs += ["".join("ACGT"[int(x)] for x in rng.integers(0, 4, 150)) for _ in range(15)]
+    base = real[0]
+    seqs += ["", base[:10], base[:2 * k], base[:2 * k + 1], base[:2 * k + 2], base[:k], "N" * 60, base.lower()[:80]]
+    sf = os.path.join(tmp, "seqs.txt")
+    with open(sf, "w") as f:
+        f.write("\n".join(seqs) + "\n")
+    thr, mn, mx = params[0]
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import golden_util as G
+    set_a = G.region_seeds(name, (thr, mn, mx))
+    set_b = np.nonzero(rng.random(n_items) < 0.5)[0].astype("<u8")
+    out = dict(seqs=np.frombuffer("\n".join(seqs).encode(), np.uint8), set_a_params=np.array([thr, mn, mx]))
+    rd = os.path.join(tmp, "out.rd")
+    for key, ids, rev in (("a_fwd", set_a, 0), ("a_rev", set_a, 1), ("b_fwd", set_b, 0), ("b_rev", set_b, 1)):
+        nf = os.path.join(tmp, "nodes.u64")
+        np.asarray(ids, "<u8").tofile(nf)
+        subprocess.run([O.ref_binary("ref_reads"), prefix, rd, sf, nf, str(rev)], check=True, capture_output=True)
+        off, flat = parse_reads_dump(rd)
+        out[key + "_off"], out[key + "_ids"] = off, flat
+        print(f"    reads {key}: kept {int((np.diff(off.astype(np.int64)) > 0).sum())}/{len(seqs)}, "
+              f"null ids {int((flat == np.uint64(2**64 - 1)).sum())}/{flat.size}")
+    out["set_b_seed"] = np.array([1000 + sum(map(ord, name))])
+    out["set_b"] = np.packbits(np.isin(np.arange(n_items), set_b), bitorder="little")
+    np.savez_compressed(os.path.join(GOLD, f"{name}.reads.npz"), **out)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("cases", nargs="*", default=list(CASES))
@@ -113,6 +174,8 @@ def main():
         g = O.OracleGraph.load(prefix)
         print(f"{name}: n_items={g.n}")
         regions(name, prefix, tmp, params, g.n)
+        if keep_files:
+            reads(name, prefix, tmp, params, g.n, g.k)
         if a.regions_only:
             if not a.keep_tmp:
                 shutil.rmtree(tmp)
