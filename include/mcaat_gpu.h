@@ -197,6 +197,41 @@ typedef struct {
 int mg_valid_subgraph(mg_graph *g, mg_subgraph *out);
 void mg_subgraph_free(mg_subgraph *sg);
 
+/* ---- read -> node-id mapping --------------------------------------------------
+ * Replaces get_reads / get_read_from_sequence, reference src/reads.cpp:56-130 (declared include/reads.h:38-75),
+ * and underneath SDBG::IndexBinarySearch, libs/megahit/src/sdbg/sdbg.h:141-207.
+ *
+ * The lookup needs three things the search path does not: tip flags with a rank, the tip labels and the bucket
+ * table (prefix_look_up_, sdbg.h:36,44-46).  mg_graph_create_from_files attaches them itself; for a graph made
+ * by mg_graph_create pass them here.  tip_labels: words_per_tip_label uint32 words per tip AS STORED IN THE GRAPH
+ * FILE (sdbg_writer.cpp:45-52), tips in item order.  bucket_first/last[b]: first and last item of bucket b;
+ * (0, 0) for a bucket absent from the file and (first, first - 1) for an empty one, as sdbg.h:36-46 leaves them. */
+typedef struct {
+  int32_t memory; /* MG_MEM_HOST or MG_MEM_DEVICE, for tip and tip_labels; the bucket table is always host memory */
+  uint32_t words_per_tip_label;
+  const uint64_t *tip; /* (n+63)/64 words, as mg_graph_desc.tip */
+  const uint32_t *tip_labels;
+  uint64_t n_tips;
+  const int64_t *bucket_first, *bucket_last;
+  uint64_t n_buckets;
+} mg_kmer_index_desc;
+int mg_kmer_index_create(mg_graph *g, const mg_kmer_index_desc *d);
+
+/* One batch of reads: seqs = the sequences back to back (ASCII, no separators), read r = seqs[seq_off[r] ..
+ * seq_off[r+1]).  reverse_complement != 0 applies reverse_pair_ends_sequence (src/reads.cpp:20-31) to every
+ * read first, as get_reads does for the second FASTQ file (:119-123).  cycle_ids = nodes_of_cycles (:101-106).
+ * Result: read r maps to ids[off[r] .. off[r+1]) — len - k + 1 node ids, UINT64_MAX (kNullID) where the k-mer is
+ * not in the graph; an empty range = the reference drops the read (len <= 2k, or neither its first nor its last
+ * k-mer is a cycle node, :62-75).  get_reads' output is the non-empty ranges in read order, file 1 then file 2. */
+typedef struct {
+  uint64_t n_reads, n_kept, n_ids;
+  uint64_t *off; /* n_reads + 1 */
+  uint64_t *ids; /* n_ids */
+} mg_reads;
+int mg_map_reads(mg_graph *g, const char *seqs, const uint64_t *seq_off, uint64_t n_reads, int reverse_complement,
+                 const uint64_t *cycle_ids, uint64_t n_cycle_ids, mg_reads *out);
+void mg_reads_free(mg_reads *r);
+
 /* Device timers: CUDA-event time (ms) and launch count accumulated per kernel family since the
  * last mg_timers_reset().  names[i] are static strings.  Returns the number of entries written
  * (<= cap). */

@@ -12,7 +12,7 @@ unsigned long long g_launches = 0;
 thread_local cudaStream_t g_alloc_stream = nullptr;
 const char *kTimerNames[T_COUNT] = {"build_index", "collect_tips", "invalidate_mult1", "peel",      "nav_cache",
                                     "candidates",  "dls",          "enumerate",        "commit",    "navigate",
-                                    "keep_regions"};
+                                    "keep_regions", "map_reads"};
 
 void set_error(const char *fmt, ...) {
   va_list ap;
@@ -93,6 +93,7 @@ int mg_graph_create(const mg_graph_desc *d, mg_graph **out) {
   mg_graph *g = new (std::nothrow) mg_graph();
   if (!g) return MG_ENOMEM;
   g->device = d->device;
+  g->k = d->k;
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, d->device) == cudaSuccess) g->sm_count = prop.multiProcessorCount;
   if (cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -122,7 +123,9 @@ void mg_graph_destroy(mg_graph *g) {
   if (g->stream) cudaStreamSynchronize(g->stream);
   flush_timers(g);
   // buffers go back to the pool on the handle's stream, which must still exist
-  for (mg::DevBuf *b : {&g->wb, &g->fb, &g->mult, &g->hints, &g->inv0, &g->adj, &g->visited, &g->enum_arena}) b->release();
+  for (mg::DevBuf *b : {&g->wb, &g->fb, &g->mult, &g->hints, &g->inv0, &g->adj, &g->visited, &g->enum_arena,
+                       &g->kx_tip, &g->kx_tip_prefix, &g->kx_labels, &g->kx_buckets})
+    b->release();
   if (g->stream) cudaStreamSynchronize(g->stream);
   for (auto e : g->event_pool) cudaEventDestroy(e);
   if (g->step_a) cudaEventDestroy(g->step_a);
@@ -206,6 +209,41 @@ int mg_keep_regions(mg_graph *g, const uint64_t *ids, uint64_t n_ids, uint64_t k
   DevBuf dev;
   MG_TRY(upload_ids(g, ids, n_ids, dev));
   return run_keep_regions(g, dev.as<uint32_t>(), n_ids, k, stats);
+}
+
+int mg_kmer_index_create(mg_graph *g, const mg_kmer_index_desc *d) {
+  MG_CHECK_HANDLE(g);
+  if (!d || !d->tip || !d->bucket_first || !d->bucket_last || (d->n_tips && d->words_per_tip_label && !d->tip_labels)) return MG_EINVAL;
+  const uint64_t n_words = (g->view.n + 63) / 64;
+  DevBuf tip, lab;
+  const uint64_t *tip_dev = d->tip;
+  const uint32_t *lab_dev = d->tip_labels;
+  if (d->memory != MG_MEM_DEVICE) {
+    MG_TRY(tip.alloc(n_words * 8 + 16));
+    MG_TRY(lab.alloc((size_t)d->n_tips * d->words_per_tip_label * 4 + 16));
+    if (n_words) MG_CUDA(cudaMemcpyAsync(tip.p, d->tip, n_words * 8, cudaMemcpyHostToDevice, g->stream));
+    if (d->n_tips && d->words_per_tip_label)
+      MG_CUDA(cudaMemcpyAsync(lab.p, d->tip_labels, (size_t)d->n_tips * d->words_per_tip_label * 4, cudaMemcpyHostToDevice, g->stream));
+    tip_dev = tip.as<uint64_t>();
+    lab_dev = lab.as<uint32_t>();
+  }
+  return attach_kmer_index(g, tip_dev, lab_dev, d->n_tips, d->words_per_tip_label, d->bucket_first, d->bucket_last, d->n_buckets);
+}
+
+int mg_map_reads(mg_graph *g, const char *seqs, const uint64_t *seq_off, uint64_t n_reads, int reverse_complement,
+                 const uint64_t *cycle_ids, uint64_t n_cycle_ids, mg_reads *out) {
+  MG_CHECK_HANDLE(g);
+  if (!out || (n_reads && (!seqs || !seq_off)) || (n_cycle_ids && !cycle_ids)) return MG_EINVAL;
+  DevBuf dev;
+  MG_TRY(upload_ids(g, cycle_ids, n_cycle_ids, dev));
+  return run_map_reads(g, seqs, seq_off, n_reads, reverse_complement, dev.as<uint32_t>(), n_cycle_ids, out);
+}
+
+void mg_reads_free(mg_reads *r) {
+  if (!r) return;
+  free(r->off);
+  free(r->ids);
+  memset(r, 0, sizeof *r);
 }
 
 int mg_valid_subgraph(mg_graph *g, mg_subgraph *out) {

@@ -12,6 +12,7 @@
 
 #include "../../include/mcaat_gpu.h"
 #include "sdbg_dev.cuh"
+#include "kmer_dev.cuh"
 
 namespace mg {
 
@@ -91,6 +92,7 @@ enum TimerId {
   T_COMMIT,        // ordered commit + gather
   T_NAV,           // mg_navigate (diagnostic)
   T_REGION,        // mg_keep_regions
+  T_READS,         // mg_map_reads
   T_COUNT
 };
 extern const char *kTimerNames[T_COUNT];
@@ -108,6 +110,11 @@ struct mg_graph {
   mg::DevBuf enum_arena; // per-worker search arenas of the enumeration pipeline (grow-only)
   uint64_t enum_arena_sig = 0;  // layout the arenas were initialised for
   bool pruned = false;
+  // k-mer lookup index, optional
+  uint32_t k = 0;
+  bool has_kx = false;
+  mg::KmerIndex kx{};
+  mg::DevBuf kx_tip, kx_tip_prefix, kx_labels, kx_buckets;
   uint64_t device_bytes = 0;
   int sm_count = 148;
   // timers
@@ -175,6 +182,11 @@ int gather_mult(mg_graph *g, const uint32_t *ids_dev, uint64_t n, std::vector<ui
 // regions.cu
 int run_keep_regions(mg_graph *g, const uint32_t *ids_dev, uint64_t n_ids, uint64_t k, mg_region_stats *st);
 int run_valid_subgraph(mg_graph *g, mg_subgraph *out);
+// reads.cu
+int attach_kmer_index(mg_graph *g, const uint64_t *tip_dev, const uint32_t *labels_dev, uint64_t n_tips, uint32_t wptl,
+                      const int64_t *first_host, const int64_t *second_host, uint64_t n_buckets);
+int run_map_reads(mg_graph *g, const char *seqs, const uint64_t *seq_off, uint64_t n_reads, int reverse,
+                  const uint32_t *cycle_ids_dev, uint64_t n_cycle_ids, mg_reads *out);
 // enumerate.cu
 int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len, int max_len, mg_cycles *out);
 

@@ -24,7 +24,7 @@ struct BucketDev {
   uint64_t byte_end;    // end of the bucket's file (decoding never reads past it)
   uint64_t first_item;  // accumulate_item_count
   uint32_t n_items;
-  uint32_t pad;
+  uint32_t first_tip;   // accumulate_tip_count (sdbg_raw_content.cpp:58-60)
 };
 
 // Sub-word writes at bucket borders go through atomicOr; whole 64-bit words are stored directly.
@@ -34,12 +34,13 @@ __device__ __forceinline__ void flush_or(uint64_t *dst, uint64_t v) {
 
 __global__ void k_ingest(const uint8_t *__restrict__ raw, const BucketDev *__restrict__ buckets, uint32_t n_buckets,
                          uint32_t words_per_tip_label, uint64_t *w, uint64_t *last, uint64_t *tip, uint16_t *mult,
-                         int *bad) {
+                         uint32_t *labels, uint32_t n_tips_total, int *bad) {
   const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= n_buckets) return;
   const BucketDev B = buckets[b];
   uint64_t off = B.byte_off;
   uint64_t wacc = 0, lacc = 0, tacc = 0;
+  uint32_t tip_no = B.first_tip;
   for (uint32_t i = 0; i < B.n_items; ++i) {
     if (off + 2 > B.byte_end) { *bad = 1; return; }
     const uint64_t idx = B.first_item + i;
@@ -52,7 +53,16 @@ __global__ void k_ingest(const uint8_t *__restrict__ raw, const BucketDev *__res
       off += 2;
     }
     const uint32_t is_tip = (b0 >> 5) & 1u;
-    if (is_tip) off += (uint64_t)words_per_tip_label * 4;  // the label is not used by the hot path
+    if (is_tip) {  // the label feeds the k-mer lookup (reads.cu); words kept as stored
+      if (off + (uint64_t)words_per_tip_label * 4 > B.byte_end || tip_no >= n_tips_total) { *bad = 1; return; }
+      for (uint32_t j = 0; j < words_per_tip_label; ++j) {
+        const uint8_t *q = raw + off + 4 * j;
+        labels[(uint64_t)tip_no * words_per_tip_label + j] =
+            (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+      }
+      ++tip_no;
+      off += (uint64_t)words_per_tip_label * 4;
+    }
     mult[idx] = (uint16_t)m;
     wacc |= (uint64_t)(b0 & 15u) << ((idx & 15) * 4);
     lacc |= (uint64_t)((b0 >> 4) & 1u) << (idx & 63);
@@ -118,11 +128,16 @@ extern "C" int mg_graph_create_from_files(const char *prefix, int device, mg_gra
   memset(&d, 0, sizeof d);
   for (int i = 0; i < 6; ++i) d.f[i] = 0;
   d.f[0] = -1;
-  uint64_t n = 0;
-  std::vector<uint64_t> first_item(used.size());
+  uint64_t n = 0, n_tips = 0;
+  std::vector<uint64_t> first_item(used.size()), first_tip(used.size());
+  std::vector<int64_t> pl_first(nb, 0), pl_second(nb, 0);  // prefix_look_up_ (sdbg.h:36,44-46)
   for (size_t i = 0; i < used.size(); ++i) {
     if (used[i].bucket_id >= nb || used[i].file_id >= nf) { set_error("%s: bucket record out of range", info.c_str()); return MG_EINVAL; }
     first_item[i] = n;
+    first_tip[i] = n_tips;
+    pl_first[used[i].bucket_id] = (int64_t)n;
+    pl_second[used[i].bucket_id] = (int64_t)n + (int64_t)used[i].num_items - 1;
+    n_tips += used[i].num_tips;
     n += used[i].num_items;
     d.f[used[i].bucket_id / (nb / 4) + 2] += (int64_t)used[i].num_items;
   }
@@ -158,7 +173,7 @@ extern "C" int mg_graph_create_from_files(const char *prefix, int device, mg_gra
   g_alloc_stream = s;
   int rc = MG_OK;
   {
-    DevBuf raw, bdev, w, last, tip, mult, bad;
+    DevBuf raw, bdev, w, last, tip, mult, bad, labels;
     const size_t chunk = 64u << 20;
     uint8_t *pin[2] = {nullptr, nullptr};
     cudaEvent_t done[2] = {nullptr, nullptr};
@@ -166,7 +181,7 @@ extern "C" int mg_graph_create_from_files(const char *prefix, int device, mg_gra
       for (FILE *x : fh) if (x) fclose(x);
       for (int i = 0; i < 2; ++i) { if (pin[i]) cudaFreeHost(pin[i]); if (done[i]) cudaEventDestroy(done[i]); }
     };
-#define ING_TRY(call) do { rc = (call); if (rc != MG_OK) { cleanup(); raw.release(); bdev.release(); w.release(); last.release(); tip.release(); mult.release(); bad.release(); cudaStreamSynchronize(s); cudaStreamDestroy(s); return rc; } } while (0)
+#define ING_TRY(call) do { rc = (call); if (rc != MG_OK) { cleanup(); raw.release(); bdev.release(); w.release(); last.release(); tip.release(); mult.release(); bad.release(); labels.release(); cudaStreamSynchronize(s); cudaStreamDestroy(s); return rc; } } while (0)
     auto cuda_rc = [&](cudaError_t ce, const char *what) { if (ce != cudaSuccess) { set_error("%s -> %s", what, cudaGetErrorString(ce)); return (int)MG_ECUDA; } return (int)MG_OK; };
     ING_TRY(raw.alloc(total + 16));
     for (int i = 0; i < 2; ++i) {
@@ -192,7 +207,7 @@ extern "C" int mg_graph_create_from_files(const char *prefix, int device, mg_gra
       bh[i].byte_end = file_base[used[i].file_id + 1];
       bh[i].first_item = first_item[i];
       bh[i].n_items = (uint32_t)used[i].num_items;
-      bh[i].pad = 0;
+      bh[i].first_tip = (uint32_t)first_tip[i];
       if (used[i].num_items > 0xFFFFFFFFull || bh[i].byte_off > bh[i].byte_end) { set_error("%s: bucket %llu inconsistent", info.c_str(), (unsigned long long)used[i].bucket_id); ING_TRY(MG_EINVAL); }
     }
     const size_t w_words = (size_t)((n + 15) / 16) + 1, b_words = (size_t)((n + 63) / 64) + 1;
@@ -202,6 +217,8 @@ extern "C" int mg_graph_create_from_files(const char *prefix, int device, mg_gra
     ING_TRY(tip.alloc(b_words * 8));
     ING_TRY(mult.alloc((size_t)n * 2 + 16));
     ING_TRY(bad.alloc(16));
+    if (n_tips >= 0xFFFFFFFFull) { set_error("%s: %llu tips", info.c_str(), (unsigned long long)n_tips); ING_TRY(MG_ELIMIT); }
+    ING_TRY(labels.alloc((size_t)n_tips * wptl * 4 + 16));
     ING_TRY(cuda_rc(cudaMemsetAsync(w.p, 0, w.bytes, s), "memset"));
     ING_TRY(cuda_rc(cudaMemsetAsync(last.p, 0, last.bytes, s), "memset"));
     ING_TRY(cuda_rc(cudaMemsetAsync(tip.p, 0, tip.bytes, s), "memset"));
@@ -210,7 +227,8 @@ extern "C" int mg_graph_create_from_files(const char *prefix, int device, mg_gra
       ING_TRY(cuda_rc(cudaMemcpyAsync(bdev.p, bh.data(), bh.size() * sizeof(BucketDev), cudaMemcpyHostToDevice, s), "cudaMemcpyAsync"));
       k_ingest<<<(unsigned)((bh.size() + 63) / 64), 64, 0, s>>>(raw.as<uint8_t>(), bdev.as<BucketDev>(), (uint32_t)bh.size(),
                                                                (uint32_t)wptl, w.as<uint64_t>(), last.as<uint64_t>(),
-                                                               tip.as<uint64_t>(), mult.as<uint16_t>(), (int *)bad.p);
+                                                               tip.as<uint64_t>(), mult.as<uint16_t>(), labels.as<uint32_t>(),
+                                                               (uint32_t)n_tips, (int *)bad.p);
       ++g_launches;
       ING_TRY(cuda_rc(cudaGetLastError(), "launch k_ingest"));
     }
@@ -223,6 +241,7 @@ extern "C" int mg_graph_create_from_files(const char *prefix, int device, mg_gra
     mg_graph *g = new (std::nothrow) mg_graph();
     if (!g) ING_TRY(MG_ENOMEM);
     g->device = device;
+    g->k = (uint32_t)k;
     g->stream = s;
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) g->sm_count = prop.multiProcessorCount;
@@ -243,9 +262,12 @@ extern "C" int mg_graph_create_from_files(const char *prefix, int device, mg_gra
     d.invalid = nullptr;  // tip | (w == 0), reference sdbg.h:34,56-60
     d.mult16 = mult.as<uint16_t>();
     rc = build_graph(g, &d);
+    // the k-mer lookup index: tip flags + labels + bucket table; skipped for k beyond its limit
+    if (rc == MG_OK && (uint32_t)k <= 128)
+      rc = attach_kmer_index(g, tip.as<uint64_t>(), labels.as<uint32_t>(), n_tips, (uint32_t)wptl, pl_first.data(), pl_second.data(), nb);
     cleanup();
     if (rc != MG_OK) {
-      w.release(); last.release(); tip.release(); mult.release(); bdev.release(); bad.release();
+      w.release(); last.release(); tip.release(); mult.release(); bdev.release(); bad.release(); labels.release();
       mg_graph_destroy(g);  // also destroys the stream
       return rc;
     }

@@ -23,6 +23,7 @@ SYMBOLS = [
     "mg_navigate", "mg_prune", "mg_invalid_readback", "mg_candidates", "mg_dls", "mg_select_starts",
     "mg_bucket_starts", "mg_starts_free", "mg_find_cycles", "mg_cycles_free", "mg_visited_readback",
     "mg_keep_regions", "mg_invalid_merge", "mg_valid_subgraph", "mg_subgraph_free",
+    "mg_kmer_index_create", "mg_map_reads", "mg_reads_free",
     "mg_timers", "mg_timers_reset", "mg_step_begin", "mg_step_end", "mg_launch_count", "mg_free", "mg_last_error", "mg_version",
 ]
 
@@ -34,6 +35,15 @@ class RegionStats(C.Structure):
 class Subgraph(C.Structure):
     _fields_ = [("n_nodes", C.c_uint64), ("n_edges", C.c_uint64), ("ids", u64p), ("off", u64p),
                 ("nbr", C.POINTER(C.c_uint32))]
+
+
+class KmerIndexDesc(C.Structure):
+    _fields_ = [("memory", C.c_int32), ("words_per_tip_label", C.c_uint32), ("tip", C.c_void_p), ("tip_labels", C.c_void_p),
+                ("n_tips", C.c_uint64), ("bucket_first", C.c_void_p), ("bucket_last", C.c_void_p), ("n_buckets", C.c_uint64)]
+
+
+class Reads(C.Structure):
+    _fields_ = [("n_reads", C.c_uint64), ("n_kept", C.c_uint64), ("n_ids", C.c_uint64), ("off", u64p), ("ids", u64p)]
 
 
 class MgError(RuntimeError):
@@ -99,6 +109,11 @@ def lib():
         L.mg_find_cycles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.POINTER(Cycles)]
         L.mg_cycles_free.argtypes = [C.POINTER(Cycles)]
         L.mg_cycles_free.restype = None
+        L.mg_kmer_index_create.argtypes = [C.c_void_p, C.POINTER(KmerIndexDesc)]
+        L.mg_map_reads.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_uint64,
+                                   C.POINTER(Reads)]
+        L.mg_reads_free.argtypes = [C.POINTER(Reads)]
+        L.mg_reads_free.restype = None
         L.mg_valid_subgraph.argtypes = [C.c_void_p, C.POINTER(Subgraph)]
         L.mg_subgraph_free.argtypes = [C.POINTER(Subgraph)]
         L.mg_subgraph_free.restype = None
@@ -258,6 +273,33 @@ class DeviceGraph:
         st = RegionStats()
         _check(lib().mg_keep_regions(self.h, ids.ctypes.data, ids.size, int(k), C.byref(st)))
         return {k_: int(getattr(st, k_)) for k_, _ in RegionStats._fields_}
+
+    def set_kmer_index(self, tip_words, labels, first, second):
+        """attach the k-mer lookup index to a graph made from arrays (mg_kmer_index_create): tip bitmap words, tip
+        labels as file words [n_tips, words_per_label], bucket first/last item"""
+        tip = np.ascontiguousarray(tip_words, np.uint64)
+        labels = np.ascontiguousarray(labels, np.uint32)
+        first = np.ascontiguousarray(first, np.int64)
+        second = np.ascontiguousarray(second, np.int64)
+        d = KmerIndexDesc(0, labels.shape[1] if labels.ndim == 2 else 0, tip.ctypes.data, labels.ctypes.data,
+                          labels.shape[0], first.ctypes.data, second.ctypes.data, first.size)
+        _check(lib().mg_kmer_index_create(self.h, C.byref(d)))
+
+    def map_reads(self, seqs, cycle_ids, reverse=False):
+        """get_reads' per-file loop (reference src/reads.cpp:108-127): seqs = list of bytes/str; returns
+        (off, ids): read r -> ids[off[r]:off[r+1]], empty = dropped, 2**64-1 = k-mer not in the graph"""
+        bs = [s.encode() if isinstance(s, str) else bytes(s) for s in seqs]
+        off = np.zeros(len(bs) + 1, np.uint64)
+        if bs:
+            off[1:] = np.cumsum([len(b) for b in bs])
+        blob = b"".join(bs)
+        cyc = np.ascontiguousarray(cycle_ids, np.uint64)
+        r = Reads()
+        _check(lib().mg_map_reads(self.h, blob, off.ctypes.data, len(bs), int(reverse), cyc.ctypes.data, cyc.size, C.byref(r)))
+        o = _np(r.off, r.n_reads + 1)
+        ids = _np(r.ids, r.n_ids)
+        lib().mg_reads_free(C.byref(r))
+        return o, ids
 
     def valid_subgraph(self):
         """(ids ascending, off, nbr): the valid items and, per item, the positions of its valid out-neighbours

@@ -419,6 +419,19 @@ uint64_t orc_index_binary_search(const orc_graph *g, const uint8_t *seq) {
   }
   return ~0ull; /* kNullID */
 }
+/* raw pieces of the k-mer index, for the host build of the device code (tests/emu) */
+void orc_kmer_index_sizes(const orc_graph *g, uint64_t *n_tips, uint32_t *wptl, uint64_t *n_buckets) {
+  uint64_t t = 0;
+  for (uint64_t i = 0; i < g->n; ++i) t += g->tip[i];
+  *n_tips = g->pl_first ? t : 0; *wptl = g->wptl; *n_buckets = g->pl_first ? g->n_buckets : 0;
+}
+void orc_kmer_index_get(const orc_graph *g, uint32_t *labels, int64_t *first, int64_t *second) {
+  uint64_t t, nb; uint32_t w;
+  orc_kmer_index_sizes(g, &t, &w, &nb);
+  memcpy(labels, g->tip_labels, t * w * 4);
+  memcpy(first, g->pl_first, nb * 8);
+  memcpy(second, g->pl_second, nb * 8);
+}
 /* reads.cpp:33-54 k_mer_to_node_id: A,C,G -> 1,2,3, anything else -> 4 */
 static uint64_t kmer_node(const orc_graph *g, const char *kmer) {
   uint8_t seq[256];

@@ -109,6 +109,8 @@ void orc_result_free(orc_result *res);
 uint64_t orc_index_binary_search(const orc_graph *g, const uint8_t *seq);
 uint64_t orc_get_read(const orc_graph *g, const uint8_t *member, const char *seq, uint64_t len, uint64_t *out);
 void orc_reverse_complement(char *s, uint64_t len);
+void orc_kmer_index_sizes(const orc_graph *g, uint64_t *n_tips, uint32_t *wptl, uint64_t *n_buckets);
+void orc_kmer_index_get(const orc_graph *g, uint32_t *labels, int64_t *first, int64_t *second);
 
 /* SURVEY 8(f) N4 — keep_crispr_regions_extended_by_k (reference src/spacer_ordering.cpp:78-139): grow the set of
  * cycle node ids by k rounds of "add every in- and out-neighbour of each VALID member", then invalidate every

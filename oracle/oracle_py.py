@@ -98,6 +98,8 @@ def lib():
         L.orc_get_read.restype = C.c_uint64
         L.orc_get_read.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, C.c_uint64, C.c_void_p]
         L.orc_reverse_complement.argtypes = [C.c_char_p, C.c_uint64]
+        L.orc_kmer_index_sizes.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_kmer_index_get.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_keep_regions.restype = C.c_uint64
         L.orc_keep_regions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
         L.orc_uset_order.restype = C.c_int
@@ -220,6 +222,16 @@ class OracleGraph:
         info = dict(bound_hit=c.bound_hit, cap_hit=c.cap_hit, expansions=c.expansions, steps=c.steps)
         lib().orc_cycles_free(C.byref(c))
         return paths, info
+
+    def kmer_index(self):
+        """(tip labels as file words [n_tips, wptl], bucket first, bucket last) of a graph loaded from files"""
+        t, w, nb = C.c_uint64(0), C.c_uint32(0), C.c_uint64(0)
+        lib().orc_kmer_index_sizes(self.h, C.byref(t), C.byref(w), C.byref(nb))
+        labels = np.zeros((t.value, w.value), np.uint32)
+        first = np.zeros(nb.value, np.int64)
+        second = np.zeros(nb.value, np.int64)
+        lib().orc_kmer_index_get(self.h, labels.ctypes.data, first.ctypes.data, second.ctypes.data)
+        return labels, first, second
 
     def map_reads(self, seqs, cycle_nodes, reverse=False):
         """get_read_from_sequence (reference src/reads.cpp:56-93) per sequence (bytes/str); reverse=True applies

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "../../mcaat_b200/csrc/ball_dev.cuh"
+#include "../../mcaat_b200/csrc/kmer_dev.cuh"
 
 using namespace mg;
 
@@ -25,6 +26,11 @@ struct Emu {
   std::vector<uint32_t> hints;
   std::vector<uint64_t> adj;
   std::vector<uint32_t> visited;
+  // k-mer lookup index (N3)
+  KmerIndex kx{};
+  std::vector<uint64_t> kx_tip;
+  std::vector<uint32_t> kx_prefix, kx_labels;
+  std::vector<int64_t> kx_first, kx_second;
 };
 
 extern "C" {
@@ -263,6 +269,32 @@ void emu_keep_regions(Emu *e, const uint64_t *ids, uint64_t n_ids, uint64_t k, i
     kept_total += kept;
   }
   st[0] = added; st[1] = level; st[2] = gone; st[3] = kept_total;
+}
+
+// reads.cu's attach_kmer_index + run_map_reads with the same device functions, one "thread" at a time
+void emu_set_kmer_index(Emu *e, uint32_t k, const uint64_t *tip, const uint32_t *labels, uint64_t n_tips, uint32_t wptl,
+                        const int64_t *first, const int64_t *second, uint64_t n_buckets) {
+  const uint64_t n_words = (e->v.n + 63) / 64;
+  e->kx_tip.assign(tip, tip + n_words);
+  e->kx_prefix.assign(n_words + 1, 0);
+  uint32_t acc = 0;
+  for (uint64_t i = 0; i < n_words; ++i) { e->kx_prefix[i] = acc; acc += (uint32_t)__builtin_popcountll(tip[i]); }
+  e->kx_labels.assign(labels, labels + n_tips * wptl);
+  e->kx_labels.push_back(0);
+  e->kx_first.assign(first, first + n_buckets);
+  e->kx_second.assign(second, second + n_buckets);
+  e->kx = KmerIndex{e->kx_tip.data(), e->kx_prefix.data(), e->kx_labels.data(), wptl, (uint32_t)n_buckets,
+                    e->kx_first.data(), e->kx_second.data(), k};
+}
+// ids of one read -> out (capacity >= len); returns the count (0 = dropped); kNull ids become ~0
+uint64_t emu_map_read(Emu *e, const char *seq, uint32_t len, int reverse, const uint32_t *member, uint64_t *out) {
+  uint32_t a = kNull, b = kNull;
+  uint32_t n_out = read_ends(e->v, e->kx, seq, len, reverse != 0, member, &a, &b);
+  for (uint32_t p = 0; p < n_out; ++p) {
+    uint32_t id = read_id_at(e->v, e->kx, seq, len, reverse != 0, p, n_out, a, b);
+    out[p] = id == kNull ? ~0ull : id;
+  }
+  return n_out;
 }
 
 uint64_t emu_candidates(Emu *e, uint64_t thr, uint64_t *ids) {

@@ -10,7 +10,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "emu", "emu.cpp")
 LIB = os.path.join(HERE, "emu", "libemu.so")
-HDRS = [os.path.join(HERE, "..", "mcaat_b200", "csrc", h) for h in ("sdbg_dev.cuh", "search_dev.cuh", "ball_dev.cuh")]
+HDRS = [os.path.join(HERE, "..", "mcaat_b200", "csrc", h) for h in ("sdbg_dev.cuh", "search_dev.cuh", "ball_dev.cuh", "kmer_dev.cuh")]
 
 _lib = None
 
@@ -32,6 +32,10 @@ def lib():
         L.emu_invalid.argtypes = [C.c_void_p, C.c_void_p]
         L.emu_candidates.restype = C.c_uint64
         L.emu_keep_regions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]
+        L.emu_set_kmer_index.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32,
+                                         C.c_void_p, C.c_void_p, C.c_uint64]
+        L.emu_map_read.restype = C.c_uint64
+        L.emu_map_read.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
         L.emu_candidates.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
         L.emu_bucket.restype = C.c_int
         L.emu_bucket.argtypes = [C.c_void_p, C.c_uint64]
@@ -94,6 +98,26 @@ class EmuGraph:
         st = np.zeros(4, np.uint64)
         lib().emu_keep_regions(self.h, ids.ctypes.data, ids.size, int(k), int(reverse), st.ctypes.data)
         return dict(zip(("n_added", "levels", "n_invalidated", "n_kept"), map(int, st)))
+
+    def set_kmer_index(self, k, tip_words, labels, first, second):
+        labels = np.ascontiguousarray(labels, np.uint32)
+        self._kx = (np.ascontiguousarray(tip_words, np.uint64), labels, np.ascontiguousarray(first, np.int64),
+                    np.ascontiguousarray(second, np.int64))
+        t, l, f, s = self._kx
+        lib().emu_set_kmer_index(self.h, int(k), t.ctypes.data, l.ctypes.data, l.shape[0], l.shape[1] if l.ndim == 2 else 0,
+                                 f.ctypes.data, s.ctypes.data, f.size)
+
+    def map_reads(self, seqs, cycle_nodes, reverse=False):
+        member = np.zeros((self.n + 31) // 32 + 1, np.uint32)
+        ids = np.asarray(cycle_nodes, np.int64)
+        np.bitwise_or.at(member, ids >> 5, (np.uint32(1) << (ids & 31).astype(np.uint32)))
+        out = []
+        for s in seqs:
+            b = s.encode() if isinstance(s, str) else bytes(s)
+            buf = np.zeros(max(len(b), 1), np.uint64)
+            c = lib().emu_map_read(self.h, b, len(b), int(reverse), member.ctypes.data, buf.ctypes.data)
+            out.append(buf[:c].copy())
+        return out
 
     def candidates(self, thr):
         ids = np.empty(self.n, np.uint64)

@@ -158,3 +158,18 @@ def test_region_extraction_matches_reference(name, key, params, k):
         assert np.array_equal(g.invalid(), want)
         assert st["n_invalidated"] == int((want & ~before).sum()) and st["n_kept"] == int((~want).sum())
         assert st["levels"] <= max(k, 0)
+
+
+@pytest.mark.parametrize("name", ["tiny", "biallelic"])
+def test_read_mapping_matches_reference(tmp_path, name):
+    """index_binary_search / read_ends / read_id_at (kmer_dev.cuh, the code k_read_ends and
+    k_read_kmers run) against the UNMODIFIED reference get_read_from_sequence (tests/golden/<name>.reads.npz)."""
+    og = O.OracleGraph.load(G.unpack_sdbg_files(name, str(tmp_path)))
+    labels, first, second = og.kmer_index()
+    g = emu(name)
+    g.set_kmer_index(og.k, _cache[name]["tip"], labels, first, second)
+    seqs, variants = G.reads_case(name)
+    for key, (ids, rev, off, flat) in variants.items():
+        got = g.map_reads(seqs, ids, reverse=rev)
+        assert [x.size for x in got] == list(np.diff(off)), key
+        assert np.array_equal(np.concatenate(got), flat), key

@@ -334,3 +334,44 @@ def test_cpp_drop_in_scc_split_matches_reference(tmp_path, name):
         at = want.index(b"MCAATSCC")
         n_sub.append(int(np.frombuffer(want, "<u8", 1, at + 8)[0]))
     assert max(n_sub) >= 2
+
+
+# ------------------------------------------------------------------ read -> node ids
+@pytest.mark.parametrize("name", ["tiny", "biallelic"])
+@pytest.mark.parametrize("via", ["files", "arrays"])
+def test_read_mapping_matches_reference(tmp_path, name, via):
+    """mg_map_reads against the UNMODIFIED reference get_read_from_sequence / reverse_pair_ends_sequence /
+    IndexBinarySearch (src/reads.cpp:20-93, sdbg.h:141-207; tests/golden/<name>.reads.npz): real, mutated, random,
+    N-containing and too-short sequences, forward and reverse-complemented, two node sets.  The k-mer index comes
+    from the graph files (mg_graph_create_from_files) or is attached to an array-built graph."""
+    prefix = G.unpack_sdbg_files(name, str(tmp_path))
+    if via == "files":
+        g = DeviceGraph.from_files(prefix)
+    else:
+        g = DeviceGraph(packed(name))
+        with pytest.raises(gpu.MgError):
+            g.map_reads([b"ACGT" * 30], [1])
+        labels, first, second = O.OracleGraph.load(prefix).kmer_index()
+        g.set_kmer_index(packed(name)["tip"], labels, first, second)
+    seqs, variants = G.reads_case(name)
+    for key, (ids, rev, off, flat) in variants.items():
+        launches = gpu.launch_count()
+        got_off, got_ids = g.map_reads(seqs, ids, reverse=rev)
+        assert gpu.launch_count() > launches
+        assert np.array_equal(got_off.astype(np.int64), off), key
+        assert np.array_equal(got_ids, flat), key
+    # the search path is untouched by the index: same result as the reference dump
+    if via == "files" and name == "tiny":
+        _, thr, mn, mx, dump = [c for c in G.cases() if c[0] == "tiny" and c[1] == 20][0]
+        assert O.same_run(O.parse_dump(dump), run_gpu(g, thr, mn, mx)) == []
+
+
+def test_read_mapping_edge_cases(tmp_path):
+    g = DeviceGraph.from_files(G.unpack_sdbg_files("tiny", str(tmp_path)))
+    off, ids = g.map_reads([], [1, 2, 3])
+    assert off.tolist() == [0] and ids.size == 0
+    seqs, variants = G.reads_case("tiny")
+    off, ids = g.map_reads(seqs, [])  # no cycle nodes: every read is dropped
+    assert off.max() == 0 and ids.size == 0
+    with pytest.raises(gpu.MgError):
+        g.map_reads(seqs[:3], [g.n])
