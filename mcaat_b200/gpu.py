@@ -288,14 +288,18 @@ class DeviceGraph:
     def map_reads(self, seqs, cycle_ids, reverse=False):
         """get_reads' per-file loop (reference src/reads.cpp:108-127): seqs = list of bytes/str; returns
         (off, ids): read r -> ids[off[r]:off[r+1]], empty = dropped, 2**64-1 = k-mer not in the graph"""
-        bs = [s.encode() if isinstance(s, str) else bytes(s) for s in seqs]
-        off = np.zeros(len(bs) + 1, np.uint64)
-        if bs:
-            off[1:] = np.cumsum([len(b) for b in bs])
-        blob = b"".join(bs)
+        if isinstance(seqs, tuple):  # (uint8 array of all characters, uint64 offsets): no per-read Python objects
+            chars, off = np.ascontiguousarray(seqs[0], np.uint8), np.ascontiguousarray(seqs[1], np.uint64)
+            blob, n_reads = chars.ctypes.data_as(C.c_char_p), off.size - 1
+        else:
+            bs = [s.encode() if isinstance(s, str) else bytes(s) for s in seqs]
+            off = np.zeros(len(bs) + 1, np.uint64)
+            if bs:
+                off[1:] = np.cumsum([len(b) for b in bs])
+            blob, n_reads = b"".join(bs), len(bs)
         cyc = np.ascontiguousarray(cycle_ids, np.uint64)
         r = Reads()
-        _check(lib().mg_map_reads(self.h, blob, off.ctypes.data, len(bs), int(reverse), cyc.ctypes.data, cyc.size, C.byref(r)))
+        _check(lib().mg_map_reads(self.h, blob, off.ctypes.data, n_reads, int(reverse), cyc.ctypes.data, cyc.size, C.byref(r)))
         o = _np(r.off, r.n_reads + 1)
         ids = _np(r.ids, r.n_ids)
         lib().mg_reads_free(C.byref(r))

@@ -311,6 +311,39 @@ WORKLOADS = {
 }
 
 
+def sample_reads(name, n_reads, seed=1, read_len=150, error_rate=0.002):
+    """Reads of the community of workload `name` for the read-mapping stage: n_reads windows of
+    read_len bases drawn in proportion to each genome's share of the sequencing, either strand, with substitution
+    errors at `error_rate`.  Returns (uint8 ASCII array of n_reads * read_len characters, uint64 offsets)."""
+    import argparse
+
+    import gen_reads
+    cfg = WORKLOADS[name]
+    p = argparse.ArgumentParser()
+    for arg, kw in gen_reads.ARGSPEC:
+        p.add_argument(arg, **kw)
+    args = p.parse_args(["--out", "-", "--seed", str(cfg["seed"])] + list(cfg["argv"]))
+    genomes, abund, _ = gen_reads.build_community(args, np.random.Generator(np.random.PCG64(cfg["seed"])))
+    lens = np.array([g.size for g in genomes], np.float64)
+    share = abund * lens / float((abund * lens).sum())
+    rng = np.random.default_rng(seed)
+    which = rng.choice(len(genomes), n_reads, p=share)
+    out = np.empty((n_reads, read_len), np.uint8)
+    comp = np.arange(256, dtype=np.uint8)
+    for a, b in zip(b"ACGT", b"TGCA"):
+        comp[a] = b
+    for gi in np.unique(which):
+        rows = np.nonzero(which == gi)[0]
+        start = rng.integers(0, genomes[gi].size - read_len, rows.size)
+        win = genomes[gi][start[:, None] + np.arange(read_len)[None, :]]
+        flip = rng.random(rows.size) < 0.5
+        win[flip] = comp[win[flip][:, ::-1]]
+        out[rows] = win
+    err = rng.random(out.shape) < error_rate
+    out[err] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, int(err.sum()))]
+    return out.reshape(-1), np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(read_len)
+
+
 def make_workload(name, device="cpu", want_labels=False):
     cfg = WORKLOADS[name]
     e, c, info = community_spectrum(cfg["argv"], cfg["total_bases"], cfg["error_events"], cfg["seed"], device)
