@@ -216,6 +216,7 @@ typedef struct {
   uint64_t n_buckets;
 } mg_kmer_index_desc;
 int mg_kmer_index_create(mg_graph *g, const mg_kmer_index_desc *d);
+int mg_graph_has_kmer_index(const mg_graph *g); /* 1 / 0 */
 
 /* One batch of reads: seqs = the sequences back to back (ASCII, no separators), read r = seqs[seq_off[r] ..
  * seq_off[r+1]).  reverse_complement != 0 applies reverse_pair_ends_sequence (src/reads.cpp:20-31) to every

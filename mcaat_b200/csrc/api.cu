@@ -230,6 +230,8 @@ int mg_kmer_index_create(mg_graph *g, const mg_kmer_index_desc *d) {
   return attach_kmer_index(g, tip_dev, lab_dev, d->n_tips, d->words_per_tip_label, d->bucket_first, d->bucket_last, d->n_buckets);
 }
 
+int mg_graph_has_kmer_index(const mg_graph *g) { return g && g->has_kx ? 1 : 0; }
+
 int mg_map_reads(mg_graph *g, const char *seqs, const uint64_t *seq_off, uint64_t n_reads, int reverse_complement,
                  const uint64_t *cycle_ids, uint64_t n_cycle_ids, mg_reads *out) {
   MG_CHECK_HANDLE(g);

@@ -23,7 +23,7 @@ SYMBOLS = [
     "mg_navigate", "mg_prune", "mg_invalid_readback", "mg_candidates", "mg_dls", "mg_select_starts",
     "mg_bucket_starts", "mg_starts_free", "mg_find_cycles", "mg_cycles_free", "mg_visited_readback",
     "mg_keep_regions", "mg_invalid_merge", "mg_valid_subgraph", "mg_subgraph_free",
-    "mg_kmer_index_create", "mg_map_reads", "mg_reads_free",
+    "mg_kmer_index_create", "mg_graph_has_kmer_index", "mg_map_reads", "mg_reads_free",
     "mg_timers", "mg_timers_reset", "mg_step_begin", "mg_step_end", "mg_launch_count", "mg_free", "mg_last_error", "mg_version",
 ]
 
@@ -109,6 +109,7 @@ def lib():
         L.mg_find_cycles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.POINTER(Cycles)]
         L.mg_cycles_free.argtypes = [C.POINTER(Cycles)]
         L.mg_cycles_free.restype = None
+        L.mg_graph_has_kmer_index.argtypes = [C.c_void_p]
         L.mg_kmer_index_create.argtypes = [C.c_void_p, C.POINTER(KmerIndexDesc)]
         L.mg_map_reads.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_uint64,
                                    C.POINTER(Reads)]

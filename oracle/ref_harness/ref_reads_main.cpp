@@ -19,6 +19,13 @@
 #include "reads.h"
 #include "dump_format.h"
 
+#ifdef MCAAT_READS_VIA_GPU_DROP_IN  // mcaat_b200/host/Makefile: the same main over mcaat_b200/host/reads_gpu.cpp
+namespace mcaat_gpu {
+std::vector<std::vector<uint64_t>> map_sequences_all(const SDBG &sdbg, const std::vector<std::string> &seqs, bool reverse,
+                                                     const std::vector<std::vector<uint64_t>> &cycles);
+}
+#endif
+
 int main(int argc, char **argv) {
   if (argc < 5) {
     fprintf(stderr, "usage: %s <sdbg_prefix> <out.rd> <sequences.txt> <cycle_nodes.u64> [reverse]\n", argv[0]);
@@ -43,7 +50,19 @@ int main(int argc, char **argv) {
   if (!f) return 2;
   fwrite("MCAATRDS", 8, 1, f);
   dump_u64(f, seqs.size());
+  const size_t n_seqs = seqs.size();
   uint64_t kept = 0, ids = 0;
+#ifdef MCAAT_READS_VIA_GPU_DROP_IN
+  {
+    std::vector<std::vector<uint64_t>> cyc(1, std::vector<uint64_t>(nodes_of_cycles.begin(), nodes_of_cycles.end()));
+    for (auto &read : mcaat_gpu::map_sequences_all(g, seqs, reverse, cyc)) {
+      dump_vec(f, read);
+      kept += !read.empty();
+      ids += read.size();
+    }
+    seqs.clear();
+  }
+#endif
   for (auto &s : seqs) {
     std::string q = s;
     if (reverse) reverse_pair_ends_sequence(q);
@@ -54,6 +73,6 @@ int main(int argc, char **argv) {
   }
   fclose(f);
   printf("REF_JSON {\"n_items\": %llu, \"sequences\": %zu, \"kept\": %llu, \"ids\": %llu}\n", (unsigned long long)g.size(),
-         seqs.size(), (unsigned long long)kept, (unsigned long long)ids);
+         n_seqs, (unsigned long long)kept, (unsigned long long)ids);
   return 0;
 }

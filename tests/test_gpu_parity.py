@@ -375,3 +375,41 @@ def test_read_mapping_edge_cases(tmp_path):
     assert off.max() == 0 and ids.size == 0
     with pytest.raises(gpu.MgError):
         g.map_reads(seqs[:3], [g.n])
+
+
+@pytest.mark.parametrize("name", ["tiny", "biallelic"])
+def test_cpp_drop_in_read_mapping_matches_reference(tmp_path, name):
+    """mcaat_b200/host/reads_gpu.cpp (map_sequences_all, the body of the get_reads drop-in) under the read harness
+    main: same per-sequence node ids as the unmodified reference get_read_from_sequence."""
+    import os
+    import subprocess
+    exe = os.path.join(gpu.ROOT, "mcaat_b200", "host", "_build", "shim_reads")
+    if not os.path.exists(exe):
+        pytest.skip("shim_reads not built (needs the reference headers at build time)")
+    prefix = G.unpack_sdbg_files(name, str(tmp_path))
+    seqs, variants = G.reads_case(name)
+    sf = str(tmp_path / "seqs.txt")
+    with open(sf, "wb") as f:
+        f.write(b"\n".join(seqs) + b"\n")
+    env = dict(os.environ, MCAAT_GPU_GRAPH_PREFIX=prefix)
+    for key, (ids, rev, off, flat) in variants.items():
+        nf = str(tmp_path / (key + ".u64"))
+        np.asarray(ids, "<u8").tofile(nf)
+        out = str(tmp_path / (key + ".rd"))
+        subprocess.run([exe, prefix, out, sf, nf, "1" if rev else "0"], check=True, capture_output=True, env=env)
+        raw = open(out, "rb").read()
+        assert raw[:8] == b"MCAATRDS"
+        a = np.frombuffer(raw, "<u8", offset=8)
+        assert int(a[0]) == len(seqs)
+        pos, got_off, got = 1, [0], []
+        for _ in range(len(seqs)):
+            c = int(a[pos])
+            got.append(a[pos + 1:pos + 1 + c])
+            pos += 1 + c
+            got_off.append(got_off[-1] + c)
+        assert got_off == off.tolist(), key
+        assert np.array_equal(np.concatenate(got), flat), key
+    # without the index source the drop-in refuses instead of falling back
+    env.pop("MCAAT_GPU_GRAPH_PREFIX")
+    r = subprocess.run([exe, prefix, out, sf, nf, "0"], capture_output=True, env=env)
+    assert r.returncode != 0
