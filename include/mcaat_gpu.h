@@ -182,7 +182,7 @@ typedef struct {
 int mg_keep_regions(mg_graph *g, const uint64_t *ids, uint64_t n_ids, uint64_t k, mg_region_stats *stats);
 
 /* The valid part of the graph in compact form — the input of the reference's SCC split
- * (find_strongly_connected_components src/spacer_ordering.cpp:44-76 walks `for node < size: IsValidEdge` and
+ * (find_strongly_connected_components src/spacer_ordering.cpp:54-76 walks `for node < size: IsValidEdge` and
  * calls OutgoingEdges per node; divide_graph_into_subgraphs :141-175 does so again per component).
  * ids[0..n_nodes): valid item ids, ascending.  Row i = nbr[off[i]..off[i+1]): positions in `ids` of the valid
  * out-neighbours of ids[i], in OutgoingEdges order (descending id, sdbg.h:296-320).  Arrays are library
@@ -198,7 +198,7 @@ int mg_valid_subgraph(mg_graph *g, mg_subgraph *out);
 void mg_subgraph_free(mg_subgraph *sg);
 
 /* ---- read -> node-id mapping --------------------------------------------------
- * Replaces get_reads / get_read_from_sequence, reference src/reads.cpp:56-130 (declared include/reads.h:38-75),
+ * Replaces get_reads / get_read_from_sequence, reference src/reads.cpp:57-130 (declared include/reads.h:38-75),
  * and underneath SDBG::IndexBinarySearch, libs/megahit/src/sdbg/sdbg.h:141-207.
  *
  * The lookup needs three things the search path does not: tip flags with a rank, the tip labels and the bucket
@@ -220,10 +220,10 @@ int mg_graph_has_kmer_index(const mg_graph *g); /* 1 / 0 */
 
 /* One batch of reads: seqs = the sequences back to back (ASCII, no separators), read r = seqs[seq_off[r] ..
  * seq_off[r+1]).  reverse_complement != 0 applies reverse_pair_ends_sequence (src/reads.cpp:20-31) to every
- * read first, as get_reads does for the second FASTQ file (:119-123).  cycle_ids = nodes_of_cycles (:101-106).
+ * read first, as get_reads does for the second FASTQ file (:119-121).  cycle_ids = nodes_of_cycles (:98-103).
  * Result: read r maps to ids[off[r] .. off[r+1]) — len - k + 1 node ids, UINT64_MAX (kNullID) where the k-mer is
  * not in the graph; an empty range = the reference drops the read (len <= 2k, or neither its first nor its last
- * k-mer is a cycle node, :62-75).  get_reads' output is the non-empty ranges in read order, file 1 then file 2. */
+ * k-mer is a cycle node, :64-77).  get_reads' output is the non-empty ranges in read order, file 1 then file 2. */
 typedef struct {
   uint64_t n_reads, n_kept, n_ids;
   uint64_t *off; /* n_reads + 1 */

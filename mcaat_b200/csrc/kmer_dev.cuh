@@ -1,6 +1,6 @@
 // SURVEY 8(f) N3 — k-mer -> node id and read -> node ids, device functions (also compiled for the host by
 // tests/emu).  Reference: SDBG::IndexBinarySearch (libs/megahit/src/sdbg/sdbg.h:141-207), k_mer_to_node_id,
-// reverse_pair_ends_sequence and get_read_from_sequence (src/reads.cpp:20-93).
+// reverse_pair_ends_sequence and get_read_from_sequence (src/reads.cpp:20-89).
 #pragma once
 #include "sdbg_dev.cuh"
 
@@ -86,7 +86,7 @@ MG_HD uint32_t index_binary_search(const GraphView &g, const KmerIndex &K, const
   return kNull;
 }
 
-// k_mer_to_node_id's alphabet (src/reads.cpp:41-52): A, C, G -> 1, 2, 3, anything else -> 4; with `reverse` the
+// k_mer_to_node_id's alphabet (src/reads.cpp:44-52): A, C, G -> 1, 2, 3, anything else -> 4; with `reverse` the
 // complement of reverse_pair_ends_sequence (:23-30: A<->T, C<->G, other characters unchanged) is applied first.
 MG_HD uint8_t base_code(char c, bool reverse) {
   if (reverse) return c == 'T' ? 1 : c == 'G' ? 2 : c == 'C' ? 3 : 4;
@@ -106,20 +106,20 @@ MG_HD uint32_t lookup_at(const GraphView &g, const KmerIndex &K, const char *seq
   return index_binary_search(g, K, codes);
 }
 MG_HD bool member_get(const uint32_t *bm, uint32_t i) { return (bm[i >> 5] >> (i & 31)) & 1; }
-// get_read_from_sequence, first half (src/reads.cpp:62-75): number of ids the read maps to (0 = dropped) and the
+// get_read_from_sequence, first half (src/reads.cpp:64-77): number of ids the read maps to (0 = dropped) and the
 // ids of its first and last k-mer
 MG_HD uint32_t read_ends(const GraphView &g, const KmerIndex &K, const char *seq, uint32_t len, bool reverse,
                          const uint32_t *member, uint32_t *first_id, uint32_t *last_id) {
-  if (len <= 2 * K.k) return 0;  // :62-64
+  if (len <= 2 * K.k) return 0;  // :64-66
   const uint32_t s = lookup_at(g, K, seq, len, 0, reverse);
   const uint32_t e = lookup_at(g, K, seq, len, len - K.k, reverse);
   const bool in_s = s != kNull && member_get(member, s), in_e = e != kNull && member_get(member, e);
-  if (!in_s && !in_e) return 0;  // :72-75
+  if (!in_s && !in_e) return 0;  // :74-77
   *first_id = s;
   *last_id = e;
   return len - K.k + 1;
 }
-// second half (:77-90): id number p of a kept read
+// second half (:79-87): id number p of a kept read
 MG_HD uint32_t read_id_at(const GraphView &g, const KmerIndex &K, const char *seq, uint32_t len, bool reverse, uint32_t p,
                           uint32_t n_out, uint32_t first_id, uint32_t last_id) {
   if (p == 0) return first_id;

@@ -1,12 +1,12 @@
 // SURVEY 8(f) N3 — read -> node-id mapping on the device: get_reads / get_read_from_sequence, reference
-// src/reads.cpp:56-130, on top of SDBG::IndexBinarySearch (sdbg.h:141-207).  The reference handles one read after
+// src/reads.cpp:57-130, on top of SDBG::IndexBinarySearch (sdbg.h:141-207).  The reference handles one read after
 // the other on one core: two k-mer lookups decide whether the read touches a cycle node, then every k-mer of a kept
 // read is looked up; a lookup is a binary search over a bucket of the graph whose every probe walks up to k
 // Backward steps (rank/select).  Here one thread does one lookup and all lookups of a batch run concurrently:
-//   k_member_bits   cycle node ids -> n-bit membership bitmap (nodes_of_cycles, :101-106)
-//   k_read_ends     one thread per read: length rule (:62-64), first/last k-mer (:66-70), membership (:72-75)
+//   k_member_bits   cycle node ids -> n-bit membership bitmap (nodes_of_cycles, :98-103)
+//   k_read_ends     one thread per read: length rule (:64-66), first/last k-mer (:68-72), membership (:74-77)
 //   (scan)          ids per kept read = len - k + 1 -> output offsets
-//   k_read_kmers    one thread per output id: the remaining k-mers (:78-83)
+//   k_read_kmers    one thread per output id: the remaining k-mers (:80-85)
 // Latency-bound pointer chasing through the succinct index (≈ log2(bucket) probes x up to k Backward steps of
 // ≈ 3 dependent loads); the machine is filled with independent lookups instead of shortening one.
 #include <vector>

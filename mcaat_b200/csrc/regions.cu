@@ -223,7 +223,7 @@ int run_keep_regions(mg_graph *g, const uint32_t *ids_dev, uint64_t n_ids, uint6
 }
 
 // ------------------------------------------------------------------ valid subgraph (input of the SCC split)
-// divide_graph_into_subgraphs / find_strongly_connected_components (reference src/spacer_ordering.cpp:44-76,
+// divide_graph_into_subgraphs / find_strongly_connected_components (reference src/spacer_ordering.cpp:54-76,
 // 141-175) walk every item of the graph with IsValidEdge and call OutgoingEdges per valid node through hash
 // maps.  After region extraction only a sliver of the graph is valid, so the device compacts it: ascending
 // valid ids and, per valid node, the positions (in that list) of its valid out-neighbours in OutgoingEdges

@@ -287,7 +287,7 @@ class DeviceGraph:
         _check(lib().mg_kmer_index_create(self.h, C.byref(d)))
 
     def map_reads(self, seqs, cycle_ids, reverse=False):
-        """get_reads' per-file loop (reference src/reads.cpp:108-127): seqs = list of bytes/str; returns
+        """get_reads' per-file loop (reference src/reads.cpp:105-127): seqs = list of bytes/str; returns
         (off, ids): read r -> ids[off[r]:off[r+1]], empty = dropped, 2**64-1 = k-mer not in the graph"""
         if isinstance(seqs, tuple):  # (uint8 array of all characters, uint64 offsets): no per-read Python objects
             chars, off = np.ascontiguousarray(seqs[0], np.uint8), np.ascontiguousarray(seqs[1], np.uint64)
@@ -308,7 +308,7 @@ class DeviceGraph:
 
     def valid_subgraph(self):
         """(ids ascending, off, nbr): the valid items and, per item, the positions of its valid out-neighbours
-        in OutgoingEdges order — what the reference's SCC split walks (src/spacer_ordering.cpp:44-76,141-175)."""
+        in OutgoingEdges order — what the reference's SCC split walks (src/spacer_ordering.cpp:54-76,141-175)."""
         sg = Subgraph()
         _check(lib().mg_valid_subgraph(self.h, C.byref(sg)))
         ids = _np(sg.ids, sg.n_nodes)

@@ -1,7 +1,7 @@
-// Drop-in for the reference's get_reads (reference src/reads.cpp:95-130, declared include/reads.h:70-75): same
+// Drop-in for the reference's get_reads (reference src/reads.cpp:91-130, declared include/reads.h:70-75): same
 // arguments, same result — for every FASTQ sequence that the reference keeps (longer than 2k and starting or
-// ending on a cycle node, :62-75) the node ids of all its k-mers, file 1 in order and then file 2 reverse-
-// complemented (:119-123).  The k-mer lookups (SDBG::IndexBinarySearch, sdbg.h:141-207) run on the GPU
+// ending on a cycle node, :64-77) the node ids of all its k-mers, file 1 in order and then file 2 reverse-
+// complemented (:119-121).  The k-mer lookups (SDBG::IndexBinarySearch, sdbg.h:141-207) run on the GPU
 // (mg_map_reads, include/mcaat_gpu.h); FASTQ parsing stays the reference's own extract_sequences_from_fastq_file
 // (:3-18, kseq++).  No CPU fallback: a C-ABI error becomes std::runtime_error.
 //
@@ -11,7 +11,7 @@
 // (settings.graph_folder after src/main.cpp:522-530) and the graph is read from them for this call.
 //
 // Adoption: call mcaat_gpu::get_reads where the reference calls get_reads
-// (src/main_run_and_debug.cpp:12), or delete src/reads.cpp:95-130 and compile this file with
+// (src/main_run_and_debug.cpp:11-16), or delete src/reads.cpp:91-130 and compile this file with
 // -DMCAAT_GPU_DEFINE_REFERENCE_SYMBOLS.
 #include <cstdint>
 #include <cstdlib>
@@ -73,7 +73,7 @@ std::vector<std::vector<uint64_t>> map_sequences_all(const SDBG &sdbg, const std
   return out;
 }
 
-// reference get_reads, :95-130
+// reference get_reads, :91-130
 std::vector<std::vector<uint64_t>> get_reads(const SDBG &sdbg, const std::string &fastq_file_1,
                                              const std::optional<std::string> &fastq_file_2,
                                              const std::vector<std::vector<uint64_t>> cycles) {
@@ -81,7 +81,7 @@ std::vector<std::vector<uint64_t>> get_reads(const SDBG &sdbg, const std::string
   auto append = [&](const std::string &path, bool reverse) {
     std::vector<std::string> sequences = extract_sequences_from_fastq_file(path);  // the reference's parser
     for (auto &read : map_sequences_all(sdbg, sequences, reverse, cycles))
-      if (!read.empty()) reads.push_back(std::move(read));  // :112-114, :124-126
+      if (!read.empty()) reads.push_back(std::move(read));  // :110-112, :123-125
   };
   append(fastq_file_1, false);
   if (fastq_file_2.has_value()) append(fastq_file_2.value(), true);

@@ -83,7 +83,7 @@ void keep_crispr_regions_extended_by_k(SDBG &sdbg, const size_t &k, const std::v
   if (own) mg_graph_destroy(g);
 }
 
-// reference find_strongly_connected_components (:60-76) + _dfs (:3-58) on the compact rows: components with
+// reference find_strongly_connected_components (:54-76) + _dfs (:3-52) on the compact rows: components with
 // more than one node, in completion order, nodes in stack-pop order.  Positions, not ids.
 static std::vector<std::vector<uint32_t>> tarjan(const mg_subgraph &sg) {
   const uint32_t n = (uint32_t)sg.n_nodes, kNone = 0xFFFFFFFFu;
@@ -94,7 +94,7 @@ static std::vector<std::vector<uint32_t>> tarjan(const mg_subgraph &sg) {
   std::vector<Frame> call;
   std::vector<std::vector<uint32_t>> comps;
   uint32_t counter = 0;
-  for (uint32_t root = 0; root < n; ++root) {  // valid nodes in ascending id order (:62-73)
+  for (uint32_t root = 0; root < n; ++root) {  // valid nodes in ascending id order (:60-73)
     if (index[root] != kNone) continue;
     index[root] = low[root] = counter++;
     stack.push_back(root);
@@ -105,17 +105,17 @@ static std::vector<std::vector<uint32_t>> tarjan(const mg_subgraph &sg) {
       const uint32_t v = f.v;
       if (f.e < sg.off[v + 1]) {
         const uint32_t w = sg.nbr[f.e++];
-        if (index[w] == kNone) {  // :24-26 — the recursive call; lowlink is folded in when it returns
+        if (index[w] == kNone) {  // :30-32 — the recursive call; lowlink is folded in when it returns
           index[w] = low[w] = counter++;
           stack.push_back(w);
           on_stack[w] = 1;
           call.push_back({w, sg.off[w]});
-        } else if (on_stack[w]) {  // :27-29
+        } else if (on_stack[w]) {  // :30-32
           low[v] = std::min(low[v], index[w]);
         }
         continue;
       }
-      if (low[v] == index[v]) {  // :36-50
+      if (low[v] == index[v]) {  // :38-51
         std::vector<uint32_t> comp;
         uint32_t w;
         do {
@@ -127,7 +127,7 @@ static std::vector<std::vector<uint32_t>> tarjan(const mg_subgraph &sg) {
         if (comp.size() > 1) comps.push_back(std::move(comp));
       }
       call.pop_back();
-      if (!call.empty()) low[call.back().v] = std::min(low[call.back().v], low[v]);  // :26 after the return
+      if (!call.empty()) low[call.back().v] = std::min(low[call.back().v], low[v]);  // :29 after the return
     }
   }
   return comps;

@@ -432,7 +432,7 @@ void orc_kmer_index_get(const orc_graph *g, uint32_t *labels, int64_t *first, in
   memcpy(first, g->pl_first, nb * 8);
   memcpy(second, g->pl_second, nb * 8);
 }
-/* reads.cpp:33-54 k_mer_to_node_id: A,C,G -> 1,2,3, anything else -> 4 */
+/* reads.cpp:33-55 k_mer_to_node_id: A,C,G -> 1,2,3, anything else -> 4 */
 static uint64_t kmer_node(const orc_graph *g, const char *kmer) {
   uint8_t seq[256];
   for (uint32_t i = 0; i < g->k; ++i) seq[i] = kmer[i] == 'A' ? 1 : kmer[i] == 'C' ? 2 : kmer[i] == 'G' ? 3 : 4;
@@ -444,7 +444,7 @@ void orc_reverse_complement(char *s, uint64_t len) {
   for (uint64_t i = 0; i < len; ++i)
     s[i] = s[i] == 'A' ? 'T' : s[i] == 'T' ? 'A' : s[i] == 'C' ? 'G' : s[i] == 'G' ? 'C' : s[i];
 }
-/* reads.cpp:56-93 get_read_from_sequence; member = nodes_of_cycles as a byte per item.  Returns the number of
+/* reads.cpp:57-89 get_read_from_sequence; member = nodes_of_cycles as a byte per item.  Returns the number of
  * ids written to out (capacity >= len), 0 = the read is dropped. */
 uint64_t orc_get_read(const orc_graph *g, const uint8_t *member, const char *seq, uint64_t len, uint64_t *out) {
   const uint64_t K = g->k;

@@ -11,7 +11,9 @@
  * vector for this path (its tests/ cover only reads and set cover), so the pins are dumps of the
  * UNMODIFIED reference CycleFinder compiled by oracle/Makefile into oracle/_ref/ and run at
  * threads=1 on seeded synthetic graphs; they are committed under tests/golden/ together with the
- * script that made them (tools/make_golden.py).
+ * script that made them (tools/make_golden.py).  The "next" stages restated further down (read mapping,
+ * region extraction) are pinned the same way: oracle/_ref/ref_reads and oracle/_ref/ref_regions are the
+ * reference's src/reads.cpp and src/spacer_ordering.cpp compiled unmodified.
  */
 #ifndef MCAAT_ORACLE_H
 #define MCAAT_ORACLE_H
@@ -105,7 +107,7 @@ void orc_result_free(orc_result *res);
  * are not part of orc_from_arrays).  Pinned against the compiled reference functions: oracle/_ref/ref_reads,
  * tests/golden/<case>.reads.npz.
  * orc_index_binary_search: SDBG::IndexBinarySearch (sdbg.h:141-207), seq[0..k) in 1..4; ~0 = kNullID.
- * orc_get_read: get_read_from_sequence (src/reads.cpp:56-93); orc_reverse_complement: :20-31. */
+ * orc_get_read: get_read_from_sequence (src/reads.cpp:57-89); orc_reverse_complement: :20-31. */
 uint64_t orc_index_binary_search(const orc_graph *g, const uint8_t *seq);
 uint64_t orc_get_read(const orc_graph *g, const uint8_t *member, const char *seq, uint64_t len, uint64_t *out);
 void orc_reverse_complement(char *s, uint64_t len);

@@ -234,8 +234,8 @@ class OracleGraph:
         return labels, first, second
 
     def map_reads(self, seqs, cycle_nodes, reverse=False):
-        """get_read_from_sequence (reference src/reads.cpp:56-93) per sequence (bytes/str); reverse=True applies
-        reverse_pair_ends_sequence first (:20-31, :119-123).  Returns a list of uint64 arrays (empty = dropped)."""
+        """get_read_from_sequence (reference src/reads.cpp:57-89) per sequence (bytes/str); reverse=True applies
+        reverse_pair_ends_sequence first (:20-31, :119-121).  Returns a list of uint64 arrays (empty = dropped)."""
         member = np.zeros(self.n, np.uint8)
         member[np.asarray(cycle_nodes, np.int64)] = 1
         out = []

@@ -1,12 +1,12 @@
 // TEST INFRASTRUCTURE — NOT PRODUCT CODE.
-// Harness around the UNMODIFIED reference read mapping (reference src/reads.cpp:20-93, compiled from the source
+// Harness around the UNMODIFIED reference read mapping (reference src/reads.cpp:20-89, compiled from the source
 // where it lies by oracle/Makefile; its un-vendored kseq++ include is satisfied by a declarations-only stub).
 //   ref_reads <sdbg_prefix> <out.rd> <sequences.txt> <cycle_nodes.u64> [reverse=0]
 // sequences.txt: one sequence per line (what extract_sequences_from_fastq_file would return, src/reads.cpp:3-18);
-// cycle_nodes.u64: little-endian ids forming nodes_of_cycles (src/reads.cpp:101-106); reverse=1 applies the
-// reference's reverse_pair_ends_sequence first, as get_reads does for the second file (:119-123).
-// Per sequence the reference's get_read_from_sequence(sdbg, nodes_of_cycles, sequence) is called (:56-93).
-// Output: magic "MCAATRDS", n_sequences, then per sequence: n_ids, ids[] (empty = the read is dropped, :112-114).
+// cycle_nodes.u64: little-endian ids forming nodes_of_cycles (src/reads.cpp:98-103); reverse=1 applies the
+// reference's reverse_pair_ends_sequence first, as get_reads does for the second file (:119-121).
+// Per sequence the reference's get_read_from_sequence(sdbg, nodes_of_cycles, sequence) is called (:57-89).
+// Output: magic "MCAATRDS", n_sequences, then per sequence: n_ids, ids[] (empty = the read is dropped, :110-112).
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>

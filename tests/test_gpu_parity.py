@@ -341,7 +341,7 @@ def test_cpp_drop_in_scc_split_matches_reference(tmp_path, name):
 @pytest.mark.parametrize("via", ["files", "arrays"])
 def test_read_mapping_matches_reference(tmp_path, name, via):
     """mg_map_reads against the UNMODIFIED reference get_read_from_sequence / reverse_pair_ends_sequence /
-    IndexBinarySearch (src/reads.cpp:20-93, sdbg.h:141-207; tests/golden/<name>.reads.npz): real, mutated, random,
+    IndexBinarySearch (src/reads.cpp:20-89, sdbg.h:141-207; tests/golden/<name>.reads.npz): real, mutated, random,
     N-containing and too-short sequences, forward and reverse-complemented, two node sets.  The k-mer index comes
     from the graph files (mg_graph_create_from_files) or is attached to an array-built graph."""
     prefix = G.unpack_sdbg_files(name, str(tmp_path))

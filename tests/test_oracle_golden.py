@@ -51,7 +51,7 @@ def test_oracle_keep_regions_matches_reference(name, key, params, k):
 @pytest.mark.parametrize("name", ["tiny", "biallelic"])
 def test_oracle_read_mapping_matches_reference(tmp_path, name):
     """orc_index_binary_search / orc_get_read / orc_reverse_complement against the UNMODIFIED
-    reference (src/reads.cpp:20-93, sdbg.h:141-207; oracle/_ref/ref_reads) — real, mutated, random, N-containing
+    reference (src/reads.cpp:20-89, sdbg.h:141-207; oracle/_ref/ref_reads) — real, mutated, random, N-containing
     and too-short sequences, forward and reverse-complemented, two node sets."""
     g = O.OracleGraph.load(G.unpack_sdbg_files(name, str(tmp_path)))
     seqs, variants = G.reads_case(name)
