@@ -410,6 +410,7 @@ def main():
         cyc = [p for _, ps in hot_path_step.last_cycles for p in ps]
         cyc = np.unique(np.concatenate(cyc)).astype(np.uint64) if cyc else np.zeros(0, np.uint64)
         chars, roff = S.sample_reads(args.sample, args.reads, seed=7)
+        keep_pinned, chars = pinned(chars, torch)  # page-locked, like the e2e leg's inputs
         best = None
         for _ in range(3):
             gq.timers_reset()
@@ -427,7 +428,8 @@ def main():
         reads = dict(workload=args.sample, n_items=int(gq.n), reads=n_r, read_len=150, cycle_nodes=int(cyc.size), kept=kept,
                      kmer_lookups=lookups, wall_ms=best[0] * 1e3, device_ms=best[1], reads_per_s=n_r / best[0],
                      lookups_per_s_device=lookups / (best[1] / 1e3) if best[1] else None,
-                     note="wall = H2D of the reads + lookups + D2H of the ids, through the C ABI; graph resident")
+                     h2d_bytes=int(2 * chars.nbytes + 2 * roff.nbytes), d2h_bytes=int(8 * (i1.size + i2.size + o1.size + o2.size)),
+                     note="wall = H2D of the reads (pinned) + lookups + D2H of the ids, through the C ABI; graph resident")
         if not args.no_cpu_baseline:  # the oracle's literal restatement on a bounded sample of the same reads, 1 thread
             sys.path.insert(0, os.path.join(ROOT, "oracle"))
             import oracle_py as O
