@@ -127,13 +127,13 @@ def hot_path_step(g, rank=0, world=1, dist=None, torch=None):
     buckets, _ = g.bucket_starts(cand[ok])
     starts = np.concatenate([ids for _, ids in buckets]) if buckets else np.zeros(0, np.uint64)
     tt.append(time.perf_counter())
-    searched, cs = g.find_cycles(starts, MIN_LEN, MAX_LEN)
+    (ss, coff, noff, nodes), cs = g.find_cycles(starts, MIN_LEN, MAX_LEN, csr=True)
     tt.append(time.perf_counter())
     if dbg:
         print("[step wall ms] reset %.1f prune %.1f candidates %.1f dls %.1f bucket %.1f find_cycles %.1f" %
               tuple((b - a) * 1e3 for a, b in zip(tt, tt[1:])), file=sys.stderr)
-    res_bytes = 8 * (sum(sum(p.size for p in paths) for _, paths in searched) + len(searched))
-    hot_path_step.last_cycles = searched
+    res_bytes = 8 * int(nodes.size + ss.size)
+    hot_path_step.last_cycle_nodes = nodes  # all cycles, flattened
     stats = dict(st, n_candidates=int(cand.size), n_starts=int(starts.size), dls_expansions=int(exp), **cs)
     return stats, res_bytes
 
@@ -407,8 +407,7 @@ def main():
         S.write_megahit_files(gs, prefix)
         gq = DeviceGraph.from_files(prefix, device=local)
         hot_path_step(gq)
-        cyc = [p for _, ps in hot_path_step.last_cycles for p in ps]
-        cyc = np.unique(np.concatenate(cyc)).astype(np.uint64) if cyc else np.zeros(0, np.uint64)
+        cyc = np.unique(hot_path_step.last_cycle_nodes).astype(np.uint64)
         chars, roff = S.sample_reads(args.sample, args.reads, seed=7)
         keep_pinned, chars = pinned(chars, torch)  # page-locked, like the e2e leg's inputs
         best = None
@@ -447,8 +446,7 @@ def main():
     if rank == 0 and args.regions_check:  # k-hop region extraction around the cycles, device resident
         gr = DeviceGraph(graph, device=local)
         hot_path_step(gr)
-        seeds = [p for _, ps in hot_path_step.last_cycles for p in ps]
-        seeds = np.concatenate(seeds).astype(np.uint64) if seeds else np.zeros(0, np.uint64)
+        seeds = hot_path_step.last_cycle_nodes.astype(np.uint64)
         inv_before = gr.invalid_words().copy()
         ts_, st_r = [], None
         for _ in range(3):

@@ -345,8 +345,9 @@ class DeviceGraph:
         _check(lib().mg_bucket_starts(self.h, ids.ctypes.data, ids.size, C.byref(s)))
         return self._starts_out(s)
 
-    def find_cycles(self, starts, min_len, max_len):
-        """-> ([(start, [path ndarray, ...])] in search order, stats)"""
+    def find_cycles(self, starts, min_len, max_len, csr=False):
+        """-> ([(start, [path ndarray, ...])] in search order, stats); csr=True returns the library's own layout
+        instead — (searched_start, cyc_off, node_off, nodes) — without building a Python object per cycle"""
         starts = np.ascontiguousarray(starts, np.uint64)
         c = Cycles()
         _check(lib().mg_find_cycles(self.h, starts.ctypes.data, starts.size, int(min_len), int(max_len), C.byref(c)))
@@ -354,8 +355,8 @@ class DeviceGraph:
         noff = _np(c.node_off, c.n_cycles + 1)
         nodes = _np(c.nodes, noff[-1] if noff.size else 0)
         ss = _np(c.searched_start, c.n_searched)
-        searched = []
-        for i in range(int(c.n_searched)):
+        searched = (ss, coff, noff, nodes) if csr else []
+        for i in range(0 if csr else int(c.n_searched)):
             searched.append((int(ss[i]), [nodes[int(noff[j]):int(noff[j + 1])]
                                           for j in range(int(coff[i]), int(coff[i + 1]))]))
         stats = {k: int(getattr(c, k)) for k in ("n_searched", "n_cycles", "n_skipped", "n_bound_hits", "n_cap_hits",
