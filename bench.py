@@ -256,6 +256,7 @@ def main():
     ap.add_argument("--reads-check", action="store_true",
                     help="also time mg_map_reads (SURVEY 8(f) N3) on synthetic reads of the sample workload")
     ap.add_argument("--reads", type=int, default=400000, help="reads per file for --reads-check")
+    ap.add_argument("--reads-full", action="store_true", help="--reads-check also on the full bench workload (array-built graph)")
     ap.add_argument("--regions-check", action="store_true",
                     help="also time mg_keep_regions (SURVEY 8(f) N4, k = 128) on the cycles of the bench workload")
     args = ap.parse_args()
@@ -401,47 +402,59 @@ def main():
                       items_per_s=n_i / min(ts_), note="files in page cache; read + H2D + device decode + index build")
     reads = None
     if rank == 0 and args.reads_check:  # read -> node ids, graph (with its k-mer index) resident
-        gs, _ = S.make_workload(args.sample, device="cuda", want_labels=True)
-        tmp = tempfile.mkdtemp(prefix="mcaat_reads_")
-        prefix = os.path.join(tmp, "graph")
-        S.write_megahit_files(gs, prefix)
-        gq = DeviceGraph.from_files(prefix, device=local)
-        hot_path_step(gq)
-        cyc = np.unique(hot_path_step.last_cycle_nodes).astype(np.uint64)
-        chars, roff = S.sample_reads(args.sample, args.reads, seed=7)
-        keep_pinned, chars = pinned(chars, torch)  # page-locked, like the e2e leg's inputs
-        best = None
-        for _ in range(3):
-            gq.timers_reset()
-            torch.cuda.synchronize()
-            ta = time.perf_counter()
-            o1, i1 = gq.map_reads((chars, roff), cyc, reverse=False)  # "file 1"
-            o2, i2 = gq.map_reads((chars, roff), cyc, reverse=True)   # "file 2": reverse-complemented first
-            dt = time.perf_counter() - ta
-            dev = gq.timers().get("map_reads", {}).get("ms")
-            if best is None or dt < best[0]:
-                best = (dt, dev)
-        n_r = 2 * args.reads
-        kept = int((np.diff(o1.astype(np.int64)) > 0).sum() + (np.diff(o2.astype(np.int64)) > 0).sum())
-        lookups = 2 * n_r + int(i1.size + i2.size) - 2 * kept
-        reads = dict(workload=args.sample, n_items=int(gq.n), reads=n_r, read_len=150, cycle_nodes=int(cyc.size), kept=kept,
-                     kmer_lookups=lookups, wall_ms=best[0] * 1e3, device_ms=best[1], reads_per_s=n_r / best[0],
-                     lookups_per_s_device=lookups / (best[1] / 1e3) if best[1] else None,
-                     h2d_bytes=int(2 * chars.nbytes + 2 * roff.nbytes), d2h_bytes=int(8 * (i1.size + i2.size + o1.size + o2.size)),
-                     note="wall = H2D of the reads (pinned) + lookups + D2H of the ids, through the C ABI; graph resident")
-        if not args.no_cpu_baseline:  # the oracle's literal restatement on a bounded sample of the same reads, 1 thread
-            sys.path.insert(0, os.path.join(ROOT, "oracle"))
-            import oracle_py as O
-            og = O.OracleGraph.load(prefix)
-            m = min(args.reads, 20000)
-            sub = [bytes(chars[int(roff[i]):int(roff[i + 1])]) for i in range(m)]
-            ta = time.perf_counter()
-            want = og.map_reads(sub, cyc, reverse=False)
-            dt = time.perf_counter() - ta
-            ok = all(np.array_equal(w_, i1[int(o1[j]):int(o1[j + 1])]) for j, w_ in enumerate(want))
-            reads["cpu_baseline"] = dict(kind="port", cores=1, reads=m, seconds=dt, reads_per_s=m / dt, matches_gpu=bool(ok))
-        gq.close()
-        shutil.rmtree(tmp, ignore_errors=True)
+        def reads_leg(name, via_files):
+            gs, _ = S.make_workload(name, device="cuda", want_labels=True)
+            tmp = tempfile.mkdtemp(prefix="mcaat_reads_")
+            prefix = os.path.join(tmp, "graph")
+            if via_files:  # the index comes with the decoded graph files
+                S.write_megahit_files(gs, prefix)
+                gq = DeviceGraph.from_files(prefix, device=local)
+            else:          # array-built graph + mg_kmer_index_create
+                gq = DeviceGraph(gs, device=local)
+                gq.set_kmer_index(gs["tip"], *S.kmer_index_arrays(gs))
+            hot_path_step(gq)
+            cyc = np.unique(hot_path_step.last_cycle_nodes).astype(np.uint64)
+            chars, roff = S.sample_reads(name, args.reads, seed=7)
+            keep_pinned, chars = pinned(chars, torch)  # page-locked, like the e2e leg's inputs
+            best = None
+            for _ in range(3):
+                gq.timers_reset()
+                torch.cuda.synchronize()
+                ta = time.perf_counter()
+                o1, i1 = gq.map_reads((chars, roff), cyc, reverse=False)  # "file 1"
+                o2, i2 = gq.map_reads((chars, roff), cyc, reverse=True)   # "file 2": reverse-complemented first
+                dt = time.perf_counter() - ta
+                dev = gq.timers().get("map_reads", {}).get("ms")
+                if best is None or dt < best[0]:
+                    best = (dt, dev)
+            n_r = 2 * args.reads
+            kept = int((np.diff(o1.astype(np.int64)) > 0).sum() + (np.diff(o2.astype(np.int64)) > 0).sum())
+            lookups = 2 * n_r + int(i1.size + i2.size) - 2 * kept
+            out = dict(workload=name, n_items=int(gq.n), index="graph files" if via_files else "mg_kmer_index_create",
+                       reads=n_r, read_len=150, cycle_nodes=int(cyc.size), kept=kept, kmer_lookups=lookups,
+                       null_ids=int((i1 == np.uint64(2**64 - 1)).sum() + (i2 == np.uint64(2**64 - 1)).sum()),
+                       wall_ms=best[0] * 1e3, device_ms=best[1], reads_per_s=n_r / best[0],
+                       lookups_per_s_device=lookups / (best[1] / 1e3) if best[1] else None,
+                       h2d_bytes=int(2 * chars.nbytes + 2 * roff.nbytes), d2h_bytes=int(8 * (i1.size + i2.size + o1.size + o2.size)),
+                       note="wall = H2D of the reads (pinned) + lookups + D2H of the ids, through the C ABI; graph resident")
+            if via_files and not args.no_cpu_baseline:  # the oracle's literal restatement on a bounded sample, 1 thread
+                sys.path.insert(0, os.path.join(ROOT, "oracle"))
+                import oracle_py as O
+                og = O.OracleGraph.load(prefix)
+                m = min(args.reads, 20000)
+                sub = [bytes(chars[int(roff[i]):int(roff[i + 1])]) for i in range(m)]
+                ta = time.perf_counter()
+                want = og.map_reads(sub, cyc, reverse=False)
+                dt = time.perf_counter() - ta
+                ok = all(np.array_equal(w_, i1[int(o1[j]):int(o1[j + 1])]) for j, w_ in enumerate(want))
+                out["cpu_baseline"] = dict(kind="port", cores=1, reads=m, seconds=dt, reads_per_s=m / dt, matches_gpu=bool(ok))
+            gq.close()
+            del gs
+            shutil.rmtree(tmp, ignore_errors=True)
+            return out
+        reads = reads_leg(args.sample, True)
+        if args.reads_full:
+            reads["full_size"] = reads_leg(args.workload, False)
     regions = None
     if rank == 0 and args.regions_check:  # k-hop region extraction around the cycles, device resident
         gr = DeviceGraph(graph, device=local)

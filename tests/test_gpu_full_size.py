@@ -86,6 +86,60 @@ def test_sample_workload_regions_match_oracle():
     assert np.array_equal(dg.invalid(), og.invalid())
 
 
+def test_sample_workload_read_mapping_matches_oracle(tmp_path):
+    """SURVEY 8(f) N3 at 11.3 M items: 3 000 synthetic reads (both strands, substitution errors) through
+    mg_map_reads — index decoded from the graph files — against the oracle's restatement of
+    get_read_from_sequence, forward and reverse-complemented."""
+    import synth_sdbg as S
+    gs, _ = S.make_workload("c2_sample", device="cuda", want_labels=True)
+    prefix = str(tmp_path / "graph")
+    S.write_megahit_files(gs, prefix)
+    og = O.OracleGraph.load(prefix)
+    dg = DeviceGraph.from_files(prefix)
+    a = run(dg, 20, 27, 77)
+    cyc = np.unique(np.concatenate([p for _, ps in a.searched for p in ps])).astype(np.uint64)
+    chars, off = S.sample_reads("c2_sample", 3000, seed=11)
+    seqs = [bytes(chars[int(off[i]):int(off[i + 1])]) for i in range(3000)]
+    # half of the reads are forced to pass the filter: a random half of all ids joins the node set
+    big = np.union1d(cyc, np.nonzero(np.random.default_rng(2).random(dg.n) < 0.5)[0].astype(np.uint64))
+    for ids, rev in ((cyc, False), (big, False), (big, True)):
+        want = og.map_reads(seqs, ids, reverse=rev)
+        got_off, got_ids = dg.map_reads((chars, off), ids, reverse=rev)
+        assert [w.size for w in want] == list(np.diff(got_off.astype(np.int64)))
+        assert np.array_equal(np.concatenate(want), got_ids)
+    assert got_ids.size > 100000
+
+
+def test_full_size_read_mapping_properties():
+    """N3 at 224.7 M items (index attached to the array-built graph): kept reads carry len - k + 1 ids; mapping the
+    reverse complement of a batch with reverse=True gives the ids of the batch itself (reverse_pair_ends_sequence is
+    an involution, reference src/reads.cpp:20-31); the same k-mer always maps to the same id; repeatable."""
+    import synth_sdbg as S
+    gs, _ = S.make_workload("c2", device="cuda", want_labels=True)
+    dg = DeviceGraph(gs)
+    dg.set_kmer_index(gs["tip"], *S.kmer_index_arrays(gs))
+    n_reads, L, k = 20000, 150, gs["k"]
+    chars, off = S.sample_reads("c2", n_reads, seed=5)
+    ids_all = np.nonzero(np.random.default_rng(3).random(dg.n) < 0.5)[0].astype(np.uint64)
+    o1, i1 = dg.map_reads((chars, off), ids_all)
+    lens = np.diff(o1.astype(np.int64))
+    assert set(np.unique(lens)) <= {0, L - k + 1} and (lens > 0).sum() > n_reads // 2
+    null = np.uint64(2**64 - 1)
+    assert (i1 != null).mean() > 0.9 and (i1[i1 != null] < dg.n).all()
+    comp = np.arange(256, dtype=np.uint8)
+    for a, b in zip(b"ACGT", b"TGCA"):
+        comp[a] = b
+    rc = comp[chars.reshape(n_reads, L)[:, ::-1]].reshape(-1)
+    o2, i2 = dg.map_reads((rc, off), ids_all, reverse=True)
+    assert np.array_equal(o1, o2) and np.array_equal(i1, i2)
+    # identical k-mers -> identical ids: duplicate the batch shifted by one read
+    o3, i3 = dg.map_reads((np.concatenate([chars[L:], chars[:L]]), off), ids_all)
+    first = i1[int(o1[1]):int(o1[2])]
+    assert np.array_equal(first, i3[int(o3[0]):int(o3[1])])
+    o4, i4 = dg.map_reads((chars, off), ids_all)
+    assert np.array_equal(i1, i4)
+
+
 def test_full_size_properties():
     g = workload("c2")
     dg = DeviceGraph(g)

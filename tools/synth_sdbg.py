@@ -222,6 +222,25 @@ def write_megahit_files(g, prefix, words_per_tip_label=None):
             fo.write(f"{bk} 0 {int(off[first_item[bk]])} {int(items[bk])} {int(tips_b[bk])} {int(large_b[bk])}\n")
 
 
+def kmer_index_arrays(g, words_per_tip_label=None):
+    """What mg_kmer_index_create wants for a packed SDBG made with want_labels=True, without going through files:
+    (tip labels as file words [n_tips, words_per_tip_label], first item per bucket, last item per bucket) — the same
+    values write_megahit_files stores and SDBG::LoadFromFile derives (sdbg.h:36-46)."""
+    k = g["k"]
+    wptl = words_per_tip_label or (2 * k + 31) // 32
+    chars = g["tip_label_chars"].astype(np.uint64) << np.uint64(64 - 2 * k)
+    labels = np.zeros((chars.size, wptl), np.uint32)
+    if chars.size:
+        labels[:, 0] = (chars >> np.uint64(32)).astype(np.uint32)
+        if wptl > 1:
+            labels[:, 1] = (chars & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    nb = 65536
+    items = np.bincount(g["first8"], minlength=nb).astype(np.int64)
+    first = np.zeros(nb, np.int64)
+    np.cumsum(items[:-1], out=first[1:])
+    return labels, first, first + items - 1
+
+
 # ------------------------------------------------------------------ community -> (k+1)-mer spectrum
 def community_spectrum(argv, total_bases, error_events, seed, device="cpu", read_len=150, k=K):
     """Sample the (k+1)-mer spectrum that `total_bases` of error-prone reads of read_len would give
