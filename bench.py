@@ -502,6 +502,12 @@ def main():
     roofline = dict(bound="hbm", kernel=top, achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
                     traffic=traffic, peak_source=peak_kind, ms_per_launch=per_launch_ms,
                     algorithmic_bytes_per_launch=alg[top] / launches_per_step)
+    # the same figure for every phase and for the whole step ("per phase and overall")
+    roofline["by_phase"] = {k: dict(ms_per_step=round(v["ms"] / args.steps, 3),
+                                    achieved=round(alg[k] / (v["ms"] / args.steps * 1e-3) / 1e9, 2),
+                                    frac=alg[k] / (v["ms"] / args.steps * 1e-3) / 1e9 / peak) for k, v in fam.items()}
+    roofline["overall"] = dict(achieved=sum(alg[k] for k in fam) / (ms_per_step * 1e-3) / 1e9,
+                               frac=sum(alg[k] for k in fam) / (ms_per_step * 1e-3) / 1e9 / peak)
     phases = {k: round(v["ms"] / args.steps, 3) for k, v in timers.items() if v["launches"]}
     cpu = None
     if world == 1 and not args.no_cpu_baseline:

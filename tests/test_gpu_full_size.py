@@ -1,6 +1,6 @@
 """-m gpu: the bench workloads.
 
-* c2_sample (BASELINE.json configs[1] at 1/20 scale, 11.3 M items) against the oracle, bit for bit, at the
+* c1 (BASELINE.json configs[0], 20.0 M items) and c2_sample (configs[1] at 1/20 scale, 11.3 M items) against the oracle, bit for bit, at the
   default parameters and at a stress setting of configs[4] (bounds 20-100, threshold 10).
 * c2 itself (224.7 M items — the oracle would need minutes) through size-independent properties of the
   reference's algorithm: idempotence after reset, visited == union of all cycle nodes, every skipped
@@ -58,6 +58,18 @@ def run(dg, thr, mn, mx):
     r.searched = list(cf.results.items())
     r.stats = cf.stats
     return r
+
+
+def test_c1_workload_matches_oracle():
+    """BASELINE.json configs[0] (5 x 2 Mb genomes, 10 planted arrays, error-free; 20.0 M items — the reference's own
+    CPU-runnable case) against the oracle, bit for bit."""
+    g = workload("c1")
+    w, last, tip = unpack(g)
+    want = O.OracleGraph.from_arrays(w, last, tip, g["mult"], g["f"], g["k"]).run(20, 27, 77)
+    got = run(DeviceGraph(g), 20, 27, 77)
+    assert O.same_run(want, got) == []
+    assert want.stats["n_candidates"] == 340 and len(got.searched) >= 10  # the counts of SURVEY's C1 probe
+    _wl.pop("c1", None)
 
 
 @pytest.mark.parametrize("thr,mn,mx", [(20, 27, 77), (10, 20, 100)])
