@@ -60,7 +60,43 @@ class ClockSampler:
         self.proc = None
         self.idx = gpu_index
 
-    def start(self):
+    def start(self, uuid=None):
+        """In-process NVML polling (the library nvidia-smi itself reads; a query costs microseconds and takes no
+        driver-wide lock, whereas every `nvidia-smi -lms` tick stalled kernel launches for milliseconds and showed up
+        as one slow timed step).  Falls back to the nvidia-smi loop when pynvml is missing."""
+        self.source = "nvml"
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = None
+            if uuid:
+                for cand in (uuid, "GPU-" + uuid):
+                    try:
+                        h = pynvml.nvmlDeviceGetHandleByUUID(cand.encode() if isinstance(cand, str) else cand)
+                        break
+                    except Exception:
+                        h = None
+            if h is None:
+                h = pynvml.nvmlDeviceGetHandleByIndex(self.idx)
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            reasons_fn = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            self._stop = threading.Event()
+
+            def poll():
+                while not self._stop.is_set():
+                    try:
+                        sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                        r = int(reasons_fn(h))
+                        # row layout of the nvidia-smi query below: idx, sm, max, power, active, hw, hw_thermal, sw_thermal, sw_power
+                        flag = lambda bit: "Active" if r & bit else "Not Active"
+                        self.rows.append([str(self.idx), str(sm), str(mx), "", hex(r), flag(0x8), flag(0x40), flag(0x20), flag(0x4)])
+                    except Exception:
+                        pass
+                    self._stop.wait(0.05)
+            threading.Thread(target=poll, daemon=True).start()
+            return
+        except Exception:
+            self.source = "nvidia-smi"
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
@@ -73,6 +109,8 @@ class ClockSampler:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self):
+        if getattr(self, "_stop", None):
+            self._stop.set()
         if self.proc:
             self.proc.terminate()
         if len(self.rows) > self.rows_before:
@@ -87,7 +125,7 @@ class ClockSampler:
                     if v.lower().startswith("active"):
                         reasons.add(nm)
         return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
-                    reasons=sorted(reasons), samples=len(sm))
+                    reasons=sorted(reasons), samples=len(sm), source=getattr(self, "source", "nvidia-smi"))
 
 
 def unpack_for_oracle(g):
@@ -320,7 +358,11 @@ def main():
     #      during the timed region are used.
     clocks = ClockSampler(local)
     if rank == 0 and not os.environ.get("BENCH_NO_CLOCKS"):
-        clocks.start()
+        try:
+            uuid = str(torch.cuda.get_device_properties(local).uuid)
+        except Exception:
+            uuid = None
+        clocks.start(uuid)
     for _ in range(args.warmup):
         stats, res_bytes = hot_path_step(g, rank, world, dist, torch)
     g.timers_reset()
