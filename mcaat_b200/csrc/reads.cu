@@ -129,6 +129,11 @@ int run_map_reads(mg_graph *g, const char *seqs, const uint64_t *seq_off, uint64
       return MG_EINVAL;
     }
   }
+  // the id offsets are scanned in 32 bits: at most len - k + 1 <= len ids per read
+  if (n_chars >= 0xFFFFFFFFull) {
+    set_error("mg_map_reads: batch of %llu characters; pass batches below 2^32", (unsigned long long)n_chars);
+    return MG_ELIMIT;
+  }
   std::vector<uint32_t> h_off(n_reads + 1, 0);
   std::vector<uint64_t> h_ids;
   uint64_t total = 0;
@@ -151,11 +156,6 @@ int run_map_reads(mg_graph *g, const char *seqs, const uint64_t *seq_off, uint64
     if (n_reads) {
       MG_LAUNCH(k_read_ends, grid_for(g, n_reads, 128), 128, 0, s, g->view, g->kx, d_seqs.as<char>(), d_off.as<uint64_t>(), n_reads,
                 reverse, member.as<uint32_t>(), first_id.as<uint32_t>(), last_id.as<uint32_t>(), out_off.as<uint32_t>());
-      // guard the 32-bit scan: at most len - k + 1 <= len ids per read
-      if (n_chars >= 0xFFFFFFFFull) {
-        set_error("mg_map_reads: batch of %llu characters; pass batches below 2^32", (unsigned long long)n_chars);
-        return MG_ELIMIT;
-      }
       MG_TRY(exclusive_scan_u32(out_off.as<uint32_t>(), n_reads + 1, d_total.as<uint32_t>(), s));
       uint32_t tot = 0;
       MG_CUDA(cudaMemcpyAsync(&tot, d_total.p, 4, cudaMemcpyDeviceToHost, s));

@@ -34,6 +34,27 @@ def test_struct_layouts_match_header():
     assert C.sizeof(gpu.Cycles) == 112
 
 
+def test_struct_sizes_against_the_c_compiler(tmp_path):
+    """every struct of include/mcaat_gpu.h: sizeof as gcc lays it out == the ctypes mirror in mcaat_b200/gpu.py"""
+    import os
+    import shutil
+    import subprocess
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if not cc:
+        pytest.skip("no C compiler")
+    pairs = [("mg_graph_desc", gpu.GraphDesc), ("mg_prune_stats", gpu.PruneStats), ("mg_starts", gpu.Starts),
+             ("mg_cycles", gpu.Cycles), ("mg_region_stats", gpu.RegionStats), ("mg_subgraph", gpu.Subgraph),
+             ("mg_kmer_index_desc", gpu.KmerIndexDesc), ("mg_reads", gpu.Reads)]
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "mcaat_gpu.h"\nint main(void){' +
+                   "".join(f'printf("%zu\\n", sizeof({c}));' for c, _ in pairs) + "return 0;}\n")
+    exe = str(tmp_path / "sizes")
+    subprocess.run([cc, "-std=c11", "-I", os.path.join(gpu.ROOT, "include"), str(src), "-o", exe], check=True)
+    out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout.split()
+    for (cname, ct), size in zip(pairs, out):
+        assert C.sizeof(ct) == int(size), cname
+
+
 def _has_cuda():
     try:
         import torch
