@@ -2,6 +2,10 @@
 // compute entry returns MG_ECUDA.
 #include <stdarg.h>
 
+#include <algorithm>
+#include <mutex>
+#include <vector>
+
 #include "common.cuh"
 #include "search_dev.cuh"
 
@@ -10,6 +14,69 @@ namespace mg {
 static thread_local char g_err[512] = "";
 unsigned long long g_launches = 0;
 thread_local cudaStream_t g_alloc_stream = nullptr;
+
+// ---- exact-size free list in front of the stream-ordered pool (see DevBuf, common.cuh)
+namespace {
+struct ScratchEntry { cudaStream_t st; void *p; size_t bytes; };
+std::mutex g_scratch_mu;
+std::vector<ScratchEntry> g_scratch;
+size_t g_scratch_bytes = 0;
+constexpr size_t kScratchMaxEntries = 512;
+bool scratch_enabled() {
+  static const bool on = [] { const char *e = getenv("MCAAT_SCRATCH_CACHE"); return !(e && *e == '0'); }();
+  return on;
+}
+size_t scratch_limit() {  // bytes kept per process: a quarter of the device, at least 1 GB
+  static const size_t lim = [] {
+    size_t fr = 0, tot = 0;
+    if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) tot = (size_t)16 << 30;
+    return std::max<size_t>(tot / 4, (size_t)1 << 30);
+  }();
+  return lim;
+}
+}  // namespace
+
+void *scratch_take(cudaStream_t st, size_t bytes) {
+  if (!scratch_enabled()) return nullptr;
+  std::lock_guard<std::mutex> lk(g_scratch_mu);
+  for (size_t i = g_scratch.size(); i-- > 0;)
+    if (g_scratch[i].st == st && g_scratch[i].bytes == bytes) {
+      void *p = g_scratch[i].p;
+      g_scratch_bytes -= bytes;
+      g_scratch.erase(g_scratch.begin() + (long)i);
+      return p;
+    }
+  return nullptr;
+}
+
+bool scratch_give(cudaStream_t st, void *p, size_t bytes) {
+  if (!scratch_enabled() || !st) return false;
+  std::lock_guard<std::mutex> lk(g_scratch_mu);
+  if (bytes > scratch_limit()) return false;
+  // make room: oldest entries first (sizes that no longer occur, e.g. after another graph was searched)
+  while (!g_scratch.empty() && (g_scratch_bytes + bytes > scratch_limit() || g_scratch.size() >= kScratchMaxEntries)) {
+    cudaFreeAsync(g_scratch.front().p, g_scratch.front().st);
+    g_scratch_bytes -= g_scratch.front().bytes;
+    g_scratch.erase(g_scratch.begin());
+  }
+  g_scratch.push_back({st, p, bytes});
+  g_scratch_bytes += bytes;
+  return true;
+}
+
+void scratch_flush(cudaStream_t st) {
+  std::lock_guard<std::mutex> lk(g_scratch_mu);
+  size_t w = 0;
+  for (size_t i = 0; i < g_scratch.size(); ++i) {
+    if (g_scratch[i].st == st) {
+      cudaFreeAsync(g_scratch[i].p, st);
+      g_scratch_bytes -= g_scratch[i].bytes;
+    } else {
+      g_scratch[w++] = g_scratch[i];
+    }
+  }
+  g_scratch.resize(w);
+}
 const char *kTimerNames[T_COUNT] = {"build_index", "collect_tips", "invalidate_mult1", "peel",      "nav_cache",
                                     "candidates",  "dls",          "enumerate",        "commit",    "navigate",
                                     "keep_regions", "map_reads"};
@@ -126,6 +193,7 @@ void mg_graph_destroy(mg_graph *g) {
   for (mg::DevBuf *b : {&g->wb, &g->fb, &g->mult, &g->hints, &g->inv0, &g->adj, &g->visited, &g->enum_arena,
                        &g->kx_tip, &g->kx_tip_prefix, &g->kx_labels, &g->kx_buckets})
     b->release();
+  scratch_flush(g->stream);  // nothing cached may outlive the stream it is ordered on
   if (g->stream) cudaStreamSynchronize(g->stream);
   for (auto e : g->event_pool) cudaEventDestroy(e);
   if (g->step_a) cudaEventDestroy(g->step_a);

@@ -46,9 +46,16 @@ extern unsigned long long g_launches;
   } while (0)
 
 // Device buffers come from the device's stream-ordered memory pool (cudaMallocAsync) on the stream of
-// the graph handle the running API call belongs to: after the first pass of the hot path the scratch
-// buffers of every phase are served from the pool without touching the driver.
+// the graph handle the running API call belongs to.  In front of the pool sits an exact-size free list per
+// stream (scratch_take / scratch_give, api.cu): a pass of the hot path allocates the same ~30 scratch buffers
+// (3.5 GB at 225 M items) with the same sizes every time, so after the first pass no call reaches the driver's
+// allocator any more — on the B200 boxes a pool allocation of a GB-sized block sporadically took hundreds of
+// milliseconds (physical memory being mapped again) in the middle of a steady-state run.  Buffers are handed out
+// again only to calls on the same stream, so stream order keeps reuse safe.  MCAAT_SCRATCH_CACHE=0 disables it.
 extern thread_local cudaStream_t g_alloc_stream;
+void *scratch_take(cudaStream_t st, size_t bytes);            // nullptr when nothing of that size is cached
+bool scratch_give(cudaStream_t st, void *p, size_t bytes);    // false: not cached, the caller frees it
+void scratch_flush(cudaStream_t st);                          // frees everything cached for the stream
 struct DevBuf {
   void *p = nullptr;
   size_t bytes = 0;
@@ -58,15 +65,25 @@ struct DevBuf {
   DevBuf &operator=(const DevBuf &) = delete;
   ~DevBuf() { release(); }
   void release() {
-    if (p) cudaFreeAsync(p, st);
+    if (p && !scratch_give(st, p, bytes)) cudaFreeAsync(p, st);
     p = nullptr;
     bytes = 0;
   }
   int alloc(size_t b) {
     release();
     if (b == 0) b = 16;
+    b = (b + 255) & ~(size_t)255;
     st = g_alloc_stream;
+    p = scratch_take(st, b);
+    if (p) {
+      bytes = b;
+      return MG_OK;
+    }
     cudaError_t e = cudaMallocAsync(&p, b, st);
+    if (e != cudaSuccess) {
+      scratch_flush(st);  // give the pool its memory back and try once more
+      e = cudaMallocAsync(&p, b, st);
+    }
     if (e != cudaSuccess) {
       p = nullptr;
       set_error("cudaMallocAsync(%zu) -> %s", b, cudaGetErrorString(e));

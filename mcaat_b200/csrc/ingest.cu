@@ -181,7 +181,7 @@ extern "C" int mg_graph_create_from_files(const char *prefix, int device, mg_gra
       for (FILE *x : fh) if (x) fclose(x);
       for (int i = 0; i < 2; ++i) { if (pin[i]) cudaFreeHost(pin[i]); if (done[i]) cudaEventDestroy(done[i]); }
     };
-#define ING_TRY(call) do { rc = (call); if (rc != MG_OK) { cleanup(); raw.release(); bdev.release(); w.release(); last.release(); tip.release(); mult.release(); bad.release(); labels.release(); cudaStreamSynchronize(s); cudaStreamDestroy(s); return rc; } } while (0)
+#define ING_TRY(call) do { rc = (call); if (rc != MG_OK) { cleanup(); raw.release(); bdev.release(); w.release(); last.release(); tip.release(); mult.release(); bad.release(); labels.release(); scratch_flush(s); cudaStreamSynchronize(s); cudaStreamDestroy(s); return rc; } } while (0)
     auto cuda_rc = [&](cudaError_t ce, const char *what) { if (ce != cudaSuccess) { set_error("%s -> %s", what, cudaGetErrorString(ce)); return (int)MG_ECUDA; } return (int)MG_OK; };
     ING_TRY(raw.alloc(total + 16));
     for (int i = 0; i < 2; ++i) {
