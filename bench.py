@@ -436,6 +436,24 @@ def main():
         e2e = dict(value=st2["n_starts"] / dt, unit=UNIT, h2d_bytes_per_step=int(h2d),
                    d2h_bytes_per_step=int(inv.nbytes + rb), ms_per_step=dt * 1e3)
 
+    # ---- the same hot path on the bounded sample the CPU arms are timed on, so that the two can be compared on
+    #      identical input as well (start nodes/s is not scale-free: the sample has 1/20 of the items)
+    sample_leg = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        gsm, _ = S.make_workload(args.sample, device="cuda")
+        gq = DeviceGraph(gsm, device=local)
+        for _ in range(2):
+            st_s, _ = hot_path_step(gq)
+        ts_ = []
+        for _ in range(3):
+            gq.step_begin()
+            st_s, _ = hot_path_step(gq)
+            ts_.append(gq.step_end())
+        gq.close()
+        del gsm
+        sample_leg = dict(workload=args.sample, n_items=int(gq.n), n_starts=int(st_s["n_starts"]),
+                          ms_per_step=float(np.mean(ts_)), value=st_s["n_starts"] / (float(np.mean(ts_)) / 1e3), unit=UNIT,
+                          note="graph resident, CUDA events around the step; cpu_baseline and --impl reference run this same graph")
     ingest = None
     if rank == 0 and args.ingest_check:  # on-disk SDBG decoded on the device
         gs, _ = S.make_workload(args.sample, device="cuda", want_labels=True)
@@ -597,6 +615,8 @@ def main():
         line["reads"] = reads
     if e2e:
         line["e2e"] = e2e
+    if sample_leg:
+        line["same_input_as_cpu"] = sample_leg
     if cpu:
         line["cpu_baseline"] = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
     print(json.dumps(line))
