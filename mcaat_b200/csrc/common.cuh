@@ -131,7 +131,7 @@ struct mg_graph {
   uint32_t k = 0;
   bool has_kx = false;
   mg::KmerIndex kx{};
-  mg::DevBuf kx_tip, kx_tip_prefix, kx_labels, kx_buckets;
+  mg::DevBuf kx_tip, kx_tip_prefix, kx_labels, kx_buckets, kx_jump, kx_bucket_ok;
   uint64_t device_bytes = 0;
   int sm_count = 148;
   // timers

@@ -16,7 +16,17 @@ struct KmerIndex {
   uint32_t n_buckets;
   const int64_t *first, *second;  // per bucket; buckets absent from the file hold (0, 0) like the reference's resize()
   uint32_t k;
+  // Optional shortcut (null = off).  Every probe of the binary search first walks kJumpSteps Backward steps whose
+  // characters are the bucket's own prefix — equal to the query's by construction.  jump[x] = Backward^8(x), or
+  // kJumpLiteral when one of x, Backward(x), ..., Backward^7(x) is a tip (the reference would compare a tip label
+  // there).  bucket_ok: bit b set when the items of bucket b really carry prefix b (checked when the index is built;
+  // an absent bucket's (0, 0) range does not).  With both, a probe starts at depth 8 with ONE load instead of 8
+  // rank/select rounds; everything from there on is the literal code.
+  const uint32_t *jump;
+  const uint32_t *bucket_ok;
 };
+constexpr int kJumpSteps = 8;
+constexpr uint32_t kJumpLiteral = 0x80000000u;  // flag bit (ids are < 2^31)
 
 MG_HD bool kx_is_tip(const KmerIndex &K, uint32_t x) { return (K.tip[x >> 6] >> (x & 63)) & 1; }
 // CharAtTipLabel (sdbg.h:128-133) on file words: the reference reverses the 2-bit groups of every word when
@@ -52,11 +62,20 @@ MG_HD uint32_t index_binary_search(const GraphView &g, const KmerIndex &K, const
   uint64_t prefix = 0;
   for (uint64_t i = 0; (1u << (i * 2)) < K.n_buckets; ++i) prefix = prefix * 4 + seq[k - 1 - i] - 1;
   int64_t l = K.first[prefix], r = K.second[prefix];
+  const bool shortcut = K.jump && k > kJumpSteps && ((K.bucket_ok[prefix >> 5] >> (prefix & 31)) & 1);
   while (l <= r) {
     int cmp = 0;
     const uint32_t mid = (uint32_t)((l + r) / 2);
     uint32_t y = mid;
-    for (int i = k - 1; i >= 0; --i) {
+    int i_from = k - 1;
+    if (shortcut) {
+      const uint32_t j = K.jump[mid];
+      if (!(j & kJumpLiteral)) {  // the first 8 characters are the bucket prefix = the query's: skip them
+        y = j;
+        i_from = k - 1 - kJumpSteps;
+      }
+    }
+    for (int i = i_from; i >= 0; --i) {
       if (kx_is_tip(K, y)) {
         for (int j = 0; j < i; ++j) {
           int c = kx_tip_char(K, y, (unsigned)j);
@@ -84,6 +103,41 @@ MG_HD uint32_t index_binary_search(const GraphView &g, const KmerIndex &K, const
     else l = (int64_t)mid + 1;
   }
   return kNull;
+}
+
+// Index construction helpers.  jump_init: one Backward step (or the literal flag for a tip / a broken chain).
+MG_HD uint32_t jump_init(const GraphView &g, const KmerIndex &K, uint32_t x) {
+  if (kx_is_tip(K, x)) return kJumpLiteral;
+  const uint32_t y = backward(g, x);
+  return y < g.n ? y : kJumpLiteral;
+}
+// doubling: steps(dst) = 2 * steps(src); the flag propagates
+MG_HD uint32_t jump_double(const uint32_t *src, uint32_t x) {
+  const uint32_t v = src[x];
+  if (v & kJumpLiteral) return kJumpLiteral;
+  const uint32_t w = src[v];
+  return (w & kJumpLiteral) ? kJumpLiteral : w;
+}
+// prefix code of item x as IndexBinarySearch computes it from a query (sdbg.h:142-146), read off the graph by the
+// literal walk; -1 when a tip is met within the first `chars` steps
+MG_HD int64_t item_prefix(const GraphView &g, const KmerIndex &K, uint32_t x, int chars) {
+  int64_t code = 0;
+  uint32_t y = x;
+  for (int i = 0; i < chars; ++i) {
+    if (kx_is_tip(K, y)) return -1;
+    y = backward(g, y);
+    if (y >= g.n) return -1;
+    code = code * 4 + (int64_t)get_w(g, y) - 1;
+  }
+  return code;
+}
+// bucket b may use the shortcut when its first and last item carry prefix b (items are sorted by reversed label, so
+// everything in between does too) — or when it is empty
+MG_HD bool bucket_consistent(const GraphView &g, const KmerIndex &K, uint32_t b, int chars) {
+  const int64_t l = K.first[b], r = K.second[b];
+  if (l > r) return true;
+  if (l < 0 || (uint64_t)r >= g.n) return false;
+  return item_prefix(g, K, (uint32_t)l, chars) == (int64_t)b && item_prefix(g, K, (uint32_t)r, chars) == (int64_t)b;
 }
 
 // k_mer_to_node_id's alphabet (src/reads.cpp:44-52): A, C, G -> 1, 2, 3, anything else -> 4; with `reverse` the

@@ -27,6 +27,22 @@ __global__ void k_tip_popc(const uint64_t *tip, uint64_t n_words, uint32_t *coun
     counts[i] = (uint32_t)__popcll(tip[i]);
 }
 
+// ---- shortcut tables of the k-mer index (kmer_dev.cuh: KmerIndex::jump, bucket_ok)
+__global__ void k_jump_init(GraphView g, KmerIndex K, uint32_t *dst) {
+  for (uint64_t x = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; x < g.n; x += (uint64_t)gridDim.x * blockDim.x)
+    dst[x] = jump_init(g, K, (uint32_t)x);
+}
+__global__ void k_jump_double(uint64_t n, const uint32_t *src, uint32_t *dst) {
+  for (uint64_t x = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; x < n; x += (uint64_t)gridDim.x * blockDim.x)
+    dst[x] = jump_double(src, (uint32_t)x);
+}
+__global__ void k_bucket_ok(GraphView g, KmerIndex K, int chars, uint32_t *ok) {
+  const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool good = b < K.n_buckets && bucket_consistent(g, K, b, chars);
+  const unsigned m = __ballot_sync(0xffffffffu, good);
+  if ((threadIdx.x & 31) == 0 && b < K.n_buckets) ok[b >> 5] = m;
+}
+
 __global__ void k_member_bits(const uint32_t *ids, uint64_t n_ids, uint32_t *member) {
   for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_ids; i += (uint64_t)gridDim.x * blockDim.x)
     bm_set_atomic(member, ids[i]);
@@ -108,6 +124,28 @@ int attach_kmer_index(mg_graph *g, const uint64_t *tip_dev, const uint32_t *labe
   K.first = g->kx_buckets.as<int64_t>();
   K.second = K.first + n_buckets;
   K.k = g->k;
+  K.jump = nullptr;
+  K.bucket_ok = nullptr;
+  // shortcut tables: Backward^8 per item by pointer doubling (1 navigation pass + 3 gather passes) and the per-bucket
+  // consistency bits; 4 B per item.  MCAAT_KMER_JUMP=0 keeps the literal search only.
+  const char *je = getenv("MCAAT_KMER_JUMP");
+  if (!(je && *je == '0') && chars >= (unsigned)kJumpSteps && g->k > (uint32_t)kJumpSteps && n) {
+    DevBuf tmp;
+    MG_TRY(g->kx_jump.alloc((size_t)n * 4 + 16));
+    MG_TRY(tmp.alloc((size_t)n * 4 + 16));
+    MG_TRY(g->kx_bucket_ok.alloc((size_t)((n_buckets + 31) / 32) * 4 + 16));
+    uint32_t *a = g->kx_jump.as<uint32_t>(), *b = tmp.as<uint32_t>();
+    const unsigned grid = grid_for(g, n, 256);
+    MG_LAUNCH(k_jump_init, grid, 256, 0, s, g->view, K, b);   // 1 step  (in tmp)
+    MG_LAUNCH(k_jump_double, grid, 256, 0, s, n, b, a);        // 2 steps (in jump)
+    MG_LAUNCH(k_jump_double, grid, 256, 0, s, n, a, b);        // 4 steps (in tmp)
+    MG_LAUNCH(k_jump_double, grid, 256, 0, s, n, b, a);        // 8 steps (in jump)
+    MG_LAUNCH(k_bucket_ok, (unsigned)((n_buckets + 255) / 256), 256, 0, s, g->view, K, (int)chars, g->kx_bucket_ok.as<uint32_t>());
+    MG_CUDA(cudaStreamSynchronize(s));
+    K.jump = a;
+    K.bucket_ok = g->kx_bucket_ok.as<uint32_t>();
+    g->device_bytes += g->kx_jump.bytes + g->kx_bucket_ok.bytes;
+  }
   g->has_kx = true;
   g->device_bytes += g->kx_tip.bytes + g->kx_tip_prefix.bytes + g->kx_labels.bytes + g->kx_buckets.bytes;
   return MG_OK;

@@ -31,6 +31,7 @@ struct Emu {
   std::vector<uint64_t> kx_tip;
   std::vector<uint32_t> kx_prefix, kx_labels;
   std::vector<int64_t> kx_first, kx_second;
+  std::vector<uint32_t> kx_jump, kx_ok;
 };
 
 extern "C" {
@@ -273,7 +274,7 @@ void emu_keep_regions(Emu *e, const uint64_t *ids, uint64_t n_ids, uint64_t k, i
 
 // reads.cu's attach_kmer_index + run_map_reads with the same device functions, one "thread" at a time
 void emu_set_kmer_index(Emu *e, uint32_t k, const uint64_t *tip, const uint32_t *labels, uint64_t n_tips, uint32_t wptl,
-                        const int64_t *first, const int64_t *second, uint64_t n_buckets) {
+                        const int64_t *first, const int64_t *second, uint64_t n_buckets, int use_jump) {
   const uint64_t n_words = (e->v.n + 63) / 64;
   e->kx_tip.assign(tip, tip + n_words);
   e->kx_prefix.assign(n_words + 1, 0);
@@ -284,7 +285,30 @@ void emu_set_kmer_index(Emu *e, uint32_t k, const uint64_t *tip, const uint32_t 
   e->kx_first.assign(first, first + n_buckets);
   e->kx_second.assign(second, second + n_buckets);
   e->kx = KmerIndex{e->kx_tip.data(), e->kx_prefix.data(), e->kx_labels.data(), wptl, (uint32_t)n_buckets,
-                    e->kx_first.data(), e->kx_second.data(), k};
+                    e->kx_first.data(), e->kx_second.data(), k, nullptr, nullptr};
+  if (use_jump) {  // the same construction as attach_kmer_index (reads.cu): doubling + bucket consistency bits
+    const uint64_t n = e->v.n;
+    std::vector<uint32_t> a(n + 1), b(n + 1);
+    for (uint64_t x = 0; x < n; ++x) b[x] = jump_init(e->v, e->kx, (uint32_t)x);
+    for (uint64_t x = 0; x < n; ++x) a[x] = jump_double(b.data(), (uint32_t)x);
+    for (uint64_t x = 0; x < n; ++x) b[x] = jump_double(a.data(), (uint32_t)x);
+    for (uint64_t x = 0; x < n; ++x) a[x] = jump_double(b.data(), (uint32_t)x);
+    e->kx_jump.swap(a);
+    int chars = 0;
+    while ((1u << (chars * 2)) < n_buckets) ++chars;
+    e->kx_ok.assign((n_buckets + 31) / 32 + 1, 0);
+    for (uint64_t bk = 0; bk < n_buckets; ++bk)
+      if (bucket_consistent(e->v, e->kx, (uint32_t)bk, chars)) e->kx_ok[bk >> 5] |= 1u << (bk & 31);
+    e->kx.jump = e->kx_jump.data();
+    e->kx.bucket_ok = e->kx_ok.data();
+  }
+}
+// number of items whose probe may take the shortcut / buckets marked consistent (test diagnostics)
+void emu_kmer_index_stats(Emu *e, uint64_t *out) {
+  uint64_t j = 0, ok = 0;
+  for (uint32_t v : e->kx_jump) j += !(v & kJumpLiteral);
+  for (uint32_t w : e->kx_ok) ok += (uint64_t)__builtin_popcount(w);
+  out[0] = j; out[1] = ok;
 }
 // ids of one read -> out (capacity >= len); returns the count (0 = dropped); kNull ids become ~0
 uint64_t emu_map_read(Emu *e, const char *seq, uint32_t len, int reverse, const uint32_t *member, uint64_t *out) {

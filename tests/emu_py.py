@@ -33,7 +33,8 @@ def lib():
         L.emu_candidates.restype = C.c_uint64
         L.emu_keep_regions.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]
         L.emu_set_kmer_index.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32,
-                                         C.c_void_p, C.c_void_p, C.c_uint64]
+                                         C.c_void_p, C.c_void_p, C.c_uint64, C.c_int]
+        L.emu_kmer_index_stats.argtypes = [C.c_void_p, C.c_void_p]
         L.emu_map_read.restype = C.c_uint64
         L.emu_map_read.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
         L.emu_candidates.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
@@ -99,13 +100,18 @@ class EmuGraph:
         lib().emu_keep_regions(self.h, ids.ctypes.data, ids.size, int(k), int(reverse), st.ctypes.data)
         return dict(zip(("n_added", "levels", "n_invalidated", "n_kept"), map(int, st)))
 
-    def set_kmer_index(self, k, tip_words, labels, first, second):
+    def set_kmer_index(self, k, tip_words, labels, first, second, use_jump=True):
         labels = np.ascontiguousarray(labels, np.uint32)
         self._kx = (np.ascontiguousarray(tip_words, np.uint64), labels, np.ascontiguousarray(first, np.int64),
                     np.ascontiguousarray(second, np.int64))
         t, l, f, s = self._kx
         lib().emu_set_kmer_index(self.h, int(k), t.ctypes.data, l.ctypes.data, l.shape[0], l.shape[1] if l.ndim == 2 else 0,
-                                 f.ctypes.data, s.ctypes.data, f.size)
+                                 f.ctypes.data, s.ctypes.data, f.size, int(use_jump))
+
+    def kmer_index_stats(self):
+        st = np.zeros(2, np.uint64)
+        lib().emu_kmer_index_stats(self.h, st.ctypes.data)
+        return dict(items_with_jump=int(st[0]), buckets_ok=int(st[1]))
 
     def map_reads(self, seqs, cycle_nodes, reverse=False):
         member = np.zeros((self.n + 31) // 32 + 1, np.uint32)

@@ -166,10 +166,14 @@ def test_read_mapping_matches_reference(tmp_path, name):
     k_read_kmers run) against the UNMODIFIED reference get_read_from_sequence (tests/golden/<name>.reads.npz)."""
     og = O.OracleGraph.load(G.unpack_sdbg_files(name, str(tmp_path)))
     labels, first, second = og.kmer_index()
-    g = emu(name)
-    g.set_kmer_index(og.k, _cache[name]["tip"], labels, first, second)
     seqs, variants = G.reads_case(name)
-    for key, (ids, rev, off, flat) in variants.items():
-        got = g.map_reads(seqs, ids, reverse=rev)
-        assert [x.size for x in got] == list(np.diff(off)), key
-        assert np.array_equal(np.concatenate(got), flat), key
+    for use_jump in (False, True):  # literal search / with the Backward^8 shortcut tables
+        g = emu(name)
+        g.set_kmer_index(og.k, _cache[name]["tip"], labels, first, second, use_jump=use_jump)
+        if use_jump:
+            st = g.kmer_index_stats()
+            assert st["items_with_jump"] > 0.9 * g.n and st["buckets_ok"] > 30000
+        for key, (ids, rev, off, flat) in variants.items():
+            got = g.map_reads(seqs, ids, reverse=rev)
+            assert [x.size for x in got] == list(np.diff(off)), (key, use_jump)
+            assert np.array_equal(np.concatenate(got), flat), (key, use_jump)

@@ -123,7 +123,7 @@ def test_sample_workload_read_mapping_matches_oracle(tmp_path):
     assert got_ids.size > 100000
 
 
-def test_full_size_read_mapping_properties():
+def test_full_size_read_mapping_properties(monkeypatch):
     """N3 at 224.7 M items (index attached to the array-built graph): kept reads carry len - k + 1 ids; mapping the
     reverse complement of a batch with reverse=True gives the ids of the batch itself (reverse_pair_ends_sequence is
     an involution, reference src/reads.cpp:20-31); the same k-mer always maps to the same id; repeatable."""
@@ -151,6 +151,12 @@ def test_full_size_read_mapping_properties():
     assert np.array_equal(first, i3[int(o3[0]):int(o3[1])])
     o4, i4 = dg.map_reads((chars, off), ids_all)
     assert np.array_equal(i1, i4)
+    # the Backward^8 shortcut tables change nothing: same ids from the literal search
+    monkeypatch.setenv("MCAAT_KMER_JUMP", "0")
+    lit = DeviceGraph(gs)
+    lit.set_kmer_index(gs["tip"], *S.kmer_index_arrays(gs))
+    o5, i5 = lit.map_reads((chars, off), ids_all)
+    assert np.array_equal(o1, o5) and np.array_equal(i1, i5)
 
 
 def test_full_size_properties():

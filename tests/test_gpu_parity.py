@@ -338,14 +338,16 @@ def test_cpp_drop_in_scc_split_matches_reference(tmp_path, name):
 
 # ------------------------------------------------------------------ read -> node ids
 @pytest.mark.parametrize("name", ["tiny", "biallelic"])
-@pytest.mark.parametrize("via", ["files", "arrays"])
-def test_read_mapping_matches_reference(tmp_path, name, via):
+@pytest.mark.parametrize("via", ["files", "arrays", "files-literal"])
+def test_read_mapping_matches_reference(tmp_path, monkeypatch, name, via):
     """mg_map_reads against the UNMODIFIED reference get_read_from_sequence / reverse_pair_ends_sequence /
     IndexBinarySearch (src/reads.cpp:20-89, sdbg.h:141-207; tests/golden/<name>.reads.npz): real, mutated, random,
     N-containing and too-short sequences, forward and reverse-complemented, two node sets.  The k-mer index comes
     from the graph files (mg_graph_create_from_files) or is attached to an array-built graph."""
     prefix = G.unpack_sdbg_files(name, str(tmp_path))
-    if via == "files":
+    if via == "files-literal":  # without the Backward^8 shortcut tables
+        monkeypatch.setenv("MCAAT_KMER_JUMP", "0")
+    if via.startswith("files"):
         g = DeviceGraph.from_files(prefix)
     else:
         g = DeviceGraph(packed(name))
