@@ -123,6 +123,32 @@ def test_sample_workload_read_mapping_matches_oracle(tmp_path):
     assert got_ids.size > 100000
 
 
+def test_cpp_drop_in_equals_the_unmodified_reference_binary_on_the_sample(tmp_path):
+    """The compiled UNMODIFIED reference (oracle/_ref/ref_cyclefinder, threads=1) and the C++ drop-in
+    (mcaat_b200/host/_build/shim_cyclefinder) on the 11.3 M-item sample written in MEGAHIT's on-disk format: the two
+    dumps — host SDBG invalid bitmap, ordered start lists, raw results, unordered_map iteration order — are
+    byte-identical, with the graph passed through the SDBG getters and decoded on the device from the files."""
+    import subprocess
+    import synth_sdbg as S
+    ref = O.ref_binary("ref_cyclefinder")
+    shim = os.path.join(ROOT, "mcaat_b200", "host", "_build", "shim_cyclefinder")
+    if ref is None or not os.path.exists(shim):
+        pytest.skip("reference / drop-in binaries not built (they need the reference sources at build time)")
+    gs, _ = S.make_workload("c2_sample", device="cuda", want_labels=True)
+    prefix = str(tmp_path / "graph")
+    S.write_megahit_files(gs, prefix)
+    del gs
+    want_path = str(tmp_path / "ref.dump")
+    subprocess.run([ref, prefix, want_path, "1", "20", "27", "77"], check=True, capture_output=True)
+    want = open(want_path, "rb").read()
+    assert len(want) > 1_000_000
+    for ingest in ("0", "1"):
+        out = str(tmp_path / f"shim_{ingest}.dump")
+        subprocess.run([shim, prefix, out, "1", "20", "27", "77"], check=True, capture_output=True,
+                       env=dict(os.environ, MCAAT_GPU_INGEST_FILES=ingest))
+        assert open(out, "rb").read() == want, f"ingest={ingest}"
+
+
 def test_full_size_read_mapping_properties(monkeypatch):
     """N3 at 224.7 M items (index attached to the array-built graph): kept reads carry len - k + 1 ids; mapping the
     reverse complement of a batch with reverse=True gives the ids of the batch itself (reverse_pair_ends_sequence is
