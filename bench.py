@@ -279,6 +279,14 @@ def pinned(a, torch):
     return t, t.numpy().view(a.dtype)
 
 
+WORKLOAD_TEXT = {
+    "c2": "BASELINE.json configs[1], synthetic 50-genome community + 5 strain copies",
+    "c4": "BASELINE.json configs[3], synthetic high-diversity community (250 genomes + 10 strain copies, abundance sigma 2)",
+    "c1": "BASELINE.json configs[0], 5 x 2 Mb genomes with 10 planted arrays, error-free",
+    "c2_sample": "BASELINE.json configs[1] recipe at 1/20 scale",
+}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -295,6 +303,9 @@ def main():
                     help="also time mg_map_reads (SURVEY 8(f) N3) on synthetic reads of the sample workload")
     ap.add_argument("--reads", type=int, default=400000, help="reads per file for --reads-check")
     ap.add_argument("--reads-full", action="store_true", help="--reads-check also on the full bench workload (array-built graph)")
+    ap.add_argument("--sweep", action="store_true",
+                    help="BASELINE.json configs[4]: after the timed steps, time the hot path on the same resident graph at "
+                         "cycle bounds 27-77 / 20-100 x threshold_multiplicity 10 / 20 / 50 (1 warm-up + 2 timed passes each)")
     ap.add_argument("--regions-check", action="store_true",
                     help="also time mg_keep_regions (SURVEY 8(f) N4, k = 128) on the cycles of the bench workload")
     args = ap.parse_args()
@@ -404,6 +415,33 @@ def main():
         wall_ms = wall * 1e3
     ms_per_step = dev_ms / args.steps
     value = stats["n_starts"] / (ms_per_step / 1e3)
+
+    # ---- BASELINE.json configs[4]: search-explosion sweep on the resident graph (not part of the timed steps above)
+    sweep = None
+    if args.sweep:
+        global THR, MIN_LEN, MAX_LEN
+        saved, sweep = (THR, MIN_LEN, MAX_LEN), []
+        for mn, mx in ((27, 77), (20, 100)):
+            for thr in (10, 20, 50):
+                THR, MIN_LEN, MAX_LEN = thr, mn, mx
+                hot_path_step(g, rank, world, dist, torch)
+                g.timers_reset()
+                barrier()
+                ms = []
+                for _ in range(2):
+                    g.step_begin()
+                    st_s, _ = hot_path_step(g, rank, world, dist, torch)
+                    ms.append(g.step_end())
+                barrier()
+                tm = g.timers()
+                sweep.append(dict(threshold_multiplicity=thr, cycle_min_length=mn, cycle_max_length=mx,
+                                  ms_per_step=round(sum(ms) / len(ms), 2), start_nodes_per_s=round(st_s["n_starts"] / (sum(ms) / len(ms) / 1e3), 1),
+                                  phase_ms={k: round(v["ms"] / len(ms), 2) for k, v in tm.items() if v["launches"]},
+                                  **{k: st_s[k] for k in ("n_candidates", "n_starts", "n_searched", "n_cycles", "n_bound_hits",
+                                                          "n_cap_hits", "dls_expansions", "expansions")}))
+                if rank == 0:
+                    print("[sweep]", json.dumps(sweep[-1]), file=sys.stderr, flush=True)
+        THR, MIN_LEN, MAX_LEN = saved
 
     # ---- end to end through the C ABI with HOST buffers (N = 1): upload + index build + search + read-back
     e2e = None
@@ -590,7 +628,7 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "u32", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: BASELINE.json configs[1], synthetic 50-genome community + 5 strain copies, "
+        "config": {"workload": f"{args.workload}: {WORKLOAD_TEXT.get(args.workload, 'synthetic community')}, "
                                f"{n_items} SDBG items (k=23), built by tools/synth_sdbg.py",
                    "n_items": int(n_items), "threshold_multiplicity": THR, "cycle_min_length": MIN_LEN,
                    "cycle_max_length": MAX_LEN, "l2": "graph arrays + navigation cache (>2 GB) exceed the 126 MB L2; "
@@ -607,6 +645,8 @@ def main():
         "roofline": roofline, "setup": {"generate_s": round(gen_s, 2), "nccl_broadcast_s": round(bcast_s, 4),
                                         "graph_device_bytes": g.device_bytes() if g.h else None},
     }
+    if sweep:
+        line["sweep"] = sweep
     if ingest:
         line["ingest"] = ingest
     if regions:

@@ -118,58 +118,77 @@ def sdbg_from_kmers(edges, counts, k=K, want_labels=False):
     k-1 chars) for every suffix k-mer that no (k+1)-mer starts with.  Sort key = (label chars,
     full-length flag, W char) (:441-517); W / last / tip as in Lv2Postprocess (:520-612).
     """
+    if isinstance(edges, list):  # [codes, counts] handed over by the caller: freed here as soon as they are consumed
+        box = edges
+        edges, counts = box.pop(0), box.pop(0)
     dev = edges.device
     kk = 2 * k
     mask_k = (1 << kk) - 1
     mask_s = (1 << (kk - 2)) - 1
+    # Temporaries are dropped as soon as they are consumed: at 10^9 (k+1)-mers (workload c4) every int64 array is 8 GB.
     X = edges & mask_k          # e[1..k]
-    b = edges >> kk             # e[0]
-    P = edges >> 2              # e[0..k-1]
     Xu = torch.unique(X)        # sorted
+    P = edges >> 2              # e[0..k-1]
     Pu, p_inv = torch.unique(P, return_inverse=True)
+    del P
     p_cnt = torch.zeros(Pu.numel(), dtype=torch.int64, device=dev).index_add_(0, p_inv, counts)
+    del p_inv
     # `$`-labelled items: prefix k-mers with no incoming (k+1)-mer
     dmask = ~_isin_sorted(Pu, Xu)
     d_nodes, d_cnt = Pu[dmask], p_cnt[dmask]
+    del p_cnt, dmask
     # tips: suffix k-mers with no outgoing (k+1)-mer
     x_inv = torch.searchsorted(Xu, X)
     x_cnt = torch.zeros(Xu.numel(), dtype=torch.int64, device=dev).index_add_(0, x_inv, counts)
+    del x_inv
     tmask = ~_isin_sorted(Xu, Pu)
+    del Pu
     t_nodes, t_cnt = Xu[tmask], x_cnt[tmask]
+    del Xu, x_cnt, tmask
     t_S = t_nodes & mask_s
     t_b = t_nodes >> (kk - 2)
-    key = torch.cat([(X << 4) | 8 | b, (d_nodes << 4) | 8 | 4, ((t_S << 2) << 4) | t_b])
-    cnt = torch.cat([counts, d_cnt, t_cnt])
+    X <<= 4
+    X |= 8
+    X |= edges >> kk            # e[0]
+    del edges
+    key = torch.cat([X, (d_nodes << 4) | 8 | 4, ((t_S << 2) << 4) | t_b])
+    del X, d_nodes, t_nodes, t_S, t_b
+    cnt = torch.cat([counts, d_cnt, t_cnt]).clamp_(max=65535).to(torch.int32)  # multiplicity saturates (:579)
+    del counts, d_cnt, t_cnt
     key, order = torch.sort(key)
     cnt = cnt[order]
+    del order
     n = key.numel()
-    prev = key & 7
-    flag = (key >> 3) & 1
-    S = key >> 6
     # W: first item of an S-group carrying char c gets c+1, later ones c+5; `$` -> 0
-    sb = (S << 3) | prev
-    sb_sorted, o2 = torch.sort(sb, stable=True)
+    sb = ((key >> 6) << 3) | (key & 7)   # (S, previous char)
+    sb, o2 = torch.sort(sb, stable=True)
     first = torch.ones(n, dtype=torch.bool, device=dev)
-    first[1:] = sb_sorted[1:] != sb_sorted[:-1]
+    first[1:] = sb[1:] != sb[:-1]
+    del sb
     is_first = torch.empty(n, dtype=torch.bool, device=dev)
     is_first[o2] = first
+    del o2, first
+    prev = (key & 7).to(torch.uint8)
     w = torch.where(prev == 4, torch.zeros_like(prev), torch.where(is_first, prev + 1, prev + 5))
+    del prev, is_first
     # last: final item of a node (same label, full length); tips are never `last`
+    tip = ((key >> 3) & 1) == 0
     node = key >> 3
     last = torch.ones(n, dtype=torch.bool, device=dev)
     last[:-1] = node[1:] != node[:-1]
-    last &= flag == 1
-    tip = flag == 0
-    mult = cnt.clamp(max=65535)
+    del node
+    last &= ~tip
+    mult = cnt
     first_char = key >> (4 + kk - 2)
     per_char = torch.bincount(first_char, minlength=4)[:4]
+    del first_char
     f = torch.zeros(6, dtype=torch.int64)
     f[0] = -1
     f[2:] = torch.cumsum(per_char.cpu(), 0)
     out = dict(n=n, k=k, w=_pack_nibbles(w).cpu().numpy().view(np.uint64),
                last=_pack_bits(last).cpu().numpy().view(np.uint64),
                tip=_pack_bits(tip).cpu().numpy().view(np.uint64),
-               mult=mult.to(torch.int32).cpu().numpy().astype(np.uint16), f=f.numpy().astype(np.int64))
+               mult=mult.cpu().numpy().astype(np.uint16), f=f.numpy().astype(np.int64))
     if want_labels:
         out["tip_label_chars"] = (key[tip] >> 4).cpu().numpy()  # 2k bits, S then a zero pad char
         out["first8"] = (key >> (4 + kk - 16)).cpu().numpy()
@@ -315,6 +334,11 @@ WORKLOADS = {
                      "--biallelic-arrays", "10", "--bound-arrays", "2", "--strain-pairs", "5", "--tandem", "200",
                      "--abundance-sigma", "1.0"],
                total_bases=50_000_000 * 2 * 150, error_events=500_000, seed=12),
+    # BASELINE.json configs[3]: high-diversity community (250 genomes, steep abundance tail), ~1 B-item SDBG
+    "c4": dict(argv=["--genomes", "250", "--genome-len", "2000000", "--arrays", "500", "--shared-family-arrays", "100",
+                     "--biallelic-arrays", "50", "--bound-arrays", "4", "--strain-pairs", "10", "--tandem", "1000",
+                     "--abundance-sigma", "2.0"],
+               total_bases=250_000_000 * 2 * 150, error_events=1_200_000, seed=13),
     # 1/20 scale of the same recipe: the bounded sample the CPU baselines run on
     "c2_sample": dict(argv=["--genomes", "3", "--genome-len", "1600000", "--arrays", "6", "--shared-family-arrays", "2",
                             "--biallelic-arrays", "1", "--bound-arrays", "1", "--strain-pairs", "1", "--tandem", "12",
@@ -366,6 +390,8 @@ def sample_reads(name, n_reads, seed=1, read_len=150, error_rate=0.002):
 def make_workload(name, device="cpu", want_labels=False):
     cfg = WORKLOADS[name]
     e, c, info = community_spectrum(cfg["argv"], cfg["total_bases"], cfg["error_events"], cfg["seed"], device)
-    g = sdbg_from_kmers(e, c, want_labels=want_labels)
+    box = [e, c]
+    del e, c
+    g = sdbg_from_kmers(box, None, want_labels=want_labels)
     info.update(workload=name, n_items=g["n"])
     return g, info
