@@ -283,6 +283,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
         MG_CUDA(cudaStreamSynchronize(s));
         P.owner = nullptr;
         if (hc || getenv("MCAAT_PEEL_EXHAUSTIVE")) {  // a walk hit its hop cap: exhaustive pointer jumping
+          if (getenv("MCAAT_PEEL_VERBOSE")) fprintf(stderr, "[peel] exhaustive pointer jumping (walk cap hit: %d)\n", hc);
           for (int round = 0; round < 34; round += 2) {
             MG_CUDA(cudaMemsetAsync(unresolved, 0, 4, s));
             MG_LAUNCH(k_chain_jump, grid, 256, 0, s, n, P, unresolved);

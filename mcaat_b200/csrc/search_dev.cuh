@@ -147,9 +147,10 @@ MG_HD bool chain_jump_item(const PeelView &P, uint32_t v) {
 //   c. every other chain node takes the terminal of its owner, or — near the head of a chain, where no
 //      walk passed — walks to the first item that knows it.
 // An item that leads into a cycle of chain nodes ends with a chain node as its pointer, which
-// terminal_of() reports as unresolvable, exactly like the exhaustive pointer jumping.  Walks are
-// capped; hitting the cap (astronomically unlikely away from splitter-free cycles) makes the host
-// fall back to exhaustive pointer jumping — every pointer stays a valid forward pointer throughout.
+// terminal_of() reports as unresolvable, exactly like the exhaustive pointer jumping.  Cycles without
+// a splitter are recognised by the walks themselves (step a: the walk meets its own claim; step c: Brent's
+// checkpoint).  Walks are capped; hitting the cap (a splitter-free stretch of 4096+ chain nodes) makes the
+// host fall back to exhaustive pointer jumping — every pointer stays a valid forward pointer throughout.
 constexpr uint32_t kWalkCapSplitter = 1u << 16, kWalkCapHead = 1u << 12;
 MG_HD bool is_splitter_id(uint32_t v) { return ((v * 0x9E3779B1u) >> 26) == 0; }
 MG_HD uint32_t ld_cg_u32(const uint32_t *p) { return ld_cg32(p); }
@@ -190,11 +191,19 @@ MG_HD bool chain_resolve_item(const PeelView &P, uint32_t v) {
   uint32_t o = P.owner[v];
   if (o != kNull) { P.ptr[v] = ld_cg_u32(&P.ptr[o]); return true; }
   uint32_t p = ld_cg_u32(&P.ptr[v]);
+  // Brent's cycle detection: `mark` is the item the walk stood on 2^j hops after v.  A walk that comes back to
+  // it runs round a cycle of chain nodes with neither splitter nor owner (the closed loop of a tandem repeat
+  // whose entry and exit were filtered out has ~50 nodes, so about half of them hold no 1-in-64 splitter):
+  // v is unresolvable and ptr[v] stays its successor, a chain node — what terminal_of() tests.  Nobody
+  // writes a pointer on such a component, so the walk is deterministic: <= 3 x (tail + cycle) hops.
+  uint32_t mark = v, since = 0, power = 1;
   for (uint32_t hops = 0; hops < kWalkCapHead; ++hops) {
     if (!bm_get(P.chain, p)) { P.ptr[v] = p; return true; }
     if (is_splitter_id(p)) { P.ptr[v] = ld_cg_u32(&P.ptr[p]); return true; }
     o = ld_cg_u32(&P.owner[p]);
     if (o != kNull) { P.ptr[v] = ld_cg_u32(&P.ptr[o]); return true; }
+    if (p == mark) return true;
+    if (++since == power) { mark = p; power <<= 1; since = 0; }
     p = ld_cg_u32(&P.ptr[p]);  // the successor, or already p's terminal: both lie ahead on the same chain
   }
   return false;

@@ -237,7 +237,7 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
     valid += ok;
     tips += ok && (fin[i] >> 32) == 0;
   }
-  stats[2] = peeled; stats[3] = valid; stats[4] = tips;
+  stats[2] = peeled; stats[3] = valid; stats[4] = tips; stats[5] = capped;
 }
 void emu_invalid(Emu *e, uint8_t *out) {
   for (uint64_t i = 0; i < e->v.n; ++i) out[i] = get_inv(e->v, (uint32_t)i);

@@ -85,9 +85,9 @@ class EmuGraph:
         return bad.value
 
     def prune(self, reverse_order=False):
-        st = np.zeros(5, np.uint64)
+        st = np.zeros(6, np.uint64)
         lib().emu_prune(self.h, st.ctypes.data, int(reverse_order))
-        return dict(zip(("n_tips_before", "n_mult1", "n_peeled", "n_valid", "n_tips_after"), map(int, st)))
+        return dict(zip(("n_tips_before", "n_mult1", "n_peeled", "n_valid", "n_tips_after", "walk_cap_hit"), map(int, st)))
 
     def invalid(self):
         out = np.empty(self.n, np.uint8)

@@ -28,8 +28,14 @@ _wl = {}
 
 def workload(name):
     if name not in _wl:
+        import gc
+
+        import torch
+
         import synth_sdbg as S
+        gc.collect()  # device graphs of earlier tests
         _wl[name] = S.make_workload(name, device="cuda")[0]
+        torch.cuda.empty_cache()  # the generator's blocks (~100 GB at c4) go back to the driver: the library allocates beside torch
     return _wl[name]
 
 
@@ -71,6 +77,20 @@ def test_c1_workload_matches_oracle():
     # SURVEY's C1 probe: 340 candidates, 20 searches (the coverage sampling differs a little between devices)
     assert 300 < want.stats["n_candidates"] < 380 and len(got.searched) >= 10
     _wl.pop("c1", None)
+
+
+def test_chain_cycles_without_splitter_match_oracle(monkeypatch, capfd):
+    """Closed loops of chain nodes with neither entry nor splitter (tests/test_device_logic_host.py:chain_cycle_graph):
+    same result as the oracle, and the peel recognises them without the exhaustive pointer-jumping fallback."""
+    from test_device_logic_host import chain_cycle_graph
+    monkeypatch.setenv("MCAAT_PEEL_VERBOSE", "1")
+    g = chain_cycle_graph()
+    w, last, tip = unpack(g)
+    want = O.OracleGraph.from_arrays(w, last, tip, g["mult"], g["f"], g["k"]).run(2, 27, 77)
+    got = run(DeviceGraph(g), 2, 27, 77)
+    assert O.same_run(want, got) == []
+    assert len(got.searched) > 20 and got.stats["n_peeled"] > 1000
+    assert "exhaustive pointer jumping" not in capfd.readouterr().err
 
 
 @pytest.mark.parametrize("thr,mn,mx", [(20, 27, 77), (10, 20, 100)])
