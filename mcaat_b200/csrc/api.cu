@@ -190,7 +190,7 @@ void mg_graph_destroy(mg_graph *g) {
   if (g->stream) cudaStreamSynchronize(g->stream);
   flush_timers(g);
   // buffers go back to the pool on the handle's stream, which must still exist
-  for (mg::DevBuf *b : {&g->wb, &g->fb, &g->mult, &g->hints, &g->inv0, &g->adj, &g->visited, &g->enum_arena,
+  for (mg::DevBuf *b : {&g->wb, &g->fb, &g->mult, &g->hints, &g->inv0, &g->adj, &g->merge, &g->visited, &g->enum_arena,
                        &g->kx_tip, &g->kx_tip_prefix, &g->kx_labels, &g->kx_buckets, &g->kx_jump, &g->kx_bucket_ok})
     b->release();
   scratch_flush(g->stream);  // nothing cached may outlive the stream it is ordered on

@@ -174,7 +174,10 @@ __global__ void k_cpeel(PeelView P, const uint32_t *work, uint32_t n_work, uint3
 }
 // step 4: invalid bits of the removed items, final navigation cache, "After pruning" statistics
 // (:443-452): valid count and tips
-__global__ void k_peel_final(GraphView g, PeelView P, unsigned long long *n_peeled, unsigned long long *n_valid,
+// `merge` (zeroed by the caller): bit Forward(e) for every item e that stays valid and carries a non-first label
+// (5..8, sdbg_def.h:11-29) — the nodes with a second valid incoming edge, which is all ChunkStartNodes' in-degree test
+// (:398) can accept; k_candidates_merge evaluates Backward + the group scan for those nodes only.
+__global__ void k_peel_final(GraphView g, PeelView P, uint32_t *merge, unsigned long long *n_peeled, unsigned long long *n_valid,
                              unsigned long long *n_tips) {
   __shared__ unsigned sh[3];
   BlockCounters<3> bc(sh);
@@ -186,6 +189,10 @@ __global__ void k_peel_final(GraphView g, PeelView P, unsigned long long *n_peel
       a = peel_final_item(g, P, (uint32_t)i, peeled);
       valid = !peeled && !get_inv(g, (uint32_t)i);
       tip = valid && (a >> 32) == 0;
+      if (valid && get_w(g, (uint32_t)i) > 4) {
+        uint32_t nx = a ? (uint32_t)a : forward(g, (uint32_t)i);  // the cache keeps Forward(e) of every valid item
+        if (nx < g.n) atomicOr(&merge[nx >> 5], 1u << (nx & 31));
+      }
     }
     unsigned mp = __ballot_sync(0xffffffffu, peeled), mv = __ballot_sync(0xffffffffu, valid),
              mt = __ballot_sync(0xffffffffu, tip);
@@ -365,7 +372,9 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
         }
       }
     }
-    MG_LAUNCH(k_peel_final, stream_grid(g, n, 256), 256, 0, s, v, P, c + 2, c + 3, c + 4);
+    MG_TRY(g->merge.ensure(bm_bytes));
+    MG_CUDA(cudaMemsetAsync(g->merge.p, 0, bm_bytes, s));
+    MG_LAUNCH(k_peel_final, stream_grid(g, n, 256), 256, 0, s, v, P, g->merge.as<uint32_t>(), c + 2, c + 3, c + 4);
     MG_CUDA(cudaStreamSynchronize(s));
   }
   unsigned long long h[5];

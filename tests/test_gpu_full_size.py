@@ -103,6 +103,34 @@ def test_sample_workload_matches_oracle(thr, mn, mx):
     assert len(got.searched) > 50
 
 
+@pytest.mark.parametrize("name", ["c2_sample", "chain_cycles"])
+def test_candidate_scan_variants_agree(monkeypatch, name):
+    """ChunkStartNodes' predicate (:398-408) three ways: the literal kernel on the pruned graph (MCAAT_CAND_LITERAL),
+    the streaming kernel over the nodes k_peel_final marked as having a valid non-first incoming edge, and the literal
+    kernel again after something else changed the invalid bits (the marks are dropped with the navigation cache)."""
+    if name == "chain_cycles":
+        from test_device_logic_host import chain_cycle_graph
+        g = chain_cycle_graph()
+    else:
+        g = workload(name)
+    dg = DeviceGraph(g)
+    dg.prune()
+    for thr in (0, 2, 20, 200):
+        fast = dg.candidates(thr)
+        monkeypatch.setenv("MCAAT_CAND_LITERAL", "1")
+        literal = dg.candidates(thr)
+        monkeypatch.delenv("MCAAT_CAND_LITERAL")
+        assert np.array_equal(fast, literal) and (thr > 2 or fast.size > 20)
+    # region extraction invalidates items: the in-degree of the survivors changes, the scan must follow
+    seeds = dg.candidates(2)[:50]
+    st = dg.keep_regions(seeds, 40)
+    assert st["n_invalidated"] > 0
+    after = dg.candidates(0)
+    monkeypatch.setenv("MCAAT_CAND_LITERAL", "1")
+    assert np.array_equal(after, dg.candidates(0))
+    dg.close()
+
+
 def test_sample_workload_regions_match_oracle():
     """SURVEY 8(f) N4 at 11.3 M items: cycles of the run -> mg_keep_regions (k = 128, a 150-bp read at k = 23) against
     the oracle's restatement of keep_crispr_regions_extended_by_k on the same pruned graph."""
