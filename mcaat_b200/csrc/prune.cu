@@ -46,6 +46,34 @@ __global__ void k_tips(GraphView g, uint32_t *bits, unsigned long long *count) {
   unsigned long long *dst[1] = {count};
   bc.flush(dst);
 }
+// The same bitmap from the dead ends' side (search_dev.cuh): a streaming pass marks the dead ends (one block line per
+// item), their ids are compacted, and one thread per dead end evaluates IncomingEdges — dense warps, whatever the
+// share of dead ends (0.07 % of the items at C2, 2.5 % at C4).  `bits` of k_tips_of_dead_ends is zeroed by the caller.
+__global__ void k_dead_ends(GraphView g, uint32_t *dead) {
+  const uint64_t n32 = (g.n + 31) & ~31ull;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
+    unsigned m = __ballot_sync(0xffffffffu, i < g.n && is_dead_end(g, (uint32_t)i));
+    if ((threadIdx.x & 31) == 0) dead[i >> 5] = m;
+  }
+}
+__global__ void k_tips_of_dead_ends(GraphView g, const uint32_t *ids, uint32_t n_ids, uint32_t *bits, unsigned long long *count) {
+  __shared__ unsigned sh[1];
+  BlockCounters<1> bc(sh);
+  const uint32_t n32 = (n_ids + 31) & ~31u;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
+    unsigned fresh = 0;
+    if (i < n_ids) {
+      uint32_t in[4];
+      int deg = incoming<false, false>(g, ids[i], in);
+      if (deg > 4) deg = 4;
+      for (int j = 0; j < deg; ++j) fresh += bm_set_atomic(bits, in[j]) ? 1u : 0u;
+    }
+    for (int d = 16; d; d >>= 1) fresh += __shfl_down_sync(0xffffffffu, fresh, d);
+    if ((threadIdx.x & 31) == 0) bc.add(0, fresh);
+  }
+  unsigned long long *dst[1] = {count};
+  bc.flush(dst);
+}
 // InvalidateMultiplicityOneNodes: every item with multiplicity <= 1 becomes invalid; the count
 // includes items that were invalid already, like the reference's counter.
 __global__ void k_mult1(GraphView g, unsigned long long *count) {
@@ -230,7 +258,19 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
   MG_TRY(tipbits.alloc(bm_bytes));
   if (n) {
     TimedScope ts(g, T_TIPS, n);
-    MG_LAUNCH(k_tips, stream_grid(g, n, 256), 256, 0, s, v, tipbits.as<uint32_t>(), c + 0);
+    if (getenv("MCAAT_TIPS_LITERAL")) {
+      MG_LAUNCH(k_tips, stream_grid(g, n, 256), 256, 0, s, v, tipbits.as<uint32_t>(), c + 0);
+    } else {
+      DevBuf dead, dead_ids;
+      uint64_t n_dead = 0;
+      MG_TRY(dead.alloc(bm_bytes));
+      MG_LAUNCH(k_dead_ends, stream_grid(g, n, 256), 256, 0, s, v, dead.as<uint32_t>());
+      MG_TRY(bitmap_to_ids(dead.as<uint32_t>(), n, dead_ids, &n_dead, s));
+      MG_CUDA(cudaMemsetAsync(tipbits.p, 0, bm_bytes, s));
+      if (n_dead)
+        MG_LAUNCH(k_tips_of_dead_ends, stream_grid(g, n_dead, 256), 256, 0, s, v, dead_ids.as<uint32_t>(), (uint32_t)n_dead,
+                  tipbits.as<uint32_t>(), c + 0);
+    }
   }
   // --- InvalidateMultiplicityOneNodes (:439)
   if (n) {

@@ -105,6 +105,9 @@ MG_HD unsigned get_w(const GraphView &g, uint32_t i) {
 MG_HD bool get_lt(const GraphView &g, uint32_t i) {
   return (ld_ro(&g.fb[i >> 8].lt[(i >> 6) & 3]) >> (i & 63)) & 1;
 }
+MG_HD bool get_last(const GraphView &g, uint32_t i) {
+  return (ld_ro(&g.fb[i >> 8].last[(i >> 6) & 3]) >> (i & 63)) & 1;
+}
 // COHERENT = true inside kernels that set invalid bits while other threads read them
 template <bool COHERENT = false>
 MG_HD bool get_inv(const GraphView &g, uint32_t i) {

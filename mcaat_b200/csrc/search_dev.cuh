@@ -332,6 +332,28 @@ MG_HD uint64_t peel_final_item(const GraphView &g, const PeelView &P, uint32_t v
   return (uint64_t)next | ((uint64_t)keep << 32);
 }
 
+// ------------------------------------------------------------------ CollectTips from the dead ends' side
+// CollectTips (src/cycle_finder.cpp:346-357) asks every item e for EdgeOutdegree(e) == 0: Forward(e) (rank + select)
+// and a scan of the target node's items for a valid one (sdbg.h:296-320).  The same set, turned round: an item b that
+// closes a node (`last` bit) none of whose items is valid is a dead end, and the valid items e with Forward(e) == b
+// are exactly its valid incoming edges (IncomingEdges, sdbg.h:245-287, evaluated whatever b's own invalid bit says).
+// Dead ends are rare (0.07 % of the items at C2, 2.5 % at C4), everything else is decided by the item's own block
+// line.  Returns the number of ids written to in[] (0 when b is not a dead end).
+MG_HD bool is_dead_end(const GraphView &g, uint32_t b) {
+  if (!get_last(g, b)) return false;
+  uint32_t x = b;
+  do {  // the node's items, as ComputeOutgoings scans them
+    if (!get_inv(g, x)) return false;
+    --x;
+  } while (x != kNull && !get_lt(g, x));
+  return true;
+}
+MG_HD int dead_end_incoming(const GraphView &g, uint32_t b, uint32_t *in) {
+  if (!is_dead_end(g, b)) return 0;
+  int deg = incoming<false, false>(g, b, in);
+  return deg > 4 ? 4 : deg;
+}
+
 // ------------------------------------------------------------------ start-node predicate
 // src/cycle_finder.cpp:398-408: valid, indegree >= 2, multiplicity > threshold, no incoming edge
 // equal to the node itself (_IncomingNotEqualToCurrentNode, :29-36).

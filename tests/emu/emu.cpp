@@ -141,8 +141,16 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   const size_t words = (n + 31) / 32 + 1;
   std::vector<uint32_t> tipbits(words, 0), chain(words, 0), tpeeled(words, 0), ptr(n + 1);
   uint64_t tips0 = 0;
-  for (uint64_t i = 0; i < n; ++i)
-    if (outgoing(v, (uint32_t)i, nullptr) == 0) { tipbits[i >> 5] |= 1u << (i & 31); ++tips0; }
+  if (reverse_order & 1) {  // CollectTips literally ...
+    for (uint64_t i = 0; i < n; ++i)
+      if (outgoing(v, (uint32_t)i, nullptr) == 0) { tipbits[i >> 5] |= 1u << (i & 31); ++tips0; }
+  } else {                  // ... and from the dead ends' side (k_tips_dead_ends)
+    for (uint64_t i = 0; i < n; ++i) {
+      uint32_t in[4];
+      const int deg = dead_end_incoming(v, (uint32_t)i, in);
+      for (int j = 0; j < deg; ++j) tips0 += bm_set_atomic(tipbits.data(), in[j]) ? 1 : 0;
+    }
+  }
   stats[0] = tips0;
   uint64_t m1 = 0;
   for (uint64_t i = 0; i < n; ++i)

@@ -97,13 +97,14 @@ def test_small_arena_overflow_is_rerun_exactly():
 def test_peel_variants_agree(name):
     """splitter-based chain resolution (forward / reverse item order) == exhaustive pointer jumping (2, 3);
     with and without (4..7) the re-classification of unary branch nodes"""
-    inv = []
-    for mode in range(8):
+    inv, tips = [], []
+    for mode in range(8):  # odd modes also collect the tips literally, even ones from the dead ends' side
         g = emu(name)
-        g.prune(reverse_order=mode)
+        tips.append(g.prune(reverse_order=mode)["n_tips_before"])
         inv.append(g.invalid())
     for other in inv[1:]:
         assert np.array_equal(inv[0], other)
+    assert len(set(tips)) == 1 and tips[0] > 0
 
 
 def test_dls_tiers_agree():

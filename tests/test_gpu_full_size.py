@@ -131,6 +131,27 @@ def test_candidate_scan_variants_agree(monkeypatch, name):
     dg.close()
 
 
+@pytest.mark.parametrize("name", ["c2_sample", "chain_cycles", "c1"])
+def test_tip_collection_variants_agree(monkeypatch, name):
+    """CollectTips (:346-357) literally (MCAAT_TIPS_LITERAL: EdgeOutdegree of every item) and from the dead ends' side
+    (k_tips_dead_ends: IncomingEdges of every node without a valid item): same count, same pruned graph."""
+    if name == "chain_cycles":
+        from test_device_logic_host import chain_cycle_graph
+        g = chain_cycle_graph()
+    else:
+        g = workload(name)
+    dg = DeviceGraph(g)
+    a = dg.prune()
+    inv_a = dg.invalid()
+    dg.reset()
+    monkeypatch.setenv("MCAAT_TIPS_LITERAL", "1")
+    b = dg.prune()
+    assert a == b and a["n_tips_before"] > 0
+    assert np.array_equal(inv_a, dg.invalid())
+    dg.close()
+    _wl.pop("c1", None)
+
+
 def test_sample_workload_regions_match_oracle():
     """SURVEY 8(f) N4 at 11.3 M items: cycles of the run -> mg_keep_regions (k = 128, a 150-bp read at k = 23) against
     the oracle's restatement of keep_crispr_regions_extended_by_k on the same pruned graph."""
