@@ -115,11 +115,16 @@ __global__ void k_chain_init(GraphView g, PeelView P, unsigned long long *n_pair
   bc.flush(dst);
 }
 // step 2 (search_dev.cuh): splitter walks, pointer jumping over the splitters, resolution of the rest
+// (the per-item passes are grid-stride loops; the light ones — split_mark, relink — run on a fixed grid, because with one
+//  thread per item the 4 M blocks of a 10^9-item graph cost more in block scheduling than the few bytes each of them
+//  moves; the ones that walk or insert — chain_resolve, dep_register — measured faster with one thread per item)
 __global__ void k_split_mark(uint64_t n, PeelView P, uint32_t *split) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool sp = i < n && bm_get(P.chain, (uint32_t)i) && is_splitter_id((uint32_t)i);
-  unsigned m = __ballot_sync(0xffffffffu, sp);
-  if ((threadIdx.x & 31) == 0 && i < n) split[i >> 5] = m;
+  const uint64_t n32 = (n + 31) & ~31ull;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
+    bool sp = i < n && bm_get(P.chain, (uint32_t)i) && is_splitter_id((uint32_t)i);
+    unsigned m = __ballot_sync(0xffffffffu, sp);
+    if ((threadIdx.x & 31) == 0) split[i >> 5] = m;
+  }
 }
 __global__ void k_split_walk(PeelView P, const uint32_t *ids, uint32_t n_ids, int *capped) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -131,8 +136,8 @@ __global__ void k_split_jump(PeelView P, const uint32_t *ids, uint32_t n_ids, in
   if (__any_sync(0xffffffffu, u) && (threadIdx.x & 31) == 0) *unresolved = 1;
 }
 __global__ void k_chain_resolve(uint64_t n, PeelView P, int *capped) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n && !chain_resolve_item(P, (uint32_t)i)) *capped = 1;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    if (!chain_resolve_item(P, (uint32_t)i)) *capped = 1;
 }
 // step 2b (search_dev.cuh): unary branch nodes become chain nodes
 __global__ void k_reclass(GraphView g, PeelView P, uint32_t *fresh, uint32_t *newseed, unsigned long long *n_fresh,
@@ -163,8 +168,8 @@ __global__ void k_or_words(uint32_t *dst, const uint32_t *src, size_t n_words) {
   if (i < n_words) dst[i] |= src[i];
 }
 __global__ void k_relink(uint64_t n, PeelView P, const uint32_t *fresh) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) relink_item(P, fresh, (uint32_t)i);
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    relink_item(P, fresh, (uint32_t)i);
 }
 // exhaustive fallback: one pointer-jumping round over every item
 __global__ void k_chain_jump(uint64_t n, PeelView P, int *unresolved) {
@@ -174,8 +179,8 @@ __global__ void k_chain_jump(uint64_t n, PeelView P, int *unresolved) {
 }
 // step 3a: (terminal -> dependent branch node) multimap
 __global__ void k_dep_register(GraphView g, PeelView P) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < g.n) dep_register_item(g, P, (uint32_t)i);
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < g.n; i += (uint64_t)gridDim.x * blockDim.x)
+    dep_register_item(g, P, (uint32_t)i);
 }
 // step 3b: asynchronous work list over peeled terminals; each thread follows its cascade with a
 // small private stack, the rest goes to the next work list
@@ -309,7 +314,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
         MG_CUDA(cudaMemsetAsync(owner.p, 0xFF, owner.bytes, s));
         MG_CUDA(cudaMemsetAsync(c + 7, 0, 8, s));
         P.owner = owner.as<uint32_t>();
-        MG_LAUNCH(k_split_mark, grid, 256, 0, s, n, P, split.as<uint32_t>());
+        MG_LAUNCH(k_split_mark, stream_grid(g, n, 256), 256, 0, s, n, P, split.as<uint32_t>());
         uint64_t n_split = 0;
         MG_TRY(bitmap_to_ids(split.as<uint32_t>(), n, split_ids, &n_split, s));
         if (n_split) {
@@ -370,7 +375,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
               if (!h) break;
             }
             MG_LAUNCH(k_or_words, grid_for(n_words, 256), 256, 0, s, chain.as<uint32_t>(), fresh.as<uint32_t>(), n_words);
-            MG_LAUNCH(k_relink, grid, 256, 0, s, n, P, fresh.as<uint32_t>());
+            MG_LAUNCH(k_relink, stream_grid(g, n, 256), 256, 0, s, n, P, fresh.as<uint32_t>());
           }
           if (hc[1])
             MG_LAUNCH(k_or_words, grid_for(n_words, 256), 256, 0, s, tpeeled.as<uint32_t>(), newseed.as<uint32_t>(), n_words);

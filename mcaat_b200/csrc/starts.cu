@@ -21,18 +21,20 @@ __global__ void k_candidates(GraphView g, uint64_t thr, uint32_t *bits) {
 // the nodes that have one (`merge`, bit at the node's last item).  Everything else is decided by the item's own
 // block line (validity, `last` bits) and its multiplicity: a streaming pass instead of rank + select per item.
 __global__ void k_candidates_merge(GraphView g, uint64_t thr, const uint32_t *__restrict__ merge, uint32_t *bits) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool c = false;
-  if (i < g.n) {
-    const uint32_t v = (uint32_t)i;
-    if (!get_inv(g, v) && (uint64_t)get_mult(g, v) > thr) {
-      uint32_t b = v;  // last item of v's node: a valid item is an edge of a full-length node, tips sort before the group
-      while (b + 1 < g.n && !get_lt(g, b)) ++b;
-      if (bm_get(merge, b)) c = is_candidate(g, v, thr);
+  const uint64_t n32 = (g.n + 31) & ~31ull;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
+    bool c = false;
+    if (i < g.n) {
+      const uint32_t v = (uint32_t)i;
+      if (!get_inv(g, v) && (uint64_t)get_mult(g, v) > thr) {
+        uint32_t b = v;  // last item of v's node: a valid item is an edge of a full-length node, tips sort before the group
+        while (b + 1 < g.n && !get_lt(g, b)) ++b;
+        if (bm_get(merge, b)) c = is_candidate(g, v, thr);
+      }
     }
+    unsigned m = __ballot_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0) bits[i >> 5] = m;
   }
-  unsigned m = __ballot_sync(0xffffffffu, c);
-  if ((threadIdx.x & 31) == 0 && i < g.n) bits[i >> 5] = m;
 }
 
 int run_candidates(mg_graph *g, uint64_t thr, DevBuf &ids, uint64_t *n_out) {
@@ -44,7 +46,8 @@ int run_candidates(mg_graph *g, uint64_t thr, DevBuf &ids, uint64_t *n_out) {
   if (v.n) {
     TimedScope ts(g, T_CAND, v.n);
     if (g->pruned && g->merge.p && !getenv("MCAAT_CAND_LITERAL"))
-      MG_LAUNCH(k_candidates_merge, grid_for(v.n, 256), 256, 0, s, v, thr, g->merge.as<uint32_t>(), bits.as<uint32_t>());
+      MG_LAUNCH(k_candidates_merge, std::min(grid_for(v.n, 256), (unsigned)g->sm_count * 16u), 256, 0, s, v, thr,
+                g->merge.as<uint32_t>(), bits.as<uint32_t>());
     else
       MG_LAUNCH(k_candidates, grid_for(v.n, 256), 256, 0, s, v, thr, bits.as<uint32_t>());
   }
