@@ -368,14 +368,17 @@ MG_HD_NOINLINE bool ball_dfs(int min_len, int max_len, const BallArena &A, DfsSt
         // A relax entry (x, u) only acts when lock[u] < M - x + 1, and locks never decrease during
         // a relaxation, so entries that fail the test when they would be pushed are dropped at once
         // (:198-199 push them, :195 discards them when popped); the test is repeated at the pop.
+        // The top of the relax stack lives in a register (`r`, valid while `have`): the entry pushed last is the
+        // one popped next, so a chain of single-parent relaxations never goes through memory.  Same LIFO order.
         uint32_t rn = 0;
-        A.relax[rn++] = ((uint32_t)b << 16) | v;
-        while (rn) {
-          const uint32_t r = A.relax[--rn];
+        uint32_t r = ((uint32_t)b << 16) | v;
+        bool have = true;
+        while (have) {
           const int rb = (int)(r >> 16);
           const uint32_t u = r & 0xFFFFu;
           const uint32_t mu_ = N[u].meta;
           const uint64_t ins = T[u].in4;
+          have = false;
           if ((int)(mu_ & kMetaLock) < M - rb + 1) {        // :195-196
             N[u].meta = (mu_ & ~kMetaLock) | (uint32_t)(M - rb + 1);
             ++expansions;                                   // _GetIncomings(u), :197
@@ -389,9 +392,16 @@ MG_HD_NOINLINE bool ball_dfs(int min_len, int max_len, const BallArena &A, DfsSt
             for (int i = 0; i < 4; ++i)
               if ((uint32_t)i < nin) {
                 const uint32_t w = (uint32_t)(ins >> (16 * i)) & 0xFFFFu;
-                if (!(mw[i] & kMetaOnPath) && (int)(mw[i] & kMetaLock) < M - rb)  // :198-199 + early :195
-                  A.relax[rn++] = ((uint32_t)(rb + 1) << 16) | w;
+                if (!(mw[i] & kMetaOnPath) && (int)(mw[i] & kMetaLock) < M - rb) {  // :198-199 + early :195
+                  if (have) A.relax[rn++] = r;              // the previous top goes to memory
+                  r = ((uint32_t)(rb + 1) << 16) | w;
+                  have = true;
+                }
               }
+          }
+          if (!have && rn) {
+            r = A.relax[--rn];
+            have = true;
           }
         }
       }
