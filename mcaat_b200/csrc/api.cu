@@ -162,7 +162,11 @@ int mg_graph_create(const mg_graph_desc *d, mg_graph **out) {
   g->device = d->device;
   g->k = d->k;
   cudaDeviceProp prop;
-  if (cudaGetDeviceProperties(&prop, d->device) == cudaSuccess) g->sm_count = prop.multiProcessorCount;
+  if (cudaGetDeviceProperties(&prop, d->device) == cudaSuccess) {
+    g->sm_count = prop.multiProcessorCount;
+    g->smem_per_sm = prop.sharedMemPerMultiprocessor;
+    g->smem_per_block_optin = prop.sharedMemPerBlockOptin;
+  }
   if (cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking) != cudaSuccess) {
     set_error("cudaStreamCreate failed");
     delete g;

@@ -65,6 +65,16 @@ struct BallArena {
   uint32_t cyc_cap;
   uint32_t *cyc_off;    // [kClusterBound + 1]
   Lvl *lvl;             // [M + 2] per path level (shared memory on the device)
+  // ---- contracted ball (sball_*, below)
+  uint32_t *spos;       // [node_cap] per ball node: chain id | position inside the chain << 16
+  uint32_t *ckeys;      // [node_cap] item ids grouped by chain: chain s occupies [soff[s], soff[s] + c)
+  uint16_t *soff;       // [node_cap + 1]
+  uint16_t *shead;      // [node_cap] local id of the first node of chain s
+  uint32_t *cyc_pos;    // [cyc_cap] per staged path level: where the chain's ids go in the flat cycle list
+  uint32_t *cyc_noff;   // [kClusterBound + 1] cycle boundaries in the flat list (in nodes)
+  int max_steps;        // step cap of :148-151 (kMaxSteps; the differential tests lower it)
+  uint32_t *relax_top;  // first relax_top_cap entries of the contracted search's relaxation stack (shared memory)
+  uint32_t relax_top_cap;
 };
 
 // cooperative execution policy: the device runs ball_build with the 32 lanes of a warp, the host
@@ -308,7 +318,7 @@ MG_HD_NOINLINE bool ball_dfs(int min_len, int max_len, const BallArena &A, DfsSt
       S.expansions = expansions; S.n_cycles = n_cycles; S.n_cyc = n_cyc;
       return false;
     }
-    if (++steps > kMaxSteps) { status = kEnumCap; break; }  // :148-151
+    if (++steps > A.max_steps) { status = kEnumCap; break; }  // :148-151
     const uint64_t set = cur.set;                           // :153 (copy)
     // records of all members first: the loads overlap, and no lock changes before the scan ends
     NodeHead hd[4];
@@ -414,6 +424,428 @@ done:
   R.steps = (uint32_t)steps;
   R.expansions = expansions;
   return true;
+}
+
+// ====================================================================== contracted ball
+// In a de Bruijn graph almost every node has one in- and one out-neighbour, and so has the ball: the 5 668-node ball
+// of the longest search at 225 M items is ~40 spacer-long unary chains between a handful of branching nodes, and the
+// literal search spends its 407 415 steps walking them node by node, twice (push, pop), plus once per relaxation.
+// The search below runs on the CONTRACTED ball: a maximal chain n_1 .. n_c with OUT(n_i) = {n_i+1} and
+// IN(n_i+1) = {n_i} (start node excluded: it is a chain of its own) is one record.  It is exact, not an
+// approximation, because the lock values along a chain can only ever take one shape:
+//     lock[n_i] = a + i  for i <= j,     lock[n_i] = M  for i > j            ("(a, j)", j = 0: untouched / all M)
+//   * a push at path size P passes n_1 iff P < lock[n_1]; if it does it passes the whole affine prefix (the test
+//     P + i < a + i + 1 is the same for every i) and then runs on through the M zone while P + i < M: the walk
+//     pushes t = min(c, M - P) nodes and leaves (P, t) (:168-172).  t < c: the chain could not be completed inside
+//     the length bound; nothing below it is reached, it is popped again at once with backtrack length M — no
+//     relaxation, the state stays (P, t) — and the parent's set is scanned again.  That costs 2t - 1 further loop
+//     iterations of :147 (t - 1 pushes, t pops), which only matter for the step cap;
+//   * a pop with backtrack length M leaves the locks alone; with backtrack length 1 (the only other value there is:
+//     :158 sets 1, :187 takes minima) every node of the chain is relaxed from its own pop to M (:192-196) — the
+//     in-neighbour of an inner node is still on the path, so nothing spreads until n_1 is popped, whose
+//     off-path in-neighbours are entered with level 2 (:197-199);
+//   * a relaxation arrives at the LAST node n_c with level x (inner nodes have no other in-neighbour).  It proposes
+//     M - x + 1 for n_c, one less for every node before it: again a + i with a' = M - x + 1 - c.  Against a full
+//     affine state it raises all nodes or none (same difference everywhere); against an M zone at the end it stops
+//     at n_c.  When it raises, it leaves through IN(n_1) with level x + c.
+// A chain is either completely on the path or not at all whenever a relaxation runs (an incomplete chain only exists
+// inside one step).  Neighbour sets keep the std::unordered_set iteration order of the node ids they came from
+// (OUT(n_c), IN(n_1)); the relaxation stack keeps its LIFO order; the step and expansion counters advance by what
+// the literal loop would have counted.  tests/emu compares this search with ball_dfs above (and both with the
+// reference dumps), also with lowered step caps and length bounds that cut chains.
+struct alignas(16) SHot {
+  uint16_t a, j, c;
+  uint16_t flags;    // bit 0: the chain is on the current path
+  union { uint16_t out[4]; uint64_t out4; };  // chains that OUT(n_c) leads to (chain 0 = the start node), iteration order
+};
+static_assert(sizeof(SHot) == 16, "one 16-byte access per chain record");
+constexpr uint16_t kSOnPath = 1;
+struct SBall {          // the contracted ball; records in shared memory when they fit, else in the worker's arena
+  SHot *hot;
+  uint64_t *in4;        // chains whose last node is in IN(n_1), iteration order
+  uint32_t cap;
+  uint32_t n;           // number of chains
+};
+
+MG_HD bool ball_is_head(const LNode *N, const LTail *T, uint32_t x) {
+  if (x == 0) return true;
+  const uint32_t m = N[x].meta;
+  if (((m >> kMetaInShift) & 7u) != 1) return true;
+  const uint32_t u = T[x].in[0];
+  return u == 0 || ((N[u].meta >> kMetaOutShift) & 7u) != 1;
+}
+
+// Contracts the ball of ball_build (all lanes).  Returns kEnumDone, or kEnumOverflow when B.cap is too small.
+MG_HD_NOINLINE int sball_contract(const BallArena &A, uint32_t n_nodes, SBall &B, const Coop &co) {
+  const LNode *N = A.nodes;
+  const LTail *T = A.tails;
+  // 1. chain heads, numbered in local-id order (the start node is chain 0)
+  uint32_t n_super = 0;
+  for (uint32_t base = 0; base < n_nodes; base += Coop::kLanes) {
+    const uint32_t x = base + (uint32_t)co.lane;
+    const bool head = x < n_nodes && ball_is_head(N, T, x);
+    const uint32_t before = co.exclusive_prefix(head ? 1u : 0u), cnt = co.sum(head ? 1u : 0u);
+    if (head) A.shead[n_super + before] = (uint16_t)x;
+    n_super += cnt;
+  }
+  B.n = n_super;
+  if (n_super > B.cap) return kEnumOverflow;
+  co.sync();
+  // 2. one walk per chain: membership of its nodes, length, last node
+  for (uint32_t s = (uint32_t)co.lane; s < n_super; s += Coop::kLanes) {
+    uint32_t x = A.shead[s], i = 0;
+    const uint64_t in4 = T[x].in4;
+    const uint32_t nin = (N[x].meta >> kMetaInShift) & 7u;
+    for (;;) {
+      A.spos[x] = s | (i << 16);
+      ++i;
+      if (s == 0 || ((N[x].meta >> kMetaOutShift) & 7u) != 1) break;
+      const uint32_t y = N[x].out[0];
+      if (y == 0 || ((N[y].meta >> kMetaInShift) & 7u) != 1) break;
+      x = y;
+    }
+    SHot h;
+    h.a = 0;
+    h.j = 0;
+    h.c = (uint16_t)i;
+    h.flags = 0;
+    h.out4 = N[x].out4;       // local ids of OUT(n_c); unused slots are kNoLid already
+    B.hot[s] = h;
+    uint64_t in = in4;        // IN(n_1): slots beyond |in| are not initialised by the build
+    for (uint32_t q = nin; q < 4; ++q) in |= 0xFFFFull << (16 * q);
+    B.in4[s] = in;
+  }
+  co.sync();
+  // 3. where each chain's ids go (exclusive prefix of the lengths)
+  uint32_t run = 0;
+  for (uint32_t base = 0; base < n_super; base += Coop::kLanes) {
+    const uint32_t s = base + (uint32_t)co.lane;
+    const uint32_t c = s < n_super ? B.hot[s].c : 0u;
+    const uint32_t before = co.exclusive_prefix(c), tot = co.sum(c);
+    if (s < n_super) A.soff[s] = (uint16_t)(run + before);
+    run += tot;
+  }
+  co.sync();
+  // 4. neighbour sets as chain numbers; item ids grouped by chain
+  for (uint32_t s = (uint32_t)co.lane; s < n_super; s += Coop::kLanes) {
+    uint64_t o = B.hot[s].out4, in = B.in4[s], o2 = 0, in2 = 0;
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t a = (uint32_t)(o >> (16 * q)) & 0xFFFFu, b = (uint32_t)(in >> (16 * q)) & 0xFFFFu;
+      o2 |= (uint64_t)(a == kNoLid ? kNoLid : (A.spos[a] & 0xFFFFu)) << (16 * q);
+      in2 |= (uint64_t)(b == kNoLid ? kNoLid : (A.spos[b] & 0xFFFFu)) << (16 * q);
+    }
+    B.hot[s].out4 = o2;
+    B.in4[s] = in2;
+  }
+  for (uint32_t x = (uint32_t)co.lane; x < n_nodes; x += Coop::kLanes) {
+    const uint32_t sp = A.spos[x];
+    A.ckeys[(uint32_t)A.soff[sp & 0xFFFFu] + (sp >> 16)] = N[x].key;
+  }
+  co.sync();
+  return kEnumDone;
+}
+
+struct SDfsState {  // the scalars of a paused search
+  int depth = 0;     // chains on the path
+  int plen = 0;      // path.size()
+  int counter = 0, steps = 0;
+  uint32_t expansions = 0, n_cycles = 0, n_staged = 0, n_out = 0;
+  bool started = false;
+};
+
+// Register images of the two 16-byte records the search moves (one vector access each):
+//   chain record  SHot: aj = a | j << 16, cf = c | flags << 16, out4
+//   path level    Lvl : set, pmeta = path.size() below this chain, nb = chain | backtrack length << 16
+struct HotReg {
+  uint32_t aj, cf;
+  uint64_t out4;
+  MG_HD int a() const { return (int)(aj & 0xFFFFu); }
+  MG_HD int j() const { return (int)(aj >> 16); }
+  MG_HD int c() const { return (int)(cf & 0xFFFFu); }
+  MG_HD bool on_path() const { return (cf >> 16) & kSOnPath; }
+};
+struct LvlReg {
+  uint64_t set;
+  uint32_t pmeta, nb;
+  MG_HD uint32_t node() const { return nb & 0xFFFFu; }
+  MG_HD int bl() const { return (int)(nb >> 16); }
+};
+// Where the records live.  RecsPtr: plain pointers (arena, host emulation, or shared memory through generic
+// addresses); RecsSmem (device): everything in shared memory, addressed with ld/st.shared.
+struct RecsPtr {
+  SHot *hot;
+  const uint64_t *in4;
+  Lvl *lvl;
+  uint32_t *rtop;
+  MG_HD HotReg ld_hot(uint32_t s) const {
+    HotReg h;
+#if defined(__CUDA_ARCH__)
+    const uint4 v = *reinterpret_cast<const uint4 *>(&hot[s]);
+    h.aj = v.x; h.cf = v.y; h.out4 = (uint64_t)v.z | ((uint64_t)v.w << 32);
+#else
+    const SHot &r = hot[s];
+    h.aj = (uint32_t)r.a | ((uint32_t)r.j << 16); h.cf = (uint32_t)r.c | ((uint32_t)r.flags << 16); h.out4 = r.out4;
+#endif
+    return h;
+  }
+  MG_HD void st_hot_state(uint32_t s, uint32_t aj, uint32_t cf) const {  // a, j, c, flags: the first 8 bytes
+#if defined(__CUDA_ARCH__)
+    *reinterpret_cast<uint2 *>(&hot[s]) = make_uint2(aj, cf);
+#else
+    SHot &r = hot[s];
+    r.a = (uint16_t)aj; r.j = (uint16_t)(aj >> 16); r.c = (uint16_t)cf; r.flags = (uint16_t)(cf >> 16);
+#endif
+  }
+  MG_HD uint64_t ld_in(uint32_t s) const { return in4[s]; }
+  MG_HD LvlReg ld_lvl(int i) const {
+    LvlReg l;
+#if defined(__CUDA_ARCH__)
+    const uint4 v = *reinterpret_cast<const uint4 *>(&lvl[i]);
+    l.set = (uint64_t)v.x | ((uint64_t)v.y << 32); l.pmeta = v.z; l.nb = v.w;
+#else
+    l.set = lvl[i].set; l.pmeta = lvl[i].pmeta; l.nb = (uint32_t)lvl[i].node | ((uint32_t)(uint16_t)lvl[i].bl << 16);
+#endif
+    return l;
+  }
+  MG_HD void st_lvl(int i, const LvlReg &l) const {
+#if defined(__CUDA_ARCH__)
+    *reinterpret_cast<uint4 *>(&lvl[i]) = make_uint4((uint32_t)l.set, (uint32_t)(l.set >> 32), l.pmeta, l.nb);
+#else
+    lvl[i].set = l.set; lvl[i].pmeta = l.pmeta; lvl[i].node = (uint16_t)l.nb; lvl[i].bl = (int16_t)(l.nb >> 16);
+#endif
+  }
+  MG_HD uint32_t ld_lvl_node_pmeta(int i, uint32_t &pmeta) const { pmeta = lvl[i].pmeta; return lvl[i].node; }
+  MG_HD uint32_t ld_rtop(uint32_t i) const { return rtop[i]; }
+  MG_HD void st_rtop(uint32_t i, uint32_t v) const { rtop[i] = v; }
+};
+#if defined(__CUDACC__)
+struct RecsSmem {
+  uint32_t hot, in4, lvl, rtop;  // shared-window byte addresses
+  __device__ __forceinline__ HotReg ld_hot(uint32_t s) const {
+    HotReg h;
+    uint32_t z, w;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(h.aj), "=r"(h.cf), "=r"(z), "=r"(w) : "r"(hot + s * 16u));
+    h.out4 = (uint64_t)z | ((uint64_t)w << 32);
+    return h;
+  }
+  __device__ __forceinline__ void st_hot_state(uint32_t s, uint32_t aj, uint32_t cf) const {
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(hot + s * 16u), "r"(aj), "r"(cf) : "memory");
+  }
+  __device__ __forceinline__ uint64_t ld_in(uint32_t s) const {
+    uint64_t v;
+    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(in4 + s * 8u));
+    return v;
+  }
+  __device__ __forceinline__ LvlReg ld_lvl(int i) const {
+    LvlReg l;
+    uint32_t x, y;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x), "=r"(y), "=r"(l.pmeta), "=r"(l.nb) : "r"(lvl + (uint32_t)i * 16u));
+    l.set = (uint64_t)x | ((uint64_t)y << 32);
+    return l;
+  }
+  __device__ __forceinline__ void st_lvl(int i, const LvlReg &l) const {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(lvl + (uint32_t)i * 16u), "r"((uint32_t)l.set),
+                 "r"((uint32_t)(l.set >> 32)), "r"(l.pmeta), "r"(l.nb) : "memory");
+  }
+  __device__ __forceinline__ uint32_t ld_lvl_node_pmeta(int i, uint32_t &pmeta) const {
+    uint32_t nb;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(pmeta), "=r"(nb) : "r"(lvl + (uint32_t)i * 16u + 8u));
+    return nb & 0xFFFFu;
+  }
+  __device__ __forceinline__ uint32_t ld_rtop(uint32_t i) const {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(rtop + i * 4u));
+    return v;
+  }
+  __device__ __forceinline__ void st_rtop(uint32_t i, uint32_t v) const {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(rtop + i * 4u), "r"(v) : "memory");
+  }
+};
+#endif
+
+// Literal FindCycleUtil + FindCycle (src/cycle_finder.cpp:231-243,140-225) on the contracted ball (one lane).  Runs at
+// most `budget` further chain steps; returns true when the search has ended (R filled in), false when it is paused.
+// Cycles are staged as (chain, position in the flat id list) per path level; sball_expand turns them into item ids.
+// (Inlined at each call site: the device instantiates it for records in shared memory and for records in the arena.)
+template <class Recs>
+MG_HD bool sball_dfs(int min_len, int max_len, const BallArena &A, const Recs &Q, SDfsState &S, int budget,
+                     EnumResult &R) {
+  const int M = max_len;
+  uint32_t expansions = S.expansions, n_cycles = S.n_cycles, n_staged = S.n_staged, n_out = S.n_out;
+  int plen = S.plen, depth = S.depth, counter = S.counter, steps = S.steps;
+  int32_t status = kEnumDone;
+  LvlReg cur;  // top level in registers
+  if (!S.started) {
+    S.started = true;
+    A.cyc_off[0] = 0;
+    A.cyc_noff[0] = 0;
+    const HotReg h0 = Q.ld_hot(0);
+    Q.st_hot_state(0, h0.aj, h0.cf | ((uint32_t)kSOnPath << 16));  // lock[start] = 0 (:237) is never consulted: the start stays on the path
+    cur.set = h0.out4;                     // _GetOutgoings(start), :238-240
+    cur.pmeta = 0;
+    cur.nb = 0u | ((uint32_t)M << 16);
+    plen = 1;
+    depth = 1;
+    ++expansions;
+  } else {
+    cur = Q.ld_lvl(depth - 1);
+  }
+  int left = budget;
+  while (depth > 0) {
+    if (left-- == 0) {
+      Q.st_lvl(depth - 1, cur);
+      S.depth = depth; S.plen = plen; S.counter = counter; S.steps = steps;
+      S.expansions = expansions; S.n_cycles = n_cycles; S.n_staged = n_staged; S.n_out = n_out;
+      return false;
+    }
+    if (++steps > A.max_steps) { status = kEnumCap; break; }  // :148-151
+    const uint64_t set = cur.set;                             // :153 (copy)
+    HotReg hd[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t nb = (uint32_t)(set >> (16 * i)) & 0xFFFFu;
+      if (nb != kNoLid) hd[i] = Q.ld_hot(nb);
+    }
+    bool flag = true;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t nb = (uint32_t)(set >> (16 * i)) & 0xFFFFu;
+      if (nb != kNoLid && flag) {
+        if (nb == 0) {                                        // n == start_node, :157-166
+          cur.nb = (cur.nb & 0xFFFFu) | (1u << 16);           // backtrack_lengths.back() = 1
+          if (plen > min_len) {
+            if (++counter >= kClusterBound) {                 // cluster bound: the final answer is empty
+              status = kEnumBound;
+              n_cycles = n_staged = n_out = 0;
+              goto done;
+            }
+            if (n_staged + (uint32_t)depth > A.cyc_cap) { status = kEnumOverflow; goto done; }
+            for (int l = 0; l + 1 < depth; ++l) {
+              uint32_t pm;
+              A.cyc[n_staged + l] = (uint16_t)Q.ld_lvl_node_pmeta(l, pm);
+              A.cyc_pos[n_staged + l] = n_out + pm;
+            }
+            A.cyc[n_staged + depth - 1] = (uint16_t)cur.node();
+            A.cyc_pos[n_staged + depth - 1] = n_out + cur.pmeta;
+            n_staged += (uint32_t)depth;
+            n_out += (uint32_t)plen;
+            A.cyc_off[++n_cycles] = n_staged;
+            A.cyc_noff[n_cycles] = n_out;
+          }
+        } else {
+          const HotReg h = hd[i];
+          const int lock_head = h.j() ? h.a() + 1 : M;
+          if (plen < lock_head) {                             // :168 for n_1
+            {                                                 // stack.back().erase(n), :173
+              const uint64_t low = i ? set & ((1ull << (16 * i)) - 1) : 0ull;
+              const uint64_t high = i < 3 ? (set >> (16 * (i + 1))) << (16 * i) : 0ull;
+              cur.set = low | high | (0xFFFFull << 48);
+            }
+            const int c = h.c(), t = c < M - plen ? c : M - plen;
+            expansions += (uint32_t)t;                        // one _GetOutgoings per pushed node, :174-176
+            const uint32_t aj = (uint32_t)plen | ((uint32_t)t << 16);
+            if (t < c) {                                      // cut by the length bound: popped again at once
+              Q.st_hot_state(nb, aj, h.cf);
+              steps += 2 * t - 1;
+            } else {
+              Q.st_hot_state(nb, aj, h.cf | ((uint32_t)kSOnPath << 16));
+              steps += c - 1;
+              Q.st_lvl(depth - 1, cur);
+              ++depth;
+              cur.set = h.out4;
+              cur.pmeta = (uint32_t)plen;
+              cur.nb = nb | ((uint32_t)M << 16);
+              plen += c;
+            }
+            if (steps > A.max_steps) { steps = A.max_steps + 1; status = kEnumCap; goto done; }
+            flag = false;                                     // break
+          }
+        }
+      }
+    }
+    if (flag) {                                               // :181-211
+      const uint32_t v = cur.node();
+      const int b = cur.bl(), c = plen - (int)cur.pmeta;
+      plen = (int)cur.pmeta;
+      --depth;
+      steps += c - 1;                                         // the chain's other nodes are popped one step each
+      if (steps > A.max_steps) { steps = A.max_steps + 1; status = kEnumCap; goto done; }
+      const uint32_t cf_v = (uint32_t)c;                      // flags cleared: off the path
+      uint64_t ins = 0;
+      if (b < M) {                                            // every node with lock < M goes to M, :192-196
+        const int raised = c < M - plen - 1 ? c : M - plen - 1;
+        expansions += (uint32_t)(raised > 0 ? raised : 0);
+        Q.st_hot_state(v, 0u, cf_v);
+        ins = Q.ld_in(v);
+      } else {
+        Q.st_hot_state(v, (uint32_t)plen | ((uint32_t)c << 16), cf_v);  // unchanged (plen, c): a full push left it so
+      }
+      if (depth > 0) {
+        cur = Q.ld_lvl(depth - 1);
+        if (b < cur.bl()) cur.nb = (cur.nb & 0xFFFFu) | ((uint32_t)b << 16);
+      }
+      if (b < M && plen + 1 < M) {                            // n_1 was relaxed: its off-path in-neighbours, level b + 1
+        // relax_stack (:192-210) over chains: entry = level << 16 | chain, meaning (level, last node of the chain).
+        // An entry only acts when lock[n_c] < M - level + 1, and locks never decrease during a relaxation, so
+        // entries that fail the test when they would be pushed are dropped at once; the test is repeated at the pop.
+        uint32_t rn = 0;
+        int x = b + 1;
+        for (;;) {
+          HotReg hw[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t w = (uint32_t)(ins >> (16 * i)) & 0xFFFFu;
+            if (w != kNoLid) hw[i] = Q.ld_hot(w);
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t w = (uint32_t)(ins >> (16 * i)) & 0xFFFFu;
+            if (w != kNoLid && !hw[i].on_path() && hw[i].j() == hw[i].c() &&
+                hw[i].a() + hw[i].c() < M - x + 1) {          // :198-199 + early :195
+              if (rn >= A.relax_cap + A.relax_top_cap) { status = kEnumOverflow; goto done; }
+              const uint32_t ent = ((uint32_t)x << 16) | w;
+              if (rn < A.relax_top_cap) Q.st_rtop(rn, ent);
+              else A.relax[rn - A.relax_top_cap] = ent;
+              ++rn;
+            }
+          }
+          bool acted = false;
+          while (rn && !acted) {
+            --rn;
+            const uint32_t r = rn < A.relax_top_cap ? Q.ld_rtop(rn) : A.relax[rn - A.relax_top_cap];
+            const int rx = (int)(r >> 16);
+            const uint32_t u = r & 0xFFFFu;
+            const HotReg hu = Q.ld_hot(u);
+            if (hu.j() == hu.c() && hu.a() + hu.c() < M - rx + 1) {  // :195-196 at n_c, true for the whole chain
+              Q.st_hot_state(u, (uint32_t)(M - rx + 1 - hu.c()) | ((uint32_t)hu.c() << 16), hu.cf);
+              expansions += (uint32_t)hu.c();                 // _GetIncomings per node, :197
+              ins = Q.ld_in(u);
+              x = rx + hu.c();
+              acted = true;
+            }
+          }
+          if (!acted) break;
+        }
+      }
+    }
+  }
+done:
+  R.status = status;
+  R.n_cycles = n_cycles;
+  R.n_nodes = n_out;
+  R.steps = (uint32_t)steps;
+  R.expansions = expansions;
+  S.n_staged = n_staged;
+  return true;
+}
+
+// Item ids of the staged cycles (all lanes): out[0 .. R.n_nodes), cycle q = [cyc_noff[q], cyc_noff[q + 1]).
+MG_HD void sball_expand(const BallArena &A, const SBall &B, uint32_t n_staged, uint32_t *out, const Coop &co) {
+  for (uint32_t e = (uint32_t)co.lane; e < n_staged; e += Coop::kLanes) {
+    const uint32_t s = A.cyc[e], at = A.cyc_pos[e], from = A.soff[s], c = B.hot[s].c;
+    for (uint32_t i = 0; i < c; ++i) out[at + i] = A.ckeys[from + i];
+  }
+  co.sync();
 }
 
 }  // namespace mg

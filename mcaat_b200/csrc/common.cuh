@@ -136,6 +136,7 @@ struct mg_graph {
   mg::DevBuf kx_tip, kx_tip_prefix, kx_labels, kx_buckets, kx_jump, kx_bucket_ok;
   uint64_t device_bytes = 0;
   int sm_count = 148;
+  size_t smem_per_sm = 233472, smem_per_block_optin = 232448;  // B200: 228 KB per SM, 227 KB per block (opt-in)
   // timers
   double t_ms[mg::T_COUNT] = {0};
   uint64_t t_launches[mg::T_COUNT] = {0};

@@ -83,6 +83,7 @@ struct TicketRec {
   uint32_t expansions, steps;
   uint32_t us_searched, us_committed;  // microseconds since the worker entered the kernel
   uint32_t n_ball, us_build;           // size of the last extracted ball and the time its extraction took
+  uint32_t n_chains;                   // records of its contraction
 };
 struct PipeCtl {
   uint32_t ticket;       // next ticket to hand out
@@ -212,7 +213,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_solo(GraphView g, 
         status = __shfl_sync(0xffffffffu, R.status, 0);
       }
     }
-    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0, 0, 0};
+    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0, 0, 0, 0};
     if (!skip && !stopped) {
       const uint32_t n_nodes = __shfl_sync(0xffffffffu, R.n_nodes, 0);
       const uint32_t n_cycles = __shfl_sync(0xffffffffu, R.n_cycles, 0);
@@ -264,10 +265,15 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_solo(GraphView g, 
 // ---- the pipeline proper: extracted-ball searches (ball_dev.cuh)
 struct BallLayout {  // per-worker arena in global memory (byte offsets inside one slot)
   uint32_t index_log, node_cap, relax_cap, cyc_cap, depth_cap;
-  size_t off_nodes, off_tails, off_index, off_relax, off_cyc, off_cyc_keys, off_cyc_off, bytes;
-  uint32_t smem_bytes;  // per worker: the path levels (Lvl) live in shared memory
+  size_t off_nodes, off_tails, off_index, off_relax, off_cyc, off_cyc_pos, off_cyc_keys, off_cyc_off, off_cyc_noff,
+      off_spos, off_ckeys, off_soff, off_shead, off_shot, off_sin, off_lvl, bytes;
+  // per worker in shared memory: the path levels (Lvl; in the arena instead when cycle_max_length makes them large),
+  // the top of the relaxation stack and the records of the contracted ball (up to chain_cap chains; larger
+  // contracted balls use the records in the arena)
+  uint32_t smem_bytes, smem_lvl, smem_relax, chain_cap;
 };
-static BallLayout make_ball_layout(int max_len, uint32_t index_log) {
+constexpr uint32_t kRelaxSmem = 128;  // relaxation stack entries held in shared memory (the rest spills to the arena)
+static BallLayout make_ball_layout(int max_len, uint32_t index_log, uint32_t smem_per_worker) {
   BallLayout L;
   L.index_log = index_log;
   L.node_cap = std::min<uint32_t>((1u << index_log) / 2, 65535u);
@@ -280,10 +286,24 @@ static BallLayout make_ball_layout(int max_len, uint32_t index_log) {
   L.off_index = o; o = align_up(o + ((size_t)8 << index_log), 128);
   L.off_relax = o; o = align_up(o + (size_t)L.relax_cap * 4, 128);
   L.off_cyc = o; o = align_up(o + (size_t)L.cyc_cap * 2, 128);
+  L.off_cyc_pos = o; o = align_up(o + (size_t)L.cyc_cap * 4, 128);
   L.off_cyc_keys = o; o = align_up(o + (size_t)L.cyc_cap * 4, 128);
   L.off_cyc_off = o; o = align_up(o + (size_t)(kClusterBound + 1) * 4, 128);
+  L.off_cyc_noff = o; o = align_up(o + (size_t)(kClusterBound + 1) * 4, 128);
+  L.off_spos = o; o = align_up(o + (size_t)L.node_cap * 4, 128);
+  L.off_ckeys = o; o = align_up(o + (size_t)L.node_cap * 4, 128);
+  L.off_soff = o; o = align_up(o + (size_t)(L.node_cap + 1) * 2, 128);
+  L.off_shead = o; o = align_up(o + (size_t)L.node_cap * 2, 128);
+  L.off_shot = o; o = align_up(o + (size_t)L.node_cap * sizeof(SHot), 128);
+  L.off_sin = o; o = align_up(o + (size_t)L.node_cap * 8, 128);
+  L.off_lvl = o; o = align_up(o + (size_t)L.depth_cap * sizeof(Lvl), 128);
   L.bytes = align_up(o, 128);
-  L.smem_bytes = (uint32_t)align_up((size_t)L.depth_cap * sizeof(Lvl), 16);
+  const uint32_t lvl_bytes = (uint32_t)align_up((size_t)L.depth_cap * sizeof(Lvl), 16);
+  L.smem_lvl = lvl_bytes <= smem_per_worker / 4 ? lvl_bytes : 0;  // long paths: levels in the arena
+  L.smem_relax = kRelaxSmem * 4;
+  const uint32_t rest = smem_per_worker - L.smem_lvl - L.smem_relax;
+  L.chain_cap = std::min<uint32_t>(rest / 24 / 8 * 8, L.node_cap);
+  L.smem_bytes = L.smem_lvl + L.smem_relax + L.chain_cap * 24;
   return L;
 }
 __device__ __forceinline__ BallArena ball_arena_of(uint8_t *base, uint8_t *smem, const BallLayout &L) {
@@ -298,7 +318,16 @@ __device__ __forceinline__ BallArena ball_arena_of(uint8_t *base, uint8_t *smem,
   A.cyc = (uint16_t *)(base + L.off_cyc);
   A.cyc_cap = L.cyc_cap;
   A.cyc_off = (uint32_t *)(base + L.off_cyc_off);
-  A.lvl = (Lvl *)smem;
+  A.lvl = L.smem_lvl ? (Lvl *)smem : (Lvl *)(base + L.off_lvl);
+  A.relax_top = (uint32_t *)(smem + L.smem_lvl);
+  A.relax_top_cap = kRelaxSmem;
+  A.spos = (uint32_t *)(base + L.off_spos);
+  A.ckeys = (uint32_t *)(base + L.off_ckeys);
+  A.soff = (uint16_t *)(base + L.off_soff);
+  A.shead = (uint16_t *)(base + L.off_shead);
+  A.cyc_pos = (uint32_t *)(base + L.off_cyc_pos);
+  A.cyc_noff = (uint32_t *)(base + L.off_cyc_noff);
+  A.max_steps = kMaxSteps;
   return A;
 }
 
@@ -306,12 +335,23 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
                                                      const uint32_t *__restrict__ starts, uint32_t n_end, int min_len,
                                                      int max_len, uint8_t *arena, BallLayout L, PipeCtl *ctl,
                                                      TicketRec *recs, uint32_t *pool_nodes, uint32_t pool_nodes_cap,
-                                                     uint32_t *pool_len, uint32_t pool_len_cap) {
+                                                     uint32_t *pool_len, uint32_t pool_len_cap, int force_global) {
   extern __shared__ __align__(16) uint8_t smem_all[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t worker = blockIdx.x * kWarpsPerBlock + warp;
-  const BallArena A = ball_arena_of(arena + (size_t)worker * L.bytes, smem_all + (size_t)warp * L.smem_bytes, L);
+  uint8_t *const my_smem = smem_all + (size_t)warp * L.smem_bytes;
+  const BallArena A = ball_arena_of(arena + (size_t)worker * L.bytes, my_smem, L);
   uint32_t *cyc_keys = (uint32_t *)(arena + (size_t)worker * L.bytes + L.off_cyc_keys);  // staged cycles as item ids
+  // records of the contracted ball: shared memory, or the arena when there are more than L.chain_cap chains
+  SBall Bs, Bg;
+  Bs.hot = (SHot *)(my_smem + L.smem_lvl + L.smem_relax);
+  Bs.in4 = (uint64_t *)(my_smem + L.smem_lvl + L.smem_relax + (size_t)L.chain_cap * sizeof(SHot));
+  Bs.cap = L.chain_cap;
+  Bg.hot = (SHot *)(arena + (size_t)worker * L.bytes + L.off_shot);
+  Bg.in4 = (uint64_t *)(arena + (size_t)worker * L.bytes + L.off_sin);
+  Bg.cap = L.node_cap;
+  Bs.n = Bg.n = 0;
+  uint32_t n_chains = 0;
   Coop co;
   co.lane = lane;
   unsigned long long searches = 0;
@@ -357,11 +397,28 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
         R.n_cycles = R.n_nodes = R.steps = R.expansions = 0;
         R.n_keys = live;
         if (st != kEnumDone) break;
-        DfsState ds;
+        // contract the ball (unary chains become single records) and search it
+        bool in_smem = !force_global;
+        if (in_smem) in_smem = sball_contract(A, live, Bs, co) == kEnumDone;
+        if (!in_smem) sball_contract(A, live, Bg, co);
+        const SBall &B = in_smem ? Bs : Bg;
+        n_chains = B.n;
+        SDfsState ds;
         bool restart = false;
         for (;;) {
           int fin = 0;
-          if (lane == 0) fin = ball_dfs(min_len, max_len, A, ds, exclusive ? kMaxSteps + 1 : kSliceSteps, R) ? 1 : 0;
+          if (lane == 0) {
+            const int budget = exclusive ? 0x7fffffff : kSliceSteps;
+            if (in_smem && L.smem_lvl) {
+              const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(my_smem);
+              const RecsSmem Q{sbase + L.smem_lvl + L.smem_relax, sbase + L.smem_lvl + L.smem_relax + L.chain_cap * 16u, sbase,
+                               sbase + L.smem_lvl};
+              fin = sball_dfs(min_len, max_len, A, Q, ds, budget, R) ? 1 : 0;
+            } else {
+              const RecsPtr Q{B.hot, B.in4, A.lvl, A.relax_top};
+              fin = sball_dfs(min_len, max_len, A, Q, ds, budget, R) ? 1 : 0;
+            }
+          }
           if (__shfl_sync(0xffffffffu, fin, 0)) break;
           uint32_t c_stop = 0, c_vis = 0, c_ep = 0;
           if (lane == 0) {
@@ -377,6 +434,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
             else ++abandoned;
             R.status = kEnumSkipped;
             R.n_cycles = R.n_nodes = 0;
+            ds.n_staged = 0;
             break;
           }
           if (c_ep != epoch_checked) {
@@ -385,13 +443,14 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
             if (stale(live)) { restart = true; break; }
           }
         }
-        if (!restart) break;
-        ++reruns;
+        if (restart) { ++reruns; continue; }
+        __syncwarp();  // lane 0's writes (staged cycles) are visible to the warp
+        // item ids of the staged cycles, so that the commit only has to stream them
+        const int fst = __shfl_sync(0xffffffffu, R.status, 0);
+        const uint32_t n_staged = __shfl_sync(0xffffffffu, ds.n_staged, 0);
+        if (fst == kEnumDone || fst == kEnumCap) sball_expand(A, B, n_staged, cyc_keys, co);
+        break;
       }
-      __syncwarp();  // lane 0's arena writes (staged cycles) are visible to the warp
-      // item ids of the staged cycles, so that the commit only has to stream them
-      const uint32_t n_staged = __shfl_sync(0xffffffffu, R.n_nodes, 0);
-      for (uint32_t j = lane; j < n_staged; j += 32) cyc_keys[j] = A.nodes[A.cyc[j]].key;
       __syncwarp();
     };
     // a ticket whose start is already marked is skipped for good (:476); the committing worker ahead
@@ -452,7 +511,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       }
       if (status == kEnumOverflow) stopped = 1;
     }
-    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0, live, us_build};
+    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0, live, us_build, n_chains};
     uint32_t n_nodes = 0, n_cycles = 0, node_base = 0, cyc_base = 0;
     if (!skip && !stopped) {
       n_nodes = __shfl_sync(0xffffffffu, R.n_nodes, 0);
@@ -497,7 +556,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       const unsigned m = __ballot_sync(0xffffffffu, sk);
       const int run = m == 0xffffffffu ? 32 : __ffs((int)~m) - 1;
       if (lane < run) {
-        const TicketRec skipped = {kFateSkipped, kEnumSkipped, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+        const TicketRec skipped = {kFateSkipped, kEnumSkipped, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
         recs[c] = skipped;
       }
       next += (uint32_t)run;
@@ -512,7 +571,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     // ---- off the hand-over path: results[start] = cycles (:479)
     if (rec.fate == kFateAccepted) {
       for (uint32_t j = lane; j < n_nodes; j += 32) pool_nodes[node_base + j] = cyc_keys[j];
-      for (uint32_t j = lane; j < n_cycles; j += 32) pool_len[cyc_base + j] = A.cyc_off[j + 1] - A.cyc_off[j];
+      for (uint32_t j = lane; j < n_cycles; j += 32) pool_len[cyc_base + j] = A.cyc_noff[j + 1] - A.cyc_noff[j];
     }
     if (lane == 0) {
       rec.us_committed = (uint32_t)((gtime_ns() - t_kernel) / 1000);
@@ -582,9 +641,18 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     MG_TRY(pool_len.alloc((size_t)len_cap * 4));
     // worker arenas live in the graph handle (they need no clearing between searches or calls)
     const uint32_t want =
-        (uint32_t)std::min<uint64_t>(n, (uint64_t)g->sm_count * env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32));
+        (uint32_t)std::min<uint64_t>(n, (uint64_t)g->sm_count * env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32));  // see below
     const uint32_t blocks = (want + kWarpsPerBlock - 1) / kWarpsPerBlock, workers = blocks * kWarpsPerBlock;
-    const BallLayout L = make_ball_layout(max_len, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 17));
+    // shared memory: the workers of one SM share what the device offers (227 KB opt-in, 1 KB reserved per block)
+    const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32);
+    const uint32_t blocks_per_sm = (workers_per_sm + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    const uint32_t smem_per_block = ((uint32_t)g->smem_per_sm - blocks_per_sm * 1024u) / blocks_per_sm;
+    const uint32_t smem_per_worker =
+        std::min<uint32_t>(std::min<uint32_t>(smem_per_block, (uint32_t)g->smem_per_block_optin) / kWarpsPerBlock / 16 * 16,
+                           env_u32("MCAAT_ENUM_SMEM_PER_WORKER", 1u << 20, 2048, 1u << 20));
+    const BallLayout L = make_ball_layout(max_len, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 17), smem_per_worker);
+    const int force_global = (int)env_u32("MCAAT_ENUM_CHAINS_GLOBAL", 0, 0, 1);
+    MG_CUDA(cudaFuncSetAttribute(k_enum_pipeline, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(L.smem_bytes * kWarpsPerBlock)));
     const uint64_t sig = ((uint64_t)L.bytes << 20) ^ ((uint64_t)L.index_log << 8) ^ (uint64_t)workers;
     if (g->enum_arena.bytes < (size_t)workers * L.bytes || g->enum_arena_sig != sig) {
       // the hash indices must start out empty (all ones); every launch leaves them empty again
@@ -606,9 +674,10 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
           MG_LAUNCH(k_enum_pipeline, blocks, 32 * kWarpsPerBlock, L.smem_bytes * kWarpsPerBlock, s, g->view, g->adj.as<uint64_t>(), g->visited.as<uint32_t>(),
                     starts_dev.as<uint32_t>(), (uint32_t)n, min_len, max_len, g->enum_arena.as<uint8_t>(), L,
                     ctl_dev.as<PipeCtl>(), recs_dev.as<TicketRec>(), pool_nodes.as<uint32_t>(), nodes_cap,
-                    pool_len.as<uint32_t>(), len_cap);
+                    pool_len.as<uint32_t>(), len_cap, force_global);
         } else {
           const SlotLayout LB = make_layout(max_len, big_lock_log, big_relax, kClusterBound);
+          MG_CUDA(cudaFuncSetAttribute(k_enum_solo, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LB.smem_bytes));
           if (big_arena.bytes < LB.bytes) {
             MG_TRY(big_arena.alloc(LB.bytes));
           }
@@ -656,10 +725,10 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
   flush_timers(g);
   if (const char *trace = getenv("MCAAT_ENUM_TRACE")) {  // per-ticket timeline for profiling
     if (FILE *f = fopen(trace, "w")) {
-      fprintf(f, "ticket,fate,status,steps,n_cycles,us_searched,us_committed,n_ball,us_build\n");
+      fprintf(f, "ticket,fate,status,steps,n_cycles,us_searched,us_committed,n_ball,us_build,n_chains\n");
       for (uint64_t i = 0; i < n; ++i)
-        fprintf(f, "%llu,%d,%d,%u,%u,%u,%u,%u,%u\n", (unsigned long long)i, recs[i].fate, recs[i].status, recs[i].steps,
-                recs[i].n_cycles, recs[i].us_searched, recs[i].us_committed, recs[i].n_ball, recs[i].us_build);
+        fprintf(f, "%llu,%d,%d,%u,%u,%u,%u,%u,%u,%u\n", (unsigned long long)i, recs[i].fate, recs[i].status, recs[i].steps,
+                recs[i].n_cycles, recs[i].us_searched, recs[i].us_committed, recs[i].n_ball, recs[i].us_build, recs[i].n_chains);
       fclose(f);
     }
   }

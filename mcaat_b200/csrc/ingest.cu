@@ -244,7 +244,11 @@ extern "C" int mg_graph_create_from_files(const char *prefix, int device, mg_gra
     g->k = (uint32_t)k;
     g->stream = s;
     cudaDeviceProp prop;
-    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) g->sm_count = prop.multiProcessorCount;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) {
+    g->sm_count = prop.multiProcessorCount;
+    g->smem_per_sm = prop.sharedMemPerMultiprocessor;
+    g->smem_per_block_optin = prop.sharedMemPerBlockOptin;
+  }
     {
       cudaMemPool_t pool;
       if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {

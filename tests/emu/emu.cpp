@@ -357,18 +357,25 @@ int emu_dls_bitmap(Emu *e, uint64_t start, int limit) {
   return dls_run(e->adj.data(), (uint32_t)start, limit, s, sn.data(), sd.data(), sa.data(), (uint32_t)sn.size(), exp);
 }
 
-// 0 = hash-map search (enum_run) only, 1 = extracted-ball search with enum_run as overflow fallback
-static int g_algo = 1;
+// 0 = hash-map search (enum_run) only, 1 = extracted-ball search node by node (ball_dfs) with enum_run as overflow
+// fallback, 2 = the same on the contracted ball (sball_dfs; what k_enum_pipeline runs)
+static int g_algo = 2;
 static uint32_t g_ball_log = 16;  // ball index slots (node capacity = half)
+static int g_max_steps = kMaxSteps;  // step cap (lowered by the differential tests)
+static uint32_t g_chain_cap = 0;     // > 0: capacity of the contracted ball's record array (overflow tests)
 
 struct BallSlot {
   std::vector<LNode> nodes;
   std::vector<LTail> tails;
   std::vector<uint64_t> index;
   std::vector<Lvl> lvl;
-  std::vector<uint32_t> relax, cyc_off;
-  std::vector<uint16_t> cyc;
+  std::vector<uint32_t> relax, cyc_off, spos, ckeys, cyc_pos, cyc_noff, flat, relax_top;
+  std::vector<uint16_t> cyc, soff, shead;
+  std::vector<SHot> shot;
+  std::vector<uint64_t> sin4;
   BallArena A;
+  SBall B;
+  RecsPtr recs() const { return RecsPtr{B.hot, B.in4, A.lvl, A.relax_top}; }
   uint32_t live = 0;  // nodes of the last build (their index slots are still occupied)
   void init(int M, uint32_t index_log) {
     uint32_t cap = std::min<uint32_t>((1u << index_log) / 2, 65535u);
@@ -384,6 +391,14 @@ struct BallSlot {
     A.nodes = nodes.data(); A.tails = tails.data(); A.node_cap = cap; A.index = index.data(); A.index_log = index_log;
     A.relax = relax.data(); A.relax_cap = (uint32_t)relax.size(); A.cyc = cyc.data(); A.cyc_cap = (uint32_t)cyc.size();
     A.cyc_off = cyc_off.data();
+    spos.resize(cap); ckeys.resize(cap); soff.resize(cap + 1); shead.resize(cap); cyc_pos.resize(cyc.size());
+    cyc_noff.resize(kClusterBound + 1); flat.resize(cyc.size());
+    shot.resize(cap); sin4.resize(cap);
+    memset((void *)shot.data(), 0x55, shot.size() * sizeof(SHot));
+    A.spos = spos.data(); A.ckeys = ckeys.data(); A.soff = soff.data(); A.shead = shead.data();
+    A.cyc_pos = cyc_pos.data(); A.cyc_noff = cyc_noff.data(); A.max_steps = g_max_steps;
+    relax_top.resize(3); A.relax_top = relax_top.data(); A.relax_top_cap = 3;  // tiny: the spill path is exercised
+    B.hot = shot.data(); B.in4 = sin4.data(); B.cap = g_chain_cap ? g_chain_cap : cap; B.n = 0;
   }
 };
 
@@ -432,7 +447,7 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
   EmuSlot sl;
   sl.init(max_len, lock_log, 32768, kClusterBound);
   BallSlot bs;
-  if (g_algo == 1) bs.init(max_len, g_ball_log);
+  if (g_algo >= 1) bs.init(max_len, g_ball_log);
   std::vector<uint32_t> keys, cyc_nodes_flat, cyc_lens;  // result of the last search, whatever ran it
   EnumResult RR;
   // one search against bitmap `bm`: fills RR, keys (examined nodes), cyc_lens / cyc_nodes_flat
@@ -445,7 +460,7 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
     cyc_nodes_flat.assign(c->cyc_nodes.begin(), c->cyc_nodes.begin() + c->R.n_nodes);
   };
   auto search = [&](const uint32_t *bm, uint32_t s, auto poll) {
-    if (g_algo == 1) {
+    if (g_algo >= 1) {
       Coop co;
       ball_clear(bs.A, bs.live, co);
       uint32_t nn = 0;
@@ -453,6 +468,32 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
       bs.live = nn;
       RR.status = st;
       RR.n_cycles = RR.n_nodes = RR.n_keys = RR.steps = RR.expansions = 0;
+      if (st == kEnumDone && g_algo == 2) {
+        st = sball_contract(bs.A, nn, bs.B, co);
+        RR.status = st;
+        if (st == kEnumDone) {
+          SDfsState ds;
+          while (!sball_dfs(min_len, max_len, bs.A, bs.recs(), ds, 64, RR))
+            if (poll()) {
+              RR.status = kEnumSkipped;
+              RR.n_cycles = RR.n_nodes = 0;
+              break;
+            }
+          keys.clear();
+          cyc_lens.clear();
+          cyc_nodes_flat.clear();
+          if (RR.status != kEnumOverflow) {
+            for (uint32_t j = 0; j < nn; ++j) keys.push_back(bs.nodes[j].key);
+            RR.n_keys = nn;
+            if (RR.status != kEnumSkipped) {
+              sball_expand(bs.A, bs.B, ds.n_staged, bs.flat.data(), co);
+              for (uint32_t j = 0; j < RR.n_cycles; ++j) cyc_lens.push_back(bs.cyc_noff[j + 1] - bs.cyc_noff[j]);
+              cyc_nodes_flat.assign(bs.flat.begin(), bs.flat.begin() + RR.n_nodes);
+            }
+          }
+          return;
+        }
+      }
       if (st == kEnumDone) {
         DfsState ds;
         while (!ball_dfs(min_len, max_len, bs.A, ds, 256, RR))
@@ -541,6 +582,48 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
 void emu_set_algo(int algo, uint32_t ball_log) {
   g_algo = algo;
   g_ball_log = ball_log;
+}
+void emu_set_search_limits(int max_steps, uint32_t chain_cap) {
+  g_max_steps = max_steps > 0 ? max_steps : kMaxSteps;
+  g_chain_cap = chain_cap;
+}
+
+// One search from `start` against the current invalid/visited state (visited = all clear) with the node-by-node
+// ball search (algo 1) or the contracted one (algo 2): status, counters and the flat cycles, for differential tests.
+// out_stats = {status, n_cycles, n_nodes, steps, expansions, n_ball, n_chains}
+int emu_search_one(Emu *e, uint64_t start, int min_len, int max_len, int algo, uint64_t *out_stats, uint64_t *cyc_len,
+                   uint64_t *nodes) {
+  std::fill(e->visited.begin(), e->visited.end(), 0u);
+  BallSlot bs;
+  bs.init(max_len, g_ball_log);
+  Coop co;
+  uint32_t nn = 0;
+  EnumResult RR;
+  RR.n_cycles = RR.n_nodes = RR.n_keys = RR.steps = RR.expansions = 0;
+  RR.status = ball_build(e->v, e->adj.data(), e->visited.data(), (uint32_t)start, max_len, bs.A, nn, co);
+  out_stats[5] = nn;
+  out_stats[6] = 0;
+  if (RR.status == kEnumDone) {
+    if (algo == 2) {
+      RR.status = sball_contract(bs.A, nn, bs.B, co);
+      out_stats[6] = bs.B.n;
+      if (RR.status == kEnumDone) {
+        SDfsState ds;
+        while (!sball_dfs(min_len, max_len, bs.A, bs.recs(), ds, 7, RR)) {}
+        sball_expand(bs.A, bs.B, ds.n_staged, bs.flat.data(), co);
+        for (uint32_t j = 0; j < RR.n_cycles; ++j) cyc_len[j] = bs.cyc_noff[j + 1] - bs.cyc_noff[j];
+        for (uint32_t j = 0; j < RR.n_nodes; ++j) nodes[j] = bs.flat[j];
+      }
+    } else {
+      DfsState ds;
+      while (!ball_dfs(min_len, max_len, bs.A, ds, 7, RR)) {}
+      for (uint32_t j = 0; j < RR.n_cycles; ++j) cyc_len[j] = bs.cyc_off[j + 1] - bs.cyc_off[j];
+      for (uint32_t j = 0; j < RR.n_nodes; ++j) nodes[j] = bs.nodes[bs.cyc[j]].key;
+    }
+  }
+  out_stats[0] = (uint64_t)RR.status; out_stats[1] = RR.n_cycles; out_stats[2] = RR.n_nodes;
+  out_stats[3] = RR.steps; out_stats[4] = RR.expansions;
+  return 0;
 }
 
 }  // extern "C"

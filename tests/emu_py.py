@@ -48,13 +48,21 @@ def lib():
         L.emu_find_cycles.argtypes = ([C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.c_uint32]
                                       + [C.c_void_p] * 8)
         L.emu_set_algo.argtypes = [C.c_int, C.c_uint32]
+        L.emu_set_search_limits.argtypes = [C.c_int, C.c_uint32]
+        L.emu_search_one.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
 
-def set_algo(algo=1, ball_log=16):
-    """0 = hash-map search (enum_run) only; 1 = extracted-ball search (ball_dev.cuh), enum_run on overflow"""
+def set_algo(algo=2, ball_log=16):
+    """0 = hash-map search (enum_run) only; 1 = extracted-ball search node by node (ball_dfs), enum_run on overflow;
+    2 = the same on the contracted ball (sball_dfs) — what the device runs"""
     lib().emu_set_algo(algo, ball_log)
+
+
+def set_search_limits(max_steps=0, chain_cap=0):
+    """step cap of FindCycle (0 = the reference's 10 M) and record capacity of the contracted ball (0 = no limit)"""
+    lib().emu_set_search_limits(max_steps, chain_cap)
 
 
 class EmuGraph:
@@ -139,6 +147,20 @@ class EmuGraph:
 
     def dls_bitmap(self, start, limit):
         return lib().emu_dls_bitmap(self.h, int(start), limit)
+
+    def search_one(self, start, min_len, max_len, algo):
+        """one search against an all-clear visited bitmap: (stats dict, [cycle arrays])"""
+        st = np.zeros(7, np.uint64)
+        cyc_len = np.zeros(501, np.uint64)
+        nodes = np.zeros(501 * (max_len + 1), np.uint64)
+        lib().emu_search_one(self.h, int(start), min_len, max_len, algo, st.ctypes.data, cyc_len.ctypes.data,
+                             nodes.ctypes.data)
+        d = dict(zip(("status", "n_cycles", "n_nodes", "steps", "expansions", "n_ball", "n_chains"), map(int, st)))
+        cyc, at = [], 0
+        for i in range(d["n_cycles"]):
+            cyc.append(nodes[at:at + int(cyc_len[i])].copy())
+            at += int(cyc_len[i])
+        return d, cyc
 
     def find_cycles(self, starts, min_len, max_len, window=64, lock_log=13):
         starts = np.ascontiguousarray(starts, np.uint64)

@@ -69,7 +69,19 @@ def test_hash_map_search_matches_reference_dump(name, thr, mn, mx, dump):
     try:
         got = run_emu(emu(name), thr, mn, mx)
     finally:
-        E.set_algo(1)
+        E.set_algo()
+    assert O.same_run(O.parse_dump(dump), got) == []
+
+
+@pytest.mark.parametrize("name,thr,mn,mx,dump", G.cases(),
+                         ids=lambda v: str(v) if not isinstance(v, str) or "/" not in v else "")
+def test_node_level_ball_search_matches_reference_dump(name, thr, mn, mx, dump):
+    """ball_dfs (the literal search node by node, kept as the yardstick of the contracted search) on its own"""
+    E.set_algo(1)
+    try:
+        got = run_emu(emu(name), thr, mn, mx)
+    finally:
+        E.set_algo()
     assert O.same_run(O.parse_dump(dump), got) == []
 
 
@@ -84,11 +96,11 @@ def test_speculative_window_is_order_exact(window):
 def test_small_arena_overflow_is_rerun_exactly():
     name, thr, mn, mx, dump = [c for c in G.cases() if c[0] == "repeatrich" and c[1] == 5][0]
     ref = O.parse_dump(dump)
-    E.set_algo(1, ball_log=7)  # 64-node balls: most searches overflow into the hash-map search ...
+    E.set_algo(2, ball_log=7)  # 64-node balls: most searches overflow into the hash-map search ...
     try:
         got = run_emu(emu(name), thr, mn, mx, window=32, lock_log=6)  # ... whose first arena overflows too
     finally:
-        E.set_algo(1)
+        E.set_algo()
     assert O.same_run(ref, got) == []
     assert got.stats["overflow_reruns"] > 0
 
@@ -227,3 +239,38 @@ def test_read_mapping_matches_reference(tmp_path, name):
             got = g.map_reads(seqs, ids, reverse=rev)
             assert [x.size for x in got] == list(np.diff(off)), (key, use_jump)
             assert np.array_equal(np.concatenate(got), flat), (key, use_jump)
+
+
+@pytest.mark.parametrize("name,thr", [("repeatrich", 5), ("biallelic", 10), ("strain", 10), ("tiny", 5)])
+def test_contracted_search_equals_node_level_search(name, thr):
+    """sball_dfs (chains of the ball as single records) against ball_dfs (node by node) per start node: status, raw
+    cycle sequence, and the step / expansion counters the reference's loop would have reached — with length bounds
+    that cut chains in the middle and with lowered step caps (the cap fires inside a chain)."""
+    g = emu(name)
+    g.prune()
+    cand = [int(c) for c in g.candidates(thr)]
+    rng = np.random.default_rng(5)
+    if len(cand) > 150:
+        cand = [cand[i] for i in sorted(rng.choice(len(cand), 150, replace=False))]
+    n_cut = n_cap = n_bound = n_contracted = 0
+    for mn, mx, cap in [(27, 77, 0), (5, 33, 0), (0, 12, 0), (20, 100, 0), (27, 77, 1000), (27, 77, 137), (10, 60, 5000)]:
+        E.set_search_limits(cap, 0)
+        try:
+            for s in cand:
+                a, ca = g.search_one(s, mn, mx, 1)
+                b, cb = g.search_one(s, mn, mx, 2)
+                for key in ("status", "n_cycles", "n_nodes", "steps", "expansions", "n_ball"):
+                    if key == "expansions" and a["status"] == 2:
+                        continue  # cap inside a chain: the statistic counts the whole chain (results are unaffected)
+                    assert a[key] == b[key], (name, s, mn, mx, cap, key, a, b)
+                assert len(ca) == len(cb) and all(np.array_equal(x, y) for x, y in zip(ca, cb)), (name, s, mn, mx, cap)
+                n_cap += a["status"] == 2
+                n_bound += a["status"] == 1
+                n_contracted += b["n_chains"] < b["n_ball"]
+        finally:
+            E.set_search_limits(0, 0)
+    assert n_contracted > 0
+    if name == "repeatrich":
+        assert n_cap > 0
+    if name == "biallelic":
+        assert n_bound > 0
