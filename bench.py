@@ -637,7 +637,7 @@ def main():
         "cycle_find_wall_ms": wall_ms / args.steps, "step_ms": [round(x, 2) for x in step_ms], "gpu_launches": int(launches), "clocks": clk,
         "counts": {k: stats[k] for k in ("n_tips_before", "n_mult1", "n_peeled", "n_valid", "n_tips_after", "n_candidates",
                                           "n_starts", "n_searched", "n_cycles", "n_skipped", "n_bound_hits", "n_cap_hits",
-                                          "n_reruns", "n_rounds", "n_searches_run", "n_abandoned", "dls_expansions", "expansions")},
+                                          "n_reruns", "n_rounds", "n_searches_run", "n_abandoned", "n_out_of_order", "dls_expansions", "expansions")},
         "phase_ms_per_step": phases,
         "rates": {"nodes_scanned_per_s": n_items / (ms_per_step / 1e3),
                   "candidates_per_s": stats["n_candidates"] / max(phases.get("dls", 0) / 1e3, 1e-9),

@@ -154,6 +154,7 @@ typedef struct {
   uint64_t n_searches_run;  /* searches started, speculative ones included */
   uint64_t n_abandoned;     /* running searches given up because an earlier commit marked their start */
   uint64_t expansions;      /* _GetOutgoings/_GetIncomings evaluations of committed searches */
+  uint64_t n_out_of_order;  /* searches committed ahead of their turn: no earlier start's search could touch what they read */
 } mg_cycles;
 int mg_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len, int max_len, mg_cycles *out);
 void mg_cycles_free(mg_cycles *c);

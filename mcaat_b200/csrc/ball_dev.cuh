@@ -453,16 +453,25 @@ done:
 // (OUT(n_c), IN(n_1)); the relaxation stack keeps its LIFO order; the step and expansion counters advance by what
 // the literal loop would have counted.  tests/emu compares this search with ball_dfs above (and both with the
 // reference dumps), also with lowered step caps and length bounds that cut chains.
+// One chain record, 16 bytes = one vector access:
+//   word 0: lh | j << 16      lh = lock[n_1] = (j ? a + 1 : M): what a push tests; j as above; bit 31: the chain is on
+//             | on_path << 31 the current path.  The only word the search writes.
+//   word 1: c | flags << 16   flags bits 0..3: slots of OUT(n_c) that hold a chain other than the start node; bits
+//                             12..14: slot of the start node in OUT(n_c) (7 = not a neighbour: the set holds the start
+//                             at most once, and :157-166 never erases it)
+//   words 2, 3: OUT(n_c) as four chain numbers in std::unordered_set iteration order (chain 0 = the start node);
+//               unused slots hold the number of the DUMMY record (index n, lh = 0, j != c): it fails every test, so
+//               the search loads and tests all four slots without asking which ones exist
 struct alignas(16) SHot {
-  uint16_t a, j, c;
-  uint16_t flags;    // bit 0: the chain is on the current path
-  union { uint16_t out[4]; uint64_t out4; };  // chains that OUT(n_c) leads to (chain 0 = the start node), iteration order
+  uint16_t lh, j, c;
+  uint16_t flags;
+  union { uint16_t out[4]; uint64_t out4; };
 };
 static_assert(sizeof(SHot) == 16, "one 16-byte access per chain record");
-constexpr uint16_t kSOnPath = 1;
+constexpr uint32_t kSOnPath = 1u << 31, kSStartShift = 12, kSNoStart = 7, kSLevelBits = 0x700Fu;
 struct SBall {          // the contracted ball; records in shared memory when they fit, else in the worker's arena
-  SHot *hot;
-  uint64_t *in4;        // chains whose last node is in IN(n_1), iteration order
+  SHot *hot;            // [n + 1]: the last one is the dummy
+  uint64_t *in4;        // [n + 1] chains whose last node is in IN(n_1), iteration order; unused slots = dummy
   uint32_t cap;
   uint32_t n;           // number of chains
 };
@@ -476,7 +485,7 @@ MG_HD bool ball_is_head(const LNode *N, const LTail *T, uint32_t x) {
 }
 
 // Contracts the ball of ball_build (all lanes).  Returns kEnumDone, or kEnumOverflow when B.cap is too small.
-MG_HD_NOINLINE int sball_contract(const BallArena &A, uint32_t n_nodes, SBall &B, const Coop &co) {
+MG_HD_NOINLINE int sball_contract(const BallArena &A, uint32_t n_nodes, int M, SBall &B, const Coop &co) {
   const LNode *N = A.nodes;
   const LTail *T = A.tails;
   // 1. chain heads, numbered in local-id order (the start node is chain 0)
@@ -489,7 +498,7 @@ MG_HD_NOINLINE int sball_contract(const BallArena &A, uint32_t n_nodes, SBall &B
     n_super += cnt;
   }
   B.n = n_super;
-  if (n_super > B.cap) return kEnumOverflow;
+  if (n_super + 1 > B.cap || n_super >= kNoLid) return kEnumOverflow;
   co.sync();
   // 2. one walk per chain: membership of its nodes, length, last node
   for (uint32_t s = (uint32_t)co.lane; s < n_super; s += Coop::kLanes) {
@@ -505,7 +514,7 @@ MG_HD_NOINLINE int sball_contract(const BallArena &A, uint32_t n_nodes, SBall &B
       x = y;
     }
     SHot h;
-    h.a = 0;
+    h.lh = (uint16_t)M;       // untouched: every lock is cycle_max_length (try_emplace(n, M), :168)
     h.j = 0;
     h.c = (uint16_t)i;
     h.flags = 0;
@@ -526,16 +535,31 @@ MG_HD_NOINLINE int sball_contract(const BallArena &A, uint32_t n_nodes, SBall &B
     run += tot;
   }
   co.sync();
-  // 4. neighbour sets as chain numbers; item ids grouped by chain
+  // 4. neighbour sets as chain numbers (unused slots: the dummy); item ids grouped by chain
   for (uint32_t s = (uint32_t)co.lane; s < n_super; s += Coop::kLanes) {
     uint64_t o = B.hot[s].out4, in = B.in4[s], o2 = 0, in2 = 0;
+    uint32_t sslot = kSNoStart, vmask = 0;
     for (int q = 0; q < 4; ++q) {
       const uint32_t a = (uint32_t)(o >> (16 * q)) & 0xFFFFu, b = (uint32_t)(in >> (16 * q)) & 0xFFFFu;
-      o2 |= (uint64_t)(a == kNoLid ? kNoLid : (A.spos[a] & 0xFFFFu)) << (16 * q);
-      in2 |= (uint64_t)(b == kNoLid ? kNoLid : (A.spos[b] & 0xFFFFu)) << (16 * q);
+      const uint32_t ca = a == kNoLid ? n_super : (A.spos[a] & 0xFFFFu);
+      if (ca == 0) sslot = (uint32_t)q;
+      else if (a != kNoLid) vmask |= 1u << q;
+      o2 |= (uint64_t)ca << (16 * q);
+      in2 |= (uint64_t)(b == kNoLid ? n_super : (A.spos[b] & 0xFFFFu)) << (16 * q);
     }
     B.hot[s].out4 = o2;
+    B.hot[s].flags = (uint16_t)((sslot << kSStartShift) | vmask);
     B.in4[s] = in2;
+  }
+  if (co.lane == 0) {  // the dummy
+    SHot d;
+    d.lh = 0;
+    d.j = 0x8000u;  // "on the path": no relaxation enters it
+    d.c = 1;
+    d.flags = (uint16_t)(kSNoStart << kSStartShift);
+    d.out4 = 0x0001000100010001ull * n_super;
+    B.hot[n_super] = d;
+    B.in4[n_super] = 0x0001000100010001ull * n_super;
   }
   for (uint32_t x = (uint32_t)co.lane; x < n_nodes; x += Coop::kLanes) {
     const uint32_t sp = A.spos[x];
@@ -550,26 +574,19 @@ struct SDfsState {  // the scalars of a paused search
   int plen = 0;      // path.size()
   int counter = 0, steps = 0;
   uint32_t expansions = 0, n_cycles = 0, n_staged = 0, n_out = 0;
+  uint32_t iters = 0, relax_pops = 0;  // loop iterations on the contracted ball / relaxation entries popped (profiling)
   bool started = false;
 };
 
-// Register images of the two 16-byte records the search moves (one vector access each):
-//   chain record  SHot: aj = a | j << 16, cf = c | flags << 16, out4
-//   path level    Lvl : set, pmeta = path.size() below this chain, nb = chain | backtrack length << 16
-struct HotReg {
-  uint32_t aj, cf;
-  uint64_t out4;
-  MG_HD int a() const { return (int)(aj & 0xFFFFu); }
-  MG_HD int j() const { return (int)(aj >> 16); }
-  MG_HD int c() const { return (int)(cf & 0xFFFFu); }
-  MG_HD bool on_path() const { return (cf >> 16) & kSOnPath; }
+// Register image of a 16-byte record.  A path level (Lvl) is stored as
+//   x, y: the neighbour set being scanned (OUT of the level's chain, four chain numbers)
+//   z:    chain | path.size() below this chain << 16
+//   w:    bits 0..3 slots (other than the start node's) not yet erased (:173) | bit 8: backtrack length is 1 (:158;
+//         the only other value is M) | bits 12..14 slot of the start node in the set — the record's flags, masked
+struct Rec4 {
+  uint32_t x, y, z, w;
 };
-struct LvlReg {
-  uint64_t set;
-  uint32_t pmeta, nb;
-  MG_HD uint32_t node() const { return nb & 0xFFFFu; }
-  MG_HD int bl() const { return (int)(nb >> 16); }
-};
+constexpr uint32_t kLvlReached = 1u << 8, kLvlStartShift = 12;
 // Where the records live.  RecsPtr: plain pointers (arena, host emulation, or shared memory through generic
 // addresses); RecsSmem (device): everything in shared memory, addressed with ld/st.shared.
 struct RecsPtr {
@@ -577,80 +594,81 @@ struct RecsPtr {
   const uint64_t *in4;
   Lvl *lvl;
   uint32_t *rtop;
-  MG_HD HotReg ld_hot(uint32_t s) const {
-    HotReg h;
+  MG_HD Rec4 ld_hot(uint32_t s) const {
+    Rec4 h;
 #if defined(__CUDA_ARCH__)
     const uint4 v = *reinterpret_cast<const uint4 *>(&hot[s]);
-    h.aj = v.x; h.cf = v.y; h.out4 = (uint64_t)v.z | ((uint64_t)v.w << 32);
+    h.x = v.x; h.y = v.y; h.z = v.z; h.w = v.w;
 #else
     const SHot &r = hot[s];
-    h.aj = (uint32_t)r.a | ((uint32_t)r.j << 16); h.cf = (uint32_t)r.c | ((uint32_t)r.flags << 16); h.out4 = r.out4;
+    h.x = (uint32_t)r.lh | ((uint32_t)r.j << 16); h.y = (uint32_t)r.c | ((uint32_t)r.flags << 16);
+    h.z = (uint32_t)r.out4; h.w = (uint32_t)(r.out4 >> 32);
 #endif
     return h;
   }
-  MG_HD void st_hot_state(uint32_t s, uint32_t aj, uint32_t cf) const {  // a, j, c, flags: the first 8 bytes
+  MG_HD void st_hot_w0(uint32_t s, uint32_t w0) const {
 #if defined(__CUDA_ARCH__)
-    *reinterpret_cast<uint2 *>(&hot[s]) = make_uint2(aj, cf);
+    *reinterpret_cast<uint32_t *>(&hot[s]) = w0;
 #else
-    SHot &r = hot[s];
-    r.a = (uint16_t)aj; r.j = (uint16_t)(aj >> 16); r.c = (uint16_t)cf; r.flags = (uint16_t)(cf >> 16);
+    hot[s].lh = (uint16_t)w0; hot[s].j = (uint16_t)(w0 >> 16);
 #endif
   }
-  MG_HD uint64_t ld_in(uint32_t s) const { return in4[s]; }
-  MG_HD LvlReg ld_lvl(int i) const {
-    LvlReg l;
+  MG_HD void ld_in(uint32_t s, uint32_t &lo, uint32_t &hi) const { const uint64_t v = in4[s]; lo = (uint32_t)v; hi = (uint32_t)(v >> 32); }
+  MG_HD Rec4 ld_lvl(int i) const {
+    Rec4 l;
 #if defined(__CUDA_ARCH__)
     const uint4 v = *reinterpret_cast<const uint4 *>(&lvl[i]);
-    l.set = (uint64_t)v.x | ((uint64_t)v.y << 32); l.pmeta = v.z; l.nb = v.w;
+    l.x = v.x; l.y = v.y; l.z = v.z; l.w = v.w;
 #else
-    l.set = lvl[i].set; l.pmeta = lvl[i].pmeta; l.nb = (uint32_t)lvl[i].node | ((uint32_t)(uint16_t)lvl[i].bl << 16);
+    memcpy(&l, &lvl[i], 16);
 #endif
     return l;
   }
-  MG_HD void st_lvl(int i, const LvlReg &l) const {
+  MG_HD void st_lvl(int i, const Rec4 &l) const {
 #if defined(__CUDA_ARCH__)
-    *reinterpret_cast<uint4 *>(&lvl[i]) = make_uint4((uint32_t)l.set, (uint32_t)(l.set >> 32), l.pmeta, l.nb);
+    *reinterpret_cast<uint4 *>(&lvl[i]) = make_uint4(l.x, l.y, l.z, l.w);
 #else
-    lvl[i].set = l.set; lvl[i].pmeta = l.pmeta; lvl[i].node = (uint16_t)l.nb; lvl[i].bl = (int16_t)(l.nb >> 16);
+    memcpy(&lvl[i], &l, 16);
 #endif
   }
-  MG_HD uint32_t ld_lvl_node_pmeta(int i, uint32_t &pmeta) const { pmeta = lvl[i].pmeta; return lvl[i].node; }
+  MG_HD uint32_t ld_lvl_z(int i) const {
+#if defined(__CUDA_ARCH__)
+    return reinterpret_cast<const uint32_t *>(&lvl[i])[2];
+#else
+    uint32_t z;
+    memcpy(&z, (const char *)&lvl[i] + 8, 4);
+    return z;
+#endif
+  }
   MG_HD uint32_t ld_rtop(uint32_t i) const { return rtop[i]; }
   MG_HD void st_rtop(uint32_t i, uint32_t v) const { rtop[i] = v; }
 };
 #if defined(__CUDACC__)
 struct RecsSmem {
   uint32_t hot, in4, lvl, rtop;  // shared-window byte addresses
-  __device__ __forceinline__ HotReg ld_hot(uint32_t s) const {
-    HotReg h;
-    uint32_t z, w;
-    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(h.aj), "=r"(h.cf), "=r"(z), "=r"(w) : "r"(hot + s * 16u));
-    h.out4 = (uint64_t)z | ((uint64_t)w << 32);
+  __device__ __forceinline__ Rec4 ld_hot(uint32_t s) const {
+    Rec4 h;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(h.x), "=r"(h.y), "=r"(h.z), "=r"(h.w) : "r"(hot + s * 16u));
     return h;
   }
-  __device__ __forceinline__ void st_hot_state(uint32_t s, uint32_t aj, uint32_t cf) const {
-    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(hot + s * 16u), "r"(aj), "r"(cf) : "memory");
+  __device__ __forceinline__ void st_hot_w0(uint32_t s, uint32_t w0) const {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(hot + s * 16u), "r"(w0) : "memory");
   }
-  __device__ __forceinline__ uint64_t ld_in(uint32_t s) const {
-    uint64_t v;
-    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(in4 + s * 8u));
-    return v;
+  __device__ __forceinline__ void ld_in(uint32_t s, uint32_t &lo, uint32_t &hi) const {
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(in4 + s * 8u));
   }
-  __device__ __forceinline__ LvlReg ld_lvl(int i) const {
-    LvlReg l;
-    uint32_t x, y;
-    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x), "=r"(y), "=r"(l.pmeta), "=r"(l.nb) : "r"(lvl + (uint32_t)i * 16u));
-    l.set = (uint64_t)x | ((uint64_t)y << 32);
+  __device__ __forceinline__ Rec4 ld_lvl(int i) const {
+    Rec4 l;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(l.x), "=r"(l.y), "=r"(l.z), "=r"(l.w) : "r"(lvl + (uint32_t)i * 16u));
     return l;
   }
-  __device__ __forceinline__ void st_lvl(int i, const LvlReg &l) const {
-    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(lvl + (uint32_t)i * 16u), "r"((uint32_t)l.set),
-                 "r"((uint32_t)(l.set >> 32)), "r"(l.pmeta), "r"(l.nb) : "memory");
+  __device__ __forceinline__ void st_lvl(int i, const Rec4 &l) const {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(lvl + (uint32_t)i * 16u), "r"(l.x), "r"(l.y), "r"(l.z), "r"(l.w) : "memory");
   }
-  __device__ __forceinline__ uint32_t ld_lvl_node_pmeta(int i, uint32_t &pmeta) const {
-    uint32_t nb;
-    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(pmeta), "=r"(nb) : "r"(lvl + (uint32_t)i * 16u + 8u));
-    return nb & 0xFFFFu;
+  __device__ __forceinline__ uint32_t ld_lvl_z(int i) const {
+    uint32_t z;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(z) : "r"(lvl + (uint32_t)i * 16u + 8u));
+    return z;
   }
   __device__ __forceinline__ uint32_t ld_rtop(uint32_t i) const {
     uint32_t v;
@@ -662,180 +680,192 @@ struct RecsSmem {
   }
 };
 #endif
+MG_HD int ffs32(uint32_t x) {  // 1-based position of the lowest set bit (x != 0)
+#if defined(__CUDA_ARCH__)
+  return __ffs((int)x);
+#else
+  return __builtin_ffs((int)x);
+#endif
+}
 
 // Literal FindCycleUtil + FindCycle (src/cycle_finder.cpp:231-243,140-225) on the contracted ball (one lane).  Runs at
 // most `budget` further chain steps; returns true when the search has ended (R filled in), false when it is paused.
 // Cycles are staged as (chain, position in the flat id list) per path level; sball_expand turns them into item ids.
+// The loop is bound by instruction issue of ONE thread (a dependent chain: ~4 cycles per instruction), not by memory,
+// so it is written for few instructions: 32-bit words only, all four slots of a neighbour set loaded and tested
+// without branches (dummy record), the first slot that passes picked with a bit scan.
 // (Inlined at each call site: the device instantiates it for records in shared memory and for records in the arena.)
 template <class Recs>
 MG_HD bool sball_dfs(int min_len, int max_len, const BallArena &A, const Recs &Q, SDfsState &S, int budget,
                      EnumResult &R) {
-  const int M = max_len;
+  const uint32_t M = (uint32_t)max_len;
   uint32_t expansions = S.expansions, n_cycles = S.n_cycles, n_staged = S.n_staged, n_out = S.n_out;
-  int plen = S.plen, depth = S.depth, counter = S.counter, steps = S.steps;
+  uint32_t plen = (uint32_t)S.plen;
+  int depth = S.depth, counter = S.counter, steps = S.steps;
   int32_t status = kEnumDone;
-  LvlReg cur;  // top level in registers
+  uint32_t iters = S.iters, relax_pops = S.relax_pops;
+  const int max_steps = A.max_steps;
+  Rec4 cur;  // top level in registers
   if (!S.started) {
     S.started = true;
     A.cyc_off[0] = 0;
     A.cyc_noff[0] = 0;
-    const HotReg h0 = Q.ld_hot(0);
-    Q.st_hot_state(0, h0.aj, h0.cf | ((uint32_t)kSOnPath << 16));  // lock[start] = 0 (:237) is never consulted: the start stays on the path
-    cur.set = h0.out4;                     // _GetOutgoings(start), :238-240
-    cur.pmeta = 0;
-    cur.nb = 0u | ((uint32_t)M << 16);
+    const Rec4 h0 = Q.ld_hot(0);
+    Q.st_hot_w0(0, kSOnPath);                        // lock[start] = 0 (:237); the start stays on the path
+    cur.x = h0.z;                                    // _GetOutgoings(start), :238-240
+    cur.y = h0.w;
+    cur.z = 0;
+    cur.w = (h0.y >> 16) & kSLevelBits;
     plen = 1;
     depth = 1;
     ++expansions;
   } else {
     cur = Q.ld_lvl(depth - 1);
   }
-  int left = budget;
-  while (depth > 0) {
-    if (left-- == 0) {
+  for (int left = budget; depth > 0; --left) {
+    if (left == 0) {
       Q.st_lvl(depth - 1, cur);
-      S.depth = depth; S.plen = plen; S.counter = counter; S.steps = steps;
+      S.depth = depth; S.plen = (int)plen; S.counter = counter; S.steps = steps;
       S.expansions = expansions; S.n_cycles = n_cycles; S.n_staged = n_staged; S.n_out = n_out;
+      S.iters = iters; S.relax_pops = relax_pops;
       return false;
     }
-    if (++steps > A.max_steps) { status = kEnumCap; break; }  // :148-151
-    const uint64_t set = cur.set;                             // :153 (copy)
-    HotReg hd[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const uint32_t nb = (uint32_t)(set >> (16 * i)) & 0xFFFFu;
-      if (nb != kNoLid) hd[i] = Q.ld_hot(nb);
+    ++iters;
+    // :148-151.  `steps` also advances in bulk below (a chain's inner pushes and pops are loop iterations of the
+    // reference); nothing is recorded between such an advance and this test, so one test per chain step is exact.
+    if (++steps > max_steps) { status = kEnumCap; break; }
+    // stack.back() (:153), in iteration order: up to four chains; bits 0..3 of cur.w = not erased yet
+    uint32_t first = 4, nb = 0, hy = 0, hz = 0, hw = 0;
+    if (cur.w & 0xFu) {
+      const uint32_t nb0 = cur.x & 0xFFFFu, nb1 = cur.x >> 16, nb2 = cur.y & 0xFFFFu, nb3 = cur.y >> 16;
+      const Rec4 r0 = Q.ld_hot(nb0), r1 = Q.ld_hot(nb1), r2 = Q.ld_hot(nb2), r3 = Q.ld_hot(nb3);
+      // :168 for n_1 of each member: path.size() < lock
+      uint32_t m = (plen < (r0.x & 0xFFFFu) ? 1u : 0u) | (plen < (r1.x & 0xFFFFu) ? 2u : 0u) |
+                   (plen < (r2.x & 0xFFFFu) ? 4u : 0u) | (plen < (r3.x & 0xFFFFu) ? 8u : 0u);
+      m &= cur.w;
+      if (m) {                                                // the first member that passes is pushed
+        const uint32_t b = m & (0u - m);                      // lowest set bit: 1, 2, 4 or 8
+        first = (b >> 1) - (b >> 3);
+        const bool lo2 = (b & 3u) != 0, even = (b & 5u) != 0;
+        nb = lo2 ? (even ? nb0 : nb1) : (even ? nb2 : nb3);
+        hy = lo2 ? (even ? r0.y : r1.y) : (even ? r2.y : r3.y);
+        hz = lo2 ? (even ? r0.z : r1.z) : (even ? r2.z : r3.z);
+        hw = lo2 ? (even ? r0.w : r1.w) : (even ? r2.w : r3.w);
+        cur.w ^= b;                                           // stack.back().erase(n), :173
+      }
     }
-    bool flag = true;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const uint32_t nb = (uint32_t)(set >> (16 * i)) & 0xFFFFu;
-      if (nb != kNoLid && flag) {
-        if (nb == 0) {                                        // n == start_node, :157-166
-          cur.nb = (cur.nb & 0xFFFFu) | (1u << 16);           // backtrack_lengths.back() = 1
-          if (plen > min_len) {
-            if (++counter >= kClusterBound) {                 // cluster bound: the final answer is empty
-              status = kEnumBound;
-              n_cycles = n_staged = n_out = 0;
-              goto done;
-            }
-            if (n_staged + (uint32_t)depth > A.cyc_cap) { status = kEnumOverflow; goto done; }
-            for (int l = 0; l + 1 < depth; ++l) {
-              uint32_t pm;
-              A.cyc[n_staged + l] = (uint16_t)Q.ld_lvl_node_pmeta(l, pm);
-              A.cyc_pos[n_staged + l] = n_out + pm;
-            }
-            A.cyc[n_staged + depth - 1] = (uint16_t)cur.node();
-            A.cyc_pos[n_staged + depth - 1] = n_out + cur.pmeta;
-            n_staged += (uint32_t)depth;
-            n_out += (uint32_t)plen;
-            A.cyc_off[++n_cycles] = n_staged;
-            A.cyc_noff[n_cycles] = n_out;
-          }
-        } else {
-          const HotReg h = hd[i];
-          const int lock_head = h.j() ? h.a() + 1 : M;
-          if (plen < lock_head) {                             // :168 for n_1
-            {                                                 // stack.back().erase(n), :173
-              const uint64_t low = i ? set & ((1ull << (16 * i)) - 1) : 0ull;
-              const uint64_t high = i < 3 ? (set >> (16 * (i + 1))) << (16 * i) : 0ull;
-              cur.set = low | high | (0xFFFFull << 48);
-            }
-            const int c = h.c(), t = c < M - plen ? c : M - plen;
-            expansions += (uint32_t)t;                        // one _GetOutgoings per pushed node, :174-176
-            const uint32_t aj = (uint32_t)plen | ((uint32_t)t << 16);
-            if (t < c) {                                      // cut by the length bound: popped again at once
-              Q.st_hot_state(nb, aj, h.cf);
-              steps += 2 * t - 1;
-            } else {
-              Q.st_hot_state(nb, aj, h.cf | ((uint32_t)kSOnPath << 16));
-              steps += c - 1;
-              Q.st_lvl(depth - 1, cur);
-              ++depth;
-              cur.set = h.out4;
-              cur.pmeta = (uint32_t)plen;
-              cur.nb = nb | ((uint32_t)M << 16);
-              plen += c;
-            }
-            if (steps > A.max_steps) { steps = A.max_steps + 1; status = kEnumCap; goto done; }
-            flag = false;                                     // break
-          }
+    if (((cur.w >> kSStartShift) & 7u) < first) {             // n == start_node comes before it, :157-166
+      cur.w |= kLvlReached;                                   // backtrack_lengths.back() = 1
+      if ((int)plen > min_len) {
+        if (++counter >= kClusterBound) {                     // cluster bound: the final answer is empty
+          status = kEnumBound;
+          n_cycles = n_staged = n_out = 0;
+          break;
         }
+        if (n_staged + (uint32_t)depth > A.cyc_cap) { status = kEnumOverflow; break; }
+        for (int l = 0; l + 1 < depth; ++l) {
+          const uint32_t z = Q.ld_lvl_z(l);
+          A.cyc[n_staged + l] = (uint16_t)z;
+          A.cyc_pos[n_staged + l] = n_out + (z >> 16);
+        }
+        A.cyc[n_staged + depth - 1] = (uint16_t)cur.z;
+        A.cyc_pos[n_staged + depth - 1] = n_out + (cur.z >> 16);
+        n_staged += (uint32_t)depth;
+        n_out += plen;
+        A.cyc_off[++n_cycles] = n_staged;
+        A.cyc_noff[n_cycles] = n_out;
       }
     }
-    if (flag) {                                               // :181-211
-      const uint32_t v = cur.node();
-      const int b = cur.bl(), c = plen - (int)cur.pmeta;
-      plen = (int)cur.pmeta;
-      --depth;
-      steps += c - 1;                                         // the chain's other nodes are popped one step each
-      if (steps > A.max_steps) { steps = A.max_steps + 1; status = kEnumCap; goto done; }
-      const uint32_t cf_v = (uint32_t)c;                      // flags cleared: off the path
-      uint64_t ins = 0;
-      if (b < M) {                                            // every node with lock < M goes to M, :192-196
-        const int raised = c < M - plen - 1 ? c : M - plen - 1;
-        expansions += (uint32_t)(raised > 0 ? raised : 0);
-        Q.st_hot_state(v, 0u, cf_v);
-        ins = Q.ld_in(v);
+    if (first < 4) {
+      const uint32_t c = hy & 0xFFFFu, room = M - plen, t = c < room ? c : room;
+      expansions += t;                                        // one _GetOutgoings per pushed node, :174-176
+      const uint32_t w0 = (plen + 1u) | (t << 16);            // locks of n_1..n_t become plen + i
+      if (t < c) {                                            // cut by the length bound: popped again at once
+        Q.st_hot_w0(nb, w0);
+        steps += (int)(2 * t - 1);
       } else {
-        Q.st_hot_state(v, (uint32_t)plen | ((uint32_t)c << 16), cf_v);  // unchanged (plen, c): a full push left it so
+        Q.st_hot_w0(nb, w0 | kSOnPath);
+        Q.st_lvl(depth - 1, cur);
+        steps += (int)(c - 1);
+        ++depth;
+        cur.x = hz;
+        cur.y = hw;
+        cur.z = nb | (plen << 16);
+        cur.w = (hy >> 16) & kSLevelBits;
+        plen += c;
       }
+    } else {                                                  // :181-211
+      const uint32_t v = cur.z & 0xFFFFu, below = cur.z >> 16, c = plen - below;
+      const uint32_t vw = cur.w;
+      plen = below;
+      --depth;
+      steps += (int)(c - 1);                                  // the chain's other nodes are popped one step each
       if (depth > 0) {
         cur = Q.ld_lvl(depth - 1);
-        if (b < cur.bl()) cur.nb = (cur.nb & 0xFFFFu) | ((uint32_t)b << 16);
+        cur.w |= vw & kLvlReached;                            // :187 (minimum of the two backtrack lengths)
       }
-      if (b < M && plen + 1 < M) {                            // n_1 was relaxed: its off-path in-neighbours, level b + 1
-        // relax_stack (:192-210) over chains: entry = level << 16 | chain, meaning (level, last node of the chain).
-        // An entry only acts when lock[n_c] < M - level + 1, and locks never decrease during a relaxation, so
-        // entries that fail the test when they would be pushed are dropped at once; the test is repeated at the pop.
-        uint32_t rn = 0;
-        int x = b + 1;
-        for (;;) {
-          HotReg hw[4];
+      if (!(vw & kLvlReached)) {
+        Q.st_hot_w0(v, (plen + 1u) | (c << 16));              // off the path; locks stay plen + i
+      } else {                                                // every node with lock < M goes to M, :192-196
+        const uint32_t lim = M - plen - 1u;                   // nodes i with plen + i < M
+        expansions += c < lim ? c : lim;
+        Q.st_hot_w0(v, M);
+        if (plen + 1u < M) {                                  // n_1 was relaxed: its off-path in-neighbours, level 2
+          // relax_stack (:192-210) over chains: entry = level << 16 | chain, meaning (level, last node of the chain).
+          // An entry acts iff lock[n_c] < M - level + 1 — for a fully affine chain (j == c) that is
+          // lh + c + level < M + 2, and then it holds for the whole chain.  Locks never decrease during a
+          // relaxation, so entries that fail when they would be pushed are dropped at once; the test is
+          // repeated at the pop.
+          uint32_t rn = 0, x = 2, in_lo, in_hi;
+          Q.ld_in(v, in_lo, in_hi);
+          for (;;) {
+            const uint32_t w0 = in_lo & 0xFFFFu, w1 = in_lo >> 16, w2 = in_hi & 0xFFFFu, w3 = in_hi >> 16;
+            const Rec4 q0 = Q.ld_hot(w0), q1 = Q.ld_hot(w1), q2 = Q.ld_hot(w2), q3 = Q.ld_hot(w3);
+            const uint32_t ws[4] = {w0, w1, w2, w3};
+            const Rec4 qs[4] = {q0, q1, q2, q3};
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const uint32_t w = (uint32_t)(ins >> (16 * i)) & 0xFFFFu;
-            if (w != kNoLid) hw[i] = Q.ld_hot(w);
-          }
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const uint32_t w = (uint32_t)(ins >> (16 * i)) & 0xFFFFu;
-            if (w != kNoLid && !hw[i].on_path() && hw[i].j() == hw[i].c() &&
-                hw[i].a() + hw[i].c() < M - x + 1) {          // :198-199 + early :195
-              if (rn >= A.relax_cap + A.relax_top_cap) { status = kEnumOverflow; goto done; }
-              const uint32_t ent = ((uint32_t)x << 16) | w;
-              if (rn < A.relax_top_cap) Q.st_rtop(rn, ent);
-              else A.relax[rn - A.relax_top_cap] = ent;
-              ++rn;
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t lh = qs[i].x & 0xFFFFu, j = qs[i].x >> 16, cc = qs[i].y & 0xFFFFu;
+              if (j == cc && lh + cc + x < M + 2u) {          // :198-199 (on the path: bit 15 of j) + early :195
+                if (rn >= A.relax_cap + A.relax_top_cap) { status = kEnumOverflow; goto done; }
+                const uint32_t ent = (x << 16) | ws[i];
+                if (rn < A.relax_top_cap) Q.st_rtop(rn, ent);
+                else A.relax[rn - A.relax_top_cap] = ent;
+                ++rn;
+              }
             }
-          }
-          bool acted = false;
-          while (rn && !acted) {
-            --rn;
-            const uint32_t r = rn < A.relax_top_cap ? Q.ld_rtop(rn) : A.relax[rn - A.relax_top_cap];
-            const int rx = (int)(r >> 16);
-            const uint32_t u = r & 0xFFFFu;
-            const HotReg hu = Q.ld_hot(u);
-            if (hu.j() == hu.c() && hu.a() + hu.c() < M - rx + 1) {  // :195-196 at n_c, true for the whole chain
-              Q.st_hot_state(u, (uint32_t)(M - rx + 1 - hu.c()) | ((uint32_t)hu.c() << 16), hu.cf);
-              expansions += (uint32_t)hu.c();                 // _GetIncomings per node, :197
-              ins = Q.ld_in(u);
-              x = rx + hu.c();
-              acted = true;
+            bool acted = false;
+            while (rn && !acted) {
+              --rn;
+              ++relax_pops;
+              const uint32_t r = rn < A.relax_top_cap ? Q.ld_rtop(rn) : A.relax[rn - A.relax_top_cap];
+              const uint32_t rx = r >> 16, u = r & 0xFFFFu;
+              const Rec4 hu = Q.ld_hot(u);
+              const uint32_t lh = hu.x & 0xFFFFu, j = hu.x >> 16, cc = hu.y & 0xFFFFu;
+              if (j == cc && lh + cc + rx < M + 2u) {         // :195-196 at n_c, true for the whole chain
+                Q.st_hot_w0(u, (M + 2u - rx - cc) | (cc << 16));  // lock[n_i] = M - rx + 1 - (c - i)
+                expansions += cc;                             // _GetIncomings per node, :197
+                Q.ld_in(u, in_lo, in_hi);
+                x = rx + cc;
+                acted = true;
+              }
             }
+            if (!acted) break;
           }
-          if (!acted) break;
         }
       }
     }
   }
 done:
+  if (steps > max_steps) steps = max_steps + 1;
   R.status = status;
   R.n_cycles = n_cycles;
   R.n_nodes = n_out;
   R.steps = (uint32_t)steps;
   R.expansions = expansions;
   S.n_staged = n_staged;
+  S.iters = iters;
+  S.relax_pops = relax_pops;
   return true;
 }
 

@@ -3,15 +3,21 @@
 //
 // The reference processes start nodes one after another: a start already marked visited is
 // skipped (:476), a search sees every node marked by the searches before it (:217-222).  Here the
-// loop is a persistent-kernel pipeline with an ORDERED COMMIT:
+// loop is a persistent-kernel pipeline that commits IN TICKET ORDER WHERE ORDER MATTERS:
 //   * worker warps pull tickets (= positions in the start list) from an atomic counter, so the
 //     start nodes in flight are always a contiguous window of the sequential order;
 //   * a worker searches its start immediately, reading the live `visited` bitmap: the warp extracts
-//     the ball the search can touch (parallel BFS, ball_dev.cuh), lane 0 runs the sequential search
-//     on the dense ball records;
-//   * workers commit strictly in ticket order (commit_idx hand-over).  `visited` is only ever
-//     marked inside a commit, so every mark a search sees belongs to a start that precedes it in the
-//     sequential order.  At its turn the worker knows the exact bitmap of its position:
+//     the ball the search can touch (parallel BFS, ball_dev.cuh) — everything a search reads or marks
+//     lies inside it — claims its nodes (owner[x] = min ticket, atomicMin) and publishes "built";
+//     lane 0 then runs the sequential search on the contracted ball;
+//   * once every earlier ticket has published its ball (built front), the ticket knows whether any
+//     EARLIER ticket's ball overlaps its own (min owner over its ball).  Two searches with disjoint
+//     balls commute: neither reads what the other marks.  A ticket that no earlier ball overlaps is
+//     INDEPENDENT: nothing that happens before it in the sequential order can touch its ball, later
+//     tickets that overlap it see its claim and wait for it, so its speculative result is already the
+//     sequential one and it commits at once, out of order (marks its cycles' nodes, :217-222);
+//   * every other ticket is DEPENDENT and commits at its turn (commit front == ticket: all earlier
+//     tickets are done), when it knows the exact bitmap of its position:
 //       visited[start] now                      -> skipped, like :476
 //       a node the search ACCEPTED is marked now -> the search saw a stale bitmap: it is re-run
 //                                                   on the spot (exclusive, hence exact)
@@ -19,7 +25,9 @@
 //                                                   nodes are marked (:217-222), results appended
 //     ("accepted" = the nodes of the extracted ball; nodes rejected for being visited stay rejected
 //     under a superset, the other tests of _BackgroundCheck ignore `visited`);
-//   * a running search polls visited[start] and gives up as soon as an earlier commit marks it.
+//   * marks are only ever made by commits, and a commit never marks a node of an unfinished earlier
+//     ticket's ball that it does not overlap — so a ticket that sees its own START marked, at any time,
+//     is skipped for good (the marker precedes it in the order) and gives up at once.
 // The committed sequence is identical to the reference's threads=1 loop for any number of workers.
 #include <algorithm>
 
@@ -84,6 +92,8 @@ struct TicketRec {
   uint32_t us_searched, us_committed;  // microseconds since the worker entered the kernel
   uint32_t n_ball, us_build;           // size of the last extracted ball and the time its extraction took
   uint32_t n_chains;                   // records of its contraction
+  uint32_t iters, relax_pops;          // of the last search: loop iterations on the contracted ball, relaxation entries
+  uint32_t us_started, n_restarts;     // when the last search of this ticket began; searches started for it
 };
 struct PipeCtl {
   uint32_t ticket;       // next ticket to hand out
@@ -94,8 +104,19 @@ struct PipeCtl {
   uint32_t n_reruns;
   uint32_t n_abandoned;  // searches given up because their start got marked
   uint32_t mark_epoch;   // number of commits that marked nodes so far (waiting workers re-check on change)
+  uint32_t built_idx;    // tickets [first, built_idx) have extracted and claimed their ball (or need none)
+  uint32_t ooo_limit;    // tickets beyond this one must commit in order (an earlier ball could not be claimed in full)
+  uint32_t n_ooo;        // commits made out of order (independent tickets)
   unsigned long long searches_run;
 };
+// advances a front (commit_idx / built_idx) over every ticket whose flag is set (lane 0 of any worker)
+__device__ __forceinline__ void advance_front(uint32_t *front, const uint32_t *flags, uint32_t n_end) {
+  for (;;) {
+    const uint32_t f = *(volatile uint32_t *)front;
+    if (f >= n_end || !*(const volatile uint32_t *)&flags[f]) break;
+    atomicCAS(front, f, f + 1);
+  }
+}
 
 __device__ __forceinline__ uint32_t ld_vol(const uint32_t *p) { return *(const volatile uint32_t *)p; }
 
@@ -213,7 +234,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_solo(GraphView g, 
         status = __shfl_sync(0xffffffffu, R.status, 0);
       }
     }
-    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0, 0, 0, 0};
+    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0, 0, 0, 0, 0, 0, 0, 0};
     if (!skip && !stopped) {
       const uint32_t n_nodes = __shfl_sync(0xffffffffu, R.n_nodes, 0);
       const uint32_t n_cycles = __shfl_sync(0xffffffffu, R.n_cycles, 0);
@@ -294,8 +315,8 @@ static BallLayout make_ball_layout(int max_len, uint32_t index_log, uint32_t sme
   L.off_ckeys = o; o = align_up(o + (size_t)L.node_cap * 4, 128);
   L.off_soff = o; o = align_up(o + (size_t)(L.node_cap + 1) * 2, 128);
   L.off_shead = o; o = align_up(o + (size_t)L.node_cap * 2, 128);
-  L.off_shot = o; o = align_up(o + (size_t)L.node_cap * sizeof(SHot), 128);
-  L.off_sin = o; o = align_up(o + (size_t)L.node_cap * 8, 128);
+  L.off_shot = o; o = align_up(o + (size_t)(L.node_cap + 1) * sizeof(SHot), 128);
+  L.off_sin = o; o = align_up(o + (size_t)(L.node_cap + 1) * 8, 128);
   L.off_lvl = o; o = align_up(o + (size_t)L.depth_cap * sizeof(Lvl), 128);
   L.bytes = align_up(o, 128);
   const uint32_t lvl_bytes = (uint32_t)align_up((size_t)L.depth_cap * sizeof(Lvl), 16);
@@ -335,8 +356,10 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
                                                      const uint32_t *__restrict__ starts, uint32_t n_end, int min_len,
                                                      int max_len, uint8_t *arena, BallLayout L, PipeCtl *ctl,
                                                      TicketRec *recs, uint32_t *pool_nodes, uint32_t pool_nodes_cap,
-                                                     uint32_t *pool_len, uint32_t pool_len_cap, int force_global) {
+                                                     uint32_t *pool_len, uint32_t pool_len_cap, uint32_t *owner,
+                                                     uint32_t *built, uint32_t *done, int flags) {
   extern __shared__ __align__(16) uint8_t smem_all[];
+  constexpr unsigned kFull = 0xffffffffu;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t worker = blockIdx.x * kWarpsPerBlock + warp;
   uint8_t *const my_smem = smem_all + (size_t)warp * L.smem_bytes;
@@ -349,26 +372,53 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
   Bs.cap = L.chain_cap;
   Bg.hot = (SHot *)(arena + (size_t)worker * L.bytes + L.off_shot);
   Bg.in4 = (uint64_t *)(arena + (size_t)worker * L.bytes + L.off_sin);
-  Bg.cap = L.node_cap;
+  Bg.cap = L.node_cap + 1;
   Bs.n = Bg.n = 0;
-  uint32_t n_chains = 0;
   Coop co;
   co.lane = lane;
   unsigned long long searches = 0;
-  uint32_t abandoned = 0, reruns = 0;
+  uint32_t abandoned = 0, reruns = 0, n_ooo = 0;
   uint32_t live = 0;  // ball nodes whose index slots are still occupied
   const unsigned long long t_kernel = gtime_ns();
   for (;;) {
     uint32_t t = 0;
     if (lane == 0) t = atomicAdd(&ctl->ticket, 1u);
-    t = __shfl_sync(0xffffffffu, t, 0);
-    if (t >= n_end || __shfl_sync(0xffffffffu, ld_vol(&ctl->stop), 0)) break;
+    t = __shfl_sync(kFull, t, 0);
+    if (t >= n_end || __shfl_sync(kFull, ld_vol(&ctl->stop), 0)) break;
+    if (__shfl_sync(kFull, ld_vol(&done[t]), 0)) {  // committed by an earlier launch of this call
+      if (lane == 0) advance_front(&ctl->commit_idx, done, n_end);
+      continue;
+    }
     const uint32_t s = starts[t];
     EnumResult R;
     R.status = kEnumSkipped;
     R.n_cycles = R.n_nodes = R.n_keys = R.steps = R.expansions = 0;
     int stopped = 0;
-    uint32_t us_build = 0;
+    uint32_t us_build = 0, t_iters = 0, t_relax = 0, us_started = 0, t_searches = 0, n_chains = 0;
+    bool claimed = false;  // this ticket's first ball has been claimed and "built" published
+    auto publish_built = [&]() {
+      if (claimed) return;
+      claimed = true;
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence();
+        atomicExch(&built[t], 1u);
+        fence_sc();
+        advance_front(&ctl->built_idx, built, n_end);
+      }
+    };
+    // the ticket is finished (committed or skipped): record, flag, move the commit front
+    auto finish = [&](const TicketRec &rec) {
+      __syncwarp();
+      if (lane == 0) {
+        recs[t] = rec;
+        __threadfence();
+        if (rec.n_nodes) atomicAdd(&ctl->mark_epoch, 1u);  // after the fence: the marks are visible first
+        atomicExch(&done[t], 1u);
+        fence_sc();
+        advance_front(&ctl->commit_idx, done, n_end);
+      }
+    };
     // does the search rest on a node that has been marked since its ball was built? (warp-cooperative)
     auto stale = [&](uint32_t n_keys) {
       int conflict = 0;
@@ -376,31 +426,46 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
         uint32_t k = A.nodes[j].key;
         if (k != s && visited_live(visited, k)) conflict = 1;
       }
-      return __any_sync(0xffffffffu, conflict) != 0;
+      return __any_sync(kFull, conflict) != 0;
     };
-    // Speculative search against the live bitmap (all lanes call it): the warp extracts the ball, lane 0
-    // searches it in slices of kSliceSteps steps.  Between slices the warp polls: pipeline draining ->
-    // stop; start marked by an earlier commit -> the ticket will be skipped (:476), give up; the mark
-    // epoch moved and a ball node is marked now -> the search is stale, start over at once instead
-    // of finishing a search whose result would be thrown away.  `exclusive` (at the ticket's turn:
-    // the bitmap is final) runs to the end without polling.
+    // Speculative search against the live bitmap (all lanes call it): the warp extracts the ball (and, the first
+    // time, claims it), lane 0 searches its contraction in slices of kSliceSteps chain steps.  Between slices the
+    // warp polls: pipeline draining -> stop; start marked by an earlier commit -> the ticket is skipped (:476),
+    // give up; the mark epoch moved and a ball node is marked now -> the search is stale, start over at once
+    // instead of finishing a search whose result would be thrown away.  `exclusive` (at the ticket's turn: the
+    // bitmap is final) runs to the end without polling.
     uint32_t epoch_checked = 0xFFFFFFFFu;  // `visited` as of this epoch is accounted for in R
     auto speculate = [&](bool exclusive) {
       for (;;) {
         ++searches;
-        epoch_checked = __shfl_sync(0xffffffffu, ld_vol(&ctl->mark_epoch), 0);
+        ++t_searches;
+        epoch_checked = __shfl_sync(kFull, ld_vol(&ctl->mark_epoch), 0);
         const unsigned long long t_build = gtime_ns();
+        us_started = (uint32_t)((t_build - t_kernel) / 1000);
         ball_clear(A, live, co);
         const int st = ball_build(g, adj, visited, s, max_len, A, live, co);
-        us_build = (uint32_t)((gtime_ns() - t_build) / 1000);
         R.status = st;
         R.n_cycles = R.n_nodes = R.steps = R.expansions = 0;
         R.n_keys = live;
+        if (!claimed) {
+          // claim the ball: owner[x] = smallest ticket whose ball holds x.  A ball that did not fit is claimed only in
+          // part, so no later ticket may conclude that it is independent of this one: they all commit in order.
+          if (st != kEnumDone) {
+            if (lane == 0) atomicMin(&ctl->ooo_limit, t);
+          } else {
+            for (uint32_t j = lane; j < live; j += 32) atomicMin(&owner[A.nodes[j].key], t);
+          }
+          publish_built();
+        }
+        us_build = (uint32_t)((gtime_ns() - t_build) / 1000);
         if (st != kEnumDone) break;
         // contract the ball (unary chains become single records) and search it
-        bool in_smem = !force_global;
-        if (in_smem) in_smem = sball_contract(A, live, Bs, co) == kEnumDone;
-        if (!in_smem) sball_contract(A, live, Bg, co);
+        bool in_smem = !(flags & 1);
+        if (in_smem) in_smem = sball_contract(A, live, max_len, Bs, co) == kEnumDone;
+        if (!in_smem && sball_contract(A, live, max_len, Bg, co) != kEnumDone) {
+          R.status = kEnumOverflow;  // 65535 chains: left to the hash-map search
+          break;
+        }
         const SBall &B = in_smem ? Bs : Bg;
         n_chains = B.n;
         SDfsState ds;
@@ -419,16 +484,16 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
               fin = sball_dfs(min_len, max_len, A, Q, ds, budget, R) ? 1 : 0;
             }
           }
-          if (__shfl_sync(0xffffffffu, fin, 0)) break;
+          if (__shfl_sync(kFull, fin, 0)) break;
           uint32_t c_stop = 0, c_vis = 0, c_ep = 0;
           if (lane == 0) {
             c_stop = ld_vol(&ctl->stop);
             c_vis = visited_live(visited, s);
             c_ep = ld_vol(&ctl->mark_epoch);
           }
-          c_stop = __shfl_sync(0xffffffffu, c_stop, 0);
-          c_vis = __shfl_sync(0xffffffffu, c_vis, 0);
-          c_ep = __shfl_sync(0xffffffffu, c_ep, 0);
+          c_stop = __shfl_sync(kFull, c_stop, 0);
+          c_vis = __shfl_sync(kFull, c_vis, 0);
+          c_ep = __shfl_sync(kFull, c_ep, 0);
           if (c_stop | c_vis) {
             if (c_stop) stopped = 1;
             else ++abandoned;
@@ -446,23 +511,114 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
         if (restart) { ++reruns; continue; }
         __syncwarp();  // lane 0's writes (staged cycles) are visible to the warp
         // item ids of the staged cycles, so that the commit only has to stream them
-        const int fst = __shfl_sync(0xffffffffu, R.status, 0);
-        const uint32_t n_staged = __shfl_sync(0xffffffffu, ds.n_staged, 0);
+        const int fst = __shfl_sync(kFull, R.status, 0);
+        const uint32_t n_staged = __shfl_sync(kFull, ds.n_staged, 0);
+        t_iters = __shfl_sync(kFull, ds.iters, 0);
+        t_relax = __shfl_sync(kFull, ds.relax_pops, 0);
         if (fst == kEnumDone || fst == kEnumCap) sball_expand(A, B, n_staged, cyc_keys, co);
         break;
       }
       __syncwarp();
     };
-    // a ticket whose start is already marked is skipped for good (:476); the committing worker ahead
-    // consumes such tickets itself (below), so this worker just moves on
-    if (__shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0) == 0) speculate(false);
+    TicketRec rec = {kFateSkipped, kEnumSkipped, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    // a ticket whose start is already marked is skipped for good (:476)
+    if (__shfl_sync(kFull, (int)visited_live(visited, s), 0)) {
+      publish_built();
+      finish(rec);
+      continue;
+    }
+    speculate(false);
     const uint32_t us_searched = (uint32_t)((gtime_ns() - t_kernel) / 1000);
-    // ---- wait for this ticket's turn; meanwhile keep the speculative result fresh, so that the
+    // marks the cycles' nodes (:217-222), reserves the output range and writes results[start] = cycles (:479);
+    // returns false when the output pools are full (the pipeline drains and the host enlarges them)
+    auto commit = [&](int status) -> bool {
+      const uint32_t n_nodes = __shfl_sync(kFull, R.n_nodes, 0), n_cycles = __shfl_sync(kFull, R.n_cycles, 0);
+      uint32_t node_base = 0, cyc_base = 0;
+      int full = 0;
+      if (lane == 0) {
+        node_base = atomicAdd(&ctl->pool_nodes, n_nodes);
+        cyc_base = atomicAdd(&ctl->pool_cycles, n_cycles);
+        if ((uint64_t)node_base + n_nodes > pool_nodes_cap || (uint64_t)cyc_base + n_cycles > pool_len_cap) {
+          atomicSub(&ctl->pool_nodes, n_nodes);
+          atomicSub(&ctl->pool_cycles, n_cycles);
+          full = 1;
+        }
+      }
+      if (__shfl_sync(kFull, full, 0)) return false;
+      node_base = __shfl_sync(kFull, node_base, 0);
+      cyc_base = __shfl_sync(kFull, cyc_base, 0);
+      for (uint32_t j = lane; j < n_nodes; j += 32) {
+        const uint32_t x = cyc_keys[j];
+        atomicOr(&visited[x >> 5], 1u << (x & 31));
+        pool_nodes[node_base + j] = x;
+      }
+      for (uint32_t j = lane; j < n_cycles; j += 32) pool_len[cyc_base + j] = A.cyc_noff[j + 1] - A.cyc_noff[j];
+      rec.fate = kFateAccepted;
+      rec.status = status;
+      rec.n_cycles = n_cycles;
+      rec.n_nodes = n_nodes;
+      rec.cyc_base = cyc_base;
+      rec.node_base = node_base;
+      rec.expansions = __shfl_sync(kFull, R.expansions, 0);
+      rec.steps = __shfl_sync(kFull, R.steps, 0);
+      rec.us_searched = us_searched;
+      rec.us_committed = (uint32_t)((gtime_ns() - t_kernel) / 1000);
+      rec.n_ball = live;
+      rec.us_build = us_build;
+      rec.n_chains = n_chains;
+      rec.iters = t_iters;
+      rec.relax_pops = t_relax;
+      rec.us_started = us_started;
+      rec.n_restarts = t_searches;
+      return true;
+    };
+    stopped = __shfl_sync(kFull, stopped, 0);
+    if (stopped) break;
+    int status = __shfl_sync(kFull, R.status, 0);
+    if (status == kEnumSkipped) {  // the start got marked while the search ran
+      finish(rec);
+      continue;
+    }
+    // ---- every earlier ticket has claimed its ball?  Then the owners of this ball's nodes tell whether one of them
+    //      overlaps it.
+    for (;;) {
+      uint32_t bi = 0, st = 0;
+      if (lane == 0) {
+        bi = ld_vol(&ctl->built_idx);
+        st = ld_vol(&ctl->stop);
+      }
+      bi = __shfl_sync(kFull, bi, 0);
+      st = __shfl_sync(kFull, st, 0);
+      if (st) { stopped = 1; break; }
+      if (bi > t) break;
+      __nanosleep(200u);
+    }
+    if (stopped) break;
+    bool independent = false;
+    if (status != kEnumOverflow && !(flags & 4)) {
+      __threadfence();
+      uint32_t mn = 0xFFFFFFFFu;
+      for (uint32_t j = lane; j < live; j += 32) mn = min(mn, ld_cg32(&owner[A.nodes[j].key]));
+      for (int d = 16; d; d >>= 1) mn = min(mn, __shfl_xor_sync(kFull, mn, d));
+      independent = mn >= t && t < __shfl_sync(kFull, ld_vol(&ctl->ooo_limit), 0);
+    }
+    if (independent) {
+      // no earlier ticket can read or mark a node of this ball and later ones wait for this commit: the result is
+      // the one of the sequential order
+      if (!commit(status)) {
+        if (lane == 0) atomicExch(&ctl->stop, 2u);
+        break;
+      }
+      ++n_ooo;
+      finish(rec);
+      continue;
+    }
+    // ---- dependent: wait for this ticket's turn; meanwhile keep the speculative result fresh, so that the
     //      repeat of a stale search happens here, in parallel, and not inside the ordered commit.
     //      `visited` only changes inside commits that mark nodes (mark_epoch), so the result is
     //      re-examined only when the epoch has moved; the poll itself is one 32-byte sector and backs
     //      off with the distance to the commit front, so waiting workers leave the L2 to the searches.
-    bool consumed = false;
+    bool skipped_now = false;
     for (;;) {
       uint32_t ci = 0, ep = 0;
       int st = stopped;
@@ -471,112 +627,58 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
         ep = ld_vol(&ctl->mark_epoch);
         st |= (int)ld_vol(&ctl->stop);
       }
-      ci = __shfl_sync(0xffffffffu, ci, 0);
-      ep = __shfl_sync(0xffffffffu, ep, 0);
-      st = __shfl_sync(0xffffffffu, st, 0);
+      ci = __shfl_sync(kFull, ci, 0);
+      ep = __shfl_sync(kFull, ep, 0);
+      st = __shfl_sync(kFull, st, 0);
       if (st) { stopped = 1; break; }
       if (ci == t) break;
-      if ((int32_t)(ci - t) > 0) { consumed = true; break; }  // skipped on our behalf by an earlier commit
-      const int status = __shfl_sync(0xffffffffu, R.status, 0);
-      if (ep != epoch_checked && status != kEnumSkipped && status != kEnumOverflow) {
+      status = __shfl_sync(kFull, R.status, 0);
+      if (ep != epoch_checked && status != kEnumOverflow) {
         epoch_checked = ep;  // marks made after this read are caught by the next epoch change
         __threadfence();
-        if (__shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0)) {
-          R.status = kEnumSkipped;  // an earlier start's cycles cover this one: it will be skipped
-        } else if (stale(__shfl_sync(0xffffffffu, R.n_keys, 0))) {
+        if (__shfl_sync(kFull, (int)visited_live(visited, s), 0)) {
+          skipped_now = true;  // an earlier start's cycles cover this one: skipped (:476)
+          break;
+        }
+        if (stale(__shfl_sync(kFull, R.n_keys, 0))) {
           speculate(false);
           ++reruns;
+          if (__shfl_sync(kFull, stopped, 0)) { stopped = 1; break; }
+          if (__shfl_sync(kFull, R.status, 0) == kEnumSkipped) { skipped_now = true; break; }
           continue;
         }
       }
       const uint32_t dist = t - ci;
       __nanosleep(dist <= 2 ? 100u : (dist < 100 ? dist * 200u : 20000u));
     }
-    stopped = __shfl_sync(0xffffffffu, stopped, 0);
+    stopped = __shfl_sync(kFull, stopped, 0);
     if (stopped) break;
-    if (consumed) continue;
+    if (skipped_now) {
+      finish(rec);
+      continue;
+    }
     __threadfence();  // everything committed before this turn is visible from here on
     // ---- ordered commit: the bitmap is now exactly the one of position t in the sequential loop
-    int status = __shfl_sync(0xffffffffu, R.status, 0);
-    const bool skip = __shfl_sync(0xffffffffu, (int)visited_live(visited, s), 0) != 0;  // :476
+    status = __shfl_sync(kFull, R.status, 0);
+    const bool skip = __shfl_sync(kFull, (int)visited_live(visited, s), 0) != 0;  // :476
     if (!skip) {
       // Nothing has been marked since the result was last examined (same epoch) -> it is exact.  Else
-      // re-examine it; a stale (or, impossible, abandoned) result is repeated exclusively.
-      const uint32_t ep_now = __shfl_sync(0xffffffffu, ld_vol(&ctl->mark_epoch), 0);
+      // re-examine it; a stale result is repeated exclusively.
+      const uint32_t ep_now = __shfl_sync(kFull, ld_vol(&ctl->mark_epoch), 0);
       while (status != kEnumOverflow &&
-             (status == kEnumSkipped || (ep_now != epoch_checked && stale(__shfl_sync(0xffffffffu, R.n_keys, 0))))) {
+             (status == kEnumSkipped || (ep_now != epoch_checked && stale(__shfl_sync(kFull, R.n_keys, 0))))) {
         speculate(true);  // exclusive repeat against the final bitmap (sets epoch_checked = ep_now)
         ++reruns;
-        status = __shfl_sync(0xffffffffu, R.status, 0);
+        status = __shfl_sync(kFull, R.status, 0);
       }
       if (status == kEnumOverflow) stopped = 1;
-    }
-    TicketRec rec = {kFateSkipped, status, 0, 0, 0, 0, 0, 0, us_searched, 0, live, us_build, n_chains};
-    uint32_t n_nodes = 0, n_cycles = 0, node_base = 0, cyc_base = 0;
-    if (!skip && !stopped) {
-      n_nodes = __shfl_sync(0xffffffffu, R.n_nodes, 0);
-      n_cycles = __shfl_sync(0xffffffffu, R.n_cycles, 0);
-      node_base = ld_vol(&ctl->pool_nodes);
-      cyc_base = ld_vol(&ctl->pool_cycles);
-      if ((uint64_t)node_base + n_nodes > pool_nodes_cap || (uint64_t)cyc_base + n_cycles > pool_len_cap) {
-        stopped = 2;
-      } else {
-        // :217-222 — only the marks and the reservation of the output range are on the hand-over path;
-        // the cycles themselves are copied out after the next ticket has been given its turn
-        for (uint32_t j = lane; j < n_nodes; j += 32) {
-          const uint32_t x = cyc_keys[j];
-          atomicOr(&visited[x >> 5], 1u << (x & 31));
-        }
-        rec.fate = kFateAccepted;
-        rec.n_cycles = n_cycles;
-        rec.n_nodes = n_nodes;
-        rec.cyc_base = cyc_base;
-        rec.node_base = node_base;
-        rec.expansions = __shfl_sync(0xffffffffu, R.expansions, 0);
-        rec.steps = __shfl_sync(0xffffffffu, R.steps, 0);
-        if (lane == 0) {
-          ctl->pool_nodes = node_base + n_nodes;
-          ctl->pool_cycles = cyc_base + n_cycles;
-        }
-      }
+      else if (!commit(status)) stopped = 2;
     }
     if (stopped) {  // this ticket needs the host (hash-map search in a large arena / larger pool): drain
       if (lane == 0) atomicExch(&ctl->stop, (uint32_t)stopped);
       break;
     }
-    __threadfence();
-    __syncwarp();
-    // The bitmap is now the exact one for ticket t + 1, t + 2, ... as long as those are skipped:
-    // consume every directly following ticket whose start is marked (:476), 32 at a time, so that
-    // runs of covered start nodes cost one hand-over instead of one each.
-    uint32_t next = t + 1;
-    for (;;) {
-      const uint32_t c = next + (uint32_t)lane;
-      const bool sk = c < n_end && visited_live(visited, starts[c]);
-      const unsigned m = __ballot_sync(0xffffffffu, sk);
-      const int run = m == 0xffffffffu ? 32 : __ffs((int)~m) - 1;
-      if (lane < run) {
-        const TicketRec skipped = {kFateSkipped, kEnumSkipped, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-        recs[c] = skipped;
-      }
-      next += (uint32_t)run;
-      if (run < 32) break;
-    }
-    __threadfence();
-    __syncwarp();
-    if (lane == 0) {
-      if (rec.n_nodes) atomicAdd(&ctl->mark_epoch, 1u);  // after the fence: the marks are visible first
-      atomicExch(&ctl->commit_idx, next);                // hand over
-    }
-    // ---- off the hand-over path: results[start] = cycles (:479)
-    if (rec.fate == kFateAccepted) {
-      for (uint32_t j = lane; j < n_nodes; j += 32) pool_nodes[node_base + j] = cyc_keys[j];
-      for (uint32_t j = lane; j < n_cycles; j += 32) pool_len[cyc_base + j] = A.cyc_noff[j + 1] - A.cyc_noff[j];
-    }
-    if (lane == 0) {
-      rec.us_committed = (uint32_t)((gtime_ns() - t_kernel) / 1000);
-      recs[t] = rec;
-    }
+    finish(rec);
   }
   __syncwarp();
   ball_clear(A, live, co);  // the index is left empty for the next launch
@@ -584,6 +686,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     if (searches) atomicAdd(&ctl->searches_run, searches);
     if (abandoned) atomicAdd(&ctl->n_abandoned, abandoned);
     if (reruns) atomicAdd(&ctl->n_reruns, reruns);
+    if (n_ooo) atomicAdd(&ctl->n_ooo, n_ooo);
   }
 }
 
@@ -631,11 +734,18 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
   PipeCtl ctl;
   memset(&ctl, 0, sizeof ctl);
   if (n) {
-    DevBuf starts_dev, ctl_dev, recs_dev, pool_nodes, pool_len, big_arena;
+    DevBuf starts_dev, ctl_dev, recs_dev, pool_nodes, pool_len, big_arena, owner, flags_dev;
     MG_TRY(starts_dev.alloc(n * 4));
     MG_CUDA(cudaMemcpyAsync(starts_dev.p, s32.data(), n * 4, cudaMemcpyHostToDevice, s));
     MG_TRY(ctl_dev.alloc(sizeof(PipeCtl)));
     MG_TRY(recs_dev.alloc(n * sizeof(TicketRec)));
+    // ball claims (smallest ticket whose ball holds the item) and the per-ticket built / done flags
+    MG_TRY(owner.alloc((size_t)g->view.n * 4));
+    MG_CUDA(cudaMemsetAsync(owner.p, 0xFF, (size_t)g->view.n * 4, s));
+    MG_TRY(flags_dev.alloc(n * 8));
+    MG_CUDA(cudaMemsetAsync(flags_dev.p, 0, n * 8, s));
+    uint32_t *built_dev = flags_dev.as<uint32_t>(), *done_dev = built_dev + n;
+    ctl.ooo_limit = 0xFFFFFFFFu;
     uint32_t nodes_cap = 1u << 22, len_cap = 1u << 18;
     MG_TRY(pool_nodes.alloc((size_t)nodes_cap * 4));
     MG_TRY(pool_len.alloc((size_t)len_cap * 4));
@@ -651,7 +761,8 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
         std::min<uint32_t>(std::min<uint32_t>(smem_per_block, (uint32_t)g->smem_per_block_optin) / kWarpsPerBlock / 16 * 16,
                            env_u32("MCAAT_ENUM_SMEM_PER_WORKER", 1u << 20, 2048, 1u << 20));
     const BallLayout L = make_ball_layout(max_len, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 17), smem_per_worker);
-    const int force_global = (int)env_u32("MCAAT_ENUM_CHAINS_GLOBAL", 0, 0, 1);
+    // diagnostics: chain records in the arena instead of shared memory (1); every commit in ticket order (4)
+    const int force_global = (int)(env_u32("MCAAT_ENUM_CHAINS_GLOBAL", 0, 0, 1) | (env_u32("MCAAT_ENUM_INORDER", 0, 0, 1) << 2));
     MG_CUDA(cudaFuncSetAttribute(k_enum_pipeline, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(L.smem_bytes * kWarpsPerBlock)));
     const uint64_t sig = ((uint64_t)L.bytes << 20) ^ ((uint64_t)L.index_log << 8) ^ (uint64_t)workers;
     if (g->enum_arena.bytes < (size_t)workers * L.bytes || g->enum_arena_sig != sig) {
@@ -666,6 +777,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     while (pos < n) {
       ctl.ticket = pos;
       ctl.commit_idx = pos;
+      ctl.built_idx = pos;
       ctl.stop = 0;
       MG_CUDA(cudaMemcpyAsync(ctl_dev.p, &ctl, sizeof ctl, cudaMemcpyHostToDevice, s));
       {
@@ -674,7 +786,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
           MG_LAUNCH(k_enum_pipeline, blocks, 32 * kWarpsPerBlock, L.smem_bytes * kWarpsPerBlock, s, g->view, g->adj.as<uint64_t>(), g->visited.as<uint32_t>(),
                     starts_dev.as<uint32_t>(), (uint32_t)n, min_len, max_len, g->enum_arena.as<uint8_t>(), L,
                     ctl_dev.as<PipeCtl>(), recs_dev.as<TicketRec>(), pool_nodes.as<uint32_t>(), nodes_cap,
-                    pool_len.as<uint32_t>(), len_cap, force_global);
+                    pool_len.as<uint32_t>(), len_cap, owner.as<uint32_t>(), built_dev, done_dev, force_global);
         } else {
           const SlotLayout LB = make_layout(max_len, big_lock_log, big_relax, kClusterBound);
           MG_CUDA(cudaFuncSetAttribute(k_enum_solo, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LB.smem_bytes));
@@ -691,6 +803,10 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
       MG_CUDA(cudaMemcpyAsync(&ctl, ctl_dev.p, sizeof ctl, cudaMemcpyDeviceToHost, s));
       MG_CUDA(cudaStreamSynchronize(s));
       ++out->n_rounds;
+      if (solo && ctl.commit_idx == pos + 1) {  // the ticket is done: flag it for the pipeline launches that follow
+        MG_CUDA(cudaMemsetAsync(built_dev + pos, 1, 4, s));
+        MG_CUDA(cudaMemsetAsync(done_dev + pos, 1, 4, s));
+      }
       pos = ctl.commit_idx;
       if (ctl.stop == 2) {  // output pools full: double them and resume at `pos`
         if ((uint64_t)nodes_cap * 2 > 0xFFFFFFF0ull) {
@@ -725,10 +841,11 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
   flush_timers(g);
   if (const char *trace = getenv("MCAAT_ENUM_TRACE")) {  // per-ticket timeline for profiling
     if (FILE *f = fopen(trace, "w")) {
-      fprintf(f, "ticket,fate,status,steps,n_cycles,us_searched,us_committed,n_ball,us_build,n_chains\n");
+      fprintf(f, "ticket,fate,status,steps,n_cycles,us_searched,us_committed,n_ball,us_build,n_chains,iters,relax_pops,us_started,n_searches\n");
       for (uint64_t i = 0; i < n; ++i)
-        fprintf(f, "%llu,%d,%d,%u,%u,%u,%u,%u,%u,%u\n", (unsigned long long)i, recs[i].fate, recs[i].status, recs[i].steps,
-                recs[i].n_cycles, recs[i].us_searched, recs[i].us_committed, recs[i].n_ball, recs[i].us_build, recs[i].n_chains);
+        fprintf(f, "%llu,%d,%d,%u,%u,%u,%u,%u,%u,%u,%u,%u,%u,%u\n", (unsigned long long)i, recs[i].fate, recs[i].status, recs[i].steps,
+                recs[i].n_cycles, recs[i].us_searched, recs[i].us_committed, recs[i].n_ball, recs[i].us_build, recs[i].n_chains,
+                recs[i].iters, recs[i].relax_pops, recs[i].us_started, recs[i].n_restarts);
       fclose(f);
     }
   }
@@ -767,6 +884,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
   out->n_reruns = ctl.n_reruns;
   out->n_searches_run = ctl.searches_run;
   out->n_abandoned = ctl.n_abandoned;
+  out->n_out_of_order = ctl.n_ooo;
   return MG_OK;
 }
 

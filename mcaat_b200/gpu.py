@@ -73,7 +73,8 @@ class Cycles(C.Structure):
     _fields_ = [("n_searched", C.c_uint64), ("searched_start", u64p), ("cyc_off", u64p), ("n_cycles", C.c_uint64),
                 ("node_off", u64p), ("nodes", u64p), ("n_skipped", C.c_uint64), ("n_bound_hits", C.c_uint64),
                 ("n_cap_hits", C.c_uint64), ("n_reruns", C.c_uint64), ("n_rounds", C.c_uint64),
-                ("n_searches_run", C.c_uint64), ("n_abandoned", C.c_uint64), ("expansions", C.c_uint64)]
+                ("n_searches_run", C.c_uint64), ("n_abandoned", C.c_uint64), ("expansions", C.c_uint64),
+                ("n_out_of_order", C.c_uint64)]
 
 
 _lib = None
@@ -360,7 +361,7 @@ class DeviceGraph:
             searched.append((int(ss[i]), [nodes[int(noff[j]):int(noff[j + 1])]
                                           for j in range(int(coff[i]), int(coff[i + 1]))]))
         stats = {k: int(getattr(c, k)) for k in ("n_searched", "n_cycles", "n_skipped", "n_bound_hits", "n_cap_hits",
-                                                  "n_reruns", "n_rounds", "n_searches_run", "n_abandoned", "expansions")}
+                                                  "n_reruns", "n_rounds", "n_searches_run", "n_abandoned", "expansions", "n_out_of_order")}
         lib().mg_cycles_free(C.byref(c))
         return searched, stats
 

@@ -393,12 +393,12 @@ struct BallSlot {
     A.cyc_off = cyc_off.data();
     spos.resize(cap); ckeys.resize(cap); soff.resize(cap + 1); shead.resize(cap); cyc_pos.resize(cyc.size());
     cyc_noff.resize(kClusterBound + 1); flat.resize(cyc.size());
-    shot.resize(cap); sin4.resize(cap);
+    shot.resize(cap + 1); sin4.resize(cap + 1);
     memset((void *)shot.data(), 0x55, shot.size() * sizeof(SHot));
     A.spos = spos.data(); A.ckeys = ckeys.data(); A.soff = soff.data(); A.shead = shead.data();
     A.cyc_pos = cyc_pos.data(); A.cyc_noff = cyc_noff.data(); A.max_steps = g_max_steps;
     relax_top.resize(3); A.relax_top = relax_top.data(); A.relax_top_cap = 3;  // tiny: the spill path is exercised
-    B.hot = shot.data(); B.in4 = sin4.data(); B.cap = g_chain_cap ? g_chain_cap : cap; B.n = 0;
+    B.hot = shot.data(); B.in4 = sin4.data(); B.cap = g_chain_cap ? g_chain_cap : cap + 1; B.n = 0;
   }
 };
 
@@ -469,7 +469,7 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
       RR.status = st;
       RR.n_cycles = RR.n_nodes = RR.n_keys = RR.steps = RR.expansions = 0;
       if (st == kEnumDone && g_algo == 2) {
-        st = sball_contract(bs.A, nn, bs.B, co);
+        st = sball_contract(bs.A, nn, max_len, bs.B, co);
         RR.status = st;
         if (st == kEnumDone) {
           SDfsState ds;
@@ -583,6 +583,21 @@ void emu_set_algo(int algo, uint32_t ball_log) {
   g_algo = algo;
   g_ball_log = ball_log;
 }
+// The contracted ball of `start` (visited all clear): hot[2 * i], hot[2 * i + 1] = the 16 bytes of chain record i,
+// in4[i] its in-set.  Returns the number of chains (0 on overflow).  For the device micro-benchmark of the search.
+uint64_t emu_contracted_ball(Emu *e, uint64_t start, int max_len, uint64_t *hot, uint64_t *in4, uint64_t cap) {
+  std::fill(e->visited.begin(), e->visited.end(), 0u);
+  BallSlot bs;
+  bs.init(max_len, g_ball_log);
+  Coop co;
+  uint32_t nn = 0;
+  if (ball_build(e->v, e->adj.data(), e->visited.data(), (uint32_t)start, max_len, bs.A, nn, co) != kEnumDone) return 0;
+  if (sball_contract(bs.A, nn, max_len, bs.B, co) != kEnumDone || bs.B.n + 1 > cap) return 0;
+  memcpy(hot, bs.B.hot, (size_t)(bs.B.n + 1) * 16);  // chains + the dummy record
+  memcpy(in4, bs.B.in4, (size_t)(bs.B.n + 1) * 8);
+  return bs.B.n + 1;
+}
+
 void emu_set_search_limits(int max_steps, uint32_t chain_cap) {
   g_max_steps = max_steps > 0 ? max_steps : kMaxSteps;
   g_chain_cap = chain_cap;
@@ -605,7 +620,7 @@ int emu_search_one(Emu *e, uint64_t start, int min_len, int max_len, int algo, u
   out_stats[6] = 0;
   if (RR.status == kEnumDone) {
     if (algo == 2) {
-      RR.status = sball_contract(bs.A, nn, bs.B, co);
+      RR.status = sball_contract(bs.A, nn, max_len, bs.B, co);
       out_stats[6] = bs.B.n;
       if (RR.status == kEnumDone) {
         SDfsState ds;

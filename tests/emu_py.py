@@ -49,6 +49,8 @@ def lib():
                                       + [C.c_void_p] * 8)
         L.emu_set_algo.argtypes = [C.c_int, C.c_uint32]
         L.emu_set_search_limits.argtypes = [C.c_int, C.c_uint32]
+        L.emu_contracted_ball.restype = C.c_uint64
+        L.emu_contracted_ball.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64]
         L.emu_search_one.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
@@ -161,6 +163,12 @@ class EmuGraph:
             cyc.append(nodes[at:at + int(cyc_len[i])].copy())
             at += int(cyc_len[i])
         return d, cyc
+
+    def contracted_ball(self, start, max_len, cap=65536):
+        hot = np.zeros(2 * cap, np.uint64)
+        in4 = np.zeros(cap, np.uint64)
+        n = lib().emu_contracted_ball(self.h, int(start), max_len, hot.ctypes.data, in4.ctypes.data, cap)
+        return hot[:2 * n].copy(), in4[:n].copy()
 
     def find_cycles(self, starts, min_len, max_len, window=64, lock_log=13):
         starts = np.ascontiguousarray(starts, np.uint64)

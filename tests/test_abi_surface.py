@@ -31,7 +31,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(gpu.GraphDesc) == 8 + 4 * 4 + 8 * 8 + 8 + 48
     assert C.sizeof(gpu.PruneStats) == 40
     assert C.sizeof(gpu.Starts) == 56
-    assert C.sizeof(gpu.Cycles) == 112
+    assert C.sizeof(gpu.Cycles) == 120
 
 
 def test_struct_sizes_against_the_c_compiler(tmp_path):
