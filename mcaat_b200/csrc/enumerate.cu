@@ -109,7 +109,31 @@ struct PipeCtl {
   uint32_t n_ooo;        // commits made out of order (independent tickets)
   unsigned long long searches_run;
 };
-// advances a front (commit_idx / built_idx) over every ticket whose flag is set (lane 0 of any worker)
+// Moves a front (commit_idx / built_idx) from `from` over every ticket whose flag is set — all lanes, 32 flags per
+// round trip — and tells the ticket it stops at that its turn has come (go[f] = 1; waiting workers poll their own
+// word, so there is no hot address).  Both sides of the race "flag set" / "front arrives" write, fence and read,
+// so one of them always continues the sweep.
+__device__ __forceinline__ void sweep_front(uint32_t *front, const uint32_t *flags, uint32_t *go, uint32_t from,
+                                            uint32_t n_end, int lane) {
+  uint32_t f = from;
+  for (;;) {
+    const uint32_t c = f + (uint32_t)lane;
+    const bool set = c < n_end && *(const volatile uint32_t *)&flags[c] != 0;
+    const unsigned m = __ballot_sync(0xffffffffu, set);
+    const int run = m == 0xffffffffu ? 32 : __ffs((int)~m) - 1;
+    f += (uint32_t)run;
+    if (run == 32) continue;
+    int again = 0;
+    if (lane == 0) {
+      atomicMax(front, f);
+      fence_sc();
+      if (f < n_end && *(const volatile uint32_t *)&flags[f] != 0) again = 1;
+      else if (f < n_end && go) *(volatile uint32_t *)&go[f] = 1u;
+    }
+    if (!__shfl_sync(0xffffffffu, again, 0)) break;
+  }
+}
+// advances a front over every ticket whose flag is set (lane 0 of any worker; used where no turn has to be announced)
 __device__ __forceinline__ void advance_front(uint32_t *front, const uint32_t *flags, uint32_t n_end) {
   for (;;) {
     const uint32_t f = *(volatile uint32_t *)front;
@@ -357,7 +381,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
                                                      int max_len, uint8_t *arena, BallLayout L, PipeCtl *ctl,
                                                      TicketRec *recs, uint32_t *pool_nodes, uint32_t pool_nodes_cap,
                                                      uint32_t *pool_len, uint32_t pool_len_cap, uint32_t *owner,
-                                                     uint32_t *built, uint32_t *done, int flags) {
+                                                     uint32_t *built, uint32_t *done, uint32_t *go, int flags) {
   extern __shared__ __align__(16) uint8_t smem_all[];
   constexpr unsigned kFull = 0xffffffffu;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -386,7 +410,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     t = __shfl_sync(kFull, t, 0);
     if (t >= n_end || __shfl_sync(kFull, ld_vol(&ctl->stop), 0)) break;
     if (__shfl_sync(kFull, ld_vol(&done[t]), 0)) {  // committed by an earlier launch of this call
-      if (lane == 0) advance_front(&ctl->commit_idx, done, n_end);
+      if (__shfl_sync(kFull, ld_vol(&ctl->commit_idx), 0) == t) sweep_front(&ctl->commit_idx, done, go, t + 1, n_end, lane);
       continue;
     }
     const uint32_t s = starts[t];
@@ -410,14 +434,16 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     // the ticket is finished (committed or skipped): record, flag, move the commit front
     auto finish = [&](const TicketRec &rec) {
       __syncwarp();
+      uint32_t front = 0;
       if (lane == 0) {
         recs[t] = rec;
         __threadfence();
         if (rec.n_nodes) atomicAdd(&ctl->mark_epoch, 1u);  // after the fence: the marks are visible first
         atomicExch(&done[t], 1u);
         fence_sc();
-        advance_front(&ctl->commit_idx, done, n_end);
+        front = ld_vol(&ctl->commit_idx);
       }
+      if (__shfl_sync(kFull, front, 0) == t) sweep_front(&ctl->commit_idx, done, go, t + 1, n_end, lane);
     };
     // does the search rest on a node that has been marked since its ball was built? (warp-cooperative)
     auto stale = [&](uint32_t n_keys) {
@@ -550,9 +576,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       for (uint32_t j = lane; j < n_nodes; j += 32) {
         const uint32_t x = cyc_keys[j];
         atomicOr(&visited[x >> 5], 1u << (x & 31));
-        pool_nodes[node_base + j] = x;
       }
-      for (uint32_t j = lane; j < n_cycles; j += 32) pool_len[cyc_base + j] = A.cyc_noff[j + 1] - A.cyc_noff[j];
       rec.fate = kFateAccepted;
       rec.status = status;
       rec.n_cycles = n_cycles;
@@ -571,6 +595,11 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       rec.us_started = us_started;
       rec.n_restarts = t_searches;
       return true;
+    };
+    // results[start] = cycles (:479): off the hand-over path, after the ticket has been flagged done
+    auto copy_out = [&]() {
+      for (uint32_t j = lane; j < rec.n_nodes; j += 32) pool_nodes[rec.node_base + j] = cyc_keys[j];
+      for (uint32_t j = lane; j < rec.n_cycles; j += 32) pool_len[rec.cyc_base + j] = A.cyc_noff[j + 1] - A.cyc_noff[j];
     };
     stopped = __shfl_sync(kFull, stopped, 0);
     if (stopped) break;
@@ -611,6 +640,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       }
       ++n_ooo;
       finish(rec);
+      copy_out();
       continue;
     }
     // ---- dependent: wait for this ticket's turn; meanwhile keep the speculative result fresh, so that the
@@ -619,37 +649,37 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     //      re-examined only when the epoch has moved; the poll itself is one 32-byte sector and backs
     //      off with the distance to the commit front, so waiting workers leave the L2 to the searches.
     bool skipped_now = false;
-    for (;;) {
-      uint32_t ci = 0, ep = 0;
-      int st = stopped;
-      if (lane == 0) {
-        ci = ld_vol(&ctl->commit_idx);
-        ep = ld_vol(&ctl->mark_epoch);
-        st |= (int)ld_vol(&ctl->stop);
-      }
-      ci = __shfl_sync(kFull, ci, 0);
-      ep = __shfl_sync(kFull, ep, 0);
-      st = __shfl_sync(kFull, st, 0);
-      if (st) { stopped = 1; break; }
-      if (ci == t) break;
-      status = __shfl_sync(kFull, R.status, 0);
-      if (ep != epoch_checked && status != kEnumOverflow) {
-        epoch_checked = ep;  // marks made after this read are caught by the next epoch change
-        __threadfence();
-        if (__shfl_sync(kFull, (int)visited_live(visited, s), 0)) {
-          skipped_now = true;  // an earlier start's cycles cover this one: skipped (:476)
-          break;
+    for (uint32_t polls = 0;; ++polls) {
+      // own word: set by whoever moves the commit front onto this ticket
+      if (__shfl_sync(kFull, ld_vol(&go[t]), 0)) break;
+      if ((polls & 15u) == 0) {  // the shared control words, less often
+        uint32_t ep = 0;
+        int st = stopped;
+        if (lane == 0) {
+          ep = ld_vol(&ctl->mark_epoch);
+          st |= (int)ld_vol(&ctl->stop);
         }
-        if (stale(__shfl_sync(kFull, R.n_keys, 0))) {
-          speculate(false);
-          ++reruns;
-          if (__shfl_sync(kFull, stopped, 0)) { stopped = 1; break; }
-          if (__shfl_sync(kFull, R.status, 0) == kEnumSkipped) { skipped_now = true; break; }
-          continue;
+        ep = __shfl_sync(kFull, ep, 0);
+        st = __shfl_sync(kFull, st, 0);
+        if (st) { stopped = 1; break; }
+        status = __shfl_sync(kFull, R.status, 0);
+        if (ep != epoch_checked && status != kEnumOverflow) {
+          epoch_checked = ep;  // marks made after this read are caught by the next epoch change
+          __threadfence();
+          if (__shfl_sync(kFull, (int)visited_live(visited, s), 0)) {
+            skipped_now = true;  // an earlier start's cycles cover this one: skipped (:476)
+            break;
+          }
+          if (stale(__shfl_sync(kFull, R.n_keys, 0))) {
+            speculate(false);
+            ++reruns;
+            if (__shfl_sync(kFull, stopped, 0)) { stopped = 1; break; }
+            if (__shfl_sync(kFull, R.status, 0) == kEnumSkipped) { skipped_now = true; break; }
+            continue;
+          }
         }
       }
-      const uint32_t dist = t - ci;
-      __nanosleep(dist <= 2 ? 100u : (dist < 100 ? dist * 200u : 20000u));
+      __nanosleep(300u);
     }
     stopped = __shfl_sync(kFull, stopped, 0);
     if (stopped) break;
@@ -679,6 +709,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       break;
     }
     finish(rec);
+    copy_out();
   }
   __syncwarp();
   ball_clear(A, live, co);  // the index is left empty for the next launch
@@ -742,9 +773,9 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     // ball claims (smallest ticket whose ball holds the item) and the per-ticket built / done flags
     MG_TRY(owner.alloc((size_t)g->view.n * 4));
     MG_CUDA(cudaMemsetAsync(owner.p, 0xFF, (size_t)g->view.n * 4, s));
-    MG_TRY(flags_dev.alloc(n * 8));
-    MG_CUDA(cudaMemsetAsync(flags_dev.p, 0, n * 8, s));
-    uint32_t *built_dev = flags_dev.as<uint32_t>(), *done_dev = built_dev + n;
+    MG_TRY(flags_dev.alloc((n + 1) * 12));
+    MG_CUDA(cudaMemsetAsync(flags_dev.p, 0, (n + 1) * 12, s));
+    uint32_t *built_dev = flags_dev.as<uint32_t>(), *done_dev = built_dev + n + 1, *go_dev = done_dev + n + 1;
     ctl.ooo_limit = 0xFFFFFFFFu;
     uint32_t nodes_cap = 1u << 22, len_cap = 1u << 18;
     MG_TRY(pool_nodes.alloc((size_t)nodes_cap * 4));
@@ -780,13 +811,14 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
       ctl.built_idx = pos;
       ctl.stop = 0;
       MG_CUDA(cudaMemcpyAsync(ctl_dev.p, &ctl, sizeof ctl, cudaMemcpyHostToDevice, s));
+      MG_CUDA(cudaMemsetAsync(go_dev + pos, 1, 4, s));  // the commit front stands on ticket `pos`
       {
         TimedScope ts(g, T_ENUM, solo ? 1 : n - pos);
         if (!solo) {
           MG_LAUNCH(k_enum_pipeline, blocks, 32 * kWarpsPerBlock, L.smem_bytes * kWarpsPerBlock, s, g->view, g->adj.as<uint64_t>(), g->visited.as<uint32_t>(),
                     starts_dev.as<uint32_t>(), (uint32_t)n, min_len, max_len, g->enum_arena.as<uint8_t>(), L,
                     ctl_dev.as<PipeCtl>(), recs_dev.as<TicketRec>(), pool_nodes.as<uint32_t>(), nodes_cap,
-                    pool_len.as<uint32_t>(), len_cap, owner.as<uint32_t>(), built_dev, done_dev, force_global);
+                    pool_len.as<uint32_t>(), len_cap, owner.as<uint32_t>(), built_dev, done_dev, go_dev, force_global);
         } else {
           const SlotLayout LB = make_layout(max_len, big_lock_log, big_relax, kClusterBound);
           MG_CUDA(cudaFuncSetAttribute(k_enum_solo, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LB.smem_bytes));
