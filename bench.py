@@ -172,6 +172,7 @@ def hot_path_step(g, rank=0, world=1, dist=None, torch=None):
               tuple((b - a) * 1e3 for a, b in zip(tt, tt[1:])), file=sys.stderr)
     res_bytes = 8 * int(nodes.size + ss.size)
     hot_path_step.last_cycle_nodes = nodes  # all cycles, flattened
+    hot_path_step.last_result = (ss, coff, noff, nodes)
     stats = dict(st, n_candidates=int(cand.size), n_starts=int(starts.size), dls_expansions=int(exp), **cs)
     return stats, res_bytes
 
@@ -203,7 +204,11 @@ def cpu_baseline_port(sample_name, device):
 
 def reference_arm(args):
     """--impl reference: the reference's own CPU CycleFinder (oracle/_ref/ref_cyclefinder, compiled from the
-    unmodified sources) with all host threads, on the bounded sample of the same workload."""
+    unmodified sources) with all host threads it can use (BASELINE.json quotes --threads 16), on the SAME graph as the
+    B200 arm (args.workload).  The graph files are written once, loaded once; every repetition constructs the
+    CycleFinder in a forked child (oracle/ref_harness/ref_cyclefinder_main.cpp --bench).  Repetitions stop when
+    --warmup + --steps are done or the time budget (BENCH_REF_BUDGET_S, default 240 s) is used up; the number
+    actually timed is printed."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -216,59 +221,67 @@ def reference_arm(args):
     except Exception:
         device = "cpu"
     try:
-        cores = len(os.sched_getaffinity(0))  # what `nproc` reports; os.cpu_count() ignores the container's CPU set
+        cores_avail = len(os.sched_getaffinity(0))  # what `nproc` reports; os.cpu_count() ignores the container's CPU set
     except AttributeError:
-        cores = os.cpu_count() or 1
-    note = ""
-    g, info = S.make_workload(args.sample, device=device, want_labels=True)
+        cores_avail = os.cpu_count() or 1
+    workload = args.workload if device == "cuda" or args.workload != "c2" else args.sample  # no GPU: the full graph cannot be generated
+    g, info = S.make_workload(workload, device=device, want_labels=True)
+    n_items = int(g["n"])
+    budget = float(os.environ.get("BENCH_REF_BUDGET_S", "240"))
+    rep_timeout = float(os.environ.get("BENCH_REF_TIMEOUT_S", "400"))
     exe = O.ref_binary("ref_cyclefinder")
-    times, n_starts, kind = [], 0, "reference"
+    times, n_starts, kind, threads_used, why, load_s = [], 0, "reference", 0, "", None
+    threads_requested = min(cores_avail, 16)
     if exe:
         tmp = tempfile.mkdtemp(prefix="mcaat_ref_")
         prefix = os.path.join(tmp, "graph")
         S.write_megahit_files(g, prefix)
-        env = dict(os.environ, MCAAT_REF_COUNT_STARTS="1")
-        # BASELINE.json quotes the reference at --threads 16.  With more than one thread the reference
-        # races on its result map and can corrupt it and spin forever, so every run is
-        # bounded and the arm falls back to fewer threads instead of hanging.
-        for cores in [c for c in (min(cores, 16), min(cores, 4), 1) if c >= 1]:
-            times = []
-            try:
-                for i in range(args.warmup + args.steps):
-                    out = subprocess.run([exe, prefix, "-", str(cores), str(THR), str(MIN_LEN), str(MAX_LEN)], check=True,
-                                         capture_output=True, text=True, env=env, timeout=120).stdout
-                    js = json.loads([ln for ln in out.splitlines() if ln.startswith("REF_JSON ")][0][9:])
-                    n_starts = js["start_nodes"]
-                    if i >= args.warmup:
-                        times.append(js["ctor_s"])
+        # With more than one thread the reference races on its result map and can corrupt it or never
+        # return, so every repetition is bounded and the arm falls back to fewer threads instead of hanging.
+        for threads in sorted({threads_requested, min(cores_avail, 4), 1}, reverse=True):
+            p = subprocess.run([exe, "--bench", prefix, str(threads), str(THR), str(MIN_LEN), str(MAX_LEN),
+                                str(args.warmup + args.steps), str(budget), str(rep_timeout)], capture_output=True, text=True)
+            reps = [json.loads(ln[9:]) for ln in p.stdout.splitlines() if ln.startswith("REF_JSON ")]
+            for ln in p.stdout.splitlines():
+                if ln.startswith("REF_LOAD "):
+                    load_s = json.loads(ln[9:])["load_s"]
+            if reps:
+                threads_used = threads
+                n_starts = reps[-1]["start_nodes"]
+                times = [r["ctor_s"] for r in reps]
+                if len(times) > args.warmup:  # enough repetitions fitted: drop the warm-up ones
+                    times = times[args.warmup:]
                 break
-            except (subprocess.TimeoutExpired, subprocess.CalledProcessError, IndexError) as e:
-                note += f" [{cores} threads: {type(e).__name__}]"
-                times = []
+            fails = [ln for ln in p.stdout.splitlines() if ln.startswith("REF_FAIL ")]
+            why += f"{threads}t:{json.loads(fails[-1][9:])['why'] if fails else 'rc%d' % p.returncode};"
+        shutil.rmtree(tmp, ignore_errors=True)
         if not times:
             exe = None
     if not exe:  # reference binary absent (or it failed at every thread count): the oracle port is the CPU implementation
-        kind, cores = "port", 1
+        kind, threads_used = "port", 1
         w, last, tip = unpack_for_oracle(g)
+        t_start = time.perf_counter()
         for i in range(args.warmup + args.steps):
             og = O.OracleGraph.from_arrays(w, last, tip, g["mult"], g["f"], g["k"])
             t0 = time.perf_counter()
             r = og.run(THR, MIN_LEN, MAX_LEN)
-            if i >= args.warmup:
-                times.append(time.perf_counter() - t0)
+            times.append(time.perf_counter() - t0)
             n_starts = int(r.start_list().size)
+            if time.perf_counter() - t_start > budget:
+                break
     dt = float(np.mean(times))
     val = n_starts / dt
-    sample = (f"workload '{args.sample}' (same recipe at 1/20 scale): {g['n']} items, {n_starts} start nodes; "
-              f"CycleFinder constructor {dt:.2f} s with {cores} threads" + note)
+    sample = (f"whole workload '{workload}': {n_items} items, {n_starts} start nodes; CycleFinder constructor "
+              f"{dt:.2f} s, {threads_used} threads, {len(times)} repetitions timed")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: BASELINE.json configs[1]; timed on the bounded sample '{args.sample}'",
-                   "sample_n_items": int(g["n"]), "threshold_multiplicity": THR,
-                   "cycle_min_length": MIN_LEN, "cycle_max_length": MAX_LEN},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "config": config_dict(workload, n_items, args.gpus),
+        "reps_timed": len(times), "rep_s": [round(t, 3) for t in times], "threads_requested": threads_requested,
+        "threads_used": threads_used, "cores_available": cores_avail, "fallback_reason": why or None,
+        "load_s": load_s, "n_starts": n_starts,
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads_used, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -277,6 +290,26 @@ def pinned(a, torch):
     """numpy array -> numpy view of a pinned (page-locked) copy"""
     t = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).copy()).pin_memory()
     return t, t.numpy().view(a.dtype)
+
+
+def config_dict(workload, n_items, world):
+    """the `config` object of the JSON line — identical for both arms (--impl reference times the same graph)"""
+    return {"workload": f"{workload}: {WORKLOAD_TEXT.get(workload, 'synthetic community')}, "
+                        f"{n_items} SDBG items (k=23), built by tools/synth_sdbg.py",
+            "n_items": int(n_items), "threshold_multiplicity": THR, "cycle_min_length": MIN_LEN,
+            "cycle_max_length": MAX_LEN, "l2": "graph arrays + navigation cache (>2 GB) exceed the 126 MB L2; "
+                                                "no explicit flush", "parallelism": f"dls-shard x{world}",
+            "timing": "CUDA events on the library stream around each step (mg_step_begin/end), max over ranks"}
+
+
+def result_digest(ss, coff, noff, nodes, inv_words):
+    """sha256 over the canonical result: invalid bitmap words, searched start ids in insertion order, cycle offsets,
+    node offsets, node ids (all little-endian uint64) — equal results <=> equal digests"""
+    import hashlib
+    h = hashlib.sha256()
+    for a in (inv_words, ss, coff, noff, nodes):
+        h.update(np.ascontiguousarray(a, np.uint64).tobytes())
+    return h.hexdigest()
 
 
 WORKLOAD_TEXT = {
@@ -415,6 +448,15 @@ def main():
         wall_ms = wall * 1e3
     ms_per_step = dev_ms / args.steps
     value = stats["n_starts"] / (ms_per_step / 1e3)
+    # ---- what the step computed, as a digest: equal on every rank, and equal for every N
+    result_sha = result_digest(*hot_path_step.last_result, g.invalid_words())
+    graph_device_bytes = g.device_bytes()
+    ranks_agree = True
+    if world > 1:
+        mine = torch.tensor(list(bytes.fromhex(result_sha)), dtype=torch.uint8, device="cuda")
+        every = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        ranks_agree = all(bool(torch.equal(e, every[0])) for e in every)
 
     # ---- BASELINE.json configs[4]: search-explosion sweep on the resident graph (not part of the timed steps above)
     sweep = None
@@ -443,36 +485,63 @@ def main():
                     print("[sweep]", json.dumps(sweep[-1]), file=sys.stderr, flush=True)
         THR, MIN_LEN, MAX_LEN = saved
 
-    # ---- end to end through the C ABI with HOST buffers (N = 1): upload + index build + search + read-back
+    # ---- end to end through the C ABI with HOST buffers: upload + index build + search + read-back inside the timed
+    #      region.  N > 1: rank 0 holds the pinned host arrays; upload on rank 0, NCCL broadcast of the raw arrays,
+    #      every rank builds its replica and runs the step (admission searches sharded), rank 0 reads the results back.
     e2e = None
-    if world == 1 and not args.no_e2e:
-        keep, host = [], dict(n=graph["n"], k=graph["k"], f=graph["f"])
-        for key in ("w", "last", "tip", "mult"):
-            t, v = pinned(graph[key], torch)
-            keep.append(t)
-            host[key] = v
-        h2d = sum(host[k].nbytes for k in ("w", "last", "tip", "mult"))
+    if not args.no_e2e:
+        keep, host, h2d = [], None, 0
+        if rank == 0:
+            host = dict(n=graph["n"], k=graph["k"], f=graph["f"])
+            for key in ("w", "last", "tip", "mult"):
+                t, v = pinned(graph[key], torch)
+                keep.append(t)
+                host[key] = v
+            h2d = sum(host[k].nbytes for k in ("w", "last", "tip", "mult"))
         g.close()
+        if world > 1:
+            del dev, packed_dev
+            torch.cuda.empty_cache()
         e2e_t = []
         for i in range(1 + max(1, min(args.steps, 2))):
-            torch.cuda.synchronize()
+            barrier()
             ta = time.perf_counter()
-            g2 = DeviceGraph(host, device=local)
+            if world == 1:
+                g2 = DeviceGraph(host, device=local)
+            else:
+                dev2 = {}
+                for key, size, dt in zip(("w", "last", "tip", "mult"), m["sizes"], (torch.int64, torch.int64, torch.int64, torch.int16)):
+                    if rank == 0:
+                        t = torch.from_numpy(host[key].view(np.int64 if dt == torch.int64 else np.int16)).cuda(non_blocking=True)
+                    else:
+                        t = torch.empty(size, dtype=dt, device="cuda")
+                    dist.broadcast(t.view(torch.uint8), src=0)
+                    dev2[key] = t
+                torch.cuda.synchronize()
+                g2 = DeviceGraph(dict(n=m["n"], k=m["k"], f=np.array(m["f"], np.int64), **dev2), device=local, memory=gpu.MG_MEM_DEVICE)
             t_up = time.perf_counter()
-            st2, rb = hot_path_step(g2)
+            st2, rb = hot_path_step(g2, rank, world, dist, torch)
             t_hp = time.perf_counter()
-            inv = g2.invalid_words()
-            torch.cuda.synchronize()
+            inv = g2.invalid_words() if rank == 0 else None
+            barrier()
             tb_ = time.perf_counter()
-            if os.environ.get("BENCH_DEBUG"):
+            if os.environ.get("BENCH_DEBUG") and rank == 0:
                 print("[e2e wall ms] upload+index %.1f hot path %.1f invalid read-back %.1f" %
                       ((t_up - ta) * 1e3, (t_hp - t_up) * 1e3, (tb_ - t_hp) * 1e3), file=sys.stderr)
             g2.close()
+            if world > 1:
+                del dev2
             if i > 0:
                 e2e_t.append(tb_ - ta)
         dt = float(np.mean(e2e_t))
-        e2e = dict(value=st2["n_starts"] / dt, unit=UNIT, h2d_bytes_per_step=int(h2d),
-                   d2h_bytes_per_step=int(inv.nbytes + rb), ms_per_step=dt * 1e3)
+        if world > 1:
+            tt_ = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt_, op=dist.ReduceOp.MAX)
+            dt = float(tt_[0])
+        if rank == 0:
+            e2e = dict(value=st2["n_starts"] / dt, unit=UNIT, h2d_bytes_per_step=int(h2d),
+                       d2h_bytes_per_step=int(inv.nbytes + rb), ms_per_step=dt * 1e3,
+                       nccl_broadcast_bytes_per_step=int(h2d) if world > 1 else 0)
 
     # ---- the same hot path on the bounded sample the CPU arms are timed on, so that the two can be compared on
     #      identical input as well (start nodes/s is not scale-free: the sample has 1/20 of the items)
@@ -604,7 +673,7 @@ def main():
     traffic = None  # DRAM bytes per launch of that kernel from the committed ncu --set full capture (same workload)
     if args.workload == "c2":
         try:
-            with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:  # written from the ncu capture of THIS kernel version
                 traffic = json.load(f).get(top, {}).get("bytes_per_launch")
         except Exception:
             traffic = None
@@ -628,12 +697,8 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "u32", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {WORKLOAD_TEXT.get(args.workload, 'synthetic community')}, "
-                               f"{n_items} SDBG items (k=23), built by tools/synth_sdbg.py",
-                   "n_items": int(n_items), "threshold_multiplicity": THR, "cycle_min_length": MIN_LEN,
-                   "cycle_max_length": MAX_LEN, "l2": "graph arrays + navigation cache (>2 GB) exceed the 126 MB L2; "
-                                                       "no explicit flush", "parallelism": f"dls-shard x{world}",
-                   "timing": "CUDA events on the library stream around each step (mg_step_begin/end), max over ranks"},
+        "config": config_dict(args.workload, n_items, world),
+        "result_sha": result_sha, "ranks_agree": bool(ranks_agree),
         "cycle_find_wall_ms": wall_ms / args.steps, "step_ms": [round(x, 2) for x in step_ms], "gpu_launches": int(launches), "clocks": clk,
         "counts": {k: stats[k] for k in ("n_tips_before", "n_mult1", "n_peeled", "n_valid", "n_tips_after", "n_candidates",
                                           "n_starts", "n_searched", "n_cycles", "n_skipped", "n_bound_hits", "n_cap_hits",
@@ -643,7 +708,7 @@ def main():
                   "candidates_per_s": stats["n_candidates"] / max(phases.get("dls", 0) / 1e3, 1e-9),
                   "edges_traversed_per_s": (stats["dls_expansions"] + stats["expansions"] + stats["n_peeled"]) / (ms_per_step / 1e3)},
         "roofline": roofline, "setup": {"generate_s": round(gen_s, 2), "nccl_broadcast_s": round(bcast_s, 4),
-                                        "graph_device_bytes": g.device_bytes() if g.h else None},
+                                        "graph_device_bytes": graph_device_bytes},
     }
     if sweep:
         line["sweep"] = sweep

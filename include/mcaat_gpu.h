@@ -99,6 +99,10 @@ typedef struct {
 } mg_prune_stats;
 int mg_prune(mg_graph *g, mg_prune_stats *stats);
 
+/* CollectTips (reference src/cycle_finder.cpp:346-357) on the CURRENT invalid bitmap: the valid items whose
+ * out-degree is 0, ascending ids, found and compacted on the device.  *ids is library allocated (mg_free). */
+int mg_collect_tips(mg_graph *g, uint64_t **ids, uint64_t *n);
+
 /* Current invalid bitmap -> host words ((n+63)/64 uint64), for write-back into the host SDBG
  * (reference SetInvalidEdge, sdbg.h:94). */
 int mg_invalid_readback(mg_graph *g, uint64_t *host_words);

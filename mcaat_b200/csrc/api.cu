@@ -364,6 +364,26 @@ int mg_candidates(mg_graph *g, uint64_t thr, uint64_t **ids, uint64_t *n) {
   return MG_OK;
 }
 
+int mg_collect_tips(mg_graph *g, uint64_t **ids, uint64_t *n) {
+  MG_CHECK_HANDLE(g);
+  if (!ids || !n) return MG_EINVAL;
+  *ids = nullptr;
+  *n = 0;
+  DevBuf dev;
+  uint64_t cnt = 0;
+  MG_TRY(run_collect_tips(g, dev, &cnt));
+  std::vector<uint32_t> h(cnt);
+  if (cnt) MG_CUDA(cudaMemcpyAsync(h.data(), dev.p, cnt * 4, cudaMemcpyDeviceToHost, g->stream));
+  MG_CUDA(cudaStreamSynchronize(g->stream));
+  flush_timers(g);
+  uint64_t *o = (uint64_t *)malloc((cnt + 1) * 8);
+  if (!o) return MG_ENOMEM;
+  for (uint64_t i = 0; i < cnt; ++i) o[i] = h[i];
+  *ids = o;
+  *n = cnt;
+  return MG_OK;
+}
+
 int mg_dls(mg_graph *g, const uint64_t *ids, uint64_t n, int limit, uint8_t *pass, uint64_t *expansions) {
   MG_CHECK_HANDLE(g);
   if (n && (!ids || !pass)) return MG_EINVAL;

@@ -192,6 +192,7 @@ int build_graph(mg_graph *g, const mg_graph_desc *d);
 int reset_graph(mg_graph *g);
 // prune.cu
 int run_prune(mg_graph *g, mg_prune_stats *st);
+int run_collect_tips(mg_graph *g, DevBuf &ids, uint64_t *n_tips);
 int run_navigate(mg_graph *g, uint64_t first, uint64_t count, int8_t *outdeg, int8_t *indeg, uint64_t *out_ids,
                  uint64_t *in_ids, uint16_t *mult);
 // starts.cu

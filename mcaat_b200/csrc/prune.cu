@@ -246,6 +246,31 @@ __global__ void k_peel_final(GraphView g, PeelView P, uint32_t *merge, unsigned 
   bc.flush(dst);
 }
 
+// CollectTips (reference src/cycle_finder.cpp:346-357) on the CURRENT graph state: ascending ids of the valid items
+// with out-degree 0, compacted on the device (dead ends -> their valid incoming edges -> bitmap -> ids).
+int run_collect_tips(mg_graph *g, DevBuf &ids, uint64_t *n_tips) {
+  GraphView &v = g->view;
+  cudaStream_t s = g->stream;
+  const uint64_t n = v.n;
+  *n_tips = 0;
+  if (!n) return MG_OK;
+  TimedScope ts(g, T_TIPS, n);
+  const size_t bm_bytes = ((n + 31) / 32 + 1) * 4;
+  DevBuf tipbits, dead, dead_ids, counter;
+  MG_TRY(tipbits.alloc(bm_bytes));
+  MG_TRY(dead.alloc(bm_bytes));
+  MG_TRY(counter.alloc(8));
+  MG_CUDA(cudaMemsetAsync(counter.p, 0, 8, s));
+  MG_CUDA(cudaMemsetAsync(tipbits.p, 0, bm_bytes, s));
+  uint64_t n_dead = 0;
+  MG_LAUNCH(k_dead_ends, stream_grid(g, n, 256), 256, 0, s, v, dead.as<uint32_t>());
+  MG_TRY(bitmap_to_ids(dead.as<uint32_t>(), n, dead_ids, &n_dead, s));
+  if (n_dead)
+    MG_LAUNCH(k_tips_of_dead_ends, stream_grid(g, n_dead, 256), 256, 0, s, v, dead_ids.as<uint32_t>(), (uint32_t)n_dead,
+              tipbits.as<uint32_t>(), counter.as<unsigned long long>());
+  return bitmap_to_ids(tipbits.as<uint32_t>(), n, ids, n_tips, s);
+}
+
 int run_prune(mg_graph *g, mg_prune_stats *st) {
   GraphView &v = g->view;
   cudaStream_t s = g->stream;

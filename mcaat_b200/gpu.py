@@ -20,7 +20,7 @@ MG_MEM_HOST, MG_MEM_DEVICE = 0, 1
 # every symbol include/mcaat_gpu.h declares (tests check that the library exports all of them)
 SYMBOLS = [
     "mg_graph_create", "mg_graph_create_from_files", "mg_graph_destroy", "mg_graph_reset", "mg_graph_size", "mg_graph_device_bytes",
-    "mg_navigate", "mg_prune", "mg_invalid_readback", "mg_candidates", "mg_dls", "mg_select_starts",
+    "mg_navigate", "mg_prune", "mg_collect_tips", "mg_invalid_readback", "mg_candidates", "mg_dls", "mg_select_starts",
     "mg_bucket_starts", "mg_starts_free", "mg_find_cycles", "mg_cycles_free", "mg_visited_readback",
     "mg_keep_regions", "mg_invalid_merge", "mg_valid_subgraph", "mg_subgraph_free",
     "mg_kmer_index_create", "mg_graph_has_kmer_index", "mg_map_reads", "mg_reads_free",
@@ -102,6 +102,7 @@ def lib():
         L.mg_invalid_readback.argtypes = [C.c_void_p, C.c_void_p]
         L.mg_visited_readback.argtypes = [C.c_void_p, C.c_void_p]
         L.mg_candidates.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(u64p), C.POINTER(C.c_uint64)]
+        L.mg_collect_tips.argtypes = [C.c_void_p, C.POINTER(u64p), C.POINTER(C.c_uint64)]
         L.mg_dls.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]
         L.mg_select_starts.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.POINTER(Starts)]
         L.mg_bucket_starts.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(Starts)]
@@ -259,6 +260,15 @@ class DeviceGraph:
         st = PruneStats()
         _check(lib().mg_prune(self.h, C.byref(st)))
         return {k: int(getattr(st, k)) for k, _ in PruneStats._fields_}
+
+    def collect_tips(self):
+        """CollectTips (reference src/cycle_finder.cpp:346-357) on the current graph state: ascending ids"""
+        ids = u64p()
+        n = C.c_uint64(0)
+        _check(lib().mg_collect_tips(self.h, C.byref(ids), C.byref(n)))
+        out = _np(ids, n.value)
+        lib().mg_free(ids)
+        return out
 
     def candidates(self, threshold_multiplicity):
         ids = u64p()

@@ -10,7 +10,9 @@
 //
 // Build: see mcaat_b200/host/Makefile (needs the reference's headers on the include path; nothing
 // of the reference is copied).  Device: env MCAAT_GPU_DEVICE (default 0).
+#include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <iostream>
 #include <mutex>
@@ -118,16 +120,37 @@ mg_graph *upload(SDBG &sdbg) {
 namespace {
 using mcaat_gpu_bridge::upload;
 
-// Opt-in fast path (env MCAAT_GPU_INGEST_FILES=1): the graph files the host loaded the SDBG from are
-// decoded on the device (mg_graph_create_from_files) instead of extracting every item through the
-// getters.  `prefix` = settings.graph_folder, which the reference's main has turned into the file
-// prefix before constructing CycleFinder (reference src/main.cpp:522-530).  Only valid while the host
-// has not invalidated anything since SDBG::LoadFromFile — true for the reference's pipeline.
+// Fast path, taken whenever settings.graph_folder names graph files (MCAAT_GPU_INGEST_FILES=0 turns it off): the files
+// the host loaded the SDBG from are decoded on the device (mg_graph_create_from_files) instead of extracting every
+// item through the getters.  `prefix` = settings.graph_folder, which the reference's main has turned into the file
+// prefix before constructing CycleFinder (reference src/main.cpp:522-530).  The files give the LOADED graph; whatever
+// the host invalidated since SDBG::LoadFromFile is ORed in afterwards (mg_invalid_merge), so the device graph equals
+// the host's current state in every case.
+bool graph_files_exist(const std::string &prefix) {
+  if (prefix.empty()) return false;
+  FILE *f = std::fopen((prefix + ".sdbg_info").c_str(), "rb");
+  if (!f) return false;
+  std::fclose(f);
+  return true;
+}
 mg_graph *ingest(const std::string &prefix, SDBG &sdbg) {
   const char *dev = std::getenv("MCAAT_GPU_DEVICE");
   mg_graph *g = nullptr;
   int rc = mg_graph_create_from_files(prefix.c_str(), dev ? std::atoi(dev) : 0, &g);
   if (rc != MG_OK) fail("mg_graph_create_from_files", rc);
+  if (mg_graph_size(g) == (uint64_t)sdbg.size()) {
+    const uint64_t n = sdbg.size();
+    const int64_t n_words = (int64_t)((n + 63) / 64);
+    std::vector<uint64_t> inv((size_t)n_words + 1, 0);
+#pragma omp parallel for schedule(static)
+    for (int64_t wi = 0; wi < n_words; ++wi) {
+      uint64_t lo = (uint64_t)wi * 64, hi = std::min<uint64_t>(lo + 64, n), iw = 0;
+      for (uint64_t i = lo; i < hi; ++i) iw |= (uint64_t)(!sdbg.IsValidEdge(i)) << (i & 63);
+      inv[wi] = iw;
+    }
+    rc = mg_invalid_merge(g, inv.data(), nullptr);
+    if (rc != MG_OK) fail("mg_invalid_merge", rc);
+  }
   if (mg_graph_size(g) != (uint64_t)sdbg.size()) {
     mg_graph_destroy(g);
     throw std::runtime_error("libmcaat_gpu: graph files at '" + prefix + "' do not match the loaded SDBG");
@@ -140,7 +163,7 @@ GpuState &state_of(const CycleFinder *cf, SDBG &sdbg, const std::string &prefix 
   GpuState &s = g_state[cf];
   if (!s.g) {
     const char *fast = std::getenv("MCAAT_GPU_INGEST_FILES");
-    s.g = (fast && *fast == '1' && !prefix.empty()) ? ingest(prefix, sdbg) : upload(sdbg);
+    s.g = (!(fast && *fast == '0') && graph_files_exist(prefix)) ? ingest(prefix, sdbg) : upload(sdbg);
     s.sdbg = &sdbg;
   }
   return s;
@@ -204,13 +227,11 @@ CycleFinder::~CycleFinder() {
 vector<uint64_t> CycleFinder::CollectTips() {
   SDBG &sdbg = *this->settings.sdbg;
   GpuState &s = state_of(this, sdbg, this->settings.graph_folder);
-  const uint64_t n = sdbg.size();
-  std::vector<int8_t> od(n);
-  int rc = mg_navigate(s.g, 0, n, od.data(), nullptr, nullptr, nullptr, nullptr);
-  if (rc != MG_OK) fail("mg_navigate", rc);
-  vector<uint64_t> tips;
-  for (uint64_t i = 0; i < n; ++i)
-    if (od[i] == 0) tips.push_back(i);
+  uint64_t *ids = nullptr, n_tips = 0;
+  int rc = mg_collect_tips(s.g, &ids, &n_tips);  // found and compacted on the device; only the ids cross the bus
+  if (rc != MG_OK) fail("mg_collect_tips", rc);
+  vector<uint64_t> tips(ids, ids + n_tips);
+  mg_free(ids);
   return tips;
 }
 
@@ -245,6 +266,8 @@ size_t CycleFinder::ChunkStartNodes(map<int, vector<uint64_t>, greater<int>> &st
     v.insert(v.end(), st.start_ids + st.bucket_off[b], st.start_ids + st.bucket_off[b + 1]);
   }
   mg_starts_free(&st);
+  // the scan's progress lines (:403): one per 50 M valid items at threads=1
+  for (uint64_t m = 50; m * 1000000ull <= s.stats.n_valid; m += 50) std::cout << "ChunkStartNodes: scanned " << m << "M nodes" << std::endl;
   size_t total = 0;
   for (const auto &[key, value] : start_nodes_chunked) {
     std::cout << "Chunked start nodes: multiplicity bucket (log2)=" << key << ", nodes=" << value.size() << std::endl;

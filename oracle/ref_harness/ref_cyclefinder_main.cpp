@@ -2,6 +2,12 @@
 // Harness around the UNMODIFIED reference CycleFinder (compiled from the sources where they
 // lie under /root/reference by oracle/Makefile; nothing is copied into this repo).
 //   ref_cyclefinder <sdbg_prefix> <out.dump|-> [threads=1] [thr=20] [min=27] [max=77] [low_abundance=1]
+//   ref_cyclefinder --bench <sdbg_prefix> <threads> <thr> <min> <max> <max_reps> <budget_s> <timeout_s>
+//       loads the graph ONCE, then constructs the reference's CycleFinder in a forked child per repetition (the
+//       constructor mutates the graph; a child works on its copy-on-write image) and prints one REF_JSON line per
+//       repetition until max_reps are done or budget_s seconds have passed (at least one); a repetition that runs
+//       longer than timeout_s is killed and reported (with more than one thread the reference races on its result
+//       map, SURVEY F5, and may never return).
 // Constructs the reference's own `CycleFinder(settings)` (reference src/cycle_finder.cpp:131-138),
 // times the constructor, and dumps invalid bitmap / ordered start lists / raw results.
 // `ref_cyclefinder --nav <sdbg_prefix> <out.nav>` dumps, for every item of the LOADED graph,
@@ -15,7 +21,9 @@
 #include <map>
 #include <string>
 #include <vector>
+#include <signal.h>
 #include <sys/resource.h>
+#include <sys/wait.h>
 #include <unistd.h>
 
 #include "cycle_finder.h"
@@ -56,9 +64,73 @@ static int nav_dump(const char *prefix, const char *out) {
   return 0;
 }
 
+static int bench(int argc, char **argv) {
+  if (argc < 10) return 1;
+  Settings s;
+  s.threads = atoi(argv[3]);
+  s.cycle_finder_settings.threshold_multiplicity = strtoull(argv[4], 0, 10);
+  s.cycle_finder_settings.cycle_min_length = atoi(argv[5]);
+  s.cycle_finder_settings.cycle_max_length = atoi(argv[6]);
+  s.cycle_finder_settings.low_abundance = true;
+  const int max_reps = atoi(argv[7]);
+  const double budget_s = atof(argv[8]), timeout_s = atof(argv[9]);
+  auto t0 = std::chrono::steady_clock::now();
+  SDBG g;
+  g.LoadFromFile(argv[2]);
+  s.sdbg = &g;
+  s.graph_folder = argv[2];
+  double load_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  printf("REF_LOAD {\"n_items\": %llu, \"load_s\": %.6f}\n", (unsigned long long)g.size(), load_s);
+  fflush(stdout);
+  auto b0 = std::chrono::steady_clock::now();
+  for (int rep = 0; rep < max_reps; ++rep) {
+    if (rep > 0 && std::chrono::duration<double>(std::chrono::steady_clock::now() - b0).count() > budget_s) break;
+    pid_t pid = fork();
+    if (pid < 0) return 3;
+    if (pid == 0) {
+      omp_set_num_threads((int)s.threads);
+      auto t1 = std::chrono::steady_clock::now();
+      std::cout.setstate(std::ios_base::failbit);  // the progress lines of the constructor
+      CycleFinder cf(s);
+      double ctor_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
+      std::map<int, std::vector<uint64_t>, std::greater<int>> chunks;
+      size_t n_starts = cf.ChunkStartNodes(chunks);  // public, does not read `visited` (:387-427)
+      std::cout.clear();
+      size_t total_cycles = 0;
+      for (auto &kv : cf.results) total_cycles += kv.second.size();
+      printf("REF_JSON {\"rep\": %d, \"n_items\": %llu, \"threads\": %zu, \"ctor_s\": %.6f, \"start_nodes\": %zu, "
+             "\"searched\": %zu, \"cycles\": %zu}\n", rep, (unsigned long long)g.size(), s.threads, ctor_s, n_starts,
+             cf.results.size(), total_cycles);
+      fflush(stdout);
+      _exit(0);
+    }
+    auto w0 = std::chrono::steady_clock::now();
+    int status = 0;
+    for (;;) {
+      pid_t r = waitpid(pid, &status, WNOHANG);
+      if (r == pid) break;
+      if (std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count() > timeout_s) {
+        kill(pid, SIGKILL);
+        waitpid(pid, &status, 0);
+        printf("REF_FAIL {\"rep\": %d, \"why\": \"timeout\"}\n", rep);
+        fflush(stdout);
+        return 4;
+      }
+      usleep(20000);
+    }
+    if (!WIFEXITED(status) || WEXITSTATUS(status) != 0) {
+      printf("REF_FAIL {\"rep\": %d, \"why\": \"crash\"}\n", rep);
+      fflush(stdout);
+      return 5;
+    }
+  }
+  return 0;
+}
+
 int main(int argc, char **argv) {
   raise_stack_limit(argv);
   if (argc >= 4 && !strcmp(argv[1], "--nav")) return nav_dump(argv[2], argv[3]);
+  if (argc >= 3 && !strcmp(argv[1], "--bench")) return bench(argc, argv);
   if (argc < 3) {
     fprintf(stderr, "usage: %s <sdbg_prefix> <out.dump|-> [threads thr min max low_abundance]\n", argv[0]);
     return 1;

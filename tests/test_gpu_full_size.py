@@ -218,6 +218,55 @@ def test_cpp_drop_in_equals_the_unmodified_reference_binary_on_the_sample(tmp_pa
         assert open(out, "rb").read() == want, f"ingest={ingest}"
 
 
+@pytest.mark.skipif(not os.environ.get("MCAAT_TEST_C2_FULL"), reason="the reference needs minutes of one host core at 224.7 M "
+                    "items; run with MCAAT_TEST_C2_FULL=1 (log under profiles/)")
+@pytest.mark.parametrize("thr,mn,mx", [(20, 27, 77), (10, 20, 100)])
+def test_cpp_drop_in_equals_the_unmodified_reference_binary_at_full_size(tmp_path_factory, thr, mn, mx):
+    """The headline workload itself — c2, 224.7 M items, what bench.py times — against the compiled UNMODIFIED
+    reference at threads=1: the two dumps (host SDBG invalid bitmap after the prune, ordered start lists per bucket, raw
+    per-start cycle sequences, unordered_map iteration order) are byte-identical, at the default setting and at a
+    stress setting of BASELINE.json configs[4].  The Python binding's result on the same graph equals the dump too."""
+    import hashlib
+    import subprocess
+    import time
+    import synth_sdbg as S
+    ref = O.ref_binary("ref_cyclefinder")
+    shim = os.path.join(ROOT, "mcaat_b200", "host", "_build", "shim_cyclefinder")
+    if ref is None or not os.path.exists(shim):
+        pytest.skip("reference / drop-in binaries not built (they need the reference sources at build time)")
+    d = _wl.get("c2_files")
+    if d is None:
+        d = str(tmp_path_factory.mktemp("c2_files"))
+        gs, _ = S.make_workload("c2", device="cuda", want_labels=True)
+        S.write_megahit_files(gs, os.path.join(d, "graph"))
+        del gs
+        _wl["c2_files"] = d
+    prefix = os.path.join(d, "graph")
+    want_path = os.path.join(d, f"ref_{thr}_{mn}_{mx}.dump")
+    t0 = time.time()
+    out = subprocess.run([ref, prefix, want_path, "1", str(thr), str(mn), str(mx)], check=True, capture_output=True, text=True).stdout
+    t_ref = time.time() - t0
+    print([ln for ln in out.splitlines() if ln.startswith("REF_JSON ")][-1])
+    want = open(want_path, "rb").read()
+    for ingest in ("1", "0"):
+        got_path = os.path.join(d, f"shim_{thr}_{mn}_{mx}_{ingest}.dump")
+        t0 = time.time()
+        out = subprocess.run([shim, prefix, got_path, "1", str(thr), str(mn), str(mx)], check=True, capture_output=True, text=True,
+                             env=dict(os.environ, MCAAT_GPU_INGEST_FILES=ingest)).stdout
+        t_shim = time.time() - t0
+        print(f"ingest={ingest}", [ln for ln in out.splitlines() if ln.startswith("REF_JSON ")][-1])
+        got = open(got_path, "rb").read()
+        print(f"[c2 full size, thr={thr} bounds {mn}-{mx}, ingest={ingest}] reference process {t_ref:.1f} s, drop-in process {t_shim:.1f} s, "
+              f"dump {len(want)} bytes, sha256 ref {hashlib.sha256(want).hexdigest()[:16]} drop-in {hashlib.sha256(got).hexdigest()[:16]}")
+        assert got == want, f"ingest={ingest}"
+        os.remove(got_path)
+    # the Python binding (what bench.py calls) on the array-built graph of the same workload
+    ref_run = O.parse_dump(want_path)
+    os.remove(want_path)
+    got_run = run(DeviceGraph(workload("c2")), thr, mn, mx)
+    assert O.same_run(ref_run, got_run) == []
+
+
 def test_full_size_read_mapping_properties(monkeypatch):
     """N3 at 224.7 M items (index attached to the array-built graph): kept reads carry len - k + 1 ids; mapping the
     reverse complement of a batch with reverse=True gives the ids of the batch itself (reverse_pair_ends_sequence is

@@ -163,6 +163,41 @@ def test_cpp_drop_in_cyclefinder_matches_reference_dump(tmp_path):
             assert open(out, "rb").read() == want
 
 
+@pytest.mark.parametrize("name", ["tiny", "biallelic"])
+def test_cpp_drop_in_prints_the_reference_progress_lines(tmp_path, name):
+    """SURVEY 5 ("same text -> diffable logs"): the progress lines the reference's constructor writes to std::cout
+    (src/cycle_finder.cpp:381,403,423,437,452,456,459-461,466,485-490) against the drop-in's, line for line, on the same
+    graph at threads=1 — counts of tips, filtered items, valid edges, buckets and cycles included."""
+    import os
+    import subprocess
+    shim = os.path.join(gpu.ROOT, "mcaat_b200", "host", "_build", "shim_cyclefinder")
+    ref = O.ref_binary("ref_cyclefinder")
+    if ref is None or not os.path.exists(shim):
+        pytest.skip("reference / drop-in binaries not built (they need the reference sources at build time)")
+    prefix = G.unpack_sdbg_files(name, str(tmp_path))
+    env = {k: v for k, v in os.environ.items() if k != "MCAAT_REF_COUNT_STARTS"}
+    lines = {}
+    for exe in (ref, shim):
+        out = subprocess.run([exe, prefix, "-", "1", "20", "27", "77"], check=True, capture_output=True, text=True, env=env).stdout
+        lines[exe] = [ln for ln in out.splitlines() if not ln.startswith("REF_JSON ")]
+    assert lines[ref] == lines[shim]
+    assert any(ln.startswith("Cycle enumeration completed") for ln in lines[ref]) and len(lines[ref]) >= 8
+
+
+def test_collect_tips_on_the_device_matches_navigation():
+    """mg_collect_tips (dead ends -> incoming edges -> compaction, all on the device) == {valid, out-degree 0} from the
+    per-item navigation table, on the loaded graph and again after the prune"""
+    for name in ("tiny", "strain"):
+        g = DeviceGraph(packed(name))
+        for stage in ("loaded", "pruned"):
+            od = g.navigate()[0]
+            want = np.nonzero(od == 0)[0].astype(np.uint64)
+            got = g.collect_tips()
+            assert np.array_equal(got, want), (name, stage)
+            assert stage == "pruned" or got.size > 0
+            g.prune()
+
+
 def test_device_ingest_of_on_disk_sdbg(tmp_path):
     """the reference's own graph files (built by its SDBGBuild, 4 part files) decoded on
     the device give the same navigation tables and the same search result as the reference."""
