@@ -192,6 +192,7 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
       uint32_t lid = total_nodes + before;
       for (uint32_t j = 0; j < cnt; ++j)
         if ((mine >> j) & 1) {
+          prefetch_l2(&adj[okn[j]]);  // expanded at the next level: its navigation entry is on its way by then
           N[lid].meta = (uint32_t)M;  // lock default (try_emplace(n, cycle_max_length), :168), no edges yet
           N[lid].key = okn[j];
           N[lid].out4 = ~0ull;
@@ -876,6 +877,198 @@ MG_HD void sball_expand(const BallArena &A, const SBall &B, uint32_t n_staged, u
     for (uint32_t i = 0; i < c; ++i) out[at + i] = A.ckeys[from + i];
   }
   co.sync();
+}
+
+// ====================================================================== DepthLevelSearch on an extracted ball
+// The admission search (reference src/cycle_finder.cpp:248-343, dls_run in search_dev.cuh) is an order-dependent DFS
+// with ONE global seen-set: exact emulation is sequential, and on the graph every expansion is a dependent DRAM
+// access (~0.7 us).  99 % of the searches are short; the few thousand long ones (10^4 expansions) used to bound the
+// whole phase by the length of the longest.  For those the same two stages as for the enumeration:
+//   1. dball_build — the warp extracts the forward ball of radius `limit` (everything the DFS can reach: a node is
+//      pushed at depth <= limit, BFS distance <= DFS depth) level by level, 32 nodes at a time, with each node's
+//      OutgoingEdges list (order kept: descending ids, sdbg.h:297-320), its in-degree inside the ball and its first
+//      in-neighbour;
+//   2. dball_contract + dball_dfs — a non-start node is pushed at most once (seen-set), so a maximal chain
+//      n_1 .. n_c (one out-neighbour each, entered only through n_1) is walked exactly once, right after n_1 is
+//      popped: one record, one step.  The DFS itself is the literal one: LIFO stack, children pushed in
+//      OutgoingEdges order, the start node pushed again whenever it is reached at depth > 0, found when the start is
+//      expanded at depth > 1 (:337-339), depth test before the pushes (:312), expansion counter as dls_run counts it.
+// Capacity overflow (ball > node capacity) is reported as kDlsSetFull; the caller falls back to the bitmap tier.
+struct alignas(16) DChain {
+  uint32_t w0;   // c | tail has an out-neighbour << 16 | head seen << 31
+  uint32_t pad;
+  union { uint16_t out[4]; uint64_t out4; };  // chains OUT(n_c) leads to, OutgoingEdges order; unused = kNoLid
+};
+static_assert(sizeof(DChain) == 16, "chain record");
+constexpr uint32_t kDSeen = 1u << 31, kDTailOut = 1u << 16;
+
+MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, const BallArena &A, uint32_t &n_nodes,
+                               const Coop &co) {
+  const uint32_t imask = (1u << A.index_log) - 1;
+  LNode *N = A.nodes;
+  LTail *T = A.tails;
+  if (co.lane == 0) {
+    uint32_t h = hash_u32(start, A.index_log);
+    st_cg64(&A.index[h], ((uint64_t)start << 32) | 0u);
+    N[0].meta = 0;
+    N[0].key = start;
+    N[0].out4 = ~0ull;
+    T[0].slot = h;
+    A.relax[0] = 0;
+  }
+  co.sync();
+  uint32_t total_nodes = 1, lo = 0, hi = 1;
+  int status = kDlsNotFound;
+  for (int depth = 0; depth <= limit && lo < hi && status == kDlsNotFound; ++depth) {
+    const bool expand = depth < limit;  // nodes at distance `limit` are only asked for their out-degree (:294)
+    for (uint32_t base = lo; base < hi; base += Coop::kLanes) {
+      const uint32_t i = base + (uint32_t)co.lane;
+      uint32_t nb[4], slot[4], cnt = 0, mine = 0;
+      if (i < hi) {
+        int deg = adj_outgoing(ld_ro(&adj[N[i].key]), nb);
+        if (deg > 4) deg = 4;
+        cnt = (uint32_t)deg;
+        if (!expand) {
+          N[i].meta = cnt << kMetaOutShift;
+          cnt = 0;
+        }
+        for (uint32_t j = 0; j < cnt; ++j) {  // find or claim the neighbour's index slot
+          const uint32_t key = nb[j];
+          uint32_t h = hash_u32(key, A.index_log);
+          for (;;) {
+            uint64_t cur = ld_cg64(&A.index[h]);
+            if (cur == kIndexEmpty) {
+              cur = index_cas(&A.index[h], kIndexEmpty, ((uint64_t)key << 32) | kLidPending);
+              if (cur == kIndexEmpty) { mine |= 1u << j; break; }
+            }
+            if ((uint32_t)(cur >> 32) == key) break;
+            h = (h + 1) & imask;
+          }
+          slot[j] = h;
+        }
+      }
+      const uint32_t n_mine = (uint32_t)popc32(mine);
+      const uint32_t before = co.exclusive_prefix(n_mine), chunk_new = co.sum(n_mine);
+      if (total_nodes + chunk_new > A.node_cap) {
+        co.sync();
+        for (uint32_t j = 0; j < cnt; ++j)
+          if ((mine >> j) & 1) st_cg64(&A.index[slot[j]], kIndexEmpty);
+        co.sync();
+        status = kDlsSetFull;
+        break;
+      }
+      uint32_t lid = total_nodes + before;
+      for (uint32_t j = 0; j < cnt; ++j)
+        if ((mine >> j) & 1) {
+          prefetch_l2(&adj[nb[j]]);  // expanded (or asked for its out-degree) at the next level
+          N[lid].meta = 0;
+          N[lid].key = nb[j];
+          N[lid].out4 = ~0ull;
+          T[lid].slot = slot[j];
+          A.relax[lid] = 0;  // in-degree inside the ball
+          st_cg64(&A.index[slot[j]], ((uint64_t)nb[j] << 32) | lid);
+          ++lid;
+        }
+      total_nodes += chunk_new;
+      co.sync();
+      if (i < hi && expand) {
+        for (uint32_t j = 0; j < cnt; ++j) {
+          const uint32_t x = (uint32_t)ld_cg64(&A.index[slot[j]]);
+          N[i].out[j] = (uint16_t)x;
+          if (meta_add(&A.relax[x], 1u) == 0) T[x].in[0] = (uint16_t)i;  // the in-neighbour, if it stays the only one
+        }
+        N[i].meta = cnt << kMetaOutShift;
+      }
+    }
+    lo = hi;
+    hi = total_nodes;
+  }
+  co.sync();
+  n_nodes = total_nodes;
+  return status;
+}
+
+MG_HD bool dball_is_head(const BallArena &A, uint32_t x) {
+  if (x == 0) return true;
+  if (ld_cg32(&A.relax[x]) != 1) return true;
+  const uint32_t u = A.tails[x].in[0];
+  return u == 0 || ((A.nodes[u].meta >> kMetaOutShift) & 7u) != 1;
+}
+// chains of the ball -> C[0 .. n_chains); returns the number of chains
+MG_HD_NOINLINE uint32_t dball_contract(const BallArena &A, uint32_t n_nodes, DChain *C, const Coop &co) {
+  const LNode *N = A.nodes;
+  uint32_t n_chains = 0;
+  for (uint32_t base = 0; base < n_nodes; base += Coop::kLanes) {
+    const uint32_t x = base + (uint32_t)co.lane;
+    const bool head = x < n_nodes && dball_is_head(A, x);
+    const uint32_t before = co.exclusive_prefix(head ? 1u : 0u), cnt = co.sum(head ? 1u : 0u);
+    if (head) {
+      A.shead[n_chains + before] = (uint16_t)x;
+      A.spos[x] = n_chains + before;  // chain number of a head (other nodes are never looked up)
+    }
+    n_chains += cnt;
+  }
+  co.sync();
+  for (uint32_t s = (uint32_t)co.lane; s < n_chains; s += Coop::kLanes) {
+    uint32_t x = A.shead[s], c = 1;
+    for (;;) {
+      if (s == 0 || ((N[x].meta >> kMetaOutShift) & 7u) != 1) break;
+      const uint32_t y = N[x].out[0];
+      if (dball_is_head(A, y)) break;
+      x = y;
+      ++c;
+    }
+    const uint32_t nout = (N[x].meta >> kMetaOutShift) & 7u;
+    DChain d;
+    d.w0 = c | (nout ? kDTailOut : 0u);
+    d.pad = 0;
+    uint64_t o = N[x].out4, o2 = 0;
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t a = (uint32_t)(o >> (16 * q)) & 0xFFFFu;
+      o2 |= (uint64_t)(a == kNoLid ? kNoLid : (A.spos[a] & 0xFFFFu)) << (16 * q);  // out-neighbours of a tail are heads
+    }
+    d.out4 = o2;
+    C[s] = d;
+  }
+  co.sync();
+  return n_chains;
+}
+// Literal DepthLevelSearch(start, start, limit) on the contracted ball (one lane).  `stk` holds 4 * limit + 8 entries.
+MG_HD_NOINLINE int dball_dfs(DChain *C, int limit, uint32_t *stk, uint32_t stk_cap, uint32_t &expansions) {
+  uint32_t sp = 0;
+  stk[sp++] = 0u;  // (chain 0 = the start node, depth 0)
+  while (sp) {
+    const uint32_t e = stk[--sp];
+    const uint32_t sid = e & 0xFFFFu;
+    const int d = (int)(e >> 16);
+    const DChain R = C[sid];
+    const int c = (int)(R.w0 & 0xFFFFu);
+    const int room = limit - d + 1;                     // nodes of the chain popped at depth <= limit
+    const int t = c < room ? c : room;
+    const bool tail_out = (R.w0 & kDTailOut) != 0;
+    expansions += (uint32_t)((t < c || tail_out) ? t : t - 1);  // pops with an out-neighbour (:294 comes before the count)
+    if (t < c || !tail_out) continue;                   // cut by the depth limit inside the chain / dead end
+    const int dt = d + c - 1;                           // depth of the last node
+    if (dt >= limit) continue;                          // :312
+    uint32_t hw[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t h = (uint32_t)(R.out4 >> (16 * j)) & 0xFFFFu;
+      hw[j] = h != kNoLid ? C[h].w0 : kDSeen;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {                       // :320-334, OutgoingEdges order
+      const uint32_t h = (uint32_t)(R.out4 >> (16 * j)) & 0xFFFFu;
+      if (h == kNoLid) continue;
+      if (!(hw[j] & kDSeen) || (h == 0 && dt > 0)) {
+        C[h].w0 = hw[j] | kDSeen;
+        if (sp >= stk_cap) return kDlsStackFull;
+        stk[sp++] = h | ((uint32_t)(dt + 1) << 16);
+      }
+    }
+    if (sid == 0 && dt > 1) return kDlsFound;            // :337-339
+  }
+  return kDlsNotFound;
 }
 
 }  // namespace mg

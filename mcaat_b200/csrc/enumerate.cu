@@ -33,6 +33,7 @@
 
 #include "common.cuh"
 #include "ball_dev.cuh"
+#include "ball_layout.cuh"
 #include "search_dev.cuh"
 
 namespace mg {
@@ -42,7 +43,6 @@ struct SlotLayout {  // per-worker arena in global memory (byte offsets inside o
   size_t off_index, off_hot, off_cold, off_relax, off_cyc_nodes, off_cyc_off, bytes;
   uint32_t smem_bytes;  // per worker: path, pent, bl, stk live in shared memory
 };
-static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 static SlotLayout make_layout(int max_len, uint32_t index_log, uint32_t relax_cap, uint32_t cyc_cap_cycles) {
   SlotLayout L;
   L.index_log = index_log;
@@ -307,75 +307,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_enum_solo(GraphView g, 
   }
 }
 
-// ---- the pipeline proper: extracted-ball searches (ball_dev.cuh)
-struct BallLayout {  // per-worker arena in global memory (byte offsets inside one slot)
-  uint32_t index_log, node_cap, relax_cap, cyc_cap, depth_cap;
-  size_t off_nodes, off_tails, off_index, off_relax, off_cyc, off_cyc_pos, off_cyc_keys, off_cyc_off, off_cyc_noff,
-      off_spos, off_ckeys, off_soff, off_shead, off_shot, off_sin, off_lvl, bytes;
-  // per worker in shared memory: the path levels (Lvl; in the arena instead when cycle_max_length makes them large),
-  // the top of the relaxation stack and the records of the contracted ball (up to chain_cap chains; larger
-  // contracted balls use the records in the arena)
-  uint32_t smem_bytes, smem_lvl, smem_relax, chain_cap;
-};
-constexpr uint32_t kRelaxSmem = 128;  // relaxation stack entries held in shared memory (the rest spills to the arena)
-static BallLayout make_ball_layout(int max_len, uint32_t index_log, uint32_t smem_per_worker) {
-  BallLayout L;
-  L.index_log = index_log;
-  L.node_cap = std::min<uint32_t>((1u << index_log) / 2, 65535u);
-  L.relax_cap = std::max<uint32_t>(L.node_cap, 32768u);  // also holds the in-degree counters of the build
-  L.depth_cap = (uint32_t)max_len + 4;
-  L.cyc_cap = (uint32_t)kClusterBound * (uint32_t)(max_len + 1);
-  size_t o = 0;
-  L.off_nodes = o; o = align_up(o + (size_t)L.node_cap * sizeof(LNode), 128);
-  L.off_tails = o; o = align_up(o + (size_t)L.node_cap * sizeof(LTail), 128);
-  L.off_index = o; o = align_up(o + ((size_t)8 << index_log), 128);
-  L.off_relax = o; o = align_up(o + (size_t)L.relax_cap * 4, 128);
-  L.off_cyc = o; o = align_up(o + (size_t)L.cyc_cap * 2, 128);
-  L.off_cyc_pos = o; o = align_up(o + (size_t)L.cyc_cap * 4, 128);
-  L.off_cyc_keys = o; o = align_up(o + (size_t)L.cyc_cap * 4, 128);
-  L.off_cyc_off = o; o = align_up(o + (size_t)(kClusterBound + 1) * 4, 128);
-  L.off_cyc_noff = o; o = align_up(o + (size_t)(kClusterBound + 1) * 4, 128);
-  L.off_spos = o; o = align_up(o + (size_t)L.node_cap * 4, 128);
-  L.off_ckeys = o; o = align_up(o + (size_t)L.node_cap * 4, 128);
-  L.off_soff = o; o = align_up(o + (size_t)(L.node_cap + 1) * 2, 128);
-  L.off_shead = o; o = align_up(o + (size_t)L.node_cap * 2, 128);
-  L.off_shot = o; o = align_up(o + (size_t)(L.node_cap + 1) * sizeof(SHot), 128);
-  L.off_sin = o; o = align_up(o + (size_t)(L.node_cap + 1) * 8, 128);
-  L.off_lvl = o; o = align_up(o + (size_t)L.depth_cap * sizeof(Lvl), 128);
-  L.bytes = align_up(o, 128);
-  const uint32_t lvl_bytes = (uint32_t)align_up((size_t)L.depth_cap * sizeof(Lvl), 16);
-  L.smem_lvl = lvl_bytes <= smem_per_worker / 4 ? lvl_bytes : 0;  // long paths: levels in the arena
-  L.smem_relax = kRelaxSmem * 4;
-  const uint32_t rest = smem_per_worker - L.smem_lvl - L.smem_relax;
-  L.chain_cap = std::min<uint32_t>(rest / 24 / 8 * 8, L.node_cap);
-  L.smem_bytes = L.smem_lvl + L.smem_relax + L.chain_cap * 24;
-  return L;
-}
-__device__ __forceinline__ BallArena ball_arena_of(uint8_t *base, uint8_t *smem, const BallLayout &L) {
-  BallArena A;
-  A.nodes = (LNode *)(base + L.off_nodes);
-  A.tails = (LTail *)(base + L.off_tails);
-  A.node_cap = L.node_cap;
-  A.index = (uint64_t *)(base + L.off_index);
-  A.index_log = L.index_log;
-  A.relax = (uint32_t *)(base + L.off_relax);
-  A.relax_cap = L.relax_cap;
-  A.cyc = (uint16_t *)(base + L.off_cyc);
-  A.cyc_cap = L.cyc_cap;
-  A.cyc_off = (uint32_t *)(base + L.off_cyc_off);
-  A.lvl = L.smem_lvl ? (Lvl *)smem : (Lvl *)(base + L.off_lvl);
-  A.relax_top = (uint32_t *)(smem + L.smem_lvl);
-  A.relax_top_cap = kRelaxSmem;
-  A.spos = (uint32_t *)(base + L.off_spos);
-  A.ckeys = (uint32_t *)(base + L.off_ckeys);
-  A.soff = (uint16_t *)(base + L.off_soff);
-  A.shead = (uint16_t *)(base + L.off_shead);
-  A.cyc_pos = (uint32_t *)(base + L.off_cyc_pos);
-  A.cyc_noff = (uint32_t *)(base + L.off_cyc_noff);
-  A.max_steps = kMaxSteps;
-  return A;
-}
-
+// ---- the pipeline proper: extracted-ball searches (ball_dev.cuh; worker arenas: ball_layout.cuh)
 __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphView g, const uint64_t *__restrict__ adj, uint32_t *visited,
                                                      const uint32_t *__restrict__ starts, uint32_t n_end, int min_len,
                                                      int max_len, uint8_t *arena, BallLayout L, PipeCtl *ctl,
@@ -786,22 +718,13 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     const uint32_t blocks = (want + kWarpsPerBlock - 1) / kWarpsPerBlock, workers = blocks * kWarpsPerBlock;
     // shared memory: the workers of one SM share what the device offers (227 KB opt-in, 1 KB reserved per block)
     const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32);
-    const uint32_t blocks_per_sm = (workers_per_sm + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    const uint32_t smem_per_block = ((uint32_t)g->smem_per_sm - blocks_per_sm * 1024u) / blocks_per_sm;
-    const uint32_t smem_per_worker =
-        std::min<uint32_t>(std::min<uint32_t>(smem_per_block, (uint32_t)g->smem_per_block_optin) / kWarpsPerBlock / 16 * 16,
-                           env_u32("MCAAT_ENUM_SMEM_PER_WORKER", 1u << 20, 2048, 1u << 20));
+    const uint32_t smem_per_worker = std::min<uint32_t>(ball_smem_per_worker(g, workers_per_sm, kWarpsPerBlock),
+                                                        env_u32("MCAAT_ENUM_SMEM_PER_WORKER", 1u << 20, 2048, 1u << 20));
     const BallLayout L = make_ball_layout(max_len, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 17), smem_per_worker);
     // diagnostics: chain records in the arena instead of shared memory (1); every commit in ticket order (4)
     const int force_global = (int)(env_u32("MCAAT_ENUM_CHAINS_GLOBAL", 0, 0, 1) | (env_u32("MCAAT_ENUM_INORDER", 0, 0, 1) << 2));
     MG_CUDA(cudaFuncSetAttribute(k_enum_pipeline, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(L.smem_bytes * kWarpsPerBlock)));
-    const uint64_t sig = ((uint64_t)L.bytes << 20) ^ ((uint64_t)L.index_log << 8) ^ (uint64_t)workers;
-    if (g->enum_arena.bytes < (size_t)workers * L.bytes || g->enum_arena_sig != sig) {
-      // the hash indices must start out empty (all ones); every launch leaves them empty again
-      MG_TRY(g->enum_arena.ensure((size_t)workers * L.bytes));
-      MG_CUDA(cudaMemsetAsync(g->enum_arena.p, 0xFF, g->enum_arena.bytes, s));
-      g->enum_arena_sig = sig;
-    }
+    MG_TRY(ensure_ball_arena(g, workers, L));
     uint32_t big_lock_log = env_u32("MCAAT_ENUM_LOCK_LOG", 19, 6, 26), big_relax = 1u << 20;
     uint32_t pos = 0;
     bool solo = false;  // the ticket at `pos` overflowed a worker arena: run it alone in the big arena

@@ -4,6 +4,7 @@
 
 #include "common.cuh"
 #include "search_dev.cuh"
+#include "ball_layout.cuh"
 
 namespace mg {
 
@@ -150,6 +151,52 @@ __global__ void __launch_bounds__(128) k_dls(const uint64_t *__restrict__ adj, c
   if ((threadIdx.x & 31) == 0 && exp_total) atomicAdd(expansions, exp_total);
 }
 
+// Middle tier: the long searches (those whose seen-set outgrew tier 1) on their extracted, contracted ball — one warp
+// per search: dball_build / dball_contract by the warp, the literal DFS by lane 0 (ball_dev.cuh).  The DFS stack is in
+// shared memory when it fits (stk_smem entries per warp), else in the worker's arena.
+constexpr int kDlsBallWarps = 4;
+__global__ void __launch_bounds__(32 * kDlsBallWarps) k_dls_ball(const uint64_t *__restrict__ adj, const uint32_t *__restrict__ cand,
+                                                          const uint32_t *__restrict__ todo, uint32_t n_todo, int limit,
+                                                          uint8_t *arena, BallLayout L, int8_t *result, uint32_t *queue,
+                                                          unsigned long long *expansions, uint32_t *per_search,
+                                                          uint32_t stk_smem) {
+  extern __shared__ __align__(16) uint8_t dls_ball_smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t worker = blockIdx.x * kDlsBallWarps + warp;
+  uint8_t *base = arena + (size_t)worker * L.bytes;
+  const BallArena A = ball_arena_of(base, base + L.off_lvl, L);
+  DChain *C = (DChain *)(base + L.off_shot);
+  const uint32_t stk_cap = (uint32_t)(4 * limit + 8);
+  uint32_t *stk = stk_smem ? (uint32_t *)dls_ball_smem + (size_t)warp * stk_smem : (uint32_t *)(base + L.off_cyc_pos);
+  Coop co;
+  co.lane = lane;
+  uint32_t live = 0;
+  unsigned long long exp_total = 0;
+  for (;;) {
+    uint32_t q = 0;
+    if (lane == 0) q = atomicAdd(queue, 1u);
+    q = __shfl_sync(0xffffffffu, q, 0);
+    if (q >= n_todo) break;
+    const uint32_t idx = todo[q];
+    ball_clear(A, live, co);
+    int r = dball_build(adj, cand[idx], limit, A, live, co);
+    uint32_t exp = 0;
+    if (r != kDlsSetFull) {
+      dball_contract(A, live, C, co);
+      if (lane == 0) r = dball_dfs(C, limit, stk, stk_cap, exp);
+      __syncwarp();
+    }
+    if (lane == 0) {
+      result[idx] = (int8_t)r;
+      if (per_search) per_search[idx] = exp;
+      if (r >= 0) exp_total += exp;
+    }
+  }
+  __syncwarp();
+  ball_clear(A, live, co);  // the index is left empty for the next launch
+  if (lane == 0 && exp_total) atomicAdd(expansions, exp_total);
+}
+
 // Last tier (exact fallback when the largest hash set fills up): one block per candidate, `seen` is a full
 // bitmap over the graph's items; thread 0 searches, the block clears the bitmap afterwards.
 __global__ void __launch_bounds__(256) k_dls_big(const uint64_t *__restrict__ adj, const uint32_t *__restrict__ cand,
@@ -215,14 +262,54 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
   const bool verbose = getenv("MCAAT_DLS_VERBOSE") != nullptr;
   DevBuf per_search;
   if (verbose) MG_TRY(per_search.alloc(n * 4));
+  const bool use_ball = env_u32("MCAAT_DLS_BALL", 1, 0, 1) != 0;
   for (int tier = 0; tier < 2; ++tier) {
     const uint64_t n_work = tier == 0 ? n : todo.size();
-    if (n_work == 0 || (tier == 1 && tier_log[1] <= tier_log[0])) continue;
+    if (n_work == 0 || (tier == 1 && !use_ball && tier_log[1] <= tier_log[0])) continue;
+    if (tier == 1 && use_ball) {
+      // ---- long searches: one warp each on the extracted ball (arenas shared with the enumeration pipeline)
+      const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32);
+      const uint32_t want = (uint32_t)std::min<uint64_t>(n_work, (uint64_t)g->sm_count * workers_per_sm);
+      const uint32_t blocks = (want + kDlsBallWarps - 1) / kDlsBallWarps, workers = blocks * kDlsBallWarps;
+      const BallLayout L = make_ball_layout(limit, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 17),
+                                            std::min<uint32_t>(ball_smem_per_worker(g, workers_per_sm, kDlsBallWarps),
+                                                               env_u32("MCAAT_ENUM_SMEM_PER_WORKER", 1u << 20, 2048, 1u << 20)));
+      const uint32_t stk_entries = (uint32_t)(4 * limit + 8);
+      const uint32_t stk_smem = (size_t)stk_entries * 4 * kDlsBallWarps <= 48 * 1024 ? stk_entries : 0;  // else: in the arena
+      if ((size_t)stk_entries * 4 > (size_t)L.cyc_cap * 4) {
+        set_error("mg_dls: limit %d: DFS stack does not fit the worker arena (internal)", limit);
+        return MG_EINTERNAL;
+      }
+      MG_TRY(ensure_ball_arena(g, workers, L));
+      MG_TRY(todo_b.alloc(todo.size() * 4));
+      MG_CUDA(cudaMemcpyAsync(todo_b.p, todo.data(), todo.size() * 4, cudaMemcpyHostToDevice, s));
+      MG_CUDA(cudaMemsetAsync(ctr.p, 0, 4, s));
+      {
+        TimedScope ts(g, T_DLS, 0);
+        MG_LAUNCH(k_dls_ball, blocks, 32 * kDlsBallWarps, (size_t)stk_smem * 4 * kDlsBallWarps, s, g->adj.as<uint64_t>(), ids_dev,
+                  todo_b.as<uint32_t>(), (uint32_t)n_work, limit, g->enum_arena.as<uint8_t>(), L, result.as<int8_t>(),
+                  ctr.as<uint32_t>(), exp_dev, verbose ? per_search.as<uint32_t>() : nullptr, stk_smem);
+      }
+      MG_CUDA(cudaMemcpyAsync(res.data(), result.p, n, cudaMemcpyDeviceToHost, s));
+      MG_CUDA(cudaStreamSynchronize(s));
+      std::vector<uint32_t> next;
+      for (uint32_t i : todo) {
+        if (res[i] == kDlsSetFull) next.push_back(i);
+        else if (res[i] == kDlsStackFull) {
+          set_error("mg_dls: DFS stack bound violated (internal)");
+          return MG_EINTERNAL;
+        }
+      }
+      if (verbose) fprintf(stderr, "[mg_dls] ball tier: %llu searches, %zu overflowed\n", (unsigned long long)n_work, next.size());
+      todo.swap(next);
+      continue;
+    }
     // tier 1: 128-thread blocks, stacks in global memory; tier 2: 32-thread blocks, stacks in shared memory
     const int tblock = tier == 0 ? block : 32;
     uint32_t blocks = (uint32_t)std::min<uint64_t>((tier_threads[tier] + tblock - 1) / tblock, (n_work + tblock - 1) / tblock);
     const size_t threads = (size_t)blocks * tblock;
-    const size_t smem = tier == 0 ? 0 : (size_t)tblock * A.stk_cap * 14;
+    size_t smem = tier == 0 ? 0 : (size_t)tblock * A.stk_cap * 14;
+    if (smem > g->smem_per_block_optin) smem = 0;  // long searches with a large depth limit: stacks in global memory
     if (smem) MG_CUDA(cudaFuncSetAttribute(k_dls, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     A.log2cap = tier_log[tier];
     A.max_count = (1u << A.log2cap) / 2;
@@ -231,7 +318,7 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
     MG_TRY(slotlog.alloc(threads * A.max_count * 2));
     MG_TRY(sn.ensure(threads * A.stk_cap * 4));
     MG_TRY(sd.ensure(threads * A.stk_cap * 2));
-    if (tier == 0) MG_TRY(sa.ensure(threads * A.stk_cap * 8));
+    if (tier == 0 || !smem) MG_TRY(sa.ensure(threads * A.stk_cap * 8));
     MG_CUDA(cudaMemsetAsync(tabs.p, 0xFF, tabs.bytes, s));
     MG_CUDA(cudaMemsetAsync(ctr.p, 0, 4, s));
     if (tier == 1) {
@@ -247,7 +334,7 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
       TimedScope ts(g, T_DLS, tier == 0 ? n : 0);
       MG_LAUNCH(k_dls, blocks, tblock, smem, s, g->adj.as<uint64_t>(), ids_dev, tier == 0 ? nullptr : todo_b.as<uint32_t>(),
                 (uint32_t)n_work, limit, A, result.as<int8_t>(), ctr.as<uint32_t>(), exp_dev,
-                verbose ? per_search.as<uint32_t>() : nullptr, tier == 0 ? 0 : 1);
+                verbose ? per_search.as<uint32_t>() : nullptr, smem ? 1 : 0);
     }
     if (verbose) {
       std::vector<uint32_t> ps(n);

@@ -357,6 +357,10 @@ int emu_dls_bitmap(Emu *e, uint64_t start, int limit) {
   return dls_run(e->adj.data(), (uint32_t)start, limit, s, sn.data(), sd.data(), sa.data(), (uint32_t)sn.size(), exp);
 }
 
+// DepthLevelSearch on the extracted, contracted ball (dball_*: the middle tier of run_dls, starts.cu); returns the
+// dls_run code (kDlsSetFull when the ball does not fit 2^ball_log / 2 nodes)
+int emu_dls_ball(Emu *e, uint64_t start, int limit, uint32_t ball_log, uint64_t *expansions, uint64_t *n_chains);
+
 // 0 = hash-map search (enum_run) only, 1 = extracted-ball search node by node (ball_dfs) with enum_run as overflow
 // fallback, 2 = the same on the contracted ball (sball_dfs; what k_enum_pipeline runs)
 static int g_algo = 2;
@@ -577,6 +581,24 @@ int emu_find_cycles(Emu *e, const uint64_t *starts, uint64_t n, int min_len, int
     stats[2] += RR.status == kEnumCap;
   }
   return 0;
+}
+
+int emu_dls_ball(Emu *e, uint64_t start, int limit, uint32_t ball_log, uint64_t *expansions, uint64_t *n_chains) {
+  BallSlot bs;
+  bs.init(limit, ball_log);
+  Coop co;
+  uint32_t nn = 0;
+  int r = dball_build(e->adj.data(), (uint32_t)start, limit, bs.A, nn, co);
+  if (n_chains) *n_chains = 0;
+  if (r == kDlsSetFull) return r;
+  std::vector<DChain> C(nn + 1);
+  uint32_t nc = dball_contract(bs.A, nn, C.data(), co);
+  if (n_chains) *n_chains = nc;
+  std::vector<uint32_t> stk(4 * limit + 8);
+  uint32_t exp = 0;
+  r = dball_dfs(C.data(), limit, stk.data(), (uint32_t)stk.size(), exp);
+  if (expansions) *expansions += exp;
+  return r;
 }
 
 void emu_set_algo(int algo, uint32_t ball_log) {

@@ -42,6 +42,8 @@ def lib():
         L.emu_bucket.argtypes = [C.c_void_p, C.c_uint64]
         L.emu_dls.restype = C.c_int
         L.emu_dls.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p]
+        L.emu_dls_ball.restype = C.c_int
+        L.emu_dls_ball.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p]
         L.emu_dls_bitmap.restype = C.c_int
         L.emu_dls_bitmap.argtypes = [C.c_void_p, C.c_uint64, C.c_int]
         L.emu_find_cycles.restype = C.c_int
@@ -146,6 +148,12 @@ class EmuGraph:
     def dls(self, start, limit, log2cap=11):
         exp = C.c_uint64(0)
         return lib().emu_dls(self.h, int(start), limit, log2cap, C.byref(exp)), exp.value
+
+    def dls_ball(self, start, limit, ball_log=16):
+        """(code, expansions, chains) of the admission search on the extracted, contracted ball"""
+        exp, nc = C.c_uint64(0), C.c_uint64(0)
+        r = lib().emu_dls_ball(self.h, int(start), limit, ball_log, C.byref(exp), C.byref(nc))
+        return r, exp.value, nc.value
 
     def dls_bitmap(self, start, limit):
         return lib().emu_dls_bitmap(self.h, int(start), limit)

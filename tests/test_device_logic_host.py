@@ -105,6 +105,30 @@ def test_small_arena_overflow_is_rerun_exactly():
     assert got.stats["overflow_reruns"] > 0
 
 
+@pytest.mark.parametrize("name,thr", [("strain", 10), ("repeatrich", 5), ("biallelic", 10), ("tiny", 5)])
+def test_dls_on_the_contracted_ball_equals_the_literal_search(name, thr):
+    """dball_build / dball_contract / dball_dfs (the tier of the long admission searches) against dls_run on the graph
+    itself: verdict AND expansion count, at depth limits that cut chains in the middle; small balls overflow"""
+    g = emu(name)
+    g.prune()
+    cand = [int(c) for c in g.candidates(thr)]
+    rng = np.random.default_rng(7)
+    if len(cand) > 250:
+        cand = [cand[i] for i in sorted(rng.choice(len(cand), 250, replace=False))]
+    found = contracted = overflow = 0
+    for limit in (77, 12, 33, 120, 1000):
+        for c in cand:
+            want, want_exp = g.dls(c, limit, log2cap=16)
+            assert want in (0, 1)
+            got, got_exp, chains = g.dls_ball(c, limit)
+            assert (got, got_exp) == (want, want_exp), (name, c, limit)
+            found += got
+            contracted += chains > 0
+            if g.dls_ball(c, limit, ball_log=6)[0] == -1:
+                overflow += 1
+    assert found > 0 and contracted > 0 and overflow > 0
+
+
 @pytest.mark.parametrize("name", ["tiny", "strain", "repeatrich"])
 def test_peel_variants_agree(name):
     """splitter-based chain resolution (forward / reverse item order) == exhaustive pointer jumping (2, 3);
