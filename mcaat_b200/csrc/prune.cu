@@ -310,19 +310,18 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
   // --- RecursiveReduction for every tip (:440-442), valid-edge count (:443-449), CollectTips (:451)
   MG_TRY(g->adj.ensure((size_t)n * 8 + 16));
   if (n) {
-    DevBuf ptr, chain, tpeeled, dep, work, next;
-    MG_TRY(ptr.alloc((size_t)n * 4 + 16));
+    DevBuf ent, chain, tpeeled, dep, work, next;
+    MG_TRY(ent.alloc((size_t)n * 8 + 16));
     MG_TRY(chain.alloc(bm_bytes));
     MG_TRY(tpeeled.alloc(bm_bytes));
     PeelView P;
     P.adj = g->adj.as<uint64_t>();
-    P.ptr = ptr.as<uint32_t>();
+    P.ent = ent.as<uint64_t>();
     P.chain = chain.as<uint32_t>();
     P.tpeeled = tpeeled.as<uint32_t>();
     P.tipbits = tipbits.as<uint32_t>();
     P.dep = nullptr;
     P.dep_log = 0;
-    P.owner = nullptr;
     {
       TimedScope ts(g, T_ADJ, n);
       MG_LAUNCH(k_chain_init, stream_grid(g, n, 256), 256, 0, s, v, P, c + 5);
@@ -333,12 +332,9 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     if (n_work) {
       int *unresolved = (int *)(c + 7), *capped = (int *)(c + 7) + 1;
       {  // chain nodes -> terminals through 1-in-64 splitters
-        DevBuf owner, split, split_ids;
-        MG_TRY(owner.alloc((size_t)n * 4 + 16));
+        DevBuf split, split_ids;
         MG_TRY(split.alloc(bm_bytes));
-        MG_CUDA(cudaMemsetAsync(owner.p, 0xFF, owner.bytes, s));
         MG_CUDA(cudaMemsetAsync(c + 7, 0, 8, s));
-        P.owner = owner.as<uint32_t>();
         MG_LAUNCH(k_split_mark, stream_grid(g, n, 256), 256, 0, s, n, P, split.as<uint32_t>());
         uint64_t n_split = 0;
         MG_TRY(bitmap_to_ids(split.as<uint32_t>(), n, split_ids, &n_split, s));
@@ -358,7 +354,6 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
         int hc = 0;
         MG_CUDA(cudaMemcpyAsync(&hc, capped, 4, cudaMemcpyDeviceToHost, s));
         MG_CUDA(cudaStreamSynchronize(s));
-        P.owner = nullptr;
         if (hc || getenv("MCAAT_PEEL_EXHAUSTIVE")) {  // a walk hit its hop cap: exhaustive pointer jumping
           if (getenv("MCAAT_PEEL_VERBOSE")) fprintf(stderr, "[peel] exhaustive pointer jumping (walk cap hit: %d)\n", hc);
           for (int round = 0; round < 34; round += 2) {

@@ -83,14 +83,17 @@ MG_HD void fence_sc() {
 //      evaluated by an asynchronous work list over a (terminal -> dependent branch nodes) multimap.
 struct PeelView {
   uint64_t *adj;            // per item: Forward | validity mask << 32 on the post-filter graph
-  uint32_t *ptr;            // chain pointer
+  uint64_t *ent;            // per item: chain pointer (low word) | owner: splitter whose walk passed the item, step 2
+                            // (bits 32..62, kNoOwner = none) | item was classified a chain node by step 1 (bit 63).
+                            // One 8-byte entry = one sector per hop of a walk.
   uint32_t *chain;          // bitmap: chain nodes
   uint32_t *tpeeled;        // bitmap: peeled terminals
   const uint32_t *tipbits;  // bitmap: CollectTips on the loaded graph (:436)
   uint64_t *dep;            // multimap entries (terminal << 32 | branch node), empty = ~0
   uint32_t dep_log;
-  uint32_t *owner;          // splitter whose walk passed the item (kNull = none), step 2
 };
+constexpr uint32_t kNoOwner = 0x7FFFFFFFu, kEntChain = 0x80000000u;
+MG_HD uint32_t &peel_ptr(const PeelView &P, uint32_t v) { return ((uint32_t *)P.ent)[2 * (size_t)v]; }
 MG_HD bool bm_get(const uint32_t *bm, uint32_t i) { return (bm[i >> 5] >> (i & 31)) & 1; }
 MG_HD bool bm_get_coherent(const uint32_t *bm, uint32_t i) { return (ld_cg32(&bm[i >> 5]) >> (i & 31)) & 1; }
 // returns true when this call set the bit
@@ -117,24 +120,27 @@ MG_HD int chain_init_item(const GraphView &g, const PeelView &P, uint32_t v, boo
   uint64_t a = adj_encode(g, v);
   P.adj[v] = a;
   is_chain = is_seed = false;
-  P.ptr[v] = v;
-  if (get_inv(g, v)) return -1;
-  uint32_t mask = (uint32_t)(a >> 32) & 0xFFu;
-  int deg = popc32(mask);
-  if (deg == 1) {
-    is_chain = true;
-    P.ptr[v] = (uint32_t)a - (uint32_t)ctz32(mask);
-  } else if (deg == 0) {
-    is_seed = bm_get(P.tipbits, v);  // a collected tip that survived the multiplicity filter
+  uint32_t ptr = v;
+  int deg = -1;
+  if (!get_inv(g, v)) {
+    uint32_t mask = (uint32_t)(a >> 32) & 0xFFu;
+    deg = popc32(mask);
+    if (deg == 1) {
+      is_chain = true;
+      ptr = (uint32_t)a - (uint32_t)ctz32(mask);
+    } else if (deg == 0) {
+      is_seed = bm_get(P.tipbits, v);  // a collected tip that survived the multiplicity filter
+    }
   }
+  P.ent[v] = (uint64_t)ptr | ((uint64_t)(kNoOwner | (is_chain ? kEntChain : 0u)) << 32);
   return deg;
 }
 // Step 2, one round for one item; returns true while the item is still unresolved.
 MG_HD bool chain_jump_item(const PeelView &P, uint32_t v) {
   if (!bm_get(P.chain, v)) return false;
-  uint32_t p = P.ptr[v];
+  uint32_t p = peel_ptr(P, v);
   if (!bm_get(P.chain, p)) return false;
-  P.ptr[v] = P.ptr[p];
+  peel_ptr(P, v) = peel_ptr(P, p);
   return true;
 }
 // Step 2, work-efficient form.  Pointer jumping over ALL chain nodes costs one pass over the graph
@@ -154,43 +160,52 @@ MG_HD bool chain_jump_item(const PeelView &P, uint32_t v) {
 constexpr uint32_t kWalkCapSplitter = 1u << 16, kWalkCapHead = 1u << 12;
 MG_HD bool is_splitter_id(uint32_t v) { return ((v * 0x9E3779B1u) >> 26) == 0; }
 MG_HD uint32_t ld_cg_u32(const uint32_t *p) { return ld_cg32(p); }
-MG_HD uint32_t owner_claim(uint32_t *p, uint32_t s) {
+MG_HD uint64_t ent_cas(uint64_t *p, uint64_t expect, uint64_t val) {
 #if defined(__CUDA_ARCH__)
-  return atomicCAS(p, kNull, s);
+  return (uint64_t)atomicCAS((unsigned long long *)p, (unsigned long long)expect, (unsigned long long)val);
 #else
-  uint32_t old = *p;
-  if (old == kNull) *p = s;
+  uint64_t old = *p;
+  if (old == expect) *p = val;
   return old;
 #endif
 }
 // a. walk of splitter s; returns false when the hop cap was hit (ptr[s] is then left untouched)
 MG_HD bool split_walk_item(const PeelView &P, uint32_t s) {
-  uint32_t p = P.ptr[s], next = kNull;
+  uint32_t p = peel_ptr(P, s), next = kNull;
   for (uint32_t hops = 0; hops < kWalkCapSplitter; ++hops) {
-    if (!bm_get(P.chain, p) || is_splitter_id(p)) { next = p; break; }
-    uint32_t old = owner_claim(&P.owner[p], s);
-    if (old != kNull) { next = old; break; }  // old == s: the walk has run into a splitter-free cycle
-    p = ld_cg_u32(&P.ptr[p]);
+    if (is_splitter_id(p)) { next = p; break; }      // another splitter (or a terminal whose id hashes like one)
+    const uint64_t e = ld_cg64(&P.ent[p]);
+    const uint32_t hi = (uint32_t)(e >> 32);
+    if (!(hi & kEntChain)) { next = p; break; }      // terminal
+    if ((hi & kNoOwner) != kNoOwner) { next = hi & kNoOwner; break; }  // claimed; == s: a splitter-free cycle
+    // nobody writes the pointer of an unclaimed non-splitter chain node during the walks, so a failed exchange
+    // means another walk has claimed the item in between
+    const uint64_t old = ent_cas(&P.ent[p], e, (e & 0x80000000FFFFFFFFull) | ((uint64_t)s << 32));
+    if (old != e) { next = (uint32_t)(old >> 32) & kNoOwner; break; }
+    p = (uint32_t)e;
   }
   if (next == kNull) return false;
-  P.ptr[s] = next;
+  peel_ptr(P, s) = next;
   return true;
 }
 // b. one pointer-jumping round for splitter s; returns true while it is still unresolved
 MG_HD bool split_jump_item(const PeelView &P, uint32_t s) {
-  uint32_t p = ld_cg_u32(&P.ptr[s]);
+  uint32_t p = ld_cg_u32(&peel_ptr(P, s));
   if (!bm_get(P.chain, p) || p == s) return false;  // terminal reached / known to be unresolvable
-  uint32_t q = ld_cg_u32(&P.ptr[p]);
+  uint32_t q = ld_cg_u32(&peel_ptr(P, p));
   if (q == p) q = s;  // the splitter ahead is unresolvable, so is this one
-  P.ptr[s] = q;
+  peel_ptr(P, s) = q;
   return true;
 }
 // c. every chain node that is not a splitter; returns false when the hop cap was hit
 MG_HD bool chain_resolve_item(const PeelView &P, uint32_t v) {
-  if (!bm_get(P.chain, v) || is_splitter_id(v)) return true;
-  uint32_t o = P.owner[v];
-  if (o != kNull) { P.ptr[v] = ld_cg_u32(&P.ptr[o]); return true; }
-  uint32_t p = ld_cg_u32(&P.ptr[v]);
+  if (is_splitter_id(v)) return true;
+  const uint64_t ev = P.ent[v];
+  const uint32_t hv = (uint32_t)(ev >> 32);
+  if (!(hv & kEntChain)) return true;
+  uint32_t o = hv & kNoOwner;
+  if (o != kNoOwner) { peel_ptr(P, v) = ld_cg_u32(&peel_ptr(P, o)); return true; }
+  uint32_t p = (uint32_t)ev;
   // Brent's cycle detection: `mark` is the item the walk stood on 2^j hops after v.  A walk that comes back to
   // it runs round a cycle of chain nodes with neither splitter nor owner (the closed loop of a tandem repeat
   // whose entry and exit were filtered out has ~50 nodes, so about half of them hold no 1-in-64 splitter):
@@ -198,20 +213,27 @@ MG_HD bool chain_resolve_item(const PeelView &P, uint32_t v) {
   // writes a pointer on such a component, so the walk is deterministic: <= 3 x (tail + cycle) hops.
   uint32_t mark = v, since = 0, power = 1;
   for (uint32_t hops = 0; hops < kWalkCapHead; ++hops) {
-    if (!bm_get(P.chain, p)) { P.ptr[v] = p; return true; }
-    if (is_splitter_id(p)) { P.ptr[v] = ld_cg_u32(&P.ptr[p]); return true; }
-    o = ld_cg_u32(&P.owner[p]);
-    if (o != kNull) { P.ptr[v] = ld_cg_u32(&P.ptr[o]); return true; }
+    if (is_splitter_id(p)) {
+      // a chain splitter knows its terminal; an item that merely hashes like one is a terminal itself
+      const uint64_t ep = ld_cg64(&P.ent[p]);
+      peel_ptr(P, v) = ((uint32_t)(ep >> 32) & kEntChain) ? (uint32_t)ep : p;
+      return true;
+    }
+    const uint64_t ep = ld_cg64(&P.ent[p]);  // one entry: chain flag, owner and successor of p
+    const uint32_t hp = (uint32_t)(ep >> 32);
+    if (!(hp & kEntChain)) { peel_ptr(P, v) = p; return true; }
+    o = hp & kNoOwner;
+    if (o != kNoOwner) { peel_ptr(P, v) = ld_cg_u32(&peel_ptr(P, o)); return true; }
     if (p == mark) return true;
     if (++since == power) { mark = p; power <<= 1; since = 0; }
-    p = ld_cg_u32(&P.ptr[p]);  // the successor, or already p's terminal: both lie ahead on the same chain
+    p = (uint32_t)ep;  // the successor, or already p's terminal: both lie ahead on the same chain
   }
   return false;
 }
 // terminal of an out-neighbour (kNull when it sits on an unresolvable chain cycle)
 MG_HD uint32_t terminal_of(const PeelView &P, uint32_t c) {
   if (!bm_get(P.chain, c)) return c;
-  uint32_t t = ld_ro(&P.ptr[c]);
+  uint32_t t = ld_ro(&peel_ptr(P, c));
   return bm_get(P.chain, t) ? kNull : t;
 }
 // Step 2b: UNARY branch nodes.  A branch node whose out-neighbours all resolve to terminals that are
@@ -238,23 +260,23 @@ MG_HD int reclass_item(const GraphView &g, const PeelView &P, uint32_t b) {
     else if (uniq != tc) return 0;                 // two distinct open dependencies: a true AND node
   }
   if (uniq == kNull) return 2;
-  P.ptr[b] = uniq;
+  peel_ptr(P, b) = uniq;
   return 1;
 }
 // resolution among the re-classified nodes of one round (`fresh` = their bitmap); true while unresolved
 MG_HD bool reclass_jump_item(const PeelView &P, const uint32_t *fresh, uint32_t b) {
-  uint32_t p = ld_cg_u32(&P.ptr[b]);
+  uint32_t p = ld_cg_u32(&peel_ptr(P, b));
   if (!bm_get(fresh, p) || p == b) return false;
-  uint32_t q = ld_cg_u32(&P.ptr[p]);
+  uint32_t q = ld_cg_u32(&peel_ptr(P, p));
   if (q == p) q = b;  // the node ahead is known to be cyclic, so is this one
-  P.ptr[b] = q;
+  peel_ptr(P, b) = q;
   return true;
 }
 // chain nodes whose terminal has just been re-classified move on to that node's terminal
 MG_HD void relink_item(const PeelView &P, const uint32_t *fresh, uint32_t v) {
   if (!bm_get(P.chain, v)) return;
-  uint32_t t = ld_cg_u32(&P.ptr[v]);
-  if (bm_get(fresh, t) && t != v) P.ptr[v] = ld_cg_u32(&P.ptr[t]);
+  uint32_t t = ld_cg_u32(&peel_ptr(P, v));
+  if (bm_get(fresh, t) && t != v) peel_ptr(P, v) = ld_cg_u32(&peel_ptr(P, t));
 }
 MG_HD void dep_insert(const PeelView &P, uint32_t term, uint32_t b) {
   uint32_t mask = (1u << P.dep_log) - 1, h = hash_u32_fwd(term, P.dep_log);

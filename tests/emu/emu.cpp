@@ -139,7 +139,8 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   GraphView &v = e->v;
   const uint64_t n = v.n;
   const size_t words = (n + 31) / 32 + 1;
-  std::vector<uint32_t> tipbits(words, 0), chain(words, 0), tpeeled(words, 0), ptr(n + 1);
+  std::vector<uint32_t> tipbits(words, 0), chain(words, 0), tpeeled(words, 0);
+  std::vector<uint64_t> ent(n + 1);
   uint64_t tips0 = 0;
   if (reverse_order & 1) {  // CollectTips literally ...
     for (uint64_t i = 0; i < n; ++i)
@@ -158,8 +159,8 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   stats[1] = m1;
   e->adj.assign(n + 1, 0);
   PeelView P;
-  P.adj = e->adj.data(); P.ptr = ptr.data(); P.chain = chain.data(); P.tpeeled = tpeeled.data();
-  P.tipbits = tipbits.data(); P.dep = nullptr; P.dep_log = 0; P.owner = nullptr;
+  P.adj = e->adj.data(); P.ent = ent.data(); P.chain = chain.data(); P.tpeeled = tpeeled.data();
+  P.tipbits = tipbits.data(); P.dep = nullptr; P.dep_log = 0;
   uint64_t pairs = 0;
   std::vector<uint32_t> work, next;
   for (uint64_t i = 0; i < n; ++i) {
@@ -173,8 +174,7 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   // forward or reverse item order; reverse_order & 2 forces the exhaustive pointer jumping instead
   bool capped = false;
   if (!(reverse_order & 2)) {
-    std::vector<uint32_t> owner(n + 1, kNull), split_ids;
-    P.owner = owner.data();
+    std::vector<uint32_t> split_ids;
     for (uint64_t i = 0; i < n; ++i)
       if (bm_get(P.chain, (uint32_t)i) && is_splitter_id((uint32_t)i)) split_ids.push_back((uint32_t)i);
     if (reverse_order & 1) std::reverse(split_ids.begin(), split_ids.end());
@@ -186,7 +186,6 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
     }
     if (reverse_order & 1) { for (uint64_t i = n; i-- > 0;) capped |= !chain_resolve_item(P, (uint32_t)i); }
     else for (uint64_t i = 0; i < n; ++i) capped |= !chain_resolve_item(P, (uint32_t)i);
-    P.owner = nullptr;
   }
   if (capped || (reverse_order & 2))
     for (int round = 0; round < 34; ++round) {
