@@ -167,9 +167,9 @@ __global__ void k_or_words(uint32_t *dst, const uint32_t *src, size_t n_words) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n_words) dst[i] |= src[i];
 }
-__global__ void k_relink(uint64_t n, PeelView P, const uint32_t *fresh) {
+__global__ void k_relink_final(uint64_t n, PeelView P) {
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
-    relink_item(P, fresh, (uint32_t)i);
+    relink_final_item(P, (uint32_t)i);
 }
 // exhaustive fallback: one pointer-jumping round over every item
 __global__ void k_chain_jump(uint64_t n, PeelView P, int *unresolved) {
@@ -310,7 +310,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
   // --- RecursiveReduction for every tip (:440-442), valid-edge count (:443-449), CollectTips (:451)
   MG_TRY(g->adj.ensure((size_t)n * 8 + 16));
   if (n) {
-    DevBuf ent, chain, tpeeled, dep, work, next;
+    DevBuf ent, chain, tpeeled, dep, work, next, recl;
     MG_TRY(ent.alloc((size_t)n * 8 + 16));
     MG_TRY(chain.alloc(bm_bytes));
     MG_TRY(tpeeled.alloc(bm_bytes));
@@ -320,6 +320,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     P.chain = chain.as<uint32_t>();
     P.tpeeled = tpeeled.as<uint32_t>();
     P.tipbits = tipbits.as<uint32_t>();
+    P.recl = nullptr;
     P.dep = nullptr;
     P.dep_log = 0;
     {
@@ -369,6 +370,9 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
       }
       if (!getenv("MCAAT_PEEL_NO_RECLASS")) {  // unary branch nodes -> chain nodes, a few rounds
         DevBuf fresh, newseed, fresh_ids;
+        MG_TRY(recl.alloc(bm_bytes));
+        MG_CUDA(cudaMemsetAsync(recl.p, 0, bm_bytes, s));
+        P.recl = recl.as<uint32_t>();
         MG_TRY(fresh.alloc(bm_bytes));
         MG_TRY(newseed.alloc(bm_bytes));
         const size_t n_words = (size_t)((n + 31) / 32);
@@ -394,8 +398,10 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
               MG_CUDA(cudaStreamSynchronize(s));
               if (!h) break;
             }
+            // the round's nodes are chain nodes from now on; pointers that name one of them as a terminal are
+            // followed through it by terminal_of (no pass over the items)
             MG_LAUNCH(k_or_words, grid_for(n_words, 256), 256, 0, s, chain.as<uint32_t>(), fresh.as<uint32_t>(), n_words);
-            MG_LAUNCH(k_relink, stream_grid(g, n, 256), 256, 0, s, n, P, fresh.as<uint32_t>());
+            MG_LAUNCH(k_or_words, grid_for(n_words, 256), 256, 0, s, recl.as<uint32_t>(), fresh.as<uint32_t>(), n_words);
           }
           if (hc[1])
             MG_LAUNCH(k_or_words, grid_for(n_words, 256), 256, 0, s, tpeeled.as<uint32_t>(), newseed.as<uint32_t>(), n_words);
@@ -403,6 +409,8 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
             fprintf(stderr, "[peel] reclass round %d: %llu unary branch nodes, %llu new seeds\n", round, hc[0], hc[1]);
           if (hc[0] + hc[1] < 64) break;
         }
+        MG_LAUNCH(k_relink_final, stream_grid(g, n, 256), 256, 0, s, n, P);
+        P.recl = nullptr;
         MG_TRY(bitmap_to_ids(tpeeled.as<uint32_t>(), n, work, &n_work, s));  // collected tips + new seeds
       }
       unsigned long long pairs = 0;

@@ -89,6 +89,7 @@ struct PeelView {
   uint32_t *chain;          // bitmap: chain nodes
   uint32_t *tpeeled;        // bitmap: peeled terminals
   const uint32_t *tipbits;  // bitmap: CollectTips on the loaded graph (:436)
+  const uint32_t *recl;     // bitmap: branch nodes re-classified as chain nodes by step 2b (all rounds so far)
   uint64_t *dep;            // multimap entries (terminal << 32 | branch node), empty = ~0
   uint32_t dep_log;
 };
@@ -230,11 +231,23 @@ MG_HD bool chain_resolve_item(const PeelView &P, uint32_t v) {
   }
   return false;
 }
-// terminal of an out-neighbour (kNull when it sits on an unresolvable chain cycle)
+// terminal of an out-neighbour (kNull when it sits on an unresolvable chain cycle).  A chain node's pointer names
+// the terminal its chain ended in when it was resolved; if step 2b has re-classified that terminal as a chain node
+// since, the walk goes on through it (at most one hop per round of step 2b) — this replaces a pass over all items
+// per round that moved every such pointer on.
 MG_HD uint32_t terminal_of(const PeelView &P, uint32_t c) {
+  // (chain / recl bitmaps and the pointers of chain nodes are not written by the kernels that call this)
   if (!bm_get(P.chain, c)) return c;
   uint32_t t = ld_ro(&peel_ptr(P, c));
-  return bm_get(P.chain, t) ? kNull : t;
+  if (!bm_get(P.chain, t)) return t;
+  for (int hop = 0; hop < 8; ++hop) {
+    if (!P.recl || !bm_get(P.recl, t)) return kNull;            // an original chain node: a cycle of chain nodes
+    const uint32_t t2 = ld_ro(&peel_ptr(P, t));
+    if (t2 == t) return kNull;                                  // known to be cyclic (reclass_jump_item)
+    t = t2;
+    if (!bm_get(P.chain, t)) return t;
+  }
+  return kNull;
 }
 // Step 2b: UNARY branch nodes.  A branch node whose out-neighbours all resolve to terminals that are
 // already peeled (collected tips) — except for ONE distinct terminal T — is peeled iff T is: for the
@@ -272,11 +285,21 @@ MG_HD bool reclass_jump_item(const PeelView &P, const uint32_t *fresh, uint32_t 
   peel_ptr(P, b) = q;
   return true;
 }
-// chain nodes whose terminal has just been re-classified move on to that node's terminal
-MG_HD void relink_item(const PeelView &P, const uint32_t *fresh, uint32_t v) {
+// After the last round of step 2b: every chain node takes its final terminal (one pass instead of one per round;
+// terminal_of needs no second hop afterwards, the caller clears P.recl).  A node on an unresolvable cycle keeps its
+// pointer to a chain node.
+MG_HD void relink_final_item(const PeelView &P, uint32_t v) {
   if (!bm_get(P.chain, v)) return;
-  uint32_t t = ld_cg_u32(&peel_ptr(P, v));
-  if (bm_get(fresh, t) && t != v) peel_ptr(P, v) = ld_cg_u32(&peel_ptr(P, t));
+  const uint32_t t = ld_cg_u32(&peel_ptr(P, v));
+  if (!bm_get(P.chain, t)) return;  // resolved, terminal untouched by step 2b: the common case
+  uint32_t u = t;
+  for (int hop = 0; hop < 8; ++hop) {
+    if (!bm_get(P.recl, u)) return;
+    const uint32_t u2 = ld_cg_u32(&peel_ptr(P, u));
+    if (u2 == u) return;
+    u = u2;
+    if (!bm_get(P.chain, u)) { peel_ptr(P, v) = u; return; }
+  }
 }
 MG_HD void dep_insert(const PeelView &P, uint32_t term, uint32_t b) {
   uint32_t mask = (1u << P.dep_log) - 1, h = hash_u32_fwd(term, P.dep_log);

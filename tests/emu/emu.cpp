@@ -161,6 +161,8 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   PeelView P;
   P.adj = e->adj.data(); P.ent = ent.data(); P.chain = chain.data(); P.tpeeled = tpeeled.data();
   P.tipbits = tipbits.data(); P.dep = nullptr; P.dep_log = 0;
+  std::vector<uint32_t> recl(words, 0);
+  P.recl = recl.data();
   uint64_t pairs = 0;
   std::vector<uint32_t> work, next;
   for (uint64_t i = 0; i < n; ++i) {
@@ -209,10 +211,12 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
         for (uint32_t b : ids) any |= reclass_jump_item(P, fresh.data(), b);
         if (!any) break;
       }
-      for (size_t w = 0; w < words; ++w) { chain[w] |= fresh[w]; tpeeled[w] |= newseed[w]; }
-      if (nf) for (uint64_t i = 0; i < n; ++i) relink_item(P, fresh.data(), (uint32_t)i);
+      for (size_t w = 0; w < words; ++w) { chain[w] |= fresh[w]; recl[w] |= fresh[w]; tpeeled[w] |= newseed[w]; }
       if (nf + ns < 64) break;
     }
+    if (reverse_order & 1) { for (uint64_t i = n; i-- > 0;) relink_final_item(P, (uint32_t)i); }
+    else for (uint64_t i = 0; i < n; ++i) relink_final_item(P, (uint32_t)i);
+    P.recl = nullptr;
     work.clear();
     for (uint64_t i = 0; i < n; ++i)
       if (bm_get(P.tpeeled, (uint32_t)i)) work.push_back((uint32_t)i);
