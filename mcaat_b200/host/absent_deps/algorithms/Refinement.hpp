@@ -1,3 +1,3 @@
 #pragma once
-// TEST INFRASTRUCTURE. See core/cft.hpp in this directory.
+// STAND-IN: see core/cft.hpp in this directory.
 #include "core/cft.hpp"

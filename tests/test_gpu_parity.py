@@ -184,6 +184,44 @@ def test_cpp_drop_in_prints_the_reference_progress_lines(tmp_path, name):
     assert any(ln.startswith("Cycle enumeration completed") for ln in lines[ref]) and len(lines[ref]) >= 8
 
 
+@pytest.mark.parametrize("name", ["tiny", "biallelic"])
+def test_crispr_arrays_file_is_identical_end_to_end(tmp_path, name):
+    """SURVEY 8(f) N1 / north_star's second correctness criterion: the reference's release pipeline from the loaded graph
+    to CRISPR_Arrays.txt (src/main.cpp:520-580: CycleFinder -> read mapping -> region split -> set cover -> spacer ordering
+    -> CRISPRAnalyzer), every stage the reference's own unmodified translation unit, built three times:
+      oracle/_ref/ref_pipeline          with the reference's src/cycle_finder.cpp
+      host/_build/shim_pipeline         with the GPU CycleFinder drop-in
+      host/_build/shim_pipeline_all     with the GPU drop-ins for CycleFinder, get_reads and get_crispr_regions_extended_by_k
+    on the graph files of a golden case and the reads they were built from.  The output files are byte-identical, and so
+    is everything the stages print (cycle order, spacer order, repeats, confidence values) except the wall times.
+    kseq++ and cft, which this image lacks, are the same deterministic stand-ins (mcaat_b200/host/absent_deps) in all three."""
+    import os
+    import re
+    import subprocess
+    import sys
+    sys.path.insert(0, os.path.join(gpu.ROOT, "tools"))
+    import make_golden as MG
+    ref = O.ref_binary("ref_pipeline")
+    shims = [os.path.join(gpu.ROOT, "mcaat_b200", "host", "_build", b) for b in ("shim_pipeline", "shim_pipeline_all")]
+    if ref is None or not all(os.path.exists(b) for b in shims):
+        pytest.skip("reference / drop-in pipeline binaries not built (they need the reference sources at build time)")
+    prefix = G.unpack_sdbg_files(name, str(tmp_path))
+    subprocess.run([sys.executable, os.path.join(gpu.ROOT, "tools", "gen_reads.py"), "--out", str(tmp_path)] + MG.CASES[name][0],
+                   check=True, capture_output=True)
+    outs, logs = {}, {}
+    for exe in [ref] + shims:
+        out = str(tmp_path / (os.path.basename(exe) + ".CRISPR_Arrays.txt"))
+        p = subprocess.run([exe, prefix, str(tmp_path / "r1.fq"), str(tmp_path / "r2.fq"), out, "1", "20", "27", "77"],
+                           check=True, capture_output=True, text=True, env=dict(os.environ, MCAAT_GPU_GRAPH_PREFIX=prefix))
+        outs[exe] = open(out, "rb").read()
+        logs[exe] = [ln for ln in p.stdout.replace(out, "<out>").splitlines() if "Time elapsed" not in ln]
+    assert b"Number of Systems: " in outs[ref] and outs[ref].count(b"Number of Spacers: ") >= 2
+    for exe in shims:
+        assert outs[exe] == outs[ref], os.path.basename(exe)
+        assert logs[exe] == logs[ref], os.path.basename(exe)
+    assert int(re.search(r'"systems": (\d+)', "\n".join(logs[ref])).group(1)) >= 2
+
+
 def test_collect_tips_on_the_device_matches_navigation():
     """mg_collect_tips (dead ends -> incoming edges -> compaction, all on the device) == {valid, out-degree 0} from the
     per-item navigation table, on the loaded graph and again after the prune"""
