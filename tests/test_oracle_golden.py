@@ -101,3 +101,17 @@ def test_rank_select_edge_cases():
     assert L.orc_select_last(g.h, tot) == n
     assert L.orc_select_last(g.h, tot + 1) == -1
     assert L.orc_rank_last(g.h, L.orc_select_last(g.h, 5)) == 6
+
+
+def test_reference_unit_tests_pass_against_the_stand_ins():
+    """The reference's OWN unit tests (tests/test_reads.cpp: 5 of reverse_pair_ends_sequence; tests/test_spacer_ordering.cpp:
+    7 of solve_min_cover_problem), compiled unmodified (oracle/Makefile: _ref/ref_unit_tests; a minimal gtest interface
+    stands in for the absent googletest submodule) and run against the deterministic stand-ins for kseq++ and cft that the
+    end-to-end CRISPR_Arrays.txt comparison uses (mcaat_b200/host/absent_deps)."""
+    import subprocess
+    exe = O.ref_binary("ref_unit_tests")
+    if exe is None:
+        pytest.skip("oracle/_ref/ref_unit_tests not built (needs the reference sources at build time)")
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout[-2000:]
+    assert "UNIT_TESTS 12 run, 0 failed expectations" in out.stdout
