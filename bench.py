@@ -339,6 +339,8 @@ def main():
     ap.add_argument("--sweep", action="store_true",
                     help="BASELINE.json configs[4]: after the timed steps, time the hot path on the same resident graph at "
                          "cycle bounds 27-77 / 20-100 x threshold_multiplicity 10 / 20 / 50 (1 warm-up + 2 timed passes each)")
+    ap.add_argument("--no-dropin", action="store_true",
+                    help="skip the leg that times the C++ drop-in's CycleFinder constructor (shim_cyclefinder) on the bench workload")
     ap.add_argument("--regions-check", action="store_true",
                     help="also time mg_keep_regions (SURVEY 8(f) N4, k = 128) on the cycles of the bench workload")
     args = ap.parse_args()
@@ -561,6 +563,33 @@ def main():
         sample_leg = dict(workload=args.sample, n_items=int(gq.n), n_starts=int(st_s["n_starts"]),
                           ms_per_step=float(np.mean(ts_)), value=st_s["n_starts"] / (float(np.mean(ts_)) / 1e3), unit=UNIT,
                           note="graph resident, CUDA events around the step; cpu_baseline and --impl reference run this same graph")
+    # ---- SURVEY 8(d)'s T for the drop-in a maintainer links: wall time of the C++ `CycleFinder(settings)` constructor
+    #      (mcaat_b200/host/cycle_finder_gpu.cpp behind the reference's header) on the bench workload, in a fresh process:
+    #      graph onto the device (decoded from the graph files / extracted through the SDBG getters), search, results
+    #      map, write-back of the invalid bits into the host SDBG.  SDBG::LoadFromFile (host) is outside, as in the CPU arm.
+    dropin = None
+    shim = os.path.join(ROOT, "mcaat_b200", "host", "_build", "shim_cyclefinder")
+    if rank == 0 and world == 1 and not args.no_dropin and os.path.exists(shim):
+        gs, _ = S.make_workload(args.workload, device="cuda", want_labels=True)
+        tmp = tempfile.mkdtemp(prefix="mcaat_dropin_")
+        prefix = os.path.join(tmp, "graph")
+        S.write_megahit_files(gs, prefix)
+        del gs
+        dropin = {}
+        for mode, key in (("1", "device_ingest"), ("0", "sdbg_getters")):
+            best = None
+            for _ in range(2):
+                p = subprocess.run([shim, prefix, "-", str(min(16, os.cpu_count() or 1)), str(THR), str(MIN_LEN), str(MAX_LEN)],
+                                   capture_output=True, text=True, env=dict(os.environ, MCAAT_GPU_INGEST_FILES=mode, MCAAT_GPU_TIMING="1"))
+                js = [json.loads(ln[9:]) for ln in p.stdout.splitlines() if ln.startswith("REF_JSON ")]
+                tm = [json.loads(ln[16:]) for ln in p.stderr.splitlines() if ln.startswith("GPU_SHIM_TIMING ")]
+                if p.returncode == 0 and js and (best is None or js[-1]["ctor_s"] < best["ctor_ms"] / 1e3):
+                    best = dict(ctor_ms=js[-1]["ctor_s"] * 1e3, host_load_ms=js[-1]["load_s"] * 1e3, n_starts=js[-1]["start_nodes"],
+                                cycles=js[-1]["cycles"], breakdown=tm[-1] if tm else None)
+            dropin[key] = best
+        dropin["note"] = ("wall time of the C++ CycleFinder constructor in a fresh process (CUDA context creation included), best of 2; "
+                          "unit of the e2e ratio: n_starts / ctor")
+        shutil.rmtree(tmp, ignore_errors=True)
     ingest = None
     if rank == 0 and args.ingest_check:  # on-disk SDBG decoded on the device
         gs, _ = S.make_workload(args.sample, device="cuda", want_labels=True)
@@ -720,6 +749,8 @@ def main():
         line["reads"] = reads
     if e2e:
         line["e2e"] = e2e
+    if dropin:
+        line["e2e_dropin"] = dropin
     if sample_leg:
         line["same_input_as_cpu"] = sample_leg
     if cpu:

@@ -133,6 +133,26 @@ __device__ __forceinline__ void sweep_front(uint32_t *front, const uint32_t *fla
     if (!__shfl_sync(0xffffffffu, again, 0)) break;
   }
 }
+// Union-find over tickets (parent[t] <= t; the root of a group is its smallest ticket): two tickets whose balls share a
+// node are united when the later claim finds the earlier one (k_enum_pipeline).  Tickets of different groups have
+// disjoint balls and commute; inside a group commits go in ticket order.
+__device__ __forceinline__ uint32_t uf_find(uint32_t *parent, uint32_t x) {
+  for (;;) {
+    const uint32_t p = *(volatile uint32_t *)&parent[x];
+    if (p == x) return x;
+    const uint32_t gp = *(volatile uint32_t *)&parent[p];
+    if (gp != p) atomicMin(&parent[x], gp);  // path halving; parents only ever decrease
+    x = p;
+  }
+}
+__device__ __forceinline__ void uf_union(uint32_t *parent, uint32_t a, uint32_t b) {
+  for (;;) {
+    const uint32_t ra = uf_find(parent, a), rb = uf_find(parent, b);
+    if (ra == rb) return;
+    const uint32_t hi = max(ra, rb), lo = min(ra, rb);
+    if (atomicCAS(&parent[hi], hi, lo) == hi) return;
+  }
+}
 // advances a front over every ticket whose flag is set (lane 0 of any worker; used where no turn has to be announced)
 __device__ __forceinline__ void advance_front(uint32_t *front, const uint32_t *flags, uint32_t n_end) {
   for (;;) {
@@ -313,7 +333,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
                                                      int max_len, uint8_t *arena, BallLayout L, PipeCtl *ctl,
                                                      TicketRec *recs, uint32_t *pool_nodes, uint32_t pool_nodes_cap,
                                                      uint32_t *pool_len, uint32_t pool_len_cap, uint32_t *owner,
-                                                     uint32_t *built, uint32_t *done, uint32_t *go, int flags) {
+                                                     uint32_t *built, uint32_t *done, uint32_t *go, uint32_t *parent, int flags) {
   extern __shared__ __align__(16) uint8_t smem_all[];
   constexpr unsigned kFull = 0xffffffffu;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -411,7 +431,14 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
           if (st != kEnumDone) {
             if (lane == 0) atomicMin(&ctl->ooo_limit, t);
           } else {
-            for (uint32_t j = lane; j < live; j += 32) atomicMin(&owner[A.nodes[j].key], t);
+            uint32_t last = t;
+            for (uint32_t j = lane; j < live; j += 32) {
+              const uint32_t old = atomicMin(&owner[A.nodes[j].key], t);
+              if (old != 0xFFFFFFFFu && old != last) {  // another ticket's ball holds the node too: same group
+                uf_union(parent, t, old);
+                last = old;
+              }
+            }
           }
           publish_built();
         }
@@ -575,15 +602,36 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       copy_out();
       continue;
     }
-    // ---- dependent: wait for this ticket's turn; meanwhile keep the speculative result fresh, so that the
-    //      repeat of a stale search happens here, in parallel, and not inside the ordered commit.
-    //      `visited` only changes inside commits that mark nodes (mark_epoch), so the result is
-    //      re-examined only when the epoch has moved; the poll itself is one 32-byte sector and backs
-    //      off with the distance to the commit front, so waiting workers leave the L2 to the searches.
+    // ---- dependent.  Its turn has come when every earlier ticket of its GROUP is done (tickets of other groups cannot
+    //      touch its ball); the earlier tickets that are not done yet are few (the window in flight): each lane watches one.
+    //      More than 32 of them, or a ball somewhere that was claimed only in part: the turn is the commit front's.
+    uint32_t watch = 0xFFFFFFFFu;
+    bool grouped = false;
+    if (status != kEnumOverflow && !(flags & 4) && t < __shfl_sync(kFull, ld_vol(&ctl->ooo_limit), 0)) {
+      const uint32_t root = __shfl_sync(kFull, lane == 0 ? uf_find(parent, t) : 0u, 0);
+      const uint32_t front = __shfl_sync(kFull, ld_vol(&ctl->commit_idx), 0);
+      uint32_t count = 0;
+      grouped = true;
+      for (uint32_t base = front; base < t; base += 32) {
+        const uint32_t u = base + (uint32_t)lane;
+        const bool match = u < t && !ld_vol(&done[u]) && uf_find(parent, u) == root;
+        const unsigned m = __ballot_sync(kFull, match);
+        const uint32_t c = (uint32_t)__popc(m);
+        if (count + c > 32) { grouped = false; break; }
+        if ((uint32_t)lane >= count && (uint32_t)lane < count + c) watch = base + __fns(m, 0, (int)((uint32_t)lane - count) + 1);
+        count += c;
+      }
+    }
+    // ---- meanwhile keep the speculative result fresh, so that the
     bool skipped_now = false;
     for (uint32_t polls = 0;; ++polls) {
-      // own word: set by whoever moves the commit front onto this ticket
-      if (__shfl_sync(kFull, ld_vol(&go[t]), 0)) break;
+      if (grouped) {  // every watched ticket done?
+        const bool pending = watch != 0xFFFFFFFFu && !ld_vol(&done[watch]);
+        if (!pending) watch = 0xFFFFFFFFu;
+        if (!__any_sync(kFull, pending)) break;
+      } else if (__shfl_sync(kFull, ld_vol(&go[t]), 0)) {  // own word: set by whoever moves the commit front onto this ticket
+        break;
+      }
       if ((polls & 15u) == 0) {  // the shared control words, less often
         uint32_t ep = 0;
         int st = stopped;
@@ -708,6 +756,14 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     MG_TRY(flags_dev.alloc((n + 1) * 12));
     MG_CUDA(cudaMemsetAsync(flags_dev.p, 0, (n + 1) * 12, s));
     uint32_t *built_dev = flags_dev.as<uint32_t>(), *done_dev = built_dev + n + 1, *go_dev = done_dev + n + 1;
+    DevBuf parent_dev;  // union-find over tickets: groups of start nodes whose balls overlap
+    MG_TRY(parent_dev.alloc((n + 1) * 4));
+    {
+      std::vector<uint32_t> iota(n + 1);
+      for (uint64_t i = 0; i <= n; ++i) iota[i] = (uint32_t)i;
+      MG_CUDA(cudaMemcpyAsync(parent_dev.p, iota.data(), (n + 1) * 4, cudaMemcpyHostToDevice, s));
+      MG_CUDA(cudaStreamSynchronize(s));
+    }
     ctl.ooo_limit = 0xFFFFFFFFu;
     uint32_t nodes_cap = 1u << 22, len_cap = 1u << 18;
     MG_TRY(pool_nodes.alloc((size_t)nodes_cap * 4));
@@ -741,7 +797,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
           MG_LAUNCH(k_enum_pipeline, blocks, 32 * kWarpsPerBlock, L.smem_bytes * kWarpsPerBlock, s, g->view, g->adj.as<uint64_t>(), g->visited.as<uint32_t>(),
                     starts_dev.as<uint32_t>(), (uint32_t)n, min_len, max_len, g->enum_arena.as<uint8_t>(), L,
                     ctl_dev.as<PipeCtl>(), recs_dev.as<TicketRec>(), pool_nodes.as<uint32_t>(), nodes_cap,
-                    pool_len.as<uint32_t>(), len_cap, owner.as<uint32_t>(), built_dev, done_dev, go_dev, force_global);
+                    pool_len.as<uint32_t>(), len_cap, owner.as<uint32_t>(), built_dev, done_dev, go_dev, parent_dev.as<uint32_t>(), force_global);
         } else {
           const SlotLayout LB = make_layout(max_len, big_lock_log, big_relax, kClusterBound);
           MG_CUDA(cudaFuncSetAttribute(k_enum_solo, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LB.smem_bytes));

@@ -21,12 +21,23 @@
 #include <unordered_map>
 #include <vector>
 
+#include <chrono>
+
 #include "cycle_finder.h"  // the reference's header
 #include "mcaat_gpu.h"
 #include "gpu_bridge.h"
 
 namespace {
 
+// wall-clock breakdown of the constructor, printed to stderr as one "GPU_SHIM_TIMING {...}" line when MCAAT_GPU_TIMING=1
+struct Timing {
+  double graph_ms = 0, prune_ms = 0, writeback_ms = 0, starts_ms = 0, cycles_ms = 0, results_ms = 0;
+  const char *graph_path = "";
+};
+Timing g_timing;
+double now_ms() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 struct GpuState {
   mg_graph *g = nullptr;
   bool pruned = false;
@@ -163,7 +174,11 @@ GpuState &state_of(const CycleFinder *cf, SDBG &sdbg, const std::string &prefix 
   GpuState &s = g_state[cf];
   if (!s.g) {
     const char *fast = std::getenv("MCAAT_GPU_INGEST_FILES");
-    s.g = (!(fast && *fast == '0') && graph_files_exist(prefix)) ? ingest(prefix, sdbg) : upload(sdbg);
+    const bool from_files = !(fast && *fast == '0') && graph_files_exist(prefix);
+    const double t0 = now_ms();
+    s.g = from_files ? ingest(prefix, sdbg) : upload(sdbg);
+    g_timing.graph_ms = now_ms() - t0;
+    g_timing.graph_path = from_files ? "device ingest of the graph files" : "SDBG getters + upload";
     s.sdbg = &sdbg;
   }
   return s;
@@ -196,10 +211,14 @@ using mcaat_gpu_bridge::write_back_invalid;
 
 void ensure_pruned(GpuState &s, SDBG &sdbg, mg_prune_stats *out) {
   if (!s.pruned) {
+    const double t0 = now_ms();
     int rc = mg_prune(s.g, &s.stats);
     if (rc != MG_OK) fail("mg_prune", rc);
     s.pruned = true;
+    const double t1 = now_ms();
     write_back_invalid(s.g, sdbg);
+    g_timing.prune_ms = t1 - t0;
+    g_timing.writeback_ms = now_ms() - t1;
   }
   if (out) *out = s.stats;
 }
@@ -332,15 +351,20 @@ int CycleFinder::FindApproximateCRISPRArrays() {
   std::cout << "Starting cycle enumeration: max_len=" << cfs.cycle_max_length << " min_len=" << cfs.cycle_min_length
             << " threads=" << this->settings.threads << std::endl;
   map<int, vector<uint64_t>, greater<int>> start_nodes_chunked;
+  const double t_starts = now_ms();
   size_t start_nodes_amount = this->ChunkStartNodes(start_nodes_chunked);
+  g_timing.starts_ms = now_ms() - t_starts;
   std::cout << "Start nodes found in chunks: " << start_nodes_amount << std::endl;
 
   vector<uint64_t> order;
   order.reserve(start_nodes_amount);
   for (auto &kv : start_nodes_chunked) order.insert(order.end(), kv.second.begin(), kv.second.end());
   mg_cycles c{};
+  const double t_cyc = now_ms();
   int rc = mg_find_cycles(s.g, order.data(), order.size(), cfs.cycle_min_length, cfs.cycle_max_length, &c);
   if (rc != MG_OK) fail("mg_find_cycles", rc);
+  g_timing.cycles_ms = now_ms() - t_cyc;
+  const double t_res = now_ms();
   // results[start] = cycles in the reference's insertion sequence (:479; F14: downstream iterates
   // the unordered_map, whose order depends on it)
   std::unordered_map<uint64_t, uint64_t> n_cycles_of;
@@ -350,6 +374,11 @@ int CycleFinder::FindApproximateCRISPRArrays() {
     for (uint64_t j = c.node_off[c.cyc_off[i]]; j < c.node_off[c.cyc_off[i + 1]]; ++j) this->visited[c.nodes[j]] = true;
   }
   mg_cycles_free(&c);
+  g_timing.results_ms = now_ms() - t_res;
+  if (const char *tm = std::getenv("MCAAT_GPU_TIMING"); tm && *tm == '1')
+    std::fprintf(stderr, "GPU_SHIM_TIMING {\"graph\": \"%s\", \"graph_ms\": %.1f, \"prune_ms\": %.1f, \"invalid_write_back_ms\": %.1f, "
+                 "\"select_starts_ms\": %.1f, \"find_cycles_ms\": %.1f, \"results_ms\": %.1f}\n", g_timing.graph_path, g_timing.graph_ms,
+                 g_timing.prune_ms, g_timing.writeback_ms, g_timing.starts_ms, g_timing.cycles_ms, g_timing.results_ms);
   int cumulative = 0;
   for (auto &kv : start_nodes_chunked) {
     size_t in_bucket = 0;
