@@ -929,7 +929,7 @@ MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, c
         if (deg > 4) deg = 4;
         cnt = (uint32_t)deg;
         if (!expand) {
-          N[i].meta = cnt << kMetaOutShift;
+          N[i].meta = cnt << kMetaOutShift;  // out-degree on the graph (:294); no neighbours recorded
           cnt = 0;
         }
         for (uint32_t j = 0; j < cnt; ++j) {  // find or claim the neighbour's index slot
@@ -977,7 +977,7 @@ MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, c
           N[i].out[j] = (uint16_t)x;
           if (meta_add(&A.relax[x], 1u) == 0) T[x].in[0] = (uint16_t)i;  // the in-neighbour, if it stays the only one
         }
-        N[i].meta = cnt << kMetaOutShift;
+        N[i].meta = (cnt << kMetaOutShift) | (cnt << kMetaInShift);  // out-degree | out-neighbours recorded
       }
     }
     lo = hi;
@@ -988,11 +988,13 @@ MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, c
   return status;
 }
 
+// (node meta of dball_build: bits 16..18 out-degree on the graph, bits 20..22 out-neighbours recorded in the ball — the
+//  same, except for nodes at distance `limit`, which are not expanded)
 MG_HD bool dball_is_head(const BallArena &A, uint32_t x) {
   if (x == 0) return true;
   if (ld_cg32(&A.relax[x]) != 1) return true;
   const uint32_t u = A.tails[x].in[0];
-  return u == 0 || ((A.nodes[u].meta >> kMetaOutShift) & 7u) != 1;
+  return u == 0 || ((A.nodes[u].meta >> kMetaInShift) & 7u) != 1;
 }
 // chains of the ball -> C[0 .. n_chains); returns the number of chains
 MG_HD_NOINLINE uint32_t dball_contract(const BallArena &A, uint32_t n_nodes, DChain *C, const Coop &co) {
@@ -1012,15 +1014,15 @@ MG_HD_NOINLINE uint32_t dball_contract(const BallArena &A, uint32_t n_nodes, DCh
   for (uint32_t s = (uint32_t)co.lane; s < n_chains; s += Coop::kLanes) {
     uint32_t x = A.shead[s], c = 1;
     for (;;) {
-      if (s == 0 || ((N[x].meta >> kMetaOutShift) & 7u) != 1) break;
+      if (s == 0 || ((N[x].meta >> kMetaInShift) & 7u) != 1) break;
       const uint32_t y = N[x].out[0];
       if (dball_is_head(A, y)) break;
       x = y;
       ++c;
     }
-    const uint32_t nout = (N[x].meta >> kMetaOutShift) & 7u;
+    const uint32_t deg = (N[x].meta >> kMetaOutShift) & 7u;
     DChain d;
-    d.w0 = c | (nout ? kDTailOut : 0u);
+    d.w0 = c | (deg ? kDTailOut : 0u);
     d.pad = 0;
     uint64_t o = N[x].out4, o2 = 0;
     for (int q = 0; q < 4; ++q) {

@@ -776,7 +776,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32);
     const uint32_t smem_per_worker = std::min<uint32_t>(ball_smem_per_worker(g, workers_per_sm, kWarpsPerBlock),
                                                         env_u32("MCAAT_ENUM_SMEM_PER_WORKER", 1u << 20, 2048, 1u << 20));
-    const BallLayout L = make_ball_layout(max_len, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 17), smem_per_worker);
+    const BallLayout L = make_ball_layout(max_len, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 16), smem_per_worker);
     // diagnostics: chain records in the arena instead of shared memory (1); every commit in ticket order (4)
     const int force_global = (int)(env_u32("MCAAT_ENUM_CHAINS_GLOBAL", 0, 0, 1) | (env_u32("MCAAT_ENUM_INORDER", 0, 0, 1) << 2));
     MG_CUDA(cudaFuncSetAttribute(k_enum_pipeline, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(L.smem_bytes * kWarpsPerBlock)));

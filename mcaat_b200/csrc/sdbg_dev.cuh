@@ -19,7 +19,7 @@
 
 #if defined(__CUDACC__)
 #define MG_HD __host__ __device__ __forceinline__
-#define MG_HD_NOINLINE static __host__ __device__
+#define MG_HD_NOINLINE static __noinline__ __host__ __device__
 #else
 #define MG_HD inline
 #define MG_HD_NOINLINE static inline

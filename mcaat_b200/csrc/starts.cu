@@ -271,7 +271,7 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
       const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32);
       const uint32_t want = (uint32_t)std::min<uint64_t>(n_work, (uint64_t)g->sm_count * workers_per_sm);
       const uint32_t blocks = (want + kDlsBallWarps - 1) / kDlsBallWarps, workers = blocks * kDlsBallWarps;
-      const BallLayout L = make_ball_layout(limit, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 17),
+      const BallLayout L = make_ball_layout(limit, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 16),
                                             std::min<uint32_t>(ball_smem_per_worker(g, workers_per_sm, kDlsBallWarps),
                                                                env_u32("MCAAT_ENUM_SMEM_PER_WORKER", 1u << 20, 2048, 1u << 20)));
       const uint32_t stk_entries = (uint32_t)(4 * limit + 8);
