@@ -227,6 +227,7 @@ def reference_arm(args):
     workload = args.workload if device == "cuda" or args.workload != "c2" else args.sample  # no GPU: the full graph cannot be generated
     g, info = S.make_workload(workload, device=device, want_labels=True)
     n_items = int(g["n"])
+    graph_sha = graph_digest(g)
     budget = float(os.environ.get("BENCH_REF_BUDGET_S", "240"))
     rep_timeout = float(os.environ.get("BENCH_REF_TIMEOUT_S", "400"))
     exe = O.ref_binary("ref_cyclefinder")
@@ -280,7 +281,7 @@ def reference_arm(args):
         "config": config_dict(workload, n_items, args.gpus),
         "reps_timed": len(times), "rep_s": [round(t, 3) for t in times], "threads_requested": threads_requested,
         "threads_used": threads_used, "cores_available": cores_avail, "fallback_reason": why or None,
-        "load_s": load_s, "n_starts": n_starts,
+        "load_s": load_s, "n_starts": n_starts, "graph_sha256": graph_sha,
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads_used, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -302,6 +303,16 @@ def config_dict(workload, n_items, world):
             "timing": "CUDA events on the library stream around each step (mg_step_begin/end), max over ranks"}
 
 
+def graph_digest(g):
+    """sha256 over the packed SDBG arrays (w nibbles, last, tip, multiplicities) and f[]: two runs timed the same input
+    <=> equal digests (the generator samples on the device it runs on, so a CPU-built and a GPU-built graph differ)"""
+    import hashlib
+    h = hashlib.sha256()
+    for key in ("w", "last", "tip", "mult", "f"):
+        h.update(np.ascontiguousarray(g[key]).tobytes())
+    return h.hexdigest()
+
+
 def result_digest(ss, coff, noff, nodes, inv_words):
     """sha256 over the canonical result: invalid bitmap words, searched start ids in insertion order, cycle offsets,
     node offsets, node ids (all little-endian uint64) — equal results <=> equal digests"""
@@ -317,6 +328,7 @@ WORKLOAD_TEXT = {
     "c4": "BASELINE.json configs[3], synthetic high-diversity community (250 genomes + 10 strain copies, abundance sigma 2)",
     "c1": "BASELINE.json configs[0], 5 x 2 Mb genomes with 10 planted arrays, error-free",
     "c2_sample": "BASELINE.json configs[1] recipe at 1/20 scale",
+    "c2_errors": "BASELINE.json configs[1] item count with the error share of real data (12 genomes, 3.5 M substitution events)",
 }
 
 
@@ -376,9 +388,11 @@ def main():
 
     # ---- workload: built on the GPU by rank 0; raw arrays broadcast over NCCL (NVLink) to the other ranks
     t_gen = time.perf_counter()
+    graph_sha = None
     if rank == 0:
         graph, info = S.make_workload(args.workload, device="cuda")
         torch.cuda.empty_cache()
+        graph_sha = graph_digest(graph)
     if world > 1:
         meta = [dict(n=graph["n"], k=graph["k"], f=[int(x) for x in graph["f"]], info=info,
                      sizes=[graph[k].size for k in ("w", "last", "tip", "mult")])] if rank == 0 else [None]
@@ -580,7 +594,7 @@ def main():
             best = None
             for _ in range(2):
                 p = subprocess.run([shim, prefix, "-", str(min(16, os.cpu_count() or 1)), str(THR), str(MIN_LEN), str(MAX_LEN)],
-                                   capture_output=True, text=True, env=dict(os.environ, MCAAT_GPU_INGEST_FILES=mode, MCAAT_GPU_TIMING="1"))
+                                   capture_output=True, text=True, env=dict(os.environ, MCAAT_GPU_INGEST_FILES=mode, MCAAT_GPU_TIMING="1", MCAAT_REF_COUNT_STARTS="1"))
                 js = [json.loads(ln[9:]) for ln in p.stdout.splitlines() if ln.startswith("REF_JSON ")]
                 tm = [json.loads(ln[16:]) for ln in p.stderr.splitlines() if ln.startswith("GPU_SHIM_TIMING ")]
                 if p.returncode == 0 and js and (best is None or js[-1]["ctor_s"] < best["ctor_ms"] / 1e3):
@@ -737,7 +751,7 @@ def main():
                   "candidates_per_s": stats["n_candidates"] / max(phases.get("dls", 0) / 1e3, 1e-9),
                   "edges_traversed_per_s": (stats["dls_expansions"] + stats["expansions"] + stats["n_peeled"]) / (ms_per_step / 1e3)},
         "roofline": roofline, "setup": {"generate_s": round(gen_s, 2), "nccl_broadcast_s": round(bcast_s, 4),
-                                        "graph_device_bytes": graph_device_bytes},
+                                        "graph_device_bytes": graph_device_bytes, "graph_sha256": graph_sha},
     }
     if sweep:
         line["sweep"] = sweep

@@ -334,6 +334,15 @@ WORKLOADS = {
                      "--biallelic-arrays", "10", "--bound-arrays", "2", "--strain-pairs", "5", "--tandem", "200",
                      "--abundance-sigma", "1.0"],
                total_bases=50_000_000 * 2 * 150, error_events=500_000, seed=12),
+    # The same item count with the error density of real data ("mostly mult-1 error k-mers"): a quarter of
+    # the genomes, 7 x the substitution events -> ~3/4 of the items are multiplicity-1 error k-mers.  (configs[1] names
+    # BOTH "~200M-node SDBG" and "50 M pairs at 0.5 % errors"; at k = 23 the latter alone would be ~3.4 G distinct error
+    # k-mers, so "c2" keeps the item count and the community and thins the errors; this variant keeps the item count and
+    # the error share instead.)
+    "c2_errors": dict(argv=["--genomes", "12", "--genome-len", "2000000", "--arrays", "100", "--shared-family-arrays", "20",
+                            "--biallelic-arrays", "10", "--bound-arrays", "2", "--strain-pairs", "2", "--tandem", "200",
+                            "--abundance-sigma", "1.0"],
+                      total_bases=12_000_000 * 2 * 150, error_events=3_500_000, seed=12),
     # BASELINE.json configs[3]: high-diversity community (250 genomes, steep abundance tail), ~1 B-item SDBG
     "c4": dict(argv=["--genomes", "250", "--genome-len", "2000000", "--arrays", "500", "--shared-family-arrays", "100",
                      "--biallelic-arrays", "50", "--bound-arrays", "4", "--strain-pairs", "10", "--tandem", "1000",
