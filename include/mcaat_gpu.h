@@ -106,6 +106,14 @@ int mg_collect_tips(mg_graph *g, uint64_t **ids, uint64_t *n);
 /* Current invalid bitmap -> host words ((n+63)/64 uint64), for write-back into the host SDBG
  * (reference SetInvalidEdge, sdbg.h:94). */
 int mg_invalid_readback(mg_graph *g, uint64_t *host_words);
+/* mg_invalid_readback without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  The staging buffer is a static 4 MiB device array inside the library (held by every GPU that
+ * loads it until the process exits), so graphs of more than MG_NOALLOC_MAX_ITEMS items are refused with
+ * MG_ELIMIT.  Calls no cudaMalloc / cudaFree / pool routine.  All calls on one device share the array: calls
+ * that overlap on the GPU (two graphs or streams of the same device) race on it. */
+#define MG_NOALLOC_MAX_ITEMS (1ull << 25)
+int mg_invalid_readback_noalloc(mg_graph *g, uint64_t *host_words);
 /* The other direction: ORs the host SDBG's invalid bits (!IsValidEdge, sdbg.h:88-92; (n+63)/64 uint64 words)
  * into the device bitmap, so that a device graph kept resident across stages follows SetInvalidEdge calls the
  * host made in between.  *n_new (may be NULL) = bits that were not set on the device.  When anything changed,

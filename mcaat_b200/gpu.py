@@ -20,7 +20,7 @@ MG_MEM_HOST, MG_MEM_DEVICE = 0, 1
 # every symbol include/mcaat_gpu.h declares (tests check that the library exports all of them)
 SYMBOLS = [
     "mg_graph_create", "mg_graph_create_from_files", "mg_graph_destroy", "mg_graph_reset", "mg_graph_size", "mg_graph_device_bytes",
-    "mg_navigate", "mg_prune", "mg_collect_tips", "mg_invalid_readback", "mg_candidates", "mg_dls", "mg_select_starts",
+    "mg_navigate", "mg_prune", "mg_collect_tips", "mg_invalid_readback", "mg_invalid_readback_noalloc", "mg_candidates", "mg_dls", "mg_select_starts",
     "mg_bucket_starts", "mg_starts_free", "mg_find_cycles", "mg_cycles_free", "mg_visited_readback",
     "mg_keep_regions", "mg_invalid_merge", "mg_valid_subgraph", "mg_subgraph_free",
     "mg_kmer_index_create", "mg_graph_has_kmer_index", "mg_map_reads", "mg_reads_free",
@@ -100,6 +100,7 @@ def lib():
         L.mg_navigate.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64] + [C.c_void_p] * 5
         L.mg_prune.argtypes = [C.c_void_p, C.POINTER(PruneStats)]
         L.mg_invalid_readback.argtypes = [C.c_void_p, C.c_void_p]
+        L.mg_invalid_readback_noalloc.argtypes = [C.c_void_p, C.c_void_p]
         L.mg_visited_readback.argtypes = [C.c_void_p, C.c_void_p]
         L.mg_candidates.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(u64p), C.POINTER(C.c_uint64)]
         L.mg_collect_tips.argtypes = [C.c_void_p, C.POINTER(u64p), C.POINTER(C.c_uint64)]
@@ -227,6 +228,13 @@ class DeviceGraph:
     def invalid_words(self):
         words = np.zeros((self.n + 63) // 64, np.uint64)
         _check(lib().mg_invalid_readback(self.h, words.ctypes.data))
+        return words
+
+    def invalid_words_noalloc(self, out=None):
+        """mg_invalid_readback_noalloc: the same words through the library's static scratch (no allocation on the
+        device side; graphs of at most MG_NOALLOC_MAX_ITEMS = 2**25 items).  `out` lets the caller own the buffer."""
+        words = np.zeros((self.n + 63) // 64, np.uint64) if out is None else out
+        _check(lib().mg_invalid_readback_noalloc(self.h, words.ctypes.data))
         return words
 
     def merge_invalid(self, invalid):
