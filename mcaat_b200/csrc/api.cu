@@ -15,34 +15,45 @@ static thread_local char g_err[512] = "";
 unsigned long long g_launches = 0;
 thread_local cudaStream_t g_alloc_stream = nullptr;
 
-// ---- exact-size free list in front of the stream-ordered pool (see DevBuf, common.cuh)
+// ---- exact-size free list in front of the stream-ordered pool (see DevBuf, common.cuh).  Entries, the byte count
+// and the byte limit are kept per device: a process that holds replicas on several GPUs neither evicts one
+// device's buffers for another's nor frees a block while a different device is current.
 namespace {
-struct ScratchEntry { cudaStream_t st; void *p; size_t bytes; };
+constexpr int kScratchMaxDevices = 64;
+struct ScratchEntry { int dev; cudaStream_t st; void *p; size_t bytes; };
 std::mutex g_scratch_mu;
 std::vector<ScratchEntry> g_scratch;
-size_t g_scratch_bytes = 0;
-constexpr size_t kScratchMaxEntries = 512;
+size_t g_scratch_bytes[kScratchMaxDevices] = {0};
+size_t g_scratch_lim[kScratchMaxDevices] = {0};
+constexpr size_t kScratchMaxEntries = 512;  // per device
 bool scratch_enabled() {
   static const bool on = [] { const char *e = getenv("MCAAT_SCRATCH_CACHE"); return !(e && *e == '0'); }();
   return on;
 }
-size_t scratch_limit() {  // bytes kept per process: a quarter of the device, at least 1 GB
-  static const size_t lim = [] {
+int scratch_device() {  // DevBuf allocates and releases with the handle's device current (MG_CHECK_HANDLE)
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= kScratchMaxDevices) return -1;
+  return d;
+}
+size_t scratch_limit(int dev) {  // bytes kept per device: a quarter of it, at least 1 GB (call with g_scratch_mu held)
+  if (!g_scratch_lim[dev]) {
     size_t fr = 0, tot = 0;
     if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) tot = (size_t)16 << 30;
-    return std::max<size_t>(tot / 4, (size_t)1 << 30);
-  }();
-  return lim;
+    g_scratch_lim[dev] = std::max<size_t>(tot / 4, (size_t)1 << 30);
+  }
+  return g_scratch_lim[dev];
 }
 }  // namespace
 
 void *scratch_take(cudaStream_t st, size_t bytes) {
   if (!scratch_enabled()) return nullptr;
+  const int dev = scratch_device();
+  if (dev < 0) return nullptr;
   std::lock_guard<std::mutex> lk(g_scratch_mu);
   for (size_t i = g_scratch.size(); i-- > 0;)
-    if (g_scratch[i].st == st && g_scratch[i].bytes == bytes) {
+    if (g_scratch[i].dev == dev && g_scratch[i].st == st && g_scratch[i].bytes == bytes) {
       void *p = g_scratch[i].p;
-      g_scratch_bytes -= bytes;
+      g_scratch_bytes[dev] -= bytes;
       g_scratch.erase(g_scratch.begin() + (long)i);
       return p;
     }
@@ -51,26 +62,33 @@ void *scratch_take(cudaStream_t st, size_t bytes) {
 
 bool scratch_give(cudaStream_t st, void *p, size_t bytes) {
   if (!scratch_enabled() || !st) return false;
+  const int dev = scratch_device();
+  if (dev < 0) return false;
   std::lock_guard<std::mutex> lk(g_scratch_mu);
-  if (bytes > scratch_limit()) return false;
-  // make room: oldest entries first (sizes that no longer occur, e.g. after another graph was searched)
-  while (!g_scratch.empty() && (g_scratch_bytes + bytes > scratch_limit() || g_scratch.size() >= kScratchMaxEntries)) {
-    cudaFreeAsync(g_scratch.front().p, g_scratch.front().st);
-    g_scratch_bytes -= g_scratch.front().bytes;
-    g_scratch.erase(g_scratch.begin());
+  const size_t lim = scratch_limit(dev);
+  if (bytes > lim) return false;
+  // make room on this device: oldest entries first (sizes that no longer occur, e.g. after another graph was searched)
+  size_t n_dev = 0;
+  for (const ScratchEntry &e : g_scratch) n_dev += e.dev == dev;
+  for (size_t i = 0; i < g_scratch.size() && (g_scratch_bytes[dev] + bytes > lim || n_dev >= kScratchMaxEntries);) {
+    if (g_scratch[i].dev != dev) { ++i; continue; }
+    cudaFreeAsync(g_scratch[i].p, g_scratch[i].st);
+    g_scratch_bytes[dev] -= g_scratch[i].bytes;
+    --n_dev;
+    g_scratch.erase(g_scratch.begin() + (long)i);
   }
-  g_scratch.push_back({st, p, bytes});
-  g_scratch_bytes += bytes;
+  g_scratch.push_back({dev, st, p, bytes});
+  g_scratch_bytes[dev] += bytes;
   return true;
 }
 
-void scratch_flush(cudaStream_t st) {
+void scratch_flush(cudaStream_t st) {  // called with the stream's device current
   std::lock_guard<std::mutex> lk(g_scratch_mu);
   size_t w = 0;
   for (size_t i = 0; i < g_scratch.size(); ++i) {
     if (g_scratch[i].st == st) {
       cudaFreeAsync(g_scratch[i].p, st);
-      g_scratch_bytes -= g_scratch[i].bytes;
+      g_scratch_bytes[g_scratch[i].dev] -= g_scratch[i].bytes;
     } else {
       g_scratch[w++] = g_scratch[i];
     }
