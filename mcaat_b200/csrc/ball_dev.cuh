@@ -97,6 +97,12 @@ struct Coop {
     return incl - x;
   }
   __device__ bool any(bool p) const { return __any_sync(0xffffffffu, p) != 0; }
+  // appends v of every lane with p to list[n..) (lane order); returns the new length.  All lanes call it.
+  __device__ uint32_t append(uint32_t *list, uint32_t n, bool p, uint32_t v) const {
+    const unsigned m = __ballot_sync(0xffffffffu, p);
+    if (p) list[n + (uint32_t)__popc(m & ((1u << lane) - 1u))] = v;
+    return n + (uint32_t)__popc(m);
+  }
 };
 MG_HD uint64_t index_cas(uint64_t *p, uint64_t expect, uint64_t val) {
   return (uint64_t)atomicCAS((unsigned long long *)p, (unsigned long long)expect, (unsigned long long)val);
@@ -111,6 +117,10 @@ struct Coop {
   uint32_t sum(uint32_t x) const { return x; }
   uint32_t exclusive_prefix(uint32_t) const { return 0; }
   bool any(bool p) const { return p; }
+  uint32_t append(uint32_t *list, uint32_t n, bool p, uint32_t v) const {
+    if (p) list[n++] = v;
+    return n;
+  }
 };
 MG_HD uint64_t index_cas(uint64_t *p, uint64_t expect, uint64_t val) {
   uint64_t old = *p;
@@ -131,6 +141,58 @@ MG_HD void ball_clear(const BallArena &A, uint32_t n_nodes, const Coop &co) {
   co.sync();
 }
 
+// Finds or claims the index slots of up to 4 keys (one lane), in two halves.  index_claim_issue: the first probes of
+// all keys are ONE round of compare-and-swaps in flight together — a claim is a single L2 round trip instead of a load
+// followed by a CAS per key, one key after the other.  index_claim_resolve: only collisions probe on.  lid[j] = the
+// local id the index already held for key j, or kLidPending when the key was claimed just now (bit j of `mine`: by this
+// lane) and has no id yet.  A caller with several nodes in hand issues for all of them before it resolves any.
+MG_HD void index_claim_issue(const BallArena &A, const uint32_t *key, uint32_t cnt, uint32_t *slot, uint64_t *got) {
+#pragma unroll
+  for (uint32_t j = 0; j < 4; ++j)
+    if (j < cnt) {
+      slot[j] = hash_u32(key[j], A.index_log);
+      got[j] = index_cas(&A.index[slot[j]], kIndexEmpty, ((uint64_t)key[j] << 32) | kLidPending);
+    }
+}
+MG_HD void index_claim_resolve(const BallArena &A, uint32_t imask, const uint32_t *key, uint32_t cnt, uint32_t *slot,
+                               const uint64_t *got, uint32_t *lid, uint32_t &mine) {
+#pragma unroll
+  for (uint32_t j = 0; j < 4; ++j)
+    if (j < cnt) {
+      uint64_t cur = got[j];
+      uint32_t h = slot[j];
+      for (;;) {
+        if (cur == kIndexEmpty) { mine |= 1u << j; cur = kLidPending; break; }
+        if ((uint32_t)(cur >> 32) == key[j]) break;
+        h = (h + 1) & imask;
+        cur = index_cas(&A.index[h], kIndexEmpty, ((uint64_t)key[j] << 32) | kLidPending);
+      }
+      slot[j] = h;
+      lid[j] = (uint32_t)cur;
+    }
+}
+// first 16 bytes of a node record (meta, key, out-neighbour set) in one load
+struct NodeHead {
+  uint32_t meta;
+  uint64_t out4;
+};
+MG_HD NodeHead ld_head(const LNode *n) {
+  NodeHead h;
+#if defined(__CUDA_ARCH__)
+  const uint4 v = *reinterpret_cast<const uint4 *>(n);
+  h.meta = v.x;
+  h.out4 = (uint64_t)v.z | ((uint64_t)v.w << 32);
+#else
+  h.meta = n->meta;
+  h.out4 = n->out4;
+#endif
+  return h;
+}
+
+#ifndef MG_BUILD_K
+#define MG_BUILD_K 2
+#endif
+constexpr int kBuildK = MG_BUILD_K;  // frontier nodes per lane and round of the ball extraction
 // Stage 1.  Returns kEnumDone or kEnumOverflow; n_nodes = number of ball nodes (also on overflow, so
 // that ball_clear can tidy up).  All lanes call it with identical arguments.
 MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uint32_t *visited, uint32_t start, int M,
@@ -152,61 +214,92 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
   uint32_t total_nodes = 1, lo = 0, hi = 1;
   int status = kEnumDone;
   for (int depth = 0; depth < M && lo < hi && status == kEnumDone; ++depth) {
-    for (uint32_t base = lo; base < hi; base += Coop::kLanes) {
-      const uint32_t i = base + (uint32_t)co.lane;
-      uint32_t okn[4], slot[4], cnt = 0, mine = 0;
-      if (i < hi) {
-        const uint32_t node = N[i].key;
-        uint32_t nb[4], nset = 0;
-        int deg = adj_outgoing(ld_ro(&adj[node]), nb);
-        if (deg > 4) deg = 4;
-        filtered_set(g, visited, node, mu, nb, deg, nset, okn);  // :58-72 incl. the set's iteration order
-        cnt = nset;
-        for (uint32_t j = 0; j < cnt; ++j) {  // find or claim the neighbour's index slot
-          const uint32_t key = okn[j];
-          uint32_t h = hash_u32(key, A.index_log);
-          for (;;) {
-            uint64_t cur = ld_cg64(&A.index[h]);
-            if (cur == kIndexEmpty) {
-              cur = index_cas(&A.index[h], kIndexEmpty, ((uint64_t)key << 32) | kLidPending);
-              if (cur == kIndexEmpty) { mine |= 1u << j; break; }
-            }
-            if ((uint32_t)(cur >> 32) == key) break;
-            h = (h + 1) & imask;
-          }
-          slot[j] = h;
-        }
+    // kBuildK frontier nodes per lane and round: their loads and claims are independent and overlap
+    for (uint32_t base = lo; base < hi; base += Coop::kLanes * kBuildK) {
+      uint32_t okn[kBuildK][4], slot[kBuildK][4], nlid[kBuildK][4], cnt[kBuildK], mine[kBuildK], node[kBuildK];
+      uint64_t av[kBuildK];
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) {
+        const uint32_t i = base + (uint32_t)k * Coop::kLanes + (uint32_t)co.lane;
+        cnt[k] = mine[k] = 0;
+        node[k] = i < hi ? N[i].key : 0u;
       }
-      // dense local ids for the newly discovered nodes of this chunk
-      const uint32_t n_mine = (uint32_t)popc32(mine);
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) {
+        const uint32_t i = base + (uint32_t)k * Coop::kLanes + (uint32_t)co.lane;
+        av[k] = i < hi ? ld_ro(&adj[node[k]]) : 0ull;
+      }
+      uint32_t nb[kBuildK][4], fm[kBuildK][4], fv[kBuildK][4];
+      int deg[kBuildK];
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) {  // multiplicity and visited words of every neighbour of every node: one wait
+        const uint32_t i = base + (uint32_t)k * Coop::kLanes + (uint32_t)co.lane;
+        deg[k] = 0;
+        if (i < hi) {
+          deg[k] = adj_outgoing(av[k], nb[k]);
+          if (deg[k] > 4) deg[k] = 4;
+        }
+        filtered_loads(g, visited, nb[k], deg[k], fm[k], fv[k]);
+      }
+      uint64_t got[kBuildK][4];
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) {
+        uint32_t nset = 0;
+        filtered_finish(node[k], mu, nb[k], deg[k], fm[k], fv[k], nset, okn[k]);  // :58-72 incl. the set's iteration order
+        cnt[k] = nset;
+      }
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) index_claim_issue(A, okn[k], cnt[k], slot[k], got[k]);  // neighbours' index slots: one wait
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) index_claim_resolve(A, imask, okn[k], cnt[k], slot[k], got[k], nlid[k], mine[k]);
+      // dense local ids for the newly discovered nodes of this round
+      uint32_t n_mine = 0;
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) n_mine += (uint32_t)popc32(mine[k]);
       const uint32_t before = co.exclusive_prefix(n_mine), chunk_new = co.sum(n_mine);
       if (total_nodes + chunk_new > A.node_cap) {
         // no room: release the claimed slots (every lane has stopped probing) and give up
         co.sync();
-        for (uint32_t j = 0; j < cnt; ++j)
-          if ((mine >> j) & 1) st_cg64(&A.index[slot[j]], kIndexEmpty);
+#pragma unroll
+        for (int k = 0; k < kBuildK; ++k)
+          for (uint32_t j = 0; j < cnt[k]; ++j)
+            if ((mine[k] >> j) & 1) st_cg64(&A.index[slot[k][j]], kIndexEmpty);
         co.sync();
         status = kEnumOverflow;
         break;
       }
       uint32_t lid = total_nodes + before;
-      for (uint32_t j = 0; j < cnt; ++j)
-        if ((mine >> j) & 1) {
-          prefetch_l2(&adj[okn[j]]);  // expanded at the next level: its navigation entry is on its way by then
-          N[lid].meta = (uint32_t)M;  // lock default (try_emplace(n, cycle_max_length), :168), no edges yet
-          N[lid].key = okn[j];
-          N[lid].out4 = ~0ull;
-          T[lid].slot = slot[j];
-          A.relax[lid] = 0;  // in-degree counter of the transpose below (the relax stack is idle during the build)
-          st_cg64(&A.index[slot[j]], ((uint64_t)okn[j] << 32) | lid);
-          ++lid;
-        }
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k)
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j)
+          if (j < cnt[k] && ((mine[k] >> j) & 1)) {
+            prefetch_l2(&adj[okn[k][j]]);  // expanded at the next level: its navigation entry is on its way by then
+            N[lid].meta = (uint32_t)M;  // lock default (try_emplace(n, cycle_max_length), :168), no edges yet
+            N[lid].key = okn[k][j];
+            N[lid].out4 = ~0ull;
+            T[lid].slot = slot[k][j];
+            A.relax[lid] = 0;  // in-degree counter of the transpose below (the relax stack is idle during the build)
+            st_cg64(&A.index[slot[k][j]], ((uint64_t)okn[k][j] << 32) | lid);
+            nlid[k][j] = lid;
+            ++lid;
+          }
       total_nodes += chunk_new;
       co.sync();
-      if (i < hi) {
-        uint32_t meta = N[i].meta;
-        for (uint32_t j = 0; j < cnt; ++j) N[i].out[j] = (uint16_t)(uint32_t)ld_cg64(&A.index[slot[j]]);
-        N[i].meta = meta | (cnt << kMetaOutShift);
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) {
+        const uint32_t i = base + (uint32_t)k * Coop::kLanes + (uint32_t)co.lane;
+        if (i < hi) {
+          uint64_t out4 = ~0ull;
+#pragma unroll
+          for (uint32_t j = 0; j < 4; ++j)
+            if (j < cnt[k]) {  // only a neighbour that another lane claimed in this very round has to be looked up
+              if (nlid[k][j] == kLidPending) nlid[k][j] = (uint32_t)ld_cg64(&A.index[slot[k][j]]);
+              out4 = (out4 & ~(0xFFFFull << (16 * j))) | ((uint64_t)(nlid[k][j] & 0xFFFFu) << (16 * j));
+            }
+          N[i].out4 = out4;
+          N[i].meta = (uint32_t)M | (cnt[k] << kMetaOutShift);  // the record still holds the default written at discovery
+        }
       }
     }
     lo = hi;
@@ -219,28 +312,63 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
   //      records and are only touched by atomics / L2 loads, so that no L1 line of a record the
   //      search reads later goes stale.
   bool too_many = false;
-  for (uint32_t u = (uint32_t)co.lane; u < total_nodes; u += Coop::kLanes) {
-    const uint32_t nout = (N[u].meta >> kMetaOutShift) & 7u;
-    for (uint32_t j = 0; j < nout; ++j) {
-      const uint32_t x = N[u].out[j];
-      const uint32_t pos = meta_add(&A.relax[x], 1u);
-      if (pos < 4) T[x].in[pos] = (uint16_t)u;
-      else too_many = true;
+  for (uint32_t u0 = (uint32_t)co.lane; u0 < total_nodes; u0 += Coop::kLanes * 2) {  // two nodes per lane: their counters overlap
+    NodeHead h[2];
+    uint32_t pos[2][4];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const uint32_t u = u0 + (uint32_t)q * Coop::kLanes;
+      h[q].meta = 0;
+      h[q].out4 = ~0ull;
+      if (u < total_nodes) h[q] = ld_head(&N[u]);
     }
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+#pragma unroll
+      for (uint32_t j = 0; j < 4; ++j)
+        if (j < ((h[q].meta >> kMetaOutShift) & 7u)) pos[q][j] = meta_add(&A.relax[(uint32_t)(h[q].out4 >> (16 * j)) & 0xFFFFu], 1u);
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+#pragma unroll
+      for (uint32_t j = 0; j < 4; ++j)
+        if (j < ((h[q].meta >> kMetaOutShift) & 7u)) {
+          const uint32_t x = (uint32_t)(h[q].out4 >> (16 * j)) & 0xFFFFu;
+          if (pos[q][j] < 4) T[x].in[pos[q][j]] = (uint16_t)(u0 + (uint32_t)q * Coop::kLanes);
+          else too_many = true;
+        }
   }
   co.sync();
   if (co.any(too_many)) return kEnumOverflow;
+  // in-degrees into the records (four nodes per lane and round); the nodes with several in-neighbours are listed
+  // (A.spos is idle until the contraction) and ordered below
+  uint32_t n_merge = 0;
+  for (uint32_t x0 = 0; x0 < total_nodes; x0 += Coop::kLanes * 4) {
+    uint32_t nin[4], meta[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t x = x0 + (uint32_t)q * Coop::kLanes + (uint32_t)co.lane;
+      nin[q] = x < total_nodes ? ld_cg32(&A.relax[x]) : 0u;
+      meta[q] = x < total_nodes ? N[x].meta : 0u;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t x = x0 + (uint32_t)q * Coop::kLanes + (uint32_t)co.lane;
+      if (nin[q]) N[x].meta = meta[q] | (nin[q] << kMetaInShift);
+      n_merge = co.append(A.spos, n_merge, nin[q] >= 2, x);
+    }
+  }
+  co.sync();
   // _GetIncomings inserts in IncomingEdges order (ascending id, sdbg.h:266-285); reproduce the
   // iteration order of the resulting std::unordered_set
-  for (uint32_t x = (uint32_t)co.lane; x < total_nodes; x += Coop::kLanes) {
-    const uint32_t nin = ld_cg32(&A.relax[x]);
-    if (nin == 0) continue;
-    N[x].meta |= nin << kMetaInShift;
-    if (nin < 2) continue;
+  for (uint32_t i = (uint32_t)co.lane; i < n_merge; i += Coop::kLanes) {
+    const uint32_t x = A.spos[i];
+    const uint32_t nin = (N[x].meta >> kMetaInShift) & 7u;
+    const uint64_t in4 = T[x].in4;
     uint32_t lid[4], key[4];
-    for (uint32_t j = 0; j < nin; ++j) {
-      lid[j] = T[x].in[j];
-      key[j] = N[lid[j]].key;
+#pragma unroll
+    for (uint32_t j = 0; j < 4; ++j) {
+      lid[j] = (uint32_t)(in4 >> (16 * j)) & 0xFFFFu;
+      key[j] = j < nin ? N[lid[j]].key : 0xFFFFFFFFu;
     }
     for (uint32_t a = 1; a < nin; ++a)  // insertion sort by key
       for (uint32_t b = a; b > 0 && key[b - 1] > key[b]; --b) {
@@ -256,24 +384,6 @@ MG_HD_NOINLINE int ball_build(const GraphView &g, const uint64_t *adj, const uin
   }
   co.sync();
   return kEnumDone;
-}
-
-// first 16 bytes of a node record (meta, key, out-neighbour set) in one load
-struct NodeHead {
-  uint32_t meta;
-  uint64_t out4;
-};
-MG_HD NodeHead ld_head(const LNode *n) {
-  NodeHead h;
-#if defined(__CUDA_ARCH__)
-  const uint4 v = *reinterpret_cast<const uint4 *>(n);
-  h.meta = v.x;
-  h.out4 = (uint64_t)v.z | ((uint64_t)v.w << 32);
-#else
-  h.meta = n->meta;
-  h.out4 = n->out4;
-#endif
-  return h;
 }
 
 // Stage 2 (one lane).  Literal FindCycleUtil + FindCycle, src/cycle_finder.cpp:231-243,140-225, on the
@@ -921,63 +1031,86 @@ MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, c
   int status = kDlsNotFound;
   for (int depth = 0; depth <= limit && lo < hi && status == kDlsNotFound; ++depth) {
     const bool expand = depth < limit;  // nodes at distance `limit` are only asked for their out-degree (:294)
-    for (uint32_t base = lo; base < hi; base += Coop::kLanes) {
-      const uint32_t i = base + (uint32_t)co.lane;
-      uint32_t nb[4], slot[4], cnt = 0, mine = 0;
-      if (i < hi) {
-        int deg = adj_outgoing(ld_ro(&adj[N[i].key]), nb);
-        if (deg > 4) deg = 4;
-        cnt = (uint32_t)deg;
-        if (!expand) {
-          N[i].meta = cnt << kMetaOutShift;  // out-degree on the graph (:294); no neighbours recorded
-          cnt = 0;
-        }
-        for (uint32_t j = 0; j < cnt; ++j) {  // find or claim the neighbour's index slot
-          const uint32_t key = nb[j];
-          uint32_t h = hash_u32(key, A.index_log);
-          for (;;) {
-            uint64_t cur = ld_cg64(&A.index[h]);
-            if (cur == kIndexEmpty) {
-              cur = index_cas(&A.index[h], kIndexEmpty, ((uint64_t)key << 32) | kLidPending);
-              if (cur == kIndexEmpty) { mine |= 1u << j; break; }
-            }
-            if ((uint32_t)(cur >> 32) == key) break;
-            h = (h + 1) & imask;
+    for (uint32_t base = lo; base < hi; base += Coop::kLanes * kBuildK) {  // kBuildK nodes per lane, as in ball_build
+      uint32_t nb[kBuildK][4], slot[kBuildK][4], nlid[kBuildK][4], cnt[kBuildK], mine[kBuildK];
+      uint64_t av[kBuildK];
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) {
+        const uint32_t i = base + (uint32_t)k * Coop::kLanes + (uint32_t)co.lane;
+        cnt[k] = mine[k] = 0;
+        av[k] = i < hi ? ld_ro(&adj[N[i].key]) : 0ull;
+      }
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) {
+        const uint32_t i = base + (uint32_t)k * Coop::kLanes + (uint32_t)co.lane;
+        if (i < hi) {
+          int deg = adj_outgoing(av[k], nb[k]);
+          if (deg > 4) deg = 4;
+          cnt[k] = (uint32_t)deg;
+          if (!expand) {
+            N[i].meta = cnt[k] << kMetaOutShift;  // out-degree on the graph (:294); no neighbours recorded
+            cnt[k] = 0;
           }
-          slot[j] = h;
         }
       }
-      const uint32_t n_mine = (uint32_t)popc32(mine);
+      uint64_t got[kBuildK][4];
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) index_claim_issue(A, nb[k], cnt[k], slot[k], got[k]);  // neighbours' index slots: one wait
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) index_claim_resolve(A, imask, nb[k], cnt[k], slot[k], got[k], nlid[k], mine[k]);
+      uint32_t n_mine = 0;
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) n_mine += (uint32_t)popc32(mine[k]);
       const uint32_t before = co.exclusive_prefix(n_mine), chunk_new = co.sum(n_mine);
       if (total_nodes + chunk_new > A.node_cap) {
         co.sync();
-        for (uint32_t j = 0; j < cnt; ++j)
-          if ((mine >> j) & 1) st_cg64(&A.index[slot[j]], kIndexEmpty);
+#pragma unroll
+        for (int k = 0; k < kBuildK; ++k)
+          for (uint32_t j = 0; j < cnt[k]; ++j)
+            if ((mine[k] >> j) & 1) st_cg64(&A.index[slot[k][j]], kIndexEmpty);
         co.sync();
         status = kDlsSetFull;
         break;
       }
       uint32_t lid = total_nodes + before;
-      for (uint32_t j = 0; j < cnt; ++j)
-        if ((mine >> j) & 1) {
-          prefetch_l2(&adj[nb[j]]);  // expanded (or asked for its out-degree) at the next level
-          N[lid].meta = 0;
-          N[lid].key = nb[j];
-          N[lid].out4 = ~0ull;
-          T[lid].slot = slot[j];
-          A.relax[lid] = 0;  // in-degree inside the ball
-          st_cg64(&A.index[slot[j]], ((uint64_t)nb[j] << 32) | lid);
-          ++lid;
-        }
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k)
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j)
+          if (j < cnt[k] && ((mine[k] >> j) & 1)) {
+            prefetch_l2(&adj[nb[k][j]]);  // expanded (or asked for its out-degree) at the next level
+            N[lid].meta = 0;
+            N[lid].key = nb[k][j];
+            N[lid].out4 = ~0ull;
+            T[lid].slot = slot[k][j];
+            A.relax[lid] = 0;  // in-degree inside the ball
+            st_cg64(&A.index[slot[k][j]], ((uint64_t)nb[k][j] << 32) | lid);
+            nlid[k][j] = lid;
+            ++lid;
+          }
       total_nodes += chunk_new;
       co.sync();
-      if (i < hi && expand) {
-        for (uint32_t j = 0; j < cnt; ++j) {
-          const uint32_t x = (uint32_t)ld_cg64(&A.index[slot[j]]);
-          N[i].out[j] = (uint16_t)x;
-          if (meta_add(&A.relax[x], 1u) == 0) T[x].in[0] = (uint16_t)i;  // the in-neighbour, if it stays the only one
+#pragma unroll
+      for (int k = 0; k < kBuildK; ++k) {
+        const uint32_t i = base + (uint32_t)k * Coop::kLanes + (uint32_t)co.lane;
+        if (i < hi && expand) {
+          uint64_t out4 = ~0ull;
+          uint32_t was[4];
+#pragma unroll
+          for (uint32_t j = 0; j < 4; ++j)
+            if (j < cnt[k] && nlid[k][j] == kLidPending) nlid[k][j] = (uint32_t)ld_cg64(&A.index[slot[k][j]]);
+#pragma unroll
+          for (uint32_t j = 0; j < 4; ++j)
+            if (j < cnt[k]) {
+              out4 = (out4 & ~(0xFFFFull << (16 * j))) | ((uint64_t)(nlid[k][j] & 0xFFFFu) << (16 * j));
+              was[j] = meta_add(&A.relax[nlid[k][j]], 1u);
+            }
+#pragma unroll
+          for (uint32_t j = 0; j < 4; ++j)
+            if (j < cnt[k] && was[j] == 0) T[nlid[k][j]].in[0] = (uint16_t)i;  // the in-neighbour, if it stays the only one
+          N[i].out4 = out4;
+          N[i].meta = (cnt[k] << kMetaOutShift) | (cnt[k] << kMetaInShift);  // out-degree | out-neighbours recorded
         }
-        N[i].meta = (cnt << kMetaOutShift) | (cnt << kMetaInShift);  // out-degree | out-neighbours recorded
       }
     }
     lo = hi;

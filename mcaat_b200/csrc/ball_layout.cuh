@@ -82,7 +82,8 @@ __device__ __forceinline__ BallArena ball_arena_of(uint8_t *base, uint8_t *smem,
 
 // the worker arenas in the graph handle (grow-only; the hash indices start out empty and every kernel leaves them so)
 static inline int ensure_ball_arena(mg_graph *g, uint32_t workers, const BallLayout &L) {
-  const uint64_t sig = ((uint64_t)L.bytes << 20) ^ ((uint64_t)L.index_log << 8) ^ (uint64_t)workers;
+  // the slot layout only: the two users may run different numbers of workers over the same slots
+  const uint64_t sig = ((uint64_t)L.bytes << 20) ^ ((uint64_t)L.index_log << 8);
   if (g->enum_arena.bytes < (size_t)workers * L.bytes || g->enum_arena_sig != sig) {
     MG_TRY(g->enum_arena.ensure((size_t)workers * L.bytes));
     MG_CUDA(cudaMemsetAsync(g->enum_arena.p, 0xFF, g->enum_arena.bytes, g->stream));

@@ -94,6 +94,8 @@ struct TicketRec {
   uint32_t n_chains;                   // records of its contraction
   uint32_t iters, relax_pops;          // of the last search: loop iterations on the contracted ball, relaxation entries
   uint32_t us_started, n_restarts;     // when the last search of this ticket began; searches started for it
+  uint32_t us_claims, us_turn;         // when every earlier ticket had claimed its ball; when this ticket's turn came
+  uint32_t root, n_watched;            // group (smallest ticket) and earlier unfinished tickets of it (0xFFFFFFFF: commit front)
 };
 struct PipeCtl {
   uint32_t ticket;       // next ticket to hand out
@@ -356,6 +358,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
   uint32_t abandoned = 0, reruns = 0, n_ooo = 0;
   uint32_t live = 0;  // ball nodes whose index slots are still occupied
   const unsigned long long t_kernel = gtime_ns();
+  const uint32_t poll_ns = (uint32_t)flags >> 8 ? (uint32_t)flags >> 8 : 300u;  // pause between two looks at the watched tickets
   for (;;) {
     uint32_t t = 0;
     if (lane == 0) t = atomicAdd(&ctl->ticket, 1u);
@@ -371,6 +374,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     R.n_cycles = R.n_nodes = R.n_keys = R.steps = R.expansions = 0;
     int stopped = 0;
     uint32_t us_build = 0, t_iters = 0, t_relax = 0, us_started = 0, t_searches = 0, n_chains = 0;
+    uint32_t us_claims = 0, us_turn = 0, t_root = t, n_watched = 0;
     bool claimed = false;  // this ticket's first ball has been claimed and "built" published
     auto publish_built = [&]() {
       if (claimed) return;
@@ -532,9 +536,13 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       if (__shfl_sync(kFull, full, 0)) return false;
       node_base = __shfl_sync(kFull, node_base, 0);
       cyc_base = __shfl_sync(kFull, cyc_base, 0);
-      for (uint32_t j = lane; j < n_nodes; j += 32) {
-        const uint32_t x = cyc_keys[j];
-        atomicOr(&visited[x >> 5], 1u << (x & 31));
+      for (uint32_t j = lane; j < n_nodes; j += 128) {  // four independent loads in flight per lane
+        uint32_t x[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) x[q] = j + 32u * q < n_nodes ? cyc_keys[j + 32u * q] : 0xFFFFFFFFu;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (x[q] != 0xFFFFFFFFu) atomicOr(&visited[x[q] >> 5], 1u << (x[q] & 31));
       }
       rec.fate = kFateAccepted;
       rec.status = status;
@@ -553,6 +561,10 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       rec.relax_pops = t_relax;
       rec.us_started = us_started;
       rec.n_restarts = t_searches;
+      rec.us_claims = us_claims;
+      rec.us_turn = us_turn;
+      rec.root = t_root;
+      rec.n_watched = n_watched;
       return true;
     };
     // results[start] = cycles (:479): off the hand-over path, after the ticket has been flagged done
@@ -582,6 +594,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       __nanosleep(200u);
     }
     if (stopped) break;
+    us_turn = us_claims = (uint32_t)((gtime_ns() - t_kernel) / 1000);
     bool independent = false;
     if (status != kEnumOverflow && !(flags & 4)) {
       __threadfence();
@@ -606,29 +619,43 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
     //      touch its ball); the earlier tickets that are not done yet are few (the window in flight): each lane watches one.
     //      More than 32 of them, or a ball somewhere that was claimed only in part: the turn is the commit front's.
     uint32_t watch = 0xFFFFFFFFu;
-    bool grouped = false;
-    if (status != kEnumOverflow && !(flags & 4) && t < __shfl_sync(kFull, ld_vol(&ctl->ooo_limit), 0)) {
+    bool more = false;  // the group has further unfinished members below the watched ones
+    const bool grouped = status != kEnumOverflow && !(flags & 4) && t < __shfl_sync(kFull, ld_vol(&ctl->ooo_limit), 0);
+    // the (up to 32) largest unfinished tickets of this ticket's group below `t`, one per lane; windows of 32 tickets from
+    // t downwards, a window is taken whole or left for the next batch
+    auto collect_watch = [&]() {
       const uint32_t root = __shfl_sync(kFull, lane == 0 ? uf_find(parent, t) : 0u, 0);
       const uint32_t front = __shfl_sync(kFull, ld_vol(&ctl->commit_idx), 0);
       uint32_t count = 0;
-      grouped = true;
-      for (uint32_t base = front; base < t; base += 32) {
+      watch = 0xFFFFFFFFu;
+      more = false;
+      t_root = root;
+      for (uint32_t hi = t; hi > front;) {
+        const uint32_t base = hi - front >= 32u ? hi - 32u : front;
         const uint32_t u = base + (uint32_t)lane;
-        const bool match = u < t && !ld_vol(&done[u]) && uf_find(parent, u) == root;
+        const bool match = u < hi && !ld_vol(&done[u]) && uf_find(parent, u) == root;
         const unsigned m = __ballot_sync(kFull, match);
         const uint32_t c = (uint32_t)__popc(m);
-        if (count + c > 32) { grouped = false; break; }
+        if (count + c > 32) { more = true; break; }
         if ((uint32_t)lane >= count && (uint32_t)lane < count + c) watch = base + __fns(m, 0, (int)((uint32_t)lane - count) + 1);
         count += c;
+        hi = base;
       }
-    }
+      return count;
+    };
+    if (grouped) n_watched = collect_watch();
+    else n_watched = 0xFFFFFFFFu;
     // ---- meanwhile keep the speculative result fresh, so that the
     bool skipped_now = false;
     for (uint32_t polls = 0;; ++polls) {
       if (grouped) {  // every watched ticket done?
         const bool pending = watch != 0xFFFFFFFFu && !ld_vol(&done[watch]);
         if (!pending) watch = 0xFFFFFFFFu;
-        if (!__any_sync(kFull, pending)) break;
+        if (!__any_sync(kFull, pending)) {
+          if (!more) break;
+          collect_watch();  // the next batch of earlier members (usually none is left unfinished: they commit in order)
+          continue;
+        }
       } else if (__shfl_sync(kFull, ld_vol(&go[t]), 0)) {  // own word: set by whoever moves the commit front onto this ticket
         break;
       }
@@ -659,7 +686,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
           }
         }
       }
-      __nanosleep(300u);
+      __nanosleep(poll_ns);
     }
     stopped = __shfl_sync(kFull, stopped, 0);
     if (stopped) break;
@@ -667,6 +694,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       finish(rec);
       continue;
     }
+    us_turn = (uint32_t)((gtime_ns() - t_kernel) / 1000);
     __threadfence();  // everything committed before this turn is visible from here on
     // ---- ordered commit: the bitmap is now exactly the one of position t in the sequential loop
     status = __shfl_sync(kFull, R.status, 0);
@@ -770,15 +798,16 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     MG_TRY(pool_len.alloc((size_t)len_cap * 4));
     // worker arenas live in the graph handle (they need no clearing between searches or calls)
     const uint32_t want =
-        (uint32_t)std::min<uint64_t>(n, (uint64_t)g->sm_count * env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32));  // see below
+        (uint32_t)std::min<uint64_t>(n, (uint64_t)g->sm_count * env_u32("MCAAT_ENUM_WORKERS_PER_SM", 4, 1, 32));  // see below
     const uint32_t blocks = (want + kWarpsPerBlock - 1) / kWarpsPerBlock, workers = blocks * kWarpsPerBlock;
     // shared memory: the workers of one SM share what the device offers (227 KB opt-in, 1 KB reserved per block)
-    const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32);
+    const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 4, 1, 32);
     const uint32_t smem_per_worker = std::min<uint32_t>(ball_smem_per_worker(g, workers_per_sm, kWarpsPerBlock),
                                                         env_u32("MCAAT_ENUM_SMEM_PER_WORKER", 1u << 20, 2048, 1u << 20));
     const BallLayout L = make_ball_layout(max_len, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 16), smem_per_worker);
     // diagnostics: chain records in the arena instead of shared memory (1); every commit in ticket order (4)
-    const int force_global = (int)(env_u32("MCAAT_ENUM_CHAINS_GLOBAL", 0, 0, 1) | (env_u32("MCAAT_ENUM_INORDER", 0, 0, 1) << 2));
+    const int force_global = (int)(env_u32("MCAAT_ENUM_CHAINS_GLOBAL", 0, 0, 1) | (env_u32("MCAAT_ENUM_INORDER", 0, 0, 1) << 2) |
+                                 (env_u32("MCAAT_ENUM_POLL_NS", 0, 0, 100000) << 8));
     MG_CUDA(cudaFuncSetAttribute(k_enum_pipeline, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(L.smem_bytes * kWarpsPerBlock)));
     MG_TRY(ensure_ball_arena(g, workers, L));
     uint32_t big_lock_log = env_u32("MCAAT_ENUM_LOCK_LOG", 19, 6, 26), big_relax = 1u << 20;
@@ -852,11 +881,12 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
   flush_timers(g);
   if (const char *trace = getenv("MCAAT_ENUM_TRACE")) {  // per-ticket timeline for profiling
     if (FILE *f = fopen(trace, "w")) {
-      fprintf(f, "ticket,fate,status,steps,n_cycles,us_searched,us_committed,n_ball,us_build,n_chains,iters,relax_pops,us_started,n_searches\n");
+      fprintf(f, "ticket,fate,status,steps,n_cycles,us_searched,us_committed,n_ball,us_build,n_chains,iters,relax_pops,us_started,n_searches,us_claims,us_turn,root,n_watched\n");
       for (uint64_t i = 0; i < n; ++i)
-        fprintf(f, "%llu,%d,%d,%u,%u,%u,%u,%u,%u,%u,%u,%u,%u,%u\n", (unsigned long long)i, recs[i].fate, recs[i].status, recs[i].steps,
+        fprintf(f, "%llu,%d,%d,%u,%u,%u,%u,%u,%u,%u,%u,%u,%u,%u,%u,%u,%u,%d\n", (unsigned long long)i, recs[i].fate, recs[i].status, recs[i].steps,
                 recs[i].n_cycles, recs[i].us_searched, recs[i].us_committed, recs[i].n_ball, recs[i].us_build, recs[i].n_chains,
-                recs[i].iters, recs[i].relax_pops, recs[i].us_started, recs[i].n_restarts);
+                recs[i].iters, recs[i].relax_pops, recs[i].us_started, recs[i].n_restarts, recs[i].us_claims, recs[i].us_turn, recs[i].root,
+                (int)recs[i].n_watched);
       fclose(f);
     }
   }

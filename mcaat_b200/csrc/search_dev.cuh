@@ -660,15 +660,19 @@ MG_HD uint32_t lock_get(EnumArena &A, uint32_t &n_keys, uint32_t key, int32_t de
 
 // _BackgroundCheck (src/cycle_finder.cpp:40-52) for up to 4 neighbours at once: all multiplicity and
 // visited words are loaded before any is tested, so the loads overlap instead of forming a chain.
-MG_HD void filtered_set(const GraphView &g, const uint32_t *visited, uint32_t node, uint32_t mu, const uint32_t *nb,
-                        int deg, uint32_t &n_out, uint32_t *out) {
-  uint32_t m[4] = {0, 0, 0, 0}, vw[4] = {0, 0, 0, 0};
+// (two halves, so that a caller with several nodes in hand can issue the loads of all of them before any test)
+MG_HD void filtered_loads(const GraphView &g, const uint32_t *visited, const uint32_t *nb, int deg, uint32_t *m, uint32_t *vw) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < 4; ++i) {
+    m[i] = vw[i] = 0;
     if (i < deg) {
       m[i] = ld_ro(&g.mult[nb[i]]);
       vw[i] = ld_cg32(&visited[nb[i] >> 5]);
     }
+  }
+}
+MG_HD void filtered_finish(uint32_t node, uint32_t mu, const uint32_t *nb, int deg, const uint32_t *m, const uint32_t *vw,
+                           uint32_t &n_out, uint32_t *out) {
   USet s;
   s.n = 0;
 #pragma unroll
@@ -679,6 +683,12 @@ MG_HD void filtered_set(const GraphView &g, const uint32_t *visited, uint32_t no
     }
   n_out = s.n;
   for (uint32_t i = 0; i < s.n && i < 4; ++i) out[i] = s.e[i];
+}
+MG_HD void filtered_set(const GraphView &g, const uint32_t *visited, uint32_t node, uint32_t mu, const uint32_t *nb,
+                        int deg, uint32_t &n_out, uint32_t *out) {
+  uint32_t m[4], vw[4];
+  filtered_loads(g, visited, nb, deg, m, vw);
+  filtered_finish(node, mu, nb, deg, m, vw, n_out, out);
 }
 // _GetOutgoings(node,set,mult), src/cycle_finder.cpp:58-72, memoised in the node's entry
 MG_HD void enum_outgoings(const GraphView &g, const uint64_t *adj, const uint32_t *visited, HotEnt &e, uint32_t mu,

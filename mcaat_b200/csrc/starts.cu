@@ -268,8 +268,11 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
     if (n_work == 0 || (tier == 1 && !use_ball && tier_log[1] <= tier_log[0])) continue;
     if (tier == 1 && use_ball) {
       // ---- long searches: one warp each on the extracted ball (arenas shared with the enumeration pipeline)
-      const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 8, 1, 32);
-      const uint32_t want = (uint32_t)std::min<uint64_t>(n_work, (uint64_t)g->sm_count * workers_per_sm);
+      const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 4, 1, 32);
+      // the searches of this tier are bound by the latency of their ball extraction, not by any throughput: more
+      // warps per SM than the enumeration runs (its limit is shared memory; here a worker only keeps its DFS stack there)
+      const uint32_t dls_workers_per_sm = env_u32("MCAAT_DLS_WORKERS_PER_SM", 16, 1, 32);
+      const uint32_t want = (uint32_t)std::min<uint64_t>(n_work, (uint64_t)g->sm_count * dls_workers_per_sm);
       const uint32_t blocks = (want + kDlsBallWarps - 1) / kDlsBallWarps, workers = blocks * kDlsBallWarps;
       const BallLayout L = make_ball_layout(limit, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 16),
                                             std::min<uint32_t>(ball_smem_per_worker(g, workers_per_sm, kDlsBallWarps),

@@ -623,6 +623,9 @@ uint64_t emu_contracted_ball(Emu *e, uint64_t start, int max_len, uint64_t *hot,
   return bs.B.n + 1;
 }
 
+// The navigation cache of the pruned graph (n entries), for the device micro-benchmark of the ball extraction.
+void emu_adj(Emu *e, uint64_t *out) { memcpy(out, e->adj.data(), (size_t)e->v.n * 8); }
+
 void emu_set_search_limits(int max_steps, uint32_t chain_cap) {
   g_max_steps = max_steps > 0 ? max_steps : kMaxSteps;
   g_chain_cap = chain_cap;

@@ -52,6 +52,7 @@ def lib():
         L.emu_set_algo.argtypes = [C.c_int, C.c_uint32]
         L.emu_set_search_limits.argtypes = [C.c_int, C.c_uint32]
         L.emu_contracted_ball.restype = C.c_uint64
+        L.emu_adj.argtypes = [C.c_void_p, C.c_void_p]
         L.emu_contracted_ball.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64]
         L.emu_search_one.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
@@ -177,6 +178,12 @@ class EmuGraph:
         in4 = np.zeros(cap, np.uint64)
         n = lib().emu_contracted_ball(self.h, int(start), max_len, hot.ctypes.data, in4.ctypes.data, cap)
         return hot[:2 * n].copy(), in4[:n].copy()
+
+    def adj(self):
+        """navigation cache of the pruned graph (call prune() first)"""
+        out = np.zeros(self.n, np.uint64)
+        lib().emu_adj(self.h, out.ctypes.data)
+        return out
 
     def find_cycles(self, starts, min_len, max_len, window=64, lock_log=13):
         starts = np.ascontiguousarray(starts, np.uint64)
