@@ -30,6 +30,7 @@
 //     is skipped for good (the marker precedes it in the order) and gives up at once.
 // The committed sequence is identical to the reference's threads=1 loop for any number of workers.
 #include <algorithm>
+#include <chrono>
 
 #include "common.cuh"
 #include "ball_dev.cuh"
@@ -751,6 +752,10 @@ static int grow_copy(DevBuf &buf, size_t new_bytes, size_t keep_bytes, cudaStrea
 int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len, int max_len, mg_cycles *out) {
   cudaStream_t s = g->stream;
   memset(out, 0, sizeof *out);
+  const bool host_timing = getenv("MCAAT_ENUM_HOST_TIMING") != nullptr;  // diagnostic: where the host side of the call spends its time
+  auto now_ms = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  const double t_enter = now_ms();
+  double t_launched = 0, t_kernels = 0, t_read = 0;
   if (!g->pruned || !g->adj.p) {
     set_error("mg_find_cycles: call mg_prune first (it builds the navigation cache)");
     return MG_EINVAL;
@@ -813,6 +818,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     uint32_t big_lock_log = env_u32("MCAAT_ENUM_LOCK_LOG", 19, 6, 26), big_relax = 1u << 20;
     uint32_t pos = 0;
     bool solo = false;  // the ticket at `pos` overflowed a worker arena: run it alone in the big arena
+    t_launched = now_ms();
     while (pos < n) {
       ctl.ticket = pos;
       ctl.commit_idx = pos;
@@ -871,6 +877,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
         solo = false;
       }
     }
+    t_kernels = now_ms();
     MG_CUDA(cudaMemcpyAsync(recs.data(), recs_dev.p, n * sizeof(TicketRec), cudaMemcpyDeviceToHost, s));
     h_nodes.resize(ctl.pool_nodes);
     h_len.resize(ctl.pool_cycles);
@@ -878,6 +885,7 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
     if (ctl.pool_cycles) MG_CUDA(cudaMemcpyAsync(h_len.data(), pool_len.p, (size_t)ctl.pool_cycles * 4, cudaMemcpyDeviceToHost, s));
     MG_CUDA(cudaStreamSynchronize(s));
   }
+  t_read = now_ms();
   flush_timers(g);
   if (const char *trace = getenv("MCAAT_ENUM_TRACE")) {  // per-ticket timeline for profiling
     if (FILE *f = fopen(trace, "w")) {
@@ -926,6 +934,9 @@ int run_find_cycles(mg_graph *g, const uint64_t *starts, uint64_t n, int min_len
   out->n_searches_run = ctl.searches_run;
   out->n_abandoned = ctl.n_abandoned;
   out->n_out_of_order = ctl.n_ooo;
+  if (host_timing)
+    fprintf(stderr, "[mg_find_cycles host ms] setup %.3f kernels+sync %.3f read-back %.3f assemble %.3f\n", t_launched - t_enter,
+            t_kernels - t_launched, t_read - t_kernels, now_ms() - t_read);
   return MG_OK;
 }
 

@@ -126,9 +126,14 @@ __global__ void k_split_mark(uint64_t n, PeelView P, uint32_t *split) {
     if ((threadIdx.x & 31) == 0) split[i >> 5] = m;
   }
 }
-__global__ void k_split_walk(PeelView P, const uint32_t *ids, uint32_t n_ids, int *capped) {
+__global__ void k_split_walk(PeelView P, uint32_t n_ids, int *capped) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n_ids && !split_walk_item(P, ids[i])) *capped = 1;
+  if (i < n_ids && !split_walk_item(P, i)) *capped = 1;
+}
+// the splitters' resolved pointers, densely (PeelView::sterm)
+__global__ void k_split_gather(PeelView P, uint32_t n_ids) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_ids) P.sterm[i] = peel_ptr(P, P.split_ids[i]);
 }
 __global__ void k_split_jump(PeelView P, const uint32_t *ids, uint32_t n_ids, int *unresolved) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -323,6 +328,8 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     P.recl = nullptr;
     P.dep = nullptr;
     P.dep_log = 0;
+    P.split_ids = nullptr;
+    P.sterm = nullptr;
     {
       TimedScope ts(g, T_ADJ, n);
       MG_LAUNCH(k_chain_init, stream_grid(g, n, 256), 256, 0, s, v, P, c + 5);
@@ -333,14 +340,17 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     if (n_work) {
       int *unresolved = (int *)(c + 7), *capped = (int *)(c + 7) + 1;
       {  // chain nodes -> terminals through 1-in-64 splitters
-        DevBuf split, split_ids;
+        DevBuf split, split_ids, sterm;
         MG_TRY(split.alloc(bm_bytes));
         MG_CUDA(cudaMemsetAsync(c + 7, 0, 8, s));
         MG_LAUNCH(k_split_mark, stream_grid(g, n, 256), 256, 0, s, n, P, split.as<uint32_t>());
         uint64_t n_split = 0;
         MG_TRY(bitmap_to_ids(split.as<uint32_t>(), n, split_ids, &n_split, s));
         if (n_split) {
-          MG_LAUNCH(k_split_walk, grid_for(n_split, 128), 128, 0, s, P, split_ids.as<uint32_t>(), (uint32_t)n_split, capped);
+          MG_TRY(sterm.alloc(n_split * 4));
+          P.split_ids = split_ids.as<uint32_t>();
+          P.sterm = sterm.as<uint32_t>();
+          MG_LAUNCH(k_split_walk, grid_for(n_split, 128), 128, 0, s, P, (uint32_t)n_split, capped);
           for (int round = 0; round < 36; round += 4) {
             MG_CUDA(cudaMemsetAsync(unresolved, 0, 4, s));
             for (int k = 0; k < 4; ++k)
@@ -350,6 +360,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
             MG_CUDA(cudaStreamSynchronize(s));
             if (!h) break;
           }
+          MG_LAUNCH(k_split_gather, grid_for(n_split, 256), 256, 0, s, P, (uint32_t)n_split);
         }
         MG_LAUNCH(k_chain_resolve, grid, 256, 0, s, n, P, capped);
         int hc = 0;

@@ -83,9 +83,13 @@ MG_HD void fence_sc() {
 //      evaluated by an asynchronous work list over a (terminal -> dependent branch nodes) multimap.
 struct PeelView {
   uint64_t *adj;            // per item: Forward | validity mask << 32 on the post-filter graph
-  uint64_t *ent;            // per item: chain pointer (low word) | owner: splitter whose walk passed the item, step 2
-                            // (bits 32..62, kNoOwner = none) | item was classified a chain node by step 1 (bit 63).
-                            // One 8-byte entry = one sector per hop of a walk.
+  uint64_t *ent;            // per item: chain pointer (low word) | owner: the splitter whose walk passed the item, step 2, as
+                            // its position in split_ids (bits 32..62, kNoOwner = none) | item was classified a chain node
+                            // by step 1 (bit 63).  One 8-byte entry = one sector per hop of a walk.
+  const uint32_t *split_ids;  // the splitters (ascending item ids)
+  uint32_t *sterm;          // per splitter: its pointer after step 2b — 4 bytes per 64 chain nodes, so the table the
+                            // resolution pass reads at random stays in L2 (the splitters' own entries, spread over the
+                            // whole entry array, do not: 64 B of DRAM traffic per resolved item)
   uint32_t *chain;          // bitmap: chain nodes
   uint32_t *tpeeled;        // bitmap: peeled terminals
   const uint32_t *tipbits;  // bitmap: CollectTips on the loaded graph (:436)
@@ -170,19 +174,20 @@ MG_HD uint64_t ent_cas(uint64_t *p, uint64_t expect, uint64_t val) {
   return old;
 #endif
 }
-// a. walk of splitter s; returns false when the hop cap was hit (ptr[s] is then left untouched)
-MG_HD bool split_walk_item(const PeelView &P, uint32_t s) {
+// a. walk of splitter number k; returns false when the hop cap was hit (ptr[s] is then left untouched)
+MG_HD bool split_walk_item(const PeelView &P, uint32_t k) {
+  const uint32_t s = P.split_ids[k];
   uint32_t p = peel_ptr(P, s), next = kNull;
   for (uint32_t hops = 0; hops < kWalkCapSplitter; ++hops) {
     if (is_splitter_id(p)) { next = p; break; }      // another splitter (or a terminal whose id hashes like one)
     const uint64_t e = ld_cg64(&P.ent[p]);
     const uint32_t hi = (uint32_t)(e >> 32);
     if (!(hi & kEntChain)) { next = p; break; }      // terminal
-    if ((hi & kNoOwner) != kNoOwner) { next = hi & kNoOwner; break; }  // claimed; == s: a splitter-free cycle
+    if ((hi & kNoOwner) != kNoOwner) { next = P.split_ids[hi & kNoOwner]; break; }  // claimed; by k itself: a splitter-free cycle
     // nobody writes the pointer of an unclaimed non-splitter chain node during the walks, so a failed exchange
     // means another walk has claimed the item in between
-    const uint64_t old = ent_cas(&P.ent[p], e, (e & 0x80000000FFFFFFFFull) | ((uint64_t)s << 32));
-    if (old != e) { next = (uint32_t)(old >> 32) & kNoOwner; break; }
+    const uint64_t old = ent_cas(&P.ent[p], e, (e & 0x80000000FFFFFFFFull) | ((uint64_t)k << 32));
+    if (old != e) { next = P.split_ids[(uint32_t)(old >> 32) & kNoOwner]; break; }
     p = (uint32_t)e;
   }
   if (next == kNull) return false;
@@ -205,7 +210,7 @@ MG_HD bool chain_resolve_item(const PeelView &P, uint32_t v) {
   const uint32_t hv = (uint32_t)(ev >> 32);
   if (!(hv & kEntChain)) return true;
   uint32_t o = hv & kNoOwner;
-  if (o != kNoOwner) { peel_ptr(P, v) = ld_cg_u32(&peel_ptr(P, o)); return true; }
+  if (o != kNoOwner) { peel_ptr(P, v) = P.sterm[o]; return true; }
   uint32_t p = (uint32_t)ev;
   // Brent's cycle detection: `mark` is the item the walk stood on 2^j hops after v.  A walk that comes back to
   // it runs round a cycle of chain nodes with neither splitter nor owner (the closed loop of a tandem repeat
@@ -224,7 +229,7 @@ MG_HD bool chain_resolve_item(const PeelView &P, uint32_t v) {
     const uint32_t hp = (uint32_t)(ep >> 32);
     if (!(hp & kEntChain)) { peel_ptr(P, v) = p; return true; }
     o = hp & kNoOwner;
-    if (o != kNoOwner) { peel_ptr(P, v) = ld_cg_u32(&peel_ptr(P, o)); return true; }
+    if (o != kNoOwner) { peel_ptr(P, v) = P.sterm[o]; return true; }
     if (p == mark) return true;
     if (++since == power) { mark = p; power <<= 1; since = 0; }
     p = (uint32_t)ep;  // the successor, or already p's terminal: both lie ahead on the same chain

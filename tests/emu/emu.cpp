@@ -161,6 +161,7 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   PeelView P;
   P.adj = e->adj.data(); P.ent = ent.data(); P.chain = chain.data(); P.tpeeled = tpeeled.data();
   P.tipbits = tipbits.data(); P.dep = nullptr; P.dep_log = 0;
+  P.split_ids = nullptr; P.sterm = nullptr;
   std::vector<uint32_t> recl(words, 0);
   P.recl = recl.data();
   uint64_t pairs = 0;
@@ -179,13 +180,19 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
     std::vector<uint32_t> split_ids;
     for (uint64_t i = 0; i < n; ++i)
       if (bm_get(P.chain, (uint32_t)i) && is_splitter_id((uint32_t)i)) split_ids.push_back((uint32_t)i);
-    if (reverse_order & 1) std::reverse(split_ids.begin(), split_ids.end());
-    for (uint32_t sid : split_ids) capped |= !split_walk_item(P, sid);
+    // (the walks of the device run in any order: here ascending or descending splitter number)
+    std::vector<uint32_t> sterm(split_ids.size() + 1, 0);
+    P.split_ids = split_ids.data();
+    P.sterm = sterm.data();
+    const uint32_t ns = (uint32_t)split_ids.size();
+    if (reverse_order & 1) { for (uint32_t k = ns; k-- > 0;) capped |= !split_walk_item(P, k); }
+    else for (uint32_t k = 0; k < ns; ++k) capped |= !split_walk_item(P, k);
     for (int round = 0; round < 36; ++round) {
       bool any = false;
       for (uint32_t sid : split_ids) any |= split_jump_item(P, sid);
       if (!any) break;
     }
+    for (uint32_t k = 0; k < ns; ++k) sterm[k] = peel_ptr(P, split_ids[k]);
     if (reverse_order & 1) { for (uint64_t i = n; i-- > 0;) capped |= !chain_resolve_item(P, (uint32_t)i); }
     else for (uint64_t i = 0; i < n; ++i) capped |= !chain_resolve_item(P, (uint32_t)i);
   }
