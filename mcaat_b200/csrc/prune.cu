@@ -94,7 +94,7 @@ __global__ void k_mult1(GraphView g, unsigned long long *count) {
 }
 // ---- RecursiveReduction by chain contraction (search_dev.cuh, "peel") -------------------------
 // step 1: navigation cache on the post-filter graph, chain / seed bitmaps, chain pointers
-__global__ void k_chain_init(GraphView g, PeelView P, unsigned long long *n_pairs) {
+__global__ void k_chain_init(GraphView g, PeelView P, uint32_t *branch, unsigned long long *n_pairs) {
   __shared__ unsigned sh[1];
   BlockCounters<1> bc(sh);
   const uint64_t n32 = (g.n + 31) & ~31ull;
@@ -103,11 +103,13 @@ __global__ void k_chain_init(GraphView g, PeelView P, unsigned long long *n_pair
     int deg = -1;
     if (i < g.n) deg = chain_init_item(g, P, (uint32_t)i, is_chain, is_seed);
     unsigned mc = __ballot_sync(0xffffffffu, is_chain), ms = __ballot_sync(0xffffffffu, is_seed);
+    unsigned mb = __ballot_sync(0xffffffffu, deg >= 2);  // branch nodes: all that steps 2b and 3a ever look at
     unsigned pairs = deg >= 2 ? (unsigned)deg : 0u;
     for (int d = 16; d; d >>= 1) pairs += __shfl_down_sync(0xffffffffu, pairs, d);
     if ((threadIdx.x & 31) == 0) {
       P.chain[i >> 5] = mc;
       P.tpeeled[i >> 5] = ms;
+      branch[i >> 5] = mb;
       bc.add(0, pairs);
     }
   }
@@ -145,17 +147,19 @@ __global__ void k_chain_resolve(uint64_t n, PeelView P, int *capped) {
     if (!chain_resolve_item(P, (uint32_t)i)) *capped = 1;
 }
 // step 2b (search_dev.cuh): unary branch nodes become chain nodes
-__global__ void k_reclass(GraphView g, PeelView P, uint32_t *fresh, uint32_t *newseed, unsigned long long *n_fresh,
-                          unsigned long long *n_seed) {
+// (over the list of branch nodes; `fresh` / `newseed` are zeroed by the caller)
+__global__ void k_reclass(GraphView g, PeelView P, const uint32_t *ids, uint32_t n_ids, uint32_t *fresh, uint32_t *newseed,
+                          unsigned long long *n_fresh, unsigned long long *n_seed) {
   __shared__ unsigned sh[2];
   BlockCounters<2> bc(sh);
-  const uint64_t n32 = (g.n + 31) & ~31ull;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
-    int r = i < g.n ? reclass_item(g, P, (uint32_t)i) : 0;
+  const uint32_t n32 = (n_ids + 31) & ~31u;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += gridDim.x * blockDim.x) {
+    const uint32_t b = i < n_ids ? ids[i] : 0u;
+    const int r = i < n_ids ? reclass_item(g, P, b) : 0;
+    if (r == 1) atomicOr(&fresh[b >> 5], 1u << (b & 31));
+    if (r == 2) atomicOr(&newseed[b >> 5], 1u << (b & 31));
     unsigned mf = __ballot_sync(0xffffffffu, r == 1), ms = __ballot_sync(0xffffffffu, r == 2);
     if ((threadIdx.x & 31) == 0) {
-      fresh[i >> 5] = mf;
-      newseed[i >> 5] = ms;
       bc.add(0, (unsigned)__popc(mf));
       bc.add(1, (unsigned)__popc(ms));
     }
@@ -183,9 +187,9 @@ __global__ void k_chain_jump(uint64_t n, PeelView P, int *unresolved) {
   if (__any_sync(0xffffffffu, u) && (threadIdx.x & 31) == 0) *unresolved = 1;
 }
 // step 3a: (terminal -> dependent branch node) multimap
-__global__ void k_dep_register(GraphView g, PeelView P) {
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < g.n; i += (uint64_t)gridDim.x * blockDim.x)
-    dep_register_item(g, P, (uint32_t)i);
+__global__ void k_dep_register(GraphView g, PeelView P, const uint32_t *ids, uint32_t n_ids) {  // over the branch nodes
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_ids; i += gridDim.x * blockDim.x)
+    dep_register_item(g, P, ids[i]);
 }
 // step 3b: asynchronous work list over peeled terminals; each thread follows its cascade with a
 // small private stack, the rest goes to the next work list
@@ -330,13 +334,17 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     P.dep_log = 0;
     P.split_ids = nullptr;
     P.sterm = nullptr;
+    DevBuf branch, branch_ids;
+    MG_TRY(branch.alloc(bm_bytes));
     {
       TimedScope ts(g, T_ADJ, n);
-      MG_LAUNCH(k_chain_init, stream_grid(g, n, 256), 256, 0, s, v, P, c + 5);
+      MG_LAUNCH(k_chain_init, stream_grid(g, n, 256), 256, 0, s, v, P, branch.as<uint32_t>(), c + 5);
     }
     uint64_t n_work = 0;
     MG_TRY(bitmap_to_ids(tpeeled.as<uint32_t>(), n, work, &n_work, s));  // seeds
     TimedScope ts(g, T_PEEL, n);
+    uint64_t n_branch = 0;
+    if (n_work) MG_TRY(bitmap_to_ids(branch.as<uint32_t>(), n, branch_ids, &n_branch, s));
     if (n_work) {
       int *unresolved = (int *)(c + 7), *capped = (int *)(c + 7) + 1;
       {  // chain nodes -> terminals through 1-in-64 splitters
@@ -391,8 +399,11 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
         MG_TRY(rc.alloc(16));
         for (int round = 0; round < 4; ++round) {
           MG_CUDA(cudaMemsetAsync(rc.p, 0, 16, s));
-          MG_LAUNCH(k_reclass, stream_grid(g, n, 256), 256, 0, s, v, P, fresh.as<uint32_t>(), newseed.as<uint32_t>(),
-                    rc.as<unsigned long long>(), rc.as<unsigned long long>() + 1);
+          MG_CUDA(cudaMemsetAsync(fresh.p, 0, bm_bytes, s));
+          MG_CUDA(cudaMemsetAsync(newseed.p, 0, bm_bytes, s));
+          if (n_branch)
+            MG_LAUNCH(k_reclass, stream_grid(g, n_branch, 256), 256, 0, s, v, P, branch_ids.as<uint32_t>(), (uint32_t)n_branch,
+                      fresh.as<uint32_t>(), newseed.as<uint32_t>(), rc.as<unsigned long long>(), rc.as<unsigned long long>() + 1);
           unsigned long long hc[2];
           MG_CUDA(cudaMemcpyAsync(hc, rc.p, 16, cudaMemcpyDeviceToHost, s));
           MG_CUDA(cudaStreamSynchronize(s));
@@ -433,7 +444,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
       MG_CUDA(cudaMemsetAsync(dep.p, 0xFF, dep.bytes, s));
       P.dep = dep.as<uint64_t>();
       P.dep_log = dep_log;
-      MG_LAUNCH(k_dep_register, grid, 256, 0, s, v, P);
+      if (n_branch) MG_LAUNCH(k_dep_register, grid_for(n_branch, 256), 256, 0, s, v, P, branch_ids.as<uint32_t>(), (uint32_t)n_branch);
       uint32_t next_cap = (uint32_t)(pairs + 1024 < 0xFFFFFFF0ull ? pairs + 1024 : 0xFFFFFFF0ull);
       uint32_t *next_count = (uint32_t *)(c + 6);
       int *overflow = (int *)(c + 6) + 1;
