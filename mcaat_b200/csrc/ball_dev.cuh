@@ -97,6 +97,8 @@ struct Coop {
     return incl - x;
   }
   __device__ bool any(bool p) const { return __any_sync(0xffffffffu, p) != 0; }
+  // position of this lane among the lanes with p (all lanes call it)
+  __device__ uint32_t rank(bool p) const { return (uint32_t)__popc(__ballot_sync(0xffffffffu, p) & ((1u << lane) - 1u)); }
   // appends v of every lane with p to list[n..) (lane order); returns the new length.  All lanes call it.
   __device__ uint32_t append(uint32_t *list, uint32_t n, bool p, uint32_t v) const {
     const unsigned m = __ballot_sync(0xffffffffu, p);
@@ -108,6 +110,7 @@ MG_HD uint64_t index_cas(uint64_t *p, uint64_t expect, uint64_t val) {
   return (uint64_t)atomicCAS((unsigned long long *)p, (unsigned long long)expect, (unsigned long long)val);
 }
 MG_HD uint32_t meta_add(uint32_t *p, uint32_t v) { return atomicAdd(p, v); }
+MG_HD void meta_or(uint32_t *p, uint32_t v) { atomicOr(p, v); }
 MG_HD void st_cg64(uint64_t *p, uint64_t v) { __stcg((unsigned long long *)p, (unsigned long long)v); }
 #else
 struct Coop {
@@ -117,6 +120,7 @@ struct Coop {
   uint32_t sum(uint32_t x) const { return x; }
   uint32_t exclusive_prefix(uint32_t) const { return 0; }
   bool any(bool p) const { return p; }
+  uint32_t rank(bool) const { return 0; }
   uint32_t append(uint32_t *list, uint32_t n, bool p, uint32_t v) const {
     if (p) list[n++] = v;
     return n;
@@ -132,6 +136,7 @@ MG_HD uint32_t meta_add(uint32_t *p, uint32_t v) {
   *p = old + v;
   return old;
 }
+MG_HD void meta_or(uint32_t *p, uint32_t v) { *p |= v; }
 MG_HD void st_cg64(uint64_t *p, uint64_t v) { *p = v; }
 #endif
 
@@ -189,6 +194,19 @@ MG_HD NodeHead ld_head(const LNode *n) {
   return h;
 }
 
+// the same through L2 (records another lane has just changed with an atomic)
+MG_HD NodeHead ld_head_cg(const LNode *n) {
+  NodeHead h;
+#if defined(__CUDA_ARCH__)
+  const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(n));
+  h.meta = v.x;
+  h.out4 = (uint64_t)v.z | ((uint64_t)v.w << 32);
+#else
+  h.meta = n->meta;
+  h.out4 = n->out4;
+#endif
+  return h;
+}
 #ifndef MG_BUILD_K
 #define MG_BUILD_K 2
 #endif
@@ -1011,6 +1029,10 @@ struct alignas(16) DChain {
 };
 static_assert(sizeof(DChain) == 16, "chain record");
 constexpr uint32_t kDSeen = 1u << 31, kDTailOut = 1u << 16;
+// node meta of dball_build beyond the degree fields: the node starts a chain record although it continues a chain (every
+// kDChainCut-th level: bounds the serial walk of the contraction), the node continues the chain of its in-neighbour
+constexpr uint32_t kDMetaCut = 1u << 25, kDMetaNonHead = 1u << 26;
+constexpr int kDChainCut = 16;
 
 MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, const BallArena &A, uint32_t &n_nodes,
                                const Coop &co) {
@@ -1031,6 +1053,8 @@ MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, c
   int status = kDlsNotFound;
   for (int depth = 0; depth <= limit && lo < hi && status == kDlsNotFound; ++depth) {
     const bool expand = depth < limit;  // nodes at distance `limit` are only asked for their out-degree (:294)
+    const uint32_t cut_here = depth > 0 && depth % kDChainCut == 0 ? kDMetaCut : 0u;
+    const uint32_t cut_next = (depth + 1) % kDChainCut == 0 ? kDMetaCut : 0u;
     for (uint32_t base = lo; base < hi; base += Coop::kLanes * kBuildK) {  // kBuildK nodes per lane, as in ball_build
       uint32_t nb[kBuildK][4], slot[kBuildK][4], nlid[kBuildK][4], cnt[kBuildK], mine[kBuildK];
       uint64_t av[kBuildK];
@@ -1048,7 +1072,7 @@ MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, c
           if (deg > 4) deg = 4;
           cnt[k] = (uint32_t)deg;
           if (!expand) {
-            N[i].meta = cnt[k] << kMetaOutShift;  // out-degree on the graph (:294); no neighbours recorded
+            N[i].meta = (cnt[k] << kMetaOutShift) | cut_here;  // out-degree on the graph (:294); no neighbours recorded
             cnt[k] = 0;
           }
         }
@@ -1079,7 +1103,7 @@ MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, c
         for (uint32_t j = 0; j < 4; ++j)
           if (j < cnt[k] && ((mine[k] >> j) & 1)) {
             prefetch_l2(&adj[nb[k][j]]);  // expanded (or asked for its out-degree) at the next level
-            N[lid].meta = 0;
+            N[lid].meta = cut_next;
             N[lid].key = nb[k][j];
             N[lid].out4 = ~0ull;
             T[lid].slot = slot[k][j];
@@ -1109,7 +1133,7 @@ MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, c
           for (uint32_t j = 0; j < 4; ++j)
             if (j < cnt[k] && was[j] == 0) T[nlid[k][j]].in[0] = (uint16_t)i;  // the in-neighbour, if it stays the only one
           N[i].out4 = out4;
-          N[i].meta = (cnt[k] << kMetaOutShift) | (cnt[k] << kMetaInShift);  // out-degree | out-neighbours recorded
+          N[i].meta = (cnt[k] << kMetaOutShift) | (cnt[k] << kMetaInShift) | cut_here;  // out-degree | out-neighbours recorded
         }
       }
     }
@@ -1123,41 +1147,58 @@ MG_HD_NOINLINE int dball_build(const uint64_t *adj, uint32_t start, int limit, c
 
 // (node meta of dball_build: bits 16..18 out-degree on the graph, bits 20..22 out-neighbours recorded in the ball — the
 //  same, except for nodes at distance `limit`, which are not expanded)
-MG_HD bool dball_is_head(const BallArena &A, uint32_t x) {
-  if (x == 0) return true;
-  if (ld_cg32(&A.relax[x]) != 1) return true;
-  const uint32_t u = A.tails[x].in[0];
-  return u == 0 || ((A.nodes[u].meta >> kMetaInShift) & 7u) != 1;
-}
-// chains of the ball -> C[0 .. n_chains); returns the number of chains
+// chains of the ball -> C[0 .. n_chains); returns the number of chains.  A node continues the chain of its in-neighbour
+// u when it is not the start, has no other in-neighbour, u is not the start and has no other out-neighbour — and the
+// node does not lie on a level where chains are cut (any partition of a chain into consecutive pieces is searched
+// alike: a piece is one step of the search, its tail pushes the head of the next piece).
 MG_HD_NOINLINE uint32_t dball_contract(const BallArena &A, uint32_t n_nodes, DChain *C, const Coop &co) {
-  const LNode *N = A.nodes;
+  LNode *N = A.nodes;
+  // parents mark the children that continue their chain (four nodes per lane and round: the loads overlap)
+  for (uint32_t u0 = 0; u0 < n_nodes; u0 += Coop::kLanes * 4) {
+    NodeHead h[4];
+    uint32_t indeg[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t u = u0 + (uint32_t)q * Coop::kLanes + (uint32_t)co.lane;
+      h[q].meta = 0;
+      h[q].out4 = ~0ull;
+      if (u != 0 && u < n_nodes) h[q] = ld_head(&N[u]);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t x = (uint32_t)h[q].out4 & 0xFFFFu;
+      indeg[q] = ((h[q].meta >> kMetaInShift) & 7u) == 1 && x != 0 ? ld_cg32(&A.relax[x]) : 0u;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (indeg[q] == 1) meta_or(&N[(uint32_t)h[q].out4 & 0xFFFFu].meta, kDMetaNonHead);
+  }
+  co.sync();
   uint32_t n_chains = 0;
   for (uint32_t base = 0; base < n_nodes; base += Coop::kLanes) {
     const uint32_t x = base + (uint32_t)co.lane;
-    const bool head = x < n_nodes && dball_is_head(A, x);
-    const uint32_t before = co.exclusive_prefix(head ? 1u : 0u), cnt = co.sum(head ? 1u : 0u);
-    if (head) {
-      A.shead[n_chains + before] = (uint16_t)x;
-      A.spos[x] = n_chains + before;  // chain number of a head (other nodes are never looked up)
-    }
-    n_chains += cnt;
+    const uint32_t m = x < n_nodes ? ld_cg32(&N[x].meta) : 0u;
+    const bool head = x < n_nodes && (!(m & kDMetaNonHead) || (m & kDMetaCut));
+    const uint32_t r = co.rank(head);
+    if (head) A.spos[x] = n_chains + r;  // chain number of a head (other nodes are never looked up)
+    n_chains = co.append(A.ckeys, n_chains, head, x);
   }
   co.sync();
   for (uint32_t s = (uint32_t)co.lane; s < n_chains; s += Coop::kLanes) {
-    uint32_t x = A.shead[s], c = 1;
-    for (;;) {
-      if (s == 0 || ((N[x].meta >> kMetaInShift) & 7u) != 1) break;
-      const uint32_t y = N[x].out[0];
-      if (dball_is_head(A, y)) break;
-      x = y;
+    uint32_t c = 1;
+    NodeHead cur = ld_head_cg(&N[A.ckeys[s]]);
+    for (;;) {  // one load per node of the chain
+      if (s == 0 || ((cur.meta >> kMetaInShift) & 7u) != 1) break;
+      const NodeHead nx = ld_head_cg(&N[(uint32_t)cur.out4 & 0xFFFFu]);
+      if (!(nx.meta & kDMetaNonHead) || (nx.meta & kDMetaCut)) break;
+      cur = nx;
       ++c;
     }
-    const uint32_t deg = (N[x].meta >> kMetaOutShift) & 7u;
+    const uint32_t deg = (cur.meta >> kMetaOutShift) & 7u;
     DChain d;
     d.w0 = c | (deg ? kDTailOut : 0u);
     d.pad = 0;
-    uint64_t o = N[x].out4, o2 = 0;
+    uint64_t o = cur.out4, o2 = 0;
     for (int q = 0; q < 4; ++q) {
       const uint32_t a = (uint32_t)(o >> (16 * q)) & 0xFFFFu;
       o2 |= (uint64_t)(a == kNoLid ? kNoLid : (A.spos[a] & 0xFFFFu)) << (16 * q);  // out-neighbours of a tail are heads

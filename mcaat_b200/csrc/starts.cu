@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(32 * kDlsBallWarps) k_dls_ball(const uint64_t 
                                                           const uint32_t *__restrict__ todo, uint32_t n_todo, int limit,
                                                           uint8_t *arena, BallLayout L, int8_t *result, uint32_t *queue,
                                                           unsigned long long *expansions, uint32_t *per_search,
-                                                          uint32_t stk_smem) {
+                                                          uint32_t stk_smem, uint32_t n_total) {
   extern __shared__ __align__(16) uint8_t dls_ball_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t worker = blockIdx.x * kDlsBallWarps + warp;
@@ -178,8 +178,11 @@ __global__ void __launch_bounds__(32 * kDlsBallWarps) k_dls_ball(const uint64_t 
     q = __shfl_sync(0xffffffffu, q, 0);
     if (q >= n_todo) break;
     const uint32_t idx = todo[q];
+    unsigned long long t0 = 0, t1 = 0, t2 = 0;
+    if (per_search) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
     ball_clear(A, live, co);
     int r = dball_build(adj, cand[idx], limit, A, live, co);
+    if (per_search) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
     uint32_t exp = 0;
     if (r != kDlsSetFull) {
       dball_contract(A, live, C, co);
@@ -188,7 +191,13 @@ __global__ void __launch_bounds__(32 * kDlsBallWarps) k_dls_ball(const uint64_t 
     }
     if (lane == 0) {
       result[idx] = (int8_t)r;
-      if (per_search) per_search[idx] = exp;
+      if (per_search) {  // diagnostics (MCAAT_DLS_VERBOSE): expansions, ball size, extraction and search time
+        if (per_search[0] == 0) per_search[0] = 1;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t2));
+        per_search[idx] = exp;
+        uint32_t *d = per_search + n_total + 4 * (size_t)q;
+        d[0] = live; d[1] = (uint32_t)((t1 - t0) / 1000); d[2] = (uint32_t)((t2 - t1) / 1000); d[3] = (uint32_t)(t0 / 1000);
+      }
       if (r >= 0) exp_total += exp;
     }
   }
@@ -261,7 +270,7 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
   A.stk_cap = (uint32_t)(4 * limit + 8) | 1u;  // odd: per-thread stacks in shared memory spread over the banks
   const bool verbose = getenv("MCAAT_DLS_VERBOSE") != nullptr;
   DevBuf per_search;
-  if (verbose) MG_TRY(per_search.alloc(n * 4));
+  if (verbose) MG_TRY(per_search.alloc(n * 4 * 5));
   const bool use_ball = env_u32("MCAAT_DLS_BALL", 1, 0, 1) != 0;
   for (int tier = 0; tier < 2; ++tier) {
     const uint64_t n_work = tier == 0 ? n : todo.size();
@@ -291,7 +300,29 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
         TimedScope ts(g, T_DLS, 0);
         MG_LAUNCH(k_dls_ball, blocks, 32 * kDlsBallWarps, (size_t)stk_smem * 4 * kDlsBallWarps, s, g->adj.as<uint64_t>(), ids_dev,
                   todo_b.as<uint32_t>(), (uint32_t)n_work, limit, g->enum_arena.as<uint8_t>(), L, result.as<int8_t>(),
-                  ctr.as<uint32_t>(), exp_dev, verbose ? per_search.as<uint32_t>() : nullptr, stk_smem);
+                  ctr.as<uint32_t>(), exp_dev, verbose ? per_search.as<uint32_t>() : nullptr, stk_smem, (uint32_t)n);
+      }
+      if (verbose) {
+        std::vector<uint32_t> d(n_work * 4);
+        MG_CUDA(cudaMemcpyAsync(d.data(), per_search.as<uint32_t>() + n, n_work * 16, cudaMemcpyDeviceToHost, s));
+        MG_CUDA(cudaStreamSynchronize(s));
+        uint64_t sb = 0, sd = 0, mb = 0, md = 0, t_first = ~0ull, t_last = 0;
+        for (uint64_t i = 0; i < n_work; ++i) {
+          sb += d[4 * i + 1]; sd += d[4 * i + 2];
+          mb = std::max<uint64_t>(mb, d[4 * i + 1]); md = std::max<uint64_t>(md, d[4 * i + 2]);
+          t_first = std::min<uint64_t>(t_first, d[4 * i + 3]);
+          t_last = std::max<uint64_t>(t_last, (uint64_t)d[4 * i + 3] + d[4 * i + 1] + d[4 * i + 2]);
+        }
+        fprintf(stderr, "[mg_dls] ball tier: %u workers; extraction us mean %.0f max %llu; search us mean %.0f max %llu; span %llu us\n", workers,
+                (double)sb / n_work, (unsigned long long)mb, (double)sd / n_work, (unsigned long long)md, (unsigned long long)(t_last - t_first));
+        if (const char *f = getenv("MCAAT_DLS_TRACE")) {
+          if (FILE *fp = fopen(f, "w")) {
+            fprintf(fp, "q,n_ball,us_build,us_search,us_start\n");
+            for (uint64_t i = 0; i < n_work; ++i)
+              fprintf(fp, "%llu,%u,%u,%u,%llu\n", (unsigned long long)i, d[4 * i], d[4 * i + 1], d[4 * i + 2], (unsigned long long)(d[4 * i + 3] - (uint32_t)t_first));
+            fclose(fp);
+          }
+        }
       }
       MG_CUDA(cudaMemcpyAsync(res.data(), result.p, n, cudaMemcpyDeviceToHost, s));
       MG_CUDA(cudaStreamSynchronize(s));
