@@ -142,9 +142,32 @@ __global__ void k_split_jump(PeelView P, const uint32_t *ids, uint32_t n_ids, in
   bool u = i < n_ids && split_jump_item(P, ids[i]);
   if (__any_sync(0xffffffffu, u) && (threadIdx.x & 31) == 0) *unresolved = 1;
 }
+// (four items per thread and round: these passes are bound by the latency of two dependent loads per item — the entry,
+//  then what it names — so the loads of several items have to be in flight per thread)
 __global__ void k_chain_resolve(uint64_t n, PeelView P, int *capped) {
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
-    if (!chain_resolve_item(P, (uint32_t)i)) *capped = 1;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 4 * stride) {
+    uint64_t ev[4];
+    uint32_t tv[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint64_t v = i0 + q * stride;
+      ev[q] = v < n && !is_splitter_id((uint32_t)v) ? P.ent[v] : 0ull;  // 0: not a chain node
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {  // the common case: a walk passed the item, its splitter knows the terminal
+      const uint32_t hv = (uint32_t)(ev[q] >> 32);
+      tv[q] = (hv & kEntChain) && (hv & kNoOwner) != kNoOwner ? P.sterm[hv & kNoOwner] : 0u;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint64_t v = i0 + q * stride;
+      const uint32_t hv = (uint32_t)(ev[q] >> 32);
+      if (!(hv & kEntChain)) continue;
+      if ((hv & kNoOwner) != kNoOwner) peel_ptr(P, (uint32_t)v) = tv[q];
+      else if (!chain_resolve_item(P, (uint32_t)v)) *capped = 1;  // head of a chain: walks to the first item that knows
+    }
+  }
 }
 // step 2b (search_dev.cuh): unary branch nodes become chain nodes
 // (over the list of branch nodes; `fresh` / `newseed` are zeroed by the caller)
@@ -177,8 +200,21 @@ __global__ void k_or_words(uint32_t *dst, const uint32_t *src, size_t n_words) {
   if (i < n_words) dst[i] |= src[i];
 }
 __global__ void k_relink_final(uint64_t n, PeelView P) {
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
-    relink_final_item(P, (uint32_t)i);
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 4 * stride) {
+    uint32_t t[4];
+    bool moved[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint64_t v = i0 + q * stride;
+      t[q] = v < n && bm_get(P.chain, (uint32_t)v) ? ld_cg_u32(&peel_ptr(P, (uint32_t)v)) : kNull;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) moved[q] = t[q] != kNull && bm_get(P.chain, t[q]);  // terminal re-classified by step 2b: rare
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (moved[q]) relink_final_item(P, (uint32_t)(i0 + q * stride));
+  }
 }
 // exhaustive fallback: one pointer-jumping round over every item
 __global__ void k_chain_jump(uint64_t n, PeelView P, int *unresolved) {
@@ -370,7 +406,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
           }
           MG_LAUNCH(k_split_gather, grid_for(n_split, 256), 256, 0, s, P, (uint32_t)n_split);
         }
-        MG_LAUNCH(k_chain_resolve, grid, 256, 0, s, n, P, capped);
+        MG_LAUNCH(k_chain_resolve, stream_grid(g, n, 256), 256, 0, s, n, P, capped);
         int hc = 0;
         MG_CUDA(cudaMemcpyAsync(&hc, capped, 4, cudaMemcpyDeviceToHost, s));
         MG_CUDA(cudaStreamSynchronize(s));
