@@ -168,6 +168,7 @@ def hot_path_step(g, rank=0, world=1, dist=None, torch=None):
     (ss, coff, noff, nodes), cs = g.find_cycles(starts, MIN_LEN, MAX_LEN, csr=True)
     tt.append(time.perf_counter())
     if dbg:
+        print("[buckets] " + " ".join("%d:%d" % (int(k), len(ids)) for k, ids in buckets), file=sys.stderr)
         print("[step wall ms] reset %.1f prune %.1f candidates %.1f dls %.1f bucket %.1f find_cycles %.1f" %
               tuple((b - a) * 1e3 for a, b in zip(tt, tt[1:])), file=sys.stderr)
     res_bytes = 8 * int(nodes.size + ss.size)

@@ -128,6 +128,7 @@ struct mg_graph {
   mg::DevBuf visited;    // n bits, uint32 words
   mg::DevBuf enum_arena; // per-worker search arenas of the enumeration pipeline (grow-only)
   uint64_t enum_arena_sig = 0;  // layout the arenas were initialised for
+  uint32_t n_ball_tier_calls = 0;  // passes of the admission search that reached its ball tier (starts.cu)
   bool pruned = false;
   // k-mer lookup index, optional
   uint32_t k = 0;

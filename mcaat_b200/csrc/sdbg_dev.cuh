@@ -87,10 +87,19 @@ MG_HD uint64_t nib_eq(uint64_t x, unsigned a) {
 // position of the r-th (0-based) set bit of x; x must have > r bits set
 MG_HD int select64(uint64_t x, int r) {
 #if defined(__CUDA_ARCH__)
-  uint32_t lo = (uint32_t)x;
-  int c = __popc(lo);
-  if (r < c) return __fns(lo, 0, r + 1);
-  return 32 + __fns((uint32_t)(x >> 32), 0, r - c + 1);
+  // branch-free binary search over popcounts (__fns is a software loop over the bytes of the word)
+  uint32_t w = (uint32_t)x;
+  int c = __popc(w), pos = 0;
+  if (r >= c) { r -= c; w = (uint32_t)(x >> 32); pos = 32; }
+  c = __popc(w & 0xFFFFu);
+  if (r >= c) { r -= c; w >>= 16; pos += 16; }
+  c = __popc(w & 0xFFu);
+  if (r >= c) { r -= c; w >>= 8; pos += 8; }
+  c = __popc(w & 0xFu);
+  if (r >= c) { r -= c; w >>= 4; pos += 4; }
+  c = __popc(w & 0x3u);
+  if (r >= c) { r -= c; w >>= 2; pos += 2; }
+  return pos + (r >= (int)(w & 1u) ? 1 : 0);
 #else
   for (int i = 0; i < r; ++i) x &= x - 1;
   return __builtin_ctzll(x);

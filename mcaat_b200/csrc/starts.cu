@@ -280,7 +280,11 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
       const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 4, 1, 32);
       // the searches of this tier are bound by the latency of their ball extraction, not by any throughput: more
       // warps per SM than the enumeration runs (its limit is shared memory; here a worker only keeps its DFS stack there)
-      const uint32_t dls_workers_per_sm = env_u32("MCAAT_DLS_WORKERS_PER_SM", 16, 1, 32);
+      // Each worker owns an arena slot (3.2 MB), and fresh device memory costs ~0.1 s per GB to map: the first pass of a
+      // handle — all a one-shot run of the reference program ever makes — stays with the slots the enumeration needs
+      // anyway; a handle that is used again (a long-lived process, the bench) is in steady state and takes the rest.
+      const uint32_t dls_workers_per_sm =
+          env_u32("MCAAT_DLS_WORKERS_PER_SM", g->n_ball_tier_calls++ == 0 ? workers_per_sm : 16, 1, 32);
       const uint32_t want = (uint32_t)std::min<uint64_t>(n_work, (uint64_t)g->sm_count * dls_workers_per_sm);
       const uint32_t blocks = (want + kDlsBallWarps - 1) / kDlsBallWarps, workers = blocks * kDlsBallWarps;
       const BallLayout L = make_ball_layout(limit, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 16),
