@@ -1,2 +1,2 @@
-python -m pytest tests/test_gpu_parity.py -x -q -m gpu > gpurun_out/parity12.log 2>&1
-python bench.py --steps 4 --warmup 2 --no-cpu-baseline --no-e2e --no-dropin > gpurun_out/sel.json 2>/dev/null
+CMD="python bench.py --workload c4 --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-dropin"
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:^k_ --csv --log-file gpurun_out/r02_launches_c4.csv $CMD > /dev/null 2>&1
