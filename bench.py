@@ -515,6 +515,8 @@ def main():
                 keep.append(t)
                 host[key] = v
             h2d = sum(host[k].nbytes for k in ("w", "last", "tip", "mult"))
+            t_inv, inv_buf = pinned(np.zeros((graph["n"] + 63) // 64, np.uint64), torch)  # page-locked like the inputs
+            keep.append(t_inv)
         g.close()
         if world > 1:
             del dev, packed_dev
@@ -539,7 +541,7 @@ def main():
             t_up = time.perf_counter()
             st2, rb = hot_path_step(g2, rank, world, dist, torch)
             t_hp = time.perf_counter()
-            inv = g2.invalid_words() if rank == 0 else None
+            inv = g2.invalid_words(out=inv_buf) if rank == 0 else None
             barrier()
             tb_ = time.perf_counter()
             if os.environ.get("BENCH_DEBUG") and rank == 0:

@@ -95,6 +95,28 @@ void scratch_flush(cudaStream_t st) {  // called with the stream's device curren
   }
   g_scratch.resize(w);
 }
+namespace {
+std::mutex g_pinned_mu;
+PinnedBuf g_pinned_spare;
+}  // namespace
+void pinned_spare_take(PinnedBuf &into) {
+  std::lock_guard<std::mutex> lk(g_pinned_mu);
+  if (!into.p && g_pinned_spare.p) {
+    into = g_pinned_spare;
+    g_pinned_spare.p = nullptr;
+    g_pinned_spare.bytes = 0;
+  }
+}
+void pinned_spare_give(PinnedBuf &from) {
+  std::lock_guard<std::mutex> lk(g_pinned_mu);
+  if (from.p && from.bytes > g_pinned_spare.bytes) {
+    g_pinned_spare.release();
+    g_pinned_spare = from;
+    from.p = nullptr;
+    from.bytes = 0;
+  }
+  from.release();
+}
 const char *kTimerNames[T_COUNT] = {"build_index", "collect_tips", "invalidate_mult1", "peel",      "nav_cache",
                                     "candidates",  "dls",          "enumerate",        "commit",    "navigate",
                                     "keep_regions", "map_reads"};
@@ -215,6 +237,7 @@ void mg_graph_destroy(mg_graph *g) {
   for (mg::DevBuf *b : {&g->wb, &g->fb, &g->mult, &g->hints, &g->inv0, &g->adj, &g->merge, &g->visited, &g->enum_arena,
                        &g->kx_tip, &g->kx_tip_prefix, &g->kx_labels, &g->kx_buckets, &g->kx_jump, &g->kx_bucket_ok})
     b->release();
+  pinned_spare_give(g->host_stage);
   scratch_flush(g->stream);  // nothing cached may outlive the stream it is ordered on
   if (g->stream) cudaStreamSynchronize(g->stream);
   for (auto e : g->event_pool) cudaEventDestroy(e);

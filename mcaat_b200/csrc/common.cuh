@@ -97,6 +97,34 @@ struct DevBuf {
   template <class T> T *as() const { return (T *)p; }
 };
 
+// page-locked host memory for results on their way back (grow-only, one per graph handle)
+struct PinnedBuf {
+  void *p = nullptr;
+  size_t bytes = 0;
+  int ensure(size_t b) {
+    if (b <= bytes) return MG_OK;
+    release();
+    b = (b + (b >> 2) + 4095) & ~(size_t)4095;
+    cudaError_t e = cudaMallocHost(&p, b);
+    if (e != cudaSuccess) {
+      p = nullptr;
+      set_error("cudaMallocHost(%zu) -> %s", b, cudaGetErrorString(e));
+      return MG_ENOMEM;
+    }
+    bytes = b;
+    return MG_OK;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    bytes = 0;
+  }
+};
+
+// one spare staging buffer per process: a fresh handle takes it over instead of page-locking memory again (4 ms for 5 MB)
+void pinned_spare_take(PinnedBuf &into);
+void pinned_spare_give(PinnedBuf &from);
+
 enum TimerId {
   T_BUILD = 0,     // index construction
   T_TIPS,          // CollectTips scans
@@ -128,6 +156,7 @@ struct mg_graph {
   mg::DevBuf visited;    // n bits, uint32 words
   mg::DevBuf enum_arena; // per-worker search arenas of the enumeration pipeline (grow-only)
   uint64_t enum_arena_sig = 0;  // layout the arenas were initialised for
+  mg::PinnedBuf host_stage;     // read-back staging of mg_find_cycles (taken from / returned to a process-wide spare)
   uint32_t n_ball_tier_calls = 0;  // passes of the admission search that reached its ball tier (starts.cu)
   bool pruned = false;
   // k-mer lookup index, optional

@@ -133,6 +133,28 @@ int build_graph(mg_graph *g, const mg_graph_desc *d) {
   MG_TRY(st.stage(d->tip, b_words * 8, d->memory, s));
   MG_TRY(si.stage(d->invalid, b_words * 8, d->memory, s));
 
+  // The multiplicities are three quarters of the upload (2 of 2.75 bytes per item) and no kernel of the index build reads
+  // them: from host memory they travel on a stream of their own, behind the three arrays the build waits for, while
+  // the build runs.
+  cudaStream_t mult_stream = nullptr;
+  cudaEvent_t mult_ev = nullptr;
+  const bool mult_aside = d->mult16 && d->memory != MG_MEM_DEVICE && n > 0;
+  if (mult_aside) {
+    MG_TRY(g->mult.alloc((size_t)n * 2 + 16));
+    MG_CUDA(cudaStreamCreateWithFlags(&mult_stream, cudaStreamNonBlocking));
+    MG_CUDA(cudaEventCreateWithFlags(&mult_ev, cudaEventDisableTiming));
+    MG_CUDA(cudaEventRecord(mult_ev, s));                  // the allocation and the three copies above come first
+    MG_CUDA(cudaStreamWaitEvent(mult_stream, mult_ev, 0));
+    MG_CUDA(cudaMemcpyAsync(g->mult.p, d->mult16, (size_t)n * 2, cudaMemcpyHostToDevice, mult_stream));
+    MG_CUDA(cudaEventRecord(mult_ev, mult_stream));
+  }
+  struct MultAside {  // joins and releases on every way out
+    cudaStream_t &st; cudaEvent_t &ev; cudaStream_t main;
+    ~MultAside() {
+      if (ev) { cudaStreamWaitEvent(main, ev, 0); cudaStreamSynchronize(st); cudaEventDestroy(ev); }
+      if (st) cudaStreamDestroy(st);
+    }
+  } mult_guard{mult_stream, mult_ev, s};
   TimedScope ts(g, T_BUILD, n);
   // --- W blocks
   MG_TRY(g->wb.alloc((size_t)(v.n_wblocks + 1) * sizeof(WBlock)));
@@ -177,8 +199,10 @@ int build_graph(mg_graph *g, const mg_graph_desc *d) {
             hbase + off[1], hbase + off[2], hbase + off[3]);
   MG_LAUNCH(k_hints_last, grid_for(v.n_fblocks, 256), 256, 0, s, v.n_fblocks, fb, totals.as<uint32_t>() + 4, hbase);
   // --- multiplicities
-  MG_TRY(g->mult.alloc((size_t)n * 2 + 16));
-  if (d->mult16) {
+  if (!mult_aside) MG_TRY(g->mult.alloc((size_t)n * 2 + 16));
+  if (mult_aside) {
+    // on its way (above); joined before the function returns
+  } else if (d->mult16) {
     MG_CUDA(cudaMemcpyAsync(g->mult.p, d->mult16, (size_t)n * 2,
                             d->memory == MG_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
   } else if (d->mult8) {
@@ -207,6 +231,7 @@ int build_graph(mg_graph *g, const mg_graph_desc *d) {
     MG_LAUNCH(k_save_inv, grid_for(v.n_fblocks * 4, 256), 256, 0, s, v.n_fblocks, fb, g->inv0.as<uint64_t>());
   MG_TRY(g->visited.alloc((size_t)((n + 31) / 32) * 4 + 16));
   MG_CUDA(cudaMemsetAsync(g->visited.p, 0, g->visited.bytes, s));
+  if (mult_aside) MG_CUDA(cudaStreamWaitEvent(s, mult_ev, 0));
   MG_CUDA(cudaStreamSynchronize(s));
   g->device_bytes = g->wb.bytes + g->fb.bytes + g->mult.bytes + g->hints.bytes + g->inv0.bytes + g->visited.bytes;
   return MG_OK;

@@ -123,7 +123,7 @@ __global__ void k_chain_init(GraphView g, PeelView P, uint32_t *branch, unsigned
 __global__ void k_split_mark(uint64_t n, PeelView P, uint32_t *split) {
   const uint64_t n32 = (n + 31) & ~31ull;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
-    bool sp = i < n && bm_get(P.chain, (uint32_t)i) && is_splitter_id((uint32_t)i);
+    bool sp = i < n && bm_get(P.chain, (uint32_t)i) && is_splitter_id(P, (uint32_t)i);
     unsigned m = __ballot_sync(0xffffffffu, sp);
     if ((threadIdx.x & 31) == 0) split[i >> 5] = m;
   }
@@ -152,7 +152,7 @@ __global__ void k_chain_resolve(uint64_t n, PeelView P, int *capped) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const uint64_t v = i0 + q * stride;
-      ev[q] = v < n && !is_splitter_id((uint32_t)v) ? P.ent[v] : 0ull;  // 0: not a chain node
+      ev[q] = v < n && !is_splitter_id(P, (uint32_t)v) ? P.ent[v] : 0ull;  // 0: not a chain node
     }
 #pragma unroll
     for (int q = 0; q < 4; ++q) {  // the common case: a walk passed the item, its splitter knows the terminal
@@ -370,6 +370,11 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     P.dep_log = 0;
     P.split_ids = nullptr;
     P.sterm = nullptr;
+    {
+      const char *e = getenv("MCAAT_PEEL_SPLIT_LOG");  // diagnostic: splitter density 2^-k (default 7: one chain node in 128)
+      const int k = e && *e ? atoi(e) : 7;
+      P.split_shift = 32u - (uint32_t)(k < 2 ? 2 : k > 12 ? 12 : k);
+    }
     DevBuf branch, branch_ids;
     MG_TRY(branch.alloc(bm_bytes));
     {

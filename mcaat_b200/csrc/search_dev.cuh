@@ -96,6 +96,7 @@ struct PeelView {
   const uint32_t *recl;     // bitmap: branch nodes re-classified as chain nodes by step 2b (all rounds so far)
   uint64_t *dep;            // multimap entries (terminal << 32 | branch node), empty = ~0
   uint32_t dep_log;
+  uint32_t split_shift;     // one chain node in 2^(32 - split_shift) is a splitter (25: one in 128, the default)
 };
 constexpr uint32_t kNoOwner = 0x7FFFFFFFu, kEntChain = 0x80000000u;
 MG_HD uint32_t &peel_ptr(const PeelView &P, uint32_t v) { return ((uint32_t *)P.ent)[2 * (size_t)v]; }
@@ -150,7 +151,7 @@ MG_HD bool chain_jump_item(const PeelView &P, uint32_t v) {
 }
 // Step 2, work-efficient form.  Pointer jumping over ALL chain nodes costs one pass over the graph
 // per doubling (18 passes for the 10^5-node chains of sequencing-error tips).  Instead one chain
-// node in 64 (by hash) is a SPLITTER:
+// node in 128 (by hash; PeelView::split_shift) is a SPLITTER:
 //   a. every splitter walks forward until it meets a terminal, another splitter or an item another
 //      walk has claimed, claiming the items it passes (owner[]) — every chain node is claimed at most
 //      once, so this is O(n) in total, in walks of ~64 hops;
@@ -163,7 +164,7 @@ MG_HD bool chain_jump_item(const PeelView &P, uint32_t v) {
 // checkpoint).  Walks are capped; hitting the cap (a splitter-free stretch of 4096+ chain nodes) makes the
 // host fall back to exhaustive pointer jumping — every pointer stays a valid forward pointer throughout.
 constexpr uint32_t kWalkCapSplitter = 1u << 16, kWalkCapHead = 1u << 12;
-MG_HD bool is_splitter_id(uint32_t v) { return ((v * 0x9E3779B1u) >> 26) == 0; }
+MG_HD bool is_splitter_id(const PeelView &P, uint32_t v) { return ((v * 0x9E3779B1u) >> P.split_shift) == 0; }
 MG_HD uint32_t ld_cg_u32(const uint32_t *p) { return ld_cg32(p); }
 MG_HD uint64_t ent_cas(uint64_t *p, uint64_t expect, uint64_t val) {
 #if defined(__CUDA_ARCH__)
@@ -179,7 +180,7 @@ MG_HD bool split_walk_item(const PeelView &P, uint32_t k) {
   const uint32_t s = P.split_ids[k];
   uint32_t p = peel_ptr(P, s), next = kNull;
   for (uint32_t hops = 0; hops < kWalkCapSplitter; ++hops) {
-    if (is_splitter_id(p)) { next = p; break; }      // another splitter (or a terminal whose id hashes like one)
+    if (is_splitter_id(P, p)) { next = p; break; }      // another splitter (or a terminal whose id hashes like one)
     const uint64_t e = ld_cg64(&P.ent[p]);
     const uint32_t hi = (uint32_t)(e >> 32);
     if (!(hi & kEntChain)) { next = p; break; }      // terminal
@@ -205,7 +206,7 @@ MG_HD bool split_jump_item(const PeelView &P, uint32_t s) {
 }
 // c. every chain node that is not a splitter; returns false when the hop cap was hit
 MG_HD bool chain_resolve_item(const PeelView &P, uint32_t v) {
-  if (is_splitter_id(v)) return true;
+  if (is_splitter_id(P, v)) return true;
   const uint64_t ev = P.ent[v];
   const uint32_t hv = (uint32_t)(ev >> 32);
   if (!(hv & kEntChain)) return true;
@@ -219,7 +220,7 @@ MG_HD bool chain_resolve_item(const PeelView &P, uint32_t v) {
   // writes a pointer on such a component, so the walk is deterministic: <= 3 x (tail + cycle) hops.
   uint32_t mark = v, since = 0, power = 1;
   for (uint32_t hops = 0; hops < kWalkCapHead; ++hops) {
-    if (is_splitter_id(p)) {
+    if (is_splitter_id(P, p)) {
       // a chain splitter knows its terminal; an item that merely hashes like one is a terminal itself
       const uint64_t ep = ld_cg64(&P.ent[p]);
       peel_ptr(P, v) = ((uint32_t)(ep >> 32) & kEntChain) ? (uint32_t)ep : p;

@@ -283,8 +283,21 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
       // Each worker owns an arena slot (3.2 MB), and fresh device memory costs ~0.1 s per GB to map: the first pass of a
       // handle — all a one-shot run of the reference program ever makes — stays with the slots the enumeration needs
       // anyway; a handle that is used again (a long-lived process, the bench) is in steady state and takes the rest.
-      const uint32_t dls_workers_per_sm =
-          env_u32("MCAAT_DLS_WORKERS_PER_SM", g->n_ball_tier_calls++ == 0 ? workers_per_sm : 16, 1, 32);
+      // Nor does that first pass hold back when the device's memory pool already has the bytes (an earlier handle of
+      // this process left them there).
+      bool wide = g->n_ball_tier_calls++ > 0;
+      if (!wide) {
+        const BallLayout L0 = make_ball_layout(limit, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 16), 4096);
+        const size_t need = (size_t)g->sm_count * 16 * L0.bytes;
+        cudaMemPool_t pool = nullptr;
+        uint64_t reserved = 0, used = 0;
+        if (g->enum_arena.bytes >= need) wide = true;
+        else if (cudaDeviceGetDefaultMemPool(&pool, g->device) == cudaSuccess &&
+                 cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved) == cudaSuccess &&
+                 cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used) == cudaSuccess)
+          wide = reserved >= used && reserved - used >= need - g->enum_arena.bytes;
+      }
+      const uint32_t dls_workers_per_sm = env_u32("MCAAT_DLS_WORKERS_PER_SM", wide ? 16 : workers_per_sm, 1, 32);
       const uint32_t want = (uint32_t)std::min<uint64_t>(n_work, (uint64_t)g->sm_count * dls_workers_per_sm);
       const uint32_t blocks = (want + kDlsBallWarps - 1) / kDlsBallWarps, workers = blocks * kDlsBallWarps;
       const BallLayout L = make_ball_layout(limit, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 16),

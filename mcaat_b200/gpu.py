@@ -225,8 +225,10 @@ class DeviceGraph:
         _check(lib().mg_invalid_readback(self.h, words.ctypes.data))
         return np.unpackbits(words.view(np.uint8), bitorder="little")[:self.n].astype(bool)
 
-    def invalid_words(self):
-        words = np.zeros((self.n + 63) // 64, np.uint64)
+    def invalid_words(self, out=None):
+        """current invalid bitmap as uint64 words; `out` lets the caller own the buffer (e.g. page-locked memory)"""
+        words = np.zeros((self.n + 63) // 64, np.uint64) if out is None else out
+        assert words.dtype == np.uint64 and words.size >= (self.n + 63) // 64
         _check(lib().mg_invalid_readback(self.h, words.ctypes.data))
         return words
 

@@ -161,7 +161,7 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   PeelView P;
   P.adj = e->adj.data(); P.ent = ent.data(); P.chain = chain.data(); P.tpeeled = tpeeled.data();
   P.tipbits = tipbits.data(); P.dep = nullptr; P.dep_log = 0;
-  P.split_ids = nullptr; P.sterm = nullptr;
+  P.split_ids = nullptr; P.sterm = nullptr; P.split_shift = 25;
   std::vector<uint32_t> recl(words, 0);
   P.recl = recl.data();
   uint64_t pairs = 0;
@@ -179,7 +179,7 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   if (!(reverse_order & 2)) {
     std::vector<uint32_t> split_ids;
     for (uint64_t i = 0; i < n; ++i)
-      if (bm_get(P.chain, (uint32_t)i) && is_splitter_id((uint32_t)i)) split_ids.push_back((uint32_t)i);
+      if (bm_get(P.chain, (uint32_t)i) && is_splitter_id(P, (uint32_t)i)) split_ids.push_back((uint32_t)i);
     // (the walks of the device run in any order: here ascending or descending splitter number)
     std::vector<uint32_t> sterm(split_ids.size() + 1, 0);
     P.split_ids = split_ids.data();
