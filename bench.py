@@ -510,11 +510,22 @@ def main():
         keep, host, h2d = [], None, 0
         if rank == 0:
             host = dict(n=graph["n"], k=graph["k"], f=graph["f"])
-            for key in ("w", "last", "tip", "mult"):
-                t, v = pinned(graph[key], torch)
+            keys = ["w", "last", "tip", "mult"]
+            src = dict(graph)
+            if world == 1:
+                # multiplicities as the reference holds them in memory (libs/megahit/src/sdbg/sdbg.h:96-105): one byte per
+                # item, sentinel 255 -> (id, value) table.  (N > 1 broadcasts the uint16 array the device keeps.)
+                mult = np.asarray(graph["mult"])
+                big = mult >= 255
+                src["mult8"] = np.where(big, 255, mult).astype(np.uint8)
+                src["large_ids"] = np.flatnonzero(big).astype(np.uint64)
+                src["large_vals"] = np.ascontiguousarray(mult[big], np.uint16)
+                keys = ["w", "last", "tip", "mult8", "large_ids", "large_vals"]
+            for key in keys:
+                t, v = pinned(src[key], torch)
                 keep.append(t)
                 host[key] = v
-            h2d = sum(host[k].nbytes for k in ("w", "last", "tip", "mult"))
+            h2d = sum(host[k].nbytes for k in keys)
             t_inv, inv_buf = pinned(np.zeros((graph["n"] + 63) // 64, np.uint64), torch)  # page-locked like the inputs
             keep.append(t_inv)
         g.close()

@@ -138,14 +138,20 @@ int build_graph(mg_graph *g, const mg_graph_desc *d) {
   // the build runs.
   cudaStream_t mult_stream = nullptr;
   cudaEvent_t mult_ev = nullptr;
-  const bool mult_aside = d->mult16 && d->memory != MG_MEM_DEVICE && n > 0;
+  const bool mult_aside = (d->mult16 || d->mult8) && d->memory != MG_MEM_DEVICE && n > 0;
   if (mult_aside) {
     MG_TRY(g->mult.alloc((size_t)n * 2 + 16));
+    if (!d->mult16) MG_TRY(sm8.own.alloc((size_t)n));
     MG_CUDA(cudaStreamCreateWithFlags(&mult_stream, cudaStreamNonBlocking));
     MG_CUDA(cudaEventCreateWithFlags(&mult_ev, cudaEventDisableTiming));
     MG_CUDA(cudaEventRecord(mult_ev, s));                  // the allocation and the three copies above come first
     MG_CUDA(cudaStreamWaitEvent(mult_stream, mult_ev, 0));
-    MG_CUDA(cudaMemcpyAsync(g->mult.p, d->mult16, (size_t)n * 2, cudaMemcpyHostToDevice, mult_stream));
+    if (d->mult16) {
+      MG_CUDA(cudaMemcpyAsync(g->mult.p, d->mult16, (size_t)n * 2, cudaMemcpyHostToDevice, mult_stream));
+    } else {  // the reference's own form (sdbg.h:96-105): one byte per item, expanded below
+      MG_CUDA(cudaMemcpyAsync(sm8.own.p, d->mult8, (size_t)n, cudaMemcpyHostToDevice, mult_stream));
+      sm8.ptr = sm8.own.p;
+    }
     MG_CUDA(cudaEventRecord(mult_ev, mult_stream));
   }
   struct MultAside {  // joins and releases on every way out
@@ -200,13 +206,14 @@ int build_graph(mg_graph *g, const mg_graph_desc *d) {
   MG_LAUNCH(k_hints_last, grid_for(v.n_fblocks, 256), 256, 0, s, v.n_fblocks, fb, totals.as<uint32_t>() + 4, hbase);
   // --- multiplicities
   if (!mult_aside) MG_TRY(g->mult.alloc((size_t)n * 2 + 16));
-  if (mult_aside) {
+  if (mult_aside && d->mult16) {
     // on its way (above); joined before the function returns
   } else if (d->mult16) {
     MG_CUDA(cudaMemcpyAsync(g->mult.p, d->mult16, (size_t)n * 2,
                             d->memory == MG_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
   } else if (d->mult8) {
-    MG_TRY(sm8.stage(d->mult8, (size_t)n, d->memory, s));
+    if (mult_aside) MG_CUDA(cudaStreamWaitEvent(s, mult_ev, 0));
+    else MG_TRY(sm8.stage(d->mult8, (size_t)n, d->memory, s));
     MG_TRY(slid.stage(d->large_ids, (size_t)d->n_large * 8, d->memory, s));
     MG_TRY(slval.stage(d->large_vals, (size_t)d->n_large * 2, d->memory, s));
     if (n) MG_LAUNCH(k_mult_expand, grid_for(n, 256), 256, 0, s, (const uint8_t *)sm8.ptr, n, g->mult.as<uint16_t>());

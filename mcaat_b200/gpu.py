@@ -180,10 +180,18 @@ class DeviceGraph:
             assert packed["w"].dtype == np.uint64 and packed["w"].size >= (n + 15) // 16
             assert packed["last"].dtype == np.uint64 and packed["last"].size >= (n + 63) // 64
             assert packed["tip"].dtype == np.uint64 and packed["tip"].size >= (n + 63) // 64
-            assert packed["mult"].dtype == np.uint16 and packed["mult"].size >= n
+            if "mult8" not in packed:
+                assert packed["mult"].dtype == np.uint16 and packed["mult"].size >= n
         d.w, d.last, d.tip = ptr(packed["w"]), ptr(packed["last"]), ptr(packed["tip"])
         d.invalid = ptr(packed.get("invalid"))
-        d.mult16 = ptr(packed["mult"])
+        if "mult8" in packed:
+            # the reference's in-memory form (sdbg.h:96-105): one byte per item, sentinel 255 -> (id, value) table by id
+            assert memory == MG_MEM_HOST and packed["mult8"].dtype == np.uint8 and packed["mult8"].size >= n
+            assert packed["large_ids"].dtype == np.uint64 and packed["large_vals"].dtype == np.uint16
+            d.mult8, d.large_ids, d.large_vals = ptr(packed["mult8"]), ptr(packed["large_ids"]), ptr(packed["large_vals"])
+            d.n_large = int(packed["large_ids"].size)
+        else:
+            d.mult16 = ptr(packed["mult"])
         f = packed["f"]
         for i in range(6):
             d.f[i] = int(f[i])
