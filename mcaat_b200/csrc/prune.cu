@@ -132,14 +132,14 @@ __global__ void k_split_walk(PeelView P, uint32_t n_ids, int *capped) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n_ids && !split_walk_item(P, i)) *capped = 1;
 }
-// the splitters' resolved pointers, densely (PeelView::sterm)
-__global__ void k_split_gather(PeelView P, uint32_t n_ids) {
+// the resolved pointers into the splitters' entries; the dense table keeps them as item ids for the resolution pass
+__global__ void k_split_settle(PeelView P, uint32_t n_ids) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n_ids) P.sterm[i] = peel_ptr(P, P.split_ids[i]);
+  if (i < n_ids) split_settle(P, i);
 }
-__global__ void k_split_jump(PeelView P, const uint32_t *ids, uint32_t n_ids, int *unresolved) {
+__global__ void k_split_jump(PeelView P, uint32_t n_ids, int *unresolved) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  bool u = i < n_ids && split_jump_item(P, ids[i]);
+  bool u = i < n_ids && split_jump_dense(P, i);
   if (__any_sync(0xffffffffu, u) && (threadIdx.x & 31) == 0) *unresolved = 1;
 }
 // (four items per thread and round: these passes are bound by the latency of two dependent loads per item — the entry,
@@ -370,6 +370,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     P.dep_log = 0;
     P.split_ids = nullptr;
     P.sterm = nullptr;
+    P.n_split = 0;
     {
       const char *e = getenv("MCAAT_PEEL_SPLIT_LOG");  // diagnostic: splitter density 2^-k (default 7: one chain node in 128)
       const int k = e && *e ? atoi(e) : 7;
@@ -399,17 +400,18 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
           MG_TRY(sterm.alloc(n_split * 4));
           P.split_ids = split_ids.as<uint32_t>();
           P.sterm = sterm.as<uint32_t>();
+          P.n_split = (uint32_t)n_split;
           MG_LAUNCH(k_split_walk, grid_for(n_split, 128), 128, 0, s, P, (uint32_t)n_split, capped);
           for (int round = 0; round < 36; round += 4) {
             MG_CUDA(cudaMemsetAsync(unresolved, 0, 4, s));
             for (int k = 0; k < 4; ++k)
-              MG_LAUNCH(k_split_jump, grid_for(n_split, 256), 256, 0, s, P, split_ids.as<uint32_t>(), (uint32_t)n_split, unresolved);
+              MG_LAUNCH(k_split_jump, grid_for(n_split, 256), 256, 0, s, P, (uint32_t)n_split, unresolved);
             int h = 0;
             MG_CUDA(cudaMemcpyAsync(&h, unresolved, 4, cudaMemcpyDeviceToHost, s));
             MG_CUDA(cudaStreamSynchronize(s));
             if (!h) break;
           }
-          MG_LAUNCH(k_split_gather, grid_for(n_split, 256), 256, 0, s, P, (uint32_t)n_split);
+          MG_LAUNCH(k_split_settle, grid_for(n_split, 256), 256, 0, s, P, (uint32_t)n_split);
         }
         MG_LAUNCH(k_chain_resolve, stream_grid(g, n, 256), 256, 0, s, n, P, capped);
         int hc = 0;

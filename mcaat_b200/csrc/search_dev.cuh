@@ -96,6 +96,7 @@ struct PeelView {
   const uint32_t *recl;     // bitmap: branch nodes re-classified as chain nodes by step 2b (all rounds so far)
   uint64_t *dep;            // multimap entries (terminal << 32 | branch node), empty = ~0
   uint32_t dep_log;
+  uint32_t n_split;         // number of splitters
   uint32_t split_shift;     // one chain node in 2^(32 - split_shift) is a splitter (25: one in 128, the default)
 };
 constexpr uint32_t kNoOwner = 0x7FFFFFFFu, kEntChain = 0x80000000u;
@@ -175,6 +176,20 @@ MG_HD uint64_t ent_cas(uint64_t *p, uint64_t expect, uint64_t val) {
   return old;
 #endif
 }
+// number of the chain splitter with item id p (binary search in the ascending id list)
+MG_HD uint32_t split_number(const PeelView &P, uint32_t p) {
+  uint32_t lo = 0, hi = P.n_split;
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (ld_ro(&P.split_ids[mid]) < p) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+// During step b the dense table holds, per splitter, where its walk ended: kSplitTerm | item id of a terminal, or the
+// NUMBER of the chain splitter ahead (its own number: known to be unresolvable) — 4 bytes per 128 chain nodes, so the
+// pointer-jumping rounds run in L2 instead of on the splitters' entries scattered over the whole entry array.
+constexpr uint32_t kSplitTerm = 0x80000000u;
 // a. walk of splitter number k; returns false when the hop cap was hit (ptr[s] is then left untouched)
 MG_HD bool split_walk_item(const PeelView &P, uint32_t k) {
   const uint32_t s = P.split_ids[k];
@@ -191,11 +206,29 @@ MG_HD bool split_walk_item(const PeelView &P, uint32_t k) {
     if (old != e) { next = P.split_ids[(uint32_t)(old >> 32) & kNoOwner]; break; }
     p = (uint32_t)e;
   }
-  if (next == kNull) return false;
+  if (next == kNull) { P.sterm[k] = k; return false; }  // (the caller falls back to exhaustive pointer jumping)
   peel_ptr(P, s) = next;
+  P.sterm[k] = bm_get(P.chain, next) ? split_number(P, next) : (kSplitTerm | next);  // a walk only ever ends at a splitter or a terminal
   return true;
 }
-// b. one pointer-jumping round for splitter s; returns true while it is still unresolved
+// b. one pointer-jumping round for splitter number k on the dense table; returns true while it is still unresolved
+MG_HD bool split_jump_dense(const PeelView &P, uint32_t k) {
+  const uint32_t v = ld_cg_u32(&P.sterm[k]);
+  if ((v & kSplitTerm) || v == k) return false;  // terminal reached / known to be unresolvable
+  uint32_t q = ld_cg_u32(&P.sterm[v]);
+  if (q == v) q = k;  // the splitter ahead is unresolvable, so is this one
+  P.sterm[k] = q;
+  return true;
+}
+// after the rounds: the splitter's entry and the table take the resolved pointer as an item id (an unresolvable
+// splitter points at a chain node: itself)
+MG_HD void split_settle(const PeelView &P, uint32_t k) {
+  const uint32_t v = P.sterm[k], s = P.split_ids[k];
+  const uint32_t t = (v & kSplitTerm) ? (v & ~kSplitTerm) : P.split_ids[v];
+  peel_ptr(P, s) = t;
+  P.sterm[k] = t;
+}
+// b. on the entries themselves (the host emulation's form): one round for splitter s; true while unresolved
 MG_HD bool split_jump_item(const PeelView &P, uint32_t s) {
   uint32_t p = ld_cg_u32(&peel_ptr(P, s));
   if (!bm_get(P.chain, p) || p == s) return false;  // terminal reached / known to be unresolvable

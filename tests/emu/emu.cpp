@@ -161,7 +161,7 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
   PeelView P;
   P.adj = e->adj.data(); P.ent = ent.data(); P.chain = chain.data(); P.tpeeled = tpeeled.data();
   P.tipbits = tipbits.data(); P.dep = nullptr; P.dep_log = 0;
-  P.split_ids = nullptr; P.sterm = nullptr; P.split_shift = 25;
+  P.split_ids = nullptr; P.sterm = nullptr; P.n_split = 0; P.split_shift = 25;
   std::vector<uint32_t> recl(words, 0);
   P.recl = recl.data();
   uint64_t pairs = 0;
@@ -184,15 +184,17 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
     std::vector<uint32_t> sterm(split_ids.size() + 1, 0);
     P.split_ids = split_ids.data();
     P.sterm = sterm.data();
+    P.n_split = (uint32_t)split_ids.size();
     const uint32_t ns = (uint32_t)split_ids.size();
     if (reverse_order & 1) { for (uint32_t k = ns; k-- > 0;) capped |= !split_walk_item(P, k); }
     else for (uint32_t k = 0; k < ns; ++k) capped |= !split_walk_item(P, k);
-    for (int round = 0; round < 36; ++round) {
+    for (int round = 0; round < 36; ++round) {  // pointer jumping on the dense table, as prune.cu
       bool any = false;
-      for (uint32_t sid : split_ids) any |= split_jump_item(P, sid);
+      if (reverse_order & 1) { for (uint32_t k = ns; k-- > 0;) any |= split_jump_dense(P, k); }
+      else for (uint32_t k = 0; k < ns; ++k) any |= split_jump_dense(P, k);
       if (!any) break;
     }
-    for (uint32_t k = 0; k < ns; ++k) sterm[k] = peel_ptr(P, split_ids[k]);
+    for (uint32_t k = 0; k < ns; ++k) split_settle(P, k);
     if (reverse_order & 1) { for (uint64_t i = n; i-- > 0;) capped |= !chain_resolve_item(P, (uint32_t)i); }
     else for (uint64_t i = 0; i < n; ++i) capped |= !chain_resolve_item(P, (uint32_t)i);
   }

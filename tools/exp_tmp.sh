@@ -1,2 +1,3 @@
-python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "dump or empty or ingest" > gpurun_out/parity14.log 2>&1
-BENCH_DEBUG=1 python bench.py --steps 4 --warmup 2 --no-cpu-baseline --no-dropin > gpurun_out/e2e.json 2> gpurun_out/e2e.err
+python -m pytest tests/test_gpu_parity.py tests/test_gpu_full_size.py -x -q -m gpu > gpurun_out/parity15.log 2>&1
+python bench.py --steps 4 --warmup 2 --no-cpu-baseline --no-e2e --no-dropin > gpurun_out/dense.json 2>/dev/null
+python bench.py --workload c4 --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --no-dropin > gpurun_out/dense_c4.json 2>/dev/null
