@@ -243,6 +243,7 @@ void mg_graph_destroy(mg_graph *g) {
   for (auto e : g->event_pool) cudaEventDestroy(e);
   if (g->step_a) cudaEventDestroy(g->step_a);
   if (g->step_b) cudaEventDestroy(g->step_b);
+  if (g->stream2) cudaStreamDestroy(g->stream2);
   if (g->stream) cudaStreamDestroy(g->stream);
   delete g;
 }

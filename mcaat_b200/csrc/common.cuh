@@ -148,6 +148,7 @@ extern const char *kTimerNames[T_COUNT];
 struct mg_graph {
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream2 = nullptr;  // kernels that run beside the main stream (ball tier of the admission search), lazily created
   mg::GraphView view{};  // pointers below
   mg::DevBuf wb, fb, mult, hints, inv0;
   mg::DevBuf adj;        // navigation cache (built by mg_prune)

@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(128) k_dls(const uint64_t *__restrict__ adj, c
                                             const uint32_t *__restrict__ todo, uint32_t n_cand, int limit, DlsArena A,
                                             int8_t *result, uint32_t *queue, unsigned long long *expansions,
                                             uint32_t *per_search /* nullable: expansions of every search */,
-                                            int smem_stack) {
+                                            int smem_stack, uint32_t *push_list, uint32_t *push_tail /* [0] pushed, [1] this kernel has finished, [3] blocks finished */) {
   extern __shared__ __align__(16) uint8_t dls_smem[];
   const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
   LoggedSet seen;
@@ -143,12 +143,28 @@ __global__ void __launch_bounds__(128) k_dls(const uint64_t *__restrict__ adj, c
     exp = 0;
     int r = dls_run(adj, cand[idx], limit, seen, stk_node, stk_depth, stk_adj, A.stk_cap, exp);
     result[idx] = (int8_t)r;
+    if (r == kDlsSetFull && push_list) {  // handed to the ball tier, which runs beside this kernel, at once
+      __threadfence();
+      const uint32_t slot = atomicAdd(push_tail, 1u);
+      *(volatile uint32_t *)&push_list[slot] = idx;
+    }
     if (per_search) per_search[idx] = exp;
     if (r >= 0) exp_total += exp;  // a search that filled its set is repeated (and counted) by the next tier
     for (uint32_t j = 0; j < seen.count; ++j) seen.tab[seen.log[j]] = kNull;  // undo
   }
   for (int d = 16; d; d >>= 1) exp_total += __shfl_down_sync(0xffffffffu, exp_total, d);
   if ((threadIdx.x & 31) == 0 && exp_total) atomicAdd(expansions, exp_total);
+  if (push_list) {  // the last block to finish tells the ball tier that nothing more will be pushed (no host-side
+                    // operation has to get past the waiting kernel for that)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(&push_tail[3], 1u) == gridDim.x - 1) {
+        __threadfence();
+        *(volatile uint32_t *)&push_tail[1] = 1u;
+      }
+    }
+  }
 }
 
 // Middle tier: the long searches (those whose seen-set outgrew tier 1) on their extracted, contracted ball — one warp
@@ -159,7 +175,7 @@ __global__ void __launch_bounds__(32 * kDlsBallWarps) k_dls_ball(const uint64_t 
                                                           const uint32_t *__restrict__ todo, uint32_t n_todo, int limit,
                                                           uint8_t *arena, BallLayout L, int8_t *result, uint32_t *queue,
                                                           unsigned long long *expansions, uint32_t *per_search,
-                                                          uint32_t stk_smem, uint32_t n_total) {
+                                                          uint32_t stk_smem, uint32_t n_total, const uint32_t *stream_ctl) {
   extern __shared__ __align__(16) uint8_t dls_ball_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t worker = blockIdx.x * kDlsBallWarps + warp;
@@ -173,11 +189,29 @@ __global__ void __launch_bounds__(32 * kDlsBallWarps) k_dls_ball(const uint64_t 
   uint32_t live = 0;
   unsigned long long exp_total = 0;
   for (;;) {
-    uint32_t q = 0;
-    if (lane == 0) q = atomicAdd(queue, 1u);
+    uint32_t q = 0, idx = 0xFFFFFFFFu;
+    if (lane == 0) {
+      q = atomicAdd(queue, 1u);
+      if (!stream_ctl) {
+        if (q < n_todo) idx = todo[q];
+      } else {
+        // streaming: `todo` is filled by the first tier while this kernel runs (empty = 0xFFFFFFFF); stream_ctl[0] is
+        // the number of entries pushed so far, stream_ctl[1] becomes non-zero once the first tier has finished
+        for (;;) {
+          idx = *(const volatile uint32_t *)&todo[q];
+          if (idx != 0xFFFFFFFFu) break;
+          if (*(const volatile uint32_t *)&stream_ctl[1]) {
+            idx = *(const volatile uint32_t *)&todo[q];  // everything pushed is visible by now
+            if (idx != 0xFFFFFFFFu || q >= *(const volatile uint32_t *)&stream_ctl[0]) break;
+          }
+          __nanosleep(1000u);
+        }
+        __threadfence();
+      }
+    }
     q = __shfl_sync(0xffffffffu, q, 0);
-    if (q >= n_todo) break;
-    const uint32_t idx = todo[q];
+    idx = __shfl_sync(0xffffffffu, idx, 0);
+    if (idx == 0xFFFFFFFFu) break;
     unsigned long long t0 = 0, t1 = 0, t2 = 0;
     if (per_search) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
     ball_clear(A, live, co);
@@ -264,7 +298,10 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
   // hash tiers: (slots per search, searches in flight).  A search whose set fills up is repeated
   // from scratch by the next tier; nothing of a failed attempt is kept.
   const uint32_t tier_log[2] = {env_u32("MCAAT_DLS_LOG2CAP", 11, 6, 16), env_u32("MCAAT_DLS_LOG2CAP2", 16, 6, 16)};
-  const uint32_t tier_threads[2] = {(uint32_t)g->sm_count * env_u32("MCAAT_DLS_BLOCKS_PER_SM", 8, 1, 16) * block,
+  const uint32_t stream_mode = env_u32("MCAAT_DLS_STREAM", 1, 0, 2);  // 0 off, 1 from 16 384 searches on, 2 always
+  const bool streaming = env_u32("MCAAT_DLS_BALL", 1, 0, 1) != 0 && (stream_mode == 2 || (stream_mode == 1 && n >= 16384));
+  // (beside the ball tier the first tier runs with half its threads: the long searches are the critical path)
+  const uint32_t tier_threads[2] = {(uint32_t)g->sm_count * env_u32("MCAAT_DLS_BLOCKS_PER_SM", streaming ? 4 : 8, 1, 16) * block,
                                     (uint32_t)g->sm_count * env_u32("MCAAT_DLS_THREADS2_PER_SM", 64, 1, 256)};
   DlsArena A;
   A.stk_cap = (uint32_t)(4 * limit + 8) | 1u;  // odd: per-thread stacks in shared memory spread over the banks
@@ -272,10 +309,8 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
   DevBuf per_search;
   if (verbose) MG_TRY(per_search.alloc(n * 4 * 5));
   const bool use_ball = env_u32("MCAAT_DLS_BALL", 1, 0, 1) != 0;
-  for (int tier = 0; tier < 2; ++tier) {
-    const uint64_t n_work = tier == 0 ? n : todo.size();
-    if (n_work == 0 || (tier == 1 && !use_ball && tier_log[1] <= tier_log[0])) continue;
-    if (tier == 1 && use_ball) {
+  struct BallSetup { BallLayout L; uint32_t blocks, workers, stk_smem; };
+  auto ball_setup = [&](uint64_t n_work, BallSetup &B) -> int {
       // ---- long searches: one warp each on the extracted ball (arenas shared with the enumeration pipeline)
       const uint32_t workers_per_sm = env_u32("MCAAT_ENUM_WORKERS_PER_SM", 4, 1, 32);
       // the searches of this tier are bound by the latency of their ball extraction, not by any throughput: more
@@ -299,17 +334,32 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
       }
       const uint32_t dls_workers_per_sm = env_u32("MCAAT_DLS_WORKERS_PER_SM", wide ? 16 : workers_per_sm, 1, 32);
       const uint32_t want = (uint32_t)std::min<uint64_t>(n_work, (uint64_t)g->sm_count * dls_workers_per_sm);
-      const uint32_t blocks = (want + kDlsBallWarps - 1) / kDlsBallWarps, workers = blocks * kDlsBallWarps;
-      const BallLayout L = make_ball_layout(limit, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 16),
+      B.blocks = (want + kDlsBallWarps - 1) / kDlsBallWarps;
+      B.workers = B.blocks * kDlsBallWarps;
+      B.L = make_ball_layout(limit, env_u32("MCAAT_ENUM_BALL_LOG", 16, 5, 16),
                                             std::min<uint32_t>(ball_smem_per_worker(g, workers_per_sm, kDlsBallWarps),
                                                                env_u32("MCAAT_ENUM_SMEM_PER_WORKER", 1u << 20, 2048, 1u << 20)));
       const uint32_t stk_entries = (uint32_t)(4 * limit + 8);
-      const uint32_t stk_smem = (size_t)stk_entries * 4 * kDlsBallWarps <= 48 * 1024 ? stk_entries : 0;  // else: in the arena
-      if ((size_t)stk_entries * 4 > (size_t)L.cyc_cap * 4) {
+      B.stk_smem = (size_t)stk_entries * 4 * kDlsBallWarps <= 48 * 1024 ? stk_entries : 0;  // else: in the arena
+      if ((size_t)stk_entries * 4 > (size_t)B.L.cyc_cap * 4) {
         set_error("mg_dls: limit %d: DFS stack does not fit the worker arena (internal)", limit);
         return MG_EINTERNAL;
       }
-      MG_TRY(ensure_ball_arena(g, workers, L));
+      MG_TRY(ensure_ball_arena(g, B.workers, B.L));
+      return MG_OK;
+  };
+  // The first tier pushes every search that outgrows its set to a list the ball tier consumes while the first tier is
+  // still running (second stream): the few thousand long searches no longer start after the last short one has ended.
+  bool ball_done = false;
+  for (int tier = 0; tier < 2; ++tier) {
+    const uint64_t n_work = tier == 0 ? n : todo.size();
+    if (n_work == 0 || (tier == 1 && !use_ball && tier_log[1] <= tier_log[0])) continue;
+    if (tier == 1 && use_ball) {
+      if (ball_done) continue;  // ran beside the first tier: what is left in `todo` goes to the bitmap tier
+      BallSetup B;
+      MG_TRY(ball_setup(n_work, B));
+      const BallLayout &L = B.L;
+      const uint32_t blocks = B.blocks, workers = B.workers, stk_smem = B.stk_smem;
       MG_TRY(todo_b.alloc(todo.size() * 4));
       MG_CUDA(cudaMemcpyAsync(todo_b.p, todo.data(), todo.size() * 4, cudaMemcpyHostToDevice, s));
       MG_CUDA(cudaMemsetAsync(ctr.p, 0, 4, s));
@@ -317,7 +367,7 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
         TimedScope ts(g, T_DLS, 0);
         MG_LAUNCH(k_dls_ball, blocks, 32 * kDlsBallWarps, (size_t)stk_smem * 4 * kDlsBallWarps, s, g->adj.as<uint64_t>(), ids_dev,
                   todo_b.as<uint32_t>(), (uint32_t)n_work, limit, g->enum_arena.as<uint8_t>(), L, result.as<int8_t>(),
-                  ctr.as<uint32_t>(), exp_dev, verbose ? per_search.as<uint32_t>() : nullptr, stk_smem, (uint32_t)n);
+                  ctr.as<uint32_t>(), exp_dev, verbose ? per_search.as<uint32_t>() : nullptr, stk_smem, (uint32_t)n, nullptr);
       }
       if (verbose) {
         std::vector<uint32_t> d(n_work * 4);
@@ -381,11 +431,43 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
     A.stk_node = sn.as<uint32_t>();
     A.stk_depth = sd.as<uint16_t>();
     A.stk_adj = sa.as<uint64_t>();
-    {
+    if (tier == 0 && streaming) {
+      BallSetup B;
+      MG_TRY(ball_setup(n, B));
+      DevBuf push;
+      MG_TRY(push.alloc(n * 4));
+      MG_CUDA(cudaMemsetAsync(push.p, 0xFF, n * 4, s));
+      MG_CUDA(cudaMemsetAsync(ctr.as<uint32_t>() + 4, 0, 16, s));  // [4] pushed so far, [5] first tier done, [6] ball tier's queue, [7] blocks done
+      if (!g->stream2) MG_CUDA(cudaStreamCreateWithFlags(&g->stream2, cudaStreamNonBlocking));
+      cudaEvent_t ev = nullptr;
+      MG_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+      cudaEventRecord(ev, s);
+      cudaStreamWaitEvent(g->stream2, ev, 0);  // the buffers above are ready
+      {
+        TimedScope ts(g, T_DLS, n);
+        // The first tier goes first: it never waits for anything, so whatever holds the second launch back (a kernel
+        // launched for the first time may make the driver wait for the device to drain) only delays the ball tier.
+        MG_LAUNCH(k_dls, blocks, tblock, smem, s, g->adj.as<uint64_t>(), ids_dev, nullptr, (uint32_t)n_work, limit, A,
+                  result.as<int8_t>(), ctr.as<uint32_t>(), exp_dev, verbose ? per_search.as<uint32_t>() : nullptr, 0,
+                  push.as<uint32_t>(), ctr.as<uint32_t>() + 4);
+        MG_LAUNCH(k_dls_ball, B.blocks, 32 * kDlsBallWarps, (size_t)B.stk_smem * 4 * kDlsBallWarps, g->stream2, g->adj.as<uint64_t>(),
+                  ids_dev, push.as<uint32_t>(), 0u, limit, g->enum_arena.as<uint8_t>(), B.L, result.as<int8_t>(),
+                  ctr.as<uint32_t>() + 6, exp_dev, nullptr, B.stk_smem, (uint32_t)n, ctr.as<uint32_t>() + 4);
+        cudaEventRecord(ev, g->stream2);
+        cudaStreamWaitEvent(s, ev, 0);
+      }
+      cudaError_t e = cudaStreamSynchronize(s);
+      cudaEventDestroy(ev);
+      if (e != cudaSuccess) {
+        set_error("mg_dls: %s", cudaGetErrorString(e));
+        return MG_ECUDA;
+      }
+      ball_done = true;
+    } else {
       TimedScope ts(g, T_DLS, tier == 0 ? n : 0);
       MG_LAUNCH(k_dls, blocks, tblock, smem, s, g->adj.as<uint64_t>(), ids_dev, tier == 0 ? nullptr : todo_b.as<uint32_t>(),
                 (uint32_t)n_work, limit, A, result.as<int8_t>(), ctr.as<uint32_t>(), exp_dev,
-                verbose ? per_search.as<uint32_t>() : nullptr, smem ? 1 : 0);
+                verbose ? per_search.as<uint32_t>() : nullptr, smem ? 1 : 0, nullptr, nullptr);
     }
     if (verbose) {
       std::vector<uint32_t> ps(n);
