@@ -108,3 +108,24 @@ def pack_raw(raw):
 
     return dict(n=n, k=raw["k"], w=w64, last=bits(raw["last"]), tip=bits(raw["tip"]),
                 mult=np.ascontiguousarray(raw["mult"], np.uint16), f=np.ascontiguousarray(raw["f"], np.int64))
+
+
+def nav_digest_cases():
+    """golden graphs whose full navigation table (unmodified reference SDBG API over every item) is pinned by SHA-256
+    digests, tests/golden/<case>.nav.sha.json (tools/add_golden_nav.py)"""
+    import glob
+    return sorted(os.path.basename(p)[:-len(".nav.sha.json")] for p in glob.glob(os.path.join(GOLD, "*.nav.sha.json")))
+
+
+def nav_digests(od, idg, m, o, i_):
+    """the digests of tools/add_golden_nav.py for a navigation table computed here"""
+    import hashlib
+    arrs = dict(od=np.ascontiguousarray(od, np.int8), id=np.ascontiguousarray(idg, np.int8), m=np.ascontiguousarray(m, np.uint16),
+                o=np.ascontiguousarray(o, np.int64), i=np.ascontiguousarray(i_, np.int64))
+    return {k: hashlib.sha256(v.tobytes()).hexdigest() for k, v in arrs.items()}
+
+
+def nav_expected(name):
+    import json
+    with open(os.path.join(GOLD, f"{name}.nav.sha.json")) as f:
+        return json.load(f)

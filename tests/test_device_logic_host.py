@@ -53,6 +53,15 @@ def test_navigation_matches_reference_api():
     assert np.array_equal(o.astype(np.int64), z["o"]) and np.array_equal(i_.astype(np.int64), z["i"])
 
 
+@pytest.mark.parametrize("name", G.nav_digest_cases())
+def test_navigation_matches_reference_api_on_every_item_of_the_larger_graphs(name):
+    want = G.nav_expected(name)
+    od, idg, o, i_ = emu(name).navigate()
+    mult = G.load_graph_npz(name)["mult"]
+    assert od.size == want["n"]
+    assert G.nav_digests(od, idg, mult, o, i_) == want["sha256"]
+
+
 @pytest.mark.parametrize("name,thr,mn,mx,dump", G.cases(),
                          ids=lambda v: str(v) if not isinstance(v, str) or "/" not in v else "")
 def test_device_logic_matches_reference_dump(name, thr, mn, mx, dump):

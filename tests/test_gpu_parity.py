@@ -47,6 +47,15 @@ def test_navigation_matches_reference_api():
     assert gpu.launch_count() > before
 
 
+@pytest.mark.parametrize("name", G.nav_digest_cases())
+def test_navigation_matches_reference_api_on_every_item_of_the_larger_graphs(name):
+    """degrees, neighbour ids and multiplicity of every item against digests of the unmodified reference API's answers"""
+    want = G.nav_expected(name)
+    od, idg, o, i_, m = DeviceGraph(packed(name)).navigate()
+    assert od.size == want["n"]
+    assert G.nav_digests(od, idg, m, o, i_) == want["sha256"]
+
+
 @pytest.mark.parametrize("name,thr,mn,mx,dump", G.cases(),
                          ids=lambda v: str(v) if not isinstance(v, str) or "/" not in v else "")
 def test_cuda_matches_reference_dump(name, thr, mn, mx, dump):

@@ -33,6 +33,16 @@ def test_oracle_navigation_matches_reference_api():
     assert np.array_equal(g.raw()["mult"], z["m"])
 
 
+@pytest.mark.parametrize("name", G.nav_digest_cases())
+def test_oracle_navigation_matches_reference_api_on_every_item_of_the_larger_graphs(name):
+    """the exhaustive table for the other golden graphs, pinned by digests of the reference's answers"""
+    want = G.nav_expected(name)
+    g = graph(name)
+    od, idg, o, i_ = g.nav_table()
+    assert od.size == want["n"]
+    assert G.nav_digests(od, idg, g.raw()["mult"], o, i_) == want["sha256"]
+
+
 @pytest.mark.parametrize("name,key,params,k", G.region_cases(), ids=lambda v: str(v) if isinstance(v, (str, int)) else "")
 def test_oracle_keep_regions_matches_reference(name, key, params, k):
     """orc_keep_regions against the UNMODIFIED keep_crispr_regions_extended_by_k
