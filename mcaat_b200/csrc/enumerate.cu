@@ -393,7 +393,6 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       __syncwarp();
       uint32_t front = 0;
       if (lane == 0) {
-        recs[t] = rec;
         __threadfence();
         if (rec.n_nodes) atomicAdd(&ctl->mark_epoch, 1u);  // after the fence: the marks are visible first
         atomicExch(&done[t], 1u);
@@ -401,13 +400,20 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
         front = ld_vol(&ctl->commit_idx);
       }
       if (__shfl_sync(kFull, front, 0) == t) sweep_front(&ctl->commit_idx, done, go, t + 1, n_end, lane);
+      if (lane == 0) recs[t] = rec;  // read by the host after the kernel: off the hand-over path
     };
     // does the search rest on a node that has been marked since its ball was built? (warp-cooperative)
     auto stale = [&](uint32_t n_keys) {
       int conflict = 0;
-      for (uint32_t j = 1 + lane; j < n_keys; j += 32) {
-        uint32_t k = A.nodes[j].key;
-        if (k != s && visited_live(visited, k)) conflict = 1;
+      for (uint32_t j0 = 1 + lane; j0 < n_keys && !conflict; j0 += 128) {  // four nodes per lane: keys, then visited words, in flight
+        uint32_t k[4], w[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) k[q] = j0 + 32u * q < n_keys ? A.nodes[j0 + 32u * q].key : s;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) w[q] = k[q] != s ? ld_cg32(&visited[k[q] >> 5]) : 0u;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (k[q] != s && ((w[q] >> (k[q] & 31)) & 1u)) conflict = 1;
       }
       return __any_sync(kFull, conflict) != 0;
     };
@@ -525,7 +531,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, 1) k_enum_pipeline(GraphV
       const uint32_t n_nodes = __shfl_sync(kFull, R.n_nodes, 0), n_cycles = __shfl_sync(kFull, R.n_cycles, 0);
       uint32_t node_base = 0, cyc_base = 0;
       int full = 0;
-      if (lane == 0) {
+      if (lane == 0 && (n_nodes | n_cycles)) {  // (most commits of a dependent chain carry no cycle: no round trip then)
         node_base = atomicAdd(&ctl->pool_nodes, n_nodes);
         cyc_base = atomicAdd(&ctl->pool_cycles, n_cycles);
         if ((uint64_t)node_base + n_nodes > pool_nodes_cap || (uint64_t)cyc_base + n_cycles > pool_len_cap) {
