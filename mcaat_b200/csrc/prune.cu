@@ -389,7 +389,7 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     if (n_work) MG_TRY(bitmap_to_ids(branch.as<uint32_t>(), n, branch_ids, &n_branch, s));
     if (n_work) {
       int *unresolved = (int *)(c + 7), *capped = (int *)(c + 7) + 1;
-      {  // chain nodes -> terminals through 1-in-64 splitters
+      {  // chain nodes -> terminals through splitters (one chain node in 128)
         DevBuf split, split_ids, sterm;
         MG_TRY(split.alloc(bm_bytes));
         MG_CUDA(cudaMemsetAsync(c + 7, 0, 8, s));

@@ -156,7 +156,7 @@ MG_HD bool chain_jump_item(const PeelView &P, uint32_t v) {
 //   a. every splitter walks forward until it meets a terminal, another splitter or an item another
 //      walk has claimed, claiming the items it passes (owner[]) — every chain node is claimed at most
 //      once, so this is O(n) in total, in walks of ~64 hops;
-//   b. pointer jumping runs over the splitters only (1/64 of the nodes);
+//   b. pointer jumping runs over the splitters only (1/128 of the nodes);
 //   c. every other chain node takes the terminal of its owner, or — near the head of a chain, where no
 //      walk passed — walks to the first item that knows it.
 // An item that leads into a cycle of chain nodes ends with a chain node as its pointer, which
@@ -248,7 +248,7 @@ MG_HD bool chain_resolve_item(const PeelView &P, uint32_t v) {
   uint32_t p = (uint32_t)ev;
   // Brent's cycle detection: `mark` is the item the walk stood on 2^j hops after v.  A walk that comes back to
   // it runs round a cycle of chain nodes with neither splitter nor owner (the closed loop of a tandem repeat
-  // whose entry and exit were filtered out has ~50 nodes, so about half of them hold no 1-in-64 splitter):
+  // whose entry and exit were filtered out has ~50 nodes, so about half of them hold no splitter):
   // v is unresolvable and ptr[v] stays its successor, a chain node — what terminal_of() tests.  Nobody
   // writes a pointer on such a component, so the walk is deterministic: <= 3 x (tail + cycle) hops.
   uint32_t mark = v, since = 0, power = 1;
