@@ -155,7 +155,7 @@ MG_HD bool chain_jump_item(const PeelView &P, uint32_t v) {
 // node in 128 (by hash; PeelView::split_shift) is a SPLITTER:
 //   a. every splitter walks forward until it meets a terminal, another splitter or an item another
 //      walk has claimed, claiming the items it passes (owner[]) — every chain node is claimed at most
-//      once, so this is O(n) in total, in walks of ~64 hops;
+//      once, so this is O(n) in total, in walks of ~128 hops;
 //   b. pointer jumping runs over the splitters only (1/128 of the nodes);
 //   c. every other chain node takes the terminal of its owner, or — near the head of a chain, where no
 //      walk passed — walks to the first item that knows it.
