@@ -434,9 +434,11 @@ int run_dls(mg_graph *g, const uint32_t *ids_dev, uint64_t n, int limit, uint8_t
     if (tier == 0 && streaming) {
       BallSetup B;
       MG_TRY(ball_setup(n, B));
+      // every worker of the ball tier claims one position past the last entry before it leaves: n + workers positions
       DevBuf push;
-      MG_TRY(push.alloc(n * 4));
-      MG_CUDA(cudaMemsetAsync(push.p, 0xFF, n * 4, s));
+      const size_t push_entries = (size_t)n + B.workers + 32;
+      MG_TRY(push.alloc(push_entries * 4));
+      MG_CUDA(cudaMemsetAsync(push.p, 0xFF, push_entries * 4, s));
       MG_CUDA(cudaMemsetAsync(ctr.as<uint32_t>() + 4, 0, 16, s));  // [4] pushed so far, [5] first tier done, [6] ball tier's queue, [7] blocks done
       if (!g->stream2) MG_CUDA(cudaStreamCreateWithFlags(&g->stream2, cudaStreamNonBlocking));
       cudaEvent_t ev = nullptr;

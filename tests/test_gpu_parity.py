@@ -103,7 +103,8 @@ def test_small_arenas_take_the_exact_fallback_tiers(monkeypatch):
 @pytest.mark.parametrize("switches", [{"MCAAT_ENUM_CHAINS_GLOBAL": "1"}, {"MCAAT_ENUM_SMEM_PER_WORKER": "2048"},
                                       {"MCAAT_ENUM_INORDER": "1"}, {"MCAAT_ENUM_WORKERS_PER_SM": "1"},
                                       {"MCAAT_ENUM_WORKERS_PER_SM": "8", "MCAAT_DLS_WORKERS_PER_SM": "3", "MCAAT_DLS_LOG2CAP": "6"},
-                                      {"MCAAT_DLS_STREAM": "2", "MCAAT_DLS_LOG2CAP": "6"}, {"MCAAT_DLS_STREAM": "0", "MCAAT_DLS_LOG2CAP": "6"}],
+                                      {"MCAAT_DLS_STREAM": "2", "MCAAT_DLS_LOG2CAP": "6"}, {"MCAAT_DLS_STREAM": "0", "MCAAT_DLS_LOG2CAP": "6"},
+                                      {"MCAAT_DLS_STREAM": "2", "MCAAT_DLS_LOG2CAP": "6", "MCAAT_ENUM_BALL_LOG": "7"}],
                          ids=lambda d: "+".join(k[6:].lower() for k in d))
 @pytest.mark.parametrize("name,thr", [("repeatrich", 5), ("biallelic", 20), ("strain", 10)])
 def test_search_variants_agree_with_the_reference(monkeypatch, switches, name, thr):
@@ -112,7 +113,8 @@ def test_search_variants_agree_with_the_reference(monkeypatch, switches, name, t
     2 KB share, which moves the path levels to the arena as well); every commit in ticket order instead of independent
     tickets committing ahead of their turn; few workers; more enumeration workers per SM than the default with fewer
     admission-search workers, every admission search past 32 nodes on the ball tier; the ball tier fed by the first
-    tier while it runs (forced: the goldens have too few candidates for the default to choose it) and after it"""
+    tier while it runs (forced: the goldens have too few candidates for the default to choose it) and after it; the same with
+    64-node arenas, so that balls overflow the ball tier (bitmap tier) and the enumeration's arenas (hash-map search)"""
     for k, v in switches.items():
         monkeypatch.setenv(k, v)
     _, _, mn, mx, dump = [c for c in G.cases() if c[0] == name and c[1] == thr][0]
