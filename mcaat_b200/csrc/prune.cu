@@ -49,11 +49,38 @@ __global__ void k_tips(GraphView g, uint32_t *bits, unsigned long long *count) {
 // The same bitmap from the dead ends' side (search_dev.cuh): a streaming pass marks the dead ends (one block line per
 // item), their ids are compacted, and one thread per dead end evaluates IncomingEdges — dense warps, whatever the
 // share of dead ends (0.07 % of the items at C2, 2.5 % at C4).  `bits` of k_tips_of_dead_ends is zeroed by the caller.
+// 64 items per thread, on the words themselves.  A node is the run of items that ends at an item with the last-or-tip
+// bit (ComputeOutgoings scans downwards until it meets one, sdbg.h:296-320); whether a run holds a valid item is a
+// carry: adding (valid & ~end) + ~end lets a valid bit ripple upwards through the non-end positions of its run and
+// deposits it at the run's end position, where both addends are zero, so it goes no further.  A run that began in the
+// previous word brings its carry along (runs are a few items long; a word without any end bit takes the literal path).
 __global__ void k_dead_ends(GraphView g, uint32_t *dead) {
-  const uint64_t n32 = (g.n + 31) & ~31ull;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
-    unsigned m = __ballot_sync(0xffffffffu, i < g.n && is_dead_end(g, (uint32_t)i));
-    if ((threadIdx.x & 31) == 0) dead[i >> 5] = m;
+  const uint64_t n_words = (g.n + 63) / 64, stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += stride) {
+    const FBlock *fb = &g.fb[w >> 2];
+    const int j = (int)(w & 3);
+    const uint64_t E = ld_ro(&fb->lt[j]), La = ld_ro(&fb->last[j]), V = ~fb->inv[j];
+    uint64_t cin = 0, d = 0;
+    bool literal = false;
+    if (w > 0) {
+      const FBlock *pb = &g.fb[(w - 1) >> 2];
+      const int pj = (int)((w - 1) & 3);
+      const uint64_t Ep = ld_ro(&pb->lt[pj]), Vp = ~pb->inv[pj];
+      if (Ep == 0) literal = true;
+      else cin = ((Vp >> (63 - __clzll((long long)Ep))) >> 1) != 0;  // valid items above the last end bit of that word
+    }
+    if (!literal) {
+      const uint64_t nE = ~E, Z = (V & nE) + nE + cin;
+      d = La & ~((Z | V) & E);
+    } else {
+      for (int b = 0; b < 64; ++b) {
+        const uint64_t i = w * 64 + b;
+        if (i < g.n && is_dead_end(g, (uint32_t)i)) d |= 1ull << b;
+      }
+    }
+    if (w == n_words - 1 && (g.n & 63)) d &= (1ull << (g.n & 63)) - 1;
+    dead[2 * w] = (uint32_t)d;
+    dead[2 * w + 1] = (uint32_t)(d >> 32);  // (the bitmaps carry four spare words)
   }
 }
 __global__ void k_tips_of_dead_ends(GraphView g, const uint32_t *ids, uint32_t n_ids, uint32_t *bits, unsigned long long *count) {
@@ -76,17 +103,33 @@ __global__ void k_tips_of_dead_ends(GraphView g, const uint32_t *ids, uint32_t n
 }
 // InvalidateMultiplicityOneNodes: every item with multiplicity <= 1 becomes invalid; the count
 // includes items that were invalid already, like the reference's counter.
+// (eight items = one 16-byte load per thread and round: with two bytes per thread in flight the pass ran at a tenth of the
+//  HBM rate; four lanes put their bits together into the 32-bit word of the block line that they own)
 __global__ void k_mult1(GraphView g, unsigned long long *count) {
   __shared__ unsigned sh[1];
   BlockCounters<1> bc(sh);
-  const uint64_t n32 = (g.n + 31) & ~31ull;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
-    bool low = i < g.n && g.mult[i] <= 1;
-    unsigned m = __ballot_sync(0xffffffffu, low);
-    if ((threadIdx.x & 31) == 0 && m) {
+  const uint64_t n_groups = ((g.n + 31) / 32) * 4, stride = (uint64_t)gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  for (uint64_t q0 = (uint64_t)blockIdx.x * blockDim.x; q0 < n_groups; q0 += stride) {  // (whole warps: shuffles below)
+    const uint64_t q = q0 + threadIdx.x, base = q * 8;
+    unsigned bits = 0;
+    if (base + 8 <= g.n) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4 *>(g.mult + base));
+      const unsigned m[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) bits |= ((m[k] & 0xFFFFu) <= 1u ? 1u : 0u) << (2 * k) | ((m[k] >> 16) <= 1u ? 1u : 0u) << (2 * k + 1);
+    } else {
+      for (int k = 0; k < 8; ++k)
+        if (base + k < g.n && g.mult[base + k] <= 1) bits |= 1u << k;
+    }
+    unsigned w = bits << (8 * (lane & 3));
+    w |= __shfl_xor_sync(0xffffffffu, w, 1);
+    w |= __shfl_xor_sync(0xffffffffu, w, 2);
+    if ((lane & 3) == 0 && w) {
+      const uint64_t i = base;  // first item of the 32-bit word
       uint32_t *w32 = (uint32_t *)&g.fb[i >> 8].inv[(i >> 6) & 3] + ((i >> 5) & 1);
-      *w32 |= m;  // this warp owns the 32-bit word and nobody else writes invalid bits in this phase
-      bc.add(0, (unsigned)__popc(m));
+      *w32 |= w;  // these four lanes own the word and nobody else writes invalid bits in this phase
+      bc.add(0, (unsigned)__popc(w));
     }
   }
   unsigned long long *dst[1] = {count};
