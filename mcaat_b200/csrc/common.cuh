@@ -152,7 +152,7 @@ struct mg_graph {
   mg::GraphView view{};  // pointers below
   mg::DevBuf wb, fb, mult, hints, inv0;
   mg::DevBuf adj;        // navigation cache (built by mg_prune)
-  mg::DevBuf merge;      // n bits: last item of every node that a valid non-first edge (label 5..8) leads to — the
+  mg::DevBuf merge;      // n bits: the valid items of every node that a valid non-first edge (label 5..8) leads to — the
                          // nodes that can have in-degree >= 2; written with the cache, valid while `pruned`
   mg::DevBuf visited;    // n bits, uint32 words
   mg::DevBuf enum_arena; // per-worker search arenas of the enumeration pipeline (grow-only)

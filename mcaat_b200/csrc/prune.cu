@@ -295,9 +295,10 @@ __global__ void k_cpeel(PeelView P, const uint32_t *work, uint32_t n_work, uint3
 }
 // step 4: invalid bits of the removed items, final navigation cache, "After pruning" statistics
 // (:443-452): valid count and tips
-// `merge` (zeroed by the caller): bit Forward(e) for every item e that stays valid and carries a non-first label
-// (5..8, sdbg_def.h:11-29) — the nodes with a second valid incoming edge, which is all ChunkStartNodes' in-degree test
-// (:398) can accept; k_candidates_merge evaluates Backward + the group scan for those nodes only.
+// `merge` (zeroed by the caller): for every item e that stays valid and carries a non-first label (5..8,
+// sdbg_def.h:11-29), the bits of the valid items of the node Forward(e) — the items with a second valid incoming edge,
+// which is all ChunkStartNodes' in-degree test (:398) can accept; k_candidates_merge evaluates Backward + the group
+// scan for those items only.
 __global__ void k_peel_final(GraphView g, PeelView P, uint32_t *merge, unsigned long long *n_peeled, unsigned long long *n_valid,
                              unsigned long long *n_tips) {
   __shared__ unsigned sh[3];
@@ -310,9 +311,13 @@ __global__ void k_peel_final(GraphView g, PeelView P, uint32_t *merge, unsigned 
       a = peel_final_item(g, P, (uint32_t)i, peeled);
       valid = !peeled && !get_inv(g, (uint32_t)i);
       tip = valid && (a >> 32) == 0;
-      if (valid && get_w(g, (uint32_t)i) > 4) {
-        uint32_t nx = a ? (uint32_t)a : forward(g, (uint32_t)i);  // the cache keeps Forward(e) of every valid item
-        if (nx < g.n) atomicOr(&merge[nx >> 5], 1u << (nx & 31));
+      if (valid && a && get_w(g, (uint32_t)i) > 4) {
+        // the cache entry names the node's last item nx and its valid items nx - j (mask bit j): one word, or two
+        // when the node straddles a 32-item boundary
+        const uint32_t nx = (uint32_t)a, pos = nx & 31u;
+        const uint64_t run = (uint64_t)__brev((uint32_t)(a >> 32) & 0xFFu) << (pos + 1u);  // bit j of the mask -> 32 + pos - j
+        if ((uint32_t)(run >> 32)) atomicOr(&merge[nx >> 5], (uint32_t)(run >> 32));
+        if ((uint32_t)run && nx >= 32u) atomicOr(&merge[(nx >> 5) - 1u], (uint32_t)run);
       }
     }
     unsigned mp = __ballot_sync(0xffffffffu, peeled), mv = __ballot_sync(0xffffffffu, valid),

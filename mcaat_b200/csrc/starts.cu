@@ -19,22 +19,21 @@ __global__ void k_candidates(GraphView g, uint64_t thr, uint32_t *bits) {
 }
 
 // The same predicate after mg_prune: in-degree >= 2 needs a valid non-first incoming edge, and k_peel_final has marked
-// the nodes that have one (`merge`, bit at the node's last item).  Everything else is decided by the item's own
-// block line (validity, `last` bits) and its multiplicity: a streaming pass instead of rank + select per item.
+// the valid items of the nodes that have one (`merge`).  64 items per thread: validity and mark are two words; the
+// literal predicate (multiplicity, Backward, self-loop test) runs for the marked valid items only.
 __global__ void k_candidates_merge(GraphView g, uint64_t thr, const uint32_t *__restrict__ merge, uint32_t *bits) {
-  const uint64_t n32 = (g.n + 31) & ~31ull;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
-    bool c = false;
-    if (i < g.n) {
-      const uint32_t v = (uint32_t)i;
-      if (!get_inv(g, v) && (uint64_t)get_mult(g, v) > thr) {
-        uint32_t b = v;  // last item of v's node: a valid item is an edge of a full-length node, tips sort before the group
-        while (b + 1 < g.n && !get_lt(g, b)) ++b;
-        if (bm_get(merge, b)) c = is_candidate(g, v, thr);
-      }
+  const uint64_t n_words = (g.n + 63) / 64, stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += stride) {
+    const uint64_t inv = g.fb[w >> 2].inv[w & 3];
+    uint64_t todo = ~inv & ((uint64_t)merge[2 * w] | ((uint64_t)merge[2 * w + 1] << 32)), c = 0;
+    if (w == n_words - 1 && (g.n & 63)) todo &= (1ull << (g.n & 63)) - 1;
+    while (todo) {
+      const int b = __ffsll((long long)todo) - 1;
+      todo &= todo - 1;
+      if (is_candidate(g, (uint32_t)(w * 64 + b), thr)) c |= 1ull << b;
     }
-    unsigned m = __ballot_sync(0xffffffffu, c);
-    if ((threadIdx.x & 31) == 0) bits[i >> 5] = m;
+    bits[2 * w] = (uint32_t)c;
+    bits[2 * w + 1] = (uint32_t)(c >> 32);  // (the bitmaps carry four spare words)
   }
 }
 
