@@ -411,6 +411,10 @@ MG_HD uint64_t peel_final_item(const GraphView &g, const PeelView &P, uint32_t v
   if (is_peeled(P, v)) { peeled = true; return 0; }
   uint64_t a = P.adj[v];
   uint32_t mask = (uint32_t)(a >> 32) & 0xFFu, next = (uint32_t)a, keep = 0;
+  // a node with ONE out-neighbour was classified a chain node: it and that neighbour end in the same terminal (or on
+  // the same unresolvable cycle), so the neighbour stays exactly when the node does — no second look-up for four items
+  // in five
+  if ((mask & (mask - 1u)) == 0) return a;
   for (int i = 0; i < 8; ++i)
     if (((mask >> i) & 1) && !is_peeled(P, next - i)) keep |= 1u << i;
   return (uint64_t)next | ((uint64_t)keep << 32);
