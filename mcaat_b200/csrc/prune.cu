@@ -137,7 +137,7 @@ __global__ void k_mult1(GraphView g, unsigned long long *count) {
 }
 // ---- RecursiveReduction by chain contraction (search_dev.cuh, "peel") -------------------------
 // step 1: navigation cache on the post-filter graph, chain / seed bitmaps, chain pointers
-__global__ void k_chain_init(GraphView g, PeelView P, uint32_t *branch, unsigned long long *n_pairs) {
+__global__ void k_chain_init(GraphView g, PeelView P, uint32_t *branch, uint32_t *split, unsigned long long *n_pairs) {
   __shared__ unsigned sh[1];
   BlockCounters<1> bc(sh);
   const uint64_t n32 = (g.n + 31) & ~31ull;
@@ -147,12 +147,14 @@ __global__ void k_chain_init(GraphView g, PeelView P, uint32_t *branch, unsigned
     if (i < g.n) deg = chain_init_item(g, P, (uint32_t)i, is_chain, is_seed);
     unsigned mc = __ballot_sync(0xffffffffu, is_chain), ms = __ballot_sync(0xffffffffu, is_seed);
     unsigned mb = __ballot_sync(0xffffffffu, deg >= 2);  // branch nodes: all that steps 2b and 3a ever look at
+    unsigned msp = __ballot_sync(0xffffffffu, is_chain && is_splitter_id(P, (uint32_t)i));  // the splitters of step 2
     unsigned pairs = deg >= 2 ? (unsigned)deg : 0u;
     for (int d = 16; d; d >>= 1) pairs += __shfl_down_sync(0xffffffffu, pairs, d);
     if ((threadIdx.x & 31) == 0) {
       P.chain[i >> 5] = mc;
       P.tpeeled[i >> 5] = ms;
       branch[i >> 5] = mb;
+      split[i >> 5] = msp;
       bc.add(0, pairs);
     }
   }
@@ -163,14 +165,6 @@ __global__ void k_chain_init(GraphView g, PeelView P, uint32_t *branch, unsigned
 // (the per-item passes are grid-stride loops; the light ones — split_mark, relink — run on a fixed grid, because with one
 //  thread per item the 4 M blocks of a 10^9-item graph cost more in block scheduling than the few bytes each of them
 //  moves; the ones that walk or insert — chain_resolve, dep_register — measured faster with one thread per item)
-__global__ void k_split_mark(uint64_t n, PeelView P, uint32_t *split) {
-  const uint64_t n32 = (n + 31) & ~31ull;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (uint64_t)gridDim.x * blockDim.x) {
-    bool sp = i < n && bm_get(P.chain, (uint32_t)i) && is_splitter_id(P, (uint32_t)i);
-    unsigned m = __ballot_sync(0xffffffffu, sp);
-    if ((threadIdx.x & 31) == 0) split[i >> 5] = m;
-  }
-}
 __global__ void k_split_walk(PeelView P, uint32_t n_ids, int *capped) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n_ids && !split_walk_item(P, i)) *capped = 1;
@@ -424,11 +418,12 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
       const int k = e && *e ? atoi(e) : 7;
       P.split_shift = 32u - (uint32_t)(k < 2 ? 2 : k > 12 ? 12 : k);
     }
-    DevBuf branch, branch_ids;
+    DevBuf branch, branch_ids, split;
     MG_TRY(branch.alloc(bm_bytes));
+    MG_TRY(split.alloc(bm_bytes));
     {
       TimedScope ts(g, T_ADJ, n);
-      MG_LAUNCH(k_chain_init, stream_grid(g, n, 256), 256, 0, s, v, P, branch.as<uint32_t>(), c + 5);
+      MG_LAUNCH(k_chain_init, stream_grid(g, n, 256), 256, 0, s, v, P, branch.as<uint32_t>(), split.as<uint32_t>(), c + 5);
     }
     uint64_t n_work = 0;
     MG_TRY(bitmap_to_ids(tpeeled.as<uint32_t>(), n, work, &n_work, s));  // seeds
@@ -438,10 +433,8 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
     if (n_work) {
       int *unresolved = (int *)(c + 7), *capped = (int *)(c + 7) + 1;
       {  // chain nodes -> terminals through splitters (one chain node in 128)
-        DevBuf split, split_ids, sterm;
-        MG_TRY(split.alloc(bm_bytes));
-        MG_CUDA(cudaMemsetAsync(c + 7, 0, 8, s));
-        MG_LAUNCH(k_split_mark, stream_grid(g, n, 256), 256, 0, s, n, P, split.as<uint32_t>());
+        DevBuf split_ids, sterm;
+        MG_CUDA(cudaMemsetAsync(c + 7, 0, 8, s));  // (the splitters were marked by the classification pass)
         uint64_t n_split = 0;
         MG_TRY(bitmap_to_ids(split.as<uint32_t>(), n, split_ids, &n_split, s));
         if (n_split) {
