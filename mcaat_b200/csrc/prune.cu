@@ -515,8 +515,14 @@ int run_prune(mg_graph *g, mg_prune_stats *st) {
             fprintf(stderr, "[peel] reclass round %d: %llu unary branch nodes, %llu new seeds\n", round, hc[0], hc[1]);
           if (hc[0] + hc[1] < 64) break;
         }
-        MG_LAUNCH(k_relink_final, stream_grid(g, n, 256), 256, 0, s, n, P);
-        P.recl = nullptr;
+        // Pointers that name a re-classified node as their terminal are followed through it by terminal_of in the passes
+        // below as well (one hop per round of step 2b at most, five at most).  Since the final pass looks up one terminal
+        // per item instead of two, that costs less than moving every such pointer on in a pass over all items
+        // (k_relink_final, 3.2 ms at C2; MCAAT_PEEL_RELINK=1 runs it: same result).
+        if (getenv("MCAAT_PEEL_RELINK")) {
+          MG_LAUNCH(k_relink_final, stream_grid(g, n, 256), 256, 0, s, n, P);
+          P.recl = nullptr;
+        }
         MG_TRY(bitmap_to_ids(tpeeled.as<uint32_t>(), n, work, &n_work, s));  // collected tips + new seeds
       }
       unsigned long long pairs = 0;

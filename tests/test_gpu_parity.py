@@ -104,7 +104,8 @@ def test_small_arenas_take_the_exact_fallback_tiers(monkeypatch):
                                       {"MCAAT_ENUM_INORDER": "1"}, {"MCAAT_ENUM_WORKERS_PER_SM": "1"},
                                       {"MCAAT_ENUM_WORKERS_PER_SM": "8", "MCAAT_DLS_WORKERS_PER_SM": "3", "MCAAT_DLS_LOG2CAP": "6"},
                                       {"MCAAT_DLS_STREAM": "2", "MCAAT_DLS_LOG2CAP": "6"}, {"MCAAT_DLS_STREAM": "0", "MCAAT_DLS_LOG2CAP": "6"},
-                                      {"MCAAT_DLS_STREAM": "2", "MCAAT_DLS_LOG2CAP": "6", "MCAAT_ENUM_BALL_LOG": "7"}],
+                                      {"MCAAT_DLS_STREAM": "2", "MCAAT_DLS_LOG2CAP": "6", "MCAAT_ENUM_BALL_LOG": "7"},
+                                      {"MCAAT_PEEL_RELINK": "1"}],
                          ids=lambda d: "+".join(k[6:].lower() for k in d))
 @pytest.mark.parametrize("name,thr", [("repeatrich", 5), ("biallelic", 20), ("strain", 10)])
 def test_search_variants_agree_with_the_reference(monkeypatch, switches, name, thr):
@@ -114,7 +115,8 @@ def test_search_variants_agree_with_the_reference(monkeypatch, switches, name, t
     tickets committing ahead of their turn; few workers; more enumeration workers per SM than the default with fewer
     admission-search workers, every admission search past 32 nodes on the ball tier; the ball tier fed by the first
     tier while it runs (forced: the goldens have too few candidates for the default to choose it) and after it; the same with
-    64-node arenas, so that balls overflow the ball tier (bitmap tier) and the enumeration's arenas (hash-map search)"""
+    64-node arenas, so that balls overflow the ball tier (bitmap tier) and the enumeration's arenas (hash-map search);
+    the peel with its relink pass (the default leaves re-classified terminals to terminal_of)"""
     for k, v in switches.items():
         monkeypatch.setenv(k, v)
     _, _, mn, mx, dump = [c for c in G.cases() if c[0] == name and c[1] == thr][0]
