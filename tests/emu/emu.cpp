@@ -223,9 +223,13 @@ void emu_prune(Emu *e, uint64_t *stats, int reverse_order) {
       for (size_t w = 0; w < words; ++w) { chain[w] |= fresh[w]; recl[w] |= fresh[w]; tpeeled[w] |= newseed[w]; }
       if (nf + ns < 64) break;
     }
-    if (reverse_order & 1) { for (uint64_t i = n; i-- > 0;) relink_final_item(P, (uint32_t)i); }
-    else for (uint64_t i = 0; i < n; ++i) relink_final_item(P, (uint32_t)i);
-    P.recl = nullptr;
+    // as prune.cu: the later passes follow re-classified terminals themselves (terminal_of); reverse_order & 8 moves the
+    // pointers on in a pass of its own first (MCAAT_PEEL_RELINK=1)
+    if (reverse_order & 8) {
+      if (reverse_order & 1) { for (uint64_t i = n; i-- > 0;) relink_final_item(P, (uint32_t)i); }
+      else for (uint64_t i = 0; i < n; ++i) relink_final_item(P, (uint32_t)i);
+      P.recl = nullptr;
+    }
     work.clear();
     for (uint64_t i = 0; i < n; ++i)
       if (bm_get(P.tpeeled, (uint32_t)i)) work.push_back((uint32_t)i);

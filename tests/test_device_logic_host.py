@@ -141,9 +141,10 @@ def test_dls_on_the_contracted_ball_equals_the_literal_search(name, thr):
 @pytest.mark.parametrize("name", ["tiny", "strain", "repeatrich"])
 def test_peel_variants_agree(name):
     """splitter-based chain resolution (forward / reverse item order) == exhaustive pointer jumping (2, 3);
-    with and without (4..7) the re-classification of unary branch nodes"""
+    with and without (4..7) the re-classification of unary branch nodes; with the relink pass (8..11) instead of
+    following re-classified terminals where they are asked for (the default, as on the device)"""
     inv, tips = [], []
-    for mode in range(8):  # odd modes also collect the tips literally, even ones from the dead ends' side
+    for mode in range(12):  # odd modes also collect the tips literally, even ones from the dead ends' side
         g = emu(name)
         tips.append(g.prune(reverse_order=mode)["n_tips_before"])
         inv.append(g.invalid())
@@ -223,7 +224,7 @@ def test_peel_cycles_of_chain_nodes_without_splitter():
     og = O.OracleGraph.from_arrays(w[:n], last, tip, g["mult"], g["f"], g["k"])
     want = og.run(2, 27, 77)
     inv = []
-    for mode in range(8):
+    for mode in range(10):
         eg = E.EmuGraph(g)
         st = eg.prune(reverse_order=mode)
         assert st["walk_cap_hit"] == 0
